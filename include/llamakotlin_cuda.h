@@ -35,6 +35,12 @@
 extern "C" {
 #endif
 
+#if defined(__GNUC__)
+#define LK_API __attribute__((visibility("default")))
+#else
+#define LK_API
+#endif
+
 #define LK_ABI_VERSION 1
 #define LK_MAX_DIMS 4           /* GGML_MAX_DIMS, core/GGMLTypes.kt:67 */
 
@@ -93,40 +99,40 @@ typedef struct lk_tensor {
 } lk_tensor;
 
 /* ---- context ------------------------------------------------------------ */
-int32_t     lk_abi_version(void);
+LK_API int32_t     lk_abi_version(void);
 /* bytes per 32-element block (GGMLType.byteSize, core/GGMLTypes.kt:99-133); 4 for F32, 0 if unknown */
-int32_t     lk_type_block_bytes(int32_t type);
+LK_API int32_t     lk_type_block_bytes(int32_t type);
 /* calculateTensorByteSize, core/GGMLTypes.kt:1136-1190 (n/32*blockBytes for Q types) */
-int64_t     lk_tensor_nbytes(const lk_tensor *t);
-lk_status   lk_ctx_create(int32_t device, lk_ctx **out);
-lk_status   lk_ctx_destroy(lk_ctx *ctx);
+LK_API int64_t     lk_tensor_nbytes(const lk_tensor *t);
+LK_API lk_status   lk_ctx_create(int32_t device, lk_ctx **out);
+LK_API lk_status   lk_ctx_destroy(lk_ctx *ctx);
 /* GGMLBackend.synchronize(), core/GGMLBackend.kt:90-157 */
-lk_status   lk_sync(lk_ctx *ctx);
+LK_API lk_status   lk_sync(lk_ctx *ctx);
 /* message of the last non-OK status on this ctx (or a static string if ctx==NULL) */
-const char *lk_last_error(lk_ctx *ctx);
+LK_API const char *lk_last_error(lk_ctx *ctx);
 /* the ctx's cudaStream_t as an opaque pointer (interop / external timing) */
-void       *lk_ctx_stream(lk_ctx *ctx);
-int32_t     lk_ctx_device(lk_ctx *ctx);
-int32_t     lk_ctx_sm_count(lk_ctx *ctx);
+LK_API void       *lk_ctx_stream(lk_ctx *ctx);
+LK_API int32_t     lk_ctx_device(lk_ctx *ctx);
+LK_API int32_t     lk_ctx_sm_count(lk_ctx *ctx);
 /* number of kernels this ctx has launched since creation (bench: gpu_launches) */
-int64_t     lk_ctx_launch_count(lk_ctx *ctx);
+LK_API int64_t     lk_ctx_launch_count(lk_ctx *ctx);
 
 /* CUDA-event timer on the ctx stream (the stream the kernels run on). */
-lk_status   lk_timer_start(lk_ctx *ctx);
-lk_status   lk_timer_stop(lk_ctx *ctx, float *ms_out);   /* synchronises */
+LK_API lk_status   lk_timer_start(lk_ctx *ctx);
+LK_API lk_status   lk_timer_stop(lk_ctx *ctx, float *ms_out);   /* synchronises */
 
 /* ---- device buffers: GGMLBackendBuffer, core/GGMLBackend.kt:45-75 ------- */
-lk_status   lk_buf_alloc(lk_ctx *ctx, uint64_t size, lk_buf **out);      /* allocBuffer */
-lk_status   lk_buf_free(lk_buf *buf);                                    /* free */
-uint64_t    lk_buf_size(const lk_buf *buf);                              /* getSize */
-void       *lk_buf_device_ptr(lk_buf *buf);                              /* getBase */
-lk_status   lk_buf_upload(lk_buf *buf, uint64_t offset, const void *host, uint64_t n);   /* setTensor */
-lk_status   lk_buf_download(lk_buf *buf, uint64_t offset, void *host, uint64_t n);       /* getTensor */
-lk_status   lk_buf_copy(lk_buf *dst, uint64_t dst_off, lk_buf *src, uint64_t src_off, uint64_t n); /* copyTensor */
-lk_status   lk_buf_clear(lk_buf *buf, uint8_t value);                    /* clear */
+LK_API lk_status   lk_buf_alloc(lk_ctx *ctx, uint64_t size, lk_buf **out);      /* allocBuffer */
+LK_API lk_status   lk_buf_free(lk_buf *buf);                                    /* free */
+LK_API uint64_t    lk_buf_size(const lk_buf *buf);                              /* getSize */
+LK_API void       *lk_buf_device_ptr(lk_buf *buf);                              /* getBase */
+LK_API lk_status   lk_buf_upload(lk_buf *buf, uint64_t offset, const void *host, uint64_t n);   /* setTensor */
+LK_API lk_status   lk_buf_download(lk_buf *buf, uint64_t offset, void *host, uint64_t n);       /* getTensor */
+LK_API lk_status   lk_buf_copy(lk_buf *dst, uint64_t dst_off, lk_buf *src, uint64_t src_off, uint64_t n); /* copyTensor */
+LK_API lk_status   lk_buf_clear(lk_buf *buf, uint8_t value);                    /* clear */
 /* Pinned host staging memory (page-locked) for callers without their own. */
-lk_status   lk_host_alloc(lk_ctx *ctx, uint64_t size, void **out);
-lk_status   lk_host_free(lk_ctx *ctx, void *p);
+LK_API lk_status   lk_host_alloc(lk_ctx *ctx, uint64_t size, void **out);
+LK_API lk_status   lk_host_free(lk_ctx *ctx, void *p);
 
 /* ---- compute ops --------------------------------------------------------
  * Destination-based like the reference: the caller owns dst, the op fills it.
@@ -142,36 +148,36 @@ lk_status   lk_host_free(lk_ctx *ctx, void *p);
  *   N == 1 (and K % 64 == 0)  -> K1 streaming decode GEMV
  *   N >= 64, Q types           -> K2 tcgen05 prefill GEMM (FP16 operands, F32 accumulate)
  *   otherwise                  -> generic F32 kernel                          */
-lk_status   lk_compute_matmul(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, const lk_tensor *dst);
+LK_API lk_status   lk_compute_matmul(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, const lk_tensor *dst);
 /* dequantizeTensor(graphAllocator, tensor) — core/GGMLComputeOps.kt:918-964. Bit-exact. dst F32, same ne. */
-lk_status   lk_compute_dequantize(lk_ctx *ctx, const lk_tensor *src, const lk_tensor *dst);
+LK_API lk_status   lk_compute_dequantize(lk_ctx *ctx, const lk_tensor *src, const lk_tensor *dst);
 /* computeAdd / computeMul F32 same-shape paths — core/GGMLComputeOps.kt:735-759, :811-835 */
-lk_status   lk_compute_add(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, const lk_tensor *dst);
-lk_status   lk_compute_mul(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, const lk_tensor *dst);
+LK_API lk_status   lk_compute_add(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, const lk_tensor *dst);
+LK_API lk_status   lk_compute_mul(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, const lk_tensor *dst);
 /* RMS_NORM node (rmsNormOp, model/GGMLIntegration.kt:181-201; src[1]=weight, opParams[0]=eps bits).
  * The reference executor leaves it a no-op (core/GGMLComputeOps.kt:2640-2645); semantics follow
  * nativeTest core/GGMLComputeOpsTest.kt:502-521 and model/LlamaModel.kt:48-63.  weight may be NULL. */
-lk_status   lk_compute_rms_norm(lk_ctx *ctx, const lk_tensor *x, const lk_tensor *weight, float eps, const lk_tensor *dst);
+LK_API lk_status   lk_compute_rms_norm(lk_ctx *ctx, const lk_tensor *x, const lk_tensor *weight, float eps, const lk_tensor *dst);
 /* SILU node (siluOp, model/GGMLIntegration.kt:206-220): x * 1/(1+exp(-x)),
  * nativeTest core/GGMLComputeOpsTest.kt:491-499 (the executor's GELU fallback is a reference defect). */
-lk_status   lk_compute_silu(lk_ctx *ctx, const lk_tensor *x, const lk_tensor *dst);
+LK_API lk_status   lk_compute_silu(lk_ctx *ctx, const lk_tensor *x, const lk_tensor *dst);
 /* SwiGLU: silu(gate) * up in one pass — model/LlamaModel.kt:165-175 */
-lk_status   lk_compute_silu_mul(lk_ctx *ctx, const lk_tensor *gate, const lk_tensor *up, const lk_tensor *dst);
+LK_API lk_status   lk_compute_silu_mul(lk_ctx *ctx, const lk_tensor *gate, const lk_tensor *up, const lk_tensor *dst);
 /* SOFT_MAX node over ne[0] — LlamaAttention.softmax, model/LlamaAttention.kt:242-288 */
-lk_status   lk_compute_softmax(lk_ctx *ctx, const lk_tensor *x, const lk_tensor *dst);
+LK_API lk_status   lk_compute_softmax(lk_ctx *ctx, const lk_tensor *x, const lk_tensor *dst);
 
 /* ---- op-sequence capture: GGMLBackend.graphCompute, core/GGMLBackend.kt:145 --
  * Between begin and end, device-resident lk_compute_* calls are recorded, not
  * run; lk_graph_launch replays the whole sequence with one submission
  * (CUDA graph with programmatic dependent launch between GEMV nodes).        */
-lk_status   lk_capture_begin(lk_ctx *ctx);
-lk_status   lk_capture_end(lk_ctx *ctx, lk_graph **out);
-lk_status   lk_graph_launch(lk_ctx *ctx, lk_graph *g);
-lk_status   lk_graph_destroy(lk_graph *g);
+LK_API lk_status   lk_capture_begin(lk_ctx *ctx);
+LK_API lk_status   lk_capture_end(lk_ctx *ctx, lk_graph **out);
+LK_API lk_status   lk_graph_launch(lk_ctx *ctx, lk_graph *g);
+LK_API lk_status   lk_graph_destroy(lk_graph *g);
 
 /* ---- tuning knobs (bench / tests only; defaults are the product settings) -- */
-lk_status   lk_set_option(lk_ctx *ctx, const char *name, int64_t value);
-int64_t     lk_get_option(lk_ctx *ctx, const char *name);
+LK_API lk_status   lk_set_option(lk_ctx *ctx, const char *name, int64_t value);
+LK_API int64_t     lk_get_option(lk_ctx *ctx, const char *name);
 
 /* ---- multi-GPU: weight rows sharded over ranks, F32 output all-gathered ----
  * One process per GPU.  Rank 0 makes an id, the host side broadcasts it
@@ -179,19 +185,24 @@ int64_t     lk_get_option(lk_ctx *ctx, const char *name);
  * counterpart exists; layout rules are §8(e).                    */
 #define LK_COMM_ID_BYTES 128
 #define LK_IPC_HANDLE_BYTES 64
-lk_status   lk_comm_unique_id(uint8_t id_out[LK_COMM_ID_BYTES]);
-lk_status   lk_comm_init(lk_ctx *ctx, int32_t nranks, int32_t rank, const uint8_t id[LK_COMM_ID_BYTES]);
-lk_status   lk_comm_destroy(lk_ctx *ctx);
+LK_API lk_status   lk_comm_unique_id(uint8_t id_out[LK_COMM_ID_BYTES]);
+LK_API lk_status   lk_comm_init(lk_ctx *ctx, int32_t nranks, int32_t rank, const uint8_t id[LK_COMM_ID_BYTES]);
+LK_API lk_status   lk_comm_destroy(lk_ctx *ctx);
 /* in-place ncclAllGather of `count` floats per rank inside buf at off (rank r's slice at off + r*count*4) */
-lk_status   lk_allgather_f32(lk_ctx *ctx, lk_buf *buf, uint64_t off, int64_t count);
+LK_API lk_status   lk_allgather_f32(lk_ctx *ctx, lk_buf *buf, uint64_t off, int64_t count);
 /* peer-mapped buffers for the fused GEMV + all-gather (direct NVLink stores) */
-lk_status   lk_buf_ipc_export(lk_buf *buf, uint8_t handle_out[LK_IPC_HANDLE_BYTES]);
-lk_status   lk_buf_ipc_import(lk_ctx *ctx, const uint8_t handle[LK_IPC_HANDLE_BYTES], uint64_t size, lk_buf **out);
+LK_API lk_status   lk_buf_ipc_export(lk_buf *buf, uint8_t handle_out[LK_IPC_HANDLE_BYTES]);
+LK_API lk_status   lk_buf_ipc_import(lk_ctx *ctx, const uint8_t handle[LK_IPC_HANDLE_BYTES], uint64_t size, lk_buf **out);
+/* Cross-rank barrier on peer-mapped flag words (4 bytes per rank in each rank's flag buffer):
+ * publishes `epoch` to every peer after the preceding ops on the ctx stream, then waits until
+ * every peer has published it here.  epoch must increase by 1 per call (wrap-safe compare). */
+LK_API lk_status   lk_peer_barrier(lk_ctx *ctx, lk_buf *own_flags, lk_buf *const *peer_flags, int32_t npeers,
+                            int32_t rank, uint32_t epoch);
 /* Sharded computeMatMul, N == 1: this rank owns rows [row0, row0 + a_shard.ne[1]) of the
  * M_total-row weight; writes its slice of dst_full (ne=[1, M_total]) locally and, when
  * peers != NULL, into the same offsets of every peer's buffer from the GEMV epilogue,
  * then signals flags.  npeers = nranks (entry `rank` is this rank's own dst).           */
-lk_status   lk_compute_matmul_sharded(lk_ctx *ctx, const lk_tensor *a_shard, const lk_tensor *b,
+LK_API lk_status   lk_compute_matmul_sharded(lk_ctx *ctx, const lk_tensor *a_shard, const lk_tensor *b,
                                       const lk_tensor *dst_full, int64_t row0, int64_t M_total,
                                       lk_buf *const *peer_dst, int32_t npeers);
 

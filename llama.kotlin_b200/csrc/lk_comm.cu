@@ -1,0 +1,186 @@
+// lk_comm.cu — multi-GPU: weight rows sharded over ranks (one process per GPU),
+// F32 outputs gathered either by ncclAllGather (baseline) or by direct NVLink
+// peer stores from the GEMV epilogue followed by a flag barrier (fused path).
+// NCCL is bound at run time (dlopen) so the library loads without it; inside a
+// torch process the already-loaded libnccl.so.2 is the one that resolves.
+#include <dlfcn.h>
+#include <string.h>
+
+#include "lk_common.cuh"
+#include "lk_shim.h"
+
+namespace {
+typedef struct { char internal[128]; } nccl_uid;
+typedef void *nccl_comm;
+typedef int (*fn_get_uid)(nccl_uid *);
+typedef int (*fn_init_rank)(nccl_comm *, int, nccl_uid, int);
+typedef int (*fn_allgather)(const void *, void *, size_t, int, nccl_comm, cudaStream_t);
+typedef int (*fn_destroy)(nccl_comm);
+typedef const char *(*fn_errstr)(int);
+struct Nccl {
+    void *h = nullptr;
+    fn_get_uid get_uid = nullptr; fn_init_rank init_rank = nullptr; fn_allgather allgather = nullptr;
+    fn_destroy destroy = nullptr; fn_errstr errstr = nullptr;
+    bool tried = false;
+} g_nccl;
+
+bool nccl_load(std::string &why) {
+    if (g_nccl.h) return true;
+    if (g_nccl.tried) { why = "libnccl not found"; return false; }
+    g_nccl.tried = true;
+    const char *names[] = {"libnccl.so.2", "libnccl.so", nullptr};
+    for (int i = 0; names[i] && !g_nccl.h; i++) g_nccl.h = dlopen(names[i], RTLD_NOW | RTLD_GLOBAL);
+    if (!g_nccl.h) { why = std::string("dlopen(libnccl.so.2) failed: ") + dlerror(); return false; }
+    g_nccl.get_uid = (fn_get_uid)dlsym(g_nccl.h, "ncclGetUniqueId");
+    g_nccl.init_rank = (fn_init_rank)dlsym(g_nccl.h, "ncclCommInitRank");
+    g_nccl.allgather = (fn_allgather)dlsym(g_nccl.h, "ncclAllGather");
+    g_nccl.destroy = (fn_destroy)dlsym(g_nccl.h, "ncclCommDestroy");
+    g_nccl.errstr = (fn_errstr)dlsym(g_nccl.h, "ncclGetErrorString");
+    if (!g_nccl.get_uid || !g_nccl.init_rank || !g_nccl.allgather || !g_nccl.destroy) {
+        why = "libnccl is missing required symbols"; g_nccl.h = nullptr; return false;
+    }
+    return true;
+}
+lk_status nccl_fail(lk_ctx *ctx, int rc, const char *what) {
+    return lk::fail(ctx, LK_ENCCL, std::string("NCCL error in ") + what + ": " + (g_nccl.errstr ? g_nccl.errstr(rc) : "?"));
+}
+
+// One warp: publish "my slice is written" to every peer, then wait until every
+// peer has published the same epoch locally.  Runs after the GEMV on the same
+// stream, so the GEMV's peer stores are complete; the system-scope fence orders
+// them before the flag stores.  Each rank owns its GPU, so the spin is safe.
+__global__ void peer_barrier_kernel(uint32_t *own, uint32_t *const *peers, int n, int rank, uint32_t epoch) {
+    const int q = threadIdx.x;
+    __threadfence_system();
+    if (q < n) {
+        if (q != rank) {
+            volatile uint32_t *f = peers[q] + rank;
+            *f = epoch;
+        } else {
+            ((volatile uint32_t *)own)[rank] = epoch;
+        }
+    }
+    __threadfence_system();
+    if (q < n) {
+        volatile uint32_t *f = own + q;
+        while ((int32_t)(*f - epoch) < 0) {
+        }
+    }
+    __threadfence_system();
+}
+}  // namespace
+
+extern "C" {
+
+lk_status lk_comm_unique_id(uint8_t id_out[LK_COMM_ID_BYTES]) {
+    std::string why;
+    if (!nccl_load(why)) return lk::fail(nullptr, LK_ENCCL, why);
+    nccl_uid id;
+    int rc = g_nccl.get_uid(&id);
+    if (rc) return nccl_fail(nullptr, rc, "ncclGetUniqueId");
+    memcpy(id_out, id.internal, LK_COMM_ID_BYTES);
+    return LK_OK;
+}
+
+lk_status lk_comm_init(lk_ctx *ctx, int32_t nranks, int32_t rank, const uint8_t id[LK_COMM_ID_BYTES]) {
+    if (!ctx || !id || nranks < 1 || rank < 0 || rank >= nranks) return lk::fail(ctx, LK_EINVAL_ARG, "lk_comm_init: bad argument");
+    std::string why;
+    if (!nccl_load(why)) return lk::fail(ctx, LK_ENCCL, why);
+    LK_CUDA(ctx, cudaSetDevice(ctx->device));
+    nccl_uid uid;
+    memcpy(uid.internal, id, LK_COMM_ID_BYTES);
+    nccl_comm c = nullptr;
+    int rc = g_nccl.init_rank(&c, nranks, uid, rank);
+    if (rc) return nccl_fail(ctx, rc, "ncclCommInitRank");
+    ctx->comm = c; ctx->nranks = nranks; ctx->rank = rank;
+    return LK_OK;
+}
+
+lk_status lk_comm_destroy(lk_ctx *ctx) {
+    if (ctx && ctx->comm && g_nccl.destroy) { g_nccl.destroy((nccl_comm)ctx->comm); ctx->comm = nullptr; }
+    if (ctx && ctx->peer_flags) { cudaFree(ctx->peer_flags); ctx->peer_flags = nullptr; }
+    return LK_OK;
+}
+
+lk_status lk_allgather_f32(lk_ctx *ctx, lk_buf *buf, uint64_t off, int64_t count) {
+    if (!ctx || !buf) return lk::fail(ctx, LK_EINVAL_ARG, "lk_allgather_f32: NULL argument");
+    if (!ctx->comm) return lk::fail(ctx, LK_ENCCL, "lk_allgather_f32: lk_comm_init has not been called");
+    const uint64_t total = (uint64_t)count * 4 * ctx->nranks;
+    if (off > buf->size || total > buf->size - off) return lk::fail(ctx, LK_EBOUNDS, "lk_allgather_f32: range outside the buffer");
+    float *base = (float *)((uint8_t *)buf->ptr + off);
+    int rc = g_nccl.allgather(base + (int64_t)ctx->rank * count, base, (size_t)count, 7 /* ncclFloat */, (nccl_comm)ctx->comm, ctx->stream);
+    if (rc) return nccl_fail(ctx, rc, "ncclAllGather");
+    return LK_OK;
+}
+
+lk_status lk_buf_ipc_export(lk_buf *buf, uint8_t handle_out[LK_IPC_HANDLE_BYTES]) {
+    if (!buf || !handle_out) return lk::fail(nullptr, LK_EINVAL_ARG, "lk_buf_ipc_export: NULL argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == LK_IPC_HANDLE_BYTES, "IPC handle size");
+    cudaIpcMemHandle_t h;
+    LK_CUDA(buf->ctx, cudaIpcGetMemHandle(&h, buf->ptr));
+    memcpy(handle_out, &h, sizeof(h));
+    return LK_OK;
+}
+
+lk_status lk_buf_ipc_import(lk_ctx *ctx, const uint8_t handle[LK_IPC_HANDLE_BYTES], uint64_t size, lk_buf **out) {
+    if (!ctx || !handle || !out) return lk::fail(ctx, LK_EINVAL_ARG, "lk_buf_ipc_import: NULL argument");
+    LK_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof(h));
+    void *p = nullptr;
+    LK_CUDA(ctx, cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    lk_buf *b = new lk_buf();
+    b->ctx = ctx; b->ptr = p; b->size = size; b->imported = true;
+    *out = b;
+    return LK_OK;
+}
+
+lk_status lk_peer_barrier(lk_ctx *ctx, lk_buf *own_flags, lk_buf *const *peer_flags, int32_t n, int32_t rank, uint32_t epoch) {
+    if (!ctx || !own_flags || !peer_flags || n < 1 || n > 8 || rank < 0 || rank >= n)
+        return lk::fail(ctx, LK_EINVAL_ARG, "lk_peer_barrier: bad argument");
+    if (own_flags->size < 4u * (unsigned)n) return lk::fail(ctx, LK_EBOUNDS, "lk_peer_barrier: flag buffer too small");
+    if (!ctx->peer_flags) LK_CUDA(ctx, cudaMalloc((void **)&ctx->peer_flags, 8 * sizeof(void *)));
+    uint32_t *ptrs[8] = {};
+    for (int q = 0; q < n; q++) ptrs[q] = (uint32_t *)(q == rank ? own_flags->ptr : (peer_flags[q] ? peer_flags[q]->ptr : nullptr));
+    for (int q = 0; q < n; q++) if (!ptrs[q]) return lk::fail(ctx, LK_EINVAL_ARG, "lk_peer_barrier: missing peer flag buffer");
+    LK_CUDA(ctx, cudaMemcpyAsync(ctx->peer_flags, ptrs, sizeof(ptrs), cudaMemcpyHostToDevice, ctx->stream));
+    peer_barrier_kernel<<<1, 32, 0, ctx->stream>>>((uint32_t *)own_flags->ptr, (uint32_t *const *)ctx->peer_flags, n, rank, epoch);
+    LK_CUDA(ctx, cudaGetLastError());
+    ctx->launches++;
+    return LK_OK;
+}
+
+lk_status lk_compute_matmul_sharded(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, const lk_tensor *dst,
+                                    int64_t row0, int64_t M_total, lk_buf *const *peer_dst, int32_t npeers) {
+    if (!ctx || !a || !b || !dst) return lk::fail(ctx, LK_EINVAL_ARG, "lk_compute_matmul_sharded: NULL argument");
+    const int64_t Ms = a->ne[1], K = a->ne[0];
+    if (K != b->ne[1]) return lk::fail(ctx, LK_EINVAL_DIM, "Dim mismatch K: a.ne[0] != b.ne[1]");
+    if (b->ne[0] != 1 || dst->ne[0] != 1) return lk::fail(ctx, LK_EINVAL_DIM, "sharded matmul supports N == 1");
+    if (dst->ne[1] != M_total || row0 < 0 || row0 + Ms > M_total) return lk::fail(ctx, LK_EINVAL_DIM, "shard rows outside dst");
+    if (lk::block_bytes(a->type) == 0 || b->type != LK_TYPE_F32 || dst->type != LK_TYPE_F32)
+        return lk::fail(ctx, LK_EINVAL_TYPE, "sharded matmul: Q4_0/Q4_1/Q8_0 x F32 -> F32");
+    if (!a->dev_buf || !b->dev_buf || !dst->dev_buf) return lk::fail(ctx, LK_EINVAL_ARG, "sharded matmul: tensors must be device resident");
+    if (npeers < 0 || npeers > 8) return lk::fail(ctx, LK_EINVAL_ARG, "sharded matmul: at most 8 peers");
+    const int64_t abytes = lk_tensor_nbytes(a);
+    if (a->data_offset + (uint64_t)abytes > a->dev_buf->size || b->data_offset + (uint64_t)K * 4 > b->dev_buf->size ||
+        dst->data_offset + (uint64_t)M_total * 4 > dst->dev_buf->size)
+        return lk::fail(ctx, LK_EBOUNDS, "sharded matmul: tensor bytes exceed the device buffer");
+    lk::GemvPeers peers;
+    for (int q = 0; q < npeers; q++) {
+        if (!peer_dst || !peer_dst[q] || peer_dst[q] == dst->dev_buf) continue;
+        if (dst->data_offset + (uint64_t)M_total * 4 > peer_dst[q]->size) return lk::fail(ctx, LK_EBOUNDS, "peer dst too small");
+        peers.ptr[peers.n++] = (float *)((uint8_t *)peer_dst[q]->ptr + dst->data_offset);
+    }
+    lk::GemvTuning tune = ctx->tune;
+    tune.pdl = (ctx->pdl_mode == 2) || (ctx->pdl_mode == 1 && ctx->capturing);
+    float *d = (float *)((uint8_t *)dst->dev_buf->ptr + dst->data_offset);
+    cudaError_t e = lk::launch_gemv(a->type, (uint8_t *)a->dev_buf->ptr + a->data_offset, K, Ms,
+                                    (const float *)((uint8_t *)b->dev_buf->ptr + b->data_offset), d, row0, peers, tune,
+                                    ctx->sm_count, ctx->stream);
+    if (e == cudaErrorNotSupported) return lk::fail(ctx, LK_ENOTIMPL, "sharded matmul: shape not supported by the streaming GEMV");
+    if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "sharded gemv launch");
+    if (ctx->capturing) ctx->capture_launches++; else ctx->launches++;
+    return LK_OK;
+}
+
+}  // extern "C"

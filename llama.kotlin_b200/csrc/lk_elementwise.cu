@@ -1,0 +1,290 @@
+// lk_elementwise.cu — K0 block dequantisation, the generic (any-shape) matmul,
+// and the F32 ops around the matmul: RMSNorm (K3), SiLU / SiLU*up (K4),
+// softmax (K5), add / mul (R4).  All HBM-bound streaming kernels.
+//
+// Reference paths relative to
+//   /root/reference/src/nativeMain/kotlin/ai/solace/llamakotlin/
+#include "lk_common.cuh"
+#include "lk_kernels.h"
+
+namespace lk {
+
+static inline int grid_for(int64_t work_items, int threads, int max_blocks = 148 * 16) {
+    int64_t g = (work_items + threads - 1) / threads;
+    if (g < 1) g = 1;
+    if (g > max_blocks) g = max_blocks;
+    return (int)g;
+}
+
+// ---------------------------------------------------------------------------
+// K0 dequantize: y = d*q | d*(nib-8) | d*nib + m, each F32 op rounded once
+// (__fmul_rn/__fadd_rn: no FMA contraction) => bit-exact with
+// dequantizeTensor, core/GGMLComputeOps.kt:932-964.  Nibble order is the
+// reference's: element e -> (qs[e/2] >> 4*(e&1)) & 15 (core/GGMLTypes.kt:647-651).
+// Each thread produces 8 consecutive elements (two coalesced 16-byte stores);
+// the packed bytes are read with 2-byte loads (blocks are only 2-byte aligned).
+// Algorithmic bytes per element: 4 (store) + blockBytes/32 (load).
+// ---------------------------------------------------------------------------
+template <int TYPE>
+__global__ void __launch_bounds__(256) dequant_kernel(const uint8_t *__restrict__ src, int64_t n,
+                                                      float *__restrict__ dst) {
+    constexpr int BB = block_bytes(TYPE);
+    const int64_t ngroups = n / 8;  // n % 32 == 0
+    for (int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < ngroups;
+         g += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t blk = g >> 2;
+        const int sub = (int)(g & 3);  // which 8 elements of the block
+        const uint8_t *p = src + blk * BB;
+        const float d = h2f(*(const uint16_t *)p);
+        float v[8];
+        if (TYPE == T_Q8_0) {
+            const uint16_t *q = (const uint16_t *)(p + 2 + sub * 8);
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                uint16_t w = q[i];
+                v[2 * i] = __fmul_rn(d, (float)(int8_t)(w & 0xFF));
+                v[2 * i + 1] = __fmul_rn(d, (float)(int8_t)(w >> 8));
+            }
+        } else {
+            constexpr int QOFF = (TYPE == T_Q4_0) ? 2 : 4;
+            const uint16_t *q = (const uint16_t *)(p + QOFF + sub * 4);
+            const uint32_t w = (uint32_t)q[0] | ((uint32_t)q[1] << 16);
+            float m = 0.f;
+            if (TYPE == T_Q4_1) m = h2f(*(const uint16_t *)(p + 2));
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                const float nib = (float)((w >> (4 * i)) & 15u);
+                if (TYPE == T_Q4_0)
+                    v[i] = __fmul_rn(d, __fsub_rn(nib, 8.0f));
+                else
+                    v[i] = __fadd_rn(__fmul_rn(d, nib), m);
+            }
+        }
+        float4 *o = (float4 *)(dst + g * 8);
+        o[0] = make_float4(v[0], v[1], v[2], v[3]);
+        o[1] = make_float4(v[4], v[5], v[6], v[7]);
+    }
+}
+
+cudaError_t launch_dequantize(int type, const void *src, int64_t n, float *dst, cudaStream_t s) {
+    if (n == 0) return cudaSuccess;
+    const int threads = 256;
+    const int grid = grid_for(n / 8, threads);
+    switch (type) {
+        case T_Q8_0: dequant_kernel<T_Q8_0><<<grid, threads, 0, s>>>((const uint8_t *)src, n, dst); break;
+        case T_Q4_0: dequant_kernel<T_Q4_0><<<grid, threads, 0, s>>>((const uint8_t *)src, n, dst); break;
+        case T_Q4_1: dequant_kernel<T_Q4_1><<<grid, threads, 0, s>>>((const uint8_t *)src, n, dst); break;
+        default: return cudaErrorNotSupported;
+    }
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
+// Generic matmul: any K, M, N; a in {F32, Q4_0, Q4_1, Q8_0}; reference layouts
+// (b element (j,k) at j + k*N, dst element (j,i) at j + i*N).  One warp per
+// (row i, tile of up to 8 columns); lanes stride over k element-wise with the
+// reference's flat block addressing (flat = i*K + k, block = flat/32,
+// core/GGMLComputeOps.kt:58-62) so K need not be a multiple of 32.
+// The dequantised weight uses the reference's exact per-element formula; only
+// the summation order differs (lane-strided + shuffle tree), which is why the
+// matmul bar is a tolerance, not bit-exactness.
+// This is the correctness fallback, not a tuned kernel.
+// ---------------------------------------------------------------------------
+template <int TYPE>
+__device__ __forceinline__ float load_weight(const void *a, int64_t flat) {
+    if (TYPE == T_F32) return ((const float *)a)[flat];
+    constexpr int BB = block_bytes(TYPE);
+    const uint8_t *p = (const uint8_t *)a + (flat >> 5) * BB;
+    const int item = (int)(flat & 31);
+    const float d = h2f(*(const uint16_t *)p);
+    if (TYPE == T_Q8_0) return __fmul_rn(d, (float)(int8_t)p[2 + item]);
+    constexpr int QOFF = (TYPE == T_Q4_0) ? 2 : 4;
+    const uint8_t byte = p[QOFF + (item >> 1)];
+    const float nib = (float)((item & 1) ? (byte >> 4) : (byte & 15));
+    if (TYPE == T_Q4_0) return __fmul_rn(d, __fsub_rn(nib, 8.0f));
+    return __fadd_rn(__fmul_rn(d, nib), h2f(*(const uint16_t *)(p + 2)));
+}
+
+template <int TYPE>
+__global__ void __launch_bounds__(128) matmul_generic_kernel(const void *__restrict__ a, int64_t K, int64_t M,
+                                                             const float *__restrict__ b, int64_t N,
+                                                             float *__restrict__ dst, int64_t ntiles_n) {
+    constexpr int TN = 8;
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t w = warp; w < M * ntiles_n; w += nwarps) {
+        const int64_t i = w / ntiles_n;
+        const int64_t j0 = (w % ntiles_n) * TN;
+        const int nj = (int)((N - j0) < TN ? (N - j0) : TN);
+        float acc[TN];
+#pragma unroll
+        for (int j = 0; j < TN; j++) acc[j] = 0.f;
+        for (int64_t k = lane; k < K; k += 32) {
+            const float wv = load_weight<TYPE>(a, i * K + k);
+            const float *bp = b + j0 + k * N;
+#pragma unroll
+            for (int j = 0; j < TN; j++)
+                if (j < nj) acc[j] = __fadd_rn(acc[j], __fmul_rn(wv, bp[j]));
+        }
+#pragma unroll
+        for (int j = 0; j < TN; j++) acc[j] = warp_sum(acc[j]);
+        if (lane == 0)
+            for (int j = 0; j < nj; j++) dst[j0 + j + i * N] = acc[j];
+    }
+}
+
+cudaError_t launch_matmul_generic(int type, const void *a, int64_t K, int64_t M, const float *b, int64_t N,
+                                  float *dst, cudaStream_t s) {
+    if (M == 0 || N == 0) return cudaSuccess;
+    const int64_t ntn = (N + 7) / 8;
+    const int threads = 128;
+    const int grid = grid_for(M * ntn * 32, threads, 148 * 32);
+    switch (type) {
+        case T_F32: matmul_generic_kernel<T_F32><<<grid, threads, 0, s>>>(a, K, M, b, N, dst, ntn); break;
+        case T_Q8_0: matmul_generic_kernel<T_Q8_0><<<grid, threads, 0, s>>>(a, K, M, b, N, dst, ntn); break;
+        case T_Q4_0: matmul_generic_kernel<T_Q4_0><<<grid, threads, 0, s>>>(a, K, M, b, N, dst, ntn); break;
+        case T_Q4_1: matmul_generic_kernel<T_Q4_1><<<grid, threads, 0, s>>>(a, K, M, b, N, dst, ntn); break;
+        default: return cudaErrorNotSupported;
+    }
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
+// R4 add / mul, K4 SiLU and SiLU*up: one pass, 16-byte vector accesses.
+// Algorithmic bytes per element: 12 (binary ops, silu_mul), 8 (silu).
+// ---------------------------------------------------------------------------
+enum { OP_ADD = 0, OP_MUL = 1, OP_SILU = 2, OP_SILU_MUL = 3 };
+
+// silu(x) = x * (1 / (1 + exp(-x))) — nativeTest core/GGMLComputeOpsTest.kt:491-499.
+// expf (not __expf) and IEEE division keep it within 2 ulp of the libm path.
+__device__ __forceinline__ float silu1(float x) { return __fmul_rn(x, __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-x)))); }
+
+template <int OP>
+__device__ __forceinline__ float ew_apply(float a, float b) {
+    if (OP == OP_ADD) return __fadd_rn(a, b);
+    if (OP == OP_MUL) return __fmul_rn(a, b);
+    if (OP == OP_SILU) return silu1(a);
+    return __fmul_rn(silu1(a), b);
+}
+
+template <int OP>
+__global__ void __launch_bounds__(256) ew_kernel(const float *__restrict__ a, const float *__restrict__ b, int64_t n,
+                                                 float *__restrict__ dst, int vec_ok) {
+    constexpr bool BIN = (OP != OP_SILU);
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
+    int64_t done = 0;
+    if (vec_ok) {
+        const int64_t n4 = n / 4;
+        for (int64_t i = tid; i < n4; i += nthr) {
+            const float4 x = ((const float4 *)a)[i];
+            float4 y = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (BIN) y = ((const float4 *)b)[i];
+            float4 r;
+            r.x = ew_apply<OP>(x.x, y.x);
+            r.y = ew_apply<OP>(x.y, y.y);
+            r.z = ew_apply<OP>(x.z, y.z);
+            r.w = ew_apply<OP>(x.w, y.w);
+            ((float4 *)dst)[i] = r;
+        }
+        done = n4 * 4;
+    }
+    for (int64_t i = done + tid; i < n; i += nthr) dst[i] = ew_apply<OP>(a[i], BIN ? b[i] : 0.f);
+}
+
+template <int OP>
+static cudaError_t launch_ew(const float *a, const float *b, int64_t n, float *dst, cudaStream_t s) {
+    if (n == 0) return cudaSuccess;
+    const uintptr_t al = (uintptr_t)a | (uintptr_t)dst | (uintptr_t)(b ? b : a);
+    const int vec_ok = (al & 15) == 0;
+    const int threads = 256;
+    ew_kernel<OP><<<grid_for((n + 3) / 4, threads), threads, 0, s>>>(a, b, n, dst, vec_ok);
+    return cudaGetLastError();
+}
+cudaError_t launch_add(const float *a, const float *b, int64_t n, float *d, cudaStream_t s) { return launch_ew<OP_ADD>(a, b, n, d, s); }
+cudaError_t launch_mul(const float *a, const float *b, int64_t n, float *d, cudaStream_t s) { return launch_ew<OP_MUL>(a, b, n, d, s); }
+cudaError_t launch_silu(const float *x, int64_t n, float *d, cudaStream_t s) { return launch_ew<OP_SILU>(x, nullptr, n, d, s); }
+cudaError_t launch_silu_mul(const float *g, const float *u, int64_t n, float *d, cudaStream_t s) { return launch_ew<OP_SILU_MUL>(g, u, n, d, s); }
+
+// ---------------------------------------------------------------------------
+// block-wide reductions (256 threads)
+// ---------------------------------------------------------------------------
+template <typename T, typename F>
+__device__ __forceinline__ T block_reduce(T v, F op, T *scratch /* >= 32 */) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = op(v, __shfl_xor_sync(0xffffffffu, v, o));
+    __syncthreads();  // scratch reuse across calls
+    if (lane == 0) scratch[wid] = v;
+    __syncthreads();
+    T r = scratch[0];
+    for (int w = 1; w < nw; w++) r = op(r, scratch[w]);
+    return r;
+}
+
+// ---------------------------------------------------------------------------
+// K3 RMSNorm — spec: manualRMSNorm, nativeTest core/GGMLComputeOpsTest.kt:502-521:
+// sum of squares accumulated in F64, rms = (float)sqrt(mean + eps), y = x / rms
+// (IEEE division), optional * weight (model/LlamaModel.kt:59-62).  x*x is exact
+// in F64 and the F64 sum differs from the sequential one only at the 1e-16
+// level, so the result is bit-identical to the oracle except where (float)sqrt
+// sits on a rounding boundary.  One CTA per row; bytes per element 8 (+4 weight).
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) rms_norm_kernel(const float *__restrict__ x, const float *__restrict__ w,
+                                                       float eps, int64_t ne0, float *__restrict__ dst) {
+    __shared__ double scratch[32];
+    const float *xr = x + (int64_t)blockIdx.x * ne0;
+    float *dr = dst + (int64_t)blockIdx.x * ne0;
+    double acc = 0.0;
+    for (int64_t i = threadIdx.x; i < ne0; i += blockDim.x) {
+        const double v = (double)xr[i];
+        acc = fma(v, v, acc);
+    }
+    const double sumsq = block_reduce(acc, [](double a, double b) { return a + b; }, scratch);
+    const float rms = (float)sqrt(sumsq / (double)ne0 + (double)eps);
+    const bool zero = (rms == 0.0f) || (rms != rms);
+    for (int64_t i = threadIdx.x; i < ne0; i += blockDim.x) {
+        float v = zero ? 0.0f : __fdiv_rn(xr[i], rms);
+        if (w != nullptr && !zero) v = __fmul_rn(v, w[i]);
+        dr[i] = v;
+    }
+}
+
+cudaError_t launch_rms_norm(const float *x, const float *w, float eps, int64_t ne0, int64_t nrows, float *dst,
+                            cudaStream_t s) {
+    if (nrows == 0 || ne0 == 0) return cudaSuccess;
+    rms_norm_kernel<<<(unsigned)nrows, 256, 0, s>>>(x, w, eps, ne0, dst);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
+// K5 softmax over ne[0] — LlamaAttention.softmax, model/LlamaAttention.kt:242-288:
+// max, exp(x - max), F32 sum, divide.  One CTA per row, three passes over a row
+// that stays in L1/L2 (8 algorithmic bytes per element).
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) softmax_kernel(const float *__restrict__ x, int64_t ne0,
+                                                      float *__restrict__ dst) {
+    __shared__ float scratch[32];
+    const float *xr = x + (int64_t)blockIdx.x * ne0;
+    float *dr = dst + (int64_t)blockIdx.x * ne0;
+    float m = -INFINITY;
+    for (int64_t i = threadIdx.x; i < ne0; i += blockDim.x) m = fmaxf(m, xr[i]);
+    m = block_reduce(m, [](float a, float b) { return fmaxf(a, b); }, scratch);
+    float sum = 0.f;
+    for (int64_t i = threadIdx.x; i < ne0; i += blockDim.x) {
+        const float e = expf(__fsub_rn(xr[i], m));
+        dr[i] = e;
+        sum += e;
+    }
+    sum = block_reduce(sum, [](float a, float b) { return a + b; }, scratch);
+    for (int64_t i = threadIdx.x; i < ne0; i += blockDim.x) dr[i] = __fdiv_rn(dr[i], sum);
+}
+
+cudaError_t launch_softmax(const float *x, int64_t ne0, int64_t nrows, float *dst, cudaStream_t s) {
+    if (nrows == 0 || ne0 == 0) return cudaSuccess;
+    softmax_kernel<<<(unsigned)nrows, 256, 0, s>>>(x, ne0, dst);
+    return cudaGetLastError();
+}
+
+}  // namespace lk

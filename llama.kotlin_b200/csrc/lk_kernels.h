@@ -1,0 +1,53 @@
+// lk_kernels.h — host-callable launchers for the sm_100a kernels.  Internal to
+// the shared library; the public surface is include/llamakotlin_cuda.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace lk {
+
+// Tunables for the K1 streaming GEMV (set through lk_set_option; defaults are
+// the product settings chosen from measurements).
+struct GemvTuning {
+    int variant = 0;        // 0 = auto
+    int stage_bytes = 0;    // 0 = auto: target bytes per TMA stage
+    int max_stages = 0;     // 0 = auto
+    int smem_budget = 0;    // 0 = auto: bytes of dynamic smem per CTA
+    int pdl = 1;            // programmatic dependent launch attribute
+    int ctas_per_sm = 1;
+};
+
+// K0: block dequantisation, bit-exact with dequantizeTensor (core/GGMLComputeOps.kt:918-964).
+cudaError_t launch_dequantize(int type, const void *src, int64_t n, float *dst, cudaStream_t s);
+
+// K1: decode GEMV, N == 1, K % 64 == 0.  Returns cudaErrorNotSupported when the
+// shape cannot take the streaming path (caller then uses the generic kernel).
+// dst_peers/npeers: optional extra destinations (peer-mapped buffers) for the
+// fused all-gather; row_offset shifts the output index (sharded weights).
+struct GemvPeers {
+    float *ptr[8];
+    int n = 0;
+};
+cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const float *b, float *dst,
+                        int64_t row_offset, const GemvPeers &peers, const GemvTuning &tune, int sm_count,
+                        cudaStream_t s);
+
+// Generic matmul for any (K, M, N) and a.type in {F32, Q4_0, Q4_1, Q8_0}; reference layouts.
+cudaError_t launch_matmul_generic(int type, const void *a, int64_t K, int64_t M, const float *b, int64_t N,
+                                  float *dst, cudaStream_t s);
+
+// K2: tcgen05 prefill GEMM (lk_gemm_tc.cu).  workspace holds the FP16 copy of b.
+size_t gemm_tc_workspace_bytes(int64_t K, int64_t N);
+cudaError_t launch_gemm_tc(int type, const void *a, int64_t K, int64_t M, const float *b, int64_t N, float *dst,
+                           void *workspace, int sm_count, cudaStream_t s);
+
+// K3-K5 + R4
+cudaError_t launch_rms_norm(const float *x, const float *w, float eps, int64_t ne0, int64_t nrows, float *dst,
+                            cudaStream_t s);
+cudaError_t launch_silu(const float *x, int64_t n, float *dst, cudaStream_t s);
+cudaError_t launch_silu_mul(const float *g, const float *u, int64_t n, float *dst, cudaStream_t s);
+cudaError_t launch_softmax(const float *x, int64_t ne0, int64_t nrows, float *dst, cudaStream_t s);
+cudaError_t launch_add(const float *a, const float *b, int64_t n, float *dst, cudaStream_t s);
+cudaError_t launch_mul(const float *a, const float *b, int64_t n, float *dst, cudaStream_t s);
+
+}  // namespace lk

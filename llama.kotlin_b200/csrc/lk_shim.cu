@@ -1,0 +1,547 @@
+// lk_shim.cu — the C ABI (include/llamakotlin_cuda.h): context, device buffers,
+// validation in the reference's order, host-tensor staging, op dispatch,
+// op-sequence capture.  No CPU compute path exists here: if CUDA is not
+// available every compute entry point fails with LK_ECUDA.
+#include "lk_shim.h"
+
+#include <string.h>
+
+#include "lk_common.cuh"
+
+static thread_local std::string g_noctx_err = "no error";
+
+namespace lk {
+lk_status fail(lk_ctx *ctx, lk_status st, const std::string &msg) {
+    if (ctx) ctx->err = msg; else g_noctx_err = msg;
+    return st;
+}
+lk_status cuda_fail(lk_ctx *ctx, cudaError_t e, const char *what) {
+    cudaGetLastError();  // clear sticky-less error state
+    return fail(ctx, e == cudaErrorMemoryAllocation ? LK_ENOMEM : LK_ECUDA,
+                std::string("CUDA error: ") + cudaGetErrorString(e) + " at " + what);
+}
+}  // namespace lk
+using lk::fail;
+
+extern "C" {
+
+int32_t lk_abi_version(void) { return LK_ABI_VERSION; }
+
+int32_t lk_type_block_bytes(int32_t type) {
+    if (type == LK_TYPE_F32) return 4;
+    if (type == LK_TYPE_F16) return 2;
+    return lk::block_bytes(type);
+}
+
+static bool is_block_type(int t) { return t == LK_TYPE_Q4_0 || t == LK_TYPE_Q4_1 || t == LK_TYPE_Q8_0; }
+
+static int64_t num_elements(const lk_tensor *t) {
+    int64_t n = 1;
+    for (int d = 0; d < LK_MAX_DIMS; d++) n *= (t->ne[d] > 0 ? t->ne[d] : (t->ne[d] == 0 && d == 0 ? 0 : 1));
+    return n;
+}
+
+int64_t lk_tensor_nbytes(const lk_tensor *t) {
+    if (!t) return -1;
+    const int64_t n = num_elements(t);
+    if (is_block_type(t->type)) return n / LK_QK * lk::block_bytes(t->type);
+    if (t->type == LK_TYPE_F32) return n * 4;
+    if (t->type == LK_TYPE_F16) return n * 2;
+    return -1;
+}
+
+lk_status lk_ctx_create(int32_t device, lk_ctx **out) {
+    if (!out) return fail(nullptr, LK_EINVAL_ARG, "lk_ctx_create: out is NULL");
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(nullptr, LK_ECUDA, "lk_ctx_create: no CUDA device (this library has no CPU fallback)");
+    }
+    if (device < 0 || device >= ndev) return fail(nullptr, LK_EINVAL_ARG, "lk_ctx_create: bad device index");
+    lk_ctx *ctx = new lk_ctx();
+    ctx->device = device;
+    LK_CUDA(nullptr, cudaSetDevice(device));
+    cudaDeviceProp prop;
+    LK_CUDA(nullptr, cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) {
+        delete ctx;
+        return fail(nullptr, LK_ECUDA, "lk_ctx_create: kernels are built for sm_100a only");
+    }
+    ctx->sm_count = prop.multiProcessorCount;
+    LK_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    LK_CUDA(nullptr, cudaEventCreate(&ctx->ev0));
+    LK_CUDA(nullptr, cudaEventCreate(&ctx->ev1));
+    *out = ctx;
+    return LK_OK;
+}
+
+lk_status lk_comm_destroy(lk_ctx *ctx);
+
+lk_status lk_ctx_destroy(lk_ctx *ctx) {
+    if (!ctx) return LK_OK;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    lk_comm_destroy(ctx);
+    if (ctx->arena) cudaFree(ctx->arena);
+    if (ctx->gemm_ws) cudaFree(ctx->gemm_ws);
+    cudaEventDestroy(ctx->ev0);
+    cudaEventDestroy(ctx->ev1);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return LK_OK;
+}
+
+lk_status lk_sync(lk_ctx *ctx) {
+    if (!ctx) return fail(nullptr, LK_EINVAL_ARG, "lk_sync: ctx is NULL");
+    LK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return LK_OK;
+}
+
+const char *lk_last_error(lk_ctx *ctx) { return ctx ? ctx->err.c_str() : g_noctx_err.c_str(); }
+void *lk_ctx_stream(lk_ctx *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
+int32_t lk_ctx_device(lk_ctx *ctx) { return ctx ? ctx->device : -1; }
+int32_t lk_ctx_sm_count(lk_ctx *ctx) { return ctx ? ctx->sm_count : 0; }
+int64_t lk_ctx_launch_count(lk_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+lk_status lk_timer_start(lk_ctx *ctx) {
+    if (!ctx) return fail(nullptr, LK_EINVAL_ARG, "lk_timer_start: ctx is NULL");
+    LK_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    return LK_OK;
+}
+lk_status lk_timer_stop(lk_ctx *ctx, float *ms_out) {
+    if (!ctx || !ms_out) return fail(ctx, LK_EINVAL_ARG, "lk_timer_stop: NULL argument");
+    LK_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    LK_CUDA(ctx, cudaEventSynchronize(ctx->ev1));
+    LK_CUDA(ctx, cudaEventElapsedTime(ms_out, ctx->ev0, ctx->ev1));
+    return LK_OK;
+}
+
+// ---- device buffers ---------------------------------------------------------
+lk_status lk_buf_alloc(lk_ctx *ctx, uint64_t size, lk_buf **out) {
+    if (!ctx || !out) return fail(ctx, LK_EINVAL_ARG, "lk_buf_alloc: NULL argument");
+    *out = nullptr;
+    LK_CUDA(ctx, cudaSetDevice(ctx->device));
+    void *p = nullptr;
+    LK_CUDA(ctx, cudaMalloc(&p, size ? size : 16));
+    lk_buf *b = new lk_buf();
+    b->ctx = ctx; b->ptr = p; b->size = size;
+    *out = b;
+    return LK_OK;
+}
+
+lk_status lk_buf_free(lk_buf *buf) {
+    if (!buf) return LK_OK;
+    lk_ctx *ctx = buf->ctx;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    if (buf->imported) cudaIpcCloseMemHandle(buf->ptr); else cudaFree(buf->ptr);
+    delete buf;
+    return LK_OK;
+}
+
+uint64_t lk_buf_size(const lk_buf *buf) { return buf ? buf->size : 0; }
+void *lk_buf_device_ptr(lk_buf *buf) { return buf ? buf->ptr : nullptr; }
+
+static lk_status buf_range(lk_buf *buf, uint64_t off, uint64_t n, const char *what) {
+    if (!buf) return fail(nullptr, LK_EINVAL_ARG, std::string(what) + ": buf is NULL");
+    if (off > buf->size || n > buf->size - off)
+        return fail(buf->ctx, LK_EBOUNDS, std::string(what) + ": range outside the buffer");
+    return LK_OK;
+}
+
+lk_status lk_buf_upload(lk_buf *buf, uint64_t off, const void *host, uint64_t n) {
+    lk_status st = buf_range(buf, off, n, "lk_buf_upload");
+    if (st != LK_OK) return st;
+    if (n == 0) return LK_OK;
+    if (!host) return fail(buf->ctx, LK_EINVAL_ARG, "lk_buf_upload: host is NULL");
+    lk_ctx *ctx = buf->ctx;
+    LK_CUDA(ctx, cudaMemcpyAsync((uint8_t *)buf->ptr + off, host, n, cudaMemcpyHostToDevice, ctx->stream));
+    LK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // host memory may be unpinned right after return
+    return LK_OK;
+}
+
+lk_status lk_buf_download(lk_buf *buf, uint64_t off, void *host, uint64_t n) {
+    lk_status st = buf_range(buf, off, n, "lk_buf_download");
+    if (st != LK_OK) return st;
+    if (n == 0) return LK_OK;
+    if (!host) return fail(buf->ctx, LK_EINVAL_ARG, "lk_buf_download: host is NULL");
+    lk_ctx *ctx = buf->ctx;
+    LK_CUDA(ctx, cudaMemcpyAsync(host, (uint8_t *)buf->ptr + off, n, cudaMemcpyDeviceToHost, ctx->stream));
+    LK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return LK_OK;
+}
+
+lk_status lk_buf_copy(lk_buf *dst, uint64_t doff, lk_buf *src, uint64_t soff, uint64_t n) {
+    lk_status st = buf_range(dst, doff, n, "lk_buf_copy(dst)");
+    if (st != LK_OK) return st;
+    st = buf_range(src, soff, n, "lk_buf_copy(src)");
+    if (st != LK_OK) return st;
+    lk_ctx *ctx = dst->ctx;
+    if (n) LK_CUDA(ctx, cudaMemcpyAsync((uint8_t *)dst->ptr + doff, (uint8_t *)src->ptr + soff, n, cudaMemcpyDeviceToDevice, ctx->stream));
+    return LK_OK;
+}
+
+lk_status lk_buf_clear(lk_buf *buf, uint8_t value) {
+    if (!buf) return fail(nullptr, LK_EINVAL_ARG, "lk_buf_clear: buf is NULL");
+    lk_ctx *ctx = buf->ctx;
+    if (buf->size) LK_CUDA(ctx, cudaMemsetAsync(buf->ptr, value, buf->size, ctx->stream));
+    return LK_OK;
+}
+
+lk_status lk_host_alloc(lk_ctx *ctx, uint64_t size, void **out) {
+    if (!ctx || !out) return fail(ctx, LK_EINVAL_ARG, "lk_host_alloc: NULL argument");
+    LK_CUDA(ctx, cudaSetDevice(ctx->device));
+    LK_CUDA(ctx, cudaHostAlloc(out, size ? size : 16, cudaHostAllocDefault));
+    return LK_OK;
+}
+lk_status lk_host_free(lk_ctx *ctx, void *p) {
+    if (p) LK_CUDA(ctx, cudaFreeHost(p));
+    return LK_OK;
+}
+
+}  // extern "C"
+
+// ---- tensor resolution: host tensors are staged through a device arena -------
+namespace {
+
+struct Staged {
+    void *dev = nullptr;       // device address the kernel uses
+    void *host = nullptr;      // non-NULL: copy back to here after the op (outputs only)
+    int64_t bytes = 0;
+};
+
+struct OpScope {
+    lk_ctx *ctx;
+    bool any_host = false;
+    std::vector<Staged> outs;
+    explicit OpScope(lk_ctx *c) : ctx(c) { c->arena_used = 0; }
+};
+
+lk_status arena_reserve(lk_ctx *ctx, size_t need) {
+    if (need <= ctx->arena_size) return LK_OK;
+    LK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ctx->arena) cudaFree(ctx->arena);
+    ctx->arena = nullptr; ctx->arena_size = 0;
+    size_t sz = need + need / 4 + (1 << 20);
+    LK_CUDA(ctx, cudaMalloc((void **)&ctx->arena, sz));
+    ctx->arena_size = sz;
+    return LK_OK;
+}
+
+bool contiguous_f32(const lk_tensor *t) {
+    bool allzero = true;
+    for (int d = 0; d < LK_MAX_DIMS; d++) allzero = allzero && t->nb[d] == 0;
+    if (allzero) return true;
+    if (t->nb[0] != 4) return false;
+    uint64_t expect = 4;
+    for (int d = 1; d < LK_MAX_DIMS; d++) {
+        expect *= (uint64_t)(t->ne[d - 1] > 0 ? t->ne[d - 1] : 1);
+        if ((t->ne[d] > 1) && t->nb[d] != expect) return false;
+    }
+    return true;
+}
+
+// total staging bytes the host tensors of one op need (each rounded to 256)
+size_t host_need(std::initializer_list<const lk_tensor *> ts) {
+    size_t need = 0;
+    for (const lk_tensor *t : ts)
+        if (t && !t->dev_buf) need += ((size_t)lk_tensor_nbytes(t) + 255) & ~(size_t)255;
+    return need;
+}
+
+lk_status resolve(OpScope &sc, const lk_tensor *t, bool is_output, void **dev_out, const char *name) {
+    lk_ctx *ctx = sc.ctx;
+    const int64_t nbytes = lk_tensor_nbytes(t);
+    if (nbytes < 0) return fail(ctx, LK_ENOTIMPL, std::string(name) + ": unsupported tensor type");
+    if (t->type == LK_TYPE_F32 && !contiguous_f32(t))
+        return fail(ctx, LK_EINVAL_ARG, std::string(name) + ": F32 tensors must be contiguous");
+    if ((t->dev_buf != nullptr) == (t->host_base != nullptr))
+        return fail(ctx, LK_EINVAL_ARG, std::string(name) + ": exactly one of host_base / dev_buf must be set");
+    if (t->dev_buf) {
+        lk_buf *b = t->dev_buf;
+        if (t->data_offset > b->size || (uint64_t)nbytes > b->size - t->data_offset)
+            return fail(ctx, LK_EBOUNDS, std::string(name) + ": tensor bytes exceed the device buffer");
+        if (t->data_offset % 16)  // GGMLDynTensorAllocator alignment, core/GGMLAlloc.kt:122,149
+            return fail(ctx, LK_EINVAL_ARG, std::string(name) + ": dataOffset must be 16-byte aligned on device");
+        *dev_out = (uint8_t *)b->ptr + t->data_offset;
+        return LK_OK;
+    }
+    // host tensor: IndexOutOfBounds semantics of the accessors (core/GGMLTypes.kt:556-558)
+    if (t->data_offset > t->buffer_size || (uint64_t)nbytes > t->buffer_size - t->data_offset)
+        return fail(ctx, LK_EBOUNDS, std::string(name) + ": tensor bytes exceed the host buffer");
+    if (ctx->capturing)
+        return fail(ctx, LK_EINVAL_ARG, std::string(name) + ": host tensors cannot be used inside a captured sequence");
+    sc.any_host = true;
+    uint8_t *d = ctx->arena + ctx->arena_used;
+    ctx->arena_used += ((size_t)nbytes + 255) & ~(size_t)255;
+    uint8_t *h = (uint8_t *)t->host_base + t->data_offset;
+    if (is_output) {
+        Staged s; s.dev = d; s.host = h; s.bytes = nbytes;
+        sc.outs.push_back(s);
+    } else if (nbytes) {
+        LK_CUDA(ctx, cudaMemcpyAsync(d, h, (size_t)nbytes, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    *dev_out = d;
+    return LK_OK;
+}
+
+// copy staged outputs back and make dst valid on return (reference semantics)
+lk_status finish(OpScope &sc) {
+    lk_ctx *ctx = sc.ctx;
+    for (const Staged &s : sc.outs)
+        if (s.bytes) LK_CUDA(ctx, cudaMemcpyAsync(s.host, s.dev, (size_t)s.bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    if (sc.any_host) LK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return LK_OK;
+}
+
+void count_launch(lk_ctx *ctx, int n = 1) {
+    if (ctx->capturing) ctx->capture_launches += n; else ctx->launches += n;
+}
+
+bool same_shape(const lk_tensor *a, const lk_tensor *b) {
+    for (int d = 0; d < LK_MAX_DIMS; d++) {
+        const int64_t x = a->ne[d] > 0 ? a->ne[d] : (d == 0 ? 0 : 1), y = b->ne[d] > 0 ? b->ne[d] : (d == 0 ? 0 : 1);
+        if (x != y) return false;
+    }
+    return true;
+}
+
+}  // namespace
+
+extern "C" {
+
+lk_status lk_compute_matmul(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, const lk_tensor *dst) {
+    if (!ctx || !a || !b || !dst) return fail(ctx, LK_EINVAL_ARG, "lk_compute_matmul: NULL argument");
+    // validation in the order of core/GGMLComputeOps.kt:1436-1446
+    const int64_t M = a->ne[1], K = a->ne[0], N = b->ne[0], Kb = b->ne[1];
+    if (K != Kb) return fail(ctx, LK_EINVAL_DIM, "Dim mismatch K: a.ne[0] != b.ne[1]");
+    if (dst->ne[0] != N || dst->ne[1] != M)
+        return fail(ctx, LK_EINVAL_DIM, "Result tensor dimensions must match expected output size [N, M]");
+    if (is_block_type(a->type) && b->type == LK_TYPE_F32) {
+        if (dst->type != LK_TYPE_F32) return fail(ctx, LK_EINVAL_TYPE, "Result tensor type must be F32 for Q x F32 matmul");
+    } else {
+        // general fallback, :1530-1565
+        if (dst->type != a->type) return fail(ctx, LK_EINVAL_TYPE, "Result tensor type must match first input type for general matmul");
+        if (a->type != LK_TYPE_F32 || b->type != LK_TYPE_F32)
+            return fail(ctx, LK_ENOTIMPL, "computeMatMul on this device path supports {F32,Q4_0,Q4_1,Q8_0} x F32 only");
+    }
+    if (M < 0 || K < 0 || N < 0) return fail(ctx, LK_EINVAL_DIM, "negative dimension");
+    if (is_block_type(a->type) && ((M * K) % LK_QK) != 0)
+        return fail(ctx, LK_EINVAL_DIM, "quantized tensor element count must be a multiple of 32");
+    LK_CUDA(ctx, cudaSetDevice(ctx->device));
+
+    OpScope sc(ctx);
+    lk_status st = arena_reserve(ctx, host_need({a, b, dst}));
+    if (st != LK_OK) return st;
+    void *da, *db, *dd;
+    if ((st = resolve(sc, a, false, &da, "a")) != LK_OK) return st;
+    if ((st = resolve(sc, b, false, &db, "b")) != LK_OK) return st;
+    if ((st = resolve(sc, dst, true, &dd, "dst")) != LK_OK) return st;
+    if (M == 0 || N == 0) return finish(sc);
+
+    cudaError_t e = cudaErrorNotSupported;
+    if (N == 1 && is_block_type(a->type)) {
+        lk::GemvTuning tune = ctx->tune;
+        tune.pdl = (ctx->pdl_mode == 2) || (ctx->pdl_mode == 1 && ctx->capturing);
+        lk::GemvPeers none;
+        e = lk::launch_gemv(a->type, da, K, M, (const float *)db, (float *)dd, 0, none, tune, ctx->sm_count, ctx->stream);
+    }
+    if (e == cudaErrorNotSupported) {
+        cudaGetLastError();
+        e = lk::launch_matmul_generic(a->type, da, K, M, (const float *)db, N, (float *)dd, ctx->stream);
+    }
+    if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "matmul launch");
+    count_launch(ctx);
+    return finish(sc);
+}
+
+lk_status lk_compute_dequantize(lk_ctx *ctx, const lk_tensor *src, const lk_tensor *dst) {
+    if (!ctx || !src || !dst) return fail(ctx, LK_EINVAL_ARG, "lk_compute_dequantize: NULL argument");
+    if (!is_block_type(src->type)) return fail(ctx, LK_ENOTIMPL, "dequantize: source must be Q4_0, Q4_1 or Q8_0");
+    if (dst->type != LK_TYPE_F32) return fail(ctx, LK_EINVAL_TYPE, "dequantize: destination must be F32");
+    const int64_t n = num_elements(src);
+    if (n != num_elements(dst)) return fail(ctx, LK_EINVAL_DIM, "dequantize: element counts differ");
+    if (n % LK_QK) return fail(ctx, LK_EINVAL_DIM, "dequantize: element count must be a multiple of 32");
+    LK_CUDA(ctx, cudaSetDevice(ctx->device));
+    OpScope sc(ctx);
+    lk_status st = arena_reserve(ctx, host_need({src, dst}));
+    if (st != LK_OK) return st;
+    void *ds, *dd;
+    if ((st = resolve(sc, src, false, &ds, "src")) != LK_OK) return st;
+    if ((st = resolve(sc, dst, true, &dd, "dst")) != LK_OK) return st;
+    cudaError_t e = lk::launch_dequantize(src->type, ds, n, (float *)dd, ctx->stream);
+    if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "dequantize launch");
+    count_launch(ctx);
+    return finish(sc);
+}
+
+typedef cudaError_t (*binary_fn)(const float *, const float *, int64_t, float *, cudaStream_t);
+
+static lk_status binary_op(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, const lk_tensor *dst, binary_fn fn,
+                           const char *name) {
+    if (!ctx || !a || !b || !dst) return fail(ctx, LK_EINVAL_ARG, std::string(name) + ": NULL argument");
+    // core/GGMLComputeOps.kt:742-750: dims must match (no broadcast), dst dims and type must match
+    if (!same_shape(a, b)) return fail(ctx, LK_EINVAL_DIM, std::string(name) + ": input dimensions differ");
+    if (!same_shape(a, dst)) return fail(ctx, LK_EINVAL_DIM, std::string(name) + ": result dimensions must match input dimensions");
+    if (dst->type != a->type || b->type != a->type) return fail(ctx, LK_EINVAL_TYPE, std::string(name) + ": tensor types must match");
+    if (a->type != LK_TYPE_F32) return fail(ctx, LK_ENOTIMPL, std::string(name) + ": F32 only on this device path");
+    LK_CUDA(ctx, cudaSetDevice(ctx->device));
+    OpScope sc(ctx);
+    lk_status st = arena_reserve(ctx, host_need({a, b, dst}));
+    if (st != LK_OK) return st;
+    void *da, *db, *dd;
+    if ((st = resolve(sc, a, false, &da, "a")) != LK_OK) return st;
+    if ((st = resolve(sc, b, false, &db, "b")) != LK_OK) return st;
+    if ((st = resolve(sc, dst, true, &dd, "dst")) != LK_OK) return st;
+    cudaError_t e = fn((const float *)da, (const float *)db, num_elements(a), (float *)dd, ctx->stream);
+    if (e != cudaSuccess) return lk::cuda_fail(ctx, e, name);
+    count_launch(ctx);
+    return finish(sc);
+}
+
+lk_status lk_compute_add(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, const lk_tensor *dst) {
+    return binary_op(ctx, a, b, dst, lk::launch_add, "computeAdd");
+}
+lk_status lk_compute_mul(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, const lk_tensor *dst) {
+    return binary_op(ctx, a, b, dst, lk::launch_mul, "computeMul");
+}
+lk_status lk_compute_silu_mul(lk_ctx *ctx, const lk_tensor *g, const lk_tensor *u, const lk_tensor *dst) {
+    return binary_op(ctx, g, u, dst, lk::launch_silu_mul, "siluMul");
+}
+
+}  // extern "C"
+
+extern "C" {
+
+static lk_status unary_check(lk_ctx *ctx, const lk_tensor *x, const lk_tensor *dst, const char *name) {
+    if (!ctx || !x || !dst) return fail(ctx, LK_EINVAL_ARG, std::string(name) + ": NULL argument");
+    if (!same_shape(x, dst)) return fail(ctx, LK_EINVAL_DIM, std::string(name) + ": result dimensions must match input dimensions");
+    if (dst->type != x->type) return fail(ctx, LK_EINVAL_TYPE, std::string(name) + ": result type must match input type");
+    if (x->type != LK_TYPE_F32) return fail(ctx, LK_ENOTIMPL, std::string(name) + ": F32 only on this device path");
+    return LK_OK;
+}
+
+lk_status lk_compute_silu(lk_ctx *ctx, const lk_tensor *x, const lk_tensor *dst) {
+    lk_status st = unary_check(ctx, x, dst, "silu");
+    if (st != LK_OK) return st;
+    LK_CUDA(ctx, cudaSetDevice(ctx->device));
+    OpScope sc(ctx);
+    if ((st = arena_reserve(ctx, host_need({x, dst}))) != LK_OK) return st;
+    void *dx, *dd;
+    if ((st = resolve(sc, x, false, &dx, "x")) != LK_OK) return st;
+    if ((st = resolve(sc, dst, true, &dd, "dst")) != LK_OK) return st;
+    cudaError_t e = lk::launch_silu((const float *)dx, num_elements(x), (float *)dd, ctx->stream);
+    if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "silu launch");
+    count_launch(ctx);
+    return finish(sc);
+}
+
+lk_status lk_compute_rms_norm(lk_ctx *ctx, const lk_tensor *x, const lk_tensor *w, float eps, const lk_tensor *dst) {
+    lk_status st = unary_check(ctx, x, dst, "rmsNorm");
+    if (st != LK_OK) return st;
+    const int64_t ne0 = x->ne[0];
+    if (w) {
+        if (w->type != LK_TYPE_F32) return fail(ctx, LK_EINVAL_TYPE, "rmsNorm: weight must be F32");
+        if (w->ne[0] != ne0 || num_elements(w) != ne0) return fail(ctx, LK_EINVAL_DIM, "rmsNorm: weight must have ne = [ne0]");
+    }
+    LK_CUDA(ctx, cudaSetDevice(ctx->device));
+    OpScope sc(ctx);
+    if ((st = arena_reserve(ctx, host_need({x, w, dst}))) != LK_OK) return st;
+    void *dx, *dw = nullptr, *dd;
+    if ((st = resolve(sc, x, false, &dx, "x")) != LK_OK) return st;
+    if (w && (st = resolve(sc, w, false, &dw, "weight")) != LK_OK) return st;
+    if ((st = resolve(sc, dst, true, &dd, "dst")) != LK_OK) return st;
+    const int64_t n = num_elements(x);
+    cudaError_t e = lk::launch_rms_norm((const float *)dx, (const float *)dw, eps, ne0, ne0 ? n / ne0 : 0, (float *)dd, ctx->stream);
+    if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "rmsNorm launch");
+    count_launch(ctx);
+    return finish(sc);
+}
+
+lk_status lk_compute_softmax(lk_ctx *ctx, const lk_tensor *x, const lk_tensor *dst) {
+    lk_status st = unary_check(ctx, x, dst, "softmax");
+    if (st != LK_OK) return st;
+    LK_CUDA(ctx, cudaSetDevice(ctx->device));
+    OpScope sc(ctx);
+    if ((st = arena_reserve(ctx, host_need({x, dst}))) != LK_OK) return st;
+    void *dx, *dd;
+    if ((st = resolve(sc, x, false, &dx, "x")) != LK_OK) return st;
+    if ((st = resolve(sc, dst, true, &dd, "dst")) != LK_OK) return st;
+    const int64_t ne0 = x->ne[0], n = num_elements(x);
+    cudaError_t e = lk::launch_softmax((const float *)dx, ne0, ne0 ? n / ne0 : 0, (float *)dd, ctx->stream);
+    if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "softmax launch");
+    count_launch(ctx);
+    return finish(sc);
+}
+
+// ---- op-sequence capture -----------------------------------------------------
+lk_status lk_capture_begin(lk_ctx *ctx) {
+    if (!ctx) return fail(nullptr, LK_EINVAL_ARG, "lk_capture_begin: ctx is NULL");
+    if (ctx->capturing) return fail(ctx, LK_EINVAL_ARG, "lk_capture_begin: already capturing");
+    LK_CUDA(ctx, cudaSetDevice(ctx->device));
+    LK_CUDA(ctx, cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
+    ctx->capturing = true;
+    ctx->capture_launches = 0;
+    return LK_OK;
+}
+
+lk_status lk_capture_end(lk_ctx *ctx, lk_graph **out) {
+    if (!ctx || !out) return fail(ctx, LK_EINVAL_ARG, "lk_capture_end: NULL argument");
+    if (!ctx->capturing) return fail(ctx, LK_EINVAL_ARG, "lk_capture_end: not capturing");
+    ctx->capturing = false;
+    cudaGraph_t g = nullptr;
+    LK_CUDA(ctx, cudaStreamEndCapture(ctx->stream, &g));
+    cudaGraphExec_t ex = nullptr;
+    cudaError_t e = cudaGraphInstantiate(&ex, g, 0);
+    if (e != cudaSuccess) { cudaGraphDestroy(g); return lk::cuda_fail(ctx, e, "cudaGraphInstantiate"); }
+    lk_graph *gr = new lk_graph();
+    gr->ctx = ctx; gr->graph = g; gr->exec = ex; gr->launches = ctx->capture_launches;
+    *out = gr;
+    return LK_OK;
+}
+
+lk_status lk_graph_launch(lk_ctx *ctx, lk_graph *g) {
+    if (!ctx || !g) return fail(ctx, LK_EINVAL_ARG, "lk_graph_launch: NULL argument");
+    LK_CUDA(ctx, cudaGraphLaunch(g->exec, ctx->stream));
+    ctx->launches += g->launches;
+    return LK_OK;
+}
+
+lk_status lk_graph_destroy(lk_graph *g) {
+    if (!g) return LK_OK;
+    cudaStreamSynchronize(g->ctx->stream);
+    cudaGraphExecDestroy(g->exec);
+    cudaGraphDestroy(g->graph);
+    delete g;
+    return LK_OK;
+}
+
+// ---- options -------------------------------------------------------------------
+lk_status lk_set_option(lk_ctx *ctx, const char *name, int64_t v) {
+    if (!ctx || !name) return fail(ctx, LK_EINVAL_ARG, "lk_set_option: NULL argument");
+    const std::string n(name);
+    if (n == "gemv_pdl") ctx->pdl_mode = (int)v;
+    else if (n == "gemv_warps") ctx->tune.variant = (int)v;
+    else if (n == "gemv_stage_bytes") ctx->tune.stage_bytes = (int)v;
+    else if (n == "gemv_max_stages") ctx->tune.max_stages = (int)v;
+    else if (n == "gemv_smem_budget") ctx->tune.smem_budget = (int)v;
+    else if (n == "gemv_ctas_per_sm") ctx->tune.ctas_per_sm = (int)v;
+    else return fail(ctx, LK_EINVAL_ARG, "lk_set_option: unknown option " + n);
+    return LK_OK;
+}
+
+int64_t lk_get_option(lk_ctx *ctx, const char *name) {
+    if (!ctx || !name) return -1;
+    const std::string n(name);
+    if (n == "gemv_pdl") return ctx->pdl_mode;
+    if (n == "gemv_warps") return ctx->tune.variant;
+    if (n == "gemv_stage_bytes") return ctx->tune.stage_bytes;
+    if (n == "gemv_max_stages") return ctx->tune.max_stages;
+    if (n == "gemv_smem_budget") return ctx->tune.smem_budget;
+    if (n == "gemv_ctas_per_sm") return ctx->tune.ctas_per_sm;
+    return -1;
+}
+
+}  // extern "C"

@@ -1,0 +1,58 @@
+// lk_shim.h — internal structs behind the opaque handles of llamakotlin_cuda.h
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/llamakotlin_cuda.h"
+#include "lk_kernels.h"
+
+struct lk_ctx {
+    int device = 0;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::string err;
+    int64_t launches = 0;
+    lk::GemvTuning tune;
+    int pdl_mode = 1;  // 0 never, 1 inside captured sequences, 2 always
+    bool capturing = false;
+    int64_t capture_launches = 0;
+    // device staging arena for host-resident tensors (bump allocated per op)
+    uint8_t *arena = nullptr;
+    size_t arena_size = 0, arena_used = 0;
+    // K2 workspace (FP16 copy of the activations)
+    void *gemm_ws = nullptr;
+    size_t gemm_ws_size = 0;
+    // multi-GPU
+    void *comm = nullptr;  // ncclComm_t
+    int nranks = 1, rank = 0;
+    uint32_t *peer_flags = nullptr;
+};
+
+struct lk_buf {
+    lk_ctx *ctx = nullptr;
+    void *ptr = nullptr;
+    uint64_t size = 0;
+    bool imported = false;  // opened from an IPC handle (peer memory)
+};
+
+struct lk_graph {
+    lk_ctx *ctx = nullptr;
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    int64_t launches = 0;  // kernels per replay
+};
+
+namespace lk {
+lk_status fail(lk_ctx *ctx, lk_status st, const std::string &msg);
+lk_status cuda_fail(lk_ctx *ctx, cudaError_t e, const char *what);
+}  // namespace lk
+
+#define LK_CUDA(ctx, call)                                             \
+    do {                                                               \
+        cudaError_t e__ = (call);                                      \
+        if (e__ != cudaSuccess) return lk::cuda_fail(ctx, e__, #call); \
+    } while (0)

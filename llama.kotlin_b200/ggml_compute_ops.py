@@ -1,0 +1,145 @@
+"""Destination-based compute ops with the reference's names and argument meaning
+(core/GGMLComputeOps.kt): computeMatMul :1435, computeAdd :735, computeMul :811,
+dequantizeTensor :918, plus the RMS_NORM / SILU / SOFT_MAX ops the reference leaves
+unimplemented (semantics from its tests).  Every op is a C-ABI call into
+libllamakotlin_cuda.so — there is no host arithmetic and no fallback in this file."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _binding as B
+from .ggml_types import GGMLContext, GGMLTensor, GGMLType
+
+_default_ctx = None
+
+
+class LkContext:
+    """Owns one lk_ctx (device + stream)."""
+
+    def __init__(self, device: int = 0):
+        h = C.c_void_p()
+        B.check(B.lib().lk_ctx_create(device, C.byref(h)))
+        self.handle = h
+        self.device = device
+
+    def sync(self) -> None:
+        B.check(B.lib().lk_sync(self.handle), self.handle)
+
+    def set_option(self, name: str, value: int) -> None:
+        B.check(B.lib().lk_set_option(self.handle, name.encode(), int(value)), self.handle)
+
+    def launch_count(self) -> int:
+        return int(B.lib().lk_ctx_launch_count(self.handle))
+
+    def sm_count(self) -> int:
+        return int(B.lib().lk_ctx_sm_count(self.handle))
+
+    def timer_start(self) -> None:
+        B.check(B.lib().lk_timer_start(self.handle), self.handle)
+
+    def timer_stop(self) -> float:
+        ms = C.c_float()
+        B.check(B.lib().lk_timer_stop(self.handle, C.byref(ms)), self.handle)
+        return float(ms.value)
+
+    def close(self) -> None:
+        if self.handle:
+            B.lib().lk_ctx_destroy(self.handle)
+            self.handle = None
+
+
+def default_context(device: int = 0) -> LkContext:
+    global _default_ctx
+    if _default_ctx is None or _default_ctx.handle is None:
+        _default_ctx = LkContext(device)
+    return _default_ctx
+
+
+def _ctx_of(graphAllocator) -> LkContext:
+    be = getattr(graphAllocator, "backend", None)
+    if be is not None and getattr(be, "lk", None) is not None:
+        return be.lk
+    return default_context()
+
+
+def describe(graphAllocator, t: GGMLTensor) -> B.lk_tensor:
+    """GGMLTensor -> lk_tensor: (buffer, dataOffset) pair, never tensor.data."""
+    d = B.lk_tensor()
+    d.type = int(t.type)
+    for i in range(4):
+        d.ne[i] = int(t.ne[i])
+        d.nb[i] = 0 if t.type.isBlockType else int(t.nb[i])
+    d.data_offset = int(t.dataOffset)
+    if t.buffer is not None:                      # device-resident (GGMLCudaBuffer)
+        d.dev_buf = t.buffer.handle
+        d.buffer_size = t.buffer.getSize()
+        return d
+    bufs = graphAllocator.buffers
+    if t.bufferId < 0 or t.bufferId >= len(bufs) or bufs[t.bufferId] is None:
+        # core/GGMLTypes.kt:552-553
+        raise B.IllegalStateException(f"Tensor buffer not found for bufferId {t.bufferId} for tensor '{t.name}'.")
+    arr = bufs[t.bufferId]
+    d.host_base = arr.ctypes.data
+    d.buffer_size = arr.size
+    return d
+
+
+def computeMatMul(graphAllocator, context: GGMLContext, a: GGMLTensor, b: GGMLTensor, dst: GGMLTensor) -> None:
+    lk = _ctx_of(graphAllocator)
+    B.check(B.lib().lk_compute_matmul(lk.handle, describe(graphAllocator, a), describe(graphAllocator, b),
+                                      describe(graphAllocator, dst)), lk.handle)
+
+
+def computeAdd(graphAllocator, context, a, b, dst) -> None:
+    lk = _ctx_of(graphAllocator)
+    B.check(B.lib().lk_compute_add(lk.handle, describe(graphAllocator, a), describe(graphAllocator, b),
+                                   describe(graphAllocator, dst)), lk.handle)
+
+
+def computeMul(graphAllocator, context, a, b, dst) -> None:
+    lk = _ctx_of(graphAllocator)
+    B.check(B.lib().lk_compute_mul(lk.handle, describe(graphAllocator, a), describe(graphAllocator, b),
+                                   describe(graphAllocator, dst)), lk.handle)
+
+
+def computeSilu(graphAllocator, context, a, dst) -> None:
+    lk = _ctx_of(graphAllocator)
+    B.check(B.lib().lk_compute_silu(lk.handle, describe(graphAllocator, a), describe(graphAllocator, dst)), lk.handle)
+
+
+def computeSiluMul(graphAllocator, context, gate, up, dst) -> None:
+    lk = _ctx_of(graphAllocator)
+    B.check(B.lib().lk_compute_silu_mul(lk.handle, describe(graphAllocator, gate), describe(graphAllocator, up),
+                                        describe(graphAllocator, dst)), lk.handle)
+
+
+def computeRmsNorm(graphAllocator, context, a, weight, eps: float, dst) -> None:
+    lk = _ctx_of(graphAllocator)
+    w = describe(graphAllocator, weight) if weight is not None else None
+    B.check(B.lib().lk_compute_rms_norm(lk.handle, describe(graphAllocator, a), w, float(eps),
+                                        describe(graphAllocator, dst)), lk.handle)
+
+
+def computeSoftMax(graphAllocator, context, a, dst) -> None:
+    lk = _ctx_of(graphAllocator)
+    B.check(B.lib().lk_compute_softmax(lk.handle, describe(graphAllocator, a), describe(graphAllocator, dst)), lk.handle)
+
+
+def dequantizeTensor(graphAllocator, tensor: GGMLTensor) -> GGMLTensor:
+    """core/GGMLComputeOps.kt:918 — returns an F32 tensor whose `data` holds the floats
+    (like the reference, the result lives in result.data, not in the allocator: SURVEY F8)."""
+    lk = _ctx_of(graphAllocator)
+    n = tensor.numElements()
+    out = np.empty(n, dtype=np.float32)
+    res = GGMLTensor(type=GGMLType.F32, ne=list(tensor.ne))
+    d = B.lk_tensor()
+    d.type = int(GGMLType.F32)
+    for i in range(4):
+        d.ne[i] = int(tensor.ne[i])
+    d.host_base = out.ctypes.data
+    d.buffer_size = out.nbytes
+    B.check(B.lib().lk_compute_dequantize(lk.handle, describe(graphAllocator, tensor), d), lk.handle)
+    res.data = out
+    return res
