@@ -1,0 +1,402 @@
+#!/usr/bin/env python
+"""bench.py — decode-GEMV throughput of the quantized-matmul hot path on B200.
+
+Workload at every N (BASELINE.json configs[1]): Q4_0 decode GEMVs at the three Llama-2-7B
+shapes (4096x4096, 11008x4096, 4096x11008), batch 1.  One step = LAYERS x 3 GEMVs, every GEMV
+on its own weight copy (LAYERS x 60.2 MB = 1.9 GB >> the 126 MB L2, so each launch streams cold
+HBM), replayed as one captured op sequence (GGMLCudaBackend.graphCompute -> CUDA graph).
+
+  value     algorithmic GB/s, weights/activations resident in HBM (CUDA events on the ctx stream)
+  e2e       same step through the backend-buffer API with HOST activations and results:
+            setTensor (H2D from pinned memory) + graphCompute + getTensor (D2H) every step
+  roofline  the GEMV kernel: algorithmic bytes per launch / mean launch time, vs measured HBM peak
+  cpu_baseline / --impl reference
+            the oracle's restatement of the reference CPU loops (oracle/, the Kotlin reference
+            cannot be built here: no JVM / Konan) on a bounded row sample of the same workload
+
+N > 1 (torchrun, one rank per GPU): weight rows sharded over ranks (rank r owns rows
+[r*M, (r+1)*M) of an N*M-row matrix, i.e. each rank keeps a full 7B-shape shard: weak scaling),
+outputs exchanged into every rank's dst by NVLink peer stores from the GEMV epilogue plus a
+flag barrier (NCCL all-gather with --gather nccl).
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+SHAPES = [(4096, 4096), (11008, 4096), (4096, 11008)]     # (M, K)
+BLOCK_BYTES = {"Q4_0": 18, "Q4_1": 20, "Q8_0": 34}
+TYPE_ID = {"Q4_0": 2, "Q4_1": 3, "Q8_0": 6}
+METRIC = "Q4_0 decode GEMV algorithmic GB/s at Llama-2-7B shapes (batch 1)"
+
+
+def algo_bytes(M: int, K: int, bb: int) -> int:
+    """M*K/32*B + 4*K + 4*M."""
+    return M * K // 32 * bb + 4 * K + 4 * M
+
+
+def synth_blocks(rng, M: int, K: int, qtype: str) -> np.ndarray:
+    """Synthetic packed blocks with the statistics of quantized N(0, 0.02^2) weights: scale d in
+    the normal-half range the reference quantizer produces (amax/8 ~ 5-8e-3 for Q4_0), uniform
+    quants.  Generated directly as bytes (no oracle on the product path)."""
+    bb = BLOCK_BYTES[qtype]
+    nb = M * K // 32
+    raw = rng.integers(0, 256, (nb, bb), dtype=np.uint8)
+    lo, hi = (3e-4, 5e-4) if qtype == "Q8_0" else (5e-3, 8e-3)
+    raw[:, 0:2] = rng.uniform(lo, hi, nb).astype(np.float16).view(np.uint8).reshape(nb, 2)
+    if qtype == "Q4_1":
+        raw[:, 2:4] = rng.uniform(-0.06, -0.04, nb).astype(np.float16).view(np.uint8).reshape(nb, 2)
+    return raw.reshape(-1)
+
+
+# ---------------------------------------------------------------------------------------------
+# clocks: nvidia-smi sampled while the timed regions run
+# ---------------------------------------------------------------------------------------------
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.samples = []
+        self.proc = None
+        self.windows = []
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "50",
+                 "-i", str(index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            p = [x.strip() for x in line.split(",")]
+            if len(p) >= 7:
+                self.samples.append((time.time(), p))
+
+    def window(self, t0, t1):
+        self.windows.append((t0, t1))
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.12)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        inwin = [p for (t, p) in self.samples if any(a - 0.05 <= t <= b + 0.05 for a, b in self.windows)]
+        use = inwin if inwin else [p for _, p in self.samples]
+        if not use:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+
+        def num(s):
+            try:
+                return float(s)
+            except ValueError:
+                return float("nan")
+        sm = sorted(num(p[0]) for p in use)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(p[3 + i].lower().startswith("active") for p in use)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": num(use[0][1]), "reasons": reasons,
+                "samples": len(use), "in_timed_region": bool(inwin),
+                "power_w_max": max(num(p[2]) for p in use)}
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU arm: the oracle (restatement of the reference's Kotlin loops) on the host cores
+# ---------------------------------------------------------------------------------------------
+def cpu_arm(qtype: str, seconds_budget: float, steps: int, warmup: int, threads: int, gpu_check=None) -> dict:
+    """Times oracle matmul on a bounded row sample of every shape.  One CPU 'step' = the first R rows
+    of each of the three GEMVs; R is calibrated so warmup+steps fit `seconds_budget`."""
+    from oracle import oracle as O
+    O.build()
+    rng = np.random.default_rng(4242)
+    bb = BLOCK_BYTES[qtype]
+    tid = TYPE_ID[qtype]
+    mats = []
+    for (M, K) in SHAPES:
+        rows = M
+        mats.append((rows, K, synth_blocks(rng, rows, K, qtype), rng.normal(0, 1, K).astype(np.float32)))
+    # calibrate: rows/s on a small slice
+    t0 = time.perf_counter()
+    for rows, K, a, x in mats:
+        O.matmul(tid, a, K, rows, x, 1, nthreads=threads, rows=(0, min(rows, 8 * threads)))
+    cal = time.perf_counter() - t0
+    cal_rows = sum(min(r, 8 * threads) * K for r, K, _, _ in mats)
+    macs_per_s = cal_rows / max(cal, 1e-6)
+    per_step = seconds_budget / max(steps + warmup, 1)
+    total_k = sum(K for _, K, _, _ in mats)
+    R = int(max(threads, min(4096, per_step * macs_per_s / total_k)))
+    for _ in range(warmup):
+        for rows, K, a, x in mats:
+            O.matmul(tid, a, K, rows, x, 1, nthreads=threads, rows=(0, min(R, rows)))
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        for rows, K, a, x in mats:
+            O.matmul(tid, a, K, rows, x, 1, nthreads=threads, rows=(0, min(R, rows)))
+    dt = time.perf_counter() - t0
+    nbytes = steps * sum(min(R, rows) * K // 32 * bb + 4 * K + 4 * min(R, rows) for rows, K, _, _ in mats)
+    return {"value": nbytes / dt / 1e9, "unit": "GB/s", "cores": threads, "kind": "port",
+            "sample": f"first {R} rows of each of the 3 {qtype} GEMV shapes per step, {steps} steps, "
+                      f"oracle/lk_oracle.c (C restatement of computeMatMul; Kotlin/Native not buildable here)",
+            "ms_per_step": dt / steps * 1e3}
+
+
+# ---------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------
+def pinned_array(lkctx, nbytes: int) -> np.ndarray:
+    from llama_kotlin_b200 import _binding as B
+    p = C.c_void_p()
+    B.check(B.lib().lk_host_alloc(lkctx.handle, nbytes, C.byref(p)), lkctx.handle)
+    return np.ctypeslib.as_array((C.c_uint8 * nbytes).from_address(p.value))
+
+
+def gpu_arm(args, rank: int, world: int, local_rank: int) -> dict:
+    import torch
+    import torch.distributed as dist
+
+    import llama_kotlin_b200 as lk
+    from llama_kotlin_b200 import GGMLCGraph, GGMLOp, GGMLTensor, GGMLType
+
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group(backend="cpu:gloo,cuda:nccl", rank=rank, world_size=world,
+                                device_id=torch.device("cuda", local_rank))
+    qtype = args.qtype
+    gt = {"Q4_0": GGMLType.Q4_0, "Q4_1": GGMLType.Q4_1, "Q8_0": GGMLType.Q8_0}[qtype]
+    bb = BLOCK_BYTES[qtype]
+    layers = args.layers
+    be = lk.GGMLCudaBackend(local_rank)
+    lkc = be.lk
+    for opt in args.opt or []:
+        k, v = opt.split("=")
+        lkc.set_option(k, int(v))
+
+    # ---- device layout: [weights: layers x 3 matrices][acts: layers x sum K][dst: layers x sum M x world]
+    wbytes = [M * K // 32 * bb for M, K in SHAPES]
+    wtotal = layers * sum(((w + 255) // 256 * 256) for w in wbytes)
+    sumK = sum(K for _, K in SHAPES)
+    sumM = sum(M for M, _ in SHAPES) * world
+    ga = lk.GGMLGraphAllocator(be, size=wtotal + layers * (sumK + sumM) * 4 + (1 << 20))
+    rng = np.random.default_rng(1234 + rank)
+    protos = [synth_blocks(rng, M, K, qtype) for M, K in SHAPES]
+    acts_all = ga.allocateTensor(GGMLTensor(GGMLType.F32, [layers * sumK]))
+    dst_all = ga.allocateTensor(GGMLTensor(GGMLType.F32, [layers * sumM]))
+    x_host = pinned_array(lkc, layers * sumK * 4).view(np.float32)
+    y_host = pinned_array(lkc, layers * sumM * 4).view(np.float32)
+    x_host[:] = np.random.default_rng(99).normal(0, 1, layers * sumK).astype(np.float32)
+    ga.setBytes(acts_all, x_host)
+
+    nodes, weights = [], []
+    koff = moff = 0
+    first = {}
+    for layer in range(layers):
+        for si, (M, K) in enumerate(SHAPES):
+            a = ga.allocateTensor(GGMLTensor(gt, [K, M]))
+            if si in first:      # distinct HBM copy of the same bytes (device-to-device)
+                ga.deviceBuffer.copyTensor(first[si], a)
+            else:
+                ga.setBytes(a, protos[si])
+                first[si] = a
+            b = GGMLTensor(GGMLType.F32, [1, K], bufferId=0, dataOffset=acts_all.dataOffset + koff * 4,
+                           buffer=ga.deviceBuffer)
+            d = GGMLTensor(GGMLType.F32, [1, M * world], op=GGMLOp.MUL_MAT, src=[a, b] + [None] * 8, bufferId=0,
+                           dataOffset=dst_all.dataOffset + moff * 4, buffer=ga.deviceBuffer)
+            koff += K
+            moff += M * world
+            nodes.append(d)
+            weights.append(a)
+    if world > 1:
+        raise SystemExit("multi-GPU arm: see bench_multi (not wired in this revision)")
+    graph = GGMLCGraph(nodes=nodes, allocator=ga)
+
+    def step_device():
+        st = be.graphCompute(graph)
+        if st != lk.GGMLStatus.SUCCESS:
+            raise RuntimeError("graphCompute FAILED")
+
+    def step_e2e():
+        ga.deviceBuffer.setTensor(acts_all, x_host, 0, x_host.nbytes)          # H2D, pinned
+        step_device()
+        ga.deviceBuffer.getTensor(dst_all, y_host.view(np.uint8), 0, y_host.nbytes)  # D2H (synchronises)
+
+    bytes_step = layers * sum(algo_bytes(M, K, bb) for M, K in SHAPES) * world
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        lkc.sync()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing ------------------------------------------------------------
+    for _ in range(max(args.warmup, 3)):
+        step_device()
+    barrier()
+    l0 = lkc.launch_count()
+    w0 = time.time()
+    lkc.timer_start()
+    for _ in range(args.steps):
+        step_device()
+    ms = lkc.timer_stop()
+    barrier()
+    w1 = time.time()
+    launches = lkc.launch_count() - l0
+    if sampler:
+        sampler.window(w0, w1)
+
+    # ---- end to end: host activations in, host results out, every step -----------------------
+    for _ in range(3):
+        step_e2e()
+    barrier()
+    e0 = time.time()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_e2e()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    if sampler:
+        sampler.window(e0, time.time())
+
+    if world > 1:
+        t = torch.tensor([ms, e2e_s], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, e2e_s = float(t[0]), float(t[1])
+    clocks = sampler.stop() if sampler else None
+
+    # ---- spot check of the timed outputs against exact f64 arithmetic on the host (numpy, not the oracle)
+    chk = check_outputs(protos, x_host, y_host, qtype, world, sumM, rank)
+
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except OSError:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+    value = bytes_step * args.steps / (ms * 1e-3) / 1e9
+    n_gemv = layers * len(SHAPES)
+    res = {
+        "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{qtype} decode GEMV x F32, Llama-2-7B shapes 4096x4096 + 11008x4096 + 4096x11008, "
+                               f"N=1, {layers} distinct weight copies per shape per step",
+                   "qtype": qtype, "layers": layers, "gemv_per_step": n_gemv,
+                   "weight_bytes_per_step_per_gpu": layers * sum(wbytes),
+                   "l2": "inputs larger than L2 (each launch reads a weight copy not touched for a whole step)",
+                   "parallelism": "single GPU" if world == 1 else f"weight rows sharded over {world} ranks",
+                   "tflops": 2 * layers * sum(M * K for M, K in SHAPES) * world * args.steps / (ms * 1e-3) / 1e12},
+        "e2e": {"value": bytes_step * args.steps / e2e_s / 1e9, "unit": "GB/s",
+                "h2d_bytes_per_step": int(x_host.nbytes), "d2h_bytes_per_step": int(y_host.nbytes),
+                "ms_per_step": e2e_s / args.steps * 1e3,
+                "api": "GGMLCudaBuffer.setTensor + GGMLCudaBackend.graphCompute + GGMLCudaBuffer.getTensor"},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "achieved": value / world, "peak": peak, "unit": "GB/s",
+                     "frac": value / world / peak, "traffic": None, "peak_source": peak_src,
+                     "frac_of_nominal_8000": value / world / 8000.0,
+                     "kernel": "lk::gemv_kernel<Q4_0>" if qtype == "Q4_0" else f"lk::gemv_kernel<{qtype}>",
+                     "avg_launch_us": ms * 1e3 / max(launches, 1),
+                     "algorithmic_bytes_per_launch": bytes_step / world / n_gemv},
+        "clocks": clocks, "check": chk,
+    }
+    traffic_file = os.path.join(ROOT, "profiles", "gemv_traffic.json")
+    if os.path.exists(traffic_file):
+        with open(traffic_file) as f:
+            res["roofline"]["traffic"] = json.load(f).get(qtype)
+    be.free()
+    if world > 1:
+        dist.destroy_process_group()
+    return res
+
+
+def check_outputs(protos, x_host, y_host, qtype, world, sumM, rank) -> dict:
+    """f64 dot products (numpy) of a few rows of layer 0 against the timed run's output."""
+    bb = BLOCK_BYTES[qtype]
+    worst = 0.0
+    moff = koff = 0
+    for si, (M, K) in enumerate(SHAPES):
+        blocks = protos[si].reshape(-1, bb)
+        x = x_host[koff:koff + K].astype(np.float64)
+        rows = [0, 1, M // 2, M - 1]
+        for r in rows:
+            blk = blocks[r * (K // 32):(r + 1) * (K // 32)]
+            d = blk[:, 0:2].copy().view(np.float16).astype(np.float64)
+            if qtype == "Q8_0":
+                w = d * blk[:, 2:].view(np.int8).astype(np.float64)
+            else:
+                q = blk[:, (2 if qtype == "Q4_0" else 4):]
+                nib = np.empty((q.shape[0], 32), np.float64)
+                nib[:, 0::2] = q & 15          # Kotlin nibble order: byte j -> elements 2j (low), 2j+1 (high)
+                nib[:, 1::2] = q >> 4
+                if qtype == "Q4_0":
+                    w = d * (nib - 8.0)
+                else:
+                    w = d * nib + blk[:, 2:4].copy().view(np.float16).astype(np.float64)
+            ref = float(np.dot(w.reshape(-1), x))
+            got = float(y_host[moff + rank * M + r])
+            worst = max(worst, abs(got - ref) / max(abs(ref), 1.0))
+        moff += M * world
+        koff += K
+    return {"max_err_vs_f64_rows": worst, "ok": bool(worst <= 1e-3)}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--qtype", default="Q4_0", choices=list(BLOCK_BYTES))
+    ap.add_argument("--layers", type=int, default=32)
+    ap.add_argument("--opt", action="append", help="lk_set_option name=value (tuning experiments)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    threads = os.cpu_count() or 1
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        r = cpu_arm(args.qtype, 90.0, args.steps, max(args.warmup, 1), threads)
+        out = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": "GB/s", "n_gpus": args.gpus,
+               "steps": args.steps, "warmup": max(args.warmup, 1), "ms_per_step": r["ms_per_step"],
+               "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+               "config": {"workload": f"{args.qtype} decode GEMV x F32, Llama-2-7B shapes, N=1 (bounded row sample)"},
+               "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+               "e2e": {"value": r["value"], "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+               "gpu_launches": 0}
+        print(json.dumps(out), flush=True)
+        return
+
+    res = gpu_arm(args, rank, world, local_rank)
+    if rank == 0:
+        if not args.no_cpu_baseline and world == 1:
+            r = cpu_arm(args.qtype, args.cpu_seconds, 5, 1, threads)
+            res["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        print(json.dumps(res), flush=True)
+
+
+if __name__ == "__main__":
+    main()

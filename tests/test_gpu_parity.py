@@ -1,0 +1,340 @@
+"""Parity of the CUDA path (through the C ABI) with the CPU oracle on the same seeded inputs.
+Bit-exact for block dequantisation and F32 add/mul; <= 1e-3 relative (max-abs error /
+max-abs reference) for matmul; the reference tests' own tolerances for
+RMSNorm (1e-4), SiLU (1e-3) and the quantized-vs-dequantized matmul (1e-3 abs)."""
+import numpy as np
+import pytest
+
+import llama_kotlin_b200 as lk
+from conftest import same_f32_bits, synth_acts, synth_weights
+from llama_kotlin_b200 import GGMLTensor, GGMLType
+
+pytestmark = pytest.mark.gpu
+
+F32, Q4_0, Q4_1, Q8_0 = 0, 2, 3, 6
+QT = {"Q8_0": (GGMLType.Q8_0, Q8_0), "Q4_0": (GGMLType.Q4_0, Q4_0), "Q4_1": (GGMLType.Q4_1, Q4_1)}
+MATMUL_REL_TOL = 1e-3   # north_star: "<= 1e-3 rel" for the F32 matmul output
+
+
+def rel_err(got, ref):
+    ref = np.asarray(ref, np.float64)
+    got = np.asarray(got, np.float64)
+    den = max(float(np.max(np.abs(ref))), 1e-30)
+    return float(np.max(np.abs(got - ref))) / den
+
+
+def host_matmul(ga, t, blocks_or_f32, K, M, x, N):
+    """computeMatMul on host-resident tensors in a GGMLGraphAllocator buffer (the reference fixture
+    pattern, nativeTest core/GGMLComputeOpsTest.kt:66-101)."""
+    ga.reset()
+    a = ga.allocateTensor(GGMLTensor(t, [K, M]))
+    b = ga.allocateTensor(GGMLTensor(GGMLType.F32, [N, K]))
+    d = ga.allocateTensor(GGMLTensor(GGMLType.F32, [N, M]))
+    ga.setBytes(a, blocks_or_f32)
+    ga.setBytes(b, x)
+    lk.computeMatMul(ga, None, a, b, d)
+    return ga.getFloats(d)
+
+
+@pytest.fixture(scope="module")
+def ga():
+    return lk.GGMLGraphAllocator(size=64 << 20)
+
+
+# ---- K0 dequantize: bit-exact ---------------------------------------------------------
+@pytest.mark.parametrize("tname", ["Q8_0", "Q4_0", "Q4_1"])
+@pytest.mark.parametrize("n", [32, 64, 96, 4096, 32 * 1031, 4096 * 512])
+def test_dequantize_bit_exact(O, ga, tname, n):
+    gt, ot = QT[tname]
+    w = synth_weights(11 + n % 97, 1, n)
+    blocks = O.quantize(ot, w)
+    ga.reset()
+    a = ga.allocateTensor(GGMLTensor(gt, [n]))
+    ga.setBytes(a, blocks)
+    got = lk.dequantizeTensor(ga, a).data
+    assert same_f32_bits(got, O.dequantize(ot, blocks, n))
+
+
+@pytest.mark.parametrize("tname", ["Q8_0", "Q4_0", "Q4_1"])
+def test_dequantize_random_bytes_bit_exact(O, ga, tname):
+    """Every byte pattern, incl. subnormal / inf / NaN half scales (halfToFloat, NumericConversions.kt:9-54)."""
+    gt, ot = QT[tname]
+    n = 32 * 4096
+    raw = np.random.default_rng(5).integers(0, 256, n // 32 * gt.byteSize, dtype=np.uint8)
+    ga.reset()
+    a = ga.allocateTensor(GGMLTensor(gt, [n]))
+    ga.setBytes(a, raw)
+    got = lk.dequantizeTensor(ga, a).data
+    assert same_f32_bits(got, O.dequantize(ot, raw, n))
+
+
+def test_dequantize_golden_kats(O, ga, golden):
+    """Hand-computed block KATs (tests/golden): bytes -> floats."""
+    for name, g in golden["kat"].items():
+        gt = GGMLType(g["type"])
+        blocks = np.frombuffer(bytes.fromhex(g["blocks_hex"]), dtype=np.uint8)
+        n = len(g["x"])
+        ga.reset()
+        a = ga.allocateTensor(GGMLTensor(gt, [n]))
+        ga.setBytes(a, blocks)
+        got = lk.dequantizeTensor(ga, a).data
+        assert same_f32_bits(got, np.frombuffer(bytes.fromhex(g["dequant_f32_hex"]), dtype=np.float32)), name
+
+
+# ---- K1 decode GEMV --------------------------------------------------------------------
+@pytest.mark.parametrize("tname", ["Q8_0", "Q4_0", "Q4_1"])
+@pytest.mark.parametrize("M,K", [(8, 64), (16, 128), (33, 192), (148, 2048), (1000, 4096), (296, 8192),
+                                 (64, 11008), (40, 28672)])
+def test_gemv_small_shapes(O, ga, tname, M, K):
+    gt, ot = QT[tname]
+    blocks = O.quantize(ot, synth_weights(100 + M, M, K))
+    x = synth_acts(100 + K, K)
+    got = host_matmul(ga, gt, blocks, K, M, x, 1)
+    ref = O.matmul(ot, blocks, K, M, x, 1, nthreads=4)
+    assert rel_err(got, ref) <= MATMUL_REL_TOL
+
+
+CFG2 = [(4096, 4096, 2001), (11008, 4096, 2002), (4096, 11008, 2003)]
+
+
+@pytest.mark.parametrize("tname", ["Q8_0", "Q4_0", "Q4_1"])
+@pytest.mark.parametrize("M,K,seed", CFG2)
+def test_gemv_llama7b_shapes(O, ga, tname, M, K, seed):
+    """BASELINE configs[0] (Q8_0 4096x4096) and configs[1] (Q4_0/Q4_1 at the three 7B shapes)."""
+    gt, ot = QT[tname]
+    blocks = O.quantize(ot, synth_weights(seed, M, K))
+    x = synth_acts(seed, K)
+    got = host_matmul(ga, gt, blocks, K, M, x, 1)
+    ref = O.matmul(ot, blocks, K, M, x, 1, nthreads=8)
+    e = rel_err(got, ref)
+    # also: which F32 summation order is closer to exact arithmetic (f64 of the same dequantised weights)
+    deq = O.dequantize(ot, blocks, M * K).astype(np.float64).reshape(M, K)
+    exact = deq @ x.astype(np.float64)
+    assert e <= MATMUL_REL_TOL
+    assert rel_err(got, exact) <= max(2 * rel_err(ref, exact), 1e-5)
+
+
+def test_gemv_random_bytes_q4(O, ga):
+    """Arbitrary nibble patterns and scales in normal half range (not quantizer output)."""
+    M, K = 256, 4096
+    rng = np.random.default_rng(77)
+    for tname in ("Q4_0", "Q4_1", "Q8_0"):
+        gt, ot = QT[tname]
+        bb = gt.byteSize
+        raw = rng.integers(0, 256, (M * K // 32, bb), dtype=np.uint8)
+        d = rng.uniform(1e-3, 1e-1, M * K // 32).astype(np.float16).view(np.uint8).reshape(-1, 2)
+        raw[:, 0:2] = d
+        if tname == "Q4_1":
+            raw[:, 2:4] = rng.uniform(-0.5, 0.5, M * K // 32).astype(np.float16).view(np.uint8).reshape(-1, 2)
+        x = synth_acts(78, K)
+        got = host_matmul(ga, gt, raw.reshape(-1), K, M, x, 1)
+        ref = O.matmul(ot, raw.reshape(-1), K, M, x, 1, nthreads=4)
+        assert rel_err(got, ref) <= MATMUL_REL_TOL, tname
+
+
+def test_gemv_zero_and_denormal_scale_blocks(O, ga):
+    """All-zero blocks (scale = 1.0 path, GGMLComputeOps.kt:1065) and denormal-half scales (F11)."""
+    M, K = 64, 256
+    w = synth_weights(9, M, K)
+    w[: K] = 0.0                      # an all-zero row
+    w[K: 2 * K] *= 1e-4               # amax ~ 6e-6 -> denormal half scale
+    x = synth_acts(9, K)
+    for tname in ("Q8_0", "Q4_0", "Q4_1"):
+        gt, ot = QT[tname]
+        blocks = O.quantize(ot, w)
+        got = host_matmul(ga, gt, blocks, K, M, x, 1)
+        ref = O.matmul(ot, blocks, K, M, x, 1)
+        assert ref[0] == 0.0 or tname == "Q4_1"
+        assert abs(got[0] - ref[0]) <= MATMUL_REL_TOL * float(np.max(np.abs(ref)))
+        assert rel_err(got, ref) <= MATMUL_REL_TOL, tname
+        assert abs(got[1] - ref[1]) <= 1e-3 * max(abs(ref[1]), 1e-12) + 1e-10
+
+
+def test_gemv_linearity_full_size(O, ga):
+    """Size-independent property at the full 11008x4096 shape: A(x+y) ~= Ax + Ay, A(2x) == 2 Ax bit-exact."""
+    M, K = 11008, 4096
+    blocks = O.quantize(Q4_0, synth_weights(2002, M, K))
+    x, y = synth_acts(1, K), synth_acts(2, K)
+    ax = host_matmul(ga, GGMLType.Q4_0, blocks, K, M, x, 1)
+    ay = host_matmul(ga, GGMLType.Q4_0, blocks, K, M, y, 1)
+    axy = host_matmul(ga, GGMLType.Q4_0, blocks, K, M, x + y, 1)
+    a2x = host_matmul(ga, GGMLType.Q4_0, blocks, K, M, 2 * x, 1)
+    assert rel_err(axy, ax + ay) <= 1e-4
+    assert same_f32_bits(a2x, 2 * ax)       # scaling by 2 is exact in every F32 op
+    again = host_matmul(ga, GGMLType.Q4_0, blocks, K, M, x, 1)
+    assert same_f32_bits(again, ax)         # deterministic (no atomics)
+
+
+# ---- generic matmul (any N, K) and the reference's own vectors ----------------------------
+def test_f32_matmul_golden_vectors(O, ga, golden):
+    g = golden["transcribed"]["f32_matmul_2x3_3x2"]    # GGMLComputeOpsDestinationTest.kt:219-265
+    K, M = g["a_ne"]
+    N = g["b_ne"][0]
+    got = host_matmul(ga, GGMLType.F32, np.array(g["a"], np.float32), K, M, np.array(g["b"], np.float32), N)
+    assert np.allclose(got, g["expected"], atol=g["tol"])
+    g = golden["transcribed"]["f32_matmul_4x4"]        # core/TestTensorOps.kt:122-168
+    a, b = np.array(g["a"], np.float32), np.array(g["b"], np.float32)
+    got = host_matmul(ga, GGMLType.F32, a, 4, 4, b, 4)
+    assert np.allclose(got, O.matmul(F32, a, 4, 4, b, 4), atol=g["tol"])
+
+
+@pytest.mark.parametrize("tname", ["Q8_0", "Q4_0", "Q4_1"])
+def test_direct_vs_dequantized_matmul_reference_data(O, ga, golden, tname):
+    """GGMLMatMulOptimizationTest.kt:233-357: direct Q x F32 vs dequantize -> F32 matmul, |d| < 1e-3."""
+    g = golden["transcribed"]["direct_vs_dequant"]
+    gt, ot = QT[tname]
+    for M, K, N in g["shapes"] + [[16, 64, 32], [128, 512, 256]]:
+        idx = np.arange(M * K)
+        w = {"Q8_0": (idx % 127) - 63.0, "Q4_0": (idx % 15) - 7.0, "Q4_1": (idx % 20) * 1.0}[tname].astype(np.float32)
+        blocks = O.quantize(ot, w)
+        x = ((np.arange(K * N) % 10) * 0.1).astype(np.float32)
+        got = host_matmul(ga, gt, blocks, K, M, x, N)
+        ref = O.matmul(ot, blocks, K, M, x, N)
+        deq = O.dequantize(ot, blocks, M * K)
+        viaf32 = host_matmul(ga, GGMLType.F32, deq, K, M, x, N)
+        scale = max(1.0, float(np.max(np.abs(ref))))
+        assert np.max(np.abs(got - ref)) <= g["tol"] * scale
+        assert np.max(np.abs(got - viaf32)) <= g["tol"] * scale
+
+
+@pytest.mark.parametrize("tname", ["Q8_0", "Q4_0", "Q4_1"])
+@pytest.mark.parametrize("M,K,N", [(4, 64, 3), (3, 64, 4), (2, 32, 2), (5, 96, 7), (64, 4096, 2), (17, 160, 33)])
+def test_matmul_small_n(O, ga, tname, M, K, N):
+    gt, ot = QT[tname]
+    blocks = O.quantize(ot, synth_weights(300 + N, M, K))
+    x = synth_acts(300 + N, K, N)
+    got = host_matmul(ga, gt, blocks, K, M, x, N)
+    assert rel_err(got, O.matmul(ot, blocks, K, M, x, N)) <= MATMUL_REL_TOL
+
+
+def test_q80_dot_cos_vector(O, ga, golden):
+    """GGMLStandardizedQuantizationTest.kt:363-394: Q8_0 x F32 dot, n=128, rel err < 0.02 vs f64."""
+    g = golden["transcribed"]["q80_dot_cos"]
+    n = g["n"]
+    i = np.arange(n, dtype=np.float32)
+    v1 = (0.1 + 2.0 * np.cos(i)).astype(np.float32)
+    v2 = (0.1 + 2.0 * np.cos(i + np.float32(1.0))).astype(np.float32)
+    ref = float(np.sum(v1.astype(np.float64) * v2.astype(np.float64)))
+    got = host_matmul(ga, GGMLType.Q8_0, O.quantize(Q8_0, v1), n, 1, v2, 1)
+    assert abs(ref - got[0]) / abs(ref) < g["rel_tol"]
+    assert abs(got[0] - O.dot(Q8_0, O.quantize(Q8_0, v1), n, 0, v2, 1, 0)) <= 1e-4 * abs(ref)
+
+
+# ---- error behaviour (assertFailsWith<IllegalArgumentException>, DestinationTest.kt:268-305) ----
+def test_matmul_error_classes(ga):
+    ga.reset()
+    a = ga.allocateTensor(GGMLTensor(GGMLType.F32, [3, 2]))
+    b_bad = ga.allocateTensor(GGMLTensor(GGMLType.F32, [2, 4]))      # K mismatch
+    b = ga.allocateTensor(GGMLTensor(GGMLType.F32, [2, 3]))
+    d = ga.allocateTensor(GGMLTensor(GGMLType.F32, [2, 2]))
+    d_bad = ga.allocateTensor(GGMLTensor(GGMLType.F32, [3, 2]))
+    with pytest.raises(lk.IllegalArgumentException):
+        lk.computeMatMul(ga, None, a, b_bad, d)
+    with pytest.raises(lk.IllegalArgumentException):
+        lk.computeMatMul(ga, None, a, b, d_bad)
+    q = ga.allocateTensor(GGMLTensor(GGMLType.Q8_0, [32, 2]))
+    bq = ga.allocateTensor(GGMLTensor(GGMLType.F32, [2, 32]))
+    dq_bad = ga.allocateTensor(GGMLTensor(GGMLType.F16, [2, 2]))
+    with pytest.raises(lk.IllegalArgumentException):                 # dst must be F32, :1517
+        lk.computeMatMul(ga, None, q, bq, dq_bad)
+    # buffer bounds -> IndexOutOfBoundsException (GGMLTypes.kt:556-558)
+    far = GGMLTensor(GGMLType.F32, [2, 2], bufferId=0, dataOffset=ga.buffers[0].size - 4)
+    with pytest.raises(lk.IndexOutOfBoundsException):
+        lk.computeMatMul(ga, None, a, b, far)
+    # add with different shapes (computeAdd :742-744)
+    with pytest.raises(lk.IllegalArgumentException):
+        lk.computeAdd(ga, None, a, b, a)
+
+
+def test_empty_matmul_is_a_noop(ga):
+    ga.reset()
+    a = ga.allocateTensor(GGMLTensor(GGMLType.Q4_0, [64, 0]))
+    b = ga.allocateTensor(GGMLTensor(GGMLType.F32, [1, 64]))
+    d = ga.allocateTensor(GGMLTensor(GGMLType.F32, [1, 0]))
+    a.ne[1] = 0
+    d.ne[1] = 0
+    lk.computeMatMul(ga, None, a, b, d)
+
+
+# ---- R1-R4 ------------------------------------------------------------------------------
+def _unary(ga, fn, x, ne, *extra):
+    ga.reset()
+    xs = ga.allocateTensor(GGMLTensor(GGMLType.F32, ne))
+    ds = ga.allocateTensor(GGMLTensor(GGMLType.F32, ne))
+    ga.setBytes(xs, x)
+    fn(ga, None, xs, *extra, ds)
+    return ga.getFloats(ds)
+
+
+def test_silu_reference_vector(O, ga, golden):
+    g = golden["transcribed"]["silu"]            # GGMLComputeOpsTest.kt:607-625
+    x = np.array(g["x"], np.float32)
+    got = _unary(ga, lk.computeSilu, x, [x.size])
+    exp = x.astype(np.float64) / (1 + np.exp(-x.astype(np.float64)))
+    assert np.allclose(got, exp, atol=g["tol"])
+    big = synth_acts(4, 11008) * 4
+    got = _unary(ga, lk.computeSilu, big, [11008])
+    ref = O.silu(big)
+    assert np.max(np.abs(got - ref)) <= 4e-7 * np.max(np.abs(ref))    # 2-ulp expf vs libm
+
+
+def test_silu_mul_swiglu(O, ga):
+    g, u = synth_acts(5, 11008) * 3, synth_acts(6, 11008)
+    ga.reset()
+    a = ga.allocateTensor(GGMLTensor(GGMLType.F32, [11008]))
+    b = ga.allocateTensor(GGMLTensor(GGMLType.F32, [11008]))
+    d = ga.allocateTensor(GGMLTensor(GGMLType.F32, [11008]))
+    ga.setBytes(a, g)
+    ga.setBytes(b, u)
+    lk.computeSiluMul(ga, None, a, b, d)
+    ref = O.silu_mul(g, u)
+    assert np.max(np.abs(ga.getFloats(d) - ref)) <= 1e-6 * np.max(np.abs(ref))
+
+
+def test_rms_norm(O, ga):
+    x = np.array([1, 2, 3, 4], np.float32)       # GGMLComputeOpsTest.kt:650-672, eps 1e-5, tol 1e-4
+    got = _unary(ga, lk.computeRmsNorm, x, [4], None, 1e-5)
+    exp = x / np.sqrt(np.mean(x.astype(np.float64) ** 2) + 1e-5)
+    assert np.allclose(got, exp, atol=1e-4)
+    for ne0, rows in ((4096, 1), (4096, 7), (11008, 3), (33, 5), (1, 4)):
+        x = synth_acts(ne0, ne0 * rows) * 2
+        w = synth_weights(ne0, 1, ne0) * 50
+        ga.reset()
+        xs = ga.allocateTensor(GGMLTensor(GGMLType.F32, [ne0, rows]))
+        ws = ga.allocateTensor(GGMLTensor(GGMLType.F32, [ne0]))
+        ds = ga.allocateTensor(GGMLTensor(GGMLType.F32, [ne0, rows]))
+        ga.setBytes(xs, x)
+        ga.setBytes(ws, w)
+        lk.computeRmsNorm(ga, None, xs, ws, 1e-6, ds)
+        ref = O.rms_norm(x, w, 1e-6, ne0)
+        assert np.allclose(ga.getFloats(ds), ref, rtol=2e-7, atol=0), (ne0, rows)
+    z = _unary(ga, lk.computeRmsNorm, np.zeros(64, np.float32), [64], None, 0.0)
+    assert same_f32_bits(z, O.rms_norm(np.zeros(64, np.float32), None, 0.0, 64))
+
+
+def test_softmax(O, ga):
+    for ne0, rows in ((1, 1), (7, 3), (2048, 32), (4096, 2), (33, 9)):
+        x = synth_acts(ne0 + rows, ne0 * rows) * 5
+        got = _unary(ga, lk.computeSoftMax, x, [ne0, rows])
+        ref = O.softmax(x, ne0)
+        assert np.allclose(got, ref, rtol=2e-5, atol=1e-12), (ne0, rows)
+        assert np.allclose(got.reshape(rows, ne0).sum(1), 1.0, atol=1e-5)
+    # shift invariance and large-magnitude stability (own vectors: the reference has no softmax test)
+    x = synth_acts(3, 512)
+    a = _unary(ga, lk.computeSoftMax, x + 1000.0, [512])
+    assert np.all(np.isfinite(a)) and abs(a.sum() - 1) < 1e-5
+    assert np.allclose(a, O.softmax(x + np.float32(1000.0), 512), rtol=2e-5)
+
+
+def test_add_mul_bit_exact(O, ga):
+    for n in (1, 5, 4096, 11008, 4099):
+        x, y = synth_acts(n, n), synth_acts(n + 1, n)
+        for fn, ofn in ((lk.computeAdd, O.add), (lk.computeMul, O.mul)):
+            ga.reset()
+            a = ga.allocateTensor(GGMLTensor(GGMLType.F32, [n]))
+            b = ga.allocateTensor(GGMLTensor(GGMLType.F32, [n]))
+            d = ga.allocateTensor(GGMLTensor(GGMLType.F32, [n]))
+            ga.setBytes(a, x)
+            ga.setBytes(b, y)
+            fn(ga, None, a, b, d)
+            assert same_f32_bits(ga.getFloats(d), ofn(x, y))
