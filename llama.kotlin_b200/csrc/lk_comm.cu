@@ -108,6 +108,7 @@ lk_status lk_allgather_f32(lk_ctx *ctx, lk_buf *buf, uint64_t off, int64_t count
     const uint64_t total = (uint64_t)count * 4 * ctx->nranks;
     if (off > buf->size || total > buf->size - off) return lk::fail(ctx, LK_EBOUNDS, "lk_allgather_f32: range outside the buffer");
     float *base = (float *)((uint8_t *)buf->ptr + off);
+    lk::chain_other(ctx, base, (size_t)total);
     int rc = g_nccl.allgather(base + (int64_t)ctx->rank * count, base, (size_t)count, 7 /* ncclFloat */, (nccl_comm)ctx->comm, ctx->stream);
     if (rc) return nccl_fail(ctx, rc, "ncclAllGather");
     return LK_OK;
@@ -144,6 +145,7 @@ lk_status lk_peer_barrier(lk_ctx *ctx, lk_buf *own_flags, lk_buf *const *peer_fl
     for (int q = 0; q < n; q++) ptrs[q] = (uint32_t *)(q == rank ? own_flags->ptr : (peer_flags[q] ? peer_flags[q]->ptr : nullptr));
     for (int q = 0; q < n; q++) if (!ptrs[q]) return lk::fail(ctx, LK_EINVAL_ARG, "lk_peer_barrier: missing peer flag buffer");
     LK_CUDA(ctx, cudaMemcpyAsync(ctx->peer_flags, ptrs, sizeof(ptrs), cudaMemcpyHostToDevice, ctx->stream));
+    lk::chain_other(ctx, own_flags->ptr, own_flags->size);
     peer_barrier_kernel<<<1, 32, 0, ctx->stream>>>((uint32_t *)own_flags->ptr, (uint32_t *const *)ctx->peer_flags, n, rank, epoch);
     LK_CUDA(ctx, cudaGetLastError());
     ctx->launches++;
@@ -173,6 +175,8 @@ lk_status lk_compute_matmul_sharded(lk_ctx *ctx, const lk_tensor *a, const lk_te
     }
     lk::GemvTuning tune = ctx->tune;
     tune.pdl = (ctx->pdl_mode == 2) || (ctx->pdl_mode == 1 && ctx->capturing);
+    tune.wait_mode = 1;
+    lk::chain_other(ctx, (uint8_t *)dst->dev_buf->ptr + dst->data_offset, (size_t)M_total * 4);
     float *d = (float *)((uint8_t *)dst->dev_buf->ptr + dst->data_offset);
     cudaError_t e = lk::launch_gemv(a->type, (uint8_t *)a->dev_buf->ptr + a->data_offset, K, Ms,
                                     (const float *)((uint8_t *)b->dev_buf->ptr + b->data_offset), d, row0, peers, tune,

@@ -5,320 +5,479 @@
 // :120-145, :70-115, :43-68) on the reference's own block layouts (34/18/20 B,
 // Kotlin nibble order core/GGMLTypes.kt:647-651).
 //
-// HBM-bound: every weight byte is read once, so the design is about keeping
-// ~100 KB per SM in flight and spending < 3 issue slots per weight element.
+// The op is HBM-bound on paper (3.5 flop/B) but at 40 weight elements per
+// clock per SM the CUDA-core instruction budget is what decides it on B200:
+// measured pipe rates (tools/ubench_pipes.cu) are 0.5 warp-instr/clk/SMSP for
+// PRMT/LOP3/SHF (ALU pipe) and for DP4A/FFMA2 (FMA pipe), the two pipes issue
+// in parallel.  A nibble -> F32 conversion costs >= 1 ALU op per element
+// (>= 16 clk per 8-nibble word per warp, more than the ~25 clk HBM allows once
+// latencies are added), so the inner product runs on DP4A instead:
 //
-//  * persistent grid, one CTA per SM; CTA c owns a contiguous, balanced row
-//    range (contiguous rows == one contiguous byte range of the packed matrix);
-//  * one producer warp streams that byte range through an NSTAGES-deep shared
-//    memory ring with 1-D TMA bulk copies (cp.async.bulk -> UBLKCP) completing
-//    on mbarriers; weights use an L2 evict_first policy (read once);
-//  * consumer thread (rg, c) owns block-pair column c (64 consecutive k) for
-//    every row of row group rg: its 64 activations live in registers for the
-//    whole kernel, so shared memory only carries weight bytes (9 / 10 / 17
+//  * activations -> 23-bit block fixed point, once per CTA: for each 64-float
+//    column, E = exponent of max|x|, T_k = rint(x_k * 2^(22-E)) (|T_k| <= 2^22),
+//    stored as three byte planes (two's-complement bytes of T: planes 0/1
+//    unsigned, plane 2 signed).  |x_k - T_k 2^(E-22)| <= 2^(E-23): one bit less
+//    than F32 for the largest element of the column, i.e. far below the F32
+//    accumulation error of the reference's sequential sum;
+//  * per 8-nibble word: AND / SHR+AND isolate the low / high nibbles as bytes
+//    (3 ALU ops), 2 x 3 DP4A accumulate exact int32 plane sums (6 FMA-pipe ops)
+//    => 12 clk per word per warp on the FMA pipe, ALU pipe half idle;
+//  * per block: I = (I2 << 16) + (I1 << 8) + I0 is exact in int32 for Q4
+//    (|I| < 2^31 by construction), one I2F, then F32: d * (s*I - 8*s*sumT)
+//    (Q4_0), d*s*I + m*s*sumT (Q4_1), d*s*I (Q8_0, planes combined in F32);
+//  * persistent grid, one CTA per SM per launch; CTA c owns a contiguous,
+//    balanced row range = one contiguous byte range of the packed matrix, which
+//    a producer warp streams through an NSTAGES-deep shared-memory ring with
+//    1-D TMA bulk copies (cp.async.bulk -> UBLKCP) completing on mbarriers;
+//    weights use an L2 evict_first policy (read once);
+//  * consumer thread (rg, c) owns block-pair column c (64 consecutive k) for the
+//    rows of row group rg: its 192 activation bytes live in 48 registers for
+//    the whole kernel, so shared memory only carries weight bytes (9 / 10 / 17
 //    conflict-free word loads per 64 elements);
-//  * nibbles are turned into F32 with one PRMT each: byte-isolate
-//    (w & 0x0F0F0F0F, (w>>4) & 0x0F0F0F0F), then PRMT the byte into mantissa
-//    bits 16..19 of 0x43000000 => exactly 128 + nib; the bias is removed once
-//    per block algebraically:  sum (nib-8) x = sum (128+nib) x - 136 * sum x.
-//    The multiply-accumulates are packed FFMA2 (fma.rn.f32x2), 2 MACs/issue;
-//  * Q8_0 bytes: XOR 0x80, PRMT into the low mantissa byte of 0x4B000000
-//    (2^23 + q + 128), exact FADD2 de-bias, FFMA2;
-//  * per-row partials: transposed warp-shuffle reduction, then a cross-warp
-//    sum through shared memory (double-buffered, one named barrier per stage);
-//  * programmatic dependent launch: weight prefetch is issued before
-//    griddepcontrol.wait (weights are immutable inside a captured op
-//    sequence), the activation vector is read after it, so back-to-back GEMVs
-//    overlap the tail of one kernel with the HBM ramp of the next.
+//  * per-row partial sums go to shared memory (one conflict-free STS per row per
+//    thread); the cross-lane / cross-warp reduction happens once at the end;
+//  * programmatic dependent launch: two CTAs (this launch's and the next one's)
+//    fit on an SM; the next GEMV's producer prefetches its weights while this one
+//    computes.  wait_mode says where griddepcontrol.wait sits: before the weight
+//    prefetch (weights written by an earlier op), before reading x (default), or
+//    at the very end (the launch touches nothing an in-flight launch writes or
+//    reads-after-write; the end wait keeps completion order = launch order).
 //
-// Numerics: F32 throughout; summation order differs from the reference's
-// sequential k loop and the +128 bias costs ~5 bits of the 24-bit accumulator
-// (bound ~3e-6 relative), far inside the 1e-3 matmul tolerance.
+// Numerics: integer dot products are exact; the only roundings are the 23-bit
+// activation rounding and ~4 F32 ops per block.  Measured error vs the oracle is
+// ~1e-6 relative (bound documented in DESIGN.md), far inside the 1e-3 bar.
 #include "lk_common.cuh"
 #include "lk_kernels.h"
 
 namespace lk {
 
 constexpr int GEMV_MAX_STAGES = 8;
-constexpr int GEMV_RED_STRIDE = 16;   // max column warps
-constexpr int GEMV_RED_ROWS = 64;     // max rows per stage
+constexpr int GEMV_XSLOT_WORDS = 28;   // 24 plane words + sumT, scale, 2 pad: 7 x 16 B => conflict-free LDS.128
+constexpr int GEMV_RED_PAD = 8;        // floats of padding per partial-sum row (bank spread for finish_rows)
 
-template <int TYPE> struct PairWords;
-template <> struct PairWords<T_Q4_0> { static constexpr int value = 9; };
-template <> struct PairWords<T_Q4_1> { static constexpr int value = 10; };
-template <> struct PairWords<T_Q8_0> { static constexpr int value = 17; };
-
-// 128 + nibble held in byte j of an isolated word (exact)
-__device__ __forceinline__ float nibf(uint32_t iso, int j) {
-    return __uint_as_float(__byte_perm(iso, 0x43000000u, 0x7044u | (uint32_t)(j << 8)));
+__device__ __forceinline__ int dp4a_uu(uint32_t a, uint32_t b, int c) {
+    int d;
+    asm("dp4a.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
 }
-// 2^23 + (unsigned byte j)
-__device__ __forceinline__ float bytef(uint32_t w, int j) {
-    return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7440u | (uint32_t)j));
+__device__ __forceinline__ int dp4a_us(uint32_t a, uint32_t b, int c) {  // a unsigned bytes, b signed bytes
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ int dp4a_su(uint32_t a, uint32_t b, int c) {  // a signed bytes, b unsigned bytes
+    int d;
+    asm("dp4a.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ int dp4a_ss(uint32_t a, uint32_t b, int c) {
+    int d;
+    asm("dp4a.s32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
 }
 
-// accumulate one word of 4-bit quants: bytes [B0, B1) of w hold element pairs P0, P0+1, ...
-template <int B0, int B1, int P0>
-__device__ __forceinline__ void q4_word(uint32_t w, const float2 (&x)[32], float2 &acc_a, float2 &acc_b) {
-    const uint32_t lo = w & 0x0F0F0F0Fu, hi = (w >> 4) & 0x0F0F0F0Fu;
+// Activation registers of one thread (one 32-element block column): q[plane][word].  For Q4 types
+// word 2j holds elements 8j+{0,2,4,6} (the low nibbles of quant word j) and word 2j+1 elements
+// 8j+{1,3,5,7}; for Q8_0 word j holds elements 4j..4j+3.
+struct XRegs {
+    uint32_t q[3][8];
+    float c;        // Q4_0: -8 * s * sumT;  Q4_1: s * sumT;  Q8_0: unused
+    float s;        // 2^(E-22)
+};
+
+// 16 quant bytes (4 aligned words) of 4-bit quants x the block's activations; exact int32
+__device__ __forceinline__ int q4_block_isum(const uint32_t (&q)[4], const XRegs &x) {
+    int i0 = 0, i1 = 0, i2 = 0;
 #pragma unroll
-    for (int j = B0; j < B1; j++) {
-        const float2 f = make_float2(nibf(lo, j), nibf(hi, j));
-        if ((j & 1) == 0) acc_a = ffma2(f, x[P0 + j - B0], acc_a);
-        else              acc_b = ffma2(f, x[P0 + j - B0], acc_b);
+    for (int j = 0; j < 4; j++) {
+        const uint32_t lo = q[j] & 0x0F0F0F0Fu, hi = (q[j] >> 4) & 0x0F0F0F0Fu;
+        i0 = dp4a_uu(lo, x.q[0][2 * j], i0);
+        i1 = dp4a_uu(lo, x.q[1][2 * j], i1);
+        i2 = dp4a_us(lo, x.q[2][2 * j], i2);
+        i0 = dp4a_uu(hi, x.q[0][2 * j + 1], i0);
+        i1 = dp4a_uu(hi, x.q[1][2 * j + 1], i1);
+        i2 = dp4a_us(hi, x.q[2][2 * j + 1], i2);
     }
+    return (i2 << 16) + ((i1 << 8) + i0);   // exact: |.| < 2^31 (nibble <= 15, |T| <= 2^22, 32 terms)
 }
 
-// accumulate bytes [B0, B1) of an int8 word; element E0 is byte B0 (E0 even, B0 even)
-template <int B0, int B1, int P0>
-__device__ __forceinline__ void q8_word(uint32_t w, const float2 (&x)[32], float2 &acc_a, float2 &acc_b) {
-    const uint32_t t = w ^ 0x80808080u;
-    const float2 bias = make_float2(-8388736.0f, -8388736.0f);  // -(2^23 + 128), exact
-#pragma unroll
-    for (int j = B0; j < B1; j += 2) {
-        const float2 f = fadd2(make_float2(bytef(t, j), bytef(t, j + 1)), bias);
-        if ((j & 2) == 0) acc_a = ffma2(f, x[P0 + (j - B0) / 2], acc_a);
-        else              acc_b = ffma2(f, x[P0 + (j - B0) / 2], acc_b);
-    }
-}
-
-// dot of one block pair (64 consecutive k of one row) with the thread's 64 activations.
-// wp: 4-byte aligned shared-memory address of the pair.  sx0/sx1: sum of x over each block.
+// dot of one block (32 consecutive k of one row) with the thread's activations.
+// row: 4-byte aligned shared-memory address of the row; b: block index within the row.
+// 18- and 34-byte blocks start on a 4-byte boundary only for even b: the thread loads the words
+// that cover its block and one PRMT per word (selector chosen by parity) realigns them.
 template <int TYPE>
-__device__ __forceinline__ float pair_dot(const uint32_t *wp, const float2 (&x)[32], float sx0, float sx1) {
-    const float2 z = make_float2(0.f, 0.f);
-    float2 a0 = z, b0 = z, a1 = z, b1 = z;
+__device__ __forceinline__ float block_dot(const uint32_t *row, int b, const XRegs &x) {
+    const bool odd = b & 1;
     if (TYPE == T_Q4_0) {
+        const uint32_t *wp = row + 4 * b + (b >> 1);
+        uint32_t w[5];
+#pragma unroll
+        for (int i = 0; i < 5; i++) w[i] = wp[i];
+        const uint32_t sel = odd ? 0x7654u : 0x5432u;
+        uint32_t q[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) q[j] = __byte_perm(w[j], w[j + 1], sel);
+        const float d = h2f((uint16_t)(odd ? (w[0] >> 16) : w[0]));
+        const float f = (float)q4_block_isum(q, x);
+        return d * fmaf(f, x.s, x.c);                       // d * (s*I - 8*s*sumT)
+    } else if (TYPE == T_Q4_1) {
+        const uint32_t *wp = row + 5 * b;
+        uint32_t w[5];
+#pragma unroll
+        for (int i = 0; i < 5; i++) w[i] = wp[i];
+        uint32_t q[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) q[j] = w[j + 1];
+        const float d = h2f((uint16_t)(w[0] & 0xFFFFu)), m = h2f((uint16_t)(w[0] >> 16));
+        const float f = (float)q4_block_isum(q, x);
+        return fmaf(d, f * x.s, m * x.c);                   // d*s*I + m*s*sumT
+    } else {
+        const uint32_t *wp = row + 8 * b + (b >> 1);
         uint32_t w[9];
 #pragma unroll
         for (int i = 0; i < 9; i++) w[i] = wp[i];
-        q4_word<2, 4, 0>(w[0], x, a0, b0);
-        q4_word<0, 4, 2>(w[1], x, a0, b0);
-        q4_word<0, 4, 6>(w[2], x, a0, b0);
-        q4_word<0, 4, 10>(w[3], x, a0, b0);
-        q4_word<0, 2, 14>(w[4], x, a0, b0);
-        q4_word<0, 4, 16>(w[5], x, a1, b1);
-        q4_word<0, 4, 20>(w[6], x, a1, b1);
-        q4_word<0, 4, 24>(w[7], x, a1, b1);
-        q4_word<0, 4, 28>(w[8], x, a1, b1);
-        const float d0 = h2f((uint16_t)(w[0] & 0xFFFFu)), d1 = h2f((uint16_t)(w[4] >> 16));
-        const float s0 = (a0.x + a0.y) + (b0.x + b0.y), s1 = (a1.x + a1.y) + (b1.x + b1.y);
-        return d0 * fmaf(-136.0f, sx0, s0) + d1 * fmaf(-136.0f, sx1, s1);
-    } else if (TYPE == T_Q4_1) {
-        uint32_t w[10];
-        const uint2 *wp2 = (const uint2 *)wp;  // pair is 8-byte aligned; LDS.64 is conflict-free at stride 40 B
+        const uint32_t sel = odd ? 0x7654u : 0x5432u;
+        int i0 = 0, i1 = 0, i2 = 0;
 #pragma unroll
-        for (int i = 0; i < 5; i++) { const uint2 v = wp2[i]; w[2 * i] = v.x; w[2 * i + 1] = v.y; }
-        q4_word<0, 4, 0>(w[1], x, a0, b0);
-        q4_word<0, 4, 4>(w[2], x, a0, b0);
-        q4_word<0, 4, 8>(w[3], x, a0, b0);
-        q4_word<0, 4, 12>(w[4], x, a0, b0);
-        q4_word<0, 4, 16>(w[6], x, a1, b1);
-        q4_word<0, 4, 20>(w[7], x, a1, b1);
-        q4_word<0, 4, 24>(w[8], x, a1, b1);
-        q4_word<0, 4, 28>(w[9], x, a1, b1);
-        const float d0 = h2f((uint16_t)(w[0] & 0xFFFFu)), m0 = h2f((uint16_t)(w[0] >> 16));
-        const float d1 = h2f((uint16_t)(w[5] & 0xFFFFu)), m1 = h2f((uint16_t)(w[5] >> 16));
-        const float s0 = (a0.x + a0.y) + (b0.x + b0.y), s1 = (a1.x + a1.y) + (b1.x + b1.y);
-        return (d0 * fmaf(-128.0f, sx0, s0) + m0 * sx0) + (d1 * fmaf(-128.0f, sx1, s1) + m1 * sx1);
-    } else {
-        uint32_t w[17];
-#pragma unroll
-        for (int i = 0; i < 17; i++) w[i] = wp[i];
-        q8_word<2, 4, 0>(w[0], x, a0, b0);
-#pragma unroll
-        for (int i = 1; i < 8; i++) {
-            // word i holds elements 2 + 4(i-1) .. => pairs 1 + 2(i-1), +1
-            const uint32_t t = w[i] ^ 0x80808080u;
-            const float2 bias = make_float2(-8388736.0f, -8388736.0f);
-            a0 = ffma2(fadd2(make_float2(bytef(t, 0), bytef(t, 1)), bias), x[1 + 2 * (i - 1)], a0);
-            b0 = ffma2(fadd2(make_float2(bytef(t, 2), bytef(t, 3)), bias), x[2 + 2 * (i - 1)], b0);
+        for (int j = 0; j < 8; j++) {
+            const uint32_t q = __byte_perm(w[j], w[j + 1], sel);
+            i0 = dp4a_su(q, x.q[0][j], i0);
+            i1 = dp4a_su(q, x.q[1][j], i1);
+            i2 = dp4a_ss(q, x.q[2][j], i2);
         }
-        q8_word<0, 2, 15>(w[8], x, a0, b0);
-#pragma unroll
-        for (int i = 0; i < 8; i++) {
-            const uint32_t t = w[9 + i] ^ 0x80808080u;
-            const float2 bias = make_float2(-8388736.0f, -8388736.0f);
-            a1 = ffma2(fadd2(make_float2(bytef(t, 0), bytef(t, 1)), bias), x[16 + 2 * i], a1);
-            b1 = ffma2(fadd2(make_float2(bytef(t, 2), bytef(t, 3)), bias), x[17 + 2 * i], b1);
-        }
-        const float d0 = h2f((uint16_t)(w[0] & 0xFFFFu)), d1 = h2f((uint16_t)(w[8] >> 16));
-        const float s0 = (a0.x + a0.y) + (b0.x + b0.y), s1 = (a1.x + a1.y) + (b1.x + b1.y);
-        return d0 * s0 + d1 * s1;
+        const float d = h2f((uint16_t)(odd ? (w[0] >> 16) : w[0]));
+        // planes combined in F32: the plane-2 term alone can exceed int32 for 8-bit quants
+        const float f = fmaf((float)i2, 65536.0f, (float)((i1 << 8) + i0));
+        return d * (f * x.s);
     }
 }
 
+// Kernel parameters.  Every launch gets a fresh parameter block, so the first touch of each of its
+// cache lines is a constant-cache miss (~500 clk measured); the fields every thread needs sit in
+// the first two 64-byte lines and the kernel touches both lines in its first instructions.
 struct GemvParams {
     const uint8_t *a;     // packed rows, 16-byte aligned
     const float *b;       // K activations, 16-byte aligned
     float *dst;           // M_total outputs
-    float *peer[8];       // optional peer-mapped copies of dst (fused all-gather)
-    int npeers;
     int K, M;             // this launch's rows
-    int64_t row_offset;   // dst index of row 0 (sharded weights)
     int row_bytes;        // K/32 * blockBytes
-    int npairs;           // K/64
-    int ncw;              // column warps = ceil(npairs/32)
+    int nblk;             // K/32 block columns
+    int ncw;              // column warps = ceil(nblk/32)
     int rg;               // row groups
     int cwarps;           // consumer warps = ncw * rg (producer is warp `cwarps`)
-    int stage_rows;       // rg * ACC
+    int stage_rows;
     int nstages;
     int unit_rows;        // CTA row ranges are multiples of this (keeps TMA sizes 16-byte multiples)
-    int x_off, stage_off; // dynamic smem offsets (bytes)
+    // ---- 64 bytes
+    int units_per_cta, units_rem;   // M / unit_rows = units_per_cta * grid + units_rem
+    int red_rows;         // rows the partial-sum buffer holds between flushes (multiple of stage_rows)
+    int red_stride;       // floats per row in the partial-sum buffer (ncw * 8 + pad)
+    int red_off, x_off, stage_off;  // dynamic smem offsets (bytes)
+    int wait_mode;        // GEMV_WAIT_*
+    int npeers;
+    int pad0;
+    int64_t row_offset;   // dst index of row 0 (sharded weights)
+    unsigned long long *tl;         // timeline buffer (tools/gemv_timeline.cu builds only), else NULL
+    // ---- 120 bytes
+    float *peer[8];       // optional peer-mapped copies of dst (fused all-gather)
 };
 
-// transposed shuffle reduction of ACC per-lane values over the 32 lanes;
-// afterwards lane l holds the full sum of value index l / (32/ACC).
-template <int ACC>
-__device__ __forceinline__ float warp_reduce_multi(float (&acc)[ACC], int lane) {
-    int o = 16;
+#ifdef LK_GEMV_TIMELINE
+// slot 0 / 29: %globaltimer at entry / exit (aligns CTAs and launches); other slots: clock64 (cheap), slot 31 = clock64 at entry
+#define LK_TL_SLOTS 32
+__device__ __forceinline__ unsigned long long lk_gtime() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+#define LK_TL(slot) do { if (p.tl) { unsigned long long *q_ = p.tl + (size_t)blockIdx.x * LK_TL_SLOTS; \
+    if ((slot) == 0) { q_[0] = lk_gtime(); q_[31] = (unsigned long long)clock64(); } \
+    else { q_[(slot)] = (unsigned long long)clock64(); if ((slot) == 7) q_[29] = lk_gtime(); } } } while (0)
+#else
+#define LK_TL(slot) do { } while (0)
+#endif
+
+// ---- activations -> byte planes, cooperatively by the consumer threads -------------------
+// task = (block column, half): 16 consecutive floats; the two lanes of a pair share a block.
+// Conversion without F2I (quarter-rate pipe): fmaf(v, c, 1.5*2^23) leaves rint(v*c) in the low
+// mantissa bits; a non-finite element poisons the block scale with NaN instead.
+template <int TYPE>
+__device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int tid, int nthreads) {
+    const int ntasks = p.nblk * 2;
+#pragma unroll 1
+    for (int base = 0; base < ntasks; base += nthreads) {
+        const int task = base + tid;
+        const bool on = task < ntasks;
+        float v[16];
+        if (on) {
+            const float4 *src = (const float4 *)(p.b + (size_t)task * 16);
 #pragma unroll
-    for (int n = ACC; n > 1; n >>= 1) {
-        const int h = n >> 1;
-        const bool up = (lane & o) != 0;
+            for (int i = 0; i < 4; i++) {
+                const float4 f = __ldg(src + i);
+                v[4 * i] = f.x; v[4 * i + 1] = f.y; v[4 * i + 2] = f.z; v[4 * i + 3] = f.w;
+            }
+        } else {
 #pragma unroll
-        for (int i = 0; i < h; i++) {
-            const float keep = up ? acc[i + h] : acc[i];
-            const float send = up ? acc[i] : acc[i + h];
-            acc[i] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+            for (int i = 0; i < 16; i++) v[i] = 0.f;
         }
-        o >>= 1;
+#ifdef LK_GEMV_TIMELINE
+        if (tid == 0 && base == 0) { if (v[0] + v[4] + v[8] + v[12] == 12345.f) xs[0] = 1; LK_TL(22); }
+#endif
+        float amax = 0.f, chk = 0.f;
+#pragma unroll
+        for (int i = 0; i < 16; i++) { amax = fmaxf(amax, fabsf(v[i])); chk = fmaf(v[i], 0.f, chk); }   // chk: NaN iff any NaN/inf
+        uint32_t ab = (chk != chk) ? 0x7FC00000u : __float_as_uint(amax);
+        ab = max(ab, __shfl_xor_sync(0xffffffffu, ab, 1));   // unsigned order: finite < inf < NaN
+        int e = (int)(ab >> 23);
+        const bool nonfinite = e == 255;
+        e = e < 24 ? 24 : e;
+        // c = 2^(22 - (e - 126)) so that |x| < 2^(e-126) maps into |T| <= 2^22;  s = 1/c
+        const float c = nonfinite ? 0.f : __uint_as_float((uint32_t)(275 - e) << 23);
+        const float s = nonfinite ? __uint_as_float(0x7FC00000u) : __uint_as_float((uint32_t)(e - 21) << 23);
+        int T[16];
+        int sumT = 0;
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            T[i] = (int)__float_as_uint(fmaf(nonfinite ? 0.f : v[i], c, 12582912.0f)) - 0x4B400000;
+            sumT += T[i];
+        }
+        sumT += __shfl_xor_sync(0xffffffffu, sumT, 1);   // both halves of the block
+#ifdef LK_GEMV_TIMELINE
+        if (tid == 0 && base == 0) { if (sumT == 0x7FFFFFFF) xs[0] = 1; LK_TL(23); }
+#endif
+        if (on) {
+            const int blk = task >> 1, h = task & 1;
+            uint32_t *slot = xs + (size_t)blk * GEMV_XSLOT_WORDS;
+#pragma unroll
+            for (int pl = 0; pl < 3; pl++) {
+                const uint32_t s2 = 0x0040u + 0x0011u * pl;   // byte pl of a, byte pl of b
+                uint32_t wds[4];
+                if (TYPE == T_Q8_0) {
+#pragma unroll
+                    for (int j = 0; j < 4; j++)
+                        wds[j] = __byte_perm(__byte_perm(T[4 * j], T[4 * j + 1], s2), __byte_perm(T[4 * j + 2], T[4 * j + 3], s2), 0x5410);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 2; j++) {   // nibble word j of my half: lo = even elements, hi = odd
+                        wds[2 * j] = __byte_perm(__byte_perm(T[8 * j], T[8 * j + 2], s2), __byte_perm(T[8 * j + 4], T[8 * j + 6], s2), 0x5410);
+                        wds[2 * j + 1] = __byte_perm(__byte_perm(T[8 * j + 1], T[8 * j + 3], s2), __byte_perm(T[8 * j + 5], T[8 * j + 7], s2), 0x5410);
+                    }
+                }
+                *(uint4 *)(slot + pl * 8 + h * 4) = make_uint4(wds[0], wds[1], wds[2], wds[3]);
+            }
+            if (h == 0) { slot[24] = __float_as_uint((float)sumT); slot[25] = __float_as_uint(s); }
+        }
     }
-    float v = acc[0];
-    for (; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    return v;
 }
 
-template <int TYPE, int ACC, int MAXW>
-__global__ void __launch_bounds__((MAXW + 1) * 32, 1) gemv_kernel(const GemvParams p) {
+enum { GEMV_WAIT_FULL = 0, GEMV_WAIT_X = 1, GEMV_WAIT_END = 2 };
+
+// cross-lane part of the final reduction: 8 lanes per row, 4 rows per warp per pass
+__device__ __forceinline__ void finish_rows(const GemvParams &p, const float *red, int nred, int64_t out0, int warp, int lane) {
+    const int sub = lane & 7, rsel = lane >> 3;
+    const int nc4 = p.red_stride >> 2;   // float4 chunks per row (columns beyond npairs hold zeros)
+#pragma unroll 1
+    for (int rb = warp * 4; rb < nred; rb += p.cwarps * 4) {   // warp-uniform trip count (shuffles inside)
+        const int r = rb + rsel;
+        float v = 0.f;
+        if (r < nred) {
+            const float4 *row = (const float4 *)(red + (size_t)r * p.red_stride);
+#pragma unroll 2
+            for (int c = sub; c < nc4; c += 8) {
+                const float4 f = row[c];
+                v += (f.x + f.y) + (f.z + f.w);
+            }
+        }
+        v += __shfl_xor_sync(0xffffffffu, v, 1);
+        v += __shfl_xor_sync(0xffffffffu, v, 2);
+        v += __shfl_xor_sync(0xffffffffu, v, 4);
+        if (sub == 0 && r < nred) {
+            const int64_t o = out0 + r;
+            p.dst[o] = v;
+#pragma unroll 1
+            for (int q = 0; q < p.npeers; q++) p.peer[q][o] = v;
+        }
+    }
+}
+
+// MINB = CTAs of consecutive launches that must fit on one SM together (registers are
+// capped accordingly): with programmatic dependent launch the next GEMV's CTA sits beside
+// this one and streams its weights while this one computes.
+template <int TYPE, int MAXW, int MINB>
+__global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t *full = (uint64_t *)smem;                   // [GEMV_MAX_STAGES]
     uint64_t *empty = full + GEMV_MAX_STAGES;            // [GEMV_MAX_STAGES]
-    uint64_t *xbar = empty + GEMV_MAX_STAGES;            // [1]
-    float *red = (float *)(smem + 256);                  // [2][GEMV_RED_ROWS][GEMV_RED_STRIDE]
-    float *xs = (float *)(smem + p.x_off);               // [K]
+    float *red = (float *)(smem + p.red_off);            // [red_rows][red_stride]
+    uint32_t *xs = (uint32_t *)(smem + p.x_off);         // [nblk][GEMV_XSLOT_WORDS]
     uint8_t *stage0 = smem + p.stage_off;
 
+    pdl_launch_dependents();  // the next GEMV may be scheduled beside us and start its weight prefetch
+    {   // touch both hot parameter lines now: the two constant-cache misses overlap instead of serialising later
+        const int t0 = p.K, t1 = p.red_stride;
+        asm volatile("" ::"r"(t0), "r"(t1));
+    }
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int stage_bytes = p.stage_rows * p.row_bytes;
 
-    // balanced contiguous row range of this CTA, in units of unit_rows
-    const int units = p.M / p.unit_rows;
-    const int r_begin = (int)((int64_t)units * blockIdx.x / gridDim.x) * p.unit_rows;
-    const int r_end = (int)((int64_t)units * (blockIdx.x + 1) / gridDim.x) * p.unit_rows;
-    const int nrows = r_end - r_begin;
-    const int niter = (nrows + p.stage_rows - 1) / p.stage_rows;
-
-    if (tid == 0) {
-        for (int s = 0; s < p.nstages; s++) {
-            mbar_init(&full[s], 1);
-            mbar_init(&empty[s], p.cwarps);
-        }
-        mbar_init(xbar, 1);
-        fence_mbar_init();
-    }
-    __syncthreads();
-    pdl_launch_dependents();  // the next GEMV may start its own weight prefetch now
+    // balanced contiguous row range of this CTA: the first `rem` CTAs own one unit more
+    const int ub = p.units_per_cta * (int)blockIdx.x + min((int)blockIdx.x, p.units_rem);
+    const int r_begin = ub * p.unit_rows;
+    const int nrows = (p.units_per_cta + ((int)blockIdx.x < p.units_rem ? 1 : 0)) * p.unit_rows;
 
     if (warp == p.cwarps) {
-        // ===== producer warp: one lane streams this CTA's byte range =====
+        // ===== producer warp: lane 0 initialises the barriers and streams this CTA's byte range =====
+        const uint8_t *src = p.a + (int64_t)r_begin * p.row_bytes;
+        int s = 0, left = nrows;
+        uint8_t *dstp = stage0;
+        uint64_t pol_w = 0;
         if (lane == 0) {
-            const uint64_t pol_w = l2_policy_evict_first();
-            const uint64_t pol_x = l2_policy_evict_last();
-            const uint8_t *src = p.a + (int64_t)r_begin * p.row_bytes;
-            int it = 0;
-            const int pre = niter < p.nstages ? niter : p.nstages;
-            for (; it < pre; it++) {  // weight prefetch: independent of the previous kernel
-                const int rows = min(p.stage_rows, nrows - it * p.stage_rows);
-                const uint32_t bytes = (uint32_t)(rows * p.row_bytes);
-                mbar_arrive_expect_tx(&full[it], bytes);
-                tma_load_1d(stage0 + (size_t)it * stage_bytes, src + (size_t)it * stage_bytes, bytes, &full[it], pol_w);
+            LK_TL(0);
+#pragma unroll 1
+            for (int i = 0; i < p.nstages; i++) {
+                mbar_init(&full[i], 1);
+                mbar_init(&empty[i], p.cwarps);
             }
-            pdl_wait();  // activations may be the previous kernel's output
-            mbar_arrive_expect_tx(xbar, (uint32_t)(p.K * 4));
-            tma_load_1d(xs, p.b, (uint32_t)(p.K * 4), xbar, pol_x);
-            for (; it < niter; it++) {
-                const int s = it % p.nstages;
-                mbar_wait(&empty[s], ((it / p.nstages) - 1) & 1);
-                const int rows = min(p.stage_rows, nrows - it * p.stage_rows);
+            fence_mbar_init();
+            if (p.wait_mode == GEMV_WAIT_FULL) pdl_wait();
+            pol_w = l2_policy_evict_first();
+#pragma unroll 1
+            for (; s < p.nstages && left > 0; s++) {   // first pass over the ring: no waiting
+                const int rows = min(p.stage_rows, left);
                 const uint32_t bytes = (uint32_t)(rows * p.row_bytes);
                 mbar_arrive_expect_tx(&full[s], bytes);
-                tma_load_1d(stage0 + (size_t)s * stage_bytes, src + (size_t)it * stage_bytes, bytes, &full[s], pol_w);
+                tma_load_1d(dstp, src, bytes, &full[s], pol_w);
+                src += bytes; left -= rows; dstp += stage_bytes;
             }
+            LK_TL(1);
+        }
+        __syncwarp();
+        __syncthreads();   // consumers may now wait on the barriers
+        if (lane == 0 && left > 0) {
+            int round = 1;
+            s = 0; dstp = stage0;
+#pragma unroll 1
+            while (left > 0) {
+                mbar_wait(&empty[s], (round - 1) & 1);
+                const int rows = min(p.stage_rows, left);
+                const uint32_t bytes = (uint32_t)(rows * p.row_bytes);
+                mbar_arrive_expect_tx(&full[s], bytes);
+                tma_load_1d(dstp, src, bytes, &full[s], pol_w);
+                src += bytes; left -= rows; dstp += stage_bytes;
+                if (++s == p.nstages) { s = 0; round++; dstp = stage0; }
+            }
+            LK_TL(2);
         }
         return;
     }
 
     // ===== consumer warps =====
-    pdl_wait();  // orders our dst stores after the previous kernel as well
-    const int cw = warp % p.ncw;         // column warp
-    const int rgi = warp / p.ncw;        // row group
-    const int col = cw * 32 + lane;      // block-pair column
-    const bool active = col < p.npairs;
-    constexpr int PW = PairWords<TYPE>::value;
-
-    float2 x[32];
-    float sx0 = 0.f, sx1 = 0.f;
-    mbar_wait(xbar, 0);
-    if (active) {
-        const float4 *xp = (const float4 *)(xs + (size_t)col * 64);
-#pragma unroll
-        for (int i = 0; i < 16; i++) {
-            const float4 v = xp[i];
-            x[2 * i] = make_float2(v.x, v.y);
-            x[2 * i + 1] = make_float2(v.z, v.w);
-        }
-#pragma unroll
-        for (int i = 0; i < 16; i++) sx0 += x[i].x + x[i].y;
-#pragma unroll
-        for (int i = 16; i < 32; i++) sx1 += x[i].x + x[i].y;
-    } else {
-#pragma unroll
-        for (int i = 0; i < 32; i++) x[i] = make_float2(0.f, 0.f);
-    }
-
+    // Everything that does not depend on the activations happens before griddepcontrol.wait.
     const int nct = p.cwarps * 32;
-    for (int it = 0; it < niter; it++) {
-        const int s = it % p.nstages;
-        const int rows_here = min(p.stage_rows, nrows - it * p.stage_rows);
-        mbar_wait(&full[s], (it / p.nstages) & 1);
-        const uint8_t *st = stage0 + (size_t)s * stage_bytes;
-        float acc[ACC];
+    const int cw = p.rg == 1 ? warp : warp % p.ncw;   // column warp
+    const int rgi = p.rg == 1 ? 0 : warp / p.ncw;     // row group
+    const int col = cw * 32 + lane;                   // block column
+    const bool active = col < p.nblk;
+    const int colc = active ? col : 0;                // idle lanes redo column 0 and contribute 0
+    // zero the partial-sum buffer's padding columns once (finish_rows reads whole rows)
+#pragma unroll 1
+    for (int r = warp; r < p.red_rows; r += p.cwarps)
+        if (lane < GEMV_RED_PAD) red[r * p.red_stride + p.ncw * 8 + lane] = 0.f;
+    __syncthreads();   // barriers initialised by the producer
+    if (p.wait_mode != GEMV_WAIT_END) pdl_wait();  // activations may be the previous kernel's output
+    if (tid == 0) LK_TL(3);
+    prep_x<TYPE>(p, xs, tid, nct);
+    if (tid == 0) LK_TL(24);
+    asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");   // activation planes written
+    if (tid == 0) LK_TL(4);
+
+    XRegs x;
+    {
+        const uint4 *slot = (const uint4 *)(xs + (size_t)colc * GEMV_XSLOT_WORDS);
 #pragma unroll
-        for (int a = 0; a < ACC; a++) {
-            const int row = a * p.rg + rgi;
-            acc[a] = 0.f;
-            if (active && row < rows_here)
-                acc[a] = pair_dot<TYPE>((const uint32_t *)(st + (size_t)row * p.row_bytes) + col * PW, x, sx0, sx1);
+        for (int pl = 0; pl < 3; pl++)
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                const uint4 v = slot[pl * 2 + h];
+                x.q[pl][4 * h] = v.x; x.q[pl][4 * h + 1] = v.y; x.q[pl][4 * h + 2] = v.z; x.q[pl][4 * h + 3] = v.w;
+            }
+        const uint4 t = slot[6];
+        x.s = __uint_as_float(t.y);
+        x.c = ((TYPE == T_Q4_0) ? -8.0f : 1.0f) * x.s * __uint_as_float(t.x);
+    }
+    if (tid == 0) LK_TL(5);
+
+    // Stage loop: one barrier wait / release per stage; inside, this warp's rows (rgi, rgi+rg, ...)
+    // are processed UNR at a time so that UNR independent dot-product chains are in flight.
+    constexpr int UNR = 4;
+    const int rg_words = p.rg * (p.row_bytes >> 2);
+    int red_base = 0, s = 0, par = 0, it = 0;
+    const uint32_t *sp = (const uint32_t *)stage0 + (size_t)rgi * (p.row_bytes >> 2);   // my first row of the stage
+    float *rp = red + (size_t)rgi * p.red_stride + (col >> 2);
+    const int rstep = p.rg * p.red_stride;
+#pragma unroll 1
+    for (int row0 = 0; row0 < nrows; row0 += p.stage_rows, it++) {
+        if (row0 + p.stage_rows - red_base > p.red_rows) {
+            // partial-sum buffer full (a CTA that owns more rows than it holds)
+            asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
+            finish_rows(p, red, row0 - red_base, p.row_offset + r_begin + red_base, warp, lane);
+            asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
+            rp -= (size_t)(row0 - red_base) * p.red_stride;
+            red_base = row0;
+        }
+        const int rows_here = min(p.stage_rows, nrows - row0);
+        int nr = (rows_here - rgi + p.rg - 1) / p.rg;      // my rows in this stage (rg == 1 or a power-of-two-free small int)
+        mbar_wait(&full[s], par);
+        if (tid == 0 && it < 6) LK_TL(8 + 2 * it);
+        const uint32_t *wp = sp;
+        float *rq = rp;
+#pragma unroll 1
+        for (; nr > 0; nr -= UNR) {
+            // a short last step recomputes its last valid row in the unused slots (no store)
+            float v[UNR];
+#pragma unroll
+            for (int u = 0; u < UNR; u++) v[u] = block_dot<TYPE>(wp + min(u, nr - 1) * rg_words, colc, x);
+#pragma unroll
+            for (int u = 0; u < UNR; u++) v[u] = active ? v[u] : 0.f;
+#pragma unroll
+            for (int u = 0; u < UNR; u++) v[u] += __shfl_xor_sync(0xffffffffu, v[u], 1);
+#pragma unroll
+            for (int u = 0; u < UNR; u++) v[u] += __shfl_xor_sync(0xffffffffu, v[u], 2);
+            if ((lane & 3) == 0) {
+#pragma unroll
+                for (int u = 0; u < UNR; u++)
+                    if (u < nr) rq[u * rstep] = v[u];     // one partial per 4 block columns
+            }
+            wp += UNR * rg_words;
+            rq += UNR * rstep;
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty[s]);  // this warp is done reading the stage
-        float *rb = red + (it & 1) * (GEMV_RED_ROWS * GEMV_RED_STRIDE);
-        {
-            const float v = warp_reduce_multi<ACC>(acc, lane);
-            if ((lane & (32 / ACC - 1)) == 0) {
-                const int a = lane / (32 / ACC);
-                rb[(a * p.rg + rgi) * GEMV_RED_STRIDE + cw] = v;
-            }
-        }
-        asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
-        if (tid < rows_here) {
-            float v = rb[tid * GEMV_RED_STRIDE];
-            for (int c = 1; c < p.ncw; c++) v += rb[tid * GEMV_RED_STRIDE + c];
-            const int64_t o = p.row_offset + r_begin + it * p.stage_rows + tid;
-            p.dst[o] = v;
-            for (int q = 0; q < p.npeers; q++) p.peer[q][o] = v;
-        }
+        if (tid == 0 && it < 6) LK_TL(9 + 2 * it);
+        sp += (size_t)p.stage_rows * (p.row_bytes >> 2);
+        rp += (size_t)p.stage_rows * p.red_stride;
+        if (++s == p.nstages) { s = 0; par ^= 1; sp -= (size_t)p.nstages * p.stage_rows * (p.row_bytes >> 2); }
+    }
+    if (tid == 0) LK_TL(6);
+    asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
+    if (tid == 0) LK_TL(20);
+    finish_rows(p, red, nrows - red_base, p.row_offset + r_begin + red_base, warp, lane);
+    if (tid == 0) {
+        LK_TL(7);
+        // keep completion order = launch order so a later launch's wait covers every earlier one
+        if (p.wait_mode == GEMV_WAIT_END) pdl_wait();
     }
 }
 
 // ---------------------------------------------------------------------------
 // host side: shape analysis + launch
 // ---------------------------------------------------------------------------
-template <int TYPE, int ACC, int MAXW>
+template <int TYPE, int MAXW, int MINB>
 static cudaError_t launch_one(const GemvParams &p, int grid, int smem, int pdl, cudaStream_t s) {
-    auto kern = gemv_kernel<TYPE, ACC, MAXW>;
+    auto kern = gemv_kernel<TYPE, MAXW, MINB>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     if (e != cudaSuccess) return e;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
@@ -333,28 +492,18 @@ static cudaError_t launch_one(const GemvParams &p, int grid, int smem, int pdl, 
     return cudaLaunchKernelEx(&cfg, kern, p);
 }
 
-template <int TYPE, int MAXW>
-static cudaError_t launch_acc(int acc, const GemvParams &p, int grid, int smem, int pdl, cudaStream_t s) {
-    switch (acc) {
-        case 1: return launch_one<TYPE, 1, MAXW>(p, grid, smem, pdl, s);
-        case 2: return launch_one<TYPE, 2, MAXW>(p, grid, smem, pdl, s);
-        case 4: return launch_one<TYPE, 4, MAXW>(p, grid, smem, pdl, s);
-        case 8: return launch_one<TYPE, 8, MAXW>(p, grid, smem, pdl, s);
-        default: return cudaErrorInvalidValue;
-    }
-}
-
 template <int TYPE>
-static cudaError_t launch_type(int acc, const GemvParams &p, int grid, int smem, int pdl, cudaStream_t s) {
-    if (p.cwarps <= 8) return launch_acc<TYPE, 8>(acc, p, grid, smem, pdl, s);
-    return launch_acc<TYPE, 16>(acc, p, grid, smem, pdl, s);
+static cudaError_t launch_type(const GemvParams &p, int grid, int smem, int pdl, cudaStream_t s) {
+    if (p.cwarps <= 8) return launch_one<TYPE, 8, 2>(p, grid, smem, pdl, s);
+    if (p.cwarps <= 12) return launch_one<TYPE, 12, 2>(p, grid, smem, pdl, s);
+    return launch_one<TYPE, 16, 2>(p, grid, smem, pdl, s);
 }
 
 cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const float *b, float *dst,
                         int64_t row_offset, const GemvPeers &peers, const GemvTuning &tune, int sm_count,
                         cudaStream_t s) {
     const int bb = block_bytes(type);
-    if (bb == 0 || K <= 0 || M <= 0 || (K % 64) != 0 || K > 64 * 32 * 16 || M > (1 << 30))
+    if (bb == 0 || K <= 0 || M <= 0 || (K % 64) != 0 || K > 32 * 32 * 16 || M > (1 << 30))
         return cudaErrorNotSupported;
     if (((uintptr_t)a & 15) || ((uintptr_t)b & 15)) return cudaErrorNotSupported;
 
@@ -363,9 +512,11 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
     p.npeers = peers.n;
     for (int i = 0; i < peers.n && i < 8; i++) p.peer[i] = peers.ptr[i];
     p.K = (int)K; p.M = (int)M; p.row_offset = row_offset;
+    p.tl = (unsigned long long *)tune.timeline;
+    p.wait_mode = tune.wait_mode;
     p.row_bytes = (int)(K / 32) * bb;
-    p.npairs = (int)(K / 64);
-    p.ncw = (p.npairs + 31) / 32;
+    p.nblk = (int)(K / 32);
+    p.ncw = (p.nblk + 31) / 32;
     const int target_warps = tune.variant > 0 ? tune.variant : 8;   // consumer warps to aim for
     p.rg = target_warps / p.ncw;
     if (p.rg < 1) p.rg = 1;
@@ -376,17 +527,31 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
     while ((p.unit_rows * p.row_bytes) % 16) p.unit_rows *= 2;   // <= 8 because row_bytes is even
     if (M % p.unit_rows) return cudaErrorNotSupported;
 
+    // two CTAs (this launch and the next) share one SM's 227 KB when cwarps <= 12
     const int budget = tune.smem_budget > 0 ? tune.smem_budget : 112 * 1024;
-    const int stage_target = tune.stage_bytes > 0 ? tune.stage_bytes : 20 * 1024;
-    const int fixed = 256 + 2 * GEMV_RED_ROWS * GEMV_RED_STRIDE * 4;
-    p.x_off = fixed;
-    p.stage_off = (p.x_off + (int)K * 4 + 127) & ~127;
-    int acc = 8;
-    while (acc > 1 && (int64_t)p.rg * acc * p.row_bytes > stage_target) acc >>= 1;
-    while ((p.rg * acc) % p.unit_rows && acc < 8) acc <<= 1;
-    if ((p.rg * acc) % p.unit_rows) return cudaErrorNotSupported;
-    p.stage_rows = p.rg * acc;
+    const int stage_target = tune.stage_bytes > 0 ? tune.stage_bytes : 32 * 1024;
+    int quant = p.unit_rows;                       // stage_rows: multiple of unit_rows (TMA size) and of rg
+    while (quant % p.rg) quant += p.unit_rows;
+    int sr = (stage_target / p.row_bytes / quant) * quant;
+    if (sr < quant) sr = quant;
+    p.stage_rows = sr;
     const int stage_bytes = p.stage_rows * p.row_bytes;
+
+    int grid = sm_count * (tune.ctas_per_sm > 0 ? tune.ctas_per_sm : 1);
+    const int units = (int)(M / p.unit_rows);
+    if (grid > units) grid = units;
+    const int max_cta_rows = (int)(((int64_t)units + grid - 1) / grid) * p.unit_rows;
+
+    p.units_per_cta = units / grid; p.units_rem = units % grid;
+    p.red_stride = p.ncw * 8 + GEMV_RED_PAD;   // one partial per 4 block columns; pad spreads rows over banks
+    int red_rows = ((max_cta_rows + p.stage_rows - 1) / p.stage_rows) * p.stage_rows;
+    const int red_cap = (24 * 1024 / (p.red_stride * 4) / p.stage_rows) * p.stage_rows;
+    if (red_rows > red_cap) red_rows = red_cap;
+    if (red_rows < p.stage_rows) red_rows = p.stage_rows;
+    p.red_rows = red_rows;
+    p.red_off = 256;
+    p.x_off = (p.red_off + p.red_rows * p.red_stride * 4 + 15) & ~15;
+    p.stage_off = (p.x_off + p.nblk * GEMV_XSLOT_WORDS * 4 + 127) & ~127;
     int nst = (budget - p.stage_off) / stage_bytes;
     const int max_st = tune.max_stages > 0 ? tune.max_stages : GEMV_MAX_STAGES;
     if (nst > max_st) nst = max_st;
@@ -398,14 +563,10 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
     p.nstages = nst;
     const int smem = p.stage_off + nst * stage_bytes;
 
-    int grid = sm_count * (tune.ctas_per_sm > 0 ? tune.ctas_per_sm : 1);
-    const int units = (int)(M / p.unit_rows);
-    if (grid > units) grid = units;
-
     switch (type) {
-        case T_Q4_0: return launch_type<T_Q4_0>(acc, p, grid, smem, tune.pdl, s);
-        case T_Q4_1: return launch_type<T_Q4_1>(acc, p, grid, smem, tune.pdl, s);
-        case T_Q8_0: return launch_type<T_Q8_0>(acc, p, grid, smem, tune.pdl, s);
+        case T_Q4_0: return launch_type<T_Q4_0>(p, grid, smem, tune.pdl, s);
+        case T_Q4_1: return launch_type<T_Q4_1>(p, grid, smem, tune.pdl, s);
+        case T_Q8_0: return launch_type<T_Q8_0>(p, grid, smem, tune.pdl, s);
         default: return cudaErrorNotSupported;
     }
 }

@@ -20,8 +20,17 @@ lk_status cuda_fail(lk_ctx *ctx, cudaError_t e, const char *what) {
     return fail(ctx, e == cudaErrorMemoryAllocation ? LK_ENOMEM : LK_ECUDA,
                 std::string("CUDA error: ") + cudaGetErrorString(e) + " at " + what);
 }
+// a non-GEMV op (normal kernel / copy): serialises fully behind everything earlier; remember what it wrote
+void chain_other(lk_ctx *ctx, const void *dst, size_t bytes) {
+    ctx->chain_reads.clear();
+    ctx->chain_writes.clear();
+    typedef std::pair<uintptr_t, uintptr_t> Range;
+    if (ctx->other_writes.size() > 64) { ctx->other_writes.clear(); ctx->other_writes.push_back(Range(0, ~(uintptr_t)0)); }
+    ctx->other_writes.push_back(Range((uintptr_t)dst, (uintptr_t)dst + bytes));
+}
 }  // namespace lk
 using lk::fail;
+using lk::chain_other;
 
 extern "C" {
 
@@ -158,6 +167,7 @@ lk_status lk_buf_upload(lk_buf *buf, uint64_t off, const void *host, uint64_t n)
     if (!host) return fail(buf->ctx, LK_EINVAL_ARG, "lk_buf_upload: host is NULL");
     lk_ctx *ctx = buf->ctx;
     LK_CUDA(ctx, cudaMemcpyAsync((uint8_t *)buf->ptr + off, host, n, cudaMemcpyHostToDevice, ctx->stream));
+    chain_other(ctx, (uint8_t *)buf->ptr + off, n);
     LK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // host memory may be unpinned right after return
     return LK_OK;
 }
@@ -169,6 +179,7 @@ lk_status lk_buf_download(lk_buf *buf, uint64_t off, void *host, uint64_t n) {
     if (!host) return fail(buf->ctx, LK_EINVAL_ARG, "lk_buf_download: host is NULL");
     lk_ctx *ctx = buf->ctx;
     LK_CUDA(ctx, cudaMemcpyAsync(host, (uint8_t *)buf->ptr + off, n, cudaMemcpyDeviceToHost, ctx->stream));
+    chain_other(ctx, nullptr, 0);
     LK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return LK_OK;
 }
@@ -180,6 +191,7 @@ lk_status lk_buf_copy(lk_buf *dst, uint64_t doff, lk_buf *src, uint64_t soff, ui
     if (st != LK_OK) return st;
     lk_ctx *ctx = dst->ctx;
     if (n) LK_CUDA(ctx, cudaMemcpyAsync((uint8_t *)dst->ptr + doff, (uint8_t *)src->ptr + soff, n, cudaMemcpyDeviceToDevice, ctx->stream));
+    chain_other(ctx, (uint8_t *)dst->ptr + doff, n);
     return LK_OK;
 }
 
@@ -187,6 +199,7 @@ lk_status lk_buf_clear(lk_buf *buf, uint8_t value) {
     if (!buf) return fail(nullptr, LK_EINVAL_ARG, "lk_buf_clear: buf is NULL");
     lk_ctx *ctx = buf->ctx;
     if (buf->size) LK_CUDA(ctx, cudaMemsetAsync(buf->ptr, value, buf->size, ctx->stream));
+    chain_other(ctx, buf->ptr, buf->size);
     return LK_OK;
 }
 
@@ -282,6 +295,7 @@ lk_status resolve(OpScope &sc, const lk_tensor *t, bool is_output, void **dev_ou
         sc.outs.push_back(s);
     } else if (nbytes) {
         LK_CUDA(ctx, cudaMemcpyAsync(d, h, (size_t)nbytes, cudaMemcpyHostToDevice, ctx->stream));
+        chain_other(ctx, d, (size_t)nbytes);
     }
     *dev_out = d;
     return LK_OK;
@@ -292,8 +306,45 @@ lk_status finish(OpScope &sc) {
     lk_ctx *ctx = sc.ctx;
     for (const Staged &s : sc.outs)
         if (s.bytes) LK_CUDA(ctx, cudaMemcpyAsync(s.host, s.dev, (size_t)s.bytes, cudaMemcpyDeviceToHost, ctx->stream));
-    if (sc.any_host) LK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (sc.any_host) {
+        LK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        chain_other(ctx, nullptr, 0);
+    }
     return LK_OK;
+}
+
+// ---- programmatic-dependent-launch chain bookkeeping ---------------------------------------
+// A GEMV launched with the PDL attribute may start while earlier GEMVs of the chain still run.
+// It may skip the wait on its predecessor (GEMV_WAIT_END, the kernel then waits at its very end so
+// completion order stays launch order) only if it touches nothing an in-flight launch wrote and
+// writes nothing an in-flight launch read or wrote.  Any other op on the stream is a normal kernel
+// or copy that serialises fully, which closes the chain.
+typedef std::pair<uintptr_t, uintptr_t> Range;
+bool overlaps(const std::vector<Range> &v, Range r) {
+    for (const Range &q : v)
+        if (r.first < q.second && q.first < r.second) return true;
+    return false;
+}
+void chain_close(lk_ctx *ctx) { ctx->chain_reads.clear(); ctx->chain_writes.clear(); }
+
+int gemv_wait_mode(lk_ctx *ctx, const void *a, size_t abytes, const void *b, size_t bbytes, const void *d, size_t dbytes,
+                   bool pdl) {
+    const Range ra((uintptr_t)a, (uintptr_t)a + abytes), rb((uintptr_t)b, (uintptr_t)b + bbytes),
+        rd((uintptr_t)d, (uintptr_t)d + dbytes);
+    int mode = 2;   // GEMV_WAIT_END
+    if (!pdl || !ctx->overlap_mode) mode = 1;
+    if (overlaps(ctx->chain_writes, rb) || overlaps(ctx->chain_writes, rd) || overlaps(ctx->chain_reads, rd)) mode = 1;
+    if (overlaps(ctx->chain_writes, ra)) mode = 0;
+    if (!ctx->other_writes.empty()) {   // first GEMV after a normal op: it can start before that op has finished
+        mode = overlaps(ctx->other_writes, ra) ? 0 : (mode == 0 ? 0 : 1);
+        ctx->other_writes.clear();
+    }
+    if (mode != 2) chain_close(ctx);   // everything earlier has completed once this launch passes its wait
+    if (ctx->chain_reads.size() > 256) { chain_close(ctx); mode = 1; }
+    ctx->chain_reads.push_back(ra);
+    ctx->chain_reads.push_back(rb);
+    ctx->chain_writes.push_back(rd);
+    return mode;
 }
 
 void count_launch(lk_ctx *ctx, int n = 1) {
@@ -346,10 +397,15 @@ lk_status lk_compute_matmul(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b,
         lk::GemvTuning tune = ctx->tune;
         tune.pdl = (ctx->pdl_mode == 2) || (ctx->pdl_mode == 1 && ctx->capturing);
         lk::GemvPeers none;
+        // a weight that a preceding normal op wrote is covered by that op's full serialisation only if this
+        // launch waits before its prefetch; the first GEMV after a non-GEMV op therefore never uses mode END
+        tune.wait_mode = gemv_wait_mode(ctx, da, (size_t)lk_tensor_nbytes(a), db, (size_t)K * 4, dd, (size_t)M * 4, tune.pdl != 0);
+        if (sc.any_host) tune.wait_mode = 0;
         e = lk::launch_gemv(a->type, da, K, M, (const float *)db, (float *)dd, 0, none, tune, ctx->sm_count, ctx->stream);
     }
     if (e == cudaErrorNotSupported) {
         cudaGetLastError();
+        chain_other(ctx, dd, (size_t)M * N * 4);
         e = lk::launch_matmul_generic(a->type, da, K, M, (const float *)db, N, (float *)dd, ctx->stream);
     }
     if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "matmul launch");
@@ -371,6 +427,7 @@ lk_status lk_compute_dequantize(lk_ctx *ctx, const lk_tensor *src, const lk_tens
     void *ds, *dd;
     if ((st = resolve(sc, src, false, &ds, "src")) != LK_OK) return st;
     if ((st = resolve(sc, dst, true, &dd, "dst")) != LK_OK) return st;
+    chain_other(ctx, dd, (size_t)n * 4);
     cudaError_t e = lk::launch_dequantize(src->type, ds, n, (float *)dd, ctx->stream);
     if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "dequantize launch");
     count_launch(ctx);
@@ -395,6 +452,7 @@ static lk_status binary_op(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, 
     if ((st = resolve(sc, a, false, &da, "a")) != LK_OK) return st;
     if ((st = resolve(sc, b, false, &db, "b")) != LK_OK) return st;
     if ((st = resolve(sc, dst, true, &dd, "dst")) != LK_OK) return st;
+    chain_other(ctx, dd, (size_t)num_elements(a) * 4);
     cudaError_t e = fn((const float *)da, (const float *)db, num_elements(a), (float *)dd, ctx->stream);
     if (e != cudaSuccess) return lk::cuda_fail(ctx, e, name);
     count_launch(ctx);
@@ -432,6 +490,7 @@ lk_status lk_compute_silu(lk_ctx *ctx, const lk_tensor *x, const lk_tensor *dst)
     void *dx, *dd;
     if ((st = resolve(sc, x, false, &dx, "x")) != LK_OK) return st;
     if ((st = resolve(sc, dst, true, &dd, "dst")) != LK_OK) return st;
+    chain_other(ctx, dd, (size_t)num_elements(x) * 4);
     cudaError_t e = lk::launch_silu((const float *)dx, num_elements(x), (float *)dd, ctx->stream);
     if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "silu launch");
     count_launch(ctx);
@@ -454,6 +513,7 @@ lk_status lk_compute_rms_norm(lk_ctx *ctx, const lk_tensor *x, const lk_tensor *
     if (w && (st = resolve(sc, w, false, &dw, "weight")) != LK_OK) return st;
     if ((st = resolve(sc, dst, true, &dd, "dst")) != LK_OK) return st;
     const int64_t n = num_elements(x);
+    chain_other(ctx, dd, (size_t)n * 4);
     cudaError_t e = lk::launch_rms_norm((const float *)dx, (const float *)dw, eps, ne0, ne0 ? n / ne0 : 0, (float *)dd, ctx->stream);
     if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "rmsNorm launch");
     count_launch(ctx);
@@ -470,6 +530,7 @@ lk_status lk_compute_softmax(lk_ctx *ctx, const lk_tensor *x, const lk_tensor *d
     if ((st = resolve(sc, x, false, &dx, "x")) != LK_OK) return st;
     if ((st = resolve(sc, dst, true, &dd, "dst")) != LK_OK) return st;
     const int64_t ne0 = x->ne[0], n = num_elements(x);
+    chain_other(ctx, dd, (size_t)n * 4);
     cudaError_t e = lk::launch_softmax((const float *)dx, ne0, ne0 ? n / ne0 : 0, (float *)dd, ctx->stream);
     if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "softmax launch");
     count_launch(ctx);
@@ -484,6 +545,7 @@ lk_status lk_capture_begin(lk_ctx *ctx) {
     LK_CUDA(ctx, cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
     ctx->capturing = true;
     ctx->capture_launches = 0;
+    chain_other(ctx, nullptr, 0);
     return LK_OK;
 }
 
@@ -491,6 +553,7 @@ lk_status lk_capture_end(lk_ctx *ctx, lk_graph **out) {
     if (!ctx || !out) return fail(ctx, LK_EINVAL_ARG, "lk_capture_end: NULL argument");
     if (!ctx->capturing) return fail(ctx, LK_EINVAL_ARG, "lk_capture_end: not capturing");
     ctx->capturing = false;
+    chain_other(ctx, nullptr, 0);
     cudaGraph_t g = nullptr;
     LK_CUDA(ctx, cudaStreamEndCapture(ctx->stream, &g));
     cudaGraphExec_t ex = nullptr;
@@ -505,6 +568,7 @@ lk_status lk_capture_end(lk_ctx *ctx, lk_graph **out) {
 lk_status lk_graph_launch(lk_ctx *ctx, lk_graph *g) {
     if (!ctx || !g) return fail(ctx, LK_EINVAL_ARG, "lk_graph_launch: NULL argument");
     LK_CUDA(ctx, cudaGraphLaunch(g->exec, ctx->stream));
+    chain_other(ctx, nullptr, 0);
     ctx->launches += g->launches;
     return LK_OK;
 }
@@ -528,6 +592,7 @@ lk_status lk_set_option(lk_ctx *ctx, const char *name, int64_t v) {
     else if (n == "gemv_max_stages") ctx->tune.max_stages = (int)v;
     else if (n == "gemv_smem_budget") ctx->tune.smem_budget = (int)v;
     else if (n == "gemv_ctas_per_sm") ctx->tune.ctas_per_sm = (int)v;
+    else if (n == "gemv_overlap") ctx->overlap_mode = (int)v;
     else return fail(ctx, LK_EINVAL_ARG, "lk_set_option: unknown option " + n);
     return LK_OK;
 }
@@ -541,6 +606,7 @@ int64_t lk_get_option(lk_ctx *ctx, const char *name) {
     if (n == "gemv_max_stages") return ctx->tune.max_stages;
     if (n == "gemv_smem_budget") return ctx->tune.smem_budget;
     if (n == "gemv_ctas_per_sm") return ctx->tune.ctas_per_sm;
+    if (n == "gemv_overlap") return ctx->overlap_mode;
     return -1;
 }
 

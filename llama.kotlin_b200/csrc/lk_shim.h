@@ -4,6 +4,7 @@
 #include <stdint.h>
 
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/llamakotlin_cuda.h"
@@ -20,6 +21,11 @@ struct lk_ctx {
     int pdl_mode = 1;  // 0 never, 1 inside captured sequences, 2 always
     bool capturing = false;
     int64_t capture_launches = 0;
+    // Byte ranges touched by the GEMV launches that may still be in flight when the next one starts
+    // (programmatic dependent launch chain); see gemv_wait_mode() in lk_shim.cu.
+    std::vector<std::pair<uintptr_t, uintptr_t>> chain_reads, chain_writes;
+    std::vector<std::pair<uintptr_t, uintptr_t>> other_writes;   // outputs of non-GEMV ops since the last GEMV
+    int overlap_mode = 1;  // 0: every GEMV waits for its predecessor before reading x; 1: independent GEMVs overlap
     // device staging arena for host-resident tensors (bump allocated per op)
     uint8_t *arena = nullptr;
     size_t arena_size = 0, arena_used = 0;
@@ -49,6 +55,7 @@ struct lk_graph {
 namespace lk {
 lk_status fail(lk_ctx *ctx, lk_status st, const std::string &msg);
 lk_status cuda_fail(lk_ctx *ctx, cudaError_t e, const char *what);
+void chain_other(lk_ctx *ctx, const void *dst, size_t bytes);   // a non-GEMV op wrote [dst, dst+bytes)
 }  // namespace lk
 
 #define LK_CUDA(ctx, call)                                             \

@@ -338,3 +338,49 @@ def test_add_mul_bit_exact(O, ga):
             ga.setBytes(b, y)
             fn(ga, None, a, b, d)
             assert same_f32_bits(ga.getFloats(d), ofn(x, y))
+
+
+# ---- programmatic-dependent-launch chain: overlap only what is independent -------------------
+def test_graph_gemv_chain_dependencies(O):
+    """A captured op sequence whose GEMVs are a mix of independent launches (which the shim lets
+    overlap, wait at the end) and RAW / WAR / WAW dependent ones (which must wait for their
+    predecessor): replayed results must equal the op-by-op oracle chain."""
+    from llama_kotlin_b200 import GGMLCGraph, GGMLOp
+    n = 4096
+    be = lk.GGMLCudaBackend(0)
+    ga = lk.GGMLGraphAllocator(be, size=3 * (n * n // 32 * 18 + 256) + 16 * n * 4 + (1 << 20))
+    wa, wb, wc = (O.quantize(Q4_0, synth_weights(700 + i, n, n)) for i in range(3))
+    x0 = synth_acts(700, n)
+
+    def dev(t, shape, data=None):
+        tt = ga.allocateTensor(GGMLTensor(t, shape))
+        if data is not None:
+            ga.setBytes(tt, data)
+        return tt
+
+    A, B, C = dev(GGMLType.Q4_0, [n, n], wa), dev(GGMLType.Q4_0, [n, n], wb), dev(GGMLType.Q4_0, [n, n], wc)
+    x = dev(GGMLType.F32, [1, n], x0)
+    d = [dev(GGMLType.F32, [1, n], np.zeros(n, np.float32)) for _ in range(4)]
+
+    def node(w, src, dst):
+        return GGMLTensor(GGMLType.F32, [1, n], op=GGMLOp.MUL_MAT, src=[w, src] + [None] * 8, bufferId=0,
+                          dataOffset=dst.dataOffset, buffer=ga.deviceBuffer)
+    nodes = [node(A, x, d[0]),       # d0 = A x
+             node(B, x, d[1]),       # d1 = B x            independent of the first
+             node(C, d[0], d[2]),    # d2 = C d0           RAW on d0
+             node(A, d[1], d[0]),    # d0 = A d1           WAR (d2's launch read d0) + WAW
+             node(B, d[0], d[3]),    # d3 = B d0           RAW on the new d0
+             node(C, x, d[1])]       # d1 = C x            WAR: launch 4 read d1
+    graph = GGMLCGraph(nodes=nodes, allocator=ga)
+    r0 = O.matmul(Q4_0, wa, n, n, x0, 1, nthreads=8)
+    r1 = O.matmul(Q4_0, wb, n, n, x0, 1, nthreads=8)
+    r2 = O.matmul(Q4_0, wc, n, n, r0, 1, nthreads=8)
+    r0b = O.matmul(Q4_0, wa, n, n, r1, 1, nthreads=8)
+    r3 = O.matmul(Q4_0, wb, n, n, r0b, 1, nthreads=8)
+    r1b = O.matmul(Q4_0, wc, n, n, x0, 1, nthreads=8)
+    for rep in range(4):
+        assert be.graphCompute(graph) == lk.GGMLStatus.SUCCESS
+        be.synchronize()
+        for got, ref, name in ((d[0], r0b, "d0"), (d[1], r1b, "d1"), (d[2], r2, "d2"), (d[3], r3, "d3")):
+            assert rel_err(ga.getFloats(got), ref) <= MATMUL_REL_TOL, (rep, name)
+    be.free()

@@ -41,7 +41,7 @@ def main():
     lkc = be.lk
     rng = np.random.default_rng(1)
     defaults = {k: 0 for k in ("gemv_warps", "gemv_stage_bytes", "gemv_max_stages", "gemv_smem_budget")}
-    defaults.update({"gemv_ctas_per_sm": 1, "gemv_pdl": 1})
+    defaults.update({"gemv_ctas_per_sm": 1, "gemv_pdl": 1, "gemv_overlap": 1})
     keep = []
     for shp in args.shapes:
         M, K = (int(v) for v in shp.split("x"))
