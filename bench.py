@@ -204,6 +204,18 @@ def gpu_arm(args, rank: int, world: int, local_rank: int) -> dict:
     x_host[:] = np.random.default_rng(99).normal(0, 1, layers * sumK).astype(np.float32)
     ga.setBytes(acts_all, x_host)
 
+    group = peers = None
+    if world > 1:
+        # weight rows sharded over ranks: every rank allocated dst_all with the same layout, so one
+        # peer mapping of the allocator's device buffer serves every GEMV (sharded.py)
+        def exchange(obj):
+            out = [None] * world
+            dist.all_gather_object(out, obj)
+            return out
+        group = lk.ShardGroup(be, rank, world, exchange)
+        peers = group.map_dst_buffer(ga.deviceBuffer)
+        group.barrier()          # first call outside capture: uploads the peer flag table
+        lkc.sync()
     nodes, weights = [], []
     koff = moff = 0
     first = {}
@@ -217,14 +229,16 @@ def gpu_arm(args, rank: int, world: int, local_rank: int) -> dict:
                 first[si] = a
             b = GGMLTensor(GGMLType.F32, [1, K], bufferId=0, dataOffset=acts_all.dataOffset + koff * 4,
                            buffer=ga.deviceBuffer)
+            extra = {"shard": (group, rank * M, M * world, peers)} if world > 1 else None
             d = GGMLTensor(GGMLType.F32, [1, M * world], op=GGMLOp.MUL_MAT, src=[a, b] + [None] * 8, bufferId=0,
-                           dataOffset=dst_all.dataOffset + moff * 4, buffer=ga.deviceBuffer)
+                           dataOffset=dst_all.dataOffset + moff * 4, buffer=ga.deviceBuffer, extra=extra)
             koff += K
             moff += M * world
             nodes.append(d)
             weights.append(a)
-    if world > 1:
-        raise SystemExit("multi-GPU arm: see bench_multi (not wired in this revision)")
+    if world > 1:   # one exchange point per step: all peer stores of the step are visible after it
+        nodes.append(GGMLTensor(GGMLType.F32, [1], op=GGMLOp.NONE, bufferId=0, dataOffset=dst_all.dataOffset,
+                                buffer=ga.deviceBuffer, extra={"shard_barrier": group}))
     graph = GGMLCGraph(nodes=nodes, allocator=ga)
 
     def step_device():
@@ -262,6 +276,23 @@ def gpu_arm(args, rank: int, world: int, local_rank: int) -> dict:
     if sampler:
         sampler.window(w0, w1)
 
+    # ---- same step with every GEMV forced to wait for its predecessor (a fully dependent chain) ----
+    lkc.set_option("gemv_overlap", 0)
+    graph_dep = GGMLCGraph(nodes=nodes, allocator=ga)
+
+    def step_dep():
+        if be.graphCompute(graph_dep) != lk.GGMLStatus.SUCCESS:
+            raise RuntimeError("graphCompute FAILED")
+    for _ in range(3):
+        step_dep()
+    barrier()
+    lkc.timer_start()
+    for _ in range(args.steps):
+        step_dep()
+    ms_dep = lkc.timer_stop()
+    barrier()
+    lkc.set_option("gemv_overlap", 1)
+
     # ---- end to end: host activations in, host results out, every step -----------------------
     for _ in range(3):
         step_e2e()
@@ -276,9 +307,9 @@ def gpu_arm(args, rank: int, world: int, local_rank: int) -> dict:
         sampler.window(e0, time.time())
 
     if world > 1:
-        t = torch.tensor([ms, e2e_s], dtype=torch.float64, device="cuda")
+        t = torch.tensor([ms, e2e_s, ms_dep], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, e2e_s = float(t[0]), float(t[1])
+        ms, e2e_s, ms_dep = float(t[0]), float(t[1]), float(t[2])
     clocks = sampler.stop() if sampler else None
 
     # ---- spot check of the timed outputs against exact f64 arithmetic on the host (numpy, not the oracle)
@@ -303,7 +334,13 @@ def gpu_arm(args, rank: int, world: int, local_rank: int) -> dict:
                    "qtype": qtype, "layers": layers, "gemv_per_step": n_gemv,
                    "weight_bytes_per_step_per_gpu": layers * sum(wbytes),
                    "l2": "inputs larger than L2 (each launch reads a weight copy not touched for a whole step)",
-                   "parallelism": "single GPU" if world == 1 else f"weight rows sharded over {world} ranks",
+                   "launch_order": "the step's GEMVs are independent ops (own x, own dst): the backend's dependency "
+                                   "tracking lets consecutive launches overlap (PDL); dependent_chain_GBps is the same "
+                                   "step with every GEMV made to wait for its predecessor before reading x",
+                   "dependent_chain_GBps": bytes_step * args.steps / (ms_dep * 1e-3) / 1e9,
+                   "parallelism": "single GPU" if world == 1 else
+                                  f"weight rows sharded over {world} ranks (each rank a full 7B-shape shard), outputs stored "
+                                  f"into every rank's dst over NVLink from the GEMV epilogue + one flag barrier per step",
                    "tflops": 2 * layers * sum(M * K for M, K in SHAPES) * world * args.steps / (ms * 1e-3) / 1e12},
         "e2e": {"value": bytes_step * args.steps / e2e_s / 1e9, "unit": "GB/s",
                 "h2d_bytes_per_step": int(x_host.nbytes), "d2h_bytes_per_step": int(y_host.nbytes),
@@ -322,6 +359,10 @@ def gpu_arm(args, rank: int, world: int, local_rank: int) -> dict:
     if os.path.exists(traffic_file):
         with open(traffic_file) as f:
             res["roofline"]["traffic"] = json.load(f).get(qtype)
+    if group is not None:
+        res["config"]["barrier_timed_out"] = group.timed_out()
+        barrier()
+        group.close()
     be.free()
     if world > 1:
         dist.destroy_process_group()
@@ -329,7 +370,20 @@ def gpu_arm(args, rank: int, world: int, local_rank: int) -> dict:
 
 
 def check_outputs(protos, x_host, y_host, qtype, world, sumM, rank) -> dict:
-    """f64 dot products (numpy) of a few rows of layer 0 against the timed run's output."""
+    """f64 dot products (numpy) of a few rows of layer 0 against the timed run's output: this rank's
+    own slice and, for world > 1, the slice the next rank stored here over NVLink."""
+    res = _check_slice(protos, x_host, y_host, qtype, world, rank)
+    if world > 1:
+        peer = (rank + 1) % world
+        prng = np.random.default_rng(1234 + peer)
+        pprotos = [synth_blocks(prng, M, K, qtype) for M, K in SHAPES]
+        r2 = _check_slice(pprotos, x_host, y_host, qtype, world, peer)
+        res = {"max_err_vs_f64_rows": max(res["max_err_vs_f64_rows"], r2["max_err_vs_f64_rows"]),
+               "peer_slice_err": r2["max_err_vs_f64_rows"], "ok": bool(res["ok"] and r2["ok"])}
+    return res
+
+
+def _check_slice(protos, x_host, y_host, qtype, world, rank) -> dict:
     bb = BLOCK_BYTES[qtype]
     worst = 0.0
     moff = koff = 0

@@ -193,9 +193,12 @@ LK_API lk_status   lk_allgather_f32(lk_ctx *ctx, lk_buf *buf, uint64_t off, int6
 /* peer-mapped buffers for the fused GEMV + all-gather (direct NVLink stores) */
 LK_API lk_status   lk_buf_ipc_export(lk_buf *buf, uint8_t handle_out[LK_IPC_HANDLE_BYTES]);
 LK_API lk_status   lk_buf_ipc_import(lk_ctx *ctx, const uint8_t handle[LK_IPC_HANDLE_BYTES], uint64_t size, lk_buf **out);
-/* Cross-rank barrier on peer-mapped flag words (4 bytes per rank in each rank's flag buffer):
- * publishes `epoch` to every peer after the preceding ops on the ctx stream, then waits until
- * every peer has published it here.  epoch must increase by 1 per call (wrap-safe compare). */
+/* Cross-rank barrier on peer-mapped flag words (each rank's flag buffer holds 16 words, zeroed
+ * before first use): publishes `epoch` to every peer after the preceding ops on the ctx stream,
+ * then waits (bounded, ~2 s; word 14 of the own buffer is set on time-out) until every peer has
+ * published it here.  epoch must increase by 1 per call (wrap-safe compare); epoch == 0 uses a
+ * device-side counter instead, so the call can sit in a captured op sequence that is replayed.
+ * The first call (which uploads the peer table) must be made outside capture. */
 LK_API lk_status   lk_peer_barrier(lk_ctx *ctx, lk_buf *own_flags, lk_buf *const *peer_flags, int32_t npeers,
                             int32_t rank, uint32_t epoch);
 /* Sharded computeMatMul, N == 1: this rank owns rows [row0, row0 + a_shard.ne[1]) of the

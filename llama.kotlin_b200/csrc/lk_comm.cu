@@ -48,22 +48,29 @@ lk_status nccl_fail(lk_ctx *ctx, int rc, const char *what) {
 // One warp: publish "my slice is written" to every peer, then wait until every
 // peer has published the same epoch locally.  Runs after the GEMV on the same
 // stream, so the GEMV's peer stores are complete; the system-scope fence orders
-// them before the flag stores.  Each rank owns its GPU, so the spin is safe.
+// them before the flag stores.  Each rank owns its GPU, so the spin is safe; it
+// is bounded (~2 s) so a dead peer cannot hang the device: on time-out word 14
+// of the flag buffer is set and the kernel returns.
+// epoch == 0: the epoch is a device-side counter (word 15), so the same captured
+// launch can be replayed; every rank must then issue the same number of barriers.
 __global__ void peer_barrier_kernel(uint32_t *own, uint32_t *const *peers, int n, int rank, uint32_t epoch) {
     const int q = threadIdx.x;
+    if (epoch == 0) {
+        uint32_t e = 0;
+        if (q == 0) { e = own[15] + 1; own[15] = e; }
+        epoch = __shfl_sync(0xffffffffu, e, 0);
+    }
     __threadfence_system();
     if (q < n) {
-        if (q != rank) {
-            volatile uint32_t *f = peers[q] + rank;
-            *f = epoch;
-        } else {
-            ((volatile uint32_t *)own)[rank] = epoch;
-        }
+        volatile uint32_t *f = (q == rank ? own : peers[q]) + rank;
+        *f = epoch;
     }
     __threadfence_system();
     if (q < n) {
         volatile uint32_t *f = own + q;
+        const long long t0 = clock64();
         while ((int32_t)(*f - epoch) < 0) {
+            if (clock64() - t0 > 4000000000ll) { ((volatile uint32_t *)own)[14] = 1; break; }
         }
     }
     __threadfence_system();
@@ -139,16 +146,22 @@ lk_status lk_buf_ipc_import(lk_ctx *ctx, const uint8_t handle[LK_IPC_HANDLE_BYTE
 lk_status lk_peer_barrier(lk_ctx *ctx, lk_buf *own_flags, lk_buf *const *peer_flags, int32_t n, int32_t rank, uint32_t epoch) {
     if (!ctx || !own_flags || !peer_flags || n < 1 || n > 8 || rank < 0 || rank >= n)
         return lk::fail(ctx, LK_EINVAL_ARG, "lk_peer_barrier: bad argument");
-    if (own_flags->size < 4u * (unsigned)n) return lk::fail(ctx, LK_EBOUNDS, "lk_peer_barrier: flag buffer too small");
-    if (!ctx->peer_flags) LK_CUDA(ctx, cudaMalloc((void **)&ctx->peer_flags, 8 * sizeof(void *)));
+    if (own_flags->size < 64) return lk::fail(ctx, LK_EBOUNDS, "lk_peer_barrier: flag buffer must hold 16 words");
     uint32_t *ptrs[8] = {};
     for (int q = 0; q < n; q++) ptrs[q] = (uint32_t *)(q == rank ? own_flags->ptr : (peer_flags[q] ? peer_flags[q]->ptr : nullptr));
     for (int q = 0; q < n; q++) if (!ptrs[q]) return lk::fail(ctx, LK_EINVAL_ARG, "lk_peer_barrier: missing peer flag buffer");
-    LK_CUDA(ctx, cudaMemcpyAsync(ctx->peer_flags, ptrs, sizeof(ptrs), cudaMemcpyHostToDevice, ctx->stream));
+    if (!ctx->peer_flags || memcmp(ptrs, ctx->peer_flags_host, sizeof(ptrs)) != 0) {
+        // the pointer table is uploaded once (synchronously, never inside a captured sequence)
+        if (ctx->capturing) return lk::fail(ctx, LK_EINVAL_ARG, "lk_peer_barrier: call once outside capture first (sets up the peer table)");
+        if (!ctx->peer_flags) LK_CUDA(ctx, cudaMalloc((void **)&ctx->peer_flags, sizeof(ptrs)));
+        LK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        LK_CUDA(ctx, cudaMemcpy(ctx->peer_flags, ptrs, sizeof(ptrs), cudaMemcpyHostToDevice));
+        memcpy(ctx->peer_flags_host, ptrs, sizeof(ptrs));
+    }
     lk::chain_other(ctx, own_flags->ptr, own_flags->size);
     peer_barrier_kernel<<<1, 32, 0, ctx->stream>>>((uint32_t *)own_flags->ptr, (uint32_t *const *)ctx->peer_flags, n, rank, epoch);
     LK_CUDA(ctx, cudaGetLastError());
-    ctx->launches++;
+    if (ctx->capturing) ctx->capture_launches++; else ctx->launches++;
     return LK_OK;
 }
 
@@ -175,9 +188,10 @@ lk_status lk_compute_matmul_sharded(lk_ctx *ctx, const lk_tensor *a, const lk_te
     }
     lk::GemvTuning tune = ctx->tune;
     tune.pdl = (ctx->pdl_mode == 2) || (ctx->pdl_mode == 1 && ctx->capturing);
-    tune.wait_mode = 1;
-    lk::chain_other(ctx, (uint8_t *)dst->dev_buf->ptr + dst->data_offset, (size_t)M_total * 4);
     float *d = (float *)((uint8_t *)dst->dev_buf->ptr + dst->data_offset);
+    // this launch writes rows [row0, row0 + Ms) of dst here and at the same offsets on every peer
+    tune.wait_mode = lk::gemv_wait_mode(ctx, (uint8_t *)a->dev_buf->ptr + a->data_offset, (size_t)abytes,
+                                        (uint8_t *)b->dev_buf->ptr + b->data_offset, (size_t)K * 4, d + row0, (size_t)Ms * 4, tune.pdl != 0);
     cudaError_t e = lk::launch_gemv(a->type, (uint8_t *)a->dev_buf->ptr + a->data_offset, K, Ms,
                                     (const float *)((uint8_t *)b->dev_buf->ptr + b->data_offset), d, row0, peers, tune,
                                     ctx->sm_count, ctx->stream);

@@ -28,6 +28,42 @@ void chain_other(lk_ctx *ctx, const void *dst, size_t bytes) {
     if (ctx->other_writes.size() > 64) { ctx->other_writes.clear(); ctx->other_writes.push_back(Range(0, ~(uintptr_t)0)); }
     ctx->other_writes.push_back(Range((uintptr_t)dst, (uintptr_t)dst + bytes));
 }
+// ---- programmatic-dependent-launch chain bookkeeping ---------------------------------------
+// A GEMV launched with the PDL attribute may start while earlier GEMVs of the chain still run.
+// It may skip the wait on its predecessor (GEMV_WAIT_END, the kernel then waits at its very end so
+// completion order stays launch order) only if it touches nothing an in-flight launch wrote and
+// writes nothing an in-flight launch read or wrote.  Any other op on the stream is a normal kernel
+// or copy that serialises fully, which closes the chain.
+namespace {
+typedef std::pair<uintptr_t, uintptr_t> Range;
+bool overlaps(const std::vector<Range> &v, Range r) {
+    for (const Range &q : v)
+        if (r.first < q.second && q.first < r.second) return true;
+    return false;
+}
+void chain_close(lk_ctx *ctx) { ctx->chain_reads.clear(); ctx->chain_writes.clear(); }
+
+}  // namespace
+int gemv_wait_mode(lk_ctx *ctx, const void *a, size_t abytes, const void *b, size_t bbytes, const void *d, size_t dbytes,
+                   bool pdl) {
+    const Range ra((uintptr_t)a, (uintptr_t)a + abytes), rb((uintptr_t)b, (uintptr_t)b + bbytes),
+        rd((uintptr_t)d, (uintptr_t)d + dbytes);
+    int mode = 2;   // GEMV_WAIT_END
+    if (!pdl || !ctx->overlap_mode) mode = 1;
+    if (overlaps(ctx->chain_writes, rb) || overlaps(ctx->chain_writes, rd) || overlaps(ctx->chain_reads, rd)) mode = 1;
+    if (overlaps(ctx->chain_writes, ra)) mode = 0;
+    if (!ctx->other_writes.empty()) {   // first GEMV after a normal op: it can start before that op has finished
+        mode = overlaps(ctx->other_writes, ra) ? 0 : (mode == 0 ? 0 : 1);
+        ctx->other_writes.clear();
+    }
+    if (mode != 2) chain_close(ctx);   // everything earlier has completed once this launch passes its wait
+    if (ctx->chain_reads.size() > 256) { chain_close(ctx); mode = 1; }
+    ctx->chain_reads.push_back(ra);
+    ctx->chain_reads.push_back(rb);
+    ctx->chain_writes.push_back(rd);
+    return mode;
+}
+
 }  // namespace lk
 using lk::fail;
 using lk::chain_other;
@@ -313,40 +349,6 @@ lk_status finish(OpScope &sc) {
     return LK_OK;
 }
 
-// ---- programmatic-dependent-launch chain bookkeeping ---------------------------------------
-// A GEMV launched with the PDL attribute may start while earlier GEMVs of the chain still run.
-// It may skip the wait on its predecessor (GEMV_WAIT_END, the kernel then waits at its very end so
-// completion order stays launch order) only if it touches nothing an in-flight launch wrote and
-// writes nothing an in-flight launch read or wrote.  Any other op on the stream is a normal kernel
-// or copy that serialises fully, which closes the chain.
-typedef std::pair<uintptr_t, uintptr_t> Range;
-bool overlaps(const std::vector<Range> &v, Range r) {
-    for (const Range &q : v)
-        if (r.first < q.second && q.first < r.second) return true;
-    return false;
-}
-void chain_close(lk_ctx *ctx) { ctx->chain_reads.clear(); ctx->chain_writes.clear(); }
-
-int gemv_wait_mode(lk_ctx *ctx, const void *a, size_t abytes, const void *b, size_t bbytes, const void *d, size_t dbytes,
-                   bool pdl) {
-    const Range ra((uintptr_t)a, (uintptr_t)a + abytes), rb((uintptr_t)b, (uintptr_t)b + bbytes),
-        rd((uintptr_t)d, (uintptr_t)d + dbytes);
-    int mode = 2;   // GEMV_WAIT_END
-    if (!pdl || !ctx->overlap_mode) mode = 1;
-    if (overlaps(ctx->chain_writes, rb) || overlaps(ctx->chain_writes, rd) || overlaps(ctx->chain_reads, rd)) mode = 1;
-    if (overlaps(ctx->chain_writes, ra)) mode = 0;
-    if (!ctx->other_writes.empty()) {   // first GEMV after a normal op: it can start before that op has finished
-        mode = overlaps(ctx->other_writes, ra) ? 0 : (mode == 0 ? 0 : 1);
-        ctx->other_writes.clear();
-    }
-    if (mode != 2) chain_close(ctx);   // everything earlier has completed once this launch passes its wait
-    if (ctx->chain_reads.size() > 256) { chain_close(ctx); mode = 1; }
-    ctx->chain_reads.push_back(ra);
-    ctx->chain_reads.push_back(rb);
-    ctx->chain_writes.push_back(rd);
-    return mode;
-}
-
 void count_launch(lk_ctx *ctx, int n = 1) {
     if (ctx->capturing) ctx->capture_launches += n; else ctx->launches += n;
 }
@@ -399,7 +401,7 @@ lk_status lk_compute_matmul(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b,
         lk::GemvPeers none;
         // a weight that a preceding normal op wrote is covered by that op's full serialisation only if this
         // launch waits before its prefetch; the first GEMV after a non-GEMV op therefore never uses mode END
-        tune.wait_mode = gemv_wait_mode(ctx, da, (size_t)lk_tensor_nbytes(a), db, (size_t)K * 4, dd, (size_t)M * 4, tune.pdl != 0);
+        tune.wait_mode = lk::gemv_wait_mode(ctx, da, (size_t)lk_tensor_nbytes(a), db, (size_t)K * 4, dd, (size_t)M * 4, tune.pdl != 0);
         if (sc.any_host) tune.wait_mode = 0;
         e = lk::launch_gemv(a->type, da, K, M, (const float *)db, (float *)dd, 0, none, tune, ctx->sm_count, ctx->stream);
     }

@@ -35,7 +35,8 @@ struct lk_ctx {
     // multi-GPU
     void *comm = nullptr;  // ncclComm_t
     int nranks = 1, rank = 0;
-    uint32_t *peer_flags = nullptr;
+    uint32_t *peer_flags = nullptr;          // device copy of the peer flag pointer table
+    void *peer_flags_host[8] = {};           // what that table holds
 };
 
 struct lk_buf {
@@ -55,7 +56,9 @@ struct lk_graph {
 namespace lk {
 lk_status fail(lk_ctx *ctx, lk_status st, const std::string &msg);
 lk_status cuda_fail(lk_ctx *ctx, cudaError_t e, const char *what);
-void chain_other(lk_ctx *ctx, const void *dst, size_t bytes);   // a non-GEMV op wrote [dst, dst+bytes)
+void chain_other(lk_ctx *ctx, const void *dst, size_t bytes);
+// where a PDL-launched GEMV must wait (GEMV_WAIT_*), and chain bookkeeping for it
+int gemv_wait_mode(lk_ctx *ctx, const void *a, size_t abytes, const void *b, size_t bbytes, const void *d, size_t dbytes, bool pdl);   // a non-GEMV op wrote [dst, dst+bytes)
 }  // namespace lk
 
 #define LK_CUDA(ctx, call)                                             \

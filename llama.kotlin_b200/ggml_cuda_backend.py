@@ -138,9 +138,16 @@ class GGMLCudaBackend:
     # -- graph execution -------------------------------------------------------------
     def _computeNode(self, ga, node: GGMLTensor) -> None:
         op = node.op
+        ex = node.extra if isinstance(node.extra, dict) else None
+        if ex is not None and "shard_barrier" in ex:      # exchange point of a row-sharded matmul (sharded.py)
+            ex["shard_barrier"].barrier()
+            return
         if op == GGMLOp.NONE:
             return
-        if op == GGMLOp.MUL_MAT:       # computeMulMat, core/GGMLComputeOps.kt:2647-2652
+        if op == GGMLOp.MUL_MAT and ex is not None and "shard" in ex:
+            grp, row0, m_total, peers = ex["shard"]
+            grp.computeMatMulSharded(ga, node.src[0], node.src[1], node, row0, m_total, peers)
+        elif op == GGMLOp.MUL_MAT:       # computeMulMat, core/GGMLComputeOps.kt:2647-2652
             ops.computeMatMul(ga, None, node.src[0], node.src[1], node)
         elif op == GGMLOp.ADD:
             ops.computeAdd(ga, None, node.src[0], node.src[1], node)
@@ -160,7 +167,7 @@ class GGMLCudaBackend:
     def _signature(graph: GGMLCGraph):
         sig = []
         for n in graph.nodes:
-            sig.append((n.op, int(n.type), tuple(n.ne), n.dataOffset, id(n.buffer),
+            sig.append((n.op, int(n.type), tuple(n.ne), n.dataOffset, id(n.buffer), id(n.extra),
                         tuple((id(s.buffer), s.dataOffset, int(s.type), tuple(s.ne)) for s in n.src if s is not None)))
         return tuple(sig)
 

@@ -68,7 +68,7 @@ class GGMLTensor:
 
     def __init__(self, type: GGMLType = GGMLType.F32, ne=None, nb=None, op: GGMLOp = GGMLOp.NONE,
                  opParams=None, src=None, bufferId: int = -1, dataOffset: int = 0, name: str = "",
-                 buffer: Any = None, data: Any = None):
+                 buffer: Any = None, data: Any = None, extra: Any = None):
         self.type = GGMLType(type)
         self.ne = list(ne) + [1] * (GGML_MAX_DIMS - len(ne)) if ne is not None else [0] * GGML_MAX_DIMS
         self.nb = list(nb) if nb is not None else [0] * GGML_MAX_DIMS
@@ -80,6 +80,7 @@ class GGMLTensor:
         self.name = name
         self.buffer = buffer      # GGMLBackendBuffer for device-resident tensors
         self.data = data
+        self.extra = extra        # backend-private annotations (the reference's GGMLTensor.extra slot)
 
     def rank(self) -> int:
         if all(v <= 1 for v in self.ne):
