@@ -1,0 +1,492 @@
+// lk_gemm_tc.cu — K2: prefill GEMM  dst[N,M] = dequant(a[K,M]) x b[N,K]  on the tcgen05 tensor cores.
+//
+// Replaces the N > 1 case of computeMatMul's Q x F32 branch (core/GGMLComputeOps.kt:1450-1528: for every
+// (row i, column j) a dot of a's packed row i with column j of b, F32 accumulation) for the batched,
+// dense-contraction shapes (BASELINE config 3: Q8_0 11008x4096 x 4096x512).
+//
+// Data flow per CTA (one 128-row x BN-column output tile, all of K):
+//   * packed weight rows never leave their on-disk layout in HBM.  The producer warp copies, per 256-K
+//     chunk, the 128 row pieces (8 blocks = 272 / 144 / 160 bytes each) into a 2-deep raw ring with one
+//     2-D tiled TMA load (UTMALDG; 128 separate bulk copies were the bottleneck, profiles/r01c), completion
+//     on an mbarrier;
+//   * 8 dequant warps turn each raw piece into FP16 (one 32-element block per thread per 64-K step; the
+//     value is round_fp16(d*q), one rounding, because d and q are both exact in FP16) and store it into
+//     the A stage in the canonical K-major SWIZZLE_128B layout the tensor core reads;
+//   * the activations were converted once per call by pack_b_kernel into FP16 tiles already in that
+//     layout (workspace), so a B stage is a single bulk copy;
+//   * one thread issues tcgen05.mma (cta_group::1, kind::f16, M=128, N=BN, K=16) with both operands in
+//     shared memory and the F32 accumulator in tensor memory; tcgen05.commit releases the stage;
+//   * after the last K step the dequant warps read the accumulator back (tcgen05.ld 32x32b) and store
+//     dst rows directly (each thread owns one output row: 32 contiguous bytes per store pair).
+//
+// Numerics: operands are rounded to FP16 (11-bit significand), accumulation is F32 in TMEM.  Against
+// the F32 reference that is ~3e-4 of max|dst| on the BASELINE shapes; the parity tests bound it by the
+// 1e-3 relative tolerance the north star states.  |x| must be < 65504 (FP16 range); see DESIGN.md.
+#include <cuda.h>   // CUtensorMap types only; the encoder is fetched through cudaGetDriverEntryPoint (no libcuda link)
+
+#include "lk_common.cuh"
+#include "lk_kernels.h"
+
+namespace lk {
+namespace {
+
+constexpr int TC_BM = 128;            // rows of a per CTA = UMMA M
+constexpr int TC_BK = 64;             // K per stage: 64 halfs = one 128-byte swizzle row
+constexpr int TC_CHUNK_K = 256;       // K per raw chunk: 8 blocks, the smallest piece that is 16-byte aligned for all types
+constexpr int TC_DQ_WARPS = 8;
+constexpr int TC_THREADS = (2 + TC_DQ_WARPS) * 32;   // warp 0 producer, warp 1 MMA issuer, 8 dequant/epilogue warps
+constexpr int TC_A_STAGE = TC_BM * TC_BK * 2;         // 16 KB
+constexpr int TC_MAX_STAGES = 8;
+
+// bytes of one row piece (256 K) and the row stride of the raw ring = inner extent of the TMA box.  The stride is
+// an odd number of 16-byte units so that 8 consecutive rows hit 8 different bank groups with LDS.128; for Q4_1
+// the box therefore reads 16 bytes past the piece (the next piece's first bytes, or zero fill at the row end).
+template <int TYPE> struct Raw;
+template <> struct Raw<T_Q8_0> { static constexpr int bytes = 272, stride = 272; };   // 17 x 16 B
+template <> struct Raw<T_Q4_0> { static constexpr int bytes = 144, stride = 144; };   //  9 x 16 B
+template <> struct Raw<T_Q4_1> { static constexpr int bytes = 160, stride = 176; };   // 10 -> 11 x 16 B
+
+// 2-D tiled TMA load (SASS: UTMALDG): box {stride/2 uint16, 128 rows} at element coordinates (c0, c1);
+// rows past the tensor's M are zero-filled and still counted in the transaction bytes.
+__device__ __forceinline__ void tma_load_2d(void *smem_dst, const CUtensorMap *tm, int c0, int c1, uint64_t *bar, uint64_t policy) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%2, %3}], [%4], %5;"
+        ::"r"(smem_u32(smem_dst)), "l"(tm), "r"(c0), "r"(c1), "r"(smem_u32(bar)), "l"(policy)
+        : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap *tm) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(tm) : "memory");
+}
+
+// ---- tcgen05 wrappers ---------------------------------------------------------------------------
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_alloc(uint32_t *slot, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, one 128 x N x 16 step
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// arrive on `bar` when every tcgen05.mma issued so far by this thread has completed
+__device__ __forceinline__ void umma_commit(uint64_t *bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&v)[8]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+                 : "r"(taddr)
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// Shared-memory matrix descriptor, K-major, SWIZZLE_128B, dense 128-byte rows (cute/arch/mma_sm100_desc.hpp
+// field layout): start>>4 [0,14), LBO>>4 [16,30) = 1 (unused for swizzled K-major), SBO>>4 [32,46) = 64
+// (1024 B between 8-row groups), version [46,48) = 1, layout type [61,64) = 2.
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+// Instruction descriptor, kind::f16: D F32 (bit 4), A/B F16 (0), both K-major (0), N>>3 at [17,23), M>>4 at [24,29)
+__device__ __forceinline__ uint32_t umma_idesc_f16(int n) { return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24); }
+
+// ---- FP16 pair arithmetic on raw 32-bit registers ---------------------------------------------------
+__device__ __forceinline__ uint32_t h2_sub(uint32_t a, uint32_t b) {
+    __half2 r = __hsub2(*reinterpret_cast<__half2 *>(&a), *reinterpret_cast<__half2 *>(&b));
+    return *reinterpret_cast<uint32_t *>(&r);
+}
+__device__ __forceinline__ uint32_t h2_mul(uint32_t a, uint32_t b) {
+    __half2 r = __hmul2(*reinterpret_cast<__half2 *>(&a), *reinterpret_cast<__half2 *>(&b));
+    return *reinterpret_cast<uint32_t *>(&r);
+}
+__device__ __forceinline__ uint32_t h2_fma(uint32_t a, uint32_t b, uint32_t c) {
+    __half2 r = __hfma2(*reinterpret_cast<__half2 *>(&a), *reinterpret_cast<__half2 *>(&b), *reinterpret_cast<__half2 *>(&c));
+    return *reinterpret_cast<uint32_t *>(&r);
+}
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
+    return r;
+}
+__device__ __forceinline__ uint4 lds128(const uint8_t *p) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(smem_u32(p)));
+    return v;
+}
+__device__ __forceinline__ void sts128(uint8_t *p, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
+    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(smem_u32(p)), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
+}
+
+// ---- raw block -> registers ---------------------------------------------------------------------------
+// The row piece of one 256-K chunk starts 16-byte aligned in the raw ring; block BP (0..7) of it starts
+// at byte BP*block_bytes, which is only 2-byte (Q8_0, Q4_0) or 4-byte (Q4_1) aligned.  Every block lies
+// inside 3 (Q8_0) or 2 (Q4_x) aligned 16-byte windows, read with conflict-free LDS.128 (odd row stride in
+// 16-byte units) and re-aligned with compile-time funnel shifts.
+template <int NV>
+__device__ __forceinline__ void load_window(const uint8_t *p, uint32_t *w) {
+#pragma unroll
+    for (int i = 0; i < NV; i++) {
+        const uint4 v = lds128(p + 16 * i);
+        w[4 * i + 0] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w;
+    }
+}
+// 32-bit word at byte offset OFF (even) of the window
+template <int OFF>
+__device__ __forceinline__ uint32_t word_at(const uint32_t *w) {
+    if constexpr (OFF % 4 == 0) return w[OFF / 4];
+    else return __funnelshift_r(w[OFF / 4], w[OFF / 4 + 1], 16);
+}
+template <int OFF>
+__device__ __forceinline__ uint32_t half_at(const uint32_t *w) {   // 16-bit value at byte offset OFF, replicated into both halves
+    if constexpr (OFF % 4 == 0) return prmt(w[OFF / 4], 0, 0x1010);
+    else return prmt(w[OFF / 4], 0, 0x3232);
+}
+
+// One block (32 K elements) of row r -> four 16-byte chunks of the A stage row (K-major, 128-byte
+// swizzle: chunk index XOR (row & 7)).  `arow` = stage base + r*128, `c0` = first chunk (0 or 4).
+template <int TYPE, int BP>
+__device__ __forceinline__ void dequant_block(const uint8_t *rowp, uint8_t *arow, int c0, int r7) {
+    constexpr int OFF = BP * block_bytes(TYPE);
+    constexpr int S = OFF & 15;
+    const uint8_t *win = rowp + (OFF & ~15);
+    if constexpr (TYPE == T_Q8_0) {
+        uint32_t w[12];
+        load_window<3>(win, w);
+        const uint32_t d2 = half_at<S>(w);
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            uint32_t o[4];
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                const uint32_t x = word_at<S + 2>(w + 2 * c + h) ^ 0x80808080u;
+                // bytes -> 0x6400 | (q + 128) = 1024 + q + 128, exact; minus 1152 -> q; times d: one rounding
+                o[2 * h + 0] = h2_mul(h2_sub(prmt(x, 0x64646464u, 0x4140), 0x64806480u), d2);
+                o[2 * h + 1] = h2_mul(h2_sub(prmt(x, 0x64646464u, 0x4342), 0x64806480u), d2);
+            }
+            sts128(arow + (((c0 + c) ^ r7) << 4), o[0], o[1], o[2], o[3]);
+        }
+    } else {
+        uint32_t w[8];
+        load_window<2>(win, w);
+        constexpr int QOFF = S + (TYPE == T_Q4_0 ? 2 : 4);
+        const uint32_t d2 = half_at<S>(w);
+        uint32_t m2 = 0;
+        if constexpr (TYPE == T_Q4_1) m2 = half_at<S + 2>(w);
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            const uint32_t q = word_at<QOFF>(w + c);
+            const uint32_t lo = q & 0x0F0F0F0Fu, hi = (q >> 4) & 0x0F0F0F0Fu;
+            uint32_t o[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                // byte j -> elements (2j, 2j+1) = (low nibble, high nibble), core/GGMLTypes.kt nibble order;
+                // selector nibbles with bit 3 set replicate the (zero) sign bit -> 0x00
+                const uint32_t sel = (uint32_t)j | ((8u | j) << 4) | ((4u + j) << 8) | ((8u | j) << 12);
+                const uint32_t p = prmt(lo, hi, sel) | 0x64006400u;   // (1024 + lo, 1024 + hi)
+                if constexpr (TYPE == T_Q4_0) o[j] = h2_mul(h2_sub(p, 0x64086408u), d2);        // (nib - 8) * d
+                else o[j] = h2_fma(h2_sub(p, 0x64006400u), d2, m2);                             // nib * d + m, one rounding
+            }
+            sts128(arow + (((c0 + c) ^ r7) << 4), o[0], o[1], o[2], o[3]);
+        }
+    }
+}
+
+struct GemmTcParams {
+    const uint8_t *a;      // packed weight rows
+    const uint8_t *ws;     // FP16 activation tiles from pack_b_kernel
+    float *dst;
+    int M, N, K;
+    int row_bytes;         // K/32 * block_bytes
+    int nt, bn;            // column tiles per row tile, columns per tile (multiple of 16, <= 256)
+    int n_pad;             // N rounded up to 16: rows of one K-step slab in ws
+    int stages;
+    int tmem_cols;
+    int vec_ok;            // dst rows 16-byte aligned and N % 4 == 0
+};
+
+// 64-K step J (0..3) of the current raw chunk: wait for the A stage to be free, convert this thread's block,
+// publish the stage to the MMA thread.
+template <int TYPE, int J>
+__device__ __forceinline__ void dequant_step(const uint8_t *rowp, uint8_t *sA, uint64_t *full, uint64_t *empty, int row, int qb,
+                                             int lane, int stages, int &s, int &it) {
+    if (it > 0) mbar_wait(&empty[s], (it - 1) & 1);
+    uint8_t *arow = sA + (size_t)s * TC_A_STAGE + row * 128;
+    if (qb) dequant_block<TYPE, 2 * J + 1>(rowp, arow, 4, row & 7);
+    else dequant_block<TYPE, 2 * J>(rowp, arow, 0, row & 7);
+    fence_proxy_async();        // generic-proxy stores -> visible to the tensor core's async-proxy reads
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&full[s]);
+    if (++s == stages) { s = 0; it++; }
+}
+
+// ---- the GEMM -------------------------------------------------------------------------------------
+// Barriers: full[s] (1 producer arrive carrying the B bytes + 8 dequant warps), empty[s] (tcgen05.commit),
+// raw_full[2] (producer arrive carrying 128 row pieces), raw_empty[2] (8 dequant warps), acc_full (commit).
+template <int TYPE>
+__global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const GemmTcParams p, const __grid_constant__ CUtensorMap tm_a) {
+    extern __shared__ uint8_t smem_dyn[];
+    uint8_t *sm = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);   // SWIZZLE_128B atoms need 1024-byte alignment
+    const int stages = p.stages;
+    const int b_stride = p.bn * 128;
+    uint8_t *sA = sm;
+    uint8_t *sB = sA + stages * TC_A_STAGE;
+    uint8_t *sRaw = sB + stages * b_stride;
+    uint64_t *full = reinterpret_cast<uint64_t *>(sRaw + 2 * TC_BM * Raw<TYPE>::stride);
+    uint64_t *empty = full + TC_MAX_STAGES;
+    uint64_t *raw_full = empty + TC_MAX_STAGES;
+    uint64_t *raw_empty = raw_full + 2;
+    uint64_t *acc_full = raw_empty + 2;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_full + 1);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int m0 = (int)(blockIdx.x / p.nt) * TC_BM;
+    const int n0 = (int)(blockIdx.x % p.nt) * p.bn;
+    const int bn = min(p.bn, p.n_pad - n0);          // columns of this tile (multiple of 16)
+    const int nkb = p.K / TC_BK, nchunks = p.K / TC_CHUNK_K;
+
+    if (tid == 0) {
+        for (int i = 0; i < stages; i++) { mbar_init(&full[i], 1 + TC_DQ_WARPS); mbar_init(&empty[i], 1); }
+        for (int i = 0; i < 2; i++) { mbar_init(&raw_full[i], 1); mbar_init(&raw_empty[i], TC_DQ_WARPS); }
+        mbar_init(acc_full, 1);
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, (uint32_t)p.tmem_cols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_acc = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== producer: raw weight row pieces (all lanes) and FP16 activation tiles (lane 0) =====
+        if (lane == 0) tma_prefetch_desc(&tm_a);
+        const uint64_t pol = l2_policy_evict_last();   // both operands are re-read by other CTAs out of the 126 MB L2
+        const uint32_t b_bytes = (uint32_t)bn * 128u;
+        int s = 0, it = 0;
+        for (int c = 0; c < nchunks; c++) {
+            const int rs = c & 1;
+            if (c >= 2) mbar_wait(&raw_empty[rs], ((c >> 1) - 1) & 1);
+            if (lane == 0) {
+                mbar_arrive_expect_tx(&raw_full[rs], (uint32_t)(TC_BM * Raw<TYPE>::stride));
+                tma_load_2d(sRaw + (size_t)rs * TC_BM * Raw<TYPE>::stride, &tm_a, c * (Raw<TYPE>::bytes / 2), m0, &raw_full[rs], pol);
+            }
+            if (lane == 0) {
+                for (int j = 0; j < TC_CHUNK_K / TC_BK; j++) {
+                    const int kb = c * (TC_CHUNK_K / TC_BK) + j;
+                    if (it > 0) mbar_wait(&empty[s], (it - 1) & 1);
+                    mbar_arrive_expect_tx(&full[s], b_bytes);
+                    tma_load_1d(sB + (size_t)s * b_stride, p.ws + ((size_t)kb * p.n_pad + n0) * 128, b_bytes, &full[s], pol);
+                    if (++s == stages) { s = 0; it++; }
+                }
+            }
+            __syncwarp();
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer: one thread =====
+        if (lane == 0) {
+            const uint32_t idesc = umma_idesc_f16(bn);
+            int s = 0, it = 0;
+            for (int kb = 0; kb < nkb; kb++) {
+                mbar_wait(&full[s], it & 1);
+                tc_fence_after();
+                const uint64_t da = umma_desc_sw128(smem_u32(sA + (size_t)s * TC_A_STAGE));
+                const uint64_t db = umma_desc_sw128(smem_u32(sB + (size_t)s * b_stride));
+#pragma unroll
+                for (int k = 0; k < TC_BK / 16; k++)     // +32 bytes along K inside the swizzle row = +2 in the address field
+                    umma_f16(tmem_acc, da + 2 * k, db + 2 * k, idesc, (uint32_t)((kb | k) != 0));
+                umma_commit(&empty[s]);
+                if (++s == stages) { s = 0; it++; }
+            }
+            umma_commit(acc_full);
+        }
+        __syncwarp();
+    } else {
+        // ===== dequant warps: raw blocks -> FP16 A stage; then the epilogue =====
+        const int dt = tid - 64;
+        const int row = dt & (TC_BM - 1), qb = dt >> 7;     // qb: which 32-K half of the 64-K stage (warp-uniform)
+        int s = 0, it = 0;
+        for (int c = 0; c < nchunks; c++) {
+            const int rs = c & 1;
+            mbar_wait(&raw_full[rs], (c >> 1) & 1);
+            const uint8_t *rowp = sRaw + (size_t)(rs * TC_BM + row) * Raw<TYPE>::stride;
+            dequant_step<TYPE, 0>(rowp, sA, full, empty, row, qb, lane, stages, s, it);
+            dequant_step<TYPE, 1>(rowp, sA, full, empty, row, qb, lane, stages, s, it);
+            dequant_step<TYPE, 2>(rowp, sA, full, empty, row, qb, lane, stages, s, it);
+            dequant_step<TYPE, 3>(rowp, sA, full, empty, row, qb, lane, stages, s, it);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&raw_empty[rs]);
+        }
+        // epilogue: TMEM lane = output row; warp w may read lanes 32*(w%4)..+31; the two warps sharing a lane
+        // group split the columns
+        mbar_wait(acc_full, 0);
+        tc_fence_after();
+        const int g = warp & 3, half = (warp - 2) >> 2;
+        const int ncol = bn >> 1;                              // multiple of 8
+        const int grow = m0 + g * 32 + lane;
+        float *drow = p.dst + (size_t)grow * p.N + n0;
+        for (int cc = half * ncol; cc < (half + 1) * ncol; cc += 8) {
+            uint32_t v[8];
+            tmem_ld8(tmem_acc + ((uint32_t)(g * 32) << 16) + (uint32_t)cc, v);
+            tmem_ld_wait();
+            if (grow < p.M) {
+                if (p.vec_ok && n0 + cc + 8 <= p.N) {
+                    *reinterpret_cast<uint4 *>(drow + cc) = make_uint4(v[0], v[1], v[2], v[3]);
+                    *reinterpret_cast<uint4 *>(drow + cc + 4) = make_uint4(v[4], v[5], v[6], v[7]);
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 8; e++)
+                        if (n0 + cc + e < p.N) drow[cc + e] = __uint_as_float(v[e]);
+                }
+            }
+        }
+        tc_fence_before();
+    }
+    __syncthreads();
+    if (warp == 1) {
+        __syncwarp();
+        tc_fence_after();
+        tmem_dealloc(tmem_acc, (uint32_t)p.tmem_cols);
+    }
+}
+
+// ---- activations: F32 [K][N] (N fastest, core/GGMLComputeOps.kt:1474 b index j + k*N) -> FP16 tiles ----
+// ws layout: for every 64-K step kb one slab of n_pad rows x 128 bytes; row n holds b[kb*64 .. +64][n] as
+// 8 chunks of 8 halfs, chunk c stored at position c ^ (n & 7) (the 128-byte swizzle the UMMA descriptor
+// names).  A column tile [n0, n0+bn) of a K step is then one contiguous, 1024-byte aligned byte range.
+// Rows N..n_pad are zero.  One thread per 16-byte chunk; a warp reads 32 consecutive n per k (coalesced).
+__global__ void __launch_bounds__(256) pack_b_kernel(const float *__restrict__ b, uint8_t *__restrict__ ws, int K, int N, int n_pad) {
+    const int64_t total = (int64_t)(K / TC_BK) * 8 * n_pad;
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int n = (int)(t % n_pad);
+        const int c = (int)((t / n_pad) & 7);
+        const int64_t kb = t / ((int64_t)n_pad * 8);
+        uint32_t o[4] = {0, 0, 0, 0};
+        if (n < N) {
+            const float *src = b + ((size_t)kb * TC_BK + (size_t)c * 8) * N + n;
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const __half2 h = __floats2half2_rn(src[(size_t)(2 * j) * N], src[(size_t)(2 * j + 1) * N]);
+                o[j] = *reinterpret_cast<const uint32_t *>(&h);
+            }
+        }
+        *reinterpret_cast<uint4 *>(ws + ((size_t)kb * n_pad + n) * 128 + ((c ^ (n & 7)) << 4)) = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn tensor_map_encoder() {
+    static EncodeTiledFn fn = [] {
+        void *ptr = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+            ptr = nullptr;
+        return (EncodeTiledFn)ptr;
+    }();
+    return fn;
+}
+
+// The packed weight as a 2-D uint16 tensor {row_bytes/2, M}; one box = the 256-K pieces of 128 rows.
+cudaError_t make_weight_map(CUtensorMap *tm, const void *a, int64_t M, int row_bytes, int box_bytes) {
+    EncodeTiledFn enc = tensor_map_encoder();
+    if (!enc) return cudaErrorNotSupported;
+    const cuuint64_t gdim[2] = {(cuuint64_t)(row_bytes / 2), (cuuint64_t)M};
+    const cuuint64_t gstride[1] = {(cuuint64_t)row_bytes};
+    const cuuint32_t box[2] = {(cuuint32_t)(box_bytes / 2), (cuuint32_t)TC_BM};
+    const cuuint32_t estride[2] = {1, 1};
+    const CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, const_cast<void *>(a), gdim, gstride, box, estride,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
+}
+
+template <int TYPE>
+cudaError_t launch_tc(const GemmTcParams &p, int grid, size_t smem, cudaStream_t s) {
+    CUtensorMap tm;
+    cudaError_t me = make_weight_map(&tm, p.a, p.M, p.row_bytes, Raw<TYPE>::stride);
+    if (me != cudaSuccess) return me;
+    static bool configured = false;     // per process; the attribute is per function, not per context
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e != cudaSuccess) return e;
+        configured = true;
+    }
+    gemm_tc_kernel<TYPE><<<grid, TC_THREADS, smem, s>>>(p, tm);
+    return cudaGetLastError();
+}
+
+int raw_stride(int type) { return type == T_Q8_0 ? Raw<T_Q8_0>::stride : type == T_Q4_0 ? Raw<T_Q4_0>::stride : Raw<T_Q4_1>::stride; }
+
+}  // namespace
+
+size_t gemm_tc_workspace_bytes(int64_t K, int64_t N) {
+    const int64_t n_pad = (N + 15) / 16 * 16;
+    return (size_t)(K / TC_BK) * (size_t)n_pad * 128;
+}
+
+// Tile plan: BN = columns per CTA (multiple of 16, <= 256), chosen so that the tile count fills whole waves of
+// SMs.  Cost model per 64-K step: tensor pipe 2*BN clk, L2->SM (raw piece + BN*128 B) at
+// ~43 B/clk, shared memory (A write+read, B write+read, raw write+read) at 128 B/clk.
+static int plan_bn(int type, int64_t M, int64_t N, int sm_count, int *nt_out) {
+    const int64_t n_pad = (N + 15) / 16 * 16, mt = (M + TC_BM - 1) / TC_BM;
+    const double raw = 128.0 * block_bytes(type) * 2;
+    double best = 1e30;
+    int best_bn = 0, best_nt = 0;
+    for (int nt = (int)((n_pad + 255) / 256); nt <= (int)(n_pad / 16) && nt <= 64; nt++) {
+        const int bn = (int)(((n_pad + nt - 1) / nt + 15) / 16 * 16);
+        if ((int64_t)bn * (nt - 1) >= n_pad) continue;   // last tile would be empty
+        const double mma = 2.0 * bn, l2 = (raw + 128.0 * bn) / 43.0, sm = (2 * raw + 2 * TC_A_STAGE + 2 * 128.0 * bn) / 128.0;
+        const double step = mma > l2 ? (mma > sm ? mma : sm) : (l2 > sm ? l2 : sm);
+        const int64_t waves = (mt * nt + sm_count - 1) / sm_count;
+        const double cost = (double)waves * (step + 40.0);
+        if (cost < best) { best = cost; best_bn = bn; best_nt = nt; }
+    }
+    *nt_out = best_nt;
+    return best_bn;
+}
+
+cudaError_t launch_gemm_tc(int type, const void *a, int64_t K, int64_t M, const float *b, int64_t N, float *dst,
+                           void *workspace, int sm_count, cudaStream_t s) {
+    if (type != T_Q8_0 && type != T_Q4_0 && type != T_Q4_1) return cudaErrorNotSupported;
+    if (K <= 0 || K % TC_CHUNK_K || N < 16 || M < 1 || M > (1 << 30) || N > (1 << 20) || K > (1 << 24)) return cudaErrorNotSupported;
+    if (((uintptr_t)a & 15) || ((uintptr_t)workspace & 1023) || ((uintptr_t)b & 3)) return cudaErrorNotSupported;
+    GemmTcParams p;
+    p.a = (const uint8_t *)a; p.ws = (const uint8_t *)workspace; p.dst = dst;
+    p.M = (int)M; p.N = (int)N; p.K = (int)K;
+    p.row_bytes = (int)(K / LK_QK) * block_bytes(type);
+    p.n_pad = (int)((N + 15) / 16 * 16);
+    p.bn = plan_bn(type, M, N, sm_count, &p.nt);
+    if (p.bn < 16) return cudaErrorNotSupported;
+    p.tmem_cols = p.bn <= 32 ? 32 : p.bn <= 64 ? 64 : p.bn <= 128 ? 128 : 256;
+    p.vec_ok = (((uintptr_t)dst & 15) == 0 && (N % 4) == 0) ? 1 : 0;
+    const size_t fixed = 1024 + 2 * (size_t)TC_BM * raw_stride(type) + (2 * TC_MAX_STAGES + 5) * 8 + 16;
+    const size_t per_stage = TC_A_STAGE + (size_t)p.bn * 128;
+    int stages = (int)((227 * 1024 - fixed) / per_stage);
+    if (stages > TC_MAX_STAGES) stages = TC_MAX_STAGES;
+    if (stages < 2) return cudaErrorNotSupported;
+    p.stages = stages;
+    const size_t smem = fixed + stages * per_stage;
+
+    const int64_t chunks = (K / TC_BK) * 8 * (int64_t)p.n_pad;
+    int pgrid = (int)((chunks + 255) / 256);
+    if (pgrid > sm_count * 16) pgrid = sm_count * 16;
+    pack_b_kernel<<<pgrid, 256, 0, s>>>(b, (uint8_t *)workspace, (int)K, (int)N, p.n_pad);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    const int grid = (int)(((M + TC_BM - 1) / TC_BM) * p.nt);
+    switch (type) {
+        case T_Q8_0: return launch_tc<T_Q8_0>(p, grid, smem, s);
+        case T_Q4_0: return launch_tc<T_Q4_0>(p, grid, smem, s);
+        default: return launch_tc<T_Q4_1>(p, grid, smem, s);
+    }
+}
+
+}  // namespace lk

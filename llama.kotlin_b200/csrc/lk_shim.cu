@@ -131,6 +131,7 @@ lk_status lk_ctx_destroy(lk_ctx *ctx) {
     lk_comm_destroy(ctx);
     if (ctx->arena) cudaFree(ctx->arena);
     if (ctx->gemm_ws) cudaFree(ctx->gemm_ws);
+    for (void *w : ctx->gemm_ws_retired) cudaFree(w);
     cudaEventDestroy(ctx->ev0);
     cudaEventDestroy(ctx->ev1);
     cudaStreamDestroy(ctx->stream);
@@ -279,6 +280,23 @@ lk_status arena_reserve(lk_ctx *ctx, size_t need) {
     return LK_OK;
 }
 
+// K2 workspace (FP16 activation tiles).  It may have to grow inside a capture: cudaMalloc is legal there only
+// in relaxed capture mode, and the old block stays alive because an earlier captured graph may name it.
+lk_status gemm_ws_reserve(lk_ctx *ctx, size_t need) {
+    if (need <= ctx->gemm_ws_size) return LK_OK;
+    cudaStreamCaptureMode mode = cudaStreamCaptureModeRelaxed;
+    LK_CUDA(ctx, cudaThreadExchangeStreamCaptureMode(&mode));
+    void *w = nullptr;
+    const size_t sz = need + need / 4 + 4096;      // cudaMalloc returns >= 256-byte alignment; the tiles need 1024
+    cudaError_t e = cudaMalloc(&w, sz);
+    cudaThreadExchangeStreamCaptureMode(&mode);
+    if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "workspace allocation");
+    if (ctx->gemm_ws) ctx->gemm_ws_retired.push_back(ctx->gemm_ws);
+    ctx->gemm_ws = w;
+    ctx->gemm_ws_size = sz;
+    return LK_OK;
+}
+
 bool contiguous_f32(const lk_tensor *t) {
     bool allzero = true;
     for (int d = 0; d < LK_MAX_DIMS; d++) allzero = allzero && t->nb[d] == 0;
@@ -405,13 +423,21 @@ lk_status lk_compute_matmul(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b,
         if (sc.any_host) tune.wait_mode = 0;
         e = lk::launch_gemv(a->type, da, K, M, (const float *)db, (float *)dd, 0, none, tune, ctx->sm_count, ctx->stream);
     }
+    int launched = 1;
+    if (N > 1 && is_block_type(a->type) && ctx->gemm_tc_min_n > 0 && N >= ctx->gemm_tc_min_n && K > 0 && K % 256 == 0) {
+        if ((st = gemm_ws_reserve(ctx, lk::gemm_tc_workspace_bytes(K, N))) != LK_OK) return st;
+        chain_other(ctx, dd, (size_t)M * N * 4);
+        void *ws = (void *)(((uintptr_t)ctx->gemm_ws + 1023) & ~(uintptr_t)1023);
+        e = lk::launch_gemm_tc(a->type, da, K, M, (const float *)db, N, (float *)dd, ws, ctx->sm_count, ctx->stream);
+        if (e == cudaSuccess) { launched = 2; ctx->gemm_tc_launches++; }   // pack_b_kernel + gemm_tc_kernel
+    }
     if (e == cudaErrorNotSupported) {
         cudaGetLastError();
         chain_other(ctx, dd, (size_t)M * N * 4);
         e = lk::launch_matmul_generic(a->type, da, K, M, (const float *)db, N, (float *)dd, ctx->stream);
     }
     if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "matmul launch");
-    count_launch(ctx);
+    count_launch(ctx, launched);
     return finish(sc);
 }
 
@@ -595,6 +621,7 @@ lk_status lk_set_option(lk_ctx *ctx, const char *name, int64_t v) {
     else if (n == "gemv_smem_budget") ctx->tune.smem_budget = (int)v;
     else if (n == "gemv_ctas_per_sm") ctx->tune.ctas_per_sm = (int)v;
     else if (n == "gemv_overlap") ctx->overlap_mode = (int)v;
+    else if (n == "gemm_tc_min_n") ctx->gemm_tc_min_n = (int)v;
     else return fail(ctx, LK_EINVAL_ARG, "lk_set_option: unknown option " + n);
     return LK_OK;
 }
@@ -609,6 +636,8 @@ int64_t lk_get_option(lk_ctx *ctx, const char *name) {
     if (n == "gemv_smem_budget") return ctx->tune.smem_budget;
     if (n == "gemv_ctas_per_sm") return ctx->tune.ctas_per_sm;
     if (n == "gemv_overlap") return ctx->overlap_mode;
+    if (n == "gemm_tc_min_n") return ctx->gemm_tc_min_n;
+    if (n == "gemm_tc_launches") return ctx->gemm_tc_launches;
     return -1;
 }
 

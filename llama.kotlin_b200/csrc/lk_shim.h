@@ -32,6 +32,9 @@ struct lk_ctx {
     // K2 workspace (FP16 copy of the activations)
     void *gemm_ws = nullptr;
     size_t gemm_ws_size = 0;
+    std::vector<void *> gemm_ws_retired;   // smaller workspaces that captured graphs may still name; freed with the ctx
+    int gemm_tc_min_n = 16;                // N >= this takes the tcgen05 GEMM (0 = never); smaller N the generic kernel
+    int64_t gemm_tc_launches = 0;          // tcgen05 GEMM launches so far (tests assert the path taken)
     // multi-GPU
     void *comm = nullptr;  // ncclComm_t
     int nranks = 1, rank = 0;

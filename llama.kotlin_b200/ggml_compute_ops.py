@@ -30,6 +30,9 @@ class LkContext:
     def set_option(self, name: str, value: int) -> None:
         B.check(B.lib().lk_set_option(self.handle, name.encode(), int(value)), self.handle)
 
+    def get_option(self, name: str) -> int:
+        return int(B.lib().lk_get_option(self.handle, name.encode()))
+
     def launch_count(self) -> int:
         return int(B.lib().lk_ctx_launch_count(self.handle))
 

