@@ -35,7 +35,7 @@ constexpr int TC_BK = 64;             // K per stage: 64 halfs = one 128-byte sw
 constexpr int TC_CHUNK_K = 256;       // K per raw chunk: 8 blocks, the smallest piece that is 16-byte aligned for all types
 constexpr int TC_DQ_WARPS = 8;
 constexpr int TC_THREADS = (2 + TC_DQ_WARPS) * 32;   // warp 0 producer, warp 1 MMA issuer, 8 dequant/epilogue warps
-constexpr int TC_A_STAGE = TC_BM * TC_BK * 2;         // 16 KB
+constexpr int TC_A_COL0 = 256;                        // TMEM: accumulator in columns [0, 256), A stages of 32 columns from 256
 constexpr int TC_MAX_STAGES = 8;
 
 // bytes of one row piece (256 K) and the row stride of the raw ring = inner extent of the TMA box.  The stride is
@@ -77,6 +77,24 @@ __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t desc_a, uint6
         ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// same with A read from tensor memory (lane = row, 32-bit column j = K elements 2j, 2j+1): no shared-memory traffic for A
+__device__ __forceinline__ void umma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// 16 consecutive 32-bit columns of this thread's TMEM lane (lane = 32*(warp%4) + laneid)
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+        ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]),
+          "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 // arrive on `bar` when every tcgen05.mma issued so far by this thread has completed
 __device__ __forceinline__ void umma_commit(uint64_t *bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -150,10 +168,9 @@ __device__ __forceinline__ uint32_t half_at(const uint32_t *w) {   // 16-bit val
     else return prmt(w[OFF / 4], 0, 0x3232);
 }
 
-// One block (32 K elements) of row r -> four 16-byte chunks of the A stage row (K-major, 128-byte
-// swizzle: chunk index XOR (row & 7)).  `arow` = stage base + r*128, `c0` = first chunk (0 or 4).
+// One block (32 K elements) of a row -> 16 registers of FP16 pairs in K order (the A operand's TMEM row format).
 template <int TYPE, int BP>
-__device__ __forceinline__ void dequant_block(const uint8_t *rowp, uint8_t *arow, int c0, int r7) {
+__device__ __forceinline__ void dequant_block(const uint8_t *rowp, uint32_t (&out)[16]) {
     constexpr int OFF = BP * block_bytes(TYPE);
     constexpr int S = OFF & 15;
     const uint8_t *win = rowp + (OFF & ~15);
@@ -163,7 +180,7 @@ __device__ __forceinline__ void dequant_block(const uint8_t *rowp, uint8_t *arow
         const uint32_t d2 = half_at<S>(w);
 #pragma unroll
         for (int c = 0; c < 4; c++) {
-            uint32_t o[4];
+            uint32_t *o = out + 4 * c;
 #pragma unroll
             for (int h = 0; h < 2; h++) {
                 const uint32_t x = word_at<S + 2>(w + 2 * c + h) ^ 0x80808080u;
@@ -171,7 +188,6 @@ __device__ __forceinline__ void dequant_block(const uint8_t *rowp, uint8_t *arow
                 o[2 * h + 0] = h2_mul(h2_sub(prmt(x, 0x64646464u, 0x4140), 0x64806480u), d2);
                 o[2 * h + 1] = h2_mul(h2_sub(prmt(x, 0x64646464u, 0x4342), 0x64806480u), d2);
             }
-            sts128(arow + (((c0 + c) ^ r7) << 4), o[0], o[1], o[2], o[3]);
         }
     } else {
         uint32_t w[8];
@@ -184,7 +200,7 @@ __device__ __forceinline__ void dequant_block(const uint8_t *rowp, uint8_t *arow
         for (int c = 0; c < 4; c++) {
             const uint32_t q = word_at<QOFF>(w + c);
             const uint32_t lo = q & 0x0F0F0F0Fu, hi = (q >> 4) & 0x0F0F0F0Fu;
-            uint32_t o[4];
+            uint32_t *o = out + 4 * c;
 #pragma unroll
             for (int j = 0; j < 4; j++) {
                 // byte j -> elements (2j, 2j+1) = (low nibble, high nibble), core/GGMLTypes.kt nibble order;
@@ -194,7 +210,6 @@ __device__ __forceinline__ void dequant_block(const uint8_t *rowp, uint8_t *arow
                 if constexpr (TYPE == T_Q4_0) o[j] = h2_mul(h2_sub(p, 0x64086408u), d2);        // (nib - 8) * d
                 else o[j] = h2_fma(h2_sub(p, 0x64006400u), d2, m2);                             // nib * d + m, one rounding
             }
-            sts128(arow + (((c0 + c) ^ r7) << 4), o[0], o[1], o[2], o[3]);
         }
     }
 }
@@ -212,16 +227,19 @@ struct GemmTcParams {
     int vec_ok;            // dst rows 16-byte aligned and N % 4 == 0
 };
 
-// 64-K step J (0..3) of the current raw chunk: wait for the A stage to be free, convert this thread's block,
-// publish the stage to the MMA thread.
+// 64-K step J (0..3) of the current raw chunk: wait for the A stage (32 TMEM columns) to be free, convert this
+// thread's block, store it to the thread's TMEM lane, publish the stage to the MMA thread.
 template <int TYPE, int J>
-__device__ __forceinline__ void dequant_step(const uint8_t *rowp, uint8_t *sA, uint64_t *full, uint64_t *empty, int row, int qb,
+__device__ __forceinline__ void dequant_step(const uint8_t *rowp, uint32_t tmem_a_lane, uint64_t *full, uint64_t *empty, int qb,
                                              int lane, int stages, int &s, int &it) {
+    uint32_t o[16];
+    if (qb) dequant_block<TYPE, 2 * J + 1>(rowp, o);
+    else dequant_block<TYPE, 2 * J>(rowp, o);
     if (it > 0) mbar_wait(&empty[s], (it - 1) & 1);
-    uint8_t *arow = sA + (size_t)s * TC_A_STAGE + row * 128;
-    if (qb) dequant_block<TYPE, 2 * J + 1>(rowp, arow, 4, row & 7);
-    else dequant_block<TYPE, 2 * J>(rowp, arow, 0, row & 7);
-    fence_proxy_async();        // generic-proxy stores -> visible to the tensor core's async-proxy reads
+    tc_fence_after();
+    tmem_st16(tmem_a_lane + (uint32_t)(s * (TC_BK / 2) + qb * 16), o);
+    tmem_st_wait();
+    tc_fence_before();
     __syncwarp();
     if (lane == 0) mbar_arrive(&full[s]);
     if (++s == stages) { s = 0; it++; }
@@ -236,8 +254,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const GemmTcPara
     uint8_t *sm = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);   // SWIZZLE_128B atoms need 1024-byte alignment
     const int stages = p.stages;
     const int b_stride = p.bn * 128;
-    uint8_t *sA = sm;
-    uint8_t *sB = sA + stages * TC_A_STAGE;
+    uint8_t *sB = sm;
     uint8_t *sRaw = sB + stages * b_stride;
     uint64_t *full = reinterpret_cast<uint64_t *>(sRaw + 2 * TC_BM * Raw<TYPE>::stride);
     uint64_t *empty = full + TC_MAX_STAGES;
@@ -265,29 +282,28 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const GemmTcPara
     const uint32_t tmem_acc = *tmem_slot;
 
     if (warp == 0) {
-        // ===== producer: raw weight row pieces (all lanes) and FP16 activation tiles (lane 0) =====
-        if (lane == 0) tma_prefetch_desc(&tm_a);
+        // ===== producers: lane 0 streams the FP16 activation tiles (paced by the MMA through empty[]), lane 1 the
+        // raw weight pieces (paced only by the dequant warps through raw_empty[], so it runs two chunks ahead) =====
         const uint64_t pol = l2_policy_evict_last();   // both operands are re-read by other CTAs out of the 126 MB L2
-        const uint32_t b_bytes = (uint32_t)bn * 128u;
-        int s = 0, it = 0;
-        for (int c = 0; c < nchunks; c++) {
-            const int rs = c & 1;
-            if (c >= 2) mbar_wait(&raw_empty[rs], ((c >> 1) - 1) & 1);
-            if (lane == 0) {
+        if (lane == 0) {
+            const uint32_t b_bytes = (uint32_t)bn * 128u;
+            int s = 0, it = 0;
+            for (int kb = 0; kb < nkb; kb++) {
+                if (it > 0) mbar_wait(&empty[s], (it - 1) & 1);
+                mbar_arrive_expect_tx(&full[s], b_bytes);
+                tma_load_1d(sB + (size_t)s * b_stride, p.ws + ((size_t)kb * p.n_pad + n0) * 128, b_bytes, &full[s], pol);
+                if (++s == stages) { s = 0; it++; }
+            }
+        } else if (lane == 1) {
+            tma_prefetch_desc(&tm_a);
+            for (int c = 0; c < nchunks; c++) {
+                const int rs = c & 1;
+                if (c >= 2) mbar_wait(&raw_empty[rs], ((c >> 1) - 1) & 1);
                 mbar_arrive_expect_tx(&raw_full[rs], (uint32_t)(TC_BM * Raw<TYPE>::stride));
                 tma_load_2d(sRaw + (size_t)rs * TC_BM * Raw<TYPE>::stride, &tm_a, c * (Raw<TYPE>::bytes / 2), m0, &raw_full[rs], pol);
             }
-            if (lane == 0) {
-                for (int j = 0; j < TC_CHUNK_K / TC_BK; j++) {
-                    const int kb = c * (TC_CHUNK_K / TC_BK) + j;
-                    if (it > 0) mbar_wait(&empty[s], (it - 1) & 1);
-                    mbar_arrive_expect_tx(&full[s], b_bytes);
-                    tma_load_1d(sB + (size_t)s * b_stride, p.ws + ((size_t)kb * p.n_pad + n0) * 128, b_bytes, &full[s], pol);
-                    if (++s == stages) { s = 0; it++; }
-                }
-            }
-            __syncwarp();
         }
+        __syncwarp();
     } else if (warp == 1) {
         // ===== MMA issuer: one thread =====
         if (lane == 0) {
@@ -296,11 +312,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const GemmTcPara
             for (int kb = 0; kb < nkb; kb++) {
                 mbar_wait(&full[s], it & 1);
                 tc_fence_after();
-                const uint64_t da = umma_desc_sw128(smem_u32(sA + (size_t)s * TC_A_STAGE));
+                const uint32_t ta = tmem_acc + TC_A_COL0 + (uint32_t)(s * (TC_BK / 2));
                 const uint64_t db = umma_desc_sw128(smem_u32(sB + (size_t)s * b_stride));
 #pragma unroll
-                for (int k = 0; k < TC_BK / 16; k++)     // +32 bytes along K inside the swizzle row = +2 in the address field
-                    umma_f16(tmem_acc, da + 2 * k, db + 2 * k, idesc, (uint32_t)((kb | k) != 0));
+                for (int k = 0; k < TC_BK / 16; k++)     // per 16-K step: +8 TMEM columns of A, +32 bytes inside B's swizzle row (+2 in the address field)
+                    umma_f16_ts(tmem_acc, ta + 8 * k, db + 2 * k, idesc, (uint32_t)((kb | k) != 0));
                 umma_commit(&empty[s]);
                 if (++s == stages) { s = 0; it++; }
             }
@@ -309,17 +325,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const GemmTcPara
         __syncwarp();
     } else {
         // ===== dequant warps: raw blocks -> FP16 A stage; then the epilogue =====
-        const int dt = tid - 64;
-        const int row = dt & (TC_BM - 1), qb = dt >> 7;     // qb: which 32-K half of the 64-K stage (warp-uniform)
+        // a warp may only touch TMEM lanes 32*(warp%4)..+31, and TMEM lane = tile row: that fixes the row of each
+        // thread; the two warps sharing a lane group take the two 32-K halves (qb) of every 64-K step
+        const int g = warp & 3, qb = (warp - 2) >> 2;
+        const int row = g * 32 + lane;
+        const uint32_t tmem_a_lane = tmem_acc + ((uint32_t)(g * 32) << 16) + TC_A_COL0;
         int s = 0, it = 0;
         for (int c = 0; c < nchunks; c++) {
             const int rs = c & 1;
             mbar_wait(&raw_full[rs], (c >> 1) & 1);
             const uint8_t *rowp = sRaw + (size_t)(rs * TC_BM + row) * Raw<TYPE>::stride;
-            dequant_step<TYPE, 0>(rowp, sA, full, empty, row, qb, lane, stages, s, it);
-            dequant_step<TYPE, 1>(rowp, sA, full, empty, row, qb, lane, stages, s, it);
-            dequant_step<TYPE, 2>(rowp, sA, full, empty, row, qb, lane, stages, s, it);
-            dequant_step<TYPE, 3>(rowp, sA, full, empty, row, qb, lane, stages, s, it);
+            dequant_step<TYPE, 0>(rowp, tmem_a_lane, full, empty, qb, lane, stages, s, it);
+            dequant_step<TYPE, 1>(rowp, tmem_a_lane, full, empty, qb, lane, stages, s, it);
+            dequant_step<TYPE, 2>(rowp, tmem_a_lane, full, empty, qb, lane, stages, s, it);
+            dequant_step<TYPE, 3>(rowp, tmem_a_lane, full, empty, qb, lane, stages, s, it);
             __syncwarp();
             if (lane == 0) mbar_arrive(&raw_empty[rs]);
         }
@@ -327,7 +346,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const GemmTcPara
         // group split the columns
         mbar_wait(acc_full, 0);
         tc_fence_after();
-        const int g = warp & 3, half = (warp - 2) >> 2;
+        const int half = qb;
         const int ncol = bn >> 1;                              // multiple of 8
         const int grow = m0 + g * 32 + lane;
         float *drow = p.dst + (size_t)grow * p.N + n0;
@@ -443,7 +462,7 @@ static int plan_bn(int type, int64_t M, int64_t N, int sm_count, int *nt_out) {
     for (int nt = (int)((n_pad + 255) / 256); nt <= (int)(n_pad / 16) && nt <= 64; nt++) {
         const int bn = (int)(((n_pad + nt - 1) / nt + 15) / 16 * 16);
         if ((int64_t)bn * (nt - 1) >= n_pad) continue;   // last tile would be empty
-        const double mma = 2.0 * bn, l2 = (raw + 128.0 * bn) / 43.0, sm = (2 * raw + 2 * TC_A_STAGE + 2 * 128.0 * bn) / 128.0;
+        const double mma = 2.0 * bn, l2 = (raw + 128.0 * bn) / 43.0, sm = (2 * raw + 2 * 128.0 * bn) / 128.0;
         const double step = mma > l2 ? (mma > sm ? mma : sm) : (l2 > sm ? l2 : sm);
         const int64_t waves = (mt * nt + sm_count - 1) / sm_count;
         const double cost = (double)waves * (step + 40.0);
@@ -465,10 +484,10 @@ cudaError_t launch_gemm_tc(int type, const void *a, int64_t K, int64_t M, const 
     p.n_pad = (int)((N + 15) / 16 * 16);
     p.bn = plan_bn(type, M, N, sm_count, &p.nt);
     if (p.bn < 16) return cudaErrorNotSupported;
-    p.tmem_cols = p.bn <= 32 ? 32 : p.bn <= 64 ? 64 : p.bn <= 128 ? 128 : 256;
+    p.tmem_cols = 512;     // accumulator [0, 256) + up to 8 A stages x 32 columns; one CTA per SM, so no contention
     p.vec_ok = (((uintptr_t)dst & 15) == 0 && (N % 4) == 0) ? 1 : 0;
     const size_t fixed = 1024 + 2 * (size_t)TC_BM * raw_stride(type) + (2 * TC_MAX_STAGES + 5) * 8 + 16;
-    const size_t per_stage = TC_A_STAGE + (size_t)p.bn * 128;
+    const size_t per_stage = (size_t)p.bn * 128;
     int stages = (int)((227 * 1024 - fixed) / per_stage);
     if (stages > TC_MAX_STAGES) stages = TC_MAX_STAGES;
     if (stages < 2) return cudaErrorNotSupported;
