@@ -34,7 +34,8 @@ constexpr int TC_BM = 128;            // rows of a per CTA = UMMA M
 constexpr int TC_BK = 64;             // K per stage: 64 halfs = one 128-byte swizzle row
 constexpr int TC_CHUNK_K = 256;       // K per raw chunk: 8 blocks, the smallest piece that is 16-byte aligned for all types
 constexpr int TC_DQ_WARPS = 8;
-constexpr int TC_THREADS = (2 + TC_DQ_WARPS) * 32;   // warp 0 producer, warp 1 MMA issuer, 8 dequant/epilogue warps
+constexpr int TC_CTRL_WARPS = 3;      // warp 0: activation-tile producer, warp 1: MMA issuer, warp 2: raw-weight producer
+constexpr int TC_THREADS = (TC_CTRL_WARPS + TC_DQ_WARPS) * 32;
 constexpr int TC_A_COL0 = 256;                        // TMEM: accumulator in columns [0, 256), A stages of 32 columns from 256
 constexpr int TC_MAX_STAGES = 8;
 
@@ -53,6 +54,37 @@ __device__ __forceinline__ void tma_load_2d(void *smem_dst, const CUtensorMap *t
         "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%2, %3}], [%4], %5;"
         ::"r"(smem_u32(smem_dst)), "l"(tm), "r"(c0), "r"(c1), "r"(smem_u32(bar)), "l"(policy)
         : "memory");
+}
+// 1-D bulk copy delivered to the same shared-memory offset of every CTA in `mask` of this cluster; each
+// destination CTA's mbarrier (same offset) receives the transaction bytes.
+__device__ __forceinline__ void tma_load_1d_multicast(void *smem_dst, const void *gmem_src, uint32_t bytes, uint64_t *bar, uint16_t mask,
+                                                      uint64_t policy) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster.L2::cache_hint [%0], [%1], %2, [%3], %4, %5;"
+        ::"r"(smem_u32(smem_dst)), "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)), "h"(mask), "l"(policy)
+        : "memory");
+}
+// One lane of the (converged) warp.  The single-thread instructions (TMA, tcgen05.mma/commit) take uniform-register
+// operands: issued under elect.sync from a converged warp the compiler keeps addresses in uniform registers; issued
+// under `if (lane == 0)` it wraps every one of them in an ELECT/R2UR/BRA.U.ANY waterfall loop (~100 clk each,
+// profiles/r01f: the MMA thread spent more time issuing than the tensor pipe spent computing).
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(pred));
+    return pred != 0;
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap *tm) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(tm) : "memory");
@@ -98,6 +130,11 @@ __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.
 // arrive on `bar` when every tcgen05.mma issued so far by this thread has completed
 __device__ __forceinline__ void umma_commit(uint64_t *bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// the same arrive delivered to the barrier at this offset in every CTA of `mask`
+__device__ __forceinline__ void umma_commit_multicast(uint64_t *bar, uint16_t mask) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"(mask) : "memory");
 }
 __device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&v)[8]) {
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
@@ -221,7 +258,8 @@ struct GemmTcParams {
     int M, N, K;
     int row_bytes;         // K/32 * block_bytes
     int nt, bn;            // column tiles per row tile, columns per tile (multiple of 16, <= 256)
-    int n_pad;             // N rounded up to 16: rows of one K-step slab in ws
+    int cs;                // cluster size: CTAs with consecutive row tiles and the same column tile share the B tile by multicast
+    int n_pad;             // N rounded up to 32: rows of one K-step slab in ws
     int stages;
     int tmem_cols;
     int vec_ok;            // dst rows 16-byte aligned and N % 4 == 0
@@ -230,12 +268,12 @@ struct GemmTcParams {
 // 64-K step J (0..3) of the current raw chunk: wait for the A stage (32 TMEM columns) to be free, convert this
 // thread's block, store it to the thread's TMEM lane, publish the stage to the MMA thread.
 template <int TYPE, int J>
-__device__ __forceinline__ void dequant_step(const uint8_t *rowp, uint32_t tmem_a_lane, uint64_t *full, uint64_t *empty, int qb,
+__device__ __forceinline__ void dequant_step(const uint8_t *rowp, uint32_t tmem_a_lane, uint64_t *full, uint64_t *a_empty, int qb,
                                              int lane, int stages, int &s, int &it) {
     uint32_t o[16];
     if (qb) dequant_block<TYPE, 2 * J + 1>(rowp, o);
     else dequant_block<TYPE, 2 * J>(rowp, o);
-    if (it > 0) mbar_wait(&empty[s], (it - 1) & 1);
+    if (it > 0) mbar_wait(&a_empty[s], (it - 1) & 1);
     tc_fence_after();
     tmem_st16(tmem_a_lane + (uint32_t)(s * (TC_BK / 2) + qb * 16), o);
     tmem_st_wait();
@@ -246,8 +284,10 @@ __device__ __forceinline__ void dequant_step(const uint8_t *rowp, uint32_t tmem_
 }
 
 // ---- the GEMM -------------------------------------------------------------------------------------
-// Barriers: full[s] (1 producer arrive carrying the B bytes + 8 dequant warps), empty[s] (tcgen05.commit),
-// raw_full[2] (producer arrive carrying 128 row pieces), raw_empty[2] (8 dequant warps), acc_full (commit).
+// Barriers: full[s] (1 producer arrive carrying the B bytes + 8 dequant warps), a_empty[s] (local tcgen05.commit:
+// the A columns in TMEM are free), b_empty[s] (one commit from every CTA of the cluster: the B stage, which every
+// CTA of the cluster writes a slice of, is free everywhere), raw_full[2] (producer arrive carrying 128 row pieces),
+// raw_empty[2] (8 dequant warps), acc_full (commit).
 template <int TYPE>
 __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const GemmTcParams p, const __grid_constant__ CUtensorMap tm_a) {
     extern __shared__ uint8_t smem_dyn[];
@@ -257,77 +297,94 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const GemmTcPara
     uint8_t *sB = sm;
     uint8_t *sRaw = sB + stages * b_stride;
     uint64_t *full = reinterpret_cast<uint64_t *>(sRaw + 2 * TC_BM * Raw<TYPE>::stride);
-    uint64_t *empty = full + TC_MAX_STAGES;
-    uint64_t *raw_full = empty + TC_MAX_STAGES;
+    uint64_t *a_empty = full + TC_MAX_STAGES;
+    uint64_t *b_empty = a_empty + TC_MAX_STAGES;
+    uint64_t *raw_full = b_empty + TC_MAX_STAGES;
     uint64_t *raw_empty = raw_full + 2;
     uint64_t *acc_full = raw_empty + 2;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_full + 1);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int m0 = (int)(blockIdx.x / p.nt) * TC_BM;
-    const int n0 = (int)(blockIdx.x % p.nt) * p.bn;
-    const int bn = min(p.bn, p.n_pad - n0);          // columns of this tile (multiple of 16)
+    const int cs = p.cs;
+    const int crank = cs > 1 ? (int)cluster_ctarank() : 0;
+    const int group = (int)blockIdx.x / cs;             // clusters are consecutive blockIdx.x
+    const int m0 = ((group / p.nt) * cs + crank) * TC_BM;   // may lie past M (odd tile count): computed, never stored
+    const int n0 = (group % p.nt) * p.bn;
+    const int bn = min(p.bn, p.n_pad - n0);          // columns of this tile (multiple of 32)
     const int nkb = p.K / TC_BK, nchunks = p.K / TC_CHUNK_K;
 
     if (tid == 0) {
-        for (int i = 0; i < stages; i++) { mbar_init(&full[i], 1 + TC_DQ_WARPS); mbar_init(&empty[i], 1); }
+        for (int i = 0; i < stages; i++) { mbar_init(&full[i], 1 + TC_DQ_WARPS); mbar_init(&a_empty[i], 1); mbar_init(&b_empty[i], cs); }
         for (int i = 0; i < 2; i++) { mbar_init(&raw_full[i], 1); mbar_init(&raw_empty[i], TC_DQ_WARPS); }
         mbar_init(acc_full, 1);
         fence_mbar_init();
     }
     if (warp == 1) tmem_alloc(tmem_slot, (uint32_t)p.tmem_cols);
     tc_fence_before();
-    __syncthreads();
+    if (cs > 1) cluster_sync_all();     // peers multicast into this CTA's stages and arrive on its barriers
+    else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_acc = *tmem_slot;
 
     if (warp == 0) {
-        // ===== producers: lane 0 streams the FP16 activation tiles (paced by the MMA through empty[]), lane 1 the
-        // raw weight pieces (paced only by the dequant warps through raw_empty[], so it runs two chunks ahead) =====
-        const uint64_t pol = l2_policy_evict_last();   // both operands are re-read by other CTAs out of the 126 MB L2
-        if (lane == 0) {
-            const uint32_t b_bytes = (uint32_t)bn * 128u;
-            int s = 0, it = 0;
-            for (int kb = 0; kb < nkb; kb++) {
-                if (it > 0) mbar_wait(&empty[s], (it - 1) & 1);
-                mbar_arrive_expect_tx(&full[s], b_bytes);
-                tma_load_1d(sB + (size_t)s * b_stride, p.ws + ((size_t)kb * p.n_pad + n0) * 128, b_bytes, &full[s], pol);
-                if (++s == stages) { s = 0; it++; }
+        // ===== activation-tile producer (paced by the MMA through b_empty[]) =====
+        const uint64_t pol = l2_policy_evict_last();   // re-read by every row tile out of the 126 MB L2
+        const uint32_t b_bytes = (uint32_t)bn * 128u;
+        const uint32_t slice = b_bytes / (uint32_t)cs;          // rows [crank*bn/cs, +bn/cs): whole 8-row swizzle atoms
+        const uint16_t mask = (uint16_t)((1u << cs) - 1u);
+        int s = 0, it = 0;
+        for (int kb = 0; kb < nkb; kb++) {
+            if (it > 0) mbar_wait(&b_empty[s], (it - 1) & 1);
+            if (elect_one()) {
+                mbar_arrive_expect_tx(&full[s], b_bytes);           // this CTA's stage receives one slice from every CTA of the cluster
+                uint8_t *dstp = sB + (size_t)s * b_stride + (size_t)crank * slice;
+                const uint8_t *srcp = p.ws + ((size_t)kb * p.n_pad + n0) * 128 + (size_t)crank * slice;
+                if (cs > 1) tma_load_1d_multicast(dstp, srcp, slice, &full[s], mask, pol);
+                else tma_load_1d(dstp, srcp, slice, &full[s], pol);
             }
-        } else if (lane == 1) {
-            tma_prefetch_desc(&tm_a);
-            for (int c = 0; c < nchunks; c++) {
-                const int rs = c & 1;
-                if (c >= 2) mbar_wait(&raw_empty[rs], ((c >> 1) - 1) & 1);
+            __syncwarp();
+            if (++s == stages) { s = 0; it++; }
+        }
+    } else if (warp == 2) {
+        // ===== raw-weight producer (paced only by the dequant warps through raw_empty[]: runs two chunks ahead) =====
+        const uint64_t pol = l2_policy_evict_last();   // re-read by the other column tiles
+        if (elect_one()) tma_prefetch_desc(&tm_a);
+        for (int c = 0; c < nchunks; c++) {
+            const int rs = c & 1;
+            if (c >= 2) mbar_wait(&raw_empty[rs], ((c >> 1) - 1) & 1);
+            if (elect_one()) {
                 mbar_arrive_expect_tx(&raw_full[rs], (uint32_t)(TC_BM * Raw<TYPE>::stride));
                 tma_load_2d(sRaw + (size_t)rs * TC_BM * Raw<TYPE>::stride, &tm_a, c * (Raw<TYPE>::bytes / 2), m0, &raw_full[rs], pol);
             }
+            __syncwarp();
         }
-        __syncwarp();
     } else if (warp == 1) {
-        // ===== MMA issuer: one thread =====
-        if (lane == 0) {
-            const uint32_t idesc = umma_idesc_f16(bn);
-            int s = 0, it = 0;
-            for (int kb = 0; kb < nkb; kb++) {
-                mbar_wait(&full[s], it & 1);
-                tc_fence_after();
+        // ===== MMA issuer: the warp stays converged, one elected lane issues =====
+        const uint32_t idesc = umma_idesc_f16(bn);
+        const uint16_t mask = (uint16_t)((1u << cs) - 1u);
+        int s = 0, it = 0;
+        for (int kb = 0; kb < nkb; kb++) {
+            mbar_wait(&full[s], it & 1);
+            tc_fence_after();
+            if (elect_one()) {
                 const uint32_t ta = tmem_acc + TC_A_COL0 + (uint32_t)(s * (TC_BK / 2));
                 const uint64_t db = umma_desc_sw128(smem_u32(sB + (size_t)s * b_stride));
 #pragma unroll
                 for (int k = 0; k < TC_BK / 16; k++)     // per 16-K step: +8 TMEM columns of A, +32 bytes inside B's swizzle row (+2 in the address field)
                     umma_f16_ts(tmem_acc, ta + 8 * k, db + 2 * k, idesc, (uint32_t)((kb | k) != 0));
-                umma_commit(&empty[s]);
-                if (++s == stages) { s = 0; it++; }
+                umma_commit(&a_empty[s]);
+                if (cs > 1) umma_commit_multicast(&b_empty[s], mask);
+                else umma_commit(&b_empty[s]);
+                if (kb == nkb - 1) umma_commit(acc_full);
             }
-            umma_commit(acc_full);
+            __syncwarp();
+            if (++s == stages) { s = 0; it++; }
         }
-        __syncwarp();
     } else {
         // ===== dequant warps: raw blocks -> FP16 A stage; then the epilogue =====
         // a warp may only touch TMEM lanes 32*(warp%4)..+31, and TMEM lane = tile row: that fixes the row of each
         // thread; the two warps sharing a lane group take the two 32-K halves (qb) of every 64-K step
-        const int g = warp & 3, qb = (warp - 2) >> 2;
+        const int g = warp & 3, qb = (warp - TC_CTRL_WARPS) >> 2;
         const int row = g * 32 + lane;
         const uint32_t tmem_a_lane = tmem_acc + ((uint32_t)(g * 32) << 16) + TC_A_COL0;
         int s = 0, it = 0;
@@ -335,10 +392,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const GemmTcPara
             const int rs = c & 1;
             mbar_wait(&raw_full[rs], (c >> 1) & 1);
             const uint8_t *rowp = sRaw + (size_t)(rs * TC_BM + row) * Raw<TYPE>::stride;
-            dequant_step<TYPE, 0>(rowp, tmem_a_lane, full, empty, qb, lane, stages, s, it);
-            dequant_step<TYPE, 1>(rowp, tmem_a_lane, full, empty, qb, lane, stages, s, it);
-            dequant_step<TYPE, 2>(rowp, tmem_a_lane, full, empty, qb, lane, stages, s, it);
-            dequant_step<TYPE, 3>(rowp, tmem_a_lane, full, empty, qb, lane, stages, s, it);
+            dequant_step<TYPE, 0>(rowp, tmem_a_lane, full, a_empty, qb, lane, stages, s, it);
+            dequant_step<TYPE, 1>(rowp, tmem_a_lane, full, a_empty, qb, lane, stages, s, it);
+            dequant_step<TYPE, 2>(rowp, tmem_a_lane, full, a_empty, qb, lane, stages, s, it);
+            dequant_step<TYPE, 3>(rowp, tmem_a_lane, full, a_empty, qb, lane, stages, s, it);
             __syncwarp();
             if (lane == 0) mbar_arrive(&raw_empty[rs]);
         }
@@ -367,7 +424,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const GemmTcPara
         }
         tc_fence_before();
     }
-    __syncthreads();
+    if (cs > 1) cluster_sync_all();     // no CTA exits while a peer may still write its stages or barriers
+    else __syncthreads();
     if (warp == 1) {
         __syncwarp();
         tc_fence_after();
@@ -438,8 +496,19 @@ cudaError_t launch_tc(const GemmTcParams &p, int grid, size_t smem, cudaStream_t
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    gemm_tc_kernel<TYPE><<<grid, TC_THREADS, smem, s>>>(p, tm);
-    return cudaGetLastError();
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(TC_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)p.cs;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, gemm_tc_kernel<TYPE>, p, tm);
 }
 
 int raw_stride(int type) { return type == T_Q8_0 ? Raw<T_Q8_0>::stride : type == T_Q4_0 ? Raw<T_Q4_0>::stride : Raw<T_Q4_1>::stride; }
@@ -447,22 +516,22 @@ int raw_stride(int type) { return type == T_Q8_0 ? Raw<T_Q8_0>::stride : type ==
 }  // namespace
 
 size_t gemm_tc_workspace_bytes(int64_t K, int64_t N) {
-    const int64_t n_pad = (N + 15) / 16 * 16;
+    const int64_t n_pad = (N + 31) / 32 * 32;
     return (size_t)(K / TC_BK) * (size_t)n_pad * 128;
 }
 
-// Tile plan: BN = columns per CTA (multiple of 16, <= 256), chosen so that the tile count fills whole waves of
-// SMs.  Cost model per 64-K step: tensor pipe 2*BN clk, L2->SM (raw piece + BN*128 B) at
-// ~43 B/clk, shared memory (A write+read, B write+read, raw write+read) at 128 B/clk.
-static int plan_bn(int type, int64_t M, int64_t N, int sm_count, int *nt_out) {
-    const int64_t n_pad = (N + 15) / 16 * 16, mt = (M + TC_BM - 1) / TC_BM;
+// Tile plan: BN = columns per CTA (multiple of 32, <= 256), chosen so that the tile count fills whole waves of
+// SMs.  Cost model per 64-K step: tensor pipe 2*BN clk, L2->SM (raw piece + this CTA's 1/cs slice
+// of the BN*128-byte activation tile) at ~43 B/clk per SM, shared memory (B write+read, raw write+read) at 128 B/clk.
+static int plan_bn(int type, int64_t M, int64_t N, int sm_count, int cs, int *nt_out) {
+    const int64_t n_pad = (N + 31) / 32 * 32, mt = ((M + TC_BM - 1) / TC_BM + cs - 1) / cs * cs;
     const double raw = 128.0 * block_bytes(type) * 2;
     double best = 1e30;
     int best_bn = 0, best_nt = 0;
-    for (int nt = (int)((n_pad + 255) / 256); nt <= (int)(n_pad / 16) && nt <= 64; nt++) {
-        const int bn = (int)(((n_pad + nt - 1) / nt + 15) / 16 * 16);
+    for (int nt = (int)((n_pad + 255) / 256); nt <= (int)(n_pad / 32) && nt <= 64; nt++) {
+        const int bn = (int)(((n_pad + nt - 1) / nt + 31) / 32 * 32);
         if ((int64_t)bn * (nt - 1) >= n_pad) continue;   // last tile would be empty
-        const double mma = 2.0 * bn, l2 = (raw + 128.0 * bn) / 43.0, sm = (2 * raw + 2 * 128.0 * bn) / 128.0;
+        const double mma = 2.0 * bn, l2 = (raw + 128.0 * bn / cs) / 43.0, sm = (2 * raw + 2 * 128.0 * bn) / 128.0;
         const double step = mma > l2 ? (mma > sm ? mma : sm) : (l2 > sm ? l2 : sm);
         const int64_t waves = (mt * nt + sm_count - 1) / sm_count;
         const double cost = (double)waves * (step + 40.0);
@@ -473,7 +542,7 @@ static int plan_bn(int type, int64_t M, int64_t N, int sm_count, int *nt_out) {
 }
 
 cudaError_t launch_gemm_tc(int type, const void *a, int64_t K, int64_t M, const float *b, int64_t N, float *dst,
-                           void *workspace, int sm_count, cudaStream_t s) {
+                           void *workspace, int sm_count, int cluster, cudaStream_t s) {
     if (type != T_Q8_0 && type != T_Q4_0 && type != T_Q4_1) return cudaErrorNotSupported;
     if (K <= 0 || K % TC_CHUNK_K || N < 16 || M < 1 || M > (1 << 30) || N > (1 << 20) || K > (1 << 24)) return cudaErrorNotSupported;
     if (((uintptr_t)a & 15) || ((uintptr_t)workspace & 1023) || ((uintptr_t)b & 3)) return cudaErrorNotSupported;
@@ -481,12 +550,13 @@ cudaError_t launch_gemm_tc(int type, const void *a, int64_t K, int64_t M, const 
     p.a = (const uint8_t *)a; p.ws = (const uint8_t *)workspace; p.dst = dst;
     p.M = (int)M; p.N = (int)N; p.K = (int)K;
     p.row_bytes = (int)(K / LK_QK) * block_bytes(type);
-    p.n_pad = (int)((N + 15) / 16 * 16);
-    p.bn = plan_bn(type, M, N, sm_count, &p.nt);
-    if (p.bn < 16) return cudaErrorNotSupported;
+    p.n_pad = (int)((N + 31) / 32 * 32);
+    p.cs = cluster == 4 ? 4 : cluster == 1 ? 1 : 2;
+    p.bn = plan_bn(type, M, N, sm_count, p.cs, &p.nt);
+    if (p.bn < 32) return cudaErrorNotSupported;
     p.tmem_cols = 512;     // accumulator [0, 256) + up to 8 A stages x 32 columns; one CTA per SM, so no contention
     p.vec_ok = (((uintptr_t)dst & 15) == 0 && (N % 4) == 0) ? 1 : 0;
-    const size_t fixed = 1024 + 2 * (size_t)TC_BM * raw_stride(type) + (2 * TC_MAX_STAGES + 5) * 8 + 16;
+    const size_t fixed = 1024 + 2 * (size_t)TC_BM * raw_stride(type) + (3 * TC_MAX_STAGES + 5) * 8 + 16;
     const size_t per_stage = (size_t)p.bn * 128;
     int stages = (int)((227 * 1024 - fixed) / per_stage);
     if (stages > TC_MAX_STAGES) stages = TC_MAX_STAGES;
@@ -500,7 +570,7 @@ cudaError_t launch_gemm_tc(int type, const void *a, int64_t K, int64_t M, const 
     pack_b_kernel<<<pgrid, 256, 0, s>>>(b, (uint8_t *)workspace, (int)K, (int)N, p.n_pad);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    const int grid = (int)(((M + TC_BM - 1) / TC_BM) * p.nt);
+    const int grid = (int)((((M + TC_BM - 1) / TC_BM + p.cs - 1) / p.cs) * p.nt * p.cs);
     switch (type) {
         case T_Q8_0: return launch_tc<T_Q8_0>(p, grid, smem, s);
         case T_Q4_0: return launch_tc<T_Q4_0>(p, grid, smem, s);

@@ -40,8 +40,9 @@ cudaError_t launch_matmul_generic(int type, const void *a, int64_t K, int64_t M,
 
 // K2: tcgen05 prefill GEMM (lk_gemm_tc.cu).  workspace holds the FP16 copy of b.
 size_t gemm_tc_workspace_bytes(int64_t K, int64_t N);
+// cluster: 1, 2 or 4 CTAs (consecutive row tiles) share each activation tile by TMA multicast.
 cudaError_t launch_gemm_tc(int type, const void *a, int64_t K, int64_t M, const float *b, int64_t N, float *dst,
-                           void *workspace, int sm_count, cudaStream_t s);
+                           void *workspace, int sm_count, int cluster, cudaStream_t s);
 
 // K3-K5 + R4
 cudaError_t launch_rms_norm(const float *x, const float *w, float eps, int64_t ne0, int64_t nrows, float *dst,

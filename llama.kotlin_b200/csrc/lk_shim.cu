@@ -428,7 +428,7 @@ lk_status lk_compute_matmul(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b,
         if ((st = gemm_ws_reserve(ctx, lk::gemm_tc_workspace_bytes(K, N))) != LK_OK) return st;
         chain_other(ctx, dd, (size_t)M * N * 4);
         void *ws = (void *)(((uintptr_t)ctx->gemm_ws + 1023) & ~(uintptr_t)1023);
-        e = lk::launch_gemm_tc(a->type, da, K, M, (const float *)db, N, (float *)dd, ws, ctx->sm_count, ctx->stream);
+        e = lk::launch_gemm_tc(a->type, da, K, M, (const float *)db, N, (float *)dd, ws, ctx->sm_count, ctx->gemm_tc_cluster, ctx->stream);
         if (e == cudaSuccess) { launched = 2; ctx->gemm_tc_launches++; }   // pack_b_kernel + gemm_tc_kernel
     }
     if (e == cudaErrorNotSupported) {
@@ -622,6 +622,7 @@ lk_status lk_set_option(lk_ctx *ctx, const char *name, int64_t v) {
     else if (n == "gemv_ctas_per_sm") ctx->tune.ctas_per_sm = (int)v;
     else if (n == "gemv_overlap") ctx->overlap_mode = (int)v;
     else if (n == "gemm_tc_min_n") ctx->gemm_tc_min_n = (int)v;
+    else if (n == "gemm_tc_cluster") ctx->gemm_tc_cluster = (int)v;
     else return fail(ctx, LK_EINVAL_ARG, "lk_set_option: unknown option " + n);
     return LK_OK;
 }
@@ -637,6 +638,7 @@ int64_t lk_get_option(lk_ctx *ctx, const char *name) {
     if (n == "gemv_ctas_per_sm") return ctx->tune.ctas_per_sm;
     if (n == "gemv_overlap") return ctx->overlap_mode;
     if (n == "gemm_tc_min_n") return ctx->gemm_tc_min_n;
+    if (n == "gemm_tc_cluster") return ctx->gemm_tc_cluster;
     if (n == "gemm_tc_launches") return ctx->gemm_tc_launches;
     return -1;
 }

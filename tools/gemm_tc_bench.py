@@ -27,6 +27,7 @@ def main():
     ap.add_argument("--shapes", nargs="*", default=["11008x4096x512"], help="MxKxN")
     ap.add_argument("--rotate-mb", type=int, default=256)
     ap.add_argument("--reps", type=int, default=10)
+    ap.add_argument("--cluster", type=int, default=0, help="gemm_tc_cluster option (0 = library default)")
     ap.add_argument("--generic", action="store_true", help="time the CUDA-core kernel instead (gemm_tc_min_n=0)")
     args = ap.parse_args()
 
@@ -39,6 +40,8 @@ def main():
     lkc = be.lk
     if args.generic:
         lkc.set_option("gemm_tc_min_n", 0)
+    if args.cluster:
+        lkc.set_option("gemm_tc_cluster", args.cluster)
     rng = np.random.default_rng(1)
     for shp in args.shapes:
         M, K, N = (int(v) for v in shp.split("x"))
@@ -72,7 +75,7 @@ def main():
         print(json.dumps({"qtype": args.qtype, "M": M, "K": K, "N": N, "us": round(ms * 1e3, 2),
                           "TFLOPs": round(2.0 * M * K * N / (ms * 1e-3) / 1e12, 1),
                           "weight_GBps": round(wb / (ms * 1e-3) / 1e9, 1), "copies": ncopies,
-                          "path": "generic" if args.generic else "tcgen05",
+                          "path": "generic" if args.generic else "tcgen05", "cluster": lkc.get_option("gemm_tc_cluster"),
                           "tc_launches_seen": lkc.get_option("gemm_tc_launches") - before}), flush=True)
 
 
