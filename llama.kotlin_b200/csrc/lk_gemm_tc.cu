@@ -33,7 +33,10 @@ namespace {
 constexpr int TC_BM = 128;            // rows of a per CTA = UMMA M
 constexpr int TC_BK = 64;             // K per stage: 64 halfs = one 128-byte swizzle row
 constexpr int TC_CHUNK_K = 256;       // K per raw chunk: 8 blocks, the smallest piece that is 16-byte aligned for all types
-constexpr int TC_DQ_WARPS = 8;
+constexpr int TC_DQ_GROUP = 8;        // warps that fill one A stage (4 TMEM lane groups x 2 halves of the 64-K step)
+constexpr int TC_DQ_GROUPS = 1;       // 2: two groups alternate 64-K steps (measured 4% slower on config 3: the tensor pipe, not the
+                                      // convert chain, paces the loop; profiles/r01h, tools/gemm_tc_timeline.cu)
+constexpr int TC_DQ_WARPS = TC_DQ_GROUP * TC_DQ_GROUPS;
 constexpr int TC_CTRL_WARPS = 3;      // warp 0: activation-tile producer, warp 1: MMA issuer, warp 2: raw-weight producer
 constexpr int TC_THREADS = (TC_CTRL_WARPS + TC_DQ_WARPS) * 32;
 constexpr int TC_A_COL0 = 256;                        // TMEM: accumulator in columns [0, 256), A stages of 32 columns from 256
@@ -136,11 +139,13 @@ __device__ __forceinline__ void umma_commit_multicast(uint64_t *bar, uint16_t ma
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
                  ::"r"(smem_u32(bar)), "h"(mask) : "memory");
 }
-__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&v)[8]) {
-    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
-                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
-                 : "r"(taddr)
-                 : "memory");
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+          "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr)
+        : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
@@ -263,24 +268,45 @@ struct GemmTcParams {
     int stages;
     int tmem_cols;
     int vec_ok;            // dst rows 16-byte aligned and N % 4 == 0
+    unsigned long long *dbg;   // tools/gemm_tc_timeline.cu only (-DLK_TC_TIMELINE): 16 counters per CTA, else NULL
 };
 
+#ifdef LK_TC_TIMELINE
+#define TC_T0() const long long t0_ = clock64()
+#define TC_ACC(slot) do { if (p.dbg && lane == 0) p.dbg[(size_t)blockIdx.x * 16 + (slot)] += (unsigned long long)(clock64() - t0_); } while (0)
+#define TC_MARK(slot) do { if (p.dbg && lane == 0) p.dbg[(size_t)blockIdx.x * 16 + (slot)] = (unsigned long long)(clock64() - t_begin); } while (0)
+#else
+#define TC_T0() do { } while (0)
+#define TC_ACC(slot) do { } while (0)
+#define TC_MARK(slot) do { } while (0)
+#endif
+
+#ifdef LK_TC_TIMELINE
+#define g_tc_dbg_slot dbg_slot
+#endif
 // 64-K step J (0..3) of the current raw chunk: wait for the A stage (32 TMEM columns) to be free, convert this
 // thread's block, store it to the thread's TMEM lane, publish the stage to the MMA thread.
 template <int TYPE, int J>
 __device__ __forceinline__ void dequant_step(const uint8_t *rowp, uint32_t tmem_a_lane, uint64_t *full, uint64_t *a_empty, int qb,
-                                             int lane, int stages, int &s, int &it) {
+                                             int lane, int stages, int &s, int &it, unsigned long long *dbg_slot = nullptr) {
     uint32_t o[16];
     if (qb) dequant_block<TYPE, 2 * J + 1>(rowp, o);
     else dequant_block<TYPE, 2 * J>(rowp, o);
+#ifdef LK_TC_TIMELINE
+    const long long tw_ = clock64();
+#endif
     if (it > 0) mbar_wait(&a_empty[s], (it - 1) & 1);
+#ifdef LK_TC_TIMELINE
+    if (g_tc_dbg_slot && lane == 0) *g_tc_dbg_slot += (unsigned long long)(clock64() - tw_);
+#endif
     tc_fence_after();
     tmem_st16(tmem_a_lane + (uint32_t)(s * (TC_BK / 2) + qb * 16), o);
     tmem_st_wait();
     tc_fence_before();
     __syncwarp();
     if (lane == 0) mbar_arrive(&full[s]);
-    if (++s == stages) { s = 0; it++; }
+    s += TC_DQ_GROUPS;                        // this warp's next step
+    if (s >= stages) { s -= stages; it++; }
 }
 
 // ---- the GEMM -------------------------------------------------------------------------------------
@@ -305,6 +331,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const GemmTcPara
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_full + 1);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+#ifdef LK_TC_TIMELINE
+    const long long t_begin = clock64();
+#endif
     const int cs = p.cs;
     const int crank = cs > 1 ? (int)cluster_ctarank() : 0;
     const int group = (int)blockIdx.x / cs;             // clusters are consecutive blockIdx.x
@@ -314,7 +343,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const GemmTcPara
     const int nkb = p.K / TC_BK, nchunks = p.K / TC_CHUNK_K;
 
     if (tid == 0) {
-        for (int i = 0; i < stages; i++) { mbar_init(&full[i], 1 + TC_DQ_WARPS); mbar_init(&a_empty[i], 1); mbar_init(&b_empty[i], cs); }
+        for (int i = 0; i < stages; i++) { mbar_init(&full[i], 1 + TC_DQ_GROUP); mbar_init(&a_empty[i], 1); mbar_init(&b_empty[i], cs); }
         for (int i = 0; i < 2; i++) { mbar_init(&raw_full[i], 1); mbar_init(&raw_empty[i], TC_DQ_WARPS); }
         mbar_init(acc_full, 1);
         fence_mbar_init();
@@ -334,7 +363,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const GemmTcPara
         const uint16_t mask = (uint16_t)((1u << cs) - 1u);
         int s = 0, it = 0;
         for (int kb = 0; kb < nkb; kb++) {
-            if (it > 0) mbar_wait(&b_empty[s], (it - 1) & 1);
+            { TC_T0(); if (it > 0) mbar_wait(&b_empty[s], (it - 1) & 1); TC_ACC(2); }
             if (elect_one()) {
                 mbar_arrive_expect_tx(&full[s], b_bytes);           // this CTA's stage receives one slice from every CTA of the cluster
                 uint8_t *dstp = sB + (size_t)s * b_stride + (size_t)crank * slice;
@@ -351,7 +380,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const GemmTcPara
         if (elect_one()) tma_prefetch_desc(&tm_a);
         for (int c = 0; c < nchunks; c++) {
             const int rs = c & 1;
-            if (c >= 2) mbar_wait(&raw_empty[rs], ((c >> 1) - 1) & 1);
+            { TC_T0(); if (c >= 2) mbar_wait(&raw_empty[rs], ((c >> 1) - 1) & 1); TC_ACC(3); }
             if (elect_one()) {
                 mbar_arrive_expect_tx(&raw_full[rs], (uint32_t)(TC_BM * Raw<TYPE>::stride));
                 tma_load_2d(sRaw + (size_t)rs * TC_BM * Raw<TYPE>::stride, &tm_a, c * (Raw<TYPE>::bytes / 2), m0, &raw_full[rs], pol);
@@ -364,7 +393,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const GemmTcPara
         const uint16_t mask = (uint16_t)((1u << cs) - 1u);
         int s = 0, it = 0;
         for (int kb = 0; kb < nkb; kb++) {
-            mbar_wait(&full[s], it & 1);
+            if (kb == 0) TC_MARK(7);
+            { TC_T0(); mbar_wait(&full[s], it & 1); TC_ACC(1); }
+            if (kb == 0) TC_MARK(8);
             tc_fence_after();
             if (elect_one()) {
                 const uint32_t ta = tmem_acc + TC_A_COL0 + (uint32_t)(s * (TC_BK / 2));
@@ -384,50 +415,71 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const GemmTcPara
         // ===== dequant warps: raw blocks -> FP16 A stage; then the epilogue =====
         // a warp may only touch TMEM lanes 32*(warp%4)..+31, and TMEM lane = tile row: that fixes the row of each
         // thread; the two warps sharing a lane group take the two 32-K halves (qb) of every 64-K step
-        const int g = warp & 3, qb = (warp - TC_CTRL_WARPS) >> 2;
+        const int g = warp & 3, qb = ((warp - TC_CTRL_WARPS) >> 2) & 1, par = (warp - TC_CTRL_WARPS) >> 3;
         const int row = g * 32 + lane;
         const uint32_t tmem_a_lane = tmem_acc + ((uint32_t)(g * 32) << 16) + TC_A_COL0;
-        int s = 0, it = 0;
+        unsigned long long *dq_dbg = nullptr;
+#ifdef LK_TC_TIMELINE
+        if (p.dbg && warp == TC_CTRL_WARPS) dq_dbg = p.dbg + (size_t)blockIdx.x * 16 + 5;
+#endif
+        int s = par, it = 0;          // first step of this group: 64-K step `par`
         for (int c = 0; c < nchunks; c++) {
             const int rs = c & 1;
-            mbar_wait(&raw_full[rs], (c >> 1) & 1);
+            { TC_T0(); mbar_wait(&raw_full[rs], (c >> 1) & 1); if (warp == TC_CTRL_WARPS) TC_ACC(4); }
             const uint8_t *rowp = sRaw + (size_t)(rs * TC_BM + row) * Raw<TYPE>::stride;
-            dequant_step<TYPE, 0>(rowp, tmem_a_lane, full, a_empty, qb, lane, stages, s, it);
-            dequant_step<TYPE, 1>(rowp, tmem_a_lane, full, a_empty, qb, lane, stages, s, it);
-            dequant_step<TYPE, 2>(rowp, tmem_a_lane, full, a_empty, qb, lane, stages, s, it);
-            dequant_step<TYPE, 3>(rowp, tmem_a_lane, full, a_empty, qb, lane, stages, s, it);
+            if (TC_DQ_GROUPS == 1 || par == 0) {
+                dequant_step<TYPE, 0>(rowp, tmem_a_lane, full, a_empty, qb, lane, stages, s, it, dq_dbg);
+                if (TC_DQ_GROUPS == 1) dequant_step<TYPE, 1>(rowp, tmem_a_lane, full, a_empty, qb, lane, stages, s, it, dq_dbg);
+                dequant_step<TYPE, 2>(rowp, tmem_a_lane, full, a_empty, qb, lane, stages, s, it, dq_dbg);
+                if (TC_DQ_GROUPS == 1) dequant_step<TYPE, 3>(rowp, tmem_a_lane, full, a_empty, qb, lane, stages, s, it, dq_dbg);
+            } else {
+                dequant_step<TYPE, 1>(rowp, tmem_a_lane, full, a_empty, qb, lane, stages, s, it, dq_dbg);
+                dequant_step<TYPE, 3>(rowp, tmem_a_lane, full, a_empty, qb, lane, stages, s, it, dq_dbg);
+            }
             __syncwarp();
             if (lane == 0) mbar_arrive(&raw_empty[rs]);
         }
-        // epilogue: TMEM lane = output row; warp w may read lanes 32*(w%4)..+31; the two warps sharing a lane
-        // group split the columns
+        // epilogue: TMEM lane = output row; warp w may read lanes 32*(w%4)..+31
+        if (warp == TC_CTRL_WARPS) TC_MARK(9);
         mbar_wait(acc_full, 0);
+        if (warp == TC_CTRL_WARPS) TC_MARK(10);
         tc_fence_after();
-        const int half = qb;
-        const int ncol = bn >> 1;                              // multiple of 8
+        const int half = qb + 2 * par;                         // the warps sharing a lane group split the columns
+        const int ncol = bn / (2 * TC_DQ_GROUPS);              // multiple of 8
         const int grow = m0 + g * 32 + lane;
         float *drow = p.dst + (size_t)grow * p.N + n0;
-        for (int cc = half * ncol; cc < (half + 1) * ncol; cc += 8) {
-            uint32_t v[8];
-            tmem_ld8(tmem_acc + ((uint32_t)(g * 32) << 16) + (uint32_t)cc, v);
+        // 16 columns per tcgen05.ld, two loads in flight before the wait: the TMEM read latency is paid once per 32 columns
+        for (int cc = half * ncol; cc < (half + 1) * ncol; cc += 32) {
+            uint32_t v[2][16];
+            const bool second = cc + 16 < (half + 1) * ncol;       // ncol is a multiple of 16, not always of 32 (warp-uniform)
+            tmem_ld16(tmem_acc + ((uint32_t)(g * 32) << 16) + (uint32_t)cc, v[0]);
+            if (second) tmem_ld16(tmem_acc + ((uint32_t)(g * 32) << 16) + (uint32_t)(cc + 16), v[1]);
             tmem_ld_wait();
-            if (grow < p.M) {
-                if (p.vec_ok && n0 + cc + 8 <= p.N) {
-                    *reinterpret_cast<uint4 *>(drow + cc) = make_uint4(v[0], v[1], v[2], v[3]);
-                    *reinterpret_cast<uint4 *>(drow + cc + 4) = make_uint4(v[4], v[5], v[6], v[7]);
-                } else {
 #pragma unroll
-                    for (int e = 0; e < 8; e++)
-                        if (n0 + cc + e < p.N) drow[cc + e] = __uint_as_float(v[e]);
+            for (int hh = 0; hh < 2; hh++) {
+                if (hh == 1 && !second) break;
+                const int c0 = cc + 16 * hh;
+                if (grow < p.M) {
+                    if (p.vec_ok && n0 + c0 + 16 <= p.N) {
+#pragma unroll
+                        for (int q = 0; q < 4; q++)
+                            *reinterpret_cast<uint4 *>(drow + c0 + 4 * q) = make_uint4(v[hh][4 * q], v[hh][4 * q + 1], v[hh][4 * q + 2], v[hh][4 * q + 3]);
+                    } else {
+#pragma unroll
+                        for (int e = 0; e < 16; e++)
+                            if (n0 + c0 + e < p.N) drow[c0 + e] = __uint_as_float(v[hh][e]);
+                    }
                 }
             }
         }
         tc_fence_before();
+        if (warp == TC_CTRL_WARPS) TC_MARK(11);
     }
     if (cs > 1) cluster_sync_all();     // no CTA exits while a peer may still write its stages or barriers
     else __syncthreads();
     if (warp == 1) {
         __syncwarp();
+        TC_MARK(12);
         tc_fence_after();
         tmem_dealloc(tmem_acc, (uint32_t)p.tmem_cols);
     }
@@ -515,6 +567,8 @@ int raw_stride(int type) { return type == T_Q8_0 ? Raw<T_Q8_0>::stride : type ==
 
 }  // namespace
 
+void *g_gemm_tc_debug = nullptr;   // set by tools/gemm_tc_timeline.cu; NULL in the library
+
 size_t gemm_tc_workspace_bytes(int64_t K, int64_t N) {
     const int64_t n_pad = (N + 31) / 32 * 32;
     return (size_t)(K / TC_BK) * (size_t)n_pad * 128;
@@ -547,6 +601,7 @@ cudaError_t launch_gemm_tc(int type, const void *a, int64_t K, int64_t M, const 
     if (K <= 0 || K % TC_CHUNK_K || N < 16 || M < 1 || M > (1 << 30) || N > (1 << 20) || K > (1 << 24)) return cudaErrorNotSupported;
     if (((uintptr_t)a & 15) || ((uintptr_t)workspace & 1023) || ((uintptr_t)b & 3)) return cudaErrorNotSupported;
     GemmTcParams p;
+    p.dbg = (unsigned long long *)g_gemm_tc_debug;
     p.a = (const uint8_t *)a; p.ws = (const uint8_t *)workspace; p.dst = dst;
     p.M = (int)M; p.N = (int)N; p.K = (int)K;
     p.row_bytes = (int)(K / LK_QK) * block_bytes(type);
