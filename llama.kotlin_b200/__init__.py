@@ -10,6 +10,8 @@ from .ggml_compute_ops import (LkContext, computeAdd, computeMatMul, computeMul,
                                computeRmsNorm, computeSilu, computeSiluMul, computeSoftMax,
                                default_context, dequantizeTensor)
 from .ggml_cuda_backend import (GGMLCudaBackend, GGMLCudaBuffer, GGMLCudaBufferType)  # noqa: F401
+from .llama_layer import (DecoderLayer, alloc_layer, append_layer_nodes, build_decoder_graph,  # noqa: F401
+                          weight_shapes)
 from .sharded import ShardGroup, shard_byte_range, shard_rows  # noqa: F401
 from .ggml_types import (GGMLCGraph, GGMLContext, GGMLOp, GGMLStatus, GGMLTensor,  # noqa: F401
                          GGMLType, calculateContiguousStrides)

@@ -480,3 +480,42 @@ def test_prefill_gemm_tc_cluster_sizes(O, ga, cluster):
             assert rel_err(got, O.matmul(ot, blocks, K, M, x, N, nthreads=8)) <= MATMUL_REL_TOL
     finally:
         lkc.set_option("gemm_tc_cluster", old)
+
+
+# ---- config 4: one decoder layer as a GGMLCGraph -------------------------------------------------------
+@pytest.mark.parametrize("tname,hidden,ffn", [("Q4_0", 256, 704), ("Q8_0", 128, 320), ("Q4_0", 4096, 11008)])
+def test_decoder_layer_graph_matches_oracle_composition(O, tname, hidden, ffn):
+    """The 13-node layer graph (LlamaDecoderLayer.forward op order, model/LlamaModel.kt:253-285) replayed as
+    a captured sequence against the same ops composed on the oracle; two stacked layers so that the second
+    consumes the first one's output."""
+    from llama_kotlin_b200.llama_layer import alloc_layer, build_decoder_graph, oracle_layer, weight_shapes
+    gt, ot = QT[tname]
+    be = lk.GGMLCudaBackend(0)
+    shapes = weight_shapes(hidden, ffn)
+    bb = {"Q4_0": 18, "Q8_0": 34}[tname]
+    wbytes = sum(M * K // 32 * bb for M, K in shapes.values())
+    ga = lk.GGMLGraphAllocator(be, size=2 * (wbytes + 4096 + 40 * ffn * 4) + (1 << 20))
+    rng = np.random.default_rng(4001)
+    x0 = rng.normal(0, 1, hidden).astype(np.float32)
+    x = ga.allocateTensor(GGMLTensor(GGMLType.F32, [hidden]))
+    ga.setBytes(x, x0)
+    stack, host = [], []
+    for li in range(2):
+        L = alloc_layer(ga, gt, hidden, ffn)
+        blocks = {n: O.quantize(ot, synth_weights(4001 + 10 * li + i, M, K)) for i, (n, (M, K)) in enumerate(shapes.items())}
+        gains = [(1.0 + 0.1 * rng.normal(0, 1, hidden)).astype(np.float32) for _ in range(2)]
+        for n in shapes:
+            ga.setBytes(L.weights[n], blocks[n])
+        ga.setBytes(L.attn_norm, gains[0])
+        ga.setBytes(L.ffn_norm, gains[1])
+        stack.append(L)
+        host.append((blocks, gains))
+    graph, out = build_decoder_graph(ga, stack, x, hidden, ffn)
+    assert graph.nNodes == 26
+    for _ in range(3):                       # replays of the captured sequence give the same answer
+        assert be.graphCompute(graph) == lk.GGMLStatus.SUCCESS
+    got = ga.getFloats(out)
+    ref = x0
+    for blocks, gains in host:
+        ref = oracle_layer(O, ot, blocks, gains[0], gains[1], ref, hidden, ffn)
+    assert rel_err(got, ref) <= MATMUL_REL_TOL
