@@ -329,8 +329,7 @@ def gpu_arm(args, rank: int, world: int, local_rank: int) -> dict:
         "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{qtype} decode GEMV x F32, Llama-2-7B shapes 4096x4096 + 11008x4096 + 4096x11008, "
-                               f"N=1, {layers} distinct weight copies per shape per step",
+        "config": {"workload": workload_name(qtype, layers),
                    "qtype": qtype, "layers": layers, "gemv_per_step": n_gemv,
                    "weight_bytes_per_step_per_gpu": layers * sum(wbytes),
                    "l2": "inputs larger than L2 (each launch reads a weight copy not touched for a whole step)",
@@ -363,10 +362,65 @@ def gpu_arm(args, rank: int, world: int, local_rank: int) -> dict:
         res["config"]["barrier_timed_out"] = group.timed_out()
         barrier()
         group.close()
+    if world == 1 and not args.no_extras:
+        # the other two measured paths of the scope table, reported beside the headline (not part of `value`)
+        res["config"]["other_paths"] = {"prefill_gemm": prefill_gemm_line(lk, be, peaks),
+                                        "layer_graph": layer_graph_line(lk, be, peak)}
     be.free()
     if world > 1:
         dist.destroy_process_group()
     return res
+
+
+def workload_name(qtype: str, layers: int) -> str:
+    return (f"{qtype} decode GEMV x F32, Llama-2-7B shapes 4096x4096 + 11008x4096 + 4096x11008, "
+            f"N=1, {layers} distinct weight copies per shape per step")
+
+
+def prefill_gemm_line(lk, be, peaks) -> dict:
+    """BASELINE config 3: Q8_0 11008x4096 x 4096x512 F32 on the tcgen05 GEMM (pack + GEMM kernels), weights
+    rotating over 5 copies (240 MB > L2), CUDA events around 10 replays of the 5-op captured sequence."""
+    from llama_kotlin_b200 import GGMLCGraph, GGMLOp, GGMLTensor, GGMLType
+    M, K, N, copies, reps = 11008, 4096, 512, 5, 10
+    wb = M * K // 32 * 34
+    ga = lk.GGMLGraphAllocator(be, size=copies * (wb + 256) + (K * N + M * N) * 4 + (1 << 20))
+    rng = np.random.default_rng(3001)
+    b = ga.allocateTensor(GGMLTensor(GGMLType.F32, [N, K]))
+    ga.setBytes(b, rng.normal(0, 1, K * N).astype(np.float32))
+    dst = ga.allocateTensor(GGMLTensor(GGMLType.F32, [N, M]))
+    nodes, first = [], None
+    for _ in range(copies):
+        a = ga.allocateTensor(GGMLTensor(GGMLType.Q8_0, [K, M]))
+        if first is None:
+            ga.setBytes(a, synth_blocks(rng, M, K, "Q8_0"))
+            first = a
+        else:
+            ga.deviceBuffer.copyTensor(first, a)
+        nodes.append(GGMLTensor(GGMLType.F32, [N, M], op=GGMLOp.MUL_MAT, src=[a, b] + [None] * 8, bufferId=0,
+                                dataOffset=dst.dataOffset, buffer=ga.deviceBuffer))
+    graph = GGMLCGraph(nodes=nodes, allocator=ga)
+    before = be.lk.get_option("gemm_tc_launches")
+    for _ in range(3):
+        assert be.graphCompute(graph) == lk.GGMLStatus.SUCCESS
+    took_tc = be.lk.get_option("gemm_tc_launches") - before == copies
+    be.lk.sync()
+    be.lk.timer_start()
+    for _ in range(reps):
+        be.graphCompute(graph)
+    ms = be.lk.timer_stop() / (reps * copies)
+    tf = 2.0 * M * K * N / (ms * 1e-3) / 1e12
+    pk = float(peaks.get("bf16_tflops_sustained", 1400.0))
+    return {"workload": "Q8_0 11008x4096 x F32 4096x512 (BASELINE config 3), device-resident, 5 rotating weight copies",
+            "us": ms * 1e3, "TFLOPs": tf, "tcgen05_path": bool(took_tc),
+            "roofline": {"bound": "tensor", "achieved": tf, "peak": pk, "unit": "TFLOP/s", "frac": tf / pk,
+                         "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (cuBLAS bf16, same 16-bit tensor pipe)"}}
+
+
+def layer_graph_line(lk, be, hbm_peak) -> dict:
+    """BASELINE config 4: 32-layer synthetic Llama-2-7B decode step as one GGMLCGraph (tools/layer_bench.py)."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import layer_bench
+    return layer_bench.run(lk, be, "Q4_0", layers=32, steps=30, warmup=3, hbm_peak_gbs=hbm_peak)
 
 
 def check_outputs(protos, x_host, y_host, qtype, world, sumM, rank) -> dict:
@@ -423,8 +477,17 @@ def main():
     ap.add_argument("--layers", type=int, default=32)
     ap.add_argument("--opt", action="append", help="lk_set_option name=value (tuning experiments)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the config-3 / config-4 lines under config.other_paths")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     args = ap.parse_args()
+    # stdout carries exactly one JSON line: anything a library prints there (NCCL's version banner does) goes to stderr
+    json_fd = os.dup(1)
+    sys.stdout.flush()
+    os.dup2(2, 1)
+
+    def emit(obj):
+        os.write(json_fd, (json.dumps(obj) + "\n").encode())
+
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -437,11 +500,12 @@ def main():
         out = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": "GB/s", "n_gpus": args.gpus,
                "steps": args.steps, "warmup": max(args.warmup, 1), "ms_per_step": r["ms_per_step"],
                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-               "config": {"workload": f"{args.qtype} decode GEMV x F32, Llama-2-7B shapes, N=1 (bounded row sample)"},
+               "config": {"workload": workload_name(args.qtype, args.layers),
+                          "sample": "each step is a bounded row sample of that workload, see cpu_baseline.sample"},
                "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
                "e2e": {"value": r["value"], "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                "gpu_launches": 0}
-        print(json.dumps(out), flush=True)
+        emit(out)
         return
 
     res = gpu_arm(args, rank, world, local_rank)
@@ -449,7 +513,7 @@ def main():
         if not args.no_cpu_baseline and world == 1:
             r = cpu_arm(args.qtype, args.cpu_seconds, 5, 1, threads)
             res["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
-        print(json.dumps(res), flush=True)
+        emit(res)
 
 
 if __name__ == "__main__":

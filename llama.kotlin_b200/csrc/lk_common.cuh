@@ -107,6 +107,26 @@ __device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
     return d;
 }
 
+// Host: kernel launch with the programmatic-stream-serialization attribute (PDL) when `pdl` is set.  Every kernel
+// launched this way begins with pdl_wait(); pdl_launch_dependents(); -- nothing touches data before the predecessor
+// grid has completed and flushed, and the successor is released only after that, so at most one earlier kernel (this
+// one) can be running when the successor's prologue starts.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, bool pdl,
+                                 Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

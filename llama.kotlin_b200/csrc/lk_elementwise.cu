@@ -172,6 +172,8 @@ template <int OP>
 __global__ void __launch_bounds__(256) ew_kernel(const float *__restrict__ a, const float *__restrict__ b, int64_t n,
                                                  float *__restrict__ dst, int vec_ok) {
     constexpr bool BIN = (OP != OP_SILU);
+    pdl_wait();                // inputs may be the previous kernel's output
+    pdl_launch_dependents();   // the next kernel may start its prologue (a GEMV: its weight prefetch) under this one
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
     int64_t done = 0;
@@ -194,18 +196,17 @@ __global__ void __launch_bounds__(256) ew_kernel(const float *__restrict__ a, co
 }
 
 template <int OP>
-static cudaError_t launch_ew(const float *a, const float *b, int64_t n, float *dst, cudaStream_t s) {
+static cudaError_t launch_ew(const float *a, const float *b, int64_t n, float *dst, cudaStream_t s, bool pdl) {
     if (n == 0) return cudaSuccess;
     const uintptr_t al = (uintptr_t)a | (uintptr_t)dst | (uintptr_t)(b ? b : a);
     const int vec_ok = (al & 15) == 0;
     const int threads = 256;
-    ew_kernel<OP><<<grid_for((n + 3) / 4, threads), threads, 0, s>>>(a, b, n, dst, vec_ok);
-    return cudaGetLastError();
+    return launch_kernel(ew_kernel<OP>, dim3(grid_for((n + 3) / 4, threads)), dim3(threads), 0, s, pdl, a, b, n, dst, vec_ok);
 }
-cudaError_t launch_add(const float *a, const float *b, int64_t n, float *d, cudaStream_t s) { return launch_ew<OP_ADD>(a, b, n, d, s); }
-cudaError_t launch_mul(const float *a, const float *b, int64_t n, float *d, cudaStream_t s) { return launch_ew<OP_MUL>(a, b, n, d, s); }
-cudaError_t launch_silu(const float *x, int64_t n, float *d, cudaStream_t s) { return launch_ew<OP_SILU>(x, nullptr, n, d, s); }
-cudaError_t launch_silu_mul(const float *g, const float *u, int64_t n, float *d, cudaStream_t s) { return launch_ew<OP_SILU_MUL>(g, u, n, d, s); }
+cudaError_t launch_add(const float *a, const float *b, int64_t n, float *d, cudaStream_t s, bool pdl) { return launch_ew<OP_ADD>(a, b, n, d, s, pdl); }
+cudaError_t launch_mul(const float *a, const float *b, int64_t n, float *d, cudaStream_t s, bool pdl) { return launch_ew<OP_MUL>(a, b, n, d, s, pdl); }
+cudaError_t launch_silu(const float *x, int64_t n, float *d, cudaStream_t s, bool pdl) { return launch_ew<OP_SILU>(x, nullptr, n, d, s, pdl); }
+cudaError_t launch_silu_mul(const float *g, const float *u, int64_t n, float *d, cudaStream_t s, bool pdl) { return launch_ew<OP_SILU_MUL>(g, u, n, d, s, pdl); }
 
 // ---------------------------------------------------------------------------
 // block-wide reductions (256 threads)
@@ -226,23 +227,47 @@ __device__ __forceinline__ T block_reduce(T v, F op, T *scratch /* >= 32 */) {
 // ---------------------------------------------------------------------------
 // K3 RMSNorm — spec: manualRMSNorm, nativeTest core/GGMLComputeOpsTest.kt:502-521:
 // sum of squares accumulated in F64, rms = (float)sqrt(mean + eps), y = x / rms
-// (IEEE division), optional * weight (model/LlamaModel.kt:59-62).  x*x is exact
-// in F64 and the F64 sum differs from the sequential one only at the 1e-16
-// level, so the result is bit-identical to the oracle except where (float)sqrt
-// sits on a rounding boundary.  One CTA per row; bytes per element 8 (+4 weight).
+// (IEEE division), optional * weight (model/LlamaModel.kt:59-62).
+// B200's FP64 pipe is vestigial (16 DFMA + 16 F2F per thread made this a 13 us kernel for 4096 elements,
+// profiles/r01i), so each thread accumulates its share as an unevaluated float pair with error-free
+// transformations (x*x = p + e exactly by FMA; TwoSum for the running sum): ~2^-45 relative, i.e. the
+// F64 result to within a few ulp of F64; warps combine their pairs the same way through shuffles and
+// a single thread does the remaining F64 work (sum of <= 16 warp totals, divide, sqrt).  The result differs from the oracle only where (float)sqrt sits on a rounding
+// boundary.  One CTA per row; bytes per element 8 (+4 weight).
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) rms_norm_kernel(const float *__restrict__ x, const float *__restrict__ w,
+// float-pair (hi, lo) += float-pair, error-free up to second order (TwoSum on the high parts)
+__device__ __forceinline__ void pair_add(float &s, float &c, float s2, float c2) {
+    const float t = __fadd_rn(s, s2), bp = __fsub_rn(t, s);
+    const float err = __fadd_rn(__fsub_rn(s, __fsub_rn(t, bp)), __fsub_rn(s2, bp));
+    s = t;
+    c = __fadd_rn(__fadd_rn(c, c2), err);
+}
+
+__global__ void __launch_bounds__(512) rms_norm_kernel(const float *__restrict__ x, const float *__restrict__ w,
                                                        float eps, int64_t ne0, float *__restrict__ dst) {
-    __shared__ double scratch[32];
+    __shared__ float2 part[16];
+    __shared__ float rms_s;
+    pdl_wait();                // inputs may be the previous kernel's output
+    pdl_launch_dependents();   // the next kernel may start its prologue (a GEMV: its weight prefetch) under this one
     const float *xr = x + (int64_t)blockIdx.x * ne0;
     float *dr = dst + (int64_t)blockIdx.x * ne0;
-    double acc = 0.0;
+    float s = 0.f, c = 0.f;
     for (int64_t i = threadIdx.x; i < ne0; i += blockDim.x) {
-        const double v = (double)xr[i];
-        acc = fma(v, v, acc);
+        const float v = xr[i];
+        const float p = __fmul_rn(v, v), e = __fmaf_rn(v, v, -p);          // v*v = p + e exactly
+        pair_add(s, c, p, e);
     }
-    const double sumsq = block_reduce(acc, [](double a, double b) { return a + b; }, scratch);
-    const float rms = (float)sqrt(sumsq / (double)ne0 + (double)eps);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) pair_add(s, c, __shfl_xor_sync(0xffffffffu, s, o), __shfl_xor_sync(0xffffffffu, c, o));
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = make_float2(s, c);
+    __syncthreads();
+    if (threadIdx.x == 0) {    // the only F64 arithmetic of the kernel: <= 32 DADD, one divide, one sqrt, one thread
+        double sumsq = 0.0;
+        for (int wi = 0; wi < (int)(blockDim.x >> 5); wi++) sumsq += (double)part[wi].x + (double)part[wi].y;
+        rms_s = (float)sqrt(sumsq / (double)ne0 + (double)eps);
+    }
+    __syncthreads();
+    const float rms = rms_s;
     const bool zero = (rms == 0.0f) || (rms != rms);
     for (int64_t i = threadIdx.x; i < ne0; i += blockDim.x) {
         float v = zero ? 0.0f : __fdiv_rn(xr[i], rms);
@@ -252,10 +277,10 @@ __global__ void __launch_bounds__(256) rms_norm_kernel(const float *__restrict__
 }
 
 cudaError_t launch_rms_norm(const float *x, const float *w, float eps, int64_t ne0, int64_t nrows, float *dst,
-                            cudaStream_t s) {
+                            cudaStream_t s, bool pdl) {
     if (nrows == 0 || ne0 == 0) return cudaSuccess;
-    rms_norm_kernel<<<(unsigned)nrows, 256, 0, s>>>(x, w, eps, ne0, dst);
-    return cudaGetLastError();
+    const int threads = ne0 >= 2048 ? 512 : 256;
+    return launch_kernel(rms_norm_kernel, dim3((unsigned)nrows), dim3(threads), 0, s, pdl, x, w, eps, ne0, dst);
 }
 
 // ---------------------------------------------------------------------------
@@ -266,6 +291,8 @@ cudaError_t launch_rms_norm(const float *x, const float *w, float eps, int64_t n
 __global__ void __launch_bounds__(256) softmax_kernel(const float *__restrict__ x, int64_t ne0,
                                                       float *__restrict__ dst) {
     __shared__ float scratch[32];
+    pdl_wait();                // inputs may be the previous kernel's output
+    pdl_launch_dependents();   // the next kernel may start its prologue (a GEMV: its weight prefetch) under this one
     const float *xr = x + (int64_t)blockIdx.x * ne0;
     float *dr = dst + (int64_t)blockIdx.x * ne0;
     float m = -INFINITY;
@@ -281,10 +308,9 @@ __global__ void __launch_bounds__(256) softmax_kernel(const float *__restrict__ 
     for (int64_t i = threadIdx.x; i < ne0; i += blockDim.x) dr[i] = __fdiv_rn(dr[i], sum);
 }
 
-cudaError_t launch_softmax(const float *x, int64_t ne0, int64_t nrows, float *dst, cudaStream_t s) {
+cudaError_t launch_softmax(const float *x, int64_t ne0, int64_t nrows, float *dst, cudaStream_t s, bool pdl) {
     if (nrows == 0 || ne0 == 0) return cudaSuccess;
-    softmax_kernel<<<(unsigned)nrows, 256, 0, s>>>(x, ne0, dst);
-    return cudaGetLastError();
+    return launch_kernel(softmax_kernel, dim3((unsigned)nrows), dim3(256), 0, s, pdl, x, ne0, dst);
 }
 
 }  // namespace lk

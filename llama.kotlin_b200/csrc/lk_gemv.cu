@@ -312,7 +312,11 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
     uint32_t *xs = (uint32_t *)(smem + p.x_off);         // [nblk][GEMV_XSLOT_WORDS]
     uint8_t *stage0 = smem + p.stage_off;
 
-    pdl_launch_dependents();  // the next GEMV may be scheduled beside us and start its weight prefetch
+    // The next kernel of the stream may be scheduled beside us as soon as every CTA has signalled.  An independent
+    // launch (WAIT_END) signals at once; a launch that waits for its predecessor signals only after that wait, so
+    // that whatever starts next finds everything before this launch complete (the host-side bookkeeping,
+    // gemv_wait_mode in lk_shim.cu, closes its in-flight set at exactly that point).
+    if (p.wait_mode == GEMV_WAIT_END) pdl_launch_dependents();
     {   // touch both hot parameter lines now: the two constant-cache misses overlap instead of serialising later
         const int t0 = p.K, t1 = p.red_stride;
         asm volatile("" ::"r"(t0), "r"(t1));
@@ -384,7 +388,10 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
     for (int r = warp; r < p.red_rows; r += p.cwarps)
         if (lane < GEMV_RED_PAD) red[r * p.red_stride + p.ncw * 8 + lane] = 0.f;
     __syncthreads();   // barriers initialised by the producer
-    if (p.wait_mode != GEMV_WAIT_END) pdl_wait();  // activations may be the previous kernel's output
+    if (p.wait_mode != GEMV_WAIT_END) {
+        pdl_wait();                // activations may be the previous kernel's output
+        pdl_launch_dependents();   // the next kernel can start its prologue / weight prefetch under our main loop
+    }
     if (tid == 0) LK_TL(3);
     prep_x<TYPE>(p, xs, tid, nct);
     if (tid == 0) LK_TL(24);

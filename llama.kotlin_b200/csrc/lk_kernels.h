@@ -45,12 +45,14 @@ cudaError_t launch_gemm_tc(int type, const void *a, int64_t K, int64_t M, const 
                            void *workspace, int sm_count, int cluster, cudaStream_t s);
 
 // K3-K5 + R4
+// pdl: launch with programmatic stream serialization (the kernels wait for their predecessor themselves), so the
+// launch overlaps the predecessor's tail and a following GEMV can prefetch its weights under the op.
 cudaError_t launch_rms_norm(const float *x, const float *w, float eps, int64_t ne0, int64_t nrows, float *dst,
-                            cudaStream_t s);
-cudaError_t launch_silu(const float *x, int64_t n, float *dst, cudaStream_t s);
-cudaError_t launch_silu_mul(const float *g, const float *u, int64_t n, float *dst, cudaStream_t s);
-cudaError_t launch_softmax(const float *x, int64_t ne0, int64_t nrows, float *dst, cudaStream_t s);
-cudaError_t launch_add(const float *a, const float *b, int64_t n, float *dst, cudaStream_t s);
-cudaError_t launch_mul(const float *a, const float *b, int64_t n, float *dst, cudaStream_t s);
+                            cudaStream_t s, bool pdl = false);
+cudaError_t launch_silu(const float *x, int64_t n, float *dst, cudaStream_t s, bool pdl = false);
+cudaError_t launch_silu_mul(const float *g, const float *u, int64_t n, float *dst, cudaStream_t s, bool pdl = false);
+cudaError_t launch_softmax(const float *x, int64_t ne0, int64_t nrows, float *dst, cudaStream_t s, bool pdl = false);
+cudaError_t launch_add(const float *a, const float *b, int64_t n, float *dst, cudaStream_t s, bool pdl = false);
+cudaError_t launch_mul(const float *a, const float *b, int64_t n, float *dst, cudaStream_t s, bool pdl = false);
 
 }  // namespace lk

@@ -20,7 +20,9 @@ lk_status cuda_fail(lk_ctx *ctx, cudaError_t e, const char *what) {
     return fail(ctx, e == cudaErrorMemoryAllocation ? LK_ENOMEM : LK_ECUDA,
                 std::string("CUDA error: ") + cudaGetErrorString(e) + " at " + what);
 }
-// a non-GEMV op (normal kernel / copy): serialises fully behind everything earlier; remember what it wrote
+// a non-GEMV op (elementwise kernel, copy): it starts only after everything earlier has completed (normal stream
+// order, or its own griddepcontrol.wait before it releases its successor); remember what it wrote, because the next
+// GEMV may start its weight prefetch while this op is still running
 void chain_other(lk_ctx *ctx, const void *dst, size_t bytes) {
     ctx->chain_reads.clear();
     ctx->chain_writes.clear();
@@ -371,6 +373,12 @@ void count_launch(lk_ctx *ctx, int n = 1) {
     if (ctx->capturing) ctx->capture_launches += n; else ctx->launches += n;
 }
 
+// elementwise ops join the programmatic-dependent-launch chain under the same policy as the GEMV (gemv_pdl option:
+// 1 = inside captured sequences, 2 = always); host-staged operands keep plain stream order
+bool op_pdl(const lk_ctx *ctx, const OpScope &sc) {
+    return !sc.any_host && ((ctx->pdl_mode == 2) || (ctx->pdl_mode == 1 && ctx->capturing));
+}
+
 bool same_shape(const lk_tensor *a, const lk_tensor *b) {
     for (int d = 0; d < LK_MAX_DIMS; d++) {
         const int64_t x = a->ne[d] > 0 ? a->ne[d] : (d == 0 ? 0 : 1), y = b->ne[d] > 0 ? b->ne[d] : (d == 0 ? 0 : 1);
@@ -462,7 +470,7 @@ lk_status lk_compute_dequantize(lk_ctx *ctx, const lk_tensor *src, const lk_tens
     return finish(sc);
 }
 
-typedef cudaError_t (*binary_fn)(const float *, const float *, int64_t, float *, cudaStream_t);
+typedef cudaError_t (*binary_fn)(const float *, const float *, int64_t, float *, cudaStream_t, bool);
 
 static lk_status binary_op(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, const lk_tensor *dst, binary_fn fn,
                            const char *name) {
@@ -481,7 +489,7 @@ static lk_status binary_op(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, 
     if ((st = resolve(sc, b, false, &db, "b")) != LK_OK) return st;
     if ((st = resolve(sc, dst, true, &dd, "dst")) != LK_OK) return st;
     chain_other(ctx, dd, (size_t)num_elements(a) * 4);
-    cudaError_t e = fn((const float *)da, (const float *)db, num_elements(a), (float *)dd, ctx->stream);
+    cudaError_t e = fn((const float *)da, (const float *)db, num_elements(a), (float *)dd, ctx->stream, op_pdl(ctx, sc));
     if (e != cudaSuccess) return lk::cuda_fail(ctx, e, name);
     count_launch(ctx);
     return finish(sc);
@@ -519,7 +527,7 @@ lk_status lk_compute_silu(lk_ctx *ctx, const lk_tensor *x, const lk_tensor *dst)
     if ((st = resolve(sc, x, false, &dx, "x")) != LK_OK) return st;
     if ((st = resolve(sc, dst, true, &dd, "dst")) != LK_OK) return st;
     chain_other(ctx, dd, (size_t)num_elements(x) * 4);
-    cudaError_t e = lk::launch_silu((const float *)dx, num_elements(x), (float *)dd, ctx->stream);
+    cudaError_t e = lk::launch_silu((const float *)dx, num_elements(x), (float *)dd, ctx->stream, op_pdl(ctx, sc));
     if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "silu launch");
     count_launch(ctx);
     return finish(sc);
@@ -542,7 +550,7 @@ lk_status lk_compute_rms_norm(lk_ctx *ctx, const lk_tensor *x, const lk_tensor *
     if ((st = resolve(sc, dst, true, &dd, "dst")) != LK_OK) return st;
     const int64_t n = num_elements(x);
     chain_other(ctx, dd, (size_t)n * 4);
-    cudaError_t e = lk::launch_rms_norm((const float *)dx, (const float *)dw, eps, ne0, ne0 ? n / ne0 : 0, (float *)dd, ctx->stream);
+    cudaError_t e = lk::launch_rms_norm((const float *)dx, (const float *)dw, eps, ne0, ne0 ? n / ne0 : 0, (float *)dd, ctx->stream, op_pdl(ctx, sc));
     if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "rmsNorm launch");
     count_launch(ctx);
     return finish(sc);
@@ -559,7 +567,7 @@ lk_status lk_compute_softmax(lk_ctx *ctx, const lk_tensor *x, const lk_tensor *d
     if ((st = resolve(sc, dst, true, &dd, "dst")) != LK_OK) return st;
     const int64_t ne0 = x->ne[0], n = num_elements(x);
     chain_other(ctx, dd, (size_t)n * 4);
-    cudaError_t e = lk::launch_softmax((const float *)dx, ne0, ne0 ? n / ne0 : 0, (float *)dd, ctx->stream);
+    cudaError_t e = lk::launch_softmax((const float *)dx, ne0, ne0 ? n / ne0 : 0, (float *)dd, ctx->stream, op_pdl(ctx, sc));
     if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "softmax launch");
     count_launch(ctx);
     return finish(sc);

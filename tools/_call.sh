@@ -1,4 +1,2 @@
-timeout 600 python -m pytest tests/test_gpu_parity.py -x -q -k "decoder_layer" > gpurun_out/pytest_layer.log 2>&1; echo layer=$?; tail -8 gpurun_out/pytest_layer.log
-timeout 300 python tools/layer_bench.py 2>&1 | tail -2 | tee gpurun_out/layer_bench.log
-timeout 300 python tools/layer_bench.py --opt gemv_overlap=0 2>&1 | tail -1 | tee -a gpurun_out/layer_bench.log
-timeout 300 python tools/layer_bench.py --qtype Q8_0 2>&1 | tail -1 | tee -a gpurun_out/layer_bench.log
+python bench.py > gpurun_out/bench_r01e.json 2> gpurun_out/bench_r01e.err; echo bench=$?; wc -l gpurun_out/bench_r01e.json; python -c "
+import json; d=json.load(open('gpurun_out/bench_r01e.json')); print(d['value'], d['roofline']['frac'], d['e2e']['value'], d['cpu_baseline']); print(json.dumps(d['config']['other_paths'], indent=1)[:1800])"; tail -3 gpurun_out/bench_r01e.err

@@ -22,7 +22,7 @@ from bench import BLOCK_BYTES, synth_blocks  # noqa: E402
 
 
 def run(lk, be, qtype: str = "Q4_0", layers: int = 32, steps: int = 50, warmup: int = 5, hidden: int = 4096,
-        ffn: int = 11008, hbm_peak_gbs: float = 0.0) -> dict:
+        ffn: int = 11008, hbm_peak_gbs: float = 0.0, drop_ops=()) -> dict:
     from llama_kotlin_b200 import GGMLTensor, GGMLType
     from llama_kotlin_b200.llama_layer import alloc_layer, build_decoder_graph, weight_shapes
     gt = getattr(GGMLType, qtype)
@@ -48,6 +48,8 @@ def run(lk, be, qtype: str = "Q4_0", layers: int = 32, steps: int = 50, warmup: 
         ga.setBytes(L.ffn_norm, np.ones(hidden, np.float32))
         stack.append(L)
     graph, out = build_decoder_graph(ga, stack, x, hidden, ffn)
+    if drop_ops:     # timing experiments only (the numbers are then meaningless): how much of the step do these ops cost?
+        graph.nodes = [n for n in graph.nodes if n.op.name not in drop_ops]
     lkc = be.lk
     for _ in range(warmup):
         assert be.graphCompute(graph) == lk.GGMLStatus.SUCCESS
@@ -74,6 +76,7 @@ def main():
     ap.add_argument("--layers", type=int, default=32)
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--opt", action="append")
+    ap.add_argument("--drop", nargs="*", default=[], help="op names to leave out (timing experiments), e.g. RMS_NORM ADD")
     args = ap.parse_args()
     import llama_kotlin_b200 as lk
     be = lk.GGMLCudaBackend(0)
@@ -85,7 +88,10 @@ def main():
         peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", 0))
     except Exception:
         pass
-    print(json.dumps(run(lk, be, args.qtype, args.layers, args.steps, hbm_peak_gbs=peak)), flush=True)
+    res = run(lk, be, args.qtype, args.layers, args.steps, hbm_peak_gbs=peak, drop_ops=tuple(args.drop))
+    if args.drop:
+        res["dropped_ops"] = args.drop
+    print(json.dumps(res), flush=True)
 
 
 if __name__ == "__main__":
