@@ -201,6 +201,11 @@ LK_API lk_status   lk_buf_ipc_import(lk_ctx *ctx, const uint8_t handle[LK_IPC_HA
  * The first call (which uploads the peer table) must be made outside capture. */
 LK_API lk_status   lk_peer_barrier(lk_ctx *ctx, lk_buf *own_flags, lk_buf *const *peer_flags, int32_t npeers,
                             int32_t rank, uint32_t epoch);
+/* All-gather as peer stores: copies `count` floats at byte offset `off` of `local` to the same offset of every
+ * buffer in peer_bufs (entries equal to `local` or NULL are skipped) over NVLink, stream-ordered; follow it
+ * with lk_peer_barrier.  Used where the slice comes from an elementwise op instead of a GEMV epilogue. */
+LK_API lk_status   lk_peer_push_f32(lk_ctx *ctx, lk_buf *local, uint64_t off, int64_t count,
+                             lk_buf *const *peer_bufs, int32_t npeers);
 /* Sharded computeMatMul, N == 1: this rank owns rows [row0, row0 + a_shard.ne[1]) of the
  * M_total-row weight; writes its slice of dst_full (ne=[1, M_total]) locally and, when
  * peers != NULL, into the same offsets of every peer's buffer from the GEMV epilogue,

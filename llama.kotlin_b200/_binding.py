@@ -104,6 +104,7 @@ def lib() -> C.CDLL:
         "lk_buf_ipc_export": (i32, [vp, vp]),
         "lk_buf_ipc_import": (i32, [vp, vp, u64, C.POINTER(vp)]),
         "lk_peer_barrier": (i32, [vp, vp, C.POINTER(vp), i32, i32, u32]),
+        "lk_peer_push_f32": (i32, [vp, vp, u64, i64, C.POINTER(vp), i32]),
         "lk_compute_matmul_sharded": (i32, [vp, tp, tp, tp, i64, i64, C.POINTER(vp), i32]),
     }
     for name, (res, args) in sig.items():

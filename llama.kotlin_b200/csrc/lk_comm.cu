@@ -165,6 +165,39 @@ lk_status lk_peer_barrier(lk_ctx *ctx, lk_buf *own_flags, lk_buf *const *peer_fl
     return LK_OK;
 }
 
+struct PushPeers { float *ptr[8]; int n; };
+__global__ void __launch_bounds__(256) peer_push_kernel(const float *__restrict__ src, int64_t n, PushPeers peers) {
+    lk::pdl_wait();                // the slice may be the previous kernel's output
+    lk::pdl_launch_dependents();
+    const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += nthr) {
+        const float v = src[i];
+        for (int q = 0; q < peers.n; q++) peers.ptr[q][i] = v;
+    }
+}
+
+lk_status lk_peer_push_f32(lk_ctx *ctx, lk_buf *local, uint64_t off, int64_t count, lk_buf *const *peer_bufs, int32_t npeers) {
+    if (!ctx || !local || count < 0 || npeers < 0 || npeers > 8) return lk::fail(ctx, LK_EINVAL_ARG, "lk_peer_push_f32: bad argument");
+    if ((off & 3) || off > local->size || (uint64_t)count * 4 > local->size - off) return lk::fail(ctx, LK_EBOUNDS, "lk_peer_push_f32: range outside the buffer");
+    PushPeers pp = {};
+    for (int q = 0; q < npeers; q++) {
+        if (!peer_bufs || !peer_bufs[q] || peer_bufs[q] == local) continue;
+        if (off + (uint64_t)count * 4 > peer_bufs[q]->size) return lk::fail(ctx, LK_EBOUNDS, "lk_peer_push_f32: peer buffer too small");
+        pp.ptr[pp.n++] = (float *)((uint8_t *)peer_bufs[q]->ptr + off);
+    }
+    if (count == 0 || pp.n == 0) return LK_OK;
+    LK_CUDA(ctx, cudaSetDevice(ctx->device));
+    const float *src = (const float *)((uint8_t *)local->ptr + off);
+    lk::chain_other(ctx, nullptr, 0);      // writes land in peer memory only
+    const bool pdl = (ctx->pdl_mode == 2) || (ctx->pdl_mode == 1 && ctx->capturing);
+    int grid = (int)((count + 255) / 256);
+    if (grid > ctx->sm_count) grid = ctx->sm_count;
+    cudaError_t e = lk::launch_kernel(peer_push_kernel, dim3(grid), dim3(256), 0, ctx->stream, pdl, src, count, pp);
+    if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "peer push launch");
+    if (ctx->capturing) ctx->capture_launches++; else ctx->launches++;
+    return LK_OK;
+}
+
 lk_status lk_compute_matmul_sharded(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, const lk_tensor *dst,
                                     int64_t row0, int64_t M_total, lk_buf *const *peer_dst, int32_t npeers) {
     if (!ctx || !a || !b || !dst) return lk::fail(ctx, LK_EINVAL_ARG, "lk_compute_matmul_sharded: NULL argument");

@@ -503,14 +503,15 @@ template <int TYPE>
 static cudaError_t launch_type(const GemvParams &p, int grid, int smem, int pdl, cudaStream_t s) {
     if (p.cwarps <= 8) return launch_one<TYPE, 8, 2>(p, grid, smem, pdl, s);
     if (p.cwarps <= 12) return launch_one<TYPE, 12, 2>(p, grid, smem, pdl, s);
-    return launch_one<TYPE, 16, 2>(p, grid, smem, pdl, s);
+    if (p.cwarps <= 16) return launch_one<TYPE, 16, 2>(p, grid, smem, pdl, s);
+    return launch_one<TYPE, 28, 1>(p, grid, smem, pdl, s);   // K up to 28672 (Llama-2-70B down projection): one CTA per SM
 }
 
 cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const float *b, float *dst,
                         int64_t row_offset, const GemvPeers &peers, const GemvTuning &tune, int sm_count,
                         cudaStream_t s) {
     const int bb = block_bytes(type);
-    if (bb == 0 || K <= 0 || M <= 0 || (K % 64) != 0 || K > 32 * 32 * 16 || M > (1 << 30))
+    if (bb == 0 || K <= 0 || M <= 0 || (K % 64) != 0 || K > 32 * 32 * 28 || M > (1 << 30))
         return cudaErrorNotSupported;
     if (((uintptr_t)a & 15) || ((uintptr_t)b & 15)) return cudaErrorNotSupported;
 
@@ -527,15 +528,16 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
     const int target_warps = tune.variant > 0 ? tune.variant : 8;   // consumer warps to aim for
     p.rg = target_warps / p.ncw;
     if (p.rg < 1) p.rg = 1;
-    while (p.rg * p.ncw > 16) p.rg--;
-    if (p.rg < 1) return cudaErrorNotSupported;
+    while (p.rg > 1 && p.rg * p.ncw > 16) p.rg--;
+    if (p.ncw > 28) return cudaErrorNotSupported;
     p.cwarps = p.rg * p.ncw;
     p.unit_rows = 1;
     while ((p.unit_rows * p.row_bytes) % 16) p.unit_rows *= 2;   // <= 8 because row_bytes is even
     if (M % p.unit_rows) return cudaErrorNotSupported;
 
     // two CTAs (this launch and the next) share one SM's 227 KB when cwarps <= 12
-    const int budget = tune.smem_budget > 0 ? tune.smem_budget : 112 * 1024;
+    const int budget = tune.smem_budget > 0 ? tune.smem_budget : (p.ncw > 16 ? 216 : 112) * 1024;   // > 16 column warps: the
+                                                                                                     // x planes alone need up to 98 KB
     const int stage_target = tune.stage_bytes > 0 ? tune.stage_bytes : 32 * 1024;
     int quant = p.unit_rows;                       // stage_rows: multiple of unit_rows (TMA size) and of rg
     while (quant % p.rg) quant += p.unit_rows;

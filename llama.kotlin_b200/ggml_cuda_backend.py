@@ -129,10 +129,15 @@ class GGMLCudaBackend:
     def synchronize(self) -> None:
         self.lk.sync()
 
-    def free(self) -> None:
+    def releaseGraphs(self) -> None:
+        """Destroys the captured CUDA graphs (a graph holding NCCL kernels must go before its communicator)."""
+        self.lk.sync()
         for h, _ in self._captured.values():
             B.lib().lk_graph_destroy(h)
         self._captured.clear()
+
+    def free(self) -> None:
+        self.releaseGraphs()
         self.lk.close()
 
     # -- graph execution -------------------------------------------------------------
@@ -141,6 +146,14 @@ class GGMLCudaBackend:
         ex = node.extra if isinstance(node.extra, dict) else None
         if ex is not None and "shard_barrier" in ex:      # exchange point of a row-sharded matmul (sharded.py)
             ex["shard_barrier"].barrier()
+            return
+        if ex is not None and "shard_allgather" in ex:    # baseline exchange: in-place ncclAllGather of per-rank slices
+            grp, count = ex["shard_allgather"]
+            grp.allgather(node.buffer, node.dataOffset, count)
+            return
+        if ex is not None and "shard_push" in ex:         # the same exchange as peer stores (follow with shard_barrier)
+            grp, count, peers = ex["shard_push"]
+            grp.push(node.buffer, node.dataOffset, count, peers)
             return
         if op == GGMLOp.NONE:
             return

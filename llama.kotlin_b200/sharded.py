@@ -104,6 +104,13 @@ class ShardGroup:
         B.check(B.lib().lk_peer_barrier(self.lk.handle, self.flags.handle, arr, self.world, self.rank, 0), self.lk.handle)
         self._barrier_ready = True
 
+    def push(self, buf, offset: int, count: int, peer_bufs: Sequence[object]) -> None:
+        """All-gather as peer stores: this rank's `count` floats at `offset` of `buf` go to the same offset of
+        every peer's buffer (map_dst_buffer of `buf`); follow with barrier()."""
+        arr = (C.c_void_p * len(peer_bufs))(*[p if isinstance(p, C.c_void_p) else C.c_void_p(p) for p in peer_bufs])
+        B.check(B.lib().lk_peer_push_f32(self.lk.handle, buf.handle, int(offset), int(count), arr, len(peer_bufs)),
+                self.lk.handle)
+
     def timed_out(self) -> bool:
         import numpy as np
         w = np.zeros(16, np.uint32)

@@ -519,3 +519,15 @@ def test_decoder_layer_graph_matches_oracle_composition(O, tname, hidden, ffn):
     for blocks, gains in host:
         ref = oracle_layer(O, ot, blocks, gains[0], gains[1], ref, hidden, ffn)
     assert rel_err(got, ref) <= MATMUL_REL_TOL
+
+
+@pytest.mark.parametrize("tname", ["Q4_0", "Q8_0", "Q4_1"])
+@pytest.mark.parametrize("M,K", [(96, 28672), (33, 20480), (64, 16448)])
+def test_gemv_long_rows(O, ga, tname, M, K):
+    """K above 16384 (more than 16 column warps): the 28-warp, one-CTA-per-SM variant; 28672 is the
+    Llama-2-70B down projection (BASELINE config 5)."""
+    gt, ot = QT[tname]
+    blocks = O.quantize(ot, synth_weights(1200 + M, M, K))
+    x = synth_acts(1200 + M, K)
+    got = host_matmul(ga, gt, blocks, K, M, x, 1)
+    assert rel_err(got, O.matmul(ot, blocks, K, M, x, 1)) <= MATMUL_REL_TOL

@@ -1,2 +1,4 @@
-python bench.py > gpurun_out/bench_r01e.json 2> gpurun_out/bench_r01e.err; echo bench=$?; wc -l gpurun_out/bench_r01e.json; python -c "
-import json; d=json.load(open('gpurun_out/bench_r01e.json')); print(d['value'], d['roofline']['frac'], d['e2e']['value'], d['cpu_baseline']); print(json.dumps(d['config']['other_paths'], indent=1)[:1800])"; tail -3 gpurun_out/bench_r01e.err
+timeout 100 python tools/ffn70b_bench.py 2> gpurun_out/ffn_g1.err | tee gpurun_out/ffn70b.jsonl
+for g in 2 4 8; do for ex in push nccl; do
+timeout 100 python -m torch.distributed.run --nnodes=1 --nproc-per-node $g --master-addr 127.0.0.1 --master-port 2953$g tools/ffn70b_bench.py --exchange $ex 2> gpurun_out/ffn_g${g}_$ex.err | tee -a gpurun_out/ffn70b.jsonl; echo "g$g $ex rc=$?"
+done; done
