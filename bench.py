@@ -337,6 +337,7 @@ def gpu_arm(args, rank: int, world: int, local_rank: int) -> dict:
                                    "tracking lets consecutive launches overlap (PDL); dependent_chain_GBps is the same "
                                    "step with every GEMV made to wait for its predecessor before reading x",
                    "dependent_chain_GBps": bytes_step * args.steps / (ms_dep * 1e-3) / 1e9,
+                   "activation_bits": int(8 * lkc.get_option("gemv_act_planes")),
                    "parallelism": "single GPU" if world == 1 else
                                   f"weight rows sharded over {world} ranks (each rank a full 7B-shape shard), outputs stored "
                                   f"into every rank's dst over NVLink from the GEMV epilogue + one flag barrier per step",

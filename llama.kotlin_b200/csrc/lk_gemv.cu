@@ -52,7 +52,9 @@
 namespace lk {
 
 constexpr int GEMV_MAX_STAGES = 8;
-constexpr int GEMV_XSLOT_WORDS = 28;   // 24 plane words + sumT, scale, 2 pad: 7 x 16 B => conflict-free LDS.128
+// activation slot of one block column: NP planes x 8 words, then sumT, scale, pad: 7 (NP=3) or 5 (NP=2) x 16 B, an odd
+// number of 16-byte units => conflict-free LDS.128
+__host__ __device__ constexpr int gemv_xslot_words(int np) { return np * 8 + 4; }
 constexpr int GEMV_RED_PAD = 8;        // floats of padding per partial-sum row (bank spread for finish_rows)
 
 __device__ __forceinline__ int dp4a_uu(uint32_t a, uint32_t b, int c) {
@@ -79,34 +81,39 @@ __device__ __forceinline__ int dp4a_ss(uint32_t a, uint32_t b, int c) {
 // Activation registers of one thread (one 32-element block column): q[plane][word].  For Q4 types
 // word 2j holds elements 8j+{0,2,4,6} (the low nibbles of quant word j) and word 2j+1 elements
 // 8j+{1,3,5,7}; for Q8_0 word j holds elements 4j..4j+3.
+template <int NP>
 struct XRegs {
-    uint32_t q[3][8];
+    uint32_t q[NP][8];
     float c;        // Q4_0: -8 * s * sumT;  Q4_1: s * sumT;  Q8_0: unused
-    float s;        // 2^(E-22)
+    float s;        // 2^(E-22) (NP = 3) or 2^(E-14) (NP = 2)
 };
 
 // 16 quant bytes (4 aligned words) of 4-bit quants x the block's activations; exact int32
-__device__ __forceinline__ int q4_block_isum(const uint32_t (&q)[4], const XRegs &x) {
-    int i0 = 0, i1 = 0, i2 = 0;
+template <int NP>
+__device__ __forceinline__ int q4_block_isum(const uint32_t (&q)[4], const XRegs<NP> &x) {
+    int acc[NP];
+#pragma unroll
+    for (int pl = 0; pl < NP; pl++) acc[pl] = 0;
 #pragma unroll
     for (int j = 0; j < 4; j++) {
         const uint32_t lo = q[j] & 0x0F0F0F0Fu, hi = (q[j] >> 4) & 0x0F0F0F0Fu;
-        i0 = dp4a_uu(lo, x.q[0][2 * j], i0);
-        i1 = dp4a_uu(lo, x.q[1][2 * j], i1);
-        i2 = dp4a_us(lo, x.q[2][2 * j], i2);
-        i0 = dp4a_uu(hi, x.q[0][2 * j + 1], i0);
-        i1 = dp4a_uu(hi, x.q[1][2 * j + 1], i1);
-        i2 = dp4a_us(hi, x.q[2][2 * j + 1], i2);
+#pragma unroll
+        for (int pl = 0; pl < NP; pl++) {       // the top plane holds signed bytes
+            acc[pl] = (pl == NP - 1) ? dp4a_us(lo, x.q[pl][2 * j], acc[pl]) : dp4a_uu(lo, x.q[pl][2 * j], acc[pl]);
+            acc[pl] = (pl == NP - 1) ? dp4a_us(hi, x.q[pl][2 * j + 1], acc[pl]) : dp4a_uu(hi, x.q[pl][2 * j + 1], acc[pl]);
+        }
     }
-    return (i2 << 16) + ((i1 << 8) + i0);   // exact: |.| < 2^31 (nibble <= 15, |T| <= 2^22, 32 terms)
+    // exact: |.| < 2^31 (nibble <= 15, |T| <= 2^22 resp. 2^14, 32 terms)
+    if (NP == 3) return (acc[NP - 1] << 16) + ((acc[1] << 8) + acc[0]);
+    return (acc[1] << 8) + acc[0];
 }
 
 // dot of one block (32 consecutive k of one row) with the thread's activations.
 // row: 4-byte aligned shared-memory address of the row; b: block index within the row.
 // 18- and 34-byte blocks start on a 4-byte boundary only for even b: the thread loads the words
 // that cover its block and one PRMT per word (selector chosen by parity) realigns them.
-template <int TYPE>
-__device__ __forceinline__ float block_dot(const uint32_t *row, int b, const XRegs &x) {
+template <int TYPE, int NP>
+__device__ __forceinline__ float block_dot(const uint32_t *row, int b, const XRegs<NP> &x) {
     const bool odd = b & 1;
     if (TYPE == T_Q4_0) {
         const uint32_t *wp = row + 4 * b + (b >> 1);
@@ -137,17 +144,22 @@ __device__ __forceinline__ float block_dot(const uint32_t *row, int b, const XRe
 #pragma unroll
         for (int i = 0; i < 9; i++) w[i] = wp[i];
         const uint32_t sel = odd ? 0x7654u : 0x5432u;
-        int i0 = 0, i1 = 0, i2 = 0;
+        int acc[NP];
+#pragma unroll
+        for (int pl = 0; pl < NP; pl++) acc[pl] = 0;
 #pragma unroll
         for (int j = 0; j < 8; j++) {
             const uint32_t q = __byte_perm(w[j], w[j + 1], sel);
-            i0 = dp4a_su(q, x.q[0][j], i0);
-            i1 = dp4a_su(q, x.q[1][j], i1);
-            i2 = dp4a_ss(q, x.q[2][j], i2);
+#pragma unroll
+            for (int pl = 0; pl < NP; pl++)
+                acc[pl] = (pl == NP - 1) ? dp4a_ss(q, x.q[pl][j], acc[pl]) : dp4a_su(q, x.q[pl][j], acc[pl]);
         }
         const float d = h2f((uint16_t)(odd ? (w[0] >> 16) : w[0]));
-        // planes combined in F32: the plane-2 term alone can exceed int32 for 8-bit quants
-        const float f = fmaf((float)i2, 65536.0f, (float)((i1 << 8) + i0));
+        float f;
+        if (NP == 3)   // planes combined in F32: the plane-2 term alone can exceed int32 for 8-bit quants
+            f = fmaf((float)acc[NP - 1], 65536.0f, (float)((acc[1] << 8) + acc[0]));
+        else           // |acc1| <= 32*127*128 < 2^19: the 16-bit combination is exact in int32
+            f = (float)((acc[1] << 8) + acc[0]);
         return d * (f * x.s);
     }
 }
@@ -175,7 +187,7 @@ struct GemvParams {
     int red_off, x_off, stage_off;  // dynamic smem offsets (bytes)
     int wait_mode;        // GEMV_WAIT_*
     int npeers;
-    int pad0;
+    int rg_shift;         // rg == 1 << rg_shift (row groups are a power of two: no integer division per stage)
     int64_t row_offset;   // dst index of row 0 (sharded weights)
     unsigned long long *tl;         // timeline buffer (tools/gemv_timeline.cu builds only), else NULL
     // ---- 120 bytes
@@ -201,8 +213,9 @@ __device__ __forceinline__ unsigned long long lk_gtime() {
 // task = (block column, half): 16 consecutive floats; the two lanes of a pair share a block.
 // Conversion without F2I (quarter-rate pipe): fmaf(v, c, 1.5*2^23) leaves rint(v*c) in the low
 // mantissa bits; a non-finite element poisons the block scale with NaN instead.
-template <int TYPE>
+template <int TYPE, int NP>
 __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int tid, int nthreads) {
+    constexpr int TB = NP * 8 - 2;     // |T| <= 2^TB: 22 (three byte planes) or 14 (two)
     const int ntasks = p.nblk * 2;
 #pragma unroll 1
     for (int base = 0; base < ntasks; base += nthreads) {
@@ -231,9 +244,9 @@ __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int ti
         int e = (int)(ab >> 23);
         const bool nonfinite = e == 255;
         e = e < 24 ? 24 : e;
-        // c = 2^(22 - (e - 126)) so that |x| < 2^(e-126) maps into |T| <= 2^22;  s = 1/c
-        const float c = nonfinite ? 0.f : __uint_as_float((uint32_t)(275 - e) << 23);
-        const float s = nonfinite ? __uint_as_float(0x7FC00000u) : __uint_as_float((uint32_t)(e - 21) << 23);
+        // c = 2^(TB - (e - 126)) so that |x| < 2^(e-126) maps into |T| <= 2^TB;  s = 1/c
+        const float c = nonfinite ? 0.f : __uint_as_float((uint32_t)(253 + TB - e) << 23);
+        const float s = nonfinite ? __uint_as_float(0x7FC00000u) : __uint_as_float((uint32_t)(e + 1 - TB) << 23);
         int T[16];
         int sumT = 0;
 #pragma unroll
@@ -247,9 +260,9 @@ __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int ti
 #endif
         if (on) {
             const int blk = task >> 1, h = task & 1;
-            uint32_t *slot = xs + (size_t)blk * GEMV_XSLOT_WORDS;
+            uint32_t *slot = xs + (size_t)blk * gemv_xslot_words(NP);
 #pragma unroll
-            for (int pl = 0; pl < 3; pl++) {
+            for (int pl = 0; pl < NP; pl++) {
                 const uint32_t s2 = 0x0040u + 0x0011u * pl;   // byte pl of a, byte pl of b
                 uint32_t wds[4];
                 if (TYPE == T_Q8_0) {
@@ -265,7 +278,7 @@ __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int ti
                 }
                 *(uint4 *)(slot + pl * 8 + h * 4) = make_uint4(wds[0], wds[1], wds[2], wds[3]);
             }
-            if (h == 0) { slot[24] = __float_as_uint((float)sumT); slot[25] = __float_as_uint(s); }
+            if (h == 0) { slot[NP * 8] = __float_as_uint((float)sumT); slot[NP * 8 + 1] = __float_as_uint(s); }
         }
     }
 }
@@ -303,13 +316,13 @@ __device__ __forceinline__ void finish_rows(const GemvParams &p, const float *re
 // MINB = CTAs of consecutive launches that must fit on one SM together (registers are
 // capped accordingly): with programmatic dependent launch the next GEMV's CTA sits beside
 // this one and streams its weights while this one computes.
-template <int TYPE, int MAXW, int MINB>
+template <int TYPE, int MAXW, int MINB, int NP>
 __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t *full = (uint64_t *)smem;                   // [GEMV_MAX_STAGES]
     uint64_t *empty = full + GEMV_MAX_STAGES;            // [GEMV_MAX_STAGES]
     float *red = (float *)(smem + p.red_off);            // [red_rows][red_stride]
-    uint32_t *xs = (uint32_t *)(smem + p.x_off);         // [nblk][GEMV_XSLOT_WORDS]
+    uint32_t *xs = (uint32_t *)(smem + p.x_off);         // [nblk][gemv_xslot_words(NP)]
     uint8_t *stage0 = smem + p.stage_off;
 
     // The next kernel of the stream may be scheduled beside us as soon as every CTA has signalled.  An independent
@@ -393,22 +406,22 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
         pdl_launch_dependents();   // the next kernel can start its prologue / weight prefetch under our main loop
     }
     if (tid == 0) LK_TL(3);
-    prep_x<TYPE>(p, xs, tid, nct);
+    prep_x<TYPE, NP>(p, xs, tid, nct);
     if (tid == 0) LK_TL(24);
     asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");   // activation planes written
     if (tid == 0) LK_TL(4);
 
-    XRegs x;
+    XRegs<NP> x;
     {
-        const uint4 *slot = (const uint4 *)(xs + (size_t)colc * GEMV_XSLOT_WORDS);
+        const uint4 *slot = (const uint4 *)(xs + (size_t)colc * gemv_xslot_words(NP));
 #pragma unroll
-        for (int pl = 0; pl < 3; pl++)
+        for (int pl = 0; pl < NP; pl++)
 #pragma unroll
             for (int h = 0; h < 2; h++) {
                 const uint4 v = slot[pl * 2 + h];
                 x.q[pl][4 * h] = v.x; x.q[pl][4 * h + 1] = v.y; x.q[pl][4 * h + 2] = v.z; x.q[pl][4 * h + 3] = v.w;
             }
-        const uint4 t = slot[6];
+        const uint4 t = slot[NP * 2];
         x.s = __uint_as_float(t.y);
         x.c = ((TYPE == T_Q4_0) ? -8.0f : 1.0f) * x.s * __uint_as_float(t.x);
     }
@@ -433,7 +446,7 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
             red_base = row0;
         }
         const int rows_here = min(p.stage_rows, nrows - row0);
-        int nr = (rows_here - rgi + p.rg - 1) / p.rg;      // my rows in this stage (rg == 1 or a power-of-two-free small int)
+        int nr = (rows_here - rgi + p.rg - 1) >> p.rg_shift;   // my rows in this stage
         mbar_wait(&full[s], par);
         if (tid == 0 && it < 6) LK_TL(8 + 2 * it);
         const uint32_t *wp = sp;
@@ -443,7 +456,7 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
             // a short last step recomputes its last valid row in the unused slots (no store)
             float v[UNR];
 #pragma unroll
-            for (int u = 0; u < UNR; u++) v[u] = block_dot<TYPE>(wp + min(u, nr - 1) * rg_words, colc, x);
+            for (int u = 0; u < UNR; u++) v[u] = block_dot<TYPE, NP>(wp + min(u, nr - 1) * rg_words, colc, x);
 #pragma unroll
             for (int u = 0; u < UNR; u++) v[u] = active ? v[u] : 0.f;
 #pragma unroll
@@ -479,9 +492,9 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
 // ---------------------------------------------------------------------------
 // host side: shape analysis + launch
 // ---------------------------------------------------------------------------
-template <int TYPE, int MAXW, int MINB>
+template <int TYPE, int MAXW, int MINB, int NP>
 static cudaError_t launch_one(const GemvParams &p, int grid, int smem, int pdl, cudaStream_t s) {
-    auto kern = gemv_kernel<TYPE, MAXW, MINB>;
+    auto kern = gemv_kernel<TYPE, MAXW, MINB, NP>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
@@ -499,12 +512,12 @@ static cudaError_t launch_one(const GemvParams &p, int grid, int smem, int pdl, 
     return cudaLaunchKernelEx(&cfg, kern, p);
 }
 
-template <int TYPE>
+template <int TYPE, int NP>
 static cudaError_t launch_type(const GemvParams &p, int grid, int smem, int pdl, cudaStream_t s) {
-    if (p.cwarps <= 8) return launch_one<TYPE, 8, 2>(p, grid, smem, pdl, s);
-    if (p.cwarps <= 12) return launch_one<TYPE, 12, 2>(p, grid, smem, pdl, s);
-    if (p.cwarps <= 16) return launch_one<TYPE, 16, 2>(p, grid, smem, pdl, s);
-    return launch_one<TYPE, 28, 1>(p, grid, smem, pdl, s);   // K up to 28672 (Llama-2-70B down projection): one CTA per SM
+    if (p.cwarps <= 8) return launch_one<TYPE, 8, 2, NP>(p, grid, smem, pdl, s);
+    if (p.cwarps <= 12) return launch_one<TYPE, 12, 2, NP>(p, grid, smem, pdl, s);
+    if (p.cwarps <= 16) return launch_one<TYPE, 16, 2, NP>(p, grid, smem, pdl, s);
+    return launch_one<TYPE, 28, 1, NP>(p, grid, smem, pdl, s);   // K up to 28672 (Llama-2-70B down projection): one CTA per SM
 }
 
 cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const float *b, float *dst,
@@ -530,6 +543,9 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
     if (p.rg < 1) p.rg = 1;
     while (p.rg > 1 && p.rg * p.ncw > 16) p.rg--;
     if (p.ncw > 28) return cudaErrorNotSupported;
+    p.rg_shift = 0;
+    while ((2 << p.rg_shift) <= p.rg) p.rg_shift++;
+    p.rg = 1 << p.rg_shift;                        // round down to a power of two
     p.cwarps = p.rg * p.ncw;
     p.unit_rows = 1;
     while ((p.unit_rows * p.row_bytes) % 16) p.unit_rows *= 2;   // <= 8 because row_bytes is even
@@ -560,7 +576,8 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
     p.red_rows = red_rows;
     p.red_off = 256;
     p.x_off = (p.red_off + p.red_rows * p.red_stride * 4 + 15) & ~15;
-    p.stage_off = (p.x_off + p.nblk * GEMV_XSLOT_WORDS * 4 + 127) & ~127;
+    const int np = tune.act_planes == 2 ? 2 : 3;
+    p.stage_off = (p.x_off + p.nblk * gemv_xslot_words(np) * 4 + 127) & ~127;
     int nst = (budget - p.stage_off) / stage_bytes;
     const int max_st = tune.max_stages > 0 ? tune.max_stages : GEMV_MAX_STAGES;
     if (nst > max_st) nst = max_st;
@@ -572,10 +589,13 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
     p.nstages = nst;
     const int smem = p.stage_off + nst * stage_bytes;
 
-    switch (type) {
-        case T_Q4_0: return launch_type<T_Q4_0>(p, grid, smem, tune.pdl, s);
-        case T_Q4_1: return launch_type<T_Q4_1>(p, grid, smem, tune.pdl, s);
-        case T_Q8_0: return launch_type<T_Q8_0>(p, grid, smem, tune.pdl, s);
+    switch (type * 4 + np) {
+        case T_Q4_0 * 4 + 2: return launch_type<T_Q4_0, 2>(p, grid, smem, tune.pdl, s);
+        case T_Q4_1 * 4 + 2: return launch_type<T_Q4_1, 2>(p, grid, smem, tune.pdl, s);
+        case T_Q8_0 * 4 + 2: return launch_type<T_Q8_0, 2>(p, grid, smem, tune.pdl, s);
+        case T_Q4_0 * 4 + 3: return launch_type<T_Q4_0, 3>(p, grid, smem, tune.pdl, s);
+        case T_Q4_1 * 4 + 3: return launch_type<T_Q4_1, 3>(p, grid, smem, tune.pdl, s);
+        case T_Q8_0 * 4 + 3: return launch_type<T_Q8_0, 3>(p, grid, smem, tune.pdl, s);
         default: return cudaErrorNotSupported;
     }
 }

@@ -629,6 +629,7 @@ lk_status lk_set_option(lk_ctx *ctx, const char *name, int64_t v) {
     else if (n == "gemv_smem_budget") ctx->tune.smem_budget = (int)v;
     else if (n == "gemv_ctas_per_sm") ctx->tune.ctas_per_sm = (int)v;
     else if (n == "gemv_overlap") ctx->overlap_mode = (int)v;
+    else if (n == "gemv_act_planes") ctx->tune.act_planes = (v == 2) ? 2 : 3;
     else if (n == "gemm_tc_min_n") ctx->gemm_tc_min_n = (int)v;
     else if (n == "gemm_tc_cluster") ctx->gemm_tc_cluster = (int)v;
     else return fail(ctx, LK_EINVAL_ARG, "lk_set_option: unknown option " + n);
@@ -645,6 +646,7 @@ int64_t lk_get_option(lk_ctx *ctx, const char *name) {
     if (n == "gemv_smem_budget") return ctx->tune.smem_budget;
     if (n == "gemv_ctas_per_sm") return ctx->tune.ctas_per_sm;
     if (n == "gemv_overlap") return ctx->overlap_mode;
+    if (n == "gemv_act_planes") return ctx->tune.act_planes;
     if (n == "gemm_tc_min_n") return ctx->gemm_tc_min_n;
     if (n == "gemm_tc_cluster") return ctx->gemm_tc_cluster;
     if (n == "gemm_tc_launches") return ctx->gemm_tc_launches;

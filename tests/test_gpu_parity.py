@@ -531,3 +531,25 @@ def test_gemv_long_rows(O, ga, tname, M, K):
     x = synth_acts(1200 + M, K)
     got = host_matmul(ga, gt, blocks, K, M, x, 1)
     assert rel_err(got, O.matmul(ot, blocks, K, M, x, 1)) <= MATMUL_REL_TOL
+
+
+@pytest.mark.parametrize("tname", ["Q4_0", "Q4_1", "Q8_0"])
+@pytest.mark.parametrize("planes,bound", [(2, 1e-4), (3, 5e-6)])
+def test_gemv_activation_planes(O, ga, tname, planes, bound):
+    """The GEMV multiplies integer quants with block-fixed-point activations on DP4A: 24-bit (three byte planes,
+    the default: the error against f64 is the F32 reference's own) or, as an explicit option, 16-bit (two planes;
+    |x - x'| <= 2^-15 of the block maximum).  Both are far inside the 1e-3 tolerance; the bounds here are what
+    each mode actually delivers on the synthetic inputs."""
+    from llama_kotlin_b200.ggml_compute_ops import _ctx_of
+    gt, ot = QT[tname]
+    lkc = _ctx_of(ga)
+    old = lkc.get_option("gemv_act_planes")
+    try:
+        lkc.set_option("gemv_act_planes", planes)
+        for M, K in ((4096, 4096), (1000, 11008)):
+            blocks = O.quantize(ot, synth_weights(1300 + M, M, K))
+            x = synth_acts(1300 + M, K)
+            got = host_matmul(ga, gt, blocks, K, M, x, 1)
+            assert rel_err(got, O.matmul(ot, blocks, K, M, x, 1, nthreads=8)) <= bound
+    finally:
+        lkc.set_option("gemv_act_planes", old)

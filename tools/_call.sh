@@ -1,4 +1,3 @@
-timeout 100 python tools/ffn70b_bench.py 2> gpurun_out/ffn_g1.err | tee gpurun_out/ffn70b.jsonl
-for g in 2 4 8; do for ex in push nccl; do
-timeout 100 python -m torch.distributed.run --nnodes=1 --nproc-per-node $g --master-addr 127.0.0.1 --master-port 2953$g tools/ffn70b_bench.py --exchange $ex 2> gpurun_out/ffn_g${g}_$ex.err | tee -a gpurun_out/ffn70b.jsonl; echo "g$g $ex rc=$?"
-done; done
+timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo pytest=$?; tail -3 gpurun_out/pytest_gpu.log
+for o in "" "--opt gemv_act_planes=2"; do python bench.py --no-cpu-baseline --no-extras $o 2>/dev/null | python -c "
+import json,sys; d=json.loads(sys.stdin.read()); print(round(d['value'],1), round(d['roofline']['frac'],4), 'dep', round(d['config']['dependent_chain_GBps'],1), 'e2e', round(d['e2e']['value'],1), d['check'], d['config']['activation_bits'])"; done
