@@ -209,6 +209,12 @@ __device__ __forceinline__ unsigned long long lk_gtime() {
 #define LK_TL(slot) do { } while (0)
 #endif
 
+__device__ __forceinline__ float fmax3_nan_abs(float a, float b, float c) {   // max(|a|, |b|, |c|), NaN if any is NaN
+    float d;
+    asm("max.NaN.abs.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+    return d;
+}
+
 // ---- activations -> byte planes, cooperatively by the consumer threads -------------------
 // task = (block column, half): 16 consecutive floats; the two lanes of a pair share a block.
 // Conversion without F2I (quarter-rate pipe): fmaf(v, c, 1.5*2^23) leaves rint(v*c) in the low
@@ -236,22 +242,24 @@ __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int ti
 #ifdef LK_GEMV_TIMELINE
         if (tid == 0 && base == 0) { if (v[0] + v[4] + v[8] + v[12] == 12345.f) xs[0] = 1; LK_TL(22); }
 #endif
-        float amax = 0.f, chk = 0.f;
+        // max |v| with NaN propagation (3-input max.NaN.abs): a NaN or inf element leaves exponent 255 in `ab`
+        float amax = 0.f;
 #pragma unroll
-        for (int i = 0; i < 16; i++) { amax = fmaxf(amax, fabsf(v[i])); chk = fmaf(v[i], 0.f, chk); }   // chk: NaN iff any NaN/inf
-        uint32_t ab = (chk != chk) ? 0x7FC00000u : __float_as_uint(amax);
+        for (int i = 0; i < 16; i += 2) amax = fmax3_nan_abs(amax, v[i], v[i + 1]);
+        uint32_t ab = __float_as_uint(amax) & 0x7FFFFFFFu;
         ab = max(ab, __shfl_xor_sync(0xffffffffu, ab, 1));   // unsigned order: finite < inf < NaN
         int e = (int)(ab >> 23);
         const bool nonfinite = e == 255;
         e = e < 24 ? 24 : e;
-        // c = 2^(TB - (e - 126)) so that |x| < 2^(e-126) maps into |T| <= 2^TB;  s = 1/c
+        // c = 2^(TB - (e - 126)) so that |x| < 2^(e-126) maps into |T| <= 2^TB;  s = 1/c.  A non-finite block gets
+        // s = NaN, which poisons every product of the block whatever its T values are.
         const float c = nonfinite ? 0.f : __uint_as_float((uint32_t)(253 + TB - e) << 23);
         const float s = nonfinite ? __uint_as_float(0x7FC00000u) : __uint_as_float((uint32_t)(e + 1 - TB) << 23);
         int T[16];
         int sumT = 0;
 #pragma unroll
         for (int i = 0; i < 16; i++) {
-            T[i] = (int)__float_as_uint(fmaf(nonfinite ? 0.f : v[i], c, 12582912.0f)) - 0x4B400000;
+            T[i] = (int)__float_as_uint(fmaf(v[i], c, 12582912.0f)) - 0x4B400000;
             sumT += T[i];
         }
         sumT += __shfl_xor_sync(0xffffffffu, sumT, 1);   // both halves of the block
