@@ -149,6 +149,26 @@ LK_API lk_status   lk_host_free(lk_ctx *ctx, void *p);
  *   N >= 64, Q types           -> K2 tcgen05 prefill GEMM (FP16 operands, F32 accumulate)
  *   otherwise                  -> generic F32 kernel                          */
 LK_API lk_status   lk_compute_matmul(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, const lk_tensor *dst);
+
+/* computeMatMul with its neighbours in the layer graph folded into the launch (op order of
+ * LlamaDecoderLayer.forward, model/LlamaModel.kt:253-285).  Every tensor the unfused ops would have written is
+ * still written, so the graph's intermediates stay valid:
+ *   norm_x   != NULL: the activations are RMSNorm(norm_x, norm_w or NULL, eps); `b` (the RMS_NORM node's dst) also
+ *                     receives them.  1/rms multiply instead of the op's division: <= 2 ulp from lk_compute_rms_norm.
+ *   residual != NULL: sum_dst = residual + a x b (the following ADD node's dst); dst still receives a x b.
+ * N == 1, Q-type a, device-resident tensors only: anything else returns LK_ENOTIMPL and the caller issues the
+ * unfused ops.                                                                                             */
+typedef struct lk_matmul_fusion {
+    const lk_tensor *norm_x;
+    const lk_tensor *norm_w;
+    float            eps;
+    const lk_tensor *residual;
+    const lk_tensor *sum_dst;
+    int32_t          flags;      /* LK_FUSE_SKIP_B_STORE: another launch of the same RMS_NORM already stored `b` */
+} lk_matmul_fusion;
+#define LK_FUSE_SKIP_B_STORE 1
+LK_API lk_status   lk_compute_matmul_fused(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, const lk_tensor *dst,
+                                           const lk_matmul_fusion *fusion);
 /* dequantizeTensor(graphAllocator, tensor) — core/GGMLComputeOps.kt:918-964. Bit-exact. dst F32, same ne. */
 LK_API lk_status   lk_compute_dequantize(lk_ctx *ctx, const lk_tensor *src, const lk_tensor *dst);
 /* computeAdd / computeMul F32 same-shape paths — core/GGMLComputeOps.kt:735-759, :811-835 */

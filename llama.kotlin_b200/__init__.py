@@ -6,7 +6,7 @@ No CPU fallback exists anywhere in this package."""
 from ._binding import (IllegalArgumentException, IllegalStateException,  # noqa: F401
                        IndexOutOfBoundsException)
 from .ggml_alloc import GGMLGraphAllocator  # noqa: F401
-from .ggml_compute_ops import (LkContext, computeAdd, computeMatMul, computeMul,  # noqa: F401
+from .ggml_compute_ops import (LkContext, computeAdd, computeMatMul, computeMatMulFused, computeMul,  # noqa: F401
                                computeRmsNorm, computeSilu, computeSiluMul, computeSoftMax,
                                default_context, dequantizeTensor)
 from .ggml_cuda_backend import (GGMLCudaBackend, GGMLCudaBuffer, GGMLCudaBufferType)  # noqa: F401

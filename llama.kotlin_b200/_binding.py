@@ -39,6 +39,13 @@ class lk_tensor(C.Structure):
     ]
 
 
+class lk_matmul_fusion(C.Structure):
+    _fields_ = [
+        ("norm_x", C.POINTER(lk_tensor)), ("norm_w", C.POINTER(lk_tensor)), ("eps", C.c_float),
+        ("residual", C.POINTER(lk_tensor)), ("sum_dst", C.POINTER(lk_tensor)), ("flags", C.c_int32),
+    ]
+
+
 _lib = None
 
 
@@ -84,6 +91,7 @@ def lib() -> C.CDLL:
         "lk_host_alloc": (i32, [vp, u64, C.POINTER(vp)]),
         "lk_host_free": (i32, [vp, vp]),
         "lk_compute_matmul": (i32, [vp, tp, tp, tp]),
+        "lk_compute_matmul_fused": (i32, [vp, tp, tp, tp, C.POINTER(lk_matmul_fusion)]),
         "lk_compute_dequantize": (i32, [vp, tp, tp]),
         "lk_compute_add": (i32, [vp, tp, tp, tp]),
         "lk_compute_mul": (i32, [vp, tp, tp, tp]),

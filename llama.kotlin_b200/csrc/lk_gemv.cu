@@ -192,6 +192,13 @@ struct GemvParams {
     unsigned long long *tl;         // timeline buffer (tools/gemv_timeline.cu builds only), else NULL
     // ---- 120 bytes
     float *peer[8];       // optional peer-mapped copies of dst (fused all-gather)
+    // ---- fused neighbours of the matmul in the layer graph (all optional, see GemvFusion in lk_kernels.h)
+    const float *pro_w;   // RMSNorm gain (may be NULL with pro_mode 1)
+    float *b_out;         // where CTA 0 also stores the activations it actually multiplies with (the unfused op's dst)
+    const float *residual;   // dst[i] = residual[i] + (a x b)[i]
+    float *dst_raw;       // optional: the bare product, when the residual sum goes to dst
+    float pro_eps;
+    int pro_mode;         // 0: b as is; 1: b = RMSNorm(b, pro_w, pro_eps)
 };
 
 #ifdef LK_GEMV_TIMELINE
@@ -223,6 +230,30 @@ template <int TYPE, int NP>
 __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int tid, int nthreads) {
     constexpr int TB = NP * 8 - 2;     // |T| <= 2^TB: 22 (three byte planes) or 14 (two)
     const int ntasks = p.nblk * 2;
+    // Fused RMSNorm prologue (K3 folded in): every CTA needs all of x anyway, so it also takes the sum of squares
+    // (F32 partials per thread, warp shuffles, one pass over <= 28 warp totals) and multiplies with 1/rms and the
+    // gain while converting.  1/rms instead of the op's IEEE division: <= 2 ulp from the unfused RMSNorm.
+    float rinv = 1.0f;
+    if (p.pro_mode == 1) {
+        float *part = (float *)(xs + (size_t)p.nblk * gemv_xslot_words(NP)) - 32;   // tail of the last slots: rewritten below
+        float acc = 0.f;
+#pragma unroll 1
+        for (int task = tid; task < ntasks; task += nthreads) {
+            const float4 *src = (const float4 *)(p.b + (size_t)task * 16);
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const float4 f = __ldg(src + i);
+                acc = fmaf(f.x, f.x, acc); acc = fmaf(f.y, f.y, acc); acc = fmaf(f.z, f.z, acc); acc = fmaf(f.w, f.w, acc);
+            }
+        }
+        acc = warp_sum(acc);
+        if ((tid & 31) == 0) part[tid >> 5] = acc;
+        asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory");
+        float tot = 0.f;
+        for (int w = 0; w < (nthreads >> 5); w++) tot += part[w];
+        rinv = 1.0f / sqrtf(tot / (float)p.K + p.pro_eps);
+        asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory");     // `part` is about to be overwritten by the planes
+    }
 #pragma unroll 1
     for (int base = 0; base < ntasks; base += nthreads) {
         const int task = base + tid;
@@ -234,6 +265,24 @@ __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int ti
             for (int i = 0; i < 4; i++) {
                 const float4 f = __ldg(src + i);
                 v[4 * i] = f.x; v[4 * i + 1] = f.y; v[4 * i + 2] = f.z; v[4 * i + 3] = f.w;
+            }
+            if (p.pro_mode == 1) {
+#pragma unroll
+                for (int i = 0; i < 16; i++) v[i] = __fmul_rn(v[i], rinv);
+                if (p.pro_w) {
+                    const float4 *wsrc = (const float4 *)(p.pro_w + (size_t)task * 16);
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {
+                        const float4 f = __ldg(wsrc + i);
+                        v[4 * i] = __fmul_rn(v[4 * i], f.x); v[4 * i + 1] = __fmul_rn(v[4 * i + 1], f.y);
+                        v[4 * i + 2] = __fmul_rn(v[4 * i + 2], f.z); v[4 * i + 3] = __fmul_rn(v[4 * i + 3], f.w);
+                    }
+                }
+                if (p.b_out && blockIdx.x == 0) {
+                    float4 *o = (float4 *)(p.b_out + (size_t)task * 16);
+#pragma unroll
+                    for (int i = 0; i < 4; i++) o[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                }
             }
         } else {
 #pragma unroll
@@ -314,6 +363,10 @@ __device__ __forceinline__ void finish_rows(const GemvParams &p, const float *re
         v += __shfl_xor_sync(0xffffffffu, v, 4);
         if (sub == 0 && r < nred) {
             const int64_t o = out0 + r;
+            if (p.residual) {                      // fused residual ADD (computeAdd's single F32 add, same rounding)
+                if (p.dst_raw) p.dst_raw[o] = v;
+                v = __fadd_rn(p.residual[o], v);
+            }
             p.dst[o] = v;
 #pragma unroll 1
             for (int q = 0; q < p.npeers; q++) p.peer[q][o] = v;
@@ -530,7 +583,7 @@ static cudaError_t launch_type(const GemvParams &p, int grid, int smem, int pdl,
 
 cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const float *b, float *dst,
                         int64_t row_offset, const GemvPeers &peers, const GemvTuning &tune, int sm_count,
-                        cudaStream_t s) {
+                        cudaStream_t s, const GemvFusion *fusion) {
     const int bb = block_bytes(type);
     if (bb == 0 || K <= 0 || M <= 0 || (K % 64) != 0 || K > 32 * 32 * 28 || M > (1 << 30))
         return cudaErrorNotSupported;
@@ -541,6 +594,11 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
     p.npeers = peers.n;
     for (int i = 0; i < peers.n && i < 8; i++) p.peer[i] = peers.ptr[i];
     p.K = (int)K; p.M = (int)M; p.row_offset = row_offset;
+    if (fusion) {
+        if (((uintptr_t)fusion->pro_w & 15) || ((uintptr_t)fusion->b_out & 15)) return cudaErrorNotSupported;
+        p.pro_mode = fusion->pro_mode; p.pro_w = fusion->pro_w; p.pro_eps = fusion->pro_eps; p.b_out = fusion->b_out;
+        p.residual = fusion->residual; p.dst_raw = fusion->dst_raw;
+    }
     p.tl = (unsigned long long *)tune.timeline;
     p.wait_mode = tune.wait_mode;
     p.row_bytes = (int)(K / 32) * bb;

@@ -32,9 +32,18 @@ struct GemvPeers {
     float *ptr[8];
     int n = 0;
 };
+// Neighbours of the matmul in the layer graph folded into the launch; all optional.
+struct GemvFusion {
+    int pro_mode = 0;               // 1: the activations are RMSNorm(b, pro_w, pro_eps), computed by every CTA from b
+    const float *pro_w = nullptr;
+    float pro_eps = 0.f;
+    float *b_out = nullptr;         // also store the activations actually used (the unfused RMSNorm's dst)
+    const float *residual = nullptr;   // dst = residual + a x b  (the following ADD)
+    float *dst_raw = nullptr;       // also store the bare product (the unfused matmul's dst)
+};
 cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const float *b, float *dst,
                         int64_t row_offset, const GemvPeers &peers, const GemvTuning &tune, int sm_count,
-                        cudaStream_t s);
+                        cudaStream_t s, const GemvFusion *fusion = nullptr);
 
 // Generic matmul for any (K, M, N) and a.type in {F32, Q4_0, Q4_1, Q8_0}; reference layouts.
 cudaError_t launch_matmul_generic(int type, const void *a, int64_t K, int64_t M, const float *b, int64_t N,

@@ -47,12 +47,18 @@ void chain_close(lk_ctx *ctx) { ctx->chain_reads.clear(); ctx->chain_writes.clea
 
 }  // namespace
 int gemv_wait_mode(lk_ctx *ctx, const void *a, size_t abytes, const void *b, size_t bbytes, const void *d, size_t dbytes,
-                   bool pdl) {
-    const Range ra((uintptr_t)a, (uintptr_t)a + abytes), rb((uintptr_t)b, (uintptr_t)b + bbytes),
-        rd((uintptr_t)d, (uintptr_t)d + dbytes);
+                   bool pdl, const std::vector<std::pair<const void *, size_t>> *more_reads,
+                   const std::vector<std::pair<const void *, size_t>> *more_writes) {
+    const Range ra((uintptr_t)a, (uintptr_t)a + abytes);
+    std::vector<Range> rd, wr;      // what the launch reads after its wait point / writes
+    rd.push_back(Range((uintptr_t)b, (uintptr_t)b + bbytes));
+    wr.push_back(Range((uintptr_t)d, (uintptr_t)d + dbytes));
+    if (more_reads) for (const auto &r : *more_reads) if (r.first && r.second) rd.push_back(Range((uintptr_t)r.first, (uintptr_t)r.first + r.second));
+    if (more_writes) for (const auto &r : *more_writes) if (r.first && r.second) wr.push_back(Range((uintptr_t)r.first, (uintptr_t)r.first + r.second));
     int mode = 2;   // GEMV_WAIT_END
     if (!pdl || !ctx->overlap_mode) mode = 1;
-    if (overlaps(ctx->chain_writes, rb) || overlaps(ctx->chain_writes, rd) || overlaps(ctx->chain_reads, rd)) mode = 1;
+    for (const Range &r : rd) if (overlaps(ctx->chain_writes, r)) mode = 1;
+    for (const Range &r : wr) if (overlaps(ctx->chain_writes, r) || overlaps(ctx->chain_reads, r)) mode = 1;
     if (overlaps(ctx->chain_writes, ra)) mode = 0;
     if (!ctx->other_writes.empty()) {   // first GEMV after a normal op: it can start before that op has finished
         mode = overlaps(ctx->other_writes, ra) ? 0 : (mode == 0 ? 0 : 1);
@@ -61,8 +67,8 @@ int gemv_wait_mode(lk_ctx *ctx, const void *a, size_t abytes, const void *b, siz
     if (mode != 2) chain_close(ctx);   // everything earlier has completed once this launch passes its wait
     if (ctx->chain_reads.size() > 256) { chain_close(ctx); mode = 1; }
     ctx->chain_reads.push_back(ra);
-    ctx->chain_reads.push_back(rb);
-    ctx->chain_writes.push_back(rd);
+    for (const Range &r : rd) ctx->chain_reads.push_back(r);
+    for (const Range &r : wr) ctx->chain_writes.push_back(r);
     return mode;
 }
 
@@ -447,6 +453,61 @@ lk_status lk_compute_matmul(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b,
     if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "matmul launch");
     count_launch(ctx, launched);
     return finish(sc);
+}
+
+lk_status lk_compute_matmul_fused(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, const lk_tensor *dst,
+                                  const lk_matmul_fusion *f) {
+    if (!ctx || !a || !b || !dst || !f) return fail(ctx, LK_EINVAL_ARG, "lk_compute_matmul_fused: NULL argument");
+    const int64_t M = a->ne[1], K = a->ne[0], N = b->ne[0];
+    if (K != b->ne[1]) return fail(ctx, LK_EINVAL_DIM, "Dim mismatch K: a.ne[0] != b.ne[1]");
+    if (dst->ne[0] != N || dst->ne[1] != M)
+        return fail(ctx, LK_EINVAL_DIM, "Result tensor dimensions must match expected output size [N, M]");
+    if (!is_block_type(a->type) || b->type != LK_TYPE_F32 || dst->type != LK_TYPE_F32)
+        return fail(ctx, LK_ENOTIMPL, "fused matmul: Q4_0/Q4_1/Q8_0 x F32 -> F32 only");
+    if (N != 1 || M <= 0 || K <= 0) return fail(ctx, LK_ENOTIMPL, "fused matmul: N == 1 only");
+    const lk_tensor *all[] = {a, b, dst, f->norm_x, f->norm_w, f->residual, f->sum_dst};
+    for (const lk_tensor *t : all) {
+        if (!t) continue;
+        if (!t->dev_buf) return fail(ctx, LK_ENOTIMPL, "fused matmul: device-resident tensors only");
+        const int64_t nb = lk_tensor_nbytes(t);
+        if (nb < 0 || t->data_offset > t->dev_buf->size || (uint64_t)nb > t->dev_buf->size - t->data_offset)
+            return fail(ctx, LK_EBOUNDS, "fused matmul: tensor bytes exceed the device buffer");
+        if (t != a && t->type != LK_TYPE_F32) return fail(ctx, LK_EINVAL_TYPE, "fused matmul: F32 vectors expected");
+    }
+    if ((f->residual != nullptr) != (f->sum_dst != nullptr)) return fail(ctx, LK_EINVAL_ARG, "fused matmul: residual and sum_dst go together");
+    if (f->norm_x && num_elements(f->norm_x) != K) return fail(ctx, LK_EINVAL_DIM, "fused matmul: norm_x must hold K elements");
+    if (f->norm_w && num_elements(f->norm_w) != K) return fail(ctx, LK_EINVAL_DIM, "fused matmul: norm_w must hold K elements");
+    if (f->residual && (num_elements(f->residual) != M || num_elements(f->sum_dst) != M))
+        return fail(ctx, LK_EINVAL_DIM, "fused matmul: residual and sum_dst must hold M elements");
+    LK_CUDA(ctx, cudaSetDevice(ctx->device));
+    auto ptr = [](const lk_tensor *t) { return t ? (void *)((uint8_t *)t->dev_buf->ptr + t->data_offset) : nullptr; };
+    lk::GemvFusion fu;
+    const float *x = (const float *)ptr(b);
+    if (f->norm_x) {
+        fu.pro_mode = 1; fu.pro_w = (const float *)ptr(f->norm_w); fu.pro_eps = f->eps;
+        fu.b_out = (f->flags & LK_FUSE_SKIP_B_STORE) ? nullptr : (float *)ptr(b);
+        x = (const float *)ptr(f->norm_x);
+    }
+    float *out = (float *)ptr(dst);
+    if (f->residual) { fu.residual = (const float *)ptr(f->residual); fu.dst_raw = out; out = (float *)ptr(f->sum_dst); }
+    lk::GemvTuning tune = ctx->tune;
+    tune.pdl = (ctx->pdl_mode == 2) || (ctx->pdl_mode == 1 && ctx->capturing);
+    std::vector<std::pair<const void *, size_t>> rd, wr;
+    rd.push_back({fu.pro_w, (size_t)K * 4});
+    rd.push_back({fu.residual, (size_t)M * 4});
+    wr.push_back({fu.b_out, (size_t)K * 4});
+    wr.push_back({fu.dst_raw, (size_t)M * 4});
+    tune.wait_mode = lk::gemv_wait_mode(ctx, ptr(a), (size_t)lk_tensor_nbytes(a), x, (size_t)K * 4, out, (size_t)M * 4, tune.pdl != 0, &rd, &wr);
+    lk::GemvPeers none;
+    cudaError_t e = lk::launch_gemv(a->type, ptr(a), K, M, x, out, 0, none, tune, ctx->sm_count, ctx->stream, &fu);
+    if (e == cudaErrorNotSupported) {
+        cudaGetLastError();
+        chain_other(ctx, nullptr, 0);      // nothing was launched; the unfused ops that follow do their own bookkeeping
+        return fail(ctx, LK_ENOTIMPL, "fused matmul: shape not supported by the streaming GEMV");
+    }
+    if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "fused matmul launch");
+    count_launch(ctx);
+    return LK_OK;
 }
 
 lk_status lk_compute_dequantize(lk_ctx *ctx, const lk_tensor *src, const lk_tensor *dst) {

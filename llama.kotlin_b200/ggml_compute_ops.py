@@ -95,6 +95,28 @@ def computeMatMul(graphAllocator, context: GGMLContext, a: GGMLTensor, b: GGMLTe
                                       describe(graphAllocator, dst)), lk.handle)
 
 
+def computeMatMulFused(graphAllocator, context, a, b, dst, norm_x=None, norm_w=None, eps: float = 0.0,
+                       residual=None, sum_dst=None, store_b: bool = True) -> bool:
+    """computeMatMul with the RMS_NORM that produces `b` and / or the ADD that consumes `dst` folded into the GEMV
+    launch (lk_compute_matmul_fused).  Returns False when the library declines the shape (LK_ENOTIMPL): the
+    caller then issues the unfused ops."""
+    keep = [describe(graphAllocator, t) if t is not None else None for t in (norm_x, norm_w, residual, sum_dst)]
+    f = B.lk_matmul_fusion()
+    f.norm_x = C.pointer(keep[0]) if keep[0] is not None else None
+    f.norm_w = C.pointer(keep[1]) if keep[1] is not None else None
+    f.eps = float(eps)
+    f.residual = C.pointer(keep[2]) if keep[2] is not None else None
+    f.sum_dst = C.pointer(keep[3]) if keep[3] is not None else None
+    f.flags = 0 if store_b else 1        # LK_FUSE_SKIP_B_STORE
+    ctx = _ctx_of(graphAllocator)
+    st = B.lib().lk_compute_matmul_fused(ctx.handle, describe(graphAllocator, a), describe(graphAllocator, b),
+                                         describe(graphAllocator, dst), C.byref(f))
+    if st == B.LK_ENOTIMPL:
+        return False
+    B.check(st, ctx.handle)
+    return True
+
+
 def computeAdd(graphAllocator, context, a, b, dst) -> None:
     lk = _ctx_of(graphAllocator)
     B.check(B.lib().lk_compute_add(lk.handle, describe(graphAllocator, a), describe(graphAllocator, b),

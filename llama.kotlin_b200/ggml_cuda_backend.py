@@ -13,7 +13,7 @@ import numpy as np
 
 from . import _binding as B
 from . import ggml_compute_ops as ops
-from .ggml_types import GGMLCGraph, GGMLOp, GGMLStatus, GGMLTensor
+from .ggml_types import GGMLCGraph, GGMLOp, GGMLStatus, GGMLTensor, GGMLType
 
 
 class GGMLCudaBufferType:
@@ -100,6 +100,7 @@ class GGMLCudaBackend:
 
     def __init__(self, device: int = 0):
         self.lk = ops.LkContext(device)
+        self.fuseOps = True          # fold RMS_NORM / ADD neighbours into the decode GEMV inside captured sequences
         self._bt = GGMLCudaBufferType(self)
         self._captured = {}      # id(graph) -> (lk_graph handle, node signature)
         self.useCudaGraphs = True
@@ -176,6 +177,109 @@ class GGMLCudaBackend:
         else:                          # core/GGMLComputeOps.kt:2548
             raise NotImplementedError(f"Operation {op} not implemented")
 
+    # -- fusion of a matmul with its graph neighbours -----------------------------------
+    @staticmethod
+    def _key(t: GGMLTensor):
+        return (id(t.buffer), int(t.dataOffset), int(t.numElements()))
+
+    @staticmethod
+    def _span(t: GGMLTensor):
+        return (id(t.buffer), int(t.dataOffset), int(t.dataOffset) + int(t.byteSize()))
+
+    def _plan(self, graph: GGMLCGraph):
+        """Which RMS_NORM nodes fold into the matmuls that consume them and which ADD nodes fold into the matmul
+        that feeds them.  Returns (rms_of, add_of, skip): matmul index -> RMS_NORM index / ADD index, and the set
+        of node indices that are not launched on their own.  Every fused-away node's dst is still written by the
+        fused launch, so the graph's intermediates stay valid whatever reads them later."""
+        nodes = graph.nodes
+        n = len(nodes)
+
+        def is_gemv(t):
+            return (t.op == GGMLOp.MUL_MAT and not isinstance(t.extra, dict) and t.src[0] is not None and
+                    t.src[0].type.isBlockType and t.src[1] is not None and int(t.src[1].ne[0]) == 1 and
+                    t.type == GGMLType.F32)
+
+        def overlaps(a, b):
+            return a[0] == b[0] and a[1] < b[2] and b[1] < a[2]
+
+        consumers = {}
+        for j, t in enumerate(nodes):
+            for sidx, sr in enumerate(t.src):
+                if sr is not None:
+                    consumers.setdefault(self._key(sr), []).append((j, sidx))
+        rms_of, add_of, skip = {}, {}, set()
+        for i, t in enumerate(nodes):
+            if t.op == GGMLOp.RMS_NORM and t.type == GGMLType.F32 and int(t.numElements()) == int(t.ne[0]):
+                cons = [c for c in consumers.get(self._key(t), []) if c[0] > i]
+                # a later writer of the same storage before the last consumer would change what they read
+                if cons and all(is_gemv(nodes[j]) and sidx == 1 for j, sidx in cons):
+                    last = max(j for j, _ in cons)
+                    clean = all(not overlaps(self._span(nodes[k]), self._span(t)) and
+                                not overlaps(self._span(nodes[k]), self._span(t.src[0])) and
+                                (t.src[1] is None or not overlaps(self._span(nodes[k]), self._span(t.src[1])))
+                                for k in range(i + 1, last + 1) if nodes[k].op != GGMLOp.NONE)
+                    if clean:
+                        for j, _ in cons:
+                            rms_of[j] = i
+                        skip.add(i)
+        for i, t in enumerate(nodes):
+            if not is_gemv(t):
+                continue
+            cons = [c for c in consumers.get(self._key(t), []) if c[0] > i]
+            if len(cons) != 1:
+                continue
+            j, sidx = cons[0]
+            a = nodes[j]
+            if a.op != GGMLOp.ADD or a.type != GGMLType.F32 or j in skip:
+                continue
+            res = a.src[1 - sidx]
+            if res is None or int(res.numElements()) != int(t.numElements()):
+                continue
+            # the ADD moves up to the matmul's position: nothing in between may write its operand or touch its dst
+            if any(overlaps(self._span(nodes[k]), self._span(res)) or overlaps(self._span(nodes[k]), self._span(a))
+                   for k in range(i, j) if nodes[k].op != GGMLOp.NONE):
+                continue
+            if any(s2 is not None and overlaps(self._span(s2), self._span(a)) for k in range(i, j) for s2 in nodes[k].src):
+                continue
+            add_of[i] = j
+            skip.add(j)
+        return rms_of, add_of, skip
+
+    def _runNodes(self, ga, graph: GGMLCGraph, fuse: bool) -> None:
+        nodes = graph.nodes
+        if not fuse:
+            for node in nodes:
+                self._computeNode(ga, node)
+            return
+        rms_of, add_of, skip = self._plan(graph)
+        stored = set()                       # RMS_NORM nodes whose dst has been written
+        for i, node in enumerate(nodes):
+            if i in skip:
+                continue
+            if i not in rms_of and i not in add_of:
+                self._computeNode(ga, node)
+                continue
+            r = nodes[rms_of[i]] if i in rms_of else None
+            a = nodes[add_of[i]] if i in add_of else None
+            kw = {}
+            if r is not None:
+                eps = struct.unpack("<f", struct.pack("<i", int(r.opParams[0])))[0]
+                kw.update(norm_x=r.src[0], norm_w=r.src[1], eps=eps, store_b=rms_of[i] not in stored)
+            if a is not None:
+                res = a.src[1] if self._key(a.src[0]) == self._key(node) else a.src[0]
+                kw.update(residual=res, sum_dst=a)
+            if ops.computeMatMulFused(ga, None, node.src[0], node.src[1], node, **kw):
+                if r is not None:
+                    stored.add(rms_of[i])
+                continue
+            # the library declined this shape: the unfused ops, in graph order
+            if r is not None and rms_of[i] not in stored:
+                self._computeNode(ga, r)
+                stored.add(rms_of[i])
+            self._computeNode(ga, node)
+            if a is not None:
+                self._computeNode(ga, a)
+
     @staticmethod
     def _signature(graph: GGMLCGraph):
         sig = []
@@ -205,8 +309,7 @@ class GGMLCudaBackend:
                         B.lib().lk_graph_destroy(ent[0])
                     B.check(B.lib().lk_capture_begin(self.lk.handle), self.lk.handle)
                     try:
-                        for node in graph.nodes:
-                            self._computeNode(ga, node)
+                        self._runNodes(ga, graph, fuse=self.fuseOps)
                     finally:
                         h = C.c_void_p()
                         st = B.lib().lk_capture_end(self.lk.handle, C.byref(h))
@@ -215,8 +318,7 @@ class GGMLCudaBackend:
                     self._captured[id(graph)] = ent
                 B.check(B.lib().lk_graph_launch(self.lk.handle, ent[0]), self.lk.handle)
             else:
-                for node in graph.nodes:
-                    self._computeNode(ga, node)
+                self._runNodes(ga, graph, fuse=False)
             return GGMLStatus.SUCCESS
         except (B.IllegalArgumentException, B.IndexOutOfBoundsException, B.IllegalStateException,
                 NotImplementedError) as e:

@@ -553,3 +553,97 @@ def test_gemv_activation_planes(O, ga, tname, planes, bound):
             assert rel_err(got, O.matmul(ot, blocks, K, M, x, 1, nthreads=8)) <= bound
     finally:
         lkc.set_option("gemv_act_planes", old)
+
+
+# ---- fused matmul (N3): RMS_NORM prologue, residual ADD epilogue --------------------------------------------
+@pytest.mark.parametrize("tname", ["Q4_0", "Q8_0", "Q4_1"])
+@pytest.mark.parametrize("M,K", [(4096, 4096), (11008, 4096), (300, 11008), (64, 128)])
+def test_matmul_fused_rms_prologue_and_residual(O, tname, M, K):
+    """lk_compute_matmul_fused against the unfused ops: the activations it stores are RMSNorm(x)*w to <= 4 ulp
+    (1/rms multiply instead of the division), the bare product matches the oracle matmul of the ORACLE's
+    normalised vector within the matmul tolerance, and sum_dst is exactly residual + the product it stored."""
+    gt, ot = QT[tname]
+    be = lk.GGMLCudaBackend(0)
+    bb = {"Q4_0": 18, "Q8_0": 34, "Q4_1": 20}[tname]
+    ga = lk.GGMLGraphAllocator(be, size=M * K // 32 * bb + (4 * K + 4 * M) * 4 + (1 << 16))
+    blocks = O.quantize(ot, synth_weights(1400 + M, M, K))
+    x0 = synth_acts(1400 + M, K) * 3
+    w0 = (1.0 + 0.1 * synth_acts(1401 + M, K)).astype(np.float32)
+    r0 = synth_acts(1402 + M, M)
+
+    def dev(t, shape, data=None):
+        tt = ga.allocateTensor(GGMLTensor(t, shape))
+        if data is not None:
+            ga.setBytes(tt, data)
+        return tt
+    a = dev(gt, [K, M], blocks)
+    x, w, res = dev(GGMLType.F32, [K], x0), dev(GGMLType.F32, [K], w0), dev(GGMLType.F32, [M], r0)
+    b = dev(GGMLType.F32, [1, K], np.zeros(K, np.float32))
+    d = dev(GGMLType.F32, [1, M], np.zeros(M, np.float32))
+    sm = dev(GGMLType.F32, [M], np.zeros(M, np.float32))
+    assert lk.computeMatMulFused(ga, None, a, b, d, norm_x=x, norm_w=w, eps=1e-6, residual=res, sum_dst=sm)
+    be.lk.sync()
+    h_ref = O.rms_norm(x0, w0, 1e-6, K)
+    h = ga.getFloats(b)
+    assert np.allclose(h, h_ref, rtol=5e-7, atol=0)
+    prod, tot = ga.getFloats(d), ga.getFloats(sm)
+    assert rel_err(prod, O.matmul(ot, blocks, K, M, h_ref, 1, nthreads=8)) <= MATMUL_REL_TOL
+    assert same_f32_bits(tot, O.add(r0, prod))
+    # the same product as the unfused GEMV fed with the stored activations, bit for bit
+    d2 = dev(GGMLType.F32, [1, M], np.zeros(M, np.float32))
+    lk.computeMatMul(ga, None, a, b, d2)
+    be.lk.sync()
+    assert same_f32_bits(ga.getFloats(d2), prod)
+    # second consumer of the same RMS_NORM: no store of b, same product
+    ga.setBytes(b, np.full(K, 7.0, np.float32))
+    d3 = dev(GGMLType.F32, [1, M], np.zeros(M, np.float32))
+    assert lk.computeMatMulFused(ga, None, a, b, d3, norm_x=x, norm_w=w, eps=1e-6, store_b=False)
+    be.lk.sync()
+    assert same_f32_bits(ga.getFloats(d3), prod) and np.all(ga.getFloats(b) == 7.0)
+    be.free()
+
+
+def test_matmul_fused_declines_unsupported_shapes(O):
+    be = lk.GGMLCudaBackend(0)
+    ga = lk.GGMLGraphAllocator(be, size=1 << 20)
+    K, M = 96, 8                                   # K % 64 != 0: no streaming GEMV
+    a = ga.allocateTensor(GGMLTensor(GGMLType.Q4_0, [K, M]))
+    x = ga.allocateTensor(GGMLTensor(GGMLType.F32, [K]))
+    b = ga.allocateTensor(GGMLTensor(GGMLType.F32, [1, K]))
+    d = ga.allocateTensor(GGMLTensor(GGMLType.F32, [1, M]))
+    ga.setBytes(a, O.quantize(Q4_0, synth_weights(5, M, K)))
+    ga.setBytes(x, synth_acts(5, K))
+    assert lk.computeMatMulFused(ga, None, a, b, d, norm_x=x, eps=1e-6) is False
+    be.free()
+
+
+def test_decoder_layer_graph_fused_equals_unfused(O):
+    """The captured layer with the fusion pass on and off: every intermediate the graph names is still written,
+    and the outputs agree to the RMSNorm 1/rms difference (far below the matmul tolerance)."""
+    from llama_kotlin_b200.llama_layer import alloc_layer, build_decoder_graph, weight_shapes
+    hidden, ffn = 512, 1408
+    outs = []
+    for fuse in (True, False):
+        be = lk.GGMLCudaBackend(0)
+        be.fuseOps = fuse
+        shapes = weight_shapes(hidden, ffn)
+        ga = lk.GGMLGraphAllocator(be, size=2 * (sum(M * K // 32 * 18 for M, K in shapes.values()) + 64 * ffn * 4) + (1 << 20))
+        rng = np.random.default_rng(77)
+        x = ga.allocateTensor(GGMLTensor(GGMLType.F32, [hidden]))
+        ga.setBytes(x, rng.normal(0, 1, hidden).astype(np.float32))
+        stack = []
+        for li in range(2):
+            L = alloc_layer(ga, GGMLType.Q4_0, hidden, ffn)
+            for i, (n, (M, K)) in enumerate(shapes.items()):
+                ga.setBytes(L.weights[n], O.quantize(Q4_0, synth_weights(600 + 10 * li + i, M, K)))
+            ga.setBytes(L.attn_norm, (1 + 0.1 * rng.normal(0, 1, hidden)).astype(np.float32))
+            ga.setBytes(L.ffn_norm, (1 + 0.1 * rng.normal(0, 1, hidden)).astype(np.float32))
+            stack.append(L)
+        graph, out = build_decoder_graph(ga, stack, x, hidden, ffn)
+        before = be.lk.launch_count()
+        assert be.graphCompute(graph) == lk.GGMLStatus.SUCCESS
+        assert be.graphCompute(graph) == lk.GGMLStatus.SUCCESS
+        outs.append([ga.getFloats(n) for n in graph.nodes])
+        be.free()
+    for f, u in zip(*outs):
+        assert rel_err(f, u) <= 2e-6

@@ -82,7 +82,10 @@ def main():
     be = lk.GGMLCudaBackend(0)
     for kv in args.opt or []:
         k, v = kv.split("=")
-        be.lk.set_option(k, int(v))
+        if k == "nofuse":
+            be.fuseOps = not int(v)
+        else:
+            be.lk.set_option(k, int(v))
     peak = 0.0
     try:
         peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", 0))
