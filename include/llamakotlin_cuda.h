@@ -165,6 +165,16 @@ typedef struct lk_matmul_fusion {
     const lk_tensor *residual;
     const lk_tensor *sum_dst;
     int32_t          flags;      /* LK_FUSE_SKIP_B_STORE: another launch of the same RMS_NORM already stored `b` */
+    /* Stacked matmuls: n_extra (0..2) more weights of a's type and shape multiplied with the same activations by the
+     * same launch (Q/K/V, gate/up): dst_extra[i] = a_extra[i] x b.  Not combinable with residual.
+     * With n_extra == 1 and mul_dst != NULL the SwiGLU pair of LlamaMLP.forward (model/LlamaModel.kt:159-176) is
+     * finished in the epilogue: silu_dst (optional) = silu(dst), mul_dst = silu(dst) * dst_extra[0], with the
+     * elementwise kernels' roundings (lk_compute_silu, lk_compute_mul).                                          */
+    int32_t          n_extra;
+    const lk_tensor *a_extra[2];
+    const lk_tensor *dst_extra[2];
+    const lk_tensor *silu_dst;
+    const lk_tensor *mul_dst;
 } lk_matmul_fusion;
 #define LK_FUSE_SKIP_B_STORE 1
 LK_API lk_status   lk_compute_matmul_fused(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, const lk_tensor *dst,

@@ -43,6 +43,8 @@ class lk_matmul_fusion(C.Structure):
     _fields_ = [
         ("norm_x", C.POINTER(lk_tensor)), ("norm_w", C.POINTER(lk_tensor)), ("eps", C.c_float),
         ("residual", C.POINTER(lk_tensor)), ("sum_dst", C.POINTER(lk_tensor)), ("flags", C.c_int32),
+        ("n_extra", C.c_int32), ("a_extra", C.POINTER(lk_tensor) * 2), ("dst_extra", C.POINTER(lk_tensor) * 2),
+        ("silu_dst", C.POINTER(lk_tensor)), ("mul_dst", C.POINTER(lk_tensor)),
     ]
 
 

@@ -198,7 +198,15 @@ struct GemvParams {
     const float *residual;   // dst[i] = residual[i] + (a x b)[i]
     float *dst_raw;       // optional: the bare product, when the residual sum goes to dst
     float pro_eps;
+    int pair_off;         // epi_mode 1: first partial-sum row of segment 1
     int pro_mode;         // 0: b as is; 1: b = RMSNorm(b, pro_w, pro_eps)
+    // ---- stacked segments: up to 3 weights of identical shape multiplied with the same activations in one launch
+    // (Q/K/V, gate/up); every CTA runs its row range through each segment in turn (segment 0 is a / dst above)
+    int nseg;
+    int epi_mode;         // 1 (nseg == 2): epi_out[i] = silu(seg0[i]) * seg1[i], epi_act[i] = silu(seg0[i])
+    const uint8_t *a_seg[2];
+    float *dst_seg[2];
+    float *epi_act, *epi_out;
 };
 
 #ifdef LK_GEMV_TIMELINE
@@ -226,7 +234,7 @@ __device__ __forceinline__ float fmax3_nan_abs(float a, float b, float c) {   //
 // task = (block column, half): 16 consecutive floats; the two lanes of a pair share a block.
 // Conversion without F2I (quarter-rate pipe): fmaf(v, c, 1.5*2^23) leaves rint(v*c) in the low
 // mantissa bits; a non-finite element poisons the block scale with NaN instead.
-template <int TYPE, int NP>
+template <int TYPE, int NP, bool FUSED>
 __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int tid, int nthreads) {
     constexpr int TB = NP * 8 - 2;     // |T| <= 2^TB: 22 (three byte planes) or 14 (two)
     const int ntasks = p.nblk * 2;
@@ -234,7 +242,7 @@ __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int ti
     // (F32 partials per thread, warp shuffles, one pass over <= 28 warp totals) and multiplies with 1/rms and the
     // gain while converting.  1/rms instead of the op's IEEE division: <= 2 ulp from the unfused RMSNorm.
     float rinv = 1.0f;
-    if (p.pro_mode == 1) {
+    if (FUSED && p.pro_mode == 1) {
         float *part = (float *)(xs + (size_t)p.nblk * gemv_xslot_words(NP)) - 32;   // tail of the last slots: rewritten below
         float acc = 0.f;
 #pragma unroll 1
@@ -266,7 +274,7 @@ __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int ti
                 const float4 f = __ldg(src + i);
                 v[4 * i] = f.x; v[4 * i + 1] = f.y; v[4 * i + 2] = f.z; v[4 * i + 3] = f.w;
             }
-            if (p.pro_mode == 1) {
+            if (FUSED && p.pro_mode == 1) {
 #pragma unroll
                 for (int i = 0; i < 16; i++) v[i] = __fmul_rn(v[i], rinv);
                 if (p.pro_w) {
@@ -343,7 +351,10 @@ __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int ti
 enum { GEMV_WAIT_FULL = 0, GEMV_WAIT_X = 1, GEMV_WAIT_END = 2 };
 
 // cross-lane part of the final reduction: 8 lanes per row, 4 rows per warp per pass
-__device__ __forceinline__ void finish_rows(const GemvParams &p, const float *red, int nred, int64_t out0, int warp, int lane) {
+__device__ __forceinline__ float silu_f(float x) { return __fmul_rn(x, __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-x)))); }   // = lk_elementwise.cu silu1
+
+template <bool FUSED>
+__device__ __forceinline__ void finish_rows(const GemvParams &p, float *dst, const float *red, int nred, int64_t out0, int warp, int lane) {
     const int sub = lane & 7, rsel = lane >> 3;
     const int nc4 = p.red_stride >> 2;   // float4 chunks per row (columns beyond npairs hold zeros)
 #pragma unroll 1
@@ -363,13 +374,45 @@ __device__ __forceinline__ void finish_rows(const GemvParams &p, const float *re
         v += __shfl_xor_sync(0xffffffffu, v, 4);
         if (sub == 0 && r < nred) {
             const int64_t o = out0 + r;
-            if (p.residual) {                      // fused residual ADD (computeAdd's single F32 add, same rounding)
+            if (FUSED && p.residual) {             // fused residual ADD (computeAdd's single F32 add, same rounding)
                 if (p.dst_raw) p.dst_raw[o] = v;
                 v = __fadd_rn(p.residual[o], v);
             }
-            p.dst[o] = v;
+            dst[o] = v;
 #pragma unroll 1
             for (int q = 0; q < p.npeers; q++) p.peer[q][o] = v;
+        }
+    }
+}
+
+// gate/up pair (SwiGLU, LlamaMLP.forward model/LlamaModel.kt:159-176): rows [0, n) of the partial-sum buffer hold segment 0
+// (gate), rows [off, off + n) segment 1 (up).  Stores g, u, silu(g) and silu(g)*u with the elementwise kernels' roundings.
+__device__ __forceinline__ void finish_pair(const GemvParams &p, const float *red, int n, int off, int64_t out0, int warp, int lane) {
+    const int sub = lane & 7, rsel = lane >> 3;
+    const int nc4 = p.red_stride >> 2;
+#pragma unroll 1
+    for (int rb = warp * 4; rb < n; rb += p.cwarps * 4) {
+        const int r = rb + rsel;
+        float g = 0.f, u = 0.f;
+        if (r < n) {
+            const float4 *rg_ = (const float4 *)(red + (size_t)r * p.red_stride);
+            const float4 *ru_ = (const float4 *)(red + (size_t)(off + r) * p.red_stride);
+#pragma unroll 2
+            for (int c = sub; c < nc4; c += 8) {
+                const float4 a = rg_[c], b = ru_[c];
+                g += (a.x + a.y) + (a.z + a.w);
+                u += (b.x + b.y) + (b.z + b.w);
+            }
+        }
+#pragma unroll
+        for (int o = 1; o < 8; o <<= 1) { g += __shfl_xor_sync(0xffffffffu, g, o); u += __shfl_xor_sync(0xffffffffu, u, o); }
+        if (sub == 0 && r < n) {
+            const int64_t o = out0 + r;
+            const float act = silu_f(g);
+            p.dst[o] = g;
+            p.dst_seg[0][o] = u;
+            if (p.epi_act) p.epi_act[o] = act;
+            p.epi_out[o] = __fmul_rn(act, u);
         }
     }
 }
@@ -377,7 +420,9 @@ __device__ __forceinline__ void finish_rows(const GemvParams &p, const float *re
 // MINB = CTAs of consecutive launches that must fit on one SM together (registers are
 // capped accordingly): with programmatic dependent launch the next GEMV's CTA sits beside
 // this one and streams its weights while this one computes.
-template <int TYPE, int MAXW, int MINB, int NP>
+// FUSED = false is the plain computeMatMul launch: no prologue, one weight segment, plain store (the fused
+// variants cost the plain one ~8 % when they share its code: measured, profiles/r01j_gemv_ab.txt).
+template <int TYPE, int MAXW, int MINB, int NP, bool FUSED>
 __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t *full = (uint64_t *)smem;                   // [GEMV_MAX_STAGES]
@@ -397,6 +442,8 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
     }
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int stage_bytes = p.stage_rows * p.row_bytes;
+    const int nseg = FUSED ? p.nseg : 1;
+    const int epi_mode = FUSED ? p.epi_mode : 0;
 
     // balanced contiguous row range of this CTA: the first `rem` CTAs own one unit more
     const int ub = p.units_per_cta * (int)blockIdx.x + min((int)blockIdx.x, p.units_rem);
@@ -405,10 +452,20 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
 
     if (warp == p.cwarps) {
         // ===== producer warp: lane 0 initialises the barriers and streams this CTA's byte range =====
-        const uint8_t *src = p.a + (int64_t)r_begin * p.row_bytes;
-        int s = 0, left = nrows;
+        const int64_t seg_off = (int64_t)r_begin * p.row_bytes;
+        const uint8_t *src = p.a + seg_off;
+        int s = 0, left = nrows, seg = 0;
         uint8_t *dstp = stage0;
         uint64_t pol_w = 0;
+        // next chunk of this CTA's byte stream: its row range of segment 0, then of segment 1, ...; a stage never
+        // spans two segments (the consumers chunk the same way)
+        auto advance = [&]() -> bool {
+            if (left > 0) return true;
+            if (!FUSED || ++seg >= nseg) return false;
+            src = p.a_seg[seg - 1] + seg_off;
+            left = nrows;
+            return true;
+        };
         if (lane == 0) {
             LK_TL(0);
 #pragma unroll 1
@@ -420,7 +477,7 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
             if (p.wait_mode == GEMV_WAIT_FULL) pdl_wait();
             pol_w = l2_policy_evict_first();
 #pragma unroll 1
-            for (; s < p.nstages && left > 0; s++) {   // first pass over the ring: no waiting
+            for (; s < p.nstages && advance(); s++) {   // first pass over the ring: no waiting
                 const int rows = min(p.stage_rows, left);
                 const uint32_t bytes = (uint32_t)(rows * p.row_bytes);
                 mbar_arrive_expect_tx(&full[s], bytes);
@@ -431,11 +488,11 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
         }
         __syncwarp();
         __syncthreads();   // consumers may now wait on the barriers
-        if (lane == 0 && left > 0) {
+        if (lane == 0 && s == p.nstages) {
             int round = 1;
             s = 0; dstp = stage0;
 #pragma unroll 1
-            while (left > 0) {
+            while (advance()) {
                 mbar_wait(&empty[s], (round - 1) & 1);
                 const int rows = min(p.stage_rows, left);
                 const uint32_t bytes = (uint32_t)(rows * p.row_bytes);
@@ -467,7 +524,7 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
         pdl_launch_dependents();   // the next kernel can start its prologue / weight prefetch under our main loop
     }
     if (tid == 0) LK_TL(3);
-    prep_x<TYPE, NP>(p, xs, tid, nct);
+    prep_x<TYPE, NP, FUSED>(p, xs, tid, nct);
     if (tid == 0) LK_TL(24);
     asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");   // activation planes written
     if (tid == 0) LK_TL(4);
@@ -494,14 +551,19 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
     const int rg_words = p.rg * (p.row_bytes >> 2);
     int red_base = 0, s = 0, par = 0, it = 0;
     const uint32_t *sp = (const uint32_t *)stage0 + (size_t)rgi * (p.row_bytes >> 2);   // my first row of the stage
-    float *rp = red + (size_t)rgi * p.red_stride + (col >> 2);
+    float *const rp0 = red + (size_t)rgi * p.red_stride + (col >> 2);
+    float *rp = rp0;
     const int rstep = p.rg * p.red_stride;
 #pragma unroll 1
+    for (int seg = 0; seg < nseg; seg++) {
+    float *const seg_dst = (!FUSED || seg == 0) ? p.dst : p.dst_seg[seg - 1];
+    if (epi_mode == 1 && seg == 1) rp = rp0 + (size_t)p.pair_off * p.red_stride;   // the host sized the buffer for both
+#pragma unroll 1
     for (int row0 = 0; row0 < nrows; row0 += p.stage_rows, it++) {
-        if (row0 + p.stage_rows - red_base > p.red_rows) {
+        if (epi_mode != 1 && row0 + p.stage_rows - red_base > p.red_rows) {
             // partial-sum buffer full (a CTA that owns more rows than it holds)
             asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
-            finish_rows(p, red, row0 - red_base, p.row_offset + r_begin + red_base, warp, lane);
+            finish_rows<FUSED>(p, seg_dst, red, row0 - red_base, p.row_offset + r_begin + red_base, warp, lane);
             asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
             rp -= (size_t)(row0 - red_base) * p.red_stride;
             red_base = row0;
@@ -539,10 +601,21 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
         rp += (size_t)p.stage_rows * p.red_stride;
         if (++s == p.nstages) { s = 0; par ^= 1; sp -= (size_t)p.nstages * p.stage_rows * (p.row_bytes >> 2); }
     }
+    if (epi_mode == 1) continue;                // the pair is finished together below
     if (tid == 0) LK_TL(6);
     asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
     if (tid == 0) LK_TL(20);
-    finish_rows(p, red, nrows - red_base, p.row_offset + r_begin + red_base, warp, lane);
+    finish_rows<FUSED>(p, seg_dst, red, nrows - red_base, p.row_offset + r_begin + red_base, warp, lane);
+    if (seg + 1 < nseg) {                        // the buffer is reused by the next segment
+        asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
+        rp = rp0;
+        red_base = 0;
+    }
+    }
+    if (epi_mode == 1) {
+        asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
+        finish_pair(p, red, nrows, p.pair_off, p.row_offset + r_begin, warp, lane);
+    }
     if (tid == 0) {
         LK_TL(7);
         // keep completion order = launch order so a later launch's wait covers every earlier one
@@ -553,9 +626,9 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
 // ---------------------------------------------------------------------------
 // host side: shape analysis + launch
 // ---------------------------------------------------------------------------
-template <int TYPE, int MAXW, int MINB, int NP>
+template <int TYPE, int MAXW, int MINB, int NP, bool FUSED>
 static cudaError_t launch_one(const GemvParams &p, int grid, int smem, int pdl, cudaStream_t s) {
-    auto kern = gemv_kernel<TYPE, MAXW, MINB, NP>;
+    auto kern = gemv_kernel<TYPE, MAXW, MINB, NP, FUSED>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
@@ -573,12 +646,17 @@ static cudaError_t launch_one(const GemvParams &p, int grid, int smem, int pdl, 
     return cudaLaunchKernelEx(&cfg, kern, p);
 }
 
+template <int TYPE, int NP, bool FUSED>
+static cudaError_t launch_fused(const GemvParams &p, int grid, int smem, int pdl, cudaStream_t s) {
+    if (p.cwarps <= 8) return launch_one<TYPE, 8, 2, NP, FUSED>(p, grid, smem, pdl, s);
+    if (p.cwarps <= 12) return launch_one<TYPE, 12, 2, NP, FUSED>(p, grid, smem, pdl, s);
+    if (p.cwarps <= 16) return launch_one<TYPE, 16, 2, NP, FUSED>(p, grid, smem, pdl, s);
+    return launch_one<TYPE, 28, 1, NP, FUSED>(p, grid, smem, pdl, s);   // K up to 28672 (Llama-2-70B down projection): one CTA per SM
+}
+
 template <int TYPE, int NP>
-static cudaError_t launch_type(const GemvParams &p, int grid, int smem, int pdl, cudaStream_t s) {
-    if (p.cwarps <= 8) return launch_one<TYPE, 8, 2, NP>(p, grid, smem, pdl, s);
-    if (p.cwarps <= 12) return launch_one<TYPE, 12, 2, NP>(p, grid, smem, pdl, s);
-    if (p.cwarps <= 16) return launch_one<TYPE, 16, 2, NP>(p, grid, smem, pdl, s);
-    return launch_one<TYPE, 28, 1, NP>(p, grid, smem, pdl, s);   // K up to 28672 (Llama-2-70B down projection): one CTA per SM
+static cudaError_t launch_type(const GemvParams &p, bool fused, int grid, int smem, int pdl, cudaStream_t s) {
+    return fused ? launch_fused<TYPE, NP, true>(p, grid, smem, pdl, s) : launch_fused<TYPE, NP, false>(p, grid, smem, pdl, s);
 }
 
 cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const float *b, float *dst,
@@ -594,10 +672,23 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
     p.npeers = peers.n;
     for (int i = 0; i < peers.n && i < 8; i++) p.peer[i] = peers.ptr[i];
     p.K = (int)K; p.M = (int)M; p.row_offset = row_offset;
+    p.nseg = 1;
     if (fusion) {
         if (((uintptr_t)fusion->pro_w & 15) || ((uintptr_t)fusion->b_out & 15)) return cudaErrorNotSupported;
         p.pro_mode = fusion->pro_mode; p.pro_w = fusion->pro_w; p.pro_eps = fusion->pro_eps; p.b_out = fusion->b_out;
         p.residual = fusion->residual; p.dst_raw = fusion->dst_raw;
+        if (fusion->nseg_extra < 0 || fusion->nseg_extra > 2) return cudaErrorNotSupported;
+        if (fusion->nseg_extra > 0 && (fusion->residual || peers.n > 0 || row_offset != 0)) return cudaErrorNotSupported;
+        for (int i = 0; i < fusion->nseg_extra; i++) {
+            if (!fusion->a_extra[i] || !fusion->dst_extra[i] || ((uintptr_t)fusion->a_extra[i] & 15)) return cudaErrorNotSupported;
+            p.a_seg[i] = (const uint8_t *)fusion->a_extra[i];
+            p.dst_seg[i] = fusion->dst_extra[i];
+        }
+        p.nseg = 1 + fusion->nseg_extra;
+        if (fusion->epi_mode == 1) {
+            if (fusion->nseg_extra != 1 || !fusion->epi_out) return cudaErrorNotSupported;
+            p.epi_mode = 1; p.epi_act = fusion->epi_act; p.epi_out = fusion->epi_out;
+        }
     }
     p.tl = (unsigned long long *)tune.timeline;
     p.wait_mode = tune.wait_mode;
@@ -639,6 +730,13 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
     const int red_cap = (24 * 1024 / (p.red_stride * 4) / p.stage_rows) * p.stage_rows;
     if (red_rows > red_cap) red_rows = red_cap;
     if (red_rows < p.stage_rows) red_rows = p.stage_rows;
+    if (p.epi_mode == 1) {
+        // a pair keeps both segments' partial sums until the end (no flush): rows [0, n) gate, [pair_off, pair_off + n) up;
+        // 11008 rows over 148 CTAs at K = 4096 need 24 KB
+        p.pair_off = (max_cta_rows + 3) & ~3;
+        red_rows = 2 * p.pair_off;
+        if ((size_t)red_rows * p.red_stride * 4 > 40 * 1024) return cudaErrorNotSupported;
+    }
     p.red_rows = red_rows;
     p.red_off = 256;
     p.x_off = (p.red_off + p.red_rows * p.red_stride * 4 + 15) & ~15;
@@ -654,14 +752,15 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
     }
     p.nstages = nst;
     const int smem = p.stage_off + nst * stage_bytes;
+    const bool fused = p.pro_mode != 0 || p.residual != nullptr || p.nseg > 1;
 
     switch (type * 4 + np) {
-        case T_Q4_0 * 4 + 2: return launch_type<T_Q4_0, 2>(p, grid, smem, tune.pdl, s);
-        case T_Q4_1 * 4 + 2: return launch_type<T_Q4_1, 2>(p, grid, smem, tune.pdl, s);
-        case T_Q8_0 * 4 + 2: return launch_type<T_Q8_0, 2>(p, grid, smem, tune.pdl, s);
-        case T_Q4_0 * 4 + 3: return launch_type<T_Q4_0, 3>(p, grid, smem, tune.pdl, s);
-        case T_Q4_1 * 4 + 3: return launch_type<T_Q4_1, 3>(p, grid, smem, tune.pdl, s);
-        case T_Q8_0 * 4 + 3: return launch_type<T_Q8_0, 3>(p, grid, smem, tune.pdl, s);
+        case T_Q4_0 * 4 + 2: return launch_type<T_Q4_0, 2>(p, fused, grid, smem, tune.pdl, s);
+        case T_Q4_1 * 4 + 2: return launch_type<T_Q4_1, 2>(p, fused, grid, smem, tune.pdl, s);
+        case T_Q8_0 * 4 + 2: return launch_type<T_Q8_0, 2>(p, fused, grid, smem, tune.pdl, s);
+        case T_Q4_0 * 4 + 3: return launch_type<T_Q4_0, 3>(p, fused, grid, smem, tune.pdl, s);
+        case T_Q4_1 * 4 + 3: return launch_type<T_Q4_1, 3>(p, fused, grid, smem, tune.pdl, s);
+        case T_Q8_0 * 4 + 3: return launch_type<T_Q8_0, 3>(p, fused, grid, smem, tune.pdl, s);
         default: return cudaErrorNotSupported;
     }
 }

@@ -40,6 +40,14 @@ struct GemvFusion {
     float *b_out = nullptr;         // also store the activations actually used (the unfused RMSNorm's dst)
     const float *residual = nullptr;   // dst = residual + a x b  (the following ADD)
     float *dst_raw = nullptr;       // also store the bare product (the unfused matmul's dst)
+    // stacked segments: up to two more weights of the same type and shape, multiplied with the same activations by
+    // the same launch (Q/K/V, gate/up); no residual, no peers, no row offset with nseg_extra > 0
+    int nseg_extra = 0;
+    const void *a_extra[2] = {nullptr, nullptr};
+    float *dst_extra[2] = {nullptr, nullptr};
+    int epi_mode = 0;               // 1 (exactly one extra segment): SwiGLU pair, epi_out = silu(dst) * dst_extra[0]
+    float *epi_act = nullptr;       //   optional: silu(dst) (the SILU node's dst)
+    float *epi_out = nullptr;
 };
 cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const float *b, float *dst,
                         int64_t row_offset, const GemvPeers &peers, const GemvTuning &tune, int sm_count,

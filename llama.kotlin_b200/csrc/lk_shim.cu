@@ -48,8 +48,12 @@ void chain_close(lk_ctx *ctx) { ctx->chain_reads.clear(); ctx->chain_writes.clea
 }  // namespace
 int gemv_wait_mode(lk_ctx *ctx, const void *a, size_t abytes, const void *b, size_t bbytes, const void *d, size_t dbytes,
                    bool pdl, const std::vector<std::pair<const void *, size_t>> *more_reads,
-                   const std::vector<std::pair<const void *, size_t>> *more_writes) {
+                   const std::vector<std::pair<const void *, size_t>> *more_writes,
+                   const std::vector<std::pair<const void *, size_t>> *more_weights) {
     const Range ra((uintptr_t)a, (uintptr_t)a + abytes);
+    std::vector<Range> wt;          // weights: read before the wait point (prefetch)
+    wt.push_back(ra);
+    if (more_weights) for (const auto &r : *more_weights) if (r.first && r.second) wt.push_back(Range((uintptr_t)r.first, (uintptr_t)r.first + r.second));
     std::vector<Range> rd, wr;      // what the launch reads after its wait point / writes
     rd.push_back(Range((uintptr_t)b, (uintptr_t)b + bbytes));
     wr.push_back(Range((uintptr_t)d, (uintptr_t)d + dbytes));
@@ -59,14 +63,16 @@ int gemv_wait_mode(lk_ctx *ctx, const void *a, size_t abytes, const void *b, siz
     if (!pdl || !ctx->overlap_mode) mode = 1;
     for (const Range &r : rd) if (overlaps(ctx->chain_writes, r)) mode = 1;
     for (const Range &r : wr) if (overlaps(ctx->chain_writes, r) || overlaps(ctx->chain_reads, r)) mode = 1;
-    if (overlaps(ctx->chain_writes, ra)) mode = 0;
+    for (const Range &r : wt) if (overlaps(ctx->chain_writes, r)) mode = 0;
     if (!ctx->other_writes.empty()) {   // first GEMV after a normal op: it can start before that op has finished
-        mode = overlaps(ctx->other_writes, ra) ? 0 : (mode == 0 ? 0 : 1);
+        bool hit = false;
+        for (const Range &r : wt) hit = hit || overlaps(ctx->other_writes, r);
+        mode = hit ? 0 : (mode == 0 ? 0 : 1);
         ctx->other_writes.clear();
     }
     if (mode != 2) chain_close(ctx);   // everything earlier has completed once this launch passes its wait
     if (ctx->chain_reads.size() > 256) { chain_close(ctx); mode = 1; }
-    ctx->chain_reads.push_back(ra);
+    for (const Range &r : wt) ctx->chain_reads.push_back(r);
     for (const Range &r : rd) ctx->chain_reads.push_back(r);
     for (const Range &r : wr) ctx->chain_writes.push_back(r);
     return mode;
@@ -465,14 +471,29 @@ lk_status lk_compute_matmul_fused(lk_ctx *ctx, const lk_tensor *a, const lk_tens
     if (!is_block_type(a->type) || b->type != LK_TYPE_F32 || dst->type != LK_TYPE_F32)
         return fail(ctx, LK_ENOTIMPL, "fused matmul: Q4_0/Q4_1/Q8_0 x F32 -> F32 only");
     if (N != 1 || M <= 0 || K <= 0) return fail(ctx, LK_ENOTIMPL, "fused matmul: N == 1 only");
-    const lk_tensor *all[] = {a, b, dst, f->norm_x, f->norm_w, f->residual, f->sum_dst};
+    if (f->n_extra < 0 || f->n_extra > 2) return fail(ctx, LK_EINVAL_ARG, "fused matmul: n_extra must be 0..2");
+    if (f->n_extra > 0 && f->residual) return fail(ctx, LK_EINVAL_ARG, "fused matmul: stacked matmuls take no residual");
+    if (f->mul_dst && f->n_extra != 1) return fail(ctx, LK_EINVAL_ARG, "fused matmul: the SwiGLU epilogue needs exactly one extra weight");
+    if (f->silu_dst && !f->mul_dst) return fail(ctx, LK_EINVAL_ARG, "fused matmul: silu_dst goes with mul_dst");
+    const lk_tensor *all[] = {a, b, dst, f->norm_x, f->norm_w, f->residual, f->sum_dst, f->n_extra > 0 ? f->a_extra[0] : nullptr,
+                              f->n_extra > 1 ? f->a_extra[1] : nullptr, f->n_extra > 0 ? f->dst_extra[0] : nullptr,
+                              f->n_extra > 1 ? f->dst_extra[1] : nullptr, f->silu_dst, f->mul_dst};
+    for (int i = 0; i < f->n_extra; i++) {
+        if (!f->a_extra[i] || !f->dst_extra[i]) return fail(ctx, LK_EINVAL_ARG, "fused matmul: NULL extra tensor");
+        if (f->a_extra[i]->type != a->type || f->a_extra[i]->ne[0] != K || f->a_extra[i]->ne[1] != M)
+            return fail(ctx, LK_EINVAL_DIM, "fused matmul: extra weights must have a's type and shape");
+        if (num_elements(f->dst_extra[i]) != M) return fail(ctx, LK_EINVAL_DIM, "fused matmul: extra dst must hold M elements");
+    }
+    if (f->mul_dst && num_elements(f->mul_dst) != M) return fail(ctx, LK_EINVAL_DIM, "fused matmul: mul_dst must hold M elements");
+    if (f->silu_dst && num_elements(f->silu_dst) != M) return fail(ctx, LK_EINVAL_DIM, "fused matmul: silu_dst must hold M elements");
     for (const lk_tensor *t : all) {
         if (!t) continue;
         if (!t->dev_buf) return fail(ctx, LK_ENOTIMPL, "fused matmul: device-resident tensors only");
         const int64_t nb = lk_tensor_nbytes(t);
         if (nb < 0 || t->data_offset > t->dev_buf->size || (uint64_t)nb > t->dev_buf->size - t->data_offset)
             return fail(ctx, LK_EBOUNDS, "fused matmul: tensor bytes exceed the device buffer");
-        if (t != a && t->type != LK_TYPE_F32) return fail(ctx, LK_EINVAL_TYPE, "fused matmul: F32 vectors expected");
+        if (t != a && t != f->a_extra[0] && t != f->a_extra[1] && t->type != LK_TYPE_F32)
+            return fail(ctx, LK_EINVAL_TYPE, "fused matmul: F32 vectors expected");
     }
     if ((f->residual != nullptr) != (f->sum_dst != nullptr)) return fail(ctx, LK_EINVAL_ARG, "fused matmul: residual and sum_dst go together");
     if (f->norm_x && num_elements(f->norm_x) != K) return fail(ctx, LK_EINVAL_DIM, "fused matmul: norm_x must hold K elements");
@@ -492,12 +513,24 @@ lk_status lk_compute_matmul_fused(lk_ctx *ctx, const lk_tensor *a, const lk_tens
     if (f->residual) { fu.residual = (const float *)ptr(f->residual); fu.dst_raw = out; out = (float *)ptr(f->sum_dst); }
     lk::GemvTuning tune = ctx->tune;
     tune.pdl = (ctx->pdl_mode == 2) || (ctx->pdl_mode == 1 && ctx->capturing);
-    std::vector<std::pair<const void *, size_t>> rd, wr;
+    std::vector<std::pair<const void *, size_t>> rd, wr, wt;
     rd.push_back({fu.pro_w, (size_t)K * 4});
     rd.push_back({fu.residual, (size_t)M * 4});
     wr.push_back({fu.b_out, (size_t)K * 4});
     wr.push_back({fu.dst_raw, (size_t)M * 4});
-    tune.wait_mode = lk::gemv_wait_mode(ctx, ptr(a), (size_t)lk_tensor_nbytes(a), x, (size_t)K * 4, out, (size_t)M * 4, tune.pdl != 0, &rd, &wr);
+    fu.nseg_extra = f->n_extra;
+    for (int i = 0; i < f->n_extra; i++) {
+        fu.a_extra[i] = ptr(f->a_extra[i]);
+        fu.dst_extra[i] = (float *)ptr(f->dst_extra[i]);
+        wt.push_back({fu.a_extra[i], (size_t)lk_tensor_nbytes(f->a_extra[i])});
+        wr.push_back({fu.dst_extra[i], (size_t)M * 4});
+    }
+    if (f->mul_dst) {
+        fu.epi_mode = 1; fu.epi_out = (float *)ptr(f->mul_dst); fu.epi_act = (float *)ptr(f->silu_dst);
+        wr.push_back({fu.epi_out, (size_t)M * 4});
+        wr.push_back({fu.epi_act, (size_t)M * 4});
+    }
+    tune.wait_mode = lk::gemv_wait_mode(ctx, ptr(a), (size_t)lk_tensor_nbytes(a), x, (size_t)K * 4, out, (size_t)M * 4, tune.pdl != 0, &rd, &wr, &wt);
     lk::GemvPeers none;
     cudaError_t e = lk::launch_gemv(a->type, ptr(a), K, M, x, out, 0, none, tune, ctx->sm_count, ctx->stream, &fu);
     if (e == cudaErrorNotSupported) {

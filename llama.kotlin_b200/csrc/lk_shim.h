@@ -64,7 +64,8 @@ void chain_other(lk_ctx *ctx, const void *dst, size_t bytes);
 // where a PDL-launched GEMV must wait (GEMV_WAIT_*), and chain bookkeeping for it
 int gemv_wait_mode(lk_ctx *ctx, const void *a, size_t abytes, const void *b, size_t bbytes, const void *d, size_t dbytes,
                    bool pdl, const std::vector<std::pair<const void *, size_t>> *more_reads = nullptr,
-                   const std::vector<std::pair<const void *, size_t>> *more_writes = nullptr);   // a non-GEMV op wrote [dst, dst+bytes)
+                   const std::vector<std::pair<const void *, size_t>> *more_writes = nullptr,
+                   const std::vector<std::pair<const void *, size_t>> *more_weights = nullptr);   // a non-GEMV op wrote [dst, dst+bytes)
 }  // namespace lk
 
 #define LK_CUDA(ctx, call)                                             \

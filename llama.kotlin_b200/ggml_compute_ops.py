@@ -96,7 +96,7 @@ def computeMatMul(graphAllocator, context: GGMLContext, a: GGMLTensor, b: GGMLTe
 
 
 def computeMatMulFused(graphAllocator, context, a, b, dst, norm_x=None, norm_w=None, eps: float = 0.0,
-                       residual=None, sum_dst=None, store_b: bool = True) -> bool:
+                       residual=None, sum_dst=None, store_b: bool = True, extra=(), silu_dst=None, mul_dst=None) -> bool:
     """computeMatMul with the RMS_NORM that produces `b` and / or the ADD that consumes `dst` folded into the GEMV
     launch (lk_compute_matmul_fused).  Returns False when the library declines the shape (LK_ENOTIMPL): the
     caller then issues the unfused ops."""
@@ -108,6 +108,17 @@ def computeMatMulFused(graphAllocator, context, a, b, dst, norm_x=None, norm_w=N
     f.residual = C.pointer(keep[2]) if keep[2] is not None else None
     f.sum_dst = C.pointer(keep[3]) if keep[3] is not None else None
     f.flags = 0 if store_b else 1        # LK_FUSE_SKIP_B_STORE
+    # stacked matmuls on the same activations: extra = [(a1, dst1), ...]; SwiGLU epilogue with silu_dst / mul_dst
+    f.n_extra = len(extra)
+    for i, (ae, de) in enumerate(extra):
+        keep.append(describe(graphAllocator, ae))
+        f.a_extra[i] = C.pointer(keep[-1])
+        keep.append(describe(graphAllocator, de))
+        f.dst_extra[i] = C.pointer(keep[-1])
+    for name, t in (("silu_dst", silu_dst), ("mul_dst", mul_dst)):
+        if t is not None:
+            keep.append(describe(graphAllocator, t))
+            setattr(f, name, C.pointer(keep[-1]))
     ctx = _ctx_of(graphAllocator)
     st = B.lib().lk_compute_matmul_fused(ctx.handle, describe(graphAllocator, a), describe(graphAllocator, b),
                                          describe(graphAllocator, dst), C.byref(f))

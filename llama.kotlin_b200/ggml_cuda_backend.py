@@ -243,6 +243,47 @@ class GGMLCudaBackend:
                 continue
             add_of[i] = j
             skip.add(j)
+        # stacked matmuls: consecutive GEMVs (nothing but fused-away nodes between them) with the same activations
+        # and weights of one type and shape run as one launch at the first one's position; a gate/up pair whose
+        # only readers are SILU(gate) and MUL(silu, up) also takes those two nodes into its epilogue
+        group_of, pair_of = {}, {}
+        i = 0
+        while i < n:
+            t = nodes[i]
+            if i in skip or not is_gemv(t) or i in add_of:
+                i += 1
+                continue
+            members, k = [i], i + 1
+            while k < n and len(members) < 3:
+                if k in skip:
+                    k += 1
+                    continue
+                u = nodes[k]
+                if (is_gemv(u) and k not in add_of and self._key(u.src[1]) == self._key(t.src[1]) and
+                        u.src[0].type == t.src[0].type and tuple(u.src[0].ne) == tuple(t.src[0].ne) and
+                        rms_of.get(k) == rms_of.get(i) and
+                        not any(overlaps(self._span(u.src[1]), self._span(nodes[m])) for m in members)):
+                    members.append(k)
+                    k += 1
+                else:
+                    break
+            if len(members) > 1:
+                group_of[i] = members
+                for m in members[1:]:
+                    skip.add(m)
+                if len(members) == 2:
+                    g, u2 = members
+                    cg = [c for c in consumers.get(self._key(nodes[g]), []) if c[0] > g]
+                    cu = [c for c in consumers.get(self._key(nodes[u2]), []) if c[0] > u2]
+                    if len(cg) == 1 and len(cu) == 1 and nodes[cg[0][0]].op == GGMLOp.SILU and nodes[cu[0][0]].op == GGMLOp.MUL:
+                        si, mi = cg[0][0], cu[0][0]
+                        cs = [c for c in consumers.get(self._key(nodes[si]), []) if c[0] > si]
+                        if (si == u2 + 1 and mi == si + 1 and len(cs) == 1 and cs[0][0] == mi and
+                                nodes[mi].type == GGMLType.F32 and int(nodes[mi].numElements()) == int(nodes[g].numElements())):
+                            pair_of[i] = (si, mi)
+                            skip.update((si, mi))
+            i = members[-1] + 1
+        self._groups, self._pairs = group_of, pair_of
         return rms_of, add_of, skip
 
     def _runNodes(self, ga, graph: GGMLCGraph, fuse: bool) -> None:
@@ -256,9 +297,41 @@ class GGMLCudaBackend:
         for i, node in enumerate(nodes):
             if i in skip:
                 continue
+            if i in self._groups:
+                if self._runGroup(ga, nodes, i, rms_of, stored):
+                    continue
+                # declined: every member (and the SILU / MUL pair) on its own, in graph order
+                for m in self._groups[i]:
+                    self._runOne(ga, nodes, m, rms_of, add_of, stored)
+                if i in self._pairs:
+                    for k in self._pairs[i]:
+                        self._computeNode(ga, nodes[k])
+                continue
+            self._runOne(ga, nodes, i, rms_of, add_of, stored)
+
+    def _runGroup(self, ga, nodes, i, rms_of, stored) -> bool:
+        members = self._groups[i]
+        node = nodes[i]
+        kw = dict(extra=[(nodes[m].src[0], nodes[m]) for m in members[1:]])
+        if i in rms_of:
+            r = nodes[rms_of[i]]
+            eps = struct.unpack("<f", struct.pack("<i", int(r.opParams[0])))[0]
+            kw.update(norm_x=r.src[0], norm_w=r.src[1], eps=eps, store_b=rms_of[i] not in stored)
+        if i in self._pairs:
+            si, mi = self._pairs[i]
+            kw.update(silu_dst=nodes[si], mul_dst=nodes[mi])
+        if not ops.computeMatMulFused(ga, None, node.src[0], node.src[1], node, **kw):
+            return False
+        if i in rms_of:
+            stored.add(rms_of[i])
+        return True
+
+    def _runOne(self, ga, nodes, i, rms_of, add_of, stored) -> None:
+        node = nodes[i]
+        if True:
             if i not in rms_of and i not in add_of:
                 self._computeNode(ga, node)
-                continue
+                return
             r = nodes[rms_of[i]] if i in rms_of else None
             a = nodes[add_of[i]] if i in add_of else None
             kw = {}
@@ -271,7 +344,7 @@ class GGMLCudaBackend:
             if ops.computeMatMulFused(ga, None, node.src[0], node.src[1], node, **kw):
                 if r is not None:
                     stored.add(rms_of[i])
-                continue
+                return
             # the library declined this shape: the unfused ops, in graph order
             if r is not None and rms_of[i] not in stored:
                 self._computeNode(ga, r)

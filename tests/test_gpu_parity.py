@@ -617,6 +617,91 @@ def test_matmul_fused_declines_unsupported_shapes(O):
     be.free()
 
 
+@pytest.mark.parametrize("tname", ["Q4_0", "Q8_0", "Q4_1"])
+@pytest.mark.parametrize("M,K,nw", [(4096, 4096, 3), (11008, 4096, 2), (300, 1024, 3), (64, 128, 2)])
+def test_matmul_fused_stacked_weights(O, tname, M, K, nw):
+    """Two or three weights of one shape on the same activations in one launch (q/k/v, gate/up): every product
+    is bit-identical to the one the single GEMV stores, with and without the RMS_NORM prologue."""
+    gt, ot = QT[tname]
+    be = lk.GGMLCudaBackend(0)
+    bb = {"Q4_0": 18, "Q8_0": 34, "Q4_1": 20}[tname]
+    ga = lk.GGMLGraphAllocator(be, size=nw * (M * K // 32 * bb + 512) + (4 * K + 4 * nw * M) * 4 + (1 << 16))
+    x0 = synth_acts(1500 + M, K) * 2
+    w0 = (1.0 + 0.1 * synth_acts(1501 + M, K)).astype(np.float32)
+
+    def dev(t, shape, data=None):
+        tt = ga.allocateTensor(GGMLTensor(t, shape))
+        if data is not None:
+            ga.setBytes(tt, data)
+        return tt
+    ws = [dev(gt, [K, M], O.quantize(ot, synth_weights(1510 + M + i, M, K))) for i in range(nw)]
+    x, w = dev(GGMLType.F32, [K], x0), dev(GGMLType.F32, [K], w0)
+    b = dev(GGMLType.F32, [1, K], x0)
+    singles = []
+    for a in ws:
+        d = dev(GGMLType.F32, [1, M], np.zeros(M, np.float32))
+        lk.computeMatMul(ga, None, a, b, d)
+        singles.append(d)
+    ds = [dev(GGMLType.F32, [1, M], np.zeros(M, np.float32)) for _ in range(nw)]
+    assert lk.computeMatMulFused(ga, None, ws[0], b, ds[0], extra=list(zip(ws[1:], ds[1:])))
+    be.lk.sync()
+    for d, s1 in zip(ds, singles):
+        assert same_f32_bits(ga.getFloats(d), ga.getFloats(s1))
+    # with the prologue: the stored activations feed the single GEMVs
+    hb = dev(GGMLType.F32, [1, K], np.zeros(K, np.float32))
+    ds2 = [dev(GGMLType.F32, [1, M], np.zeros(M, np.float32)) for _ in range(nw)]
+    assert lk.computeMatMulFused(ga, None, ws[0], hb, ds2[0], norm_x=x, norm_w=w, eps=1e-6, extra=list(zip(ws[1:], ds2[1:])))
+    be.lk.sync()
+    assert np.allclose(ga.getFloats(hb), O.rms_norm(x0, w0, 1e-6, K), rtol=5e-7, atol=0)
+    for a, d in zip(ws, ds2):
+        s1 = dev(GGMLType.F32, [1, M], np.zeros(M, np.float32))
+        lk.computeMatMul(ga, None, a, hb, s1)
+        be.lk.sync()
+        assert same_f32_bits(ga.getFloats(d), ga.getFloats(s1))
+    be.free()
+
+
+@pytest.mark.parametrize("tname", ["Q4_0", "Q8_0", "Q4_1"])
+@pytest.mark.parametrize("M,K", [(11008, 4096), (1408, 512), (300, 1024), (64, 128)])
+def test_matmul_fused_swiglu_epilogue(O, tname, M, K):
+    """gate/up in one launch with SILU(gate) and SILU(gate)*up in its epilogue: g and u are the single GEMVs'
+    bits, silu within the SILU tolerance of the oracle on g, and the product exactly silu*u."""
+    gt, ot = QT[tname]
+    be = lk.GGMLCudaBackend(0)
+    bb = {"Q4_0": 18, "Q8_0": 34, "Q4_1": 20}[tname]
+    ga = lk.GGMLGraphAllocator(be, size=2 * (M * K // 32 * bb + 512) + (2 * K + 8 * M) * 4 + (1 << 16))
+    x0 = synth_acts(1600 + M, K)
+
+    def dev(t, shape, data=None):
+        tt = ga.allocateTensor(GGMLTensor(t, shape))
+        if data is not None:
+            ga.setBytes(tt, data)
+        return tt
+    wg = dev(gt, [K, M], O.quantize(ot, synth_weights(1610 + M, M, K)))
+    wu = dev(gt, [K, M], O.quantize(ot, synth_weights(1611 + M, M, K)))
+    b = dev(GGMLType.F32, [1, K], x0)
+    g, u, g1, u1 = (dev(GGMLType.F32, [1, M], np.zeros(M, np.float32)) for _ in range(4))
+    act, prod, act1, prod1 = (dev(GGMLType.F32, [M], np.zeros(M, np.float32)) for _ in range(4))
+    assert lk.computeMatMulFused(ga, None, wg, b, g, extra=[(wu, u)], silu_dst=act, mul_dst=prod)
+    lk.computeMatMul(ga, None, wg, b, g1)
+    lk.computeMatMul(ga, None, wu, b, u1)
+    flat = lambda t: GGMLTensor(GGMLType.F32, [M], bufferId=t.bufferId, dataOffset=t.dataOffset, buffer=t.buffer)  # noqa: E731
+    lk.computeSilu(ga, None, flat(g1), act1)
+    lk.computeMul(ga, None, act1, flat(u1), prod1)
+    be.lk.sync()
+    G, U = ga.getFloats(g), ga.getFloats(u)
+    assert same_f32_bits(G, ga.getFloats(g1)) and same_f32_bits(U, ga.getFloats(u1))
+    assert same_f32_bits(ga.getFloats(act), ga.getFloats(act1))          # the same device silu as the SILU op
+    assert same_f32_bits(ga.getFloats(prod), ga.getFloats(prod1))
+    assert rel_err(ga.getFloats(act), O.silu(G)) <= 1e-6
+    # without silu_dst only the product is written
+    prod2 = dev(GGMLType.F32, [M], np.zeros(M, np.float32))
+    assert lk.computeMatMulFused(ga, None, wg, b, g, extra=[(wu, u)], mul_dst=prod2)
+    be.lk.sync()
+    assert same_f32_bits(ga.getFloats(prod2), ga.getFloats(prod1))
+    be.free()
+
+
 def test_decoder_layer_graph_fused_equals_unfused(O):
     """The captured layer with the fusion pass on and off: every intermediate the graph names is still written,
     and the outputs agree to the RMSNorm 1/rms difference (far below the matmul tolerance)."""
