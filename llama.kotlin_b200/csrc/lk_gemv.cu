@@ -575,11 +575,10 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
         const uint32_t *wp = sp;
         float *rq = rp;
 #pragma unroll 1
-        for (; nr > 0; nr -= UNR) {
-            // a short last step recomputes its last valid row in the unused slots (no store)
+        for (; nr >= UNR; nr -= UNR) {
             float v[UNR];
 #pragma unroll
-            for (int u = 0; u < UNR; u++) v[u] = block_dot<TYPE, NP>(wp + min(u, nr - 1) * rg_words, colc, x);
+            for (int u = 0; u < UNR; u++) v[u] = block_dot<TYPE, NP>(wp + u * rg_words, colc, x);
 #pragma unroll
             for (int u = 0; u < UNR; u++) v[u] = active ? v[u] : 0.f;
 #pragma unroll
@@ -588,11 +587,38 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
             for (int u = 0; u < UNR; u++) v[u] += __shfl_xor_sync(0xffffffffu, v[u], 2);
             if ((lane & 3) == 0) {
 #pragma unroll
-                for (int u = 0; u < UNR; u++)
-                    if (u < nr) rq[u * rstep] = v[u];     // one partial per 4 block columns
+                for (int u = 0; u < UNR; u++) rq[u * rstep] = v[u];     // one partial per 4 block columns
             }
             wp += UNR * rg_words;
             rq += UNR * rstep;
+        }
+        // the rows left over: two at a time, then one
+#ifdef LK_GEMV_TAIL2
+        if (nr >= 2) {
+            float v[2];
+#pragma unroll
+            for (int u = 0; u < 2; u++) v[u] = block_dot<TYPE, NP>(wp + u * rg_words, colc, x);
+#pragma unroll
+            for (int u = 0; u < 2; u++) v[u] = active ? v[u] : 0.f;
+#pragma unroll
+            for (int u = 0; u < 2; u++) v[u] += __shfl_xor_sync(0xffffffffu, v[u], 1);
+#pragma unroll
+            for (int u = 0; u < 2; u++) v[u] += __shfl_xor_sync(0xffffffffu, v[u], 2);
+            if ((lane & 3) == 0) { rq[0] = v[0]; rq[rstep] = v[1]; }
+            wp += 2 * rg_words;
+            rq += 2 * rstep;
+            nr -= 2;
+        }
+#endif
+#pragma unroll 1
+        for (; nr > 0; nr--) {
+            float v = block_dot<TYPE, NP>(wp, colc, x);
+            v = active ? v : 0.f;
+            v += __shfl_xor_sync(0xffffffffu, v, 1);
+            v += __shfl_xor_sync(0xffffffffu, v, 2);
+            if ((lane & 3) == 0) *rq = v;
+            wp += rg_words;
+            rq += rstep;
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty[s]);  // this warp is done reading the stage
@@ -711,9 +737,19 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
     // two CTAs (this launch and the next) share one SM's 227 KB when cwarps <= 12
     const int budget = tune.smem_budget > 0 ? tune.smem_budget : (p.ncw > 16 ? 216 : 112) * 1024;   // > 16 column warps: the
                                                                                                      // x planes alone need up to 98 KB
-    const int stage_target = tune.stage_bytes > 0 ? tune.stage_bytes : 32 * 1024;
+    // Stage sizing, measured on B200 (profiles/r01k_gemv_stage_ab.txt): a launch that waits for its predecessor runs
+    // best with stages of rg * 4 rows per 40 KB target (every warp gets whole 4-row steps, fewer barrier rounds on the
+    // critical path); independent launches, which overlap pairwise on an SM, with 32 KB stages of any row count.
+    const bool dependent = tune.wait_mode != GEMV_WAIT_END;
+    const int stage_target = tune.stage_bytes > 0 ? tune.stage_bytes : (dependent ? 40 : 32) * 1024;
     int quant = p.unit_rows;                       // stage_rows: multiple of unit_rows (TMA size) and of rg
     while (quant % p.rg) quant += p.unit_rows;
+    const bool row_quant = tune.row_quant < 0 ? dependent : tune.row_quant != 0;
+    if (row_quant) {
+        int q4 = p.unit_rows;
+        while (q4 % (p.rg * 4)) q4 += p.unit_rows;
+        if ((int64_t)q4 * p.row_bytes <= stage_target + stage_target / 4) quant = q4;
+    }
     int sr = (stage_target / p.row_bytes / quant) * quant;
     if (sr < quant) sr = quant;
     p.stage_rows = sr;

@@ -17,6 +17,7 @@ struct GemvTuning {
     int ctas_per_sm = 1;
     int act_planes = 3;     // activation fixed-point planes: 3 = 24-bit (default: as accurate as the F32 reference),
                             // 2 = 16-bit (opt-in: +8 % throughput, error 5e-5 of max instead of 2e-6)
+    int row_quant = -1;     // stage rows a multiple of 4 per warp: -1 auto (dependent launches only), 0 never, 1 always
     int wait_mode = 1;      // 0 wait before the weight prefetch, 1 before reading x, 2 at the end (independent launch)
     void *timeline = nullptr;   // tools/gemv_timeline.cu only: per-CTA %globaltimer stamps
 };

@@ -719,6 +719,7 @@ lk_status lk_set_option(lk_ctx *ctx, const char *name, int64_t v) {
     if (n == "gemv_pdl") ctx->pdl_mode = (int)v;
     else if (n == "gemv_warps") ctx->tune.variant = (int)v;
     else if (n == "gemv_stage_bytes") ctx->tune.stage_bytes = (int)v;
+    else if (n == "gemv_row_quant") ctx->tune.row_quant = (int)v;
     else if (n == "gemv_max_stages") ctx->tune.max_stages = (int)v;
     else if (n == "gemv_smem_budget") ctx->tune.smem_budget = (int)v;
     else if (n == "gemv_ctas_per_sm") ctx->tune.ctas_per_sm = (int)v;
@@ -736,6 +737,7 @@ int64_t lk_get_option(lk_ctx *ctx, const char *name) {
     if (n == "gemv_pdl") return ctx->pdl_mode;
     if (n == "gemv_warps") return ctx->tune.variant;
     if (n == "gemv_stage_bytes") return ctx->tune.stage_bytes;
+    if (n == "gemv_row_quant") return ctx->tune.row_quant;
     if (n == "gemv_max_stages") return ctx->tune.max_stages;
     if (n == "gemv_smem_budget") return ctx->tune.smem_budget;
     if (n == "gemv_ctas_per_sm") return ctx->tune.ctas_per_sm;
