@@ -210,6 +210,57 @@ int lko_dequantize(int type, const uint8_t *a, int64_t n, float *out) {
     }
 }
 
+/* ---- canonical ggml nibble order -------------------------- *
+ * The Kotlin accessors put element e of a Q4 block in byte e/2, nibble e&1 (core/GGMLTypes.kt:647-651);
+ * ggml and every GGUF file put it in byte e%16, nibble e/16 (/root/reference/ggml/src/ggml-quants.c:1524-1530,
+ * :1545-1551).  Q8_0 blocks are identical in both.  to_ggml = 0: ggml order in, Kotlin order out; 1: the inverse.
+ * Scales / mins are copied; the map is a bijection on the 32 nibbles, so repack(repack(x, 1), 0) == x.      */
+int lko_repack_nibbles(int type, const uint8_t *src, int64_t nblocks, uint8_t *dst, int to_ggml) {
+    const int bb = lko_block_bytes(type);
+    if (bb == 0) return LKO_ENOTIMPL;
+    if (type == LKO_TYPE_Q8_0) { memcpy(dst, src, (size_t)nblocks * bb); return LKO_OK; }
+    const int qoff = type == LKO_TYPE_Q4_0 ? 2 : 4;
+    for (int64_t b = 0; b < nblocks; b++) {
+        const uint8_t *s = src + b * bb;
+        uint8_t *d = dst + b * bb, nib[32];
+        memcpy(d, s, qoff);
+        for (int e = 0; e < QK; e++)       /* element e of the source block */
+            nib[e] = to_ggml ? (uint8_t)((s[qoff + e / 2] >> (4 * (e & 1))) & 15) : (uint8_t)((s[qoff + e % 16] >> (4 * (e / 16))) & 15);
+        memset(d + qoff, 0, 16);
+        for (int e = 0; e < QK; e++) {
+            if (to_ggml) d[qoff + e % 16] |= (uint8_t)(nib[e] << (4 * (e / 16)));
+            else d[qoff + e / 2] |= (uint8_t)(nib[e] << (4 * (e & 1)));
+        }
+    }
+    return LKO_OK;
+}
+
+/* Direct restatement of dequantize_row_q4_0 / q4_1 / q8_0 (/root/reference/ggml/src/ggml-quants.c:1515-1555,
+ * :1609-1625): y[j] = (lo - 8) * d, y[j + 16] = (hi - 8) * d; lo * d + m, hi * d + m; q * d.               */
+int lko_dequantize_ggml(int type, const uint8_t *a, int64_t n, float *out) {
+    if (n % QK != 0) return LKO_EINVAL_DIM;
+    const int bb = lko_block_bytes(type);
+    if (bb == 0) return LKO_ENOTIMPL;
+    if (type == LKO_TYPE_Q8_0) return lko_dequantize(type, a, n, out);
+    const int qoff = type == LKO_TYPE_Q4_0 ? 2 : 4;
+    for (int64_t b = 0; b < n / QK; b++) {
+        const uint8_t *s = a + b * bb;
+        const float d = lko_half_to_float(get_u16le(s));
+        const float m = type == LKO_TYPE_Q4_1 ? lko_half_to_float(get_u16le(s + 2)) : 0.0f;
+        for (int j = 0; j < 16; j++) {
+            const int lo = s[qoff + j] & 0x0F, hi = s[qoff + j] >> 4;
+            if (type == LKO_TYPE_Q4_0) {
+                out[b * QK + j] = (float)(lo - 8) * d;
+                out[b * QK + j + 16] = (float)(hi - 8) * d;
+            } else {
+                out[b * QK + j] = (float)lo * d + m;
+                out[b * QK + j + 16] = (float)hi * d + m;
+            }
+        }
+    }
+    return LKO_OK;
+}
+
 /* ---- dot products: core/GGMLComputeOps.kt:43-68, :120-145, :70-115 ------- *
  * sum += (dequantized) * f32, F32, strictly sequential in k.                 */
 static float dot_q8_0(const uint8_t *a, int64_t K, int64_t i, const float *b, int64_t N, int64_t j) {

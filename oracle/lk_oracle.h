@@ -65,6 +65,14 @@ int lko_quantize(int type, const float *x, int64_t n, uint8_t *out);
 /* core/GGMLComputeOps.kt:918-964. n elements, flat order. */
 int lko_dequantize(int type, const uint8_t *blocks, int64_t n, float *out);
 
+/* SURVEY §8f N1 — canonical ggml / GGUF nibble order (byte j = elements j and j+16,
+ * /root/reference/ggml/src/ggml-quants.c:1515-1555) next to the Kotlin accessors' order (byte j = elements 2j and
+ * 2j+1, core/GGMLTypes.kt:647-651).  lko_repack_nibbles permutes the 32 nibbles of every Q4 block between the two
+ * (to_ggml = 1: Kotlin -> ggml, 0: ggml -> Kotlin; Q8_0 is a copy); lko_dequantize_ggml restates dequantize_row_q*.
+ * Both are checked bit for bit against the reference's own compiled C (oracle/_ref, tests/test_ref_ggml.py). */
+int lko_repack_nibbles(int type, const uint8_t *src, int64_t nblocks, uint8_t *dst, int to_ggml);
+int lko_dequantize_ggml(int type, const uint8_t *blocks, int64_t n, float *out);
+
 /* core/GGMLComputeOps.kt:43-68 / :120-145 / :70-115: one dot product,
  * row i of `a` (K/32 blocks per row) with column j of b (ne=[N,K]). */
 float lko_dot(int a_type, const uint8_t *a, int64_t K, int64_t i,

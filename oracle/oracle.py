@@ -53,6 +53,8 @@ def lib() -> C.CDLL:
         L.lko_block_bytes.argtypes = [i32]
         L.lko_quantize.argtypes = [i32, vp, i64, vp]
         L.lko_dequantize.argtypes = [i32, vp, i64, vp]
+        L.lko_repack_nibbles.argtypes = [i32, vp, i64, vp, i32]
+        L.lko_dequantize_ggml.argtypes = [i32, vp, i64, vp]
         L.lko_dot.restype = f32
         L.lko_dot.argtypes = [i32, vp, i64, i64, vp, i64, i64]
         L.lko_matmul.argtypes = [i32, vp, i64, i64, vp, i64, vp]
@@ -103,6 +105,25 @@ def dequantize(type_: int, blocks: np.ndarray, n: int) -> np.ndarray:
     rc = lib().lko_dequantize(type_, _p(blocks), n, _p(out))
     if rc != OK:
         raise ValueError(f"lko_dequantize rc={rc}")
+    return out
+
+
+def repack_nibbles(type_: int, blocks: np.ndarray, to_ggml: bool) -> np.ndarray:
+    """Kotlin accessor order <-> canonical ggml / GGUF order of the Q4 nibbles."""
+    blocks = np.ascontiguousarray(blocks, dtype=np.uint8).reshape(-1)
+    out = np.empty_like(blocks)
+    rc = lib().lko_repack_nibbles(type_, _p(blocks), blocks.size // BLOCK_BYTES[type_], _p(out), int(bool(to_ggml)))
+    if rc != OK:
+        raise ValueError(f"lko_repack_nibbles rc={rc}")
+    return out
+
+
+def dequantize_ggml(type_: int, blocks: np.ndarray, n: int) -> np.ndarray:
+    blocks = np.ascontiguousarray(blocks, dtype=np.uint8)
+    out = np.empty(n, dtype=np.float32)
+    rc = lib().lko_dequantize_ggml(type_, _p(blocks), n, _p(out))
+    if rc != OK:
+        raise ValueError(f"lko_dequantize_ggml rc={rc}")
     return out
 
 
