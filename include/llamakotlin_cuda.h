@@ -205,7 +205,14 @@ LK_API lk_status   lk_capture_end(lk_ctx *ctx, lk_graph **out);
 LK_API lk_status   lk_graph_launch(lk_ctx *ctx, lk_graph *g);
 LK_API lk_status   lk_graph_destroy(lk_graph *g);
 
-/* ---- tuning knobs (bench / tests only; defaults are the product settings) -- */
+/* ---- options ----------------------------------------------------------------
+ * "nibble_order" (product option): how the 32 four-bit quants of a Q4_0 / Q4_1 block lie in its 16
+ *   quant bytes.  0 (default) = the reference's accessors, getQ4_0NibbleWeight / getQ4_1NibbleWeight
+ *   (core/GGMLTypes.kt:627-653, :706-732): byte j = elements 2j (low nibble) and 2j+1 (high).  1 = canonical ggml,
+ *   i.e. what every real GGUF file holds (ggml/src/ggml-quants.c:1515-1555): byte j = elements j (low) and j+16
+ *   (high).  Applies to lk_compute_matmul (all three kernels), the fused / sharded matmuls and lk_compute_dequantize
+ *   of the context; Q8_0 blocks are identical in both orders.
+ * everything else: tuning knobs (bench / tests only; defaults are the product settings) */
 LK_API lk_status   lk_set_option(lk_ctx *ctx, const char *name, int64_t value);
 LK_API int64_t     lk_get_option(lk_ctx *ctx, const char *name);
 

@@ -27,7 +27,7 @@ static inline int grid_for(int64_t work_items, int threads, int max_blocks = 148
 // ---------------------------------------------------------------------------
 template <int TYPE>
 __global__ void __launch_bounds__(256) dequant_kernel(const uint8_t *__restrict__ src, int64_t n,
-                                                      float *__restrict__ dst) {
+                                                      float *__restrict__ dst, int nib) {
     constexpr int BB = block_bytes(TYPE);
     const int64_t ngroups = n / 8;  // n % 32 == 0
     for (int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < ngroups;
@@ -47,8 +47,20 @@ __global__ void __launch_bounds__(256) dequant_kernel(const uint8_t *__restrict_
             }
         } else {
             constexpr int QOFF = (TYPE == T_Q4_0) ? 2 : 4;
-            const uint16_t *q = (const uint16_t *)(p + QOFF + sub * 4);
-            const uint32_t w = (uint32_t)q[0] | ((uint32_t)q[1] << 16);
+            uint32_t w;
+            if (nib) {   // ggml order: elements 8*sub..+7 are the low (sub < 2) / high nibbles of bytes 8*(sub&1)..+7
+                const uint16_t *q = (const uint16_t *)(p + QOFF + (sub & 1) * 8);
+                const int sh = (sub >> 1) * 4;
+                w = 0;
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    const uint32_t two = q[i];
+                    w |= (((two >> sh) & 15u) | (((two >> (8 + sh)) & 15u) << 4)) << (8 * i);
+                }
+            } else {
+                const uint16_t *q = (const uint16_t *)(p + QOFF + sub * 4);
+                w = (uint32_t)q[0] | ((uint32_t)q[1] << 16);
+            }
             float m = 0.f;
             if (TYPE == T_Q4_1) m = h2f(*(const uint16_t *)(p + 2));
 #pragma unroll
@@ -66,14 +78,14 @@ __global__ void __launch_bounds__(256) dequant_kernel(const uint8_t *__restrict_
     }
 }
 
-cudaError_t launch_dequantize(int type, const void *src, int64_t n, float *dst, cudaStream_t s) {
+cudaError_t launch_dequantize(int type, const void *src, int64_t n, float *dst, cudaStream_t s, int nib) {
     if (n == 0) return cudaSuccess;
     const int threads = 256;
     const int grid = grid_for(n / 8, threads);
     switch (type) {
-        case T_Q8_0: dequant_kernel<T_Q8_0><<<grid, threads, 0, s>>>((const uint8_t *)src, n, dst); break;
-        case T_Q4_0: dequant_kernel<T_Q4_0><<<grid, threads, 0, s>>>((const uint8_t *)src, n, dst); break;
-        case T_Q4_1: dequant_kernel<T_Q4_1><<<grid, threads, 0, s>>>((const uint8_t *)src, n, dst); break;
+        case T_Q8_0: dequant_kernel<T_Q8_0><<<grid, threads, 0, s>>>((const uint8_t *)src, n, dst, nib); break;
+        case T_Q4_0: dequant_kernel<T_Q4_0><<<grid, threads, 0, s>>>((const uint8_t *)src, n, dst, nib); break;
+        case T_Q4_1: dequant_kernel<T_Q4_1><<<grid, threads, 0, s>>>((const uint8_t *)src, n, dst, nib); break;
         default: return cudaErrorNotSupported;
     }
     return cudaGetLastError();
@@ -91,7 +103,7 @@ cudaError_t launch_dequantize(int type, const void *src, int64_t n, float *dst, 
 // This is the correctness fallback, not a tuned kernel.
 // ---------------------------------------------------------------------------
 template <int TYPE>
-__device__ __forceinline__ float load_weight(const void *a, int64_t flat) {
+__device__ __forceinline__ float load_weight(const void *a, int64_t flat, int nib) {
     if (TYPE == T_F32) return ((const float *)a)[flat];
     constexpr int BB = block_bytes(TYPE);
     const uint8_t *p = (const uint8_t *)a + (flat >> 5) * BB;
@@ -99,16 +111,16 @@ __device__ __forceinline__ float load_weight(const void *a, int64_t flat) {
     const float d = h2f(*(const uint16_t *)p);
     if (TYPE == T_Q8_0) return __fmul_rn(d, (float)(int8_t)p[2 + item]);
     constexpr int QOFF = (TYPE == T_Q4_0) ? 2 : 4;
-    const uint8_t byte = p[QOFF + (item >> 1)];
-    const float nib = (float)((item & 1) ? (byte >> 4) : (byte & 15));
-    if (TYPE == T_Q4_0) return __fmul_rn(d, __fsub_rn(nib, 8.0f));
-    return __fadd_rn(__fmul_rn(d, nib), h2f(*(const uint16_t *)(p + 2)));
+    const uint8_t byte = p[QOFF + (nib ? (item & 15) : (item >> 1))];      // nib: ggml order (byte j = elements j, j+16)
+    const float q = (float)((nib ? (item >> 4) : (item & 1)) ? (byte >> 4) : (byte & 15));
+    if (TYPE == T_Q4_0) return __fmul_rn(d, __fsub_rn(q, 8.0f));
+    return __fadd_rn(__fmul_rn(d, q), h2f(*(const uint16_t *)(p + 2)));
 }
 
 template <int TYPE>
 __global__ void __launch_bounds__(128) matmul_generic_kernel(const void *__restrict__ a, int64_t K, int64_t M,
                                                              const float *__restrict__ b, int64_t N,
-                                                             float *__restrict__ dst, int64_t ntiles_n) {
+                                                             float *__restrict__ dst, int64_t ntiles_n, int nib) {
     constexpr int TN = 8;
     const int lane = threadIdx.x & 31;
     const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -121,7 +133,7 @@ __global__ void __launch_bounds__(128) matmul_generic_kernel(const void *__restr
 #pragma unroll
         for (int j = 0; j < TN; j++) acc[j] = 0.f;
         for (int64_t k = lane; k < K; k += 32) {
-            const float wv = load_weight<TYPE>(a, i * K + k);
+            const float wv = load_weight<TYPE>(a, i * K + k, nib);
             const float *bp = b + j0 + k * N;
 #pragma unroll
             for (int j = 0; j < TN; j++)
@@ -135,16 +147,16 @@ __global__ void __launch_bounds__(128) matmul_generic_kernel(const void *__restr
 }
 
 cudaError_t launch_matmul_generic(int type, const void *a, int64_t K, int64_t M, const float *b, int64_t N,
-                                  float *dst, cudaStream_t s) {
+                                  float *dst, cudaStream_t s, int nib) {
     if (M == 0 || N == 0) return cudaSuccess;
     const int64_t ntn = (N + 7) / 8;
     const int threads = 128;
     const int grid = grid_for(M * ntn * 32, threads, 148 * 32);
     switch (type) {
-        case T_F32: matmul_generic_kernel<T_F32><<<grid, threads, 0, s>>>(a, K, M, b, N, dst, ntn); break;
-        case T_Q8_0: matmul_generic_kernel<T_Q8_0><<<grid, threads, 0, s>>>(a, K, M, b, N, dst, ntn); break;
-        case T_Q4_0: matmul_generic_kernel<T_Q4_0><<<grid, threads, 0, s>>>(a, K, M, b, N, dst, ntn); break;
-        case T_Q4_1: matmul_generic_kernel<T_Q4_1><<<grid, threads, 0, s>>>(a, K, M, b, N, dst, ntn); break;
+        case T_F32: matmul_generic_kernel<T_F32><<<grid, threads, 0, s>>>(a, K, M, b, N, dst, ntn, nib); break;
+        case T_Q8_0: matmul_generic_kernel<T_Q8_0><<<grid, threads, 0, s>>>(a, K, M, b, N, dst, ntn, nib); break;
+        case T_Q4_0: matmul_generic_kernel<T_Q4_0><<<grid, threads, 0, s>>>(a, K, M, b, N, dst, ntn, nib); break;
+        case T_Q4_1: matmul_generic_kernel<T_Q4_1><<<grid, threads, 0, s>>>(a, K, M, b, N, dst, ntn, nib); break;
         default: return cudaErrorNotSupported;
     }
     return cudaGetLastError();

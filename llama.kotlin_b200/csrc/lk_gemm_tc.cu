@@ -211,7 +211,9 @@ __device__ __forceinline__ uint32_t half_at(const uint32_t *w) {   // 16-bit val
 }
 
 // One block (32 K elements) of a row -> 16 registers of FP16 pairs in K order (the A operand's TMEM row format).
-template <int TYPE, int BP>
+// GG: canonical ggml / GGUF nibble order (byte j = elements j and j+16, ggml/src/ggml-quants.c:1524-1530) instead of the
+// Kotlin accessors' (byte j = elements 2j and 2j+1); Q8_0 blocks are the same in both.
+template <int TYPE, int BP, bool GG>
 __device__ __forceinline__ void dequant_block(const uint8_t *rowp, uint32_t (&out)[16]) {
     constexpr int OFF = BP * block_bytes(TYPE);
     constexpr int S = OFF & 15;
@@ -242,6 +244,18 @@ __device__ __forceinline__ void dequant_block(const uint8_t *rowp, uint32_t (&ou
         for (int c = 0; c < 4; c++) {
             const uint32_t q = word_at<QOFF>(w + c);
             const uint32_t lo = q & 0x0F0F0F0Fu, hi = (q >> 4) & 0x0F0F0F0Fu;
+            if constexpr (GG) {
+                // quant word c: low nibbles = elements 4c..4c+3 -> out[2c], out[2c+1]; high nibbles = elements 16+4c.. -> out[8+2c], out[9+2c]
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const uint32_t src = (j & 2) ? hi : lo;
+                    const uint32_t p = prmt(src, 0u, (j & 1) ? 0xB3A2u : 0x9180u) | 0x64006400u;   // (1024 + b0, 1024 + b1) / (b2, b3)
+                    uint32_t &o = out[((j & 2) ? 8 : 0) + 2 * c + (j & 1)];
+                    if constexpr (TYPE == T_Q4_0) o = h2_mul(h2_sub(p, 0x64086408u), d2);
+                    else o = h2_fma(h2_sub(p, 0x64006400u), d2, m2);
+                }
+                continue;
+            }
             uint32_t *o = out + 4 * c;
 #pragma unroll
             for (int j = 0; j < 4; j++) {
@@ -286,12 +300,12 @@ struct GemmTcParams {
 #endif
 // 64-K step J (0..3) of the current raw chunk: wait for the A stage (32 TMEM columns) to be free, convert this
 // thread's block, store it to the thread's TMEM lane, publish the stage to the MMA thread.
-template <int TYPE, int J>
+template <int TYPE, int J, bool GG>
 __device__ __forceinline__ void dequant_step(const uint8_t *rowp, uint32_t tmem_a_lane, uint64_t *full, uint64_t *a_empty, int qb,
                                              int lane, int stages, int &s, int &it, unsigned long long *dbg_slot = nullptr) {
     uint32_t o[16];
-    if (qb) dequant_block<TYPE, 2 * J + 1>(rowp, o);
-    else dequant_block<TYPE, 2 * J>(rowp, o);
+    if (qb) dequant_block<TYPE, 2 * J + 1, GG>(rowp, o);
+    else dequant_block<TYPE, 2 * J, GG>(rowp, o);
 #ifdef LK_TC_TIMELINE
     const long long tw_ = clock64();
 #endif
@@ -314,7 +328,7 @@ __device__ __forceinline__ void dequant_step(const uint8_t *rowp, uint32_t tmem_
 // the A columns in TMEM are free), b_empty[s] (one commit from every CTA of the cluster: the B stage, which every
 // CTA of the cluster writes a slice of, is free everywhere), raw_full[2] (producer arrive carrying 128 row pieces),
 // raw_empty[2] (8 dequant warps), acc_full (commit).
-template <int TYPE>
+template <int TYPE, bool GG>
 __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const GemmTcParams p, const __grid_constant__ CUtensorMap tm_a) {
     extern __shared__ uint8_t smem_dyn[];
     uint8_t *sm = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);   // SWIZZLE_128B atoms need 1024-byte alignment
@@ -428,13 +442,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const GemmTcPara
             { TC_T0(); mbar_wait(&raw_full[rs], (c >> 1) & 1); if (warp == TC_CTRL_WARPS) TC_ACC(4); }
             const uint8_t *rowp = sRaw + (size_t)(rs * TC_BM + row) * Raw<TYPE>::stride;
             if (TC_DQ_GROUPS == 1 || par == 0) {
-                dequant_step<TYPE, 0>(rowp, tmem_a_lane, full, a_empty, qb, lane, stages, s, it, dq_dbg);
-                if (TC_DQ_GROUPS == 1) dequant_step<TYPE, 1>(rowp, tmem_a_lane, full, a_empty, qb, lane, stages, s, it, dq_dbg);
-                dequant_step<TYPE, 2>(rowp, tmem_a_lane, full, a_empty, qb, lane, stages, s, it, dq_dbg);
-                if (TC_DQ_GROUPS == 1) dequant_step<TYPE, 3>(rowp, tmem_a_lane, full, a_empty, qb, lane, stages, s, it, dq_dbg);
+                dequant_step<TYPE, 0, GG>(rowp, tmem_a_lane, full, a_empty, qb, lane, stages, s, it, dq_dbg);
+                if (TC_DQ_GROUPS == 1) dequant_step<TYPE, 1, GG>(rowp, tmem_a_lane, full, a_empty, qb, lane, stages, s, it, dq_dbg);
+                dequant_step<TYPE, 2, GG>(rowp, tmem_a_lane, full, a_empty, qb, lane, stages, s, it, dq_dbg);
+                if (TC_DQ_GROUPS == 1) dequant_step<TYPE, 3, GG>(rowp, tmem_a_lane, full, a_empty, qb, lane, stages, s, it, dq_dbg);
             } else {
-                dequant_step<TYPE, 1>(rowp, tmem_a_lane, full, a_empty, qb, lane, stages, s, it, dq_dbg);
-                dequant_step<TYPE, 3>(rowp, tmem_a_lane, full, a_empty, qb, lane, stages, s, it, dq_dbg);
+                dequant_step<TYPE, 1, GG>(rowp, tmem_a_lane, full, a_empty, qb, lane, stages, s, it, dq_dbg);
+                dequant_step<TYPE, 3, GG>(rowp, tmem_a_lane, full, a_empty, qb, lane, stages, s, it, dq_dbg);
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&raw_empty[rs]);
@@ -537,14 +551,14 @@ cudaError_t make_weight_map(CUtensorMap *tm, const void *a, int64_t M, int row_b
     return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
 }
 
-template <int TYPE>
+template <int TYPE, bool GG>
 cudaError_t launch_tc(const GemmTcParams &p, int grid, size_t smem, cudaStream_t s) {
     CUtensorMap tm;
     cudaError_t me = make_weight_map(&tm, p.a, p.M, p.row_bytes, Raw<TYPE>::stride);
     if (me != cudaSuccess) return me;
     static bool configured = false;     // per process; the attribute is per function, not per context
     if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<TYPE, GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) return e;
         configured = true;
     }
@@ -560,7 +574,7 @@ cudaError_t launch_tc(const GemmTcParams &p, int grid, size_t smem, cudaStream_t
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, gemm_tc_kernel<TYPE>, p, tm);
+    return cudaLaunchKernelEx(&cfg, gemm_tc_kernel<TYPE, GG>, p, tm);
 }
 
 int raw_stride(int type) { return type == T_Q8_0 ? Raw<T_Q8_0>::stride : type == T_Q4_0 ? Raw<T_Q4_0>::stride : Raw<T_Q4_1>::stride; }
@@ -596,7 +610,7 @@ static int plan_bn(int type, int64_t M, int64_t N, int sm_count, int cs, int *nt
 }
 
 cudaError_t launch_gemm_tc(int type, const void *a, int64_t K, int64_t M, const float *b, int64_t N, float *dst,
-                           void *workspace, int sm_count, int cluster, cudaStream_t s) {
+                           void *workspace, int sm_count, int cluster, cudaStream_t s, int nib) {
     if (type != T_Q8_0 && type != T_Q4_0 && type != T_Q4_1) return cudaErrorNotSupported;
     if (K <= 0 || K % TC_CHUNK_K || N < 16 || M < 1 || M > (1 << 30) || N > (1 << 20) || K > (1 << 24)) return cudaErrorNotSupported;
     if (((uintptr_t)a & 15) || ((uintptr_t)workspace & 1023) || ((uintptr_t)b & 3)) return cudaErrorNotSupported;
@@ -627,9 +641,9 @@ cudaError_t launch_gemm_tc(int type, const void *a, int64_t K, int64_t M, const 
     if (e != cudaSuccess) return e;
     const int grid = (int)((((M + TC_BM - 1) / TC_BM + p.cs - 1) / p.cs) * p.nt * p.cs);
     switch (type) {
-        case T_Q8_0: return launch_tc<T_Q8_0>(p, grid, smem, s);
-        case T_Q4_0: return launch_tc<T_Q4_0>(p, grid, smem, s);
-        default: return launch_tc<T_Q4_1>(p, grid, smem, s);
+        case T_Q8_0: return launch_tc<T_Q8_0, false>(p, grid, smem, s);
+        case T_Q4_0: return nib ? launch_tc<T_Q4_0, true>(p, grid, smem, s) : launch_tc<T_Q4_0, false>(p, grid, smem, s);
+        default: return nib ? launch_tc<T_Q4_1, true>(p, grid, smem, s) : launch_tc<T_Q4_1, false>(p, grid, smem, s);
     }
 }
 

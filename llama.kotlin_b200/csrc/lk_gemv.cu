@@ -186,7 +186,8 @@ struct GemvParams {
     int red_stride;       // floats per row in the partial-sum buffer (ncw * 8 + pad)
     int red_off, x_off, stage_off;  // dynamic smem offsets (bytes)
     int wait_mode;        // GEMV_WAIT_*
-    int npeers;
+    short npeers;
+    short nib;            // Q4 nibble order: 0 Kotlin accessors (byte j = elements 2j, 2j+1), 1 ggml / GGUF (byte j = elements j, j+16)
     int rg_shift;         // rg == 1 << rg_shift (row groups are a power of two: no integer division per stage)
     int64_t row_offset;   // dst index of row 0 (sharded weights)
     unsigned long long *tl;         // timeline buffer (tools/gemv_timeline.cu builds only), else NULL
@@ -330,10 +331,17 @@ __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int ti
             for (int pl = 0; pl < NP; pl++) {
                 const uint32_t s2 = 0x0040u + 0x0011u * pl;   // byte pl of a, byte pl of b
                 uint32_t wds[4];
-                if (TYPE == T_Q8_0) {
+                if (TYPE == T_Q8_0 || p.nib) {
 #pragma unroll
                     for (int j = 0; j < 4; j++)
                         wds[j] = __byte_perm(__byte_perm(T[4 * j], T[4 * j + 1], s2), __byte_perm(T[4 * j + 2], T[4 * j + 3], s2), 0x5410);
+                    if (TYPE != T_Q8_0) {
+                        // ggml order: quant word j holds elements 4j..4j+3 in its low nibbles (plane word 2j) and elements
+                        // 16+4j.. in its high nibbles (plane word 2j+1): my half h fills words 2j + h
+#pragma unroll
+                        for (int j = 0; j < 4; j++) slot[pl * 8 + 2 * j + h] = wds[j];
+                        continue;
+                    }
                 } else {
 #pragma unroll
                     for (int j = 0; j < 2; j++) {   // nibble word j of my half: lo = even elements, hi = odd
@@ -695,7 +703,8 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
 
     GemvParams p = {};
     p.a = (const uint8_t *)a; p.b = b; p.dst = dst;
-    p.npeers = peers.n;
+    p.npeers = (short)peers.n;
+    p.nib = (short)(tune.nibble_order ? 1 : 0);
     for (int i = 0; i < peers.n && i < 8; i++) p.peer[i] = peers.ptr[i];
     p.K = (int)K; p.M = (int)M; p.row_offset = row_offset;
     p.nseg = 1;

@@ -18,12 +18,15 @@ struct GemvTuning {
     int act_planes = 3;     // activation fixed-point planes: 3 = 24-bit (default: as accurate as the F32 reference),
                             // 2 = 16-bit (opt-in: +8 % throughput, error 5e-5 of max instead of 2e-6)
     int row_quant = -1;     // stage rows a multiple of 4 per warp: -1 auto (dependent launches only), 0 never, 1 always
+    int nibble_order = 0;   // Q4 blocks: 0 = the Kotlin accessors' order (byte j = elements 2j, 2j+1, core/GGMLTypes.kt:647-651),
+                            // 1 = canonical ggml / GGUF order (byte j = elements j, j+16, ggml/src/ggml-quants.c:1524-1530)
     int wait_mode = 1;      // 0 wait before the weight prefetch, 1 before reading x, 2 at the end (independent launch)
     void *timeline = nullptr;   // tools/gemv_timeline.cu only: per-CTA %globaltimer stamps
 };
 
 // K0: block dequantisation, bit-exact with dequantizeTensor (core/GGMLComputeOps.kt:918-964).
-cudaError_t launch_dequantize(int type, const void *src, int64_t n, float *dst, cudaStream_t s);
+// nib: nibble order of Q4 blocks (GemvTuning::nibble_order)
+cudaError_t launch_dequantize(int type, const void *src, int64_t n, float *dst, cudaStream_t s, int nib = 0);
 
 // K1: decode GEMV, N == 1, K % 64 == 0.  Returns cudaErrorNotSupported when the
 // shape cannot take the streaming path (caller then uses the generic kernel).
@@ -56,13 +59,13 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
 
 // Generic matmul for any (K, M, N) and a.type in {F32, Q4_0, Q4_1, Q8_0}; reference layouts.
 cudaError_t launch_matmul_generic(int type, const void *a, int64_t K, int64_t M, const float *b, int64_t N,
-                                  float *dst, cudaStream_t s);
+                                  float *dst, cudaStream_t s, int nib = 0);
 
 // K2: tcgen05 prefill GEMM (lk_gemm_tc.cu).  workspace holds the FP16 copy of b.
 size_t gemm_tc_workspace_bytes(int64_t K, int64_t N);
 // cluster: 1, 2 or 4 CTAs (consecutive row tiles) share each activation tile by TMA multicast.
 cudaError_t launch_gemm_tc(int type, const void *a, int64_t K, int64_t M, const float *b, int64_t N, float *dst,
-                           void *workspace, int sm_count, int cluster, cudaStream_t s);
+                           void *workspace, int sm_count, int cluster, cudaStream_t s, int nib = 0);
 
 // K3-K5 + R4
 // pdl: launch with programmatic stream serialization (the kernels wait for their predecessor themselves), so the

@@ -448,13 +448,13 @@ lk_status lk_compute_matmul(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b,
         if ((st = gemm_ws_reserve(ctx, lk::gemm_tc_workspace_bytes(K, N))) != LK_OK) return st;
         chain_other(ctx, dd, (size_t)M * N * 4);
         void *ws = (void *)(((uintptr_t)ctx->gemm_ws + 1023) & ~(uintptr_t)1023);
-        e = lk::launch_gemm_tc(a->type, da, K, M, (const float *)db, N, (float *)dd, ws, ctx->sm_count, ctx->gemm_tc_cluster, ctx->stream);
+        e = lk::launch_gemm_tc(a->type, da, K, M, (const float *)db, N, (float *)dd, ws, ctx->sm_count, ctx->gemm_tc_cluster, ctx->stream, ctx->tune.nibble_order);
         if (e == cudaSuccess) { launched = 2; ctx->gemm_tc_launches++; }   // pack_b_kernel + gemm_tc_kernel
     }
     if (e == cudaErrorNotSupported) {
         cudaGetLastError();
         chain_other(ctx, dd, (size_t)M * N * 4);
-        e = lk::launch_matmul_generic(a->type, da, K, M, (const float *)db, N, (float *)dd, ctx->stream);
+        e = lk::launch_matmul_generic(a->type, da, K, M, (const float *)db, N, (float *)dd, ctx->stream, ctx->tune.nibble_order);
     }
     if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "matmul launch");
     count_launch(ctx, launched);
@@ -558,7 +558,7 @@ lk_status lk_compute_dequantize(lk_ctx *ctx, const lk_tensor *src, const lk_tens
     if ((st = resolve(sc, src, false, &ds, "src")) != LK_OK) return st;
     if ((st = resolve(sc, dst, true, &dd, "dst")) != LK_OK) return st;
     chain_other(ctx, dd, (size_t)n * 4);
-    cudaError_t e = lk::launch_dequantize(src->type, ds, n, (float *)dd, ctx->stream);
+    cudaError_t e = lk::launch_dequantize(src->type, ds, n, (float *)dd, ctx->stream, ctx->tune.nibble_order);
     if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "dequantize launch");
     count_launch(ctx);
     return finish(sc);
@@ -725,6 +725,7 @@ lk_status lk_set_option(lk_ctx *ctx, const char *name, int64_t v) {
     else if (n == "gemv_ctas_per_sm") ctx->tune.ctas_per_sm = (int)v;
     else if (n == "gemv_overlap") ctx->overlap_mode = (int)v;
     else if (n == "gemv_act_planes") ctx->tune.act_planes = (v == 2) ? 2 : 3;
+    else if (n == "nibble_order") ctx->tune.nibble_order = v ? 1 : 0;
     else if (n == "gemm_tc_min_n") ctx->gemm_tc_min_n = (int)v;
     else if (n == "gemm_tc_cluster") ctx->gemm_tc_cluster = (int)v;
     else return fail(ctx, LK_EINVAL_ARG, "lk_set_option: unknown option " + n);
@@ -743,6 +744,7 @@ int64_t lk_get_option(lk_ctx *ctx, const char *name) {
     if (n == "gemv_ctas_per_sm") return ctx->tune.ctas_per_sm;
     if (n == "gemv_overlap") return ctx->overlap_mode;
     if (n == "gemv_act_planes") return ctx->tune.act_planes;
+    if (n == "nibble_order") return ctx->tune.nibble_order;
     if (n == "gemm_tc_min_n") return ctx->gemm_tc_min_n;
     if (n == "gemm_tc_cluster") return ctx->gemm_tc_cluster;
     if (n == "gemm_tc_launches") return ctx->gemm_tc_launches;

@@ -732,3 +732,73 @@ def test_decoder_layer_graph_fused_equals_unfused(O):
         be.free()
     for f, u in zip(*outs):
         assert rel_err(f, u) <= 2e-6
+
+
+# ---- N1: canonical ggml / GGUF nibble order (lk_set_option "nibble_order" = 1) ---------------------------------
+class _ggml_order:
+    def __init__(self, ga):
+        from llama_kotlin_b200.ggml_compute_ops import _ctx_of
+        self.c = _ctx_of(ga)
+
+    def __enter__(self):
+        self.c.set_option("nibble_order", 1)
+
+    def __exit__(self, *a):
+        self.c.set_option("nibble_order", 0)
+
+
+@pytest.mark.parametrize("tname", ["Q4_0", "Q4_1", "Q8_0"])
+def test_dequantize_ggml_order_bit_exact(O, ga, tname):
+    """K0 with nibble_order = 1 against the reference tree's own compiled dequantize_row_q* (oracle/_ref, when the
+    prebuilt library travelled) and against its restatement, on every byte pattern."""
+    from oracle import ref as R
+    gt, ot = QT[tname]
+    n = 32 * 4096
+    raw = np.random.default_rng(6).integers(0, 256, n // 32 * gt.byteSize, dtype=np.uint8)
+    ga.reset()
+    a = ga.allocateTensor(GGMLTensor(gt, [n]))
+    ga.setBytes(a, raw)
+    with _ggml_order(ga):
+        got = lk.dequantizeTensor(ga, a).data
+    assert same_f32_bits(got, O.dequantize_ggml(ot, raw, n))
+    if R.available():
+        assert same_f32_bits(got, R.dequantize(ot, raw, n))
+
+
+@pytest.mark.parametrize("tname", ["Q4_0", "Q4_1"])
+@pytest.mark.parametrize("M,K,N", [(4096, 4096, 1), (11008, 4096, 1), (4096, 11008, 1),   # K1 at the config-2 shapes
+                                   (33, 96, 5),                                            # generic kernel
+                                   (1000, 2048, 512), (300, 512, 72)])                     # K2 (tcgen05)
+def test_matmul_ggml_order_is_bit_identical_to_repacked(O, ga, tname, M, K, N):
+    """The nibble order only changes which activation meets which nibble: the same matrix stored in ggml order and
+    multiplied with nibble_order = 1 gives the bit-identical result of the Kotlin-order path (and so inherits all of
+    its parity tests), in all three kernels."""
+    gt, ot = QT[tname]
+    blocks = O.quantize(ot, synth_weights(1700 + M, M, K))
+    x = synth_acts(1700 + M, K, N)
+    want = host_matmul(ga, gt, blocks, K, M, x, N)
+    gg = O.repack_nibbles(ot, blocks, to_ggml=True)
+    with _ggml_order(ga):
+        got = host_matmul(ga, gt, gg, K, M, x, N)
+        wrong = host_matmul(ga, gt, blocks, K, M, x, N) if N == 1 else None
+    assert same_f32_bits(got, want)
+    assert rel_err(got, O.matmul(ot, blocks, K, M, x, N, nthreads=8)) <= (MATMUL_REL_TOL if N < 16 else 2e-3)
+    if wrong is not None:    # the switch does something: Kotlin-order bytes read in ggml order are a different matrix
+        assert rel_err(wrong, want) > 0.1
+
+
+def test_gemv_ggml_order_against_reference_mul_mat(O, ga):
+    """End to end against the reference tree's compiled ggml_mul_mat on ggml-order blocks produced by ggml's own
+    quantize_row_q4_0_ref (the quantizer real GGUF files were made with).  ggml rounds the activations to Q8_0, so the
+    two agree to ~1e-2; the F32 oracle on the repacked bytes is the tight bar."""
+    from oracle import ref as R
+    if not R.available():
+        pytest.skip("oracle/_ref not shipped")
+    M, K = 4096, 4096
+    w, x = synth_weights(1801, M, K), synth_acts(1801, K)
+    gg = R.quantize(Q4_0, w)
+    with _ggml_order(ga):
+        got = host_matmul(ga, GGMLType.Q4_0, gg, K, M, x, 1)
+    ref_c, _ = R.mul_mat(Q4_0, gg, K, M, x, 1)
+    assert rel_err(got, ref_c) <= 2e-2
+    assert rel_err(got, O.matmul(Q4_0, O.repack_nibbles(Q4_0, gg, to_ggml=False), K, M, x, 1, nthreads=8)) <= MATMUL_REL_TOL
