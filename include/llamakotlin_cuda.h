@@ -50,7 +50,8 @@ enum {
     LK_TYPE_F16  = 1,
     LK_TYPE_Q4_0 = 2,
     LK_TYPE_Q4_1 = 3,
-    LK_TYPE_Q8_0 = 6
+    LK_TYPE_Q8_0 = 6,
+    LK_TYPE_I32  = 17   /* position scalars of the attention ops */
 };
 
 /* Status codes.  The Kotlin wrapper rethrows the same exception class the
@@ -195,6 +196,31 @@ LK_API lk_status   lk_compute_silu(lk_ctx *ctx, const lk_tensor *x, const lk_ten
 LK_API lk_status   lk_compute_silu_mul(lk_ctx *ctx, const lk_tensor *gate, const lk_tensor *up, const lk_tensor *dst);
 /* SOFT_MAX node over ne[0] — LlamaAttention.softmax, model/LlamaAttention.kt:242-288 */
 LK_API lk_status   lk_compute_softmax(lk_ctx *ctx, const lk_tensor *x, const lk_tensor *dst);
+
+/* ---- attention core -------------------------------------------
+ * The position is an I32 tensor with one element (device-resident inside captured sequences), like ggml's `pos`
+ * operand of ROPE, so that one captured layer graph serves every token.  pos == NULL means position 0.           */
+/* SCALE node — LlamaAttention.scale, model/LlamaAttention.kt:166-195: value * factor */
+LK_API lk_status   lk_compute_scale(lk_ctx *ctx, const lk_tensor *x, float factor, const lk_tensor *dst);
+/* (cos, sin) of LlamaAttention.applyRoPE (model/LlamaAttention.kt:53-58) for positions [0, max_pos), computed on the
+ * host in the reference's F64 operations and rounded to F32 as it does: out[(p * head_dim/2 + i/2) * 2 + {0, 1}].
+ * Upload it once as an F32 tensor with ne = [2, head_dim/2, max_pos].                                          */
+LK_API lk_status   lk_rope_table(int32_t head_dim, float rope_theta, int32_t max_pos, float *out);
+/* ROPE node — applyRoPE, model/LlamaAttention.kt:29-72: x.ne[0] = numHeads * headDim, rows = consecutive positions
+ * starting at pos; rotates the pairs (i, i+1) of every head: (x cos - y sin, x sin + y cos), bit-exact.          */
+LK_API lk_status   lk_compute_rope(lk_ctx *ctx, const lk_tensor *x, const lk_tensor *table, const lk_tensor *pos,
+                                   int32_t head_dim, const lk_tensor *dst);
+/* KVCache.updateKey / updateValue copy loops, model/KVCache.kt:47-55, :88-96: rows of src (ne = [headDim, numHeads,
+ * newSeqLen]) go to cache rows pos .. pos+newSeqLen-1 (cache ne = [headDim, numHeads, maxSeq], device-resident).
+ * The `require(currentLength + newSeqLen <= maxSequenceLength)` of :44 is the caller's (it knows the length); the
+ * kernel never writes outside the cache.                                                                         */
+LK_API lk_status   lk_compute_kv_append(lk_ctx *ctx, const lk_tensor *src, const lk_tensor *cache, const lk_tensor *pos);
+/* LlamaAttention.computeAttention for one query position, model/LlamaAttention.kt:104-123, per head:
+ * dst[h] = softmax(scale * q[h] . K[0..pos, h]) . V[0..pos, h], softmax as :242-288; q, dst hold numHeads * headDim
+ * floats, caches ne = [headDim, numHeads, maxSeq]; length = pos + 1 (the row appended for this token included).   */
+LK_API lk_status   lk_compute_attention_decode(lk_ctx *ctx, const lk_tensor *q, const lk_tensor *kcache,
+                                               const lk_tensor *vcache, const lk_tensor *pos, float scale,
+                                               const lk_tensor *dst);
 
 /* ---- op-sequence capture: GGMLBackend.graphCompute, core/GGMLBackend.kt:145 --
  * Between begin and end, device-resident lk_compute_* calls are recorded, not

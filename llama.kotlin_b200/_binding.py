@@ -101,6 +101,11 @@ def lib() -> C.CDLL:
         "lk_compute_silu": (i32, [vp, tp, tp]),
         "lk_compute_silu_mul": (i32, [vp, tp, tp, tp]),
         "lk_compute_softmax": (i32, [vp, tp, tp]),
+        "lk_compute_scale": (i32, [vp, tp, C.c_float, tp]),
+        "lk_rope_table": (i32, [i32, C.c_float, i32, vp]),
+        "lk_compute_rope": (i32, [vp, tp, tp, tp, i32, tp]),
+        "lk_compute_kv_append": (i32, [vp, tp, tp, tp]),
+        "lk_compute_attention_decode": (i32, [vp, tp, tp, tp, tp, C.c_float, tp]),
         "lk_capture_begin": (i32, [vp]),
         "lk_capture_end": (i32, [vp, C.POINTER(vp)]),
         "lk_graph_launch": (i32, [vp, vp]),

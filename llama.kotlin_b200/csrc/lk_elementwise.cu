@@ -166,7 +166,7 @@ cudaError_t launch_matmul_generic(int type, const void *a, int64_t K, int64_t M,
 // R4 add / mul, K4 SiLU and SiLU*up: one pass, 16-byte vector accesses.
 // Algorithmic bytes per element: 12 (binary ops, silu_mul), 8 (silu).
 // ---------------------------------------------------------------------------
-enum { OP_ADD = 0, OP_MUL = 1, OP_SILU = 2, OP_SILU_MUL = 3 };
+enum { OP_ADD = 0, OP_MUL = 1, OP_SILU = 2, OP_SILU_MUL = 3, OP_SCALE = 4 };
 
 // silu(x) = x * (1 / (1 + exp(-x))) — nativeTest core/GGMLComputeOpsTest.kt:491-499.
 // expf (not __expf) and IEEE division keep it within 2 ulp of the libm path.
@@ -177,13 +177,14 @@ __device__ __forceinline__ float ew_apply(float a, float b) {
     if (OP == OP_ADD) return __fadd_rn(a, b);
     if (OP == OP_MUL) return __fmul_rn(a, b);
     if (OP == OP_SILU) return silu1(a);
+    if (OP == OP_SCALE) return __fmul_rn(a, b);     // LlamaAttention.scale: value * factor (model/LlamaAttention.kt:190-191)
     return __fmul_rn(silu1(a), b);
 }
 
 template <int OP>
 __global__ void __launch_bounds__(256) ew_kernel(const float *__restrict__ a, const float *__restrict__ b, int64_t n,
-                                                 float *__restrict__ dst, int vec_ok) {
-    constexpr bool BIN = (OP != OP_SILU);
+                                                 float *__restrict__ dst, int vec_ok, float p0) {
+    constexpr bool BIN = (OP != OP_SILU && OP != OP_SCALE);
     pdl_wait();                // inputs may be the previous kernel's output
     pdl_launch_dependents();   // the next kernel may start its prologue (a GEMV: its weight prefetch) under this one
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -193,7 +194,7 @@ __global__ void __launch_bounds__(256) ew_kernel(const float *__restrict__ a, co
         const int64_t n4 = n / 4;
         for (int64_t i = tid; i < n4; i += nthr) {
             const float4 x = ((const float4 *)a)[i];
-            float4 y = make_float4(0.f, 0.f, 0.f, 0.f);
+            float4 y = make_float4(p0, p0, p0, p0);
             if (BIN) y = ((const float4 *)b)[i];
             float4 r;
             r.x = ew_apply<OP>(x.x, y.x);
@@ -204,20 +205,21 @@ __global__ void __launch_bounds__(256) ew_kernel(const float *__restrict__ a, co
         }
         done = n4 * 4;
     }
-    for (int64_t i = done + tid; i < n; i += nthr) dst[i] = ew_apply<OP>(a[i], BIN ? b[i] : 0.f);
+    for (int64_t i = done + tid; i < n; i += nthr) dst[i] = ew_apply<OP>(a[i], BIN ? b[i] : p0);
 }
 
 template <int OP>
-static cudaError_t launch_ew(const float *a, const float *b, int64_t n, float *dst, cudaStream_t s, bool pdl) {
+static cudaError_t launch_ew(const float *a, const float *b, int64_t n, float *dst, cudaStream_t s, bool pdl, float p0 = 0.f) {
     if (n == 0) return cudaSuccess;
     const uintptr_t al = (uintptr_t)a | (uintptr_t)dst | (uintptr_t)(b ? b : a);
     const int vec_ok = (al & 15) == 0;
     const int threads = 256;
-    return launch_kernel(ew_kernel<OP>, dim3(grid_for((n + 3) / 4, threads)), dim3(threads), 0, s, pdl, a, b, n, dst, vec_ok);
+    return launch_kernel(ew_kernel<OP>, dim3(grid_for((n + 3) / 4, threads)), dim3(threads), 0, s, pdl, a, b, n, dst, vec_ok, p0);
 }
 cudaError_t launch_add(const float *a, const float *b, int64_t n, float *d, cudaStream_t s, bool pdl) { return launch_ew<OP_ADD>(a, b, n, d, s, pdl); }
 cudaError_t launch_mul(const float *a, const float *b, int64_t n, float *d, cudaStream_t s, bool pdl) { return launch_ew<OP_MUL>(a, b, n, d, s, pdl); }
 cudaError_t launch_silu(const float *x, int64_t n, float *d, cudaStream_t s, bool pdl) { return launch_ew<OP_SILU>(x, nullptr, n, d, s, pdl); }
+cudaError_t launch_scale(const float *x, float f, int64_t n, float *d, cudaStream_t s, bool pdl) { return launch_ew<OP_SCALE>(x, nullptr, n, d, s, pdl, f); }
 cudaError_t launch_silu_mul(const float *g, const float *u, int64_t n, float *d, cudaStream_t s, bool pdl) { return launch_ew<OP_SILU_MUL>(g, u, n, d, s, pdl); }
 
 // ---------------------------------------------------------------------------

@@ -77,5 +77,16 @@ cudaError_t launch_silu_mul(const float *g, const float *u, int64_t n, float *ds
 cudaError_t launch_softmax(const float *x, int64_t ne0, int64_t nrows, float *dst, cudaStream_t s, bool pdl = false);
 cudaError_t launch_add(const float *a, const float *b, int64_t n, float *dst, cudaStream_t s, bool pdl = false);
 cudaError_t launch_mul(const float *a, const float *b, int64_t n, float *dst, cudaStream_t s, bool pdl = false);
+cudaError_t launch_scale(const float *x, float factor, int64_t n, float *dst, cudaStream_t s, bool pdl = false);
+
+// N4 attention core (lk_attention.cu).  pos: device int32 scalar (may be NULL = 0 for rope / append).
+cudaError_t launch_rope(const float *x, const float *table, const int32_t *pos, int head_dim, int64_t row, int ntok,
+                        int max_pos, float *dst, cudaStream_t s, bool pdl = false);
+cudaError_t launch_kv_append(const float *src, float *cache, const int32_t *pos, int64_t row, int ntok, int64_t max_seq,
+                             cudaStream_t s, bool pdl = false);
+size_t attn_workspace_bytes(int head_dim, int nheads, int64_t max_seq);
+cudaError_t launch_attn_decode(const float *q, const float *kc, const float *vc, const int32_t *pos, int head_dim,
+                               int nheads, int64_t max_seq, float scale, float *dst, void *workspace, cudaStream_t s,
+                               bool pdl = false);
 
 }  // namespace lk

@@ -87,7 +87,7 @@ extern "C" {
 int32_t lk_abi_version(void) { return LK_ABI_VERSION; }
 
 int32_t lk_type_block_bytes(int32_t type) {
-    if (type == LK_TYPE_F32) return 4;
+    if (type == LK_TYPE_F32 || type == LK_TYPE_I32) return 4;
     if (type == LK_TYPE_F16) return 2;
     return lk::block_bytes(type);
 }
@@ -104,7 +104,7 @@ int64_t lk_tensor_nbytes(const lk_tensor *t) {
     if (!t) return -1;
     const int64_t n = num_elements(t);
     if (is_block_type(t->type)) return n / LK_QK * lk::block_bytes(t->type);
-    if (t->type == LK_TYPE_F32) return n * 4;
+    if (t->type == LK_TYPE_F32 || t->type == LK_TYPE_I32) return n * 4;
     if (t->type == LK_TYPE_F16) return n * 2;
     return -1;
 }
@@ -146,6 +146,8 @@ lk_status lk_ctx_destroy(lk_ctx *ctx) {
     if (ctx->arena) cudaFree(ctx->arena);
     if (ctx->gemm_ws) cudaFree(ctx->gemm_ws);
     for (void *w : ctx->gemm_ws_retired) cudaFree(w);
+    if (ctx->attn_ws) cudaFree(ctx->attn_ws);
+    for (void *w : ctx->attn_ws_retired) cudaFree(w);
     cudaEventDestroy(ctx->ev0);
     cudaEventDestroy(ctx->ev1);
     cudaStreamDestroy(ctx->stream);
@@ -308,6 +310,24 @@ lk_status gemm_ws_reserve(lk_ctx *ctx, size_t need) {
     if (ctx->gemm_ws) ctx->gemm_ws_retired.push_back(ctx->gemm_ws);
     ctx->gemm_ws = w;
     ctx->gemm_ws_size = sz;
+    return LK_OK;
+}
+
+// decode-attention workspace; grows like gemm_ws.  The tickets must be zero before first use: the memset is ordered on
+// the ctx stream (inside a capture it becomes a node of the graph, harmless on replay: tickets are zero between launches)
+lk_status attn_ws_reserve(lk_ctx *ctx, size_t need) {
+    if (need <= ctx->attn_ws_size) return LK_OK;
+    cudaStreamCaptureMode mode = cudaStreamCaptureModeRelaxed;
+    LK_CUDA(ctx, cudaThreadExchangeStreamCaptureMode(&mode));
+    void *w = nullptr;
+    const size_t sz = need + need / 4 + 4096;
+    cudaError_t e = cudaMalloc(&w, sz);
+    cudaThreadExchangeStreamCaptureMode(&mode);
+    if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "attention workspace allocation");
+    if (ctx->attn_ws) ctx->attn_ws_retired.push_back(ctx->attn_ws);
+    ctx->attn_ws = w;
+    ctx->attn_ws_size = sz;
+    LK_CUDA(ctx, cudaMemsetAsync(w, 0, sz, ctx->stream));
     return LK_OK;
 }
 
@@ -663,6 +683,128 @@ lk_status lk_compute_softmax(lk_ctx *ctx, const lk_tensor *x, const lk_tensor *d
     chain_other(ctx, dd, (size_t)n * 4);
     cudaError_t e = lk::launch_softmax((const float *)dx, ne0, ne0 ? n / ne0 : 0, (float *)dd, ctx->stream, op_pdl(ctx, sc));
     if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "softmax launch");
+    count_launch(ctx);
+    return finish(sc);
+}
+
+// ---- N4: attention core (lk_attention.cu) -------------------------------------------------------------------
+lk_status lk_compute_scale(lk_ctx *ctx, const lk_tensor *x, float factor, const lk_tensor *dst) {
+    lk_status st = unary_check(ctx, x, dst, "scale");
+    if (st != LK_OK) return st;
+    LK_CUDA(ctx, cudaSetDevice(ctx->device));
+    OpScope sc(ctx);
+    if ((st = arena_reserve(ctx, host_need({x, dst}))) != LK_OK) return st;
+    void *dx, *dd;
+    if ((st = resolve(sc, x, false, &dx, "x")) != LK_OK) return st;
+    if ((st = resolve(sc, dst, true, &dd, "dst")) != LK_OK) return st;
+    chain_other(ctx, dd, (size_t)num_elements(x) * 4);
+    cudaError_t e = lk::launch_scale((const float *)dx, factor, num_elements(x), (float *)dd, ctx->stream, op_pdl(ctx, sc));
+    if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "scale launch");
+    count_launch(ctx);
+    return finish(sc);
+}
+
+lk_status lk_rope_table(int32_t head_dim, float rope_theta, int32_t max_pos, float *out) {
+    if (!out || head_dim <= 0 || (head_dim & 1) || max_pos <= 0) return LK_EINVAL_ARG;
+    // applyRoPE, model/LlamaAttention.kt:53-58, in the same F64 operations
+    for (int p = 0; p < max_pos; p++)
+        for (int i = 0; i < head_dim; i += 2) {
+            const double exponent = ((double)i / 2.0) / ((double)head_dim / 2.0);
+            const double inv_freq = 1.0 / pow((double)rope_theta, exponent);
+            const double angle = (double)p * inv_freq;
+            float *o = out + ((size_t)p * (head_dim / 2) + i / 2) * 2;
+            o[0] = (float)cos(angle);
+            o[1] = (float)sin(angle);
+        }
+    return LK_OK;
+}
+
+static lk_status pos_check(lk_ctx *ctx, const lk_tensor *pos, const char *name) {
+    if (pos && (pos->type != LK_TYPE_I32 || num_elements(pos) < 1))
+        return fail(ctx, LK_EINVAL_TYPE, std::string(name) + ": position must be an I32 tensor with one element");
+    return LK_OK;
+}
+
+lk_status lk_compute_rope(lk_ctx *ctx, const lk_tensor *x, const lk_tensor *table, const lk_tensor *pos, int32_t head_dim,
+                          const lk_tensor *dst) {
+    lk_status st = unary_check(ctx, x, dst, "rope");
+    if (st != LK_OK) return st;
+    if (!table) return fail(ctx, LK_EINVAL_ARG, "rope: table is NULL");
+    if ((st = pos_check(ctx, pos, "rope")) != LK_OK) return st;
+    const int64_t row = x->ne[0];
+    if (head_dim <= 0 || (head_dim & 1) || row % head_dim) return fail(ctx, LK_EINVAL_DIM, "rope: ne[0] must be a multiple of an even head_dim");
+    if (table->type != LK_TYPE_F32 || table->ne[0] != 2 || table->ne[1] != head_dim / 2 || table->ne[2] < 1)
+        return fail(ctx, LK_EINVAL_DIM, "rope: table must be F32 with ne = [2, head_dim/2, max_pos]");
+    const int64_t ntok = row ? num_elements(x) / row : 0;
+    if (ntok > table->ne[2]) return fail(ctx, LK_EINVAL_DIM, "rope: more tokens than table positions");
+    LK_CUDA(ctx, cudaSetDevice(ctx->device));
+    OpScope sc(ctx);
+    if ((st = arena_reserve(ctx, host_need({x, table, pos, dst}))) != LK_OK) return st;
+    void *dx, *dt, *dp = nullptr, *dd;
+    if ((st = resolve(sc, x, false, &dx, "x")) != LK_OK) return st;
+    if ((st = resolve(sc, table, false, &dt, "table")) != LK_OK) return st;
+    if (pos && (st = resolve(sc, pos, false, &dp, "pos")) != LK_OK) return st;
+    if ((st = resolve(sc, dst, true, &dd, "dst")) != LK_OK) return st;
+    chain_other(ctx, dd, (size_t)num_elements(x) * 4);
+    cudaError_t e = lk::launch_rope((const float *)dx, (const float *)dt, (const int32_t *)dp, head_dim, row, (int)ntok,
+                                    (int)table->ne[2], (float *)dd, ctx->stream, op_pdl(ctx, sc));
+    if (e == cudaErrorNotSupported) return fail(ctx, LK_ENOTIMPL, "rope: unsupported shape / alignment");
+    if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "rope launch");
+    count_launch(ctx);
+    return finish(sc);
+}
+
+lk_status lk_compute_kv_append(lk_ctx *ctx, const lk_tensor *src, const lk_tensor *cache, const lk_tensor *pos) {
+    if (!ctx || !src || !cache) return fail(ctx, LK_EINVAL_ARG, "kvAppend: NULL argument");
+    if (src->type != LK_TYPE_F32 || cache->type != LK_TYPE_F32) return fail(ctx, LK_EINVAL_TYPE, "kvAppend: F32 only");
+    if (!cache->dev_buf) return fail(ctx, LK_EINVAL_ARG, "kvAppend: the cache must be device-resident");
+    lk_status st = pos_check(ctx, pos, "kvAppend");
+    if (st != LK_OK) return st;
+    // KVCache: cache ne = [headDim, numHeads, maxSeq, 1], new rows ne = [headDim, numHeads, newSeqLen, 1] (model/KVCache.kt:19-34, :43)
+    if (src->ne[0] != cache->ne[0] || src->ne[1] != cache->ne[1]) return fail(ctx, LK_EINVAL_DIM, "kvAppend: [headDim, numHeads] differ");
+    const int64_t row = cache->ne[0] * cache->ne[1], ntok = src->ne[2] > 0 ? src->ne[2] : 1, max_seq = cache->ne[2] > 0 ? cache->ne[2] : 1;
+    if (ntok > max_seq) return fail(ctx, LK_EINVAL_DIM, "Sequence length would exceed maximum");    // model/KVCache.kt:44
+    LK_CUDA(ctx, cudaSetDevice(ctx->device));
+    OpScope sc(ctx);
+    if ((st = arena_reserve(ctx, host_need({src, pos}))) != LK_OK) return st;
+    void *ds, *dc, *dp = nullptr;
+    if ((st = resolve(sc, src, false, &ds, "src")) != LK_OK) return st;
+    if ((st = resolve(sc, cache, false, &dc, "cache")) != LK_OK) return st;
+    if (pos && (st = resolve(sc, pos, false, &dp, "pos")) != LK_OK) return st;
+    chain_other(ctx, dc, (size_t)lk_tensor_nbytes(cache));
+    cudaError_t e = lk::launch_kv_append((const float *)ds, (float *)dc, (const int32_t *)dp, row, (int)ntok, max_seq, ctx->stream, op_pdl(ctx, sc));
+    if (e == cudaErrorNotSupported) return fail(ctx, LK_ENOTIMPL, "kvAppend: unsupported shape / alignment");
+    if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "kvAppend launch");
+    count_launch(ctx);
+    return finish(sc);
+}
+
+lk_status lk_compute_attention_decode(lk_ctx *ctx, const lk_tensor *q, const lk_tensor *kcache, const lk_tensor *vcache,
+                                      const lk_tensor *pos, float scale, const lk_tensor *dst) {
+    if (!ctx || !q || !kcache || !vcache || !pos || !dst) return fail(ctx, LK_EINVAL_ARG, "attention: NULL argument");
+    if (q->type != LK_TYPE_F32 || kcache->type != LK_TYPE_F32 || vcache->type != LK_TYPE_F32 || dst->type != LK_TYPE_F32)
+        return fail(ctx, LK_EINVAL_TYPE, "attention: F32 only");
+    lk_status st = pos_check(ctx, pos, "attention");
+    if (st != LK_OK) return st;
+    if (!kcache->dev_buf || !vcache->dev_buf) return fail(ctx, LK_EINVAL_ARG, "attention: the caches must be device-resident");
+    const int64_t D = kcache->ne[0], H = kcache->ne[1], max_seq = kcache->ne[2] > 0 ? kcache->ne[2] : 1;
+    if (!same_shape(kcache, vcache)) return fail(ctx, LK_EINVAL_DIM, "attention: key and value caches differ in shape");
+    if (num_elements(q) != D * H || !same_shape(q, dst)) return fail(ctx, LK_EINVAL_DIM, "attention: q / dst must hold headDim * numHeads elements");
+    LK_CUDA(ctx, cudaSetDevice(ctx->device));
+    OpScope sc(ctx);
+    if ((st = arena_reserve(ctx, host_need({q, pos, dst}))) != LK_OK) return st;
+    if ((st = attn_ws_reserve(ctx, lk::attn_workspace_bytes((int)D, (int)H, max_seq))) != LK_OK) return st;
+    void *dq, *dk, *dv, *dp, *dd;
+    if ((st = resolve(sc, q, false, &dq, "q")) != LK_OK) return st;
+    if ((st = resolve(sc, kcache, false, &dk, "kcache")) != LK_OK) return st;
+    if ((st = resolve(sc, vcache, false, &dv, "vcache")) != LK_OK) return st;
+    if ((st = resolve(sc, pos, false, &dp, "pos")) != LK_OK) return st;
+    if ((st = resolve(sc, dst, true, &dd, "dst")) != LK_OK) return st;
+    chain_other(ctx, dd, (size_t)D * H * 4);
+    cudaError_t e = lk::launch_attn_decode((const float *)dq, (const float *)dk, (const float *)dv, (const int32_t *)dp, (int)D, (int)H,
+                                           max_seq, scale, (float *)dd, ctx->attn_ws, ctx->stream, op_pdl(ctx, sc));
+    if (e == cudaErrorNotSupported) return fail(ctx, LK_ENOTIMPL, "attention: headDim must be 64 or 128, tensors 16-byte aligned");
+    if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "attention launch");
     count_launch(ctx);
     return finish(sc);
 }

@@ -33,6 +33,10 @@ struct lk_ctx {
     void *gemm_ws = nullptr;
     size_t gemm_ws_size = 0;
     std::vector<void *> gemm_ws_retired;   // smaller workspaces that captured graphs may still name; freed with the ctx
+    // decode-attention workspace (split partials + per-head tickets); same retire rule as gemm_ws
+    void *attn_ws = nullptr;
+    size_t attn_ws_size = 0;
+    std::vector<void *> attn_ws_retired;
     int gemm_tc_min_n = 16;                // N >= this takes the tcgen05 GEMM (0 = never); smaller N the generic kernel
     int gemm_tc_cluster = 1;               // CTAs per cluster sharing an activation tile by multicast (1, 2, 4); 1 measured fastest
     int64_t gemm_tc_launches = 0;          // tcgen05 GEMM launches so far (tests assert the path taken)

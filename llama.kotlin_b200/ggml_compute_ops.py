@@ -163,6 +163,97 @@ def computeSoftMax(graphAllocator, context, a, dst) -> None:
     B.check(B.lib().lk_compute_softmax(lk.handle, describe(graphAllocator, a), describe(graphAllocator, dst)), lk.handle)
 
 
+# ---- attention core: LlamaAttention / KVCache, model/LlamaAttention.kt, model/KVCache.kt -------------
+def computeScale(graphAllocator, context, a, factor: float, dst) -> None:
+    """LlamaAttention.scale (model/LlamaAttention.kt:166-195): value * factor."""
+    lk = _ctx_of(graphAllocator)
+    B.check(B.lib().lk_compute_scale(lk.handle, describe(graphAllocator, a), float(factor), describe(graphAllocator, dst)), lk.handle)
+
+
+def ropeTable(headDim: int, ropeTheta: float, maxPositions: int) -> np.ndarray:
+    """(cos, sin) of applyRoPE (model/LlamaAttention.kt:53-58) for positions [0, maxPositions): F32, ne = [2, headDim/2,
+    maxPositions], filled by the library in the reference's F64 operations."""
+    out = np.empty(maxPositions * (headDim // 2) * 2, dtype=np.float32)
+    st = B.lib().lk_rope_table(int(headDim), float(ropeTheta), int(maxPositions), out.ctypes.data)
+    if st != B.LK_OK:
+        raise B.IllegalArgumentException(f"lk_rope_table({headDim}, {ropeTheta}, {maxPositions}) -> {st}")
+    return out
+
+
+def computeRope(graphAllocator, context, a, table, position, headDim: int, dst) -> None:
+    """LlamaAttention.applyRoPE (model/LlamaAttention.kt:29-72); `position` is an I32 tensor (or None = 0)."""
+    lk = _ctx_of(graphAllocator)
+    pos = describe(graphAllocator, position) if position is not None else None
+    B.check(B.lib().lk_compute_rope(lk.handle, describe(graphAllocator, a), describe(graphAllocator, table), pos,
+                                    int(headDim), describe(graphAllocator, dst)), lk.handle)
+
+
+def computeKvAppend(graphAllocator, context, src, cache, position) -> None:
+    """The copy loops of KVCache.updateKey / updateValue (model/KVCache.kt:47-55, :88-96)."""
+    lk = _ctx_of(graphAllocator)
+    pos = describe(graphAllocator, position) if position is not None else None
+    B.check(B.lib().lk_compute_kv_append(lk.handle, describe(graphAllocator, src), describe(graphAllocator, cache), pos), lk.handle)
+
+
+def computeAttentionDecode(graphAllocator, context, q, kcache, vcache, position, scale: float, dst) -> None:
+    """LlamaAttention.computeAttention for one query position (model/LlamaAttention.kt:104-123), heads per the KVCache
+    layout [headDim, numHeads, maxSeq]; length = position + 1."""
+    lk = _ctx_of(graphAllocator)
+    B.check(B.lib().lk_compute_attention_decode(lk.handle, describe(graphAllocator, q), describe(graphAllocator, kcache),
+                                                describe(graphAllocator, vcache), describe(graphAllocator, position),
+                                                float(scale), describe(graphAllocator, dst)), lk.handle)
+
+
+class KVCache:
+    """model/KVCache.kt:9-115 on device memory: keys / values ne = [headDim, numHeads, maxSequenceLength, 1] F32 in the
+    allocator's device buffer, `currentLength` kept by the host (the `require`s of :44 and :85 live here), the
+    position handed to the kernels through a one-element I32 device tensor so that a captured layer graph can be
+    replayed for every token.  Unlike the reference, update* return nothing: the cache itself is what the attention
+    kernel reads (the reference re-copies the whole cache into a fresh tensor per token, :57-71)."""
+
+    def __init__(self, maxSequenceLength: int, numHeads: int, headDim: int):
+        self.maxSequenceLength, self.numHeads, self.headDim = maxSequenceLength, numHeads, headDim
+        self.keys = self.values = self.position = None
+        self.currentLength = 0
+
+    def initialize(self, graphAllocator) -> None:
+        ne = [self.headDim, self.numHeads, self.maxSequenceLength, 1]
+        self.keys = graphAllocator.allocateTensor(GGMLTensor(GGMLType.F32, ne))
+        self.values = graphAllocator.allocateTensor(GGMLTensor(GGMLType.F32, ne))
+        self.position = graphAllocator.allocateTensor(GGMLTensor(GGMLType.I32, [4]))   # 16 bytes; element 0 is read
+        self.currentLength = 0
+        self._ga = graphAllocator
+        self.setPosition(0)
+
+    def setPosition(self, pos: int) -> None:
+        self._ga.setBytes(self.position, np.array([pos, 0, 0, 0], dtype=np.int32))
+
+    def updateKey(self, graphAllocator, newKey: GGMLTensor) -> None:
+        if self.keys is None:
+            raise B.IllegalStateException("KVCache not initialized")
+        n = max(int(newKey.ne[2]), 1)
+        if self.currentLength + n > self.maxSequenceLength:
+            raise B.IllegalArgumentException("Sequence length would exceed maximum")
+        self.setPosition(self.currentLength)
+        computeKvAppend(graphAllocator, None, newKey, self.keys, self.position)
+        self.currentLength += n
+
+    def updateValue(self, graphAllocator, newValue: GGMLTensor) -> None:
+        if self.values is None:
+            raise B.IllegalStateException("KVCache not initialized")
+        n = max(int(newValue.ne[2]), 1)
+        if self.currentLength < n:
+            raise B.IllegalArgumentException("updateKey must be called before updateValue in a step")
+        self.setPosition(self.currentLength - n)
+        computeKvAppend(graphAllocator, None, newValue, self.values, self.position)
+
+    def clear(self) -> None:
+        self.currentLength = 0
+
+    def getCurrentLength(self) -> int:
+        return self.currentLength
+
+
 def dequantizeTensor(graphAllocator, tensor: GGMLTensor) -> GGMLTensor:
     """core/GGMLComputeOps.kt:918 — returns an F32 tensor whose `data` holds the floats
     (like the reference, the result lives in result.data, not in the allocator: SURVEY F8)."""

@@ -96,7 +96,7 @@ class GGMLCudaBackend:
     """GGMLBackend 'CUDA' (registry name as in GGMLBackendRegistry.register, core/GGMLBackend.kt:162-181)."""
 
     _SUPPORTED = {GGMLOp.MUL_MAT, GGMLOp.ADD, GGMLOp.MUL, GGMLOp.RMS_NORM, GGMLOp.SILU, GGMLOp.SOFT_MAX,
-                  GGMLOp.NONE}
+                  GGMLOp.SCALE, GGMLOp.ROPE, GGMLOp.CPY, GGMLOp.FLASH_ATTN, GGMLOp.NONE}
 
     def __init__(self, device: int = 0):
         self.lk = ops.LkContext(device)
@@ -174,6 +174,15 @@ class GGMLCudaBackend:
             ops.computeRmsNorm(ga, None, node.src[0], node.src[1], eps, node)
         elif op == GGMLOp.SOFT_MAX:
             ops.computeSoftMax(ga, None, node.src[0], node)
+        elif op == GGMLOp.SCALE:       # scaleOp: opParams[0] = factor bits (model/GGMLIntegration.kt:118-139)
+            ops.computeScale(ga, None, node.src[0], struct.unpack("<f", struct.pack("<i", int(node.opParams[0])))[0], node)
+        elif op == GGMLOp.ROPE:        # src = x, position (I32), (cos, sin) table; opParams[0] = headDim
+            ops.computeRope(ga, None, node.src[0], node.src[2], node.src[1], int(node.opParams[0]), node)
+        elif op == GGMLOp.CPY:         # KVCache append: src = new rows, cache, position; the node is a view of the cache
+            ops.computeKvAppend(ga, None, node.src[0], node.src[1], node.src[2])
+        elif op == GGMLOp.FLASH_ATTN:  # src = q, key cache, value cache, position; opParams[0] = scale bits
+            ops.computeAttentionDecode(ga, None, node.src[0], node.src[1], node.src[2], node.src[3],
+                                       struct.unpack("<f", struct.pack("<i", int(node.opParams[0])))[0], node)
         else:                          # core/GGMLComputeOps.kt:2548
             raise NotImplementedError(f"Operation {op} not implemented")
 

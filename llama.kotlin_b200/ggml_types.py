@@ -20,10 +20,11 @@ class GGMLType(enum.IntEnum):
     Q4_0 = 2
     Q4_1 = 3
     Q8_0 = 6
+    I32 = 17
 
     @property
     def byteSize(self) -> int:
-        return {0: 4, 1: 2, 2: 18, 3: 20, 6: 34}[int(self)]
+        return {0: 4, 1: 2, 2: 18, 3: 20, 6: 34, 17: 4}[int(self)]
 
     @property
     def isBlockType(self) -> bool:
@@ -38,6 +39,10 @@ class GGMLOp(enum.Enum):
     RMS_NORM = "RMS_NORM"
     SILU = "SILU"
     SOFT_MAX = "SOFT_MAX"
+    SCALE = "SCALE"
+    ROPE = "ROPE"
+    CPY = "CPY"                # here: KVCache append (src[0] = new rows, src[1] = cache, src[2] = position)
+    FLASH_ATTN = "FLASH_ATTN"  # decode attention over the KV cache (src = q, kcache, vcache, position)
     DUP = "DUP"
 
 

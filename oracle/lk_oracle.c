@@ -408,3 +408,54 @@ void lko_softmax(const float *x, int64_t ne0, int64_t nrows, float *dst) {
 /* ---- R4 add / mul: core/GGMLComputeOps.kt:735-759, :811-835 --------------- */
 void lko_add(const float *a, const float *b, int64_t n, float *dst) { for (int64_t i = 0; i < n; i++) dst[i] = a[i] + b[i]; }
 void lko_mul(const float *a, const float *b, int64_t n, float *dst) { for (int64_t i = 0; i < n; i++) dst[i] = a[i] * b[i]; }
+
+/* ---- attention core -------------------------------------------------------------------------- */
+
+/* LlamaAttention.applyRoPE, model/LlamaAttention.kt:29-72.  x: ntok rows of nheads*head_dim floats (ne[0] = hidden,
+ * ne[1] = sequence); pairs (i, i+1) inside each head; angle = (position + s) / theta^((i/2)/(headDim/2)) in F64,
+ * cos / sin rounded to F32, then x*cos - y*sin and x*sin + y*cos in F32 (two products rounded, then one add).  */
+void lko_rope(const float *x, int head_dim, int nheads, int ntok, int position, float theta, float *dst) {
+    const int64_t row = (int64_t)head_dim * nheads;
+    for (int s = 0; s < ntok; s++)
+        for (int h = 0; h < nheads; h++)
+            for (int i = 0; i < head_dim; i += 2) {
+                const int pos = position + s;                                              /* :52 */
+                const double exponent = ((double)i / 2.0) / ((double)head_dim / 2.0);      /* :53 */
+                const double inv_freq = 1.0 / pow((double)theta, exponent);                /* :54 */
+                const double angle = (double)pos * inv_freq;                               /* :55 */
+                const float c = (float)cos(angle), sn = (float)sin(angle);                 /* :56-57 */
+                const float xv = x[s * row + h * head_dim + i], yv = x[s * row + h * head_dim + i + 1];
+                dst[s * row + h * head_dim + i] = xv * c - yv * sn;                        /* :62 */
+                dst[s * row + h * head_dim + i + 1] = xv * sn + yv * c;                    /* :63 */
+            }
+}
+
+/* LlamaAttention.scale, model/LlamaAttention.kt:166-195: value * factor. */
+void lko_scale(const float *x, int64_t n, float factor, float *dst) {
+    for (int64_t i = 0; i < n; i++) dst[i] = x[i] * factor;
+}
+
+/* LlamaAttention.computeAttention for one query row, model/LlamaAttention.kt:104-123, per head of the KVCache layout
+ * [headDim, numHeads, seq] (model/KVCache.kt:19-34): scores = q.K^T as an F32 matmul (sequential k, the F32 x F32
+ * loop of core/GGMLComputeOps.kt:1532-1543), * 1/sqrt(headDim) (:108-109), softmax (:242-288, lko_softmax),
+ * weights.V with the same sequential F32 matmul.  len = rows of the cache in use.                            */
+void lko_attention_decode(const float *q, const float *kc, const float *vc, int64_t len, int head_dim, int nheads,
+                          float *dst) {
+    const int64_t row = (int64_t)head_dim * nheads;
+    const float scale = 1.0f / sqrtf((float)head_dim);
+    float *sc = (float *)malloc((size_t)len * 2 * sizeof(float)), *w = sc + len;
+    for (int h = 0; h < nheads; h++) {
+        for (int64_t s = 0; s < len; s++) {
+            float sum = 0.0f;
+            for (int d = 0; d < head_dim; d++) sum += q[h * head_dim + d] * kc[s * row + h * head_dim + d];
+            sc[s] = sum * scale;
+        }
+        lko_softmax(sc, len, 1, w);
+        for (int d = 0; d < head_dim; d++) {
+            float sum = 0.0f;
+            for (int64_t s = 0; s < len; s++) sum += w[s] * vc[s * row + h * head_dim + d];
+            dst[h * head_dim + d] = sum;
+        }
+    }
+    free(sc);
+}

@@ -114,6 +114,13 @@ void lko_softmax(const float *x, int64_t ne0, int64_t nrows, float *dst);
 void lko_add(const float *a, const float *b, int64_t n, float *dst);
 void lko_mul(const float *a, const float *b, int64_t n, float *dst);
 
+/* N4 attention core — model/LlamaAttention.kt:29-72 (applyRoPE), :166-195 (scale), :104-123 (computeAttention, one
+ * query row, heads per the KVCache layout of model/KVCache.kt:19-34). */
+void lko_rope(const float *x, int head_dim, int nheads, int ntok, int position, float theta, float *dst);
+void lko_scale(const float *x, int64_t n, float factor, float *dst);
+void lko_attention_decode(const float *q, const float *kc, const float *vc, int64_t len, int head_dim, int nheads,
+                          float *dst);
+
 #ifdef __cplusplus
 }
 #endif

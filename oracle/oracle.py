@@ -70,6 +70,12 @@ def lib() -> C.CDLL:
             getattr(L, name).argtypes = [vp, vp, i64, vp]
         L.lko_softmax.restype = None
         L.lko_softmax.argtypes = [vp, i64, i64, vp]
+        L.lko_rope.restype = None
+        L.lko_rope.argtypes = [vp, i32, i32, i32, i32, f32, vp]
+        L.lko_scale.restype = None
+        L.lko_scale.argtypes = [vp, i64, f32, vp]
+        L.lko_attention_decode.restype = None
+        L.lko_attention_decode.argtypes = [vp, vp, vp, i64, i32, i32, vp]
         _lib = L
     return _lib
 
@@ -188,4 +194,25 @@ def softmax(x, ne0: int) -> np.ndarray:
     x = _f32(x).reshape(-1)
     out = np.empty_like(x)
     lib().lko_softmax(_p(x), ne0, x.size // max(ne0, 1), _p(out))
+    return out
+
+
+def rope(x, head_dim: int, nheads: int, position: int, theta: float = 10000.0) -> np.ndarray:
+    x = _f32(x).reshape(-1)
+    out = np.empty_like(x)
+    lib().lko_rope(_p(x), head_dim, nheads, x.size // (head_dim * nheads), position, float(theta), _p(out))
+    return out
+
+
+def scale(x, factor: float) -> np.ndarray:
+    x = _f32(x).reshape(-1)
+    out = np.empty_like(x)
+    lib().lko_scale(_p(x), x.size, float(factor), _p(out))
+    return out
+
+
+def attention_decode(q, kc, vc, length: int, head_dim: int, nheads: int) -> np.ndarray:
+    q, kc, vc = _f32(q).reshape(-1), _f32(kc).reshape(-1), _f32(vc).reshape(-1)
+    out = np.empty(head_dim * nheads, dtype=np.float32)
+    lib().lko_attention_decode(_p(q), _p(kc), _p(vc), length, head_dim, nheads, _p(out))
     return out

@@ -54,6 +54,8 @@ def lib() -> C.CDLL:
         L.ref_quantize.argtypes = [i32, vp, i64, vp]
         L.ref_unary.argtypes = [i32, vp, i64, i64, f32, f32, vp, i32]
         L.ref_mul_mat.argtypes = [i32, vp, i64, i64, vp, i64, vp, i32, i32, C.POINTER(C.c_double)]
+        L.ref_gguf_write.argtypes = [C.c_char_p, i32, i32, C.POINTER(C.c_char_p), C.POINTER(i32), C.POINTER(i64),
+                                     C.POINTER(i64), C.POINTER(vp)]
         L.ref_init()
         _lib = L
     return _lib
@@ -105,3 +107,18 @@ def mul_mat(a_type: int, a: np.ndarray, K: int, M: int, b, N: int, nthreads: int
     if rc != 0:
         raise RuntimeError(f"ref_mul_mat rc={rc}")
     return dst, sec.value
+
+
+def gguf_write(path: str, tensors, alignment: int = 32) -> None:
+    """Writes a GGUF file with the reference tree's own writer (gguf_write_to_file in ggml.c).
+    tensors: list of (name, type id (0 F32, 2 Q4_0, 3 Q4_1, 6 Q8_0), ne0, ne1, payload uint8/float32 array)."""
+    n = len(tensors)
+    keep = [np.ascontiguousarray(t[4]) for t in tensors]
+    names = (C.c_char_p * n)(*[t[0].encode() for t in tensors])
+    types = (C.c_int * n)(*[int(t[1]) for t in tensors])
+    ne0 = (C.c_int64 * n)(*[int(t[2]) for t in tensors])
+    ne1 = (C.c_int64 * n)(*[int(t[3]) for t in tensors])
+    ptrs = (C.c_void_p * n)(*[k.ctypes.data for k in keep])
+    rc = lib().ref_gguf_write(path.encode(), alignment, n, names, types, ne0, ne1, ptrs)
+    if rc != 0:
+        raise RuntimeError(f"ref_gguf_write rc={rc}")

@@ -136,3 +136,36 @@ EXPORT int ref_mul_mat(int a_type, const void *a, int64_t K, int64_t M, const fl
     ggml_free(c);
     return st;
 }
+
+/* A GGUF file written by the reference tree's own writer (gguf_* in ggml.c): KV pairs general.architecture = "llama",
+ * general.name, general.alignment (u32), llama.block_count / embedding_length / rope.freq_base, a string array, plus
+ * `nt` 2-D tensors (type ids as in map_type, payload bytes given).  Fixture generator for the GGUF reader tests. */
+EXPORT int ref_gguf_write(const char *path, int alignment, int nt, const char **names, const int *types,
+                          const int64_t *ne0, const int64_t *ne1, const void **payload) {
+    ref_init();
+    size_t total = 1 << 20;
+    for (int i = 0; i < nt; i++) total += ggml_row_size(map_type(types[i]), ne0[i]) * (size_t)ne1[i] + 4096;
+    struct ggml_init_params ip = {total, NULL, 0};
+    struct ggml_context *c = ggml_init(ip);
+    if (!c) return 1;
+    struct gguf_context *g = gguf_init_empty();
+    gguf_set_val_str(g, "general.architecture", "llama");
+    gguf_set_val_str(g, "general.name", "lk-b200-fixture");
+    gguf_set_val_u32(g, "general.alignment", (uint32_t)alignment);
+    gguf_set_val_u32(g, "llama.block_count", 1);
+    gguf_set_val_u32(g, "llama.embedding_length", (uint32_t)ne0[0]);
+    gguf_set_val_f32(g, "llama.rope.freq_base", 10000.0f);
+    gguf_set_val_bool(g, "lk.flag", 1);
+    const char *toks[3] = {"<s>", "</s>", "hello"};
+    gguf_set_arr_str(g, "tokenizer.ggml.tokens", toks, 3);
+    for (int i = 0; i < nt; i++) {
+        struct ggml_tensor *t = ggml_new_tensor_2d(c, map_type(types[i]), ne0[i], ne1[i]);
+        ggml_set_name(t, names[i]);
+        memcpy(t->data, payload[i], ggml_nbytes(t));
+        gguf_add_tensor(g, t);
+    }
+    gguf_write_to_file(g, path, 0);
+    gguf_free(g);
+    ggml_free(c);
+    return 0;
+}

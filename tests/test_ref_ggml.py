@@ -92,3 +92,24 @@ def test_matmul_against_ggml_mul_mat(O, t):
     want, _ = R.mul_mat(t, O.repack_nibbles(t, qk, to_ggml=True), K, M, x, 1)
     got = O.matmul(t, qk, K, M, x, 1)
     assert np.max(np.abs(got - want)) <= 2e-2 * np.max(np.abs(want))
+
+
+def test_rope_against_ggml_rope(O):
+    # applyRoPE (model/LlamaAttention.kt:29-72): same pairing (2i, 2i+1), frequency base^(-2i/d) and sign as ggml_rope
+    # mode 0; ggml iterates theta in F32 (theta *= theta_scale), hence 1e-5, not bit-exact
+    for H, D, pos in ((4, 128, 7), (2, 64, 1000), (8, 32, 0)):
+        x = synth_acts(31 + pos, H * D)
+        got, want = O.rope(x, D, H, pos), R.unary(R.OP_ROPE, x, D, float(pos), 10000.0)
+        assert np.max(np.abs(got - want)) <= 2e-5 * np.max(np.abs(want))
+
+
+def test_attention_oracle_against_f64(O):
+    rng = np.random.default_rng(1)
+    D, H, L = 64, 3, 77
+    q, kc, vc = (rng.standard_normal(n).astype(np.float32) for n in (D * H, L * D * H, L * D * H))
+    got = O.attention_decode(q, kc, vc, L, D, H)
+    K, V, Q = kc.reshape(L, H, D).astype(np.float64), vc.reshape(L, H, D).astype(np.float64), q.reshape(H, D).astype(np.float64)
+    s = np.einsum("hd,lhd->hl", Q, K) / np.sqrt(D)
+    w = np.exp(s - s.max(1, keepdims=True))
+    w /= w.sum(1, keepdims=True)
+    assert np.max(np.abs(np.einsum("hl,lhd->hd", w, V).reshape(-1) - got)) <= 1e-6

@@ -22,15 +22,19 @@ from bench import BLOCK_BYTES, synth_blocks  # noqa: E402
 
 
 def run(lk, be, qtype: str = "Q4_0", layers: int = 32, steps: int = 50, warmup: int = 5, hidden: int = 4096,
-        ffn: int = 11008, hbm_peak_gbs: float = 0.0, drop_ops=()) -> dict:
+        ffn: int = 11008, hbm_peak_gbs: float = 0.0, drop_ops=(), ctx_len: int = 0, heads: int = 32, max_seq: int = 0) -> dict:
+    """ctx_len > 0: the 18-node layer with RoPE, KV-cache append and decode attention over `ctx_len` cached positions
+    (the token being decoded sits at position ctx_len - 1; the cache rows hold synthetic N(0,1) keys / values)."""
     from llama_kotlin_b200 import GGMLTensor, GGMLType
-    from llama_kotlin_b200.llama_layer import alloc_layer, build_decoder_graph, weight_shapes
+    from llama_kotlin_b200.llama_layer import alloc_attention, alloc_layer, build_decoder_graph, weight_shapes
     gt = getattr(GGMLType, qtype)
     bb = BLOCK_BYTES[qtype]
     shapes = weight_shapes(hidden, ffn)
     wbytes = sum(M * K // 32 * bb for M, K in shapes.values())
     act_bytes = 13 * ffn * 4 * 2
-    ga = lk.GGMLGraphAllocator(be, size=layers * (wbytes + 8 * 256 + 2 * hidden * 4 + act_bytes) + (1 << 20))
+    max_seq = max(max_seq, ctx_len)
+    kv_bytes = 2 * max_seq * hidden * 4 + 1024 if ctx_len else 0
+    ga = lk.GGMLGraphAllocator(be, size=layers * (wbytes + 8 * 256 + 2 * hidden * 4 + 2 * act_bytes + kv_bytes) + (4 << 20))
     rng = np.random.default_rng(4001)
     x = ga.allocateTensor(GGMLTensor(GGMLType.F32, [hidden]))
     ga.setBytes(x, rng.normal(0, 1, hidden).astype(np.float32))
@@ -47,7 +51,17 @@ def run(lk, be, qtype: str = "Q4_0", layers: int = 32, steps: int = 50, warmup: 
         ga.setBytes(L.attn_norm, np.ones(hidden, np.float32))
         ga.setBytes(L.ffn_norm, np.ones(hidden, np.float32))
         stack.append(L)
-    graph, out = build_decoder_graph(ga, stack, x, hidden, ffn)
+    attn = None
+    if ctx_len:
+        attn = alloc_attention(ga, heads, hidden // heads, max_seq, layers)
+        fill = rng.normal(0, 1, ctx_len * hidden).astype(np.float32)
+        rows = GGMLTensor(GGMLType.F32, [ctx_len * hidden])
+        for la in attn:                              # the same synthetic rows in every layer's cache (distinct memory)
+            for c in (la.keys, la.values):
+                rows.bufferId, rows.dataOffset, rows.buffer = c.bufferId, c.dataOffset, c.buffer
+                ga.setBytes(rows, fill)
+        ga.setBytes(attn[0].position, np.array([ctx_len - 1, 0, 0, 0], np.int32))
+    graph, out = build_decoder_graph(ga, stack, x, hidden, ffn, attn=attn)
     if drop_ops:     # timing experiments only (the numbers are then meaningless): how much of the step do these ops cost?
         graph.nodes = [n for n in graph.nodes if n.op.name not in drop_ops]
     lkc = be.lk
@@ -59,14 +73,19 @@ def run(lk, be, qtype: str = "Q4_0", layers: int = 32, steps: int = 50, warmup: 
         be.graphCompute(graph)
     ms = lkc.timer_stop() / steps
     y = ga.getFloats(out)
-    res = {"workload": f"synthetic Llama-2-7B decoder stack, {qtype}, batch 1, one-position context, {layers} layers with "
-                       f"distinct weights ({layers * wbytes / 1e9:.2f} GB > L2), 13 graph nodes per layer",
+    kv_read = 2 * ctx_len * hidden * 4
+    res = {"workload": f"synthetic Llama-2-7B decoder stack, {qtype}, batch 1, " +
+                       (f"RoPE + KV cache + decode attention over {ctx_len} positions ({heads} heads), " if ctx_len else "one-position context, ") +
+                       f"{layers} layers with distinct weights ({layers * wbytes / 1e9:.2f} GB > L2), {18 if ctx_len else 13} graph nodes per layer",
+           "ctx_len": ctx_len, "kv_bytes_read_per_layer": kv_read, "launches_per_token": int(be.lk.get_option("graph_launches")) if False else None,
            "layers": layers, "ms_per_token": ms, "tok_s": 1e3 / ms, "layer_tok_s": layers * 1e3 / ms,
            "us_per_layer": ms * 1e3 / layers, "weight_bytes_per_layer": wbytes,
            "weight_GBps": layers * wbytes / (ms * 1e-3) / 1e9, "finite_output": bool(np.all(np.isfinite(y)))}
+    res.pop("launches_per_token")
+    res["hbm_GBps"] = layers * (wbytes + kv_read) / (ms * 1e-3) / 1e9      # weights + KV rows read per token
     if hbm_peak_gbs:
-        res["hbm_frac"] = res["weight_GBps"] / hbm_peak_gbs
-        res["roofline_tok_s"] = hbm_peak_gbs * 1e9 / (layers * wbytes)
+        res["hbm_frac"] = res["hbm_GBps"] / hbm_peak_gbs
+        res["roofline_tok_s"] = hbm_peak_gbs * 1e9 / (layers * (wbytes + kv_read))
     return res
 
 
@@ -76,6 +95,7 @@ def main():
     ap.add_argument("--layers", type=int, default=32)
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--opt", action="append")
+    ap.add_argument("--ctx", type=int, default=0, help="context length: > 0 runs the layer with RoPE, KV cache and decode attention")
     ap.add_argument("--drop", nargs="*", default=[], help="op names to leave out (timing experiments), e.g. RMS_NORM ADD")
     args = ap.parse_args()
     import llama_kotlin_b200 as lk
@@ -91,7 +111,7 @@ def main():
         peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", 0))
     except Exception:
         pass
-    res = run(lk, be, args.qtype, args.layers, args.steps, hbm_peak_gbs=peak, drop_ops=tuple(args.drop))
+    res = run(lk, be, args.qtype, args.layers, args.steps, hbm_peak_gbs=peak, drop_ops=tuple(args.drop), ctx_len=args.ctx)
     if args.drop:
         res["dropped_ops"] = args.drop
     print(json.dumps(res), flush=True)
