@@ -51,7 +51,17 @@ enum {
     LK_TYPE_Q4_0 = 2,
     LK_TYPE_Q4_1 = 3,
     LK_TYPE_Q8_0 = 6,
-    LK_TYPE_I32  = 17   /* position scalars of the attention ops */
+    /* SURVEY §8f N4 — the reference's own K-quant formats (256-element super-blocks of 84 / 144 / 292 bytes,
+     * core/GGMLTypes.kt:117-122; field meaning per its accessors :737-918 and dot products
+     * core/GGMLComputeOps.kt:152-432, which is NOT ggml's) and BitNet 1.58 (32 ternary weights in 10 bytes,
+     * core/GGMLTypes.kt:127, :920-1000).  lk_compute_matmul (x F32 -> F32) and lk_compute_dequantize accept them;
+     * the fused / sharded / tensor-core entry points do not.  BITNET_1_58 has no GGMLType.fromValue id in the
+     * reference (:145-165); 40 is this ABI's own. */
+    LK_TYPE_Q2_K = 8,
+    LK_TYPE_Q4_K = 10,
+    LK_TYPE_Q8_K = 13,
+    LK_TYPE_I32  = 17,  /* position scalars of the attention ops */
+    LK_TYPE_BITNET_1_58 = 40
 };
 
 /* Status codes.  The Kotlin wrapper rethrows the same exception class the
@@ -101,7 +111,8 @@ typedef struct lk_tensor {
 
 /* ---- context ------------------------------------------------------------ */
 LK_API int32_t     lk_abi_version(void);
-/* bytes per 32-element block (GGMLType.byteSize, core/GGMLTypes.kt:99-133); 4 for F32, 0 if unknown */
+/* bytes per block (GGMLType.byteSize, core/GGMLTypes.kt:99-133: 32-element blocks, 256-element K-quant
+ * super-blocks); 4 for F32, 0 if unknown */
 LK_API int32_t     lk_type_block_bytes(int32_t type);
 /* calculateTensorByteSize, core/GGMLTypes.kt:1136-1190 (n/32*blockBytes for Q types) */
 LK_API int64_t     lk_tensor_nbytes(const lk_tensor *t);

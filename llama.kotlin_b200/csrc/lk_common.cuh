@@ -11,7 +11,8 @@
 
 namespace lk {
 
-enum : int { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q4_1 = 3, T_Q8_0 = 6 };
+enum : int { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q4_1 = 3, T_Q8_0 = 6,
+             T_Q2_K = 8, T_Q4_K = 10, T_Q8_K = 13, T_BITNET_1_58 = 40 };   // N4: the reference's K-quant / BitNet formats (lk_kquants.cu)
 
 __host__ __device__ constexpr int block_bytes(int t) {
     return t == T_Q4_0 ? 18 : t == T_Q4_1 ? 20 : t == T_Q8_0 ? 34 : 0;

@@ -61,6 +61,14 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
 cudaError_t launch_matmul_generic(int type, const void *a, int64_t K, int64_t M, const float *b, int64_t N,
                                   float *dst, cudaStream_t s, int nib = 0);
 
+// N4 (lk_kquants.cu): the reference's Q2_K / Q4_K / Q8_K / BITNET_1_58 formats.  Decode GEMV for N == 1 and rows of
+// whole blocks, the reference's literal block addressing for every other shape; bit-exact dequantize.
+cudaError_t launch_kq_matmul(int type, const void *a, int64_t K, int64_t M, const float *b, int64_t N, float *dst,
+                             int sm_count, cudaStream_t s);
+cudaError_t launch_kq_dequantize(int type, const void *src, int64_t n, float *dst, cudaStream_t s);
+int kq_type_block_bytes(int type);    // 84 / 144 / 292 / 10, else 0
+int kq_type_block_elems(int type);    // 256 / 256 / 256 / 32, else 0
+
 // K2: tcgen05 prefill GEMM (lk_gemm_tc.cu).  workspace holds the FP16 copy of b.
 size_t gemm_tc_workspace_bytes(int64_t K, int64_t N);
 // cluster: 1, 2 or 4 CTAs (consecutive row tiles) share each activation tile by TMA multicast.

@@ -89,10 +89,13 @@ int32_t lk_abi_version(void) { return LK_ABI_VERSION; }
 int32_t lk_type_block_bytes(int32_t type) {
     if (type == LK_TYPE_F32 || type == LK_TYPE_I32) return 4;
     if (type == LK_TYPE_F16) return 2;
+    if (lk::kq_type_block_bytes(type)) return lk::kq_type_block_bytes(type);
     return lk::block_bytes(type);
 }
 
 static bool is_block_type(int t) { return t == LK_TYPE_Q4_0 || t == LK_TYPE_Q4_1 || t == LK_TYPE_Q8_0; }
+// N4: Q2_K / Q4_K / Q8_K / BITNET_1_58 (lk_kquants.cu)
+static bool is_kq_type(int t) { return lk::kq_type_block_bytes(t) != 0; }
 
 static int64_t num_elements(const lk_tensor *t) {
     int64_t n = 1;
@@ -104,6 +107,7 @@ int64_t lk_tensor_nbytes(const lk_tensor *t) {
     if (!t) return -1;
     const int64_t n = num_elements(t);
     if (is_block_type(t->type)) return n / LK_QK * lk::block_bytes(t->type);
+    if (is_kq_type(t->type)) return n / lk::kq_type_block_elems(t->type) * lk::kq_type_block_bytes(t->type);
     if (t->type == LK_TYPE_F32 || t->type == LK_TYPE_I32) return n * 4;
     if (t->type == LK_TYPE_F16) return n * 2;
     return -1;
@@ -430,7 +434,7 @@ lk_status lk_compute_matmul(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b,
     if (K != Kb) return fail(ctx, LK_EINVAL_DIM, "Dim mismatch K: a.ne[0] != b.ne[1]");
     if (dst->ne[0] != N || dst->ne[1] != M)
         return fail(ctx, LK_EINVAL_DIM, "Result tensor dimensions must match expected output size [N, M]");
-    if (is_block_type(a->type) && b->type == LK_TYPE_F32) {
+    if ((is_block_type(a->type) || is_kq_type(a->type)) && b->type == LK_TYPE_F32) {
         if (dst->type != LK_TYPE_F32) return fail(ctx, LK_EINVAL_TYPE, "Result tensor type must be F32 for Q x F32 matmul");
     } else {
         // general fallback, :1530-1565
@@ -441,6 +445,8 @@ lk_status lk_compute_matmul(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b,
     if (M < 0 || K < 0 || N < 0) return fail(ctx, LK_EINVAL_DIM, "negative dimension");
     if (is_block_type(a->type) && ((M * K) % LK_QK) != 0)
         return fail(ctx, LK_EINVAL_DIM, "quantized tensor element count must be a multiple of 32");
+    if (is_kq_type(a->type) && ((M * K) % lk::kq_type_block_elems(a->type)) != 0)   // getNumBlocks, core/GGMLTypes.kt:507-535
+        return fail(ctx, LK_EINVAL_DIM, "quantized tensor element count must be a multiple of the block size");
     LK_CUDA(ctx, cudaSetDevice(ctx->device));
 
     OpScope sc(ctx);
@@ -452,6 +458,13 @@ lk_status lk_compute_matmul(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b,
     if ((st = resolve(sc, dst, true, &dd, "dst")) != LK_OK) return st;
     if (M == 0 || N == 0) return finish(sc);
 
+    if (is_kq_type(a->type)) {     // core/GGMLComputeOps.kt:1481-1513 (+ computeDotProductBitNet158F32, :635-660)
+        chain_other(ctx, dd, (size_t)M * N * 4);
+        const cudaError_t ek = lk::launch_kq_matmul(a->type, da, K, M, (const float *)db, N, (float *)dd, ctx->sm_count, ctx->stream);
+        if (ek != cudaSuccess) return lk::cuda_fail(ctx, ek, "K-quant matmul launch");
+        count_launch(ctx);
+        return finish(sc);
+    }
     cudaError_t e = cudaErrorNotSupported;
     if (N == 1 && is_block_type(a->type)) {
         lk::GemvTuning tune = ctx->tune;
@@ -565,11 +578,13 @@ lk_status lk_compute_matmul_fused(lk_ctx *ctx, const lk_tensor *a, const lk_tens
 
 lk_status lk_compute_dequantize(lk_ctx *ctx, const lk_tensor *src, const lk_tensor *dst) {
     if (!ctx || !src || !dst) return fail(ctx, LK_EINVAL_ARG, "lk_compute_dequantize: NULL argument");
-    if (!is_block_type(src->type)) return fail(ctx, LK_ENOTIMPL, "dequantize: source must be Q4_0, Q4_1 or Q8_0");
+    if (!is_block_type(src->type) && !is_kq_type(src->type))
+        return fail(ctx, LK_ENOTIMPL, "dequantize: source must be Q4_0, Q4_1, Q8_0, Q2_K, Q4_K, Q8_K or BITNET_1_58");
     if (dst->type != LK_TYPE_F32) return fail(ctx, LK_EINVAL_TYPE, "dequantize: destination must be F32");
     const int64_t n = num_elements(src);
     if (n != num_elements(dst)) return fail(ctx, LK_EINVAL_DIM, "dequantize: element counts differ");
-    if (n % LK_QK) return fail(ctx, LK_EINVAL_DIM, "dequantize: element count must be a multiple of 32");
+    if (n % (is_kq_type(src->type) ? lk::kq_type_block_elems(src->type) : LK_QK))
+        return fail(ctx, LK_EINVAL_DIM, "dequantize: element count must be a multiple of the block size");
     LK_CUDA(ctx, cudaSetDevice(ctx->device));
     OpScope sc(ctx);
     lk_status st = arena_reserve(ctx, host_need({src, dst}));
@@ -578,7 +593,8 @@ lk_status lk_compute_dequantize(lk_ctx *ctx, const lk_tensor *src, const lk_tens
     if ((st = resolve(sc, src, false, &ds, "src")) != LK_OK) return st;
     if ((st = resolve(sc, dst, true, &dd, "dst")) != LK_OK) return st;
     chain_other(ctx, dd, (size_t)n * 4);
-    cudaError_t e = lk::launch_dequantize(src->type, ds, n, (float *)dd, ctx->stream, ctx->tune.nibble_order);
+    cudaError_t e = is_kq_type(src->type) ? lk::launch_kq_dequantize(src->type, ds, n, (float *)dd, ctx->stream)
+                                          : lk::launch_dequantize(src->type, ds, n, (float *)dd, ctx->stream, ctx->tune.nibble_order);
     if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "dequantize launch");
     count_launch(ctx);
     return finish(sc);

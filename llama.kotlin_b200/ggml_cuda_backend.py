@@ -205,7 +205,8 @@ class GGMLCudaBackend:
 
         def is_gemv(t):
             return (t.op == GGMLOp.MUL_MAT and not isinstance(t.extra, dict) and t.src[0] is not None and
-                    t.src[0].type.isBlockType and t.src[1] is not None and int(t.src[1].ne[0]) == 1 and
+                    t.src[0].type in (GGMLType.Q4_0, GGMLType.Q4_1, GGMLType.Q8_0) and t.src[1] is not None and
+                    int(t.src[1].ne[0]) == 1 and
                     t.type == GGMLType.F32)
 
         def overlaps(a, b):

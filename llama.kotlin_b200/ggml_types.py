@@ -20,15 +20,24 @@ class GGMLType(enum.IntEnum):
     Q4_0 = 2
     Q4_1 = 3
     Q8_0 = 6
+    Q2_K = 8            # N4: the reference's own K-quant formats (:117-122) and BitNet 1.58 (:127)
+    Q4_K = 10
+    Q8_K = 13
     I32 = 17
+    BITNET_1_58 = 40    # no fromValue id in the reference; this ABI's own (include/llamakotlin_cuda.h)
 
     @property
     def byteSize(self) -> int:
-        return {0: 4, 1: 2, 2: 18, 3: 20, 6: 34, 17: 4}[int(self)]
+        return {0: 4, 1: 2, 2: 18, 3: 20, 6: 34, 8: 84, 10: 144, 13: 292, 17: 4, 40: 10}[int(self)]
+
+    @property
+    def blockElements(self) -> int:
+        """getNumBlocks' elementsPerBlock, core/GGMLTypes.kt:507-520 (1 for plain types)"""
+        return {2: 32, 3: 32, 6: 32, 8: 256, 10: 256, 13: 256, 40: 32}.get(int(self), 1)
 
     @property
     def isBlockType(self) -> bool:
-        return self in (GGMLType.Q4_0, GGMLType.Q4_1, GGMLType.Q8_0)
+        return self.blockElements > 1
 
 
 class GGMLOp(enum.Enum):
@@ -107,7 +116,7 @@ class GGMLTensor:
     def byteSize(self) -> int:
         """calculateTensorByteSize, core/GGMLTypes.kt:1136-1190"""
         n = self.numElements()
-        return n // 32 * self.type.byteSize if self.type.isBlockType else n * self.type.byteSize
+        return n // self.type.blockElements * self.type.byteSize
 
 
 class GGMLCGraph:

@@ -69,7 +69,7 @@ class GGUFTensorInfo:          # gguf/GGUFTypes.kt:42-47
         if self.type is None:
             raise NotImplementedError(f"tensor '{self.name}': type id {self.typeId} is not supported on this device path")
         n = self.numElements()
-        return n // 32 * self.type.byteSize if self.type.isBlockType else n * self.type.byteSize
+        return n // self.type.blockElements * self.type.byteSize
 
 
 class GGUFContext:             # gguf/GGUFContext.kt:6-13

@@ -38,7 +38,11 @@ enum {
     LKO_TYPE_F16  = 1,
     LKO_TYPE_Q4_0 = 2,
     LKO_TYPE_Q4_1 = 3,
-    LKO_TYPE_Q8_0 = 6
+    LKO_TYPE_Q8_0 = 6,
+    LKO_TYPE_Q2_K = 8,
+    LKO_TYPE_Q4_K = 10,
+    LKO_TYPE_Q8_K = 13,
+    LKO_TYPE_BITNET_1_58 = 40   /* no GGMLType.fromValue id in the reference; same id as include/llamakotlin_cuda.h */
 };
 
 /* status codes mirror include/llamakotlin_cuda.h so tests can compare 1:1 */
@@ -120,6 +124,16 @@ void lko_rope(const float *x, int head_dim, int nheads, int ntok, int position, 
 void lko_scale(const float *x, int64_t n, float factor, float *dst);
 void lko_attention_decode(const float *q, const float *kc, const float *vc, int64_t len, int head_dim, int nheads,
                           float *dst);
+
+/* N4 K-quants and BitNet 1.58 (lk_oracle_kq.c): the reference's own Q2_K / Q4_K / Q8_K / BITNET_1_58 formats —
+ * core/GGMLComputeOps.kt:152-432, :635-660 (dot products), :966-1036 + :2125-2368 (dequantize), :1365-1426 +
+ * :1741-2120 (quantizers), :1481-1513 (computeMatMul branches). */
+int   lko_kq_block_bytes(int type);
+int   lko_kq_block_elems(int type);
+int   lko_kq_quantize(int type, const float *x, int64_t n, uint8_t *out);
+int   lko_kq_dequantize(int type, const uint8_t *blocks, int64_t n, float *out);
+float lko_kq_dot(int type, const uint8_t *a, int64_t K, int64_t i, const float *b, int64_t N, int64_t j);
+int   lko_kq_matmul(int type, const uint8_t *a, int64_t K, int64_t M, const float *b, int64_t N, float *dst);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,277 @@
+/*
+ * lk_oracle_kq.c — CPU restatement of the reference's K-quant and BitNet 1.58 paths.
+ *
+ * TEST INFRASTRUCTURE ONLY (see lk_oracle.h).  Parity status: pinned by source citation and by the accuracy
+ * thresholds of nativeTest core/GGMLKQuantAccuracyTest.kt / GGMLBitNet158Test.kt (tests/test_oracle_kquants.py);
+ * the reference holds no byte-level vectors for these formats.
+ *
+ * These are the REFERENCE'S OWN formats, not ggml's: same block sizes as ggml-common.h (84 / 144 / 292 bytes per 256
+ * elements) but a simpler field meaning, and the dot products address blocks as the Kotlin code does — including where
+ * that is irregular (all cited below).  Paths relative to /root/reference/src/nativeMain/kotlin/ai/solace/llamakotlin/.
+ *
+ *   Q2_K  (84 B)  scales[16] @0 (low nibble = scale, high = min), qs[64] @16 (4 x 2 bit per byte), d f16 @80,
+ *                 dmin f16 @82                                      core/GGMLTypes.kt:737-798
+ *   Q4_K  (144 B) d f16 @0, dmin f16 @2, scales[12] @4, qs[128] @16 (low nibble = even element)
+ *                                                                   core/GGMLTypes.kt:819-850, GGMLComputeOps.kt:262-306
+ *   Q8_K  (292 B) d f32 @0, qs int8[256] @4, bsums int16[16] @260   core/GGMLTypes.kt:886-918
+ *   BITNET_1_58 (10 B per 32) d f16 @0, 7 bytes of 5 base-3 digits (digit - 1 = weight) @2, 1 pad byte
+ *                                                                   core/GGMLTypes.kt:920-1000
+ */
+#include "lk_oracle.h"
+
+#include <math.h>
+#include <string.h>
+
+#define QK_K 256
+
+static inline uint16_t get_u16le(const uint8_t *p) { return (uint16_t)(p[0] | ((uint16_t)p[1] << 8)); }
+static inline void put_u16le(uint8_t *p, uint16_t v) { p[0] = (uint8_t)(v & 0xFF); p[1] = (uint8_t)(v >> 8); }
+static inline float get_f32le(const uint8_t *p) { uint32_t u = p[0] | (p[1] << 8) | (p[2] << 16) | ((uint32_t)p[3] << 24); float f; memcpy(&f, &u, 4); return f; }
+static inline void put_f32le(uint8_t *p, float f) { uint32_t u; memcpy(&u, &f, 4); p[0] = u & 0xFF; p[1] = (u >> 8) & 0xFF; p[2] = (u >> 16) & 0xFF; p[3] = (uint8_t)(u >> 24); }
+static inline float kt_max(float a, float b) { if (isnan(a) || isnan(b)) return NAN; return a > b ? a : b; }
+static inline float kt_min(float a, float b) { if (isnan(a) || isnan(b)) return NAN; return a < b ? a : b; }
+static inline int kt_round_clamped(float v, int lo, int hi) {   /* round(v).toInt().coerceIn(lo, hi) */
+    float r = nearbyintf(v);
+    if (isnan(r)) return (0 < lo) ? lo : (0 > hi ? hi : 0);
+    if (r <= (float)lo) return lo;
+    if (r >= (float)hi) return hi;
+    return (int)r;
+}
+
+int lko_kq_block_bytes(int type) {          /* core/GGMLTypes.kt:117-127 */
+    switch (type) {
+        case LKO_TYPE_Q2_K: return 84;
+        case LKO_TYPE_Q4_K: return 144;
+        case LKO_TYPE_Q8_K: return 292;
+        case LKO_TYPE_BITNET_1_58: return 10;
+        default: return 0;
+    }
+}
+int lko_kq_block_elems(int type) {          /* core/GGMLTypes.kt:507-520 */
+    switch (type) {
+        case LKO_TYPE_Q2_K: case LKO_TYPE_Q4_K: case LKO_TYPE_Q8_K: return QK_K;
+        case LKO_TYPE_BITNET_1_58: return 32;
+        default: return 0;
+    }
+}
+
+/* ---- one dequantised element of block `blk` --------------------------------------------------------------------- */
+/* Q2_K: GGMLComputeOps.kt:181-200 (dot), :2125-2155 (dequantize): same arithmetic in both */
+static float q2_k_value(const uint8_t *a, int64_t blk, int item) {
+    const uint8_t *p = a + blk * 84;
+    float d = lko_half_to_float(get_u16le(p + 80)), dmin = lko_half_to_float(get_u16le(p + 82));
+    int sub = item / 16;
+    int sm = p[sub];
+    int qscale = sm & 0x0F, qmin = (sm >> 4) & 0x0F;
+    float scale = ((float)qscale / 15.0f) * d;
+    float min = ((float)qmin * d) + dmin;
+    int byte = p[16 + sub * 4 + (item % 16) / 4];
+    int q = (byte >> (((item % 16) % 4) * 2)) & 0x03;
+    return ((float)q / 3.0f) * scale + min;
+}
+/* Q4_K: GGMLComputeOps.kt:262-306 (dot, whole blocks), :2207-2250 (dequantize).  `partial` = the dot product's
+ * fallback for a trailing K % 256 chunk (:308-336), which adds dmin but not the sub-block min. */
+static float q4_k_value(const uint8_t *a, int64_t blk, int item, int partial) {
+    const uint8_t *p = a + blk * 144;
+    float d = lko_half_to_float(get_u16le(p)), dmin = lko_half_to_float(get_u16le(p + 2));
+    int sub = item / 32;
+    int sb = p[4 + sub];
+    int qscale = sb & 0x3F, qmin_lo = (sb >> 6) & 0x03;
+    int min_off = 4 + sub * 2 + 1;
+    int qmin_hi = (min_off < 4 + 12) ? (p[min_off] & 0x0F) : 0;
+    int qmin = qmin_lo | (qmin_hi << 2);
+    float scale = ((float)qscale / 63.0f) * d;
+    float min = ((float)qmin / 63.0f) * d + dmin;
+    int byte = p[16 + sub * 16 + (item % 32) / 2];
+    int q = ((item % 32) % 2 == 0) ? (byte & 0x0F) : ((byte >> 4) & 0x0F);
+    if (partial) return ((float)q / 15.0f) * scale + dmin;
+    return ((float)q / 15.0f) * scale + min;
+}
+/* Q8_K: GGMLComputeOps.kt:407-413, :2356-2368 */
+static float q8_k_value(const uint8_t *a, int64_t blk, int item) {
+    const uint8_t *p = a + blk * 292;
+    return (float)(int8_t)p[4 + item] * get_f32le(p);
+}
+/* BitNet 1.58: core/GGMLTypes.kt:953-1000 (base-3 digits, most significant first), GGMLComputeOps.kt:653-655.
+ * A byte >= 243 has a leading digit 3; the reference throws IllegalStateException when that digit is read
+ * (position 4): *bad is set and the value is NaN. */
+static float bitnet_value(const uint8_t *a, int64_t blk, int item, int *bad) {
+    const uint8_t *p = a + blk * 10;
+    float scale = lko_half_to_float(get_u16le(p));
+    int byte = p[2 + item / 5], pos = item % 5;
+    static const int pw[5] = {1, 3, 9, 27, 81};
+    int rem = byte, tv[5];
+    for (int i = 4; i >= 0; i--) { tv[i] = rem / pw[i]; rem %= pw[i]; }
+    if (tv[pos] > 2) { if (bad) *bad = 1; return NAN; }
+    return scale * (float)(tv[pos] - 1);
+}
+
+/* ---- dequantizeTensor: GGMLComputeOps.kt:966-1036 --------------------------------------------------------------- */
+int lko_kq_dequantize(int type, const uint8_t *a, int64_t n, float *out) {
+    int be = lko_kq_block_elems(type);
+    if (be == 0) return LKO_ENOTIMPL;
+    if (n % be != 0) return LKO_EINVAL_DIM;
+    int bad = 0;
+    for (int64_t f = 0; f < n; f++) {
+        int64_t blk = f / be; int item = (int)(f % be);
+        switch (type) {
+            case LKO_TYPE_Q2_K: out[f] = q2_k_value(a, blk, item); break;
+            case LKO_TYPE_Q4_K: out[f] = q4_k_value(a, blk, item, 0); break;
+            case LKO_TYPE_Q8_K: out[f] = q8_k_value(a, blk, item); break;
+            default: out[f] = bitnet_value(a, blk, item, &bad); break;
+        }
+    }
+    return bad ? LKO_EBOUNDS : LKO_OK;
+}
+
+/* ---- dot products: GGMLComputeOps.kt:152-236 (Q2_K), :241-341 (Q4_K), :382-432 (Q8_K), :635-660 (BitNet) ---------
+ * K-quants walk K in chunks of 256.  A whole chunk starting at k0 uses block (i*K + k0) / 256 and pairs element e of
+ * THAT block with k0 + e (when K is a multiple of 256 this is the natural layout; otherwise it is what the Kotlin code
+ * does); a trailing partial chunk addresses every element by its flat index.  Sequential F32 sum. */
+float lko_kq_dot(int type, const uint8_t *a, int64_t K, int64_t i, const float *b, int64_t N, int64_t j) {
+    float sum = 0.0f;
+    if (type == LKO_TYPE_BITNET_1_58) {
+        for (int64_t k = 0; k < K; k++) {
+            int64_t flat = i * K + k;
+            sum += bitnet_value(a, flat / 32, (int)(flat % 32), NULL) * b[j + k * N];
+        }
+        return sum;
+    }
+    for (int64_t k0 = 0; k0 < K; k0 += QK_K) {
+        int64_t k1 = (k0 + QK_K < K) ? k0 + QK_K : K;
+        int whole = (k1 - k0) == QK_K;
+        for (int64_t k = k0; k < k1; k++) {
+            int64_t blk; int item;
+            if (whole) { blk = (i * K + k0) / QK_K; item = (int)(k - k0); }
+            else { int64_t flat = i * K + k; blk = flat / QK_K; item = (int)(flat % QK_K); }
+            float w;
+            switch (type) {
+                case LKO_TYPE_Q2_K: w = q2_k_value(a, blk, item); break;
+                case LKO_TYPE_Q4_K: w = q4_k_value(a, blk, item, !whole); break;
+                case LKO_TYPE_Q8_K: w = q8_k_value(a, blk, item); break;
+                default: return NAN;
+            }
+            sum += w * b[j + k * N];
+        }
+    }
+    return sum;
+}
+
+/* computeMatMul's K-quant branches, GGMLComputeOps.kt:1481-1513 (BitNet x F32 has no branch there; the reference
+ * exposes only computeDotProductBitNet158F32 — the same M x N loop is applied to it here). */
+int lko_kq_matmul(int type, const uint8_t *a, int64_t K, int64_t M, const float *b, int64_t N, float *dst) {
+    int be = lko_kq_block_elems(type);
+    if (be == 0) return LKO_ENOTIMPL;
+    if (K < 0 || M < 0 || N < 0 || (M * K) % be != 0) return LKO_EINVAL_DIM;
+    for (int64_t i = 0; i < M; i++)
+        for (int64_t j = 0; j < N; j++)
+            dst[j + i * N] = lko_kq_dot(type, a, K, i, b, N, j);
+    return LKO_OK;
+}
+
+/* ---- quantizers (input generation): GGMLComputeOps.kt:1741-1797 (Q2_K), :1867-1934 (Q4_K), :2087-2120 (Q8_K),
+ * :1365-1426 (BitNet 1.58) ---------------------------------------------------------------------------------------- */
+static void quantize_q2_k_block(const float *v, uint8_t *o) {
+    float mn = INFINITY, mx = -INFINITY;
+    for (int i = 0; i < QK_K; i++) { mn = kt_min(mn, v[i]); mx = kt_max(mx, v[i]); }
+    float range = mx - mn;
+    float d = (range > 0.0f) ? range / 3.0f : 1.0f;
+    float dmin = mn;
+    put_u16le(o + 80, lko_float_to_half(d));
+    put_u16le(o + 82, lko_float_to_half(dmin));
+    for (int sub = 0; sub < 16; sub++) {
+        const float *s = v + sub * 16;
+        float smn = INFINITY, smx = -INFINITY;
+        for (int i = 0; i < 16; i++) { smn = kt_min(smn, s[i]); smx = kt_max(smx, s[i]); }
+        float srange = smx - smn;
+        float scale = (srange > 0.0f) ? srange / 3.0f : 1.0f;
+        int qs = kt_round_clamped((scale / d) * 15.0f, 0, 15);
+        int qm = kt_round_clamped((smn - dmin) / d, 0, 15);
+        o[sub] = (uint8_t)((qs & 0x0F) | ((qm & 0x0F) << 4));
+        for (int i = 0; i < 16; i += 4) {
+            int packed = 0;
+            for (int j = 0; j < 4; j++) {
+                int q = (srange > 0.0f) ? kt_round_clamped(((s[i + j] - smn) / srange) * 3.0f, 0, 3) : 0;
+                packed |= (q & 3) << (j * 2);
+            }
+            o[16 + sub * 4 + i / 4] = (uint8_t)packed;
+        }
+    }
+}
+static void quantize_q4_k_block(const float *v, uint8_t *o) {
+    float mn = INFINITY, mx = -INFINITY;
+    for (int i = 0; i < QK_K; i++) { mn = kt_min(mn, v[i]); mx = kt_max(mx, v[i]); }
+    float range = mx - mn;
+    float d = (range > 0.0f) ? range / 255.0f : 1.0f;
+    float dmin = mn;
+    put_u16le(o, lko_float_to_half(d));
+    put_u16le(o + 2, lko_float_to_half(dmin));
+    for (int sub = 0; sub < 8; sub++) {
+        const float *s = v + sub * 32;
+        float smn = INFINITY, smx = -INFINITY;
+        for (int i = 0; i < 32; i++) { smn = kt_min(smn, s[i]); smx = kt_max(smx, s[i]); }
+        float srange = smx - smn;
+        float scale = (srange > 0.0f) ? srange / 15.0f : 1.0f;
+        int qs = kt_round_clamped((scale / d) * 63.0f, 0, 63);
+        int qm = kt_round_clamped((smn - dmin) / d, 0, 63);
+        /* the two stores overlap across sub-blocks exactly as in the Kotlin code (:1907-1912): later sub-blocks
+         * overwrite bytes written by earlier ones */
+        o[4 + sub] = (uint8_t)((qs & 0x3F) | ((qm & 0x03) << 6));
+        if (sub * 2 + 1 < 12) o[4 + sub * 2 + 1] = (uint8_t)((qm >> 2) & 0x0F);
+        float inv = (scale > 0.0f) ? 1.0f / scale : 0.0f;
+        for (int i = 0; i < 32; i += 2) {
+            int q1 = (srange > 0.0f) ? kt_round_clamped((s[i] - smn) * inv, 0, 15) : 0;
+            int q2 = (srange > 0.0f) ? kt_round_clamped((s[i + 1] - smn) * inv, 0, 15) : 0;
+            o[16 + sub * 16 + i / 2] = (uint8_t)((q1 & 0x0F) | ((q2 & 0x0F) << 4));
+        }
+    }
+}
+static void quantize_q8_k_block(const float *v, uint8_t *o) {
+    float amax = 0.0f;
+    for (int i = 0; i < QK_K; i++) amax = kt_max(amax, fabsf(v[i]));
+    float d = (amax > 0.0f) ? amax / 127.0f : 1.0f;
+    float inv = (d > 0.0f) ? 1.0f / d : 0.0f;
+    put_f32le(o, d);
+    for (int i = 0; i < QK_K; i++) o[4 + i] = (uint8_t)(int8_t)kt_round_clamped(v[i] * inv, -128, 127);
+    for (int g = 0; g < 16; g++) {
+        int sum = 0;
+        for (int i = 0; i < 16; i++) sum += (int8_t)o[4 + g * 16 + i];
+        put_u16le(o + 4 + QK_K + g * 2, (uint16_t)(int16_t)sum);
+    }
+}
+static void quantize_bitnet_block(const float *v, uint8_t *o) {
+    float amax = 0.0f;
+    for (int i = 0; i < 32; i++) amax = kt_max(amax, fabsf(v[i]));
+    float scale = (amax == 0.0f) ? 1.0f : amax;
+    float inv = (scale == 0.0f) ? 0.0f : 1.0f / scale;
+    put_u16le(o, lko_float_to_half(scale));
+    int t[32];
+    for (int i = 0; i < 32; i++) {
+        float nv = v[i] * inv;
+        t[i] = (nv > 0.5f) ? 2 : (nv < -0.5f) ? 0 : 1;
+    }
+    static const int pw[5] = {1, 3, 9, 27, 81};
+    for (int g = 0; g < 7; g++) {
+        int packed = 0;
+        for (int p = 0; p < 5; p++) { int idx = g * 5 + p; if (idx < 32) packed += t[idx] * pw[p]; }
+        o[2 + g] = (uint8_t)packed;
+    }
+    o[9] = 0;
+}
+
+int lko_kq_quantize(int type, const float *x, int64_t n, uint8_t *out) {
+    int be = lko_kq_block_elems(type), bb = lko_kq_block_bytes(type);
+    if (be == 0) return LKO_ENOTIMPL;
+    if (n % be != 0) return LKO_EINVAL_DIM;
+    for (int64_t b = 0; b < n / be; b++) {
+        const float *v = x + b * be; uint8_t *o = out + b * bb;
+        memset(o, 0, (size_t)bb);     /* a fresh ByteArray */
+        switch (type) {
+            case LKO_TYPE_Q2_K: quantize_q2_k_block(v, o); break;
+            case LKO_TYPE_Q4_K: quantize_q4_k_block(v, o); break;
+            case LKO_TYPE_Q8_K: quantize_q8_k_block(v, o); break;
+            default: quantize_bitnet_block(v, o); break;
+        }
+    }
+    return LKO_OK;
+}

@@ -19,17 +19,18 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB_PATH = os.path.join(_HERE, "liblk_oracle.so")
 
 F32, F16, Q4_0, Q4_1, Q8_0 = 0, 1, 2, 3, 6
+Q2_K, Q4_K, Q8_K, BITNET_1_58 = 8, 10, 13, 40
 BLOCK_BYTES = {Q4_0: 18, Q4_1: 20, Q8_0: 34}
+KQ_BLOCK_BYTES = {Q2_K: 84, Q4_K: 144, Q8_K: 292, BITNET_1_58: 10}
+KQ_BLOCK_ELEMS = {Q2_K: 256, Q4_K: 256, Q8_K: 256, BITNET_1_58: 32}
 OK, EINVAL_DIM, EINVAL_TYPE, EBOUNDS, ENOTIMPL = 0, 1, 2, 3, 4
 
 
 def build(force: bool = False) -> str:
     """Compile the oracle with gcc (oracle/Makefile).  Building the checker is
     not using it; __graft_entry__.build() calls this."""
-    src = os.path.join(_HERE, "lk_oracle.c")
-    stale = (not os.path.exists(_LIB_PATH)
-             or os.path.getmtime(_LIB_PATH) < os.path.getmtime(src)
-             or os.path.getmtime(_LIB_PATH) < os.path.getmtime(os.path.join(_HERE, "lk_oracle.h")))
+    srcs = [os.path.join(_HERE, f) for f in ("lk_oracle.c", "lk_oracle_kq.c", "lk_oracle.h", "Makefile")]
+    stale = not os.path.exists(_LIB_PATH) or any(os.path.getmtime(_LIB_PATH) < os.path.getmtime(f) for f in srcs)
     if force or stale:
         subprocess.check_call(["make", "-C", _HERE, "-B", "liblk_oracle.so"],
                               stdout=subprocess.DEVNULL)
@@ -76,6 +77,13 @@ def lib() -> C.CDLL:
         L.lko_scale.argtypes = [vp, i64, f32, vp]
         L.lko_attention_decode.restype = None
         L.lko_attention_decode.argtypes = [vp, vp, vp, i64, i32, i32, vp]
+        L.lko_kq_block_bytes.argtypes = [i32]
+        L.lko_kq_block_elems.argtypes = [i32]
+        L.lko_kq_quantize.argtypes = [i32, vp, i64, vp]
+        L.lko_kq_dequantize.argtypes = [i32, vp, i64, vp]
+        L.lko_kq_dot.restype = f32
+        L.lko_kq_dot.argtypes = [i32, vp, i64, i64, vp, i64, i64]
+        L.lko_kq_matmul.argtypes = [i32, vp, i64, i64, vp, i64, vp]
         _lib = L
     return _lib
 
@@ -216,3 +224,33 @@ def attention_decode(q, kc, vc, length: int, head_dim: int, nheads: int) -> np.n
     out = np.empty(head_dim * nheads, dtype=np.float32)
     lib().lko_attention_decode(_p(q), _p(kc), _p(vc), length, head_dim, nheads, _p(out))
     return out
+
+
+# ---- N4: the reference's K-quant / BitNet 1.58 formats (oracle/lk_oracle_kq.c) ----
+def kq_quantize(type_: int, x) -> np.ndarray:
+    x = _f32(x).reshape(-1)
+    out = np.zeros(x.size // KQ_BLOCK_ELEMS[type_] * KQ_BLOCK_BYTES[type_], dtype=np.uint8)
+    rc = lib().lko_kq_quantize(type_, _p(x), x.size, _p(out))
+    if rc != OK:
+        raise ValueError(f"lko_kq_quantize rc={rc}")
+    return out
+
+
+def kq_dequantize(type_: int, blocks: np.ndarray, n: int) -> np.ndarray:
+    blocks = np.ascontiguousarray(blocks, dtype=np.uint8)
+    out = np.empty(n, dtype=np.float32)
+    rc = lib().lko_kq_dequantize(type_, _p(blocks), n, _p(out))
+    if rc != OK:
+        raise ValueError(f"lko_kq_dequantize rc={rc}")
+    return out
+
+
+def kq_matmul(type_: int, a: np.ndarray, K: int, M: int, b, N: int) -> np.ndarray:
+    a = np.ascontiguousarray(a, dtype=np.uint8)
+    b = _f32(b).reshape(-1)
+    assert b.size == N * K
+    dst = np.zeros(N * M, dtype=np.float32)
+    rc = lib().lko_kq_matmul(type_, _p(a), K, M, _p(b), N, _p(dst))
+    if rc != OK:
+        raise ValueError(f"lko_kq_matmul rc={rc}")
+    return dst
