@@ -232,6 +232,18 @@ LK_API lk_status   lk_compute_kv_append(lk_ctx *ctx, const lk_tensor *src, const
 LK_API lk_status   lk_compute_attention_decode(lk_ctx *ctx, const lk_tensor *q, const lk_tensor *kcache,
                                                const lk_tensor *vcache, const lk_tensor *pos, float scale,
                                                const lk_tensor *dst);
+/* One decode step of LlamaAttention.forward's core in ONE launch, model/LlamaAttention.kt:87-99 + :104-123:
+ * qRope = applyRoPE(q), kRope = applyRoPE(k), kvCache.updateKey(kRope), kvCache.updateValue(v), computeAttention.
+ * q, k, v: this token's projections (numHeads * headDim floats each) before RoPE; table / pos / head_dim as
+ * lk_compute_rope; caches as lk_compute_kv_append (row `pos` of both is written); q_rope_dst / k_rope_dst (optional,
+ * may be NULL) also receive the rotated vectors, so a graph that names them as nodes keeps them valid.  Results are
+ * bit-identical to lk_compute_rope x 2 + lk_compute_kv_append x 2 + lk_compute_attention_decode.  Device-resident
+ * tensors only.                                                                                                    */
+LK_API lk_status   lk_compute_attention_step(lk_ctx *ctx, const lk_tensor *q, const lk_tensor *k, const lk_tensor *v,
+                                             const lk_tensor *table, const lk_tensor *pos, int32_t head_dim,
+                                             const lk_tensor *kcache, const lk_tensor *vcache, float scale,
+                                             const lk_tensor *q_rope_dst, const lk_tensor *k_rope_dst,
+                                             const lk_tensor *dst);
 
 /* ---- op-sequence capture: GGMLBackend.graphCompute, core/GGMLBackend.kt:145 --
  * Between begin and end, device-resident lk_compute_* calls are recorded, not

@@ -8,7 +8,7 @@ from ._binding import (IllegalArgumentException, IllegalStateException,  # noqa:
 from .ggml_alloc import GGMLGraphAllocator  # noqa: F401
 from .ggml_compute_ops import (LkContext, computeAdd, computeMatMul, computeMatMulFused, computeMul,  # noqa: F401
                                computeRmsNorm, computeSilu, computeSiluMul, computeSoftMax,
-                               KVCache, computeAttentionDecode, computeKvAppend, computeRope, computeScale, ropeTable,
+                               KVCache, computeAttentionDecode, computeAttentionStep, computeKvAppend, computeRope, computeScale, ropeTable,
                                default_context, dequantizeTensor)
 from .ggml_cuda_backend import (GGMLCudaBackend, GGMLCudaBuffer, GGMLCudaBufferType)  # noqa: F401
 from .llama_layer import (DecoderLayer, alloc_layer, append_layer_nodes, build_decoder_graph,  # noqa: F401

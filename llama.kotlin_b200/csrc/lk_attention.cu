@@ -93,7 +93,22 @@ struct AttnParams {
     unsigned *tickets;     // per head, zero between launches
     int H, max_seq, chunk, nsplit;
     float scale;
+    // fused decode step (lk_compute_attention_step): q_raw != NULL => q / k / v are this token's projections BEFORE RoPE;
+    // the kernel rotates q and k itself (rope_kernel's arithmetic), appends k / v to the caches at `pos` and, where
+    // asked, also stores the rotated vectors, i.e. it does the work of ROPE, ROPE, CPY, CPY, FLASH_ATTN in one launch
+    const float *q_raw, *k_raw, *v_raw;
+    const float2 *table;   // [table_pos][D/2] (cos, sin)
+    float *q_rope, *k_rope;   // optional stores of the rotated q / k (the graph's intermediates)
+    float *kc_w, *vc_w;    // the caches again, writable
+    int table_pos;
 };
+
+__device__ __forceinline__ float2 rope_pair(float2 v, float2 cs) {   // applyRoPE, model/LlamaAttention.kt:60-66
+    float2 r;
+    r.x = __fsub_rn(__fmul_rn(v.x, cs.x), __fmul_rn(v.y, cs.y));
+    r.y = __fadd_rn(__fmul_rn(v.x, cs.y), __fmul_rn(v.y, cs.x));
+    return r;
+}
 
 template <int D>
 __global__ void __launch_bounds__(ATT_THREADS) attn_decode_kernel(const AttnParams p) {
@@ -101,23 +116,44 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_decode_kernel(const AttnPara
     extern __shared__ float sc[];              // [chunk] scores -> probabilities
     __shared__ float red[ATT_THREADS / 32];
     __shared__ int last_s;
+    __shared__ __align__(16) float qs[D];      // fused step: this head's rotated q
     pdl_wait();
     pdl_launch_dependents();
     const int h = blockIdx.x, j = blockIdx.y;
-    int len = p.pos[0] + 1;
+    const int pos_raw = p.pos[0];
+    int len = pos_raw + 1;
     len = len < 1 ? 1 : (len > p.max_seq ? p.max_seq : len);
     const int nact = (len + p.chunk - 1) / p.chunk;
     if (j >= nact) return;
     const int s0 = j * p.chunk, n = min(p.chunk, len - s0);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const size_t rowf = (size_t)p.H * D;       // floats between consecutive positions
+    const bool fused = p.q_raw != nullptr;
+    if (fused) {
+        constexpr int HALF = D / 2;            // D <= ATT_THREADS: threads [0, HALF) rotate q, [HALF, D) rotate k
+        const int pt = pos_raw < 0 ? 0 : (pos_raw >= p.table_pos ? p.table_pos - 1 : pos_raw);   // as rope_kernel clamps
+        const bool owner = j == nact - 1 && pos_raw >= 0 && pos_raw < p.max_seq;   // my chunk holds this token's row
+        if (tid < HALF) {
+            const float2 r = rope_pair(((const float2 *)(p.q_raw + (size_t)h * D))[tid], p.table[(size_t)pt * HALF + tid]);
+            ((float2 *)qs)[tid] = r;
+            if (j == 0 && p.q_rope) ((float2 *)(p.q_rope + (size_t)h * D))[tid] = r;
+        } else if (tid < D && owner) {
+            const int e = tid - HALF;
+            const float2 r = rope_pair(((const float2 *)(p.k_raw + (size_t)h * D))[e], p.table[(size_t)pt * HALF + e]);
+            ((float2 *)(p.kc_w + (size_t)pos_raw * rowf + (size_t)h * D))[e] = r;     // KVCache.updateKey :47-55
+            if (p.k_rope) ((float2 *)(p.k_rope + (size_t)h * D))[e] = r;
+        }
+        if (owner && tid < D / 4)                                                      // KVCache.updateValue :88-96
+            ((float4 *)(p.vc_w + (size_t)pos_raw * rowf + (size_t)h * D))[tid] = ((const float4 *)(p.v_raw + (size_t)h * D))[tid];
+        __syncthreads();                       // qs, and this CTA's own cache-row stores, are visible to all its threads
+    }
 
     // pass 1: scores.  lane = (row-in-quad r, sub-lane g); row float4 index g + 8*i
     {
         const int g = lane & 7, r = lane >> 3;
         float4 qv[NV];
 #pragma unroll
-        for (int i = 0; i < NV; i++) qv[i] = ((const float4 *)(p.q + (size_t)h * D))[g + 8 * i];
+        for (int i = 0; i < NV; i++) qv[i] = fused ? ((const float4 *)qs)[g + 8 * i] : ((const float4 *)(p.q + (size_t)h * D))[g + 8 * i];
         const float *kbase = p.kc + (size_t)h * D;
 #pragma unroll 2
         for (int tb = warp * 4; tb < n; tb += (ATT_THREADS / 32) * 4) {          // warp-uniform trip count (shuffles inside)
@@ -163,12 +199,19 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_decode_kernel(const AttnPara
     if (tid < D) {
         const float *vcol = p.vc + (size_t)s0 * rowf + (size_t)h * D + tid;
         int t = 0;
-        for (; t + 8 <= n; t += 8) {
-            float v[8];
+        for (; t + 16 <= n; t += 16) {          // 16 rows in flight per thread: a 64-row chunk is 4 DRAM round trips, not 8
+            float v[16];
 #pragma unroll
-            for (int u = 0; u < 8; u++) v[u] = __ldcs(vcol + (size_t)(t + u) * rowf);
+            for (int u = 0; u < 16; u++) v[u] = __ldcs(vcol + (size_t)(t + u) * rowf);
 #pragma unroll
-            for (int u = 0; u < 8; u++) acc = fmaf(sc[t + u], v[u], acc);
+            for (int u = 0; u < 16; u++) acc = fmaf(sc[t + u], v[u], acc);
+        }
+        for (; t + 4 <= n; t += 4) {
+            float v[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) v[u] = __ldcs(vcol + (size_t)(t + u) * rowf);
+#pragma unroll
+            for (int u = 0; u < 4; u++) acc = fmaf(sc[t + u], v[u], acc);
         }
         for (; t < n; t++) acc = fmaf(sc[t], __ldcs(vcol + (size_t)t * rowf), acc);
     }
@@ -219,11 +262,18 @@ size_t attn_workspace_bytes(int head_dim, int nheads, int64_t max_seq) {
 
 cudaError_t launch_attn_decode(const float *q, const float *kc, const float *vc, const int32_t *pos, int head_dim,
                                int nheads, int64_t max_seq, float scale, float *dst, void *workspace, cudaStream_t s,
-                               bool pdl) {
+                               bool pdl, const AttnStep *step) {
     if (nheads <= 0 || max_seq <= 0 || max_seq > (1 << 24)) return cudaErrorNotSupported;
     if (head_dim != 64 && head_dim != 128) return cudaErrorNotSupported;
     if ((((uintptr_t)q | (uintptr_t)kc | (uintptr_t)vc | (uintptr_t)dst) & 15) || ((uintptr_t)workspace & 255)) return cudaErrorNotSupported;
-    AttnParams p;
+    AttnParams p = {};
+    if (step) {
+        if ((((uintptr_t)step->k_raw | (uintptr_t)step->v_raw | (uintptr_t)step->q_rope | (uintptr_t)step->k_rope) & 15) ||
+            ((uintptr_t)step->table & 7) || step->table_pos <= 0)
+            return cudaErrorNotSupported;
+        p.q_raw = q; p.k_raw = step->k_raw; p.v_raw = step->v_raw; p.table = (const float2 *)step->table;
+        p.q_rope = step->q_rope; p.k_rope = step->k_rope; p.kc_w = (float *)kc; p.vc_w = (float *)vc; p.table_pos = step->table_pos;
+    }
     p.q = q; p.kc = kc; p.vc = vc; p.pos = pos; p.dst = dst;
     p.H = nheads; p.max_seq = (int)max_seq; p.scale = scale;
     attn_plan(max_seq, &p.chunk, &p.nsplit);

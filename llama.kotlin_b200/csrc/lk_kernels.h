@@ -93,8 +93,16 @@ cudaError_t launch_rope(const float *x, const float *table, const int32_t *pos, 
 cudaError_t launch_kv_append(const float *src, float *cache, const int32_t *pos, int64_t row, int ntok, int64_t max_seq,
                              cudaStream_t s, bool pdl = false);
 size_t attn_workspace_bytes(int head_dim, int nheads, int64_t max_seq);
+// step != NULL: the fused decode step — q (and step->k_raw, v_raw) are this token's projections before RoPE; the kernel
+// rotates q / k, appends k / v to the caches at pos (kc / vc are written) and attends, in one launch.
+struct AttnStep {
+    const float *k_raw, *v_raw;
+    const float *table;       // [table_pos][head_dim/2][2] (cos, sin), lk_rope_table
+    int table_pos;
+    float *q_rope, *k_rope;   // optional: where the rotated q / k are also stored
+};
 cudaError_t launch_attn_decode(const float *q, const float *kc, const float *vc, const int32_t *pos, int head_dim,
                                int nheads, int64_t max_seq, float scale, float *dst, void *workspace, cudaStream_t s,
-                               bool pdl = false);
+                               bool pdl = false, const AttnStep *step = nullptr);
 
 }  // namespace lk

@@ -202,7 +202,7 @@ __global__ void __launch_bounds__(256, 4) kq_gemv_kernel(const uint8_t *__restri
 #pragma unroll
         for (int r = 0; r < R; r++) acc[r] = 0.f;
         if (TYPE == T_BITNET_1_58) {
-            for (int64_t c = w * 32 + lane; c < nb; c += 256) {
+            for (int c = w * 32 + lane; c < (int)nb; c += 256) {
                 float xv[32], sx = 0.f;
 #pragma unroll
                 for (int q = 0; q < 8; q++) {
@@ -214,8 +214,8 @@ __global__ void __launch_bounds__(256, 4) kq_gemv_kernel(const uint8_t *__restri
                 for (int r = 0; r < R; r++) acc[r] += bitnet_lane_dot(row[r] + c * BB, xv, sx);
             }
         } else {
-#pragma unroll 2
-            for (int64_t c = w; c < nb; c += 8) {
+#pragma unroll 1      // 4 rows = 4 independent load streams per step already; unrolling further spills at 64 registers
+            for (int c = w; c < (int)nb; c += 8) {
                 const float4 x0 = __ldg((const float4 *)(b + c * 256 + lane * 8)), x1 = __ldg((const float4 *)(b + c * 256 + lane * 8 + 4));
                 const float xv[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
                 const float sx = ((x0.x + x0.y) + (x0.z + x0.w)) + ((x1.x + x1.y) + (x1.z + x1.w));

@@ -825,6 +825,58 @@ lk_status lk_compute_attention_decode(lk_ctx *ctx, const lk_tensor *q, const lk_
     return finish(sc);
 }
 
+lk_status lk_compute_attention_step(lk_ctx *ctx, const lk_tensor *q, const lk_tensor *k, const lk_tensor *v,
+                                    const lk_tensor *table, const lk_tensor *pos, int32_t head_dim, const lk_tensor *kcache,
+                                    const lk_tensor *vcache, float scale, const lk_tensor *q_rope_dst,
+                                    const lk_tensor *k_rope_dst, const lk_tensor *dst) {
+    if (!ctx || !q || !k || !v || !table || !pos || !kcache || !vcache || !dst) return fail(ctx, LK_EINVAL_ARG, "attentionStep: NULL argument");
+    const lk_tensor *all[] = {q, k, v, table, kcache, vcache, q_rope_dst, k_rope_dst, dst};
+    for (const lk_tensor *t : all) {
+        if (!t) continue;
+        if (t->type != LK_TYPE_F32) return fail(ctx, LK_EINVAL_TYPE, "attentionStep: F32 only");
+        if (!t->dev_buf) return fail(ctx, LK_ENOTIMPL, "attentionStep: device-resident tensors only");
+    }
+    lk_status st = pos_check(ctx, pos, "attentionStep");
+    if (st != LK_OK) return st;
+    if (!pos->dev_buf) return fail(ctx, LK_ENOTIMPL, "attentionStep: device-resident tensors only");
+    const int64_t D = kcache->ne[0], H = kcache->ne[1], max_seq = kcache->ne[2] > 0 ? kcache->ne[2] : 1;
+    if (!same_shape(kcache, vcache)) return fail(ctx, LK_EINVAL_DIM, "attentionStep: key and value caches differ in shape");
+    if (head_dim != D) return fail(ctx, LK_EINVAL_DIM, "attentionStep: head_dim must equal the caches' ne[0]");
+    for (const lk_tensor *t : {q, k, v, q_rope_dst, k_rope_dst, dst})
+        if (t && num_elements(t) != D * H) return fail(ctx, LK_EINVAL_DIM, "attentionStep: vectors must hold headDim * numHeads elements");
+    if (table->ne[0] != 2 || table->ne[1] != head_dim / 2 || table->ne[2] < 1)
+        return fail(ctx, LK_EINVAL_DIM, "attentionStep: table must be F32 with ne = [2, head_dim/2, max_pos]");
+    LK_CUDA(ctx, cudaSetDevice(ctx->device));
+    OpScope sc(ctx);
+    if ((st = attn_ws_reserve(ctx, lk::attn_workspace_bytes((int)D, (int)H, max_seq))) != LK_OK) return st;
+    void *dq, *dk, *dv, *dt, *dp, *dkc, *dvc, *dqr = nullptr, *dkr = nullptr, *dd;
+    if ((st = resolve(sc, q, false, &dq, "q")) != LK_OK) return st;
+    if ((st = resolve(sc, k, false, &dk, "k")) != LK_OK) return st;
+    if ((st = resolve(sc, v, false, &dv, "v")) != LK_OK) return st;
+    if ((st = resolve(sc, table, false, &dt, "table")) != LK_OK) return st;
+    if ((st = resolve(sc, pos, false, &dp, "pos")) != LK_OK) return st;
+    if ((st = resolve(sc, kcache, false, &dkc, "kcache")) != LK_OK) return st;
+    if ((st = resolve(sc, vcache, false, &dvc, "vcache")) != LK_OK) return st;
+    if (q_rope_dst && (st = resolve(sc, q_rope_dst, true, &dqr, "q_rope_dst")) != LK_OK) return st;
+    if (k_rope_dst && (st = resolve(sc, k_rope_dst, true, &dkr, "k_rope_dst")) != LK_OK) return st;
+    if ((st = resolve(sc, dst, true, &dd, "dst")) != LK_OK) return st;
+    // a fully serialising op for the GEMV chain bookkeeping: it writes dst, both rotated vectors and a row of each cache
+    chain_other(ctx, dd, (size_t)D * H * 4);
+    chain_other(ctx, dkc, (size_t)lk_tensor_nbytes(kcache));
+    chain_other(ctx, dvc, (size_t)lk_tensor_nbytes(vcache));
+    if (dqr) chain_other(ctx, dqr, (size_t)D * H * 4);
+    if (dkr) chain_other(ctx, dkr, (size_t)D * H * 4);
+    lk::AttnStep step;
+    step.k_raw = (const float *)dk; step.v_raw = (const float *)dv; step.table = (const float *)dt;
+    step.table_pos = (int)table->ne[2]; step.q_rope = (float *)dqr; step.k_rope = (float *)dkr;
+    cudaError_t e = lk::launch_attn_decode((const float *)dq, (const float *)dkc, (const float *)dvc, (const int32_t *)dp, (int)D, (int)H,
+                                           max_seq, scale, (float *)dd, ctx->attn_ws, ctx->stream, op_pdl(ctx, sc), &step);
+    if (e == cudaErrorNotSupported) return fail(ctx, LK_ENOTIMPL, "attentionStep: headDim must be 64 or 128, tensors 16-byte aligned");
+    if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "attentionStep launch");
+    count_launch(ctx);
+    return finish(sc);
+}
+
 // ---- op-sequence capture -----------------------------------------------------
 lk_status lk_capture_begin(lk_ctx *ctx) {
     if (!ctx) return fail(nullptr, LK_EINVAL_ARG, "lk_capture_begin: ctx is NULL");

@@ -204,6 +204,17 @@ def computeAttentionDecode(graphAllocator, context, q, kcache, vcache, position,
                                                 float(scale), describe(graphAllocator, dst)), lk.handle)
 
 
+def computeAttentionStep(graphAllocator, context, q, k, v, table, position, headDim: int, kcache, vcache, scale: float,
+                         dst, qRopeDst=None, kRopeDst=None) -> None:
+    """One decode step of LlamaAttention.forward's core in one launch (model/LlamaAttention.kt:87-99, :104-123):
+    applyRoPE(q), applyRoPE(k), KVCache.updateKey / updateValue at `position`, computeAttention.  Bit-identical to
+    computeRope x 2 + computeKvAppend x 2 + computeAttentionDecode."""
+    lk = _ctx_of(graphAllocator)
+    d = lambda t: describe(graphAllocator, t) if t is not None else None   # noqa: E731
+    B.check(B.lib().lk_compute_attention_step(lk.handle, d(q), d(k), d(v), d(table), d(position), int(headDim), d(kcache),
+                                              d(vcache), float(scale), d(qRopeDst), d(kRopeDst), d(dst)), lk.handle)
+
+
 class KVCache:
     """model/KVCache.kt:9-115 on device memory: keys / values ne = [headDim, numHeads, maxSequenceLength, 1] F32 in the
     allocator's device buffer, `currentLength` kept by the host (the `require`s of :44 and :85 live here), the

@@ -294,7 +294,49 @@ class GGMLCudaBackend:
                             skip.update((si, mi))
             i = members[-1] + 1
         self._groups, self._pairs = group_of, pair_of
+        self._steps = self._planAttentionSteps(nodes, skip)
         return rms_of, add_of, skip
+
+    def _planAttentionSteps(self, nodes, skip):
+        """ROPE(q), ROPE(k), CPY(k' -> key cache), CPY(v -> value cache), FLASH_ATTN — the core of one decode step of
+        LlamaAttention.forward (model/LlamaAttention.kt:87-123) — as ONE launch (lk_compute_attention_step) at the first
+        node's position.  Only the exact five-node run with one token, one position tensor and one table; anything
+        else runs node by node.  Returns {index of ROPE(q): (ROPE(q), ROPE(k), CPY k, CPY v, FLASH_ATTN indices)}."""
+        steps = {}
+        n = len(nodes)
+        for i in range(n - 4):
+            idx = tuple(range(i, i + 5))
+            if any(k in skip for k in idx):
+                continue
+            rq, rk, ck, cv, fa = (nodes[k] for k in idx)
+            if (rq.op, rk.op, ck.op, cv.op, fa.op) != (GGMLOp.ROPE, GGMLOp.ROPE, GGMLOp.CPY, GGMLOp.CPY, GGMLOp.FLASH_ATTN):
+                continue
+            if any(isinstance(t.extra, dict) for t in (rq, rk, ck, cv, fa)):
+                continue
+            pos, table, hd = rq.src[1], rq.src[2], int(rq.opParams[0])
+            if pos is None or table is None or rk.src[1] is None or rk.src[2] is None:
+                continue
+            same = lambda a, b: a is not None and b is not None and self._span(a) == self._span(b)   # noqa: E731
+            if not (same(rk.src[1], pos) and same(rk.src[2], table) and int(rk.opParams[0]) == hd and
+                    same(ck.src[2], pos) and same(cv.src[2], pos) and same(fa.src[3], pos)):
+                continue
+            kc, vc = ck.src[1], cv.src[1]
+            if kc is None or vc is None or int(kc.ne[0]) != hd or tuple(kc.ne) != tuple(vc.ne):
+                continue
+            rowlen = int(kc.ne[0]) * int(kc.ne[1])
+            if not (int(rq.numElements()) == rowlen and int(rk.numElements()) == rowlen and
+                    int(ck.src[0].numElements()) == rowlen and int(cv.src[0].numElements()) == rowlen and
+                    int(fa.numElements()) == rowlen):
+                continue                                   # one token only
+            if not (same(ck.src[0], rk) and same(fa.src[0], rq) and same(fa.src[1], kc) and same(fa.src[2], vc)):
+                continue
+            # the five dsts and the raw inputs must not alias each other
+            spans = [self._span(t) for t in (rq, rk, fa, kc, vc, rq.src[0], rk.src[0], cv.src[0])]
+            if any(a[0] == b[0] and a[1] < b[2] and b[1] < a[2] for x, a in enumerate(spans) for b in spans[x + 1:]):
+                continue
+            steps[i] = idx
+            skip.update(idx[1:])
+        return steps
 
     def _runNodes(self, ga, graph: GGMLCGraph, fuse: bool) -> None:
         nodes = graph.nodes
@@ -306,6 +348,16 @@ class GGMLCudaBackend:
         stored = set()                       # RMS_NORM nodes whose dst has been written
         for i, node in enumerate(nodes):
             if i in skip:
+                continue
+            if i in self._steps:
+                rq, rk, ck, cv, fa = (nodes[k] for k in self._steps[i])
+                scale = struct.unpack("<f", struct.pack("<i", int(fa.opParams[0])))[0]
+                try:
+                    ops.computeAttentionStep(ga, None, rq.src[0], rk.src[0], cv.src[0], rq.src[2], rq.src[1], int(rq.opParams[0]),
+                                             ck.src[1], cv.src[1], scale, fa, qRopeDst=rq, kRopeDst=rk)
+                except NotImplementedError:      # the library declined this shape: the five ops, in graph order
+                    for k in self._steps[i]:
+                        self._computeNode(ga, nodes[k])
                 continue
             if i in self._groups:
                 if self._runGroup(ga, nodes, i, rms_of, stored):

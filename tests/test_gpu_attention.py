@@ -233,3 +233,82 @@ def test_decoder_layer_with_attention_decodes_tokens(O, tname, hidden, ffn, H):
     for la, (_, _, st) in zip(attn, host):
         assert rel_err(ga.getFloats(la.keys)[:ntok * hidden], st["kc"][:ntok * hidden]) <= 1e-3
     be.free()
+
+
+# ---- fused decode step: ROPE(q) + ROPE(k) + append k / v + attention in one launch -------------------------------
+@pytest.mark.parametrize("H,D,maxseq,positions", [
+    (2, 64, 64, [0, 1, 63]),
+    (4, 64, 300, [0, 63, 64, 65, 128, 299]),      # chunk boundaries: the owner of the new row changes
+    (32, 128, 2048, [0, 127, 128, 1000, 2047]),   # Llama-2-7B heads
+])
+def test_attention_step_bit_identical_to_the_five_ops(be, H, D, maxseq, positions):
+    """lk_compute_attention_step == computeRope x 2 + computeKvAppend x 2 + computeAttentionDecode, bit for bit
+    (LlamaAttention.forward's core, model/LlamaAttention.kt:87-123), on caches that already hold earlier rows."""
+    n = H * D
+    ga = lk.GGMLGraphAllocator(be, size=4 * maxseq * n * 4 + maxseq * D * 4 + (4 << 20))
+    rng = np.random.default_rng(H + D)
+    table = ga.allocateTensor(GGMLTensor(GGMLType.F32, [2, D // 2, maxseq]))
+    ga.setBytes(table, lk.ropeTable(D, 10000.0, maxseq))
+    pos = ga.allocateTensor(GGMLTensor(GGMLType.I32, [4]))
+    caches = [ga.allocateTensor(GGMLTensor(GGMLType.F32, [D, H, maxseq])) for _ in range(4)]   # k, v (5 ops); k, v (fused)
+    base_k = rng.normal(0, 1, maxseq * n).astype(np.float32)
+    base_v = rng.normal(0, 1, maxseq * n).astype(np.float32)
+    vec = lambda: ga.allocateTensor(GGMLTensor(GGMLType.F32, [n]))   # noqa: E731
+    q, k, v, qr1, kr1, o1, qr2, kr2, o2 = (vec() for _ in range(9))
+    row = lambda t: GGMLTensor(GGMLType.F32, [D, H, 1], bufferId=t.bufferId, dataOffset=t.dataOffset, buffer=t.buffer)   # noqa: E731
+    scale = 1.0 / float(np.sqrt(np.float32(D)))
+    for p in positions:
+        for c, b in zip(caches, (base_k, base_v, base_k, base_v)):
+            ga.setBytes(c, b)
+        ga.setBytes(pos, np.array([p, 0, 0, 0], np.int32))
+        for t in (q, k, v):
+            ga.setBytes(t, rng.normal(0, 1, n).astype(np.float32))
+        lk.computeRope(ga, None, q, table, pos, D, qr1)
+        lk.computeRope(ga, None, k, table, pos, D, kr1)
+        lk.computeKvAppend(ga, None, row(kr1), caches[0], pos)
+        lk.computeKvAppend(ga, None, row(v), caches[1], pos)
+        lk.computeAttentionDecode(ga, None, qr1, caches[0], caches[1], pos, scale, o1)
+        lk.computeAttentionStep(ga, None, q, k, v, table, pos, D, caches[2], caches[3], scale, o2, qRopeDst=qr2, kRopeDst=kr2)
+        assert same_f32_bits(ga.getFloats(qr2), ga.getFloats(qr1)), p
+        assert same_f32_bits(ga.getFloats(kr2), ga.getFloats(kr1)), p
+        assert same_f32_bits(ga.getFloats(caches[2]), ga.getFloats(caches[0])), p
+        assert same_f32_bits(ga.getFloats(caches[3]), ga.getFloats(caches[1])), p
+        assert same_f32_bits(ga.getFloats(o2), ga.getFloats(o1)), p
+        # optional stores may be left out
+        ga.setBytes(o2, np.zeros(n, np.float32))
+        lk.computeAttentionStep(ga, None, q, k, v, table, pos, D, caches[2], caches[3], scale, o2)
+        assert same_f32_bits(ga.getFloats(o2), ga.getFloats(o1)), p
+
+
+def test_attention_step_argument_errors(be):
+    ga = lk.GGMLGraphAllocator(be, size=8 << 20)
+    H, D, S = 2, 64, 16
+    n = H * D
+    table = ga.allocateTensor(GGMLTensor(GGMLType.F32, [2, D // 2, S]))
+    pos = ga.allocateTensor(GGMLTensor(GGMLType.I32, [4]))
+    kc = ga.allocateTensor(GGMLTensor(GGMLType.F32, [D, H, S]))
+    vc = ga.allocateTensor(GGMLTensor(GGMLType.F32, [D, H, S]))
+    q, k, v, o = (ga.allocateTensor(GGMLTensor(GGMLType.F32, [n])) for _ in range(4))
+    short = ga.allocateTensor(GGMLTensor(GGMLType.F32, [n - 2]))
+    with pytest.raises(lk.IllegalArgumentException):
+        lk.computeAttentionStep(ga, None, q, short, v, table, pos, D, kc, vc, 0.125, o)
+    with pytest.raises(lk.IllegalArgumentException):
+        lk.computeAttentionStep(ga, None, q, k, v, table, pos, 32, kc, vc, 0.125, o)      # head_dim != cache ne[0]
+    fpos = ga.allocateTensor(GGMLTensor(GGMLType.F32, [4]))
+    with pytest.raises(lk.IllegalArgumentException):
+        lk.computeAttentionStep(ga, None, q, k, v, table, fpos, D, kc, vc, 0.125, o)      # position must be I32
+
+
+def test_planner_fuses_the_attention_core(be):
+    """the backend planner turns the layer's ROPE, ROPE, CPY, CPY, FLASH_ATTN run into one launch"""
+    from llama_kotlin_b200 import llama_layer as LL
+    hidden, ffn, H = 256, 704, 4
+    ga = lk.GGMLGraphAllocator(be, size=64 << 20)
+    layers = [LL.alloc_layer(ga, GGMLType.Q4_0, hidden, ffn)]
+    attn = LL.alloc_attention(ga, H, hidden // H, 64, 1)
+    x = ga.allocateTensor(GGMLTensor(GGMLType.F32, [hidden]))
+    graph, _ = LL.build_decoder_graph(ga, layers, x, hidden, ffn, attn=attn)
+    be._plan(graph)
+    assert len(be._steps) == 1
+    (first, idx), = be._steps.items()
+    assert [graph.nodes[i].op for i in idx] == [lk.GGMLOp.ROPE, lk.GGMLOp.ROPE, lk.GGMLOp.CPY, lk.GGMLOp.CPY, lk.GGMLOp.FLASH_ATTN]
