@@ -102,7 +102,7 @@ struct AttnStep {
     float *q_rope, *k_rope;   // optional: where the rotated q / k are also stored
 };
 cudaError_t launch_attn_decode(const float *q, const float *kc, const float *vc, const int32_t *pos, int head_dim,
-                               int nheads, int64_t max_seq, float scale, float *dst, void *workspace, cudaStream_t s,
-                               bool pdl = false, const AttnStep *step = nullptr);
+                               int nheads, int64_t max_seq, float scale, float *dst, void *workspace, int sm_count,
+                               cudaStream_t s, bool pdl = false, const AttnStep *step = nullptr);
 
 }  // namespace lk

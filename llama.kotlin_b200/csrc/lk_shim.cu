@@ -818,7 +818,7 @@ lk_status lk_compute_attention_decode(lk_ctx *ctx, const lk_tensor *q, const lk_
     if ((st = resolve(sc, dst, true, &dd, "dst")) != LK_OK) return st;
     chain_other(ctx, dd, (size_t)D * H * 4);
     cudaError_t e = lk::launch_attn_decode((const float *)dq, (const float *)dk, (const float *)dv, (const int32_t *)dp, (int)D, (int)H,
-                                           max_seq, scale, (float *)dd, ctx->attn_ws, ctx->stream, op_pdl(ctx, sc));
+                                           max_seq, scale, (float *)dd, ctx->attn_ws, ctx->sm_count, ctx->stream, op_pdl(ctx, sc));
     if (e == cudaErrorNotSupported) return fail(ctx, LK_ENOTIMPL, "attention: headDim must be 64 or 128, tensors 16-byte aligned");
     if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "attention launch");
     count_launch(ctx);
@@ -870,7 +870,7 @@ lk_status lk_compute_attention_step(lk_ctx *ctx, const lk_tensor *q, const lk_te
     step.k_raw = (const float *)dk; step.v_raw = (const float *)dv; step.table = (const float *)dt;
     step.table_pos = (int)table->ne[2]; step.q_rope = (float *)dqr; step.k_rope = (float *)dkr;
     cudaError_t e = lk::launch_attn_decode((const float *)dq, (const float *)dkc, (const float *)dvc, (const int32_t *)dp, (int)D, (int)H,
-                                           max_seq, scale, (float *)dd, ctx->attn_ws, ctx->stream, op_pdl(ctx, sc), &step);
+                                           max_seq, scale, (float *)dd, ctx->attn_ws, ctx->sm_count, ctx->stream, op_pdl(ctx, sc), &step);
     if (e == cudaErrorNotSupported) return fail(ctx, LK_ENOTIMPL, "attentionStep: headDim must be 64 or 128, tensors 16-byte aligned");
     if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "attentionStep launch");
     count_launch(ctx);
