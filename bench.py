@@ -366,7 +366,10 @@ def gpu_arm(args, rank: int, world: int, local_rank: int) -> dict:
     if world == 1 and not args.no_extras:
         # the other two measured paths of the scope table, reported beside the headline (not part of `value`)
         res["config"]["other_paths"] = {"prefill_gemm": prefill_gemm_line(lk, be, peaks),
-                                        "layer_graph": layer_graph_line(lk, be, peak)}
+                                        "layer_graph": layer_graph_line(lk, be, peak),
+                                        "layer_graph_ctx2048": layer_graph_line(lk, be, peak, ctx_len=2048),
+                                        "gemv_act16": act16_line(lk, be, graph, step_device, args, bytes_step, peak,
+                                                                 protos, x_host, y_host, ga, dst_all, qtype)}
     be.free()
     if world > 1:
         dist.destroy_process_group()
@@ -417,11 +420,38 @@ def prefill_gemm_line(lk, be, peaks) -> dict:
                          "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (cuBLAS bf16, same 16-bit tensor pipe)"}}
 
 
-def layer_graph_line(lk, be, hbm_peak) -> dict:
-    """BASELINE config 4: 32-layer synthetic Llama-2-7B decode step as one GGMLCGraph (tools/layer_bench.py)."""
+def layer_graph_line(lk, be, hbm_peak, ctx_len: int = 0) -> dict:
+    """BASELINE config 4: 32-layer synthetic Llama-2-7B decode step as one GGMLCGraph (tools/layer_bench.py); with
+    ctx_len > 0 the layer also carries RoPE, the KV-cache append and decode attention over that many positions."""
     sys.path.insert(0, os.path.join(ROOT, "tools"))
     import layer_bench
-    return layer_bench.run(lk, be, "Q4_0", layers=32, steps=30, warmup=3, hbm_peak_gbs=hbm_peak)
+    return layer_bench.run(lk, be, "Q4_0", layers=32, steps=30, warmup=3, hbm_peak_gbs=hbm_peak, ctx_len=ctx_len)
+
+
+def act16_line(lk, be, graph, step_device, args, bytes_step, peak, protos, x_host, y_host, ga, dst_all, qtype) -> dict:
+    """The headline step again with the GEMV's opt-in 16-bit activation planes (gemv_act_planes = 2: two byte planes,
+    2/3 of the DP4As, |x - x'| <= 2^-15 of the block maximum).  NOT the default and not `value`: the default keeps 24-bit
+    planes (error ~1e-6, below the reference's own F32 summation error); this line shows what the looser mode buys and
+    what it costs, against the same f64 check."""
+    from llama_kotlin_b200 import GGMLCGraph
+    lkc = be.lk
+    lkc.set_option("gemv_act_planes", 2)
+    g16 = GGMLCGraph(nodes=graph.nodes, allocator=graph.allocator)     # fresh object => fresh capture with the option
+    try:
+        for _ in range(3):
+            assert be.graphCompute(g16) == lk.GGMLStatus.SUCCESS
+        lkc.sync()
+        lkc.timer_start()
+        for _ in range(args.steps):
+            be.graphCompute(g16)
+        ms = lkc.timer_stop() / args.steps
+        ga.deviceBuffer.getTensor(dst_all, y_host.view(np.uint8), 0, y_host.nbytes)
+        chk = _check_slice(protos, x_host, y_host, qtype, 1, 0)
+    finally:
+        lkc.set_option("gemv_act_planes", 3)
+    gbps = bytes_step / (ms * 1e-3) / 1e9
+    return {"activation_bits": 16, "GBps": gbps, "frac_of_measured_hbm": gbps / peak if peak else None,
+            "ms_per_step": ms, "max_err_vs_f64_rows": chk.get("max_err_vs_f64_rows"), "default": False}
 
 
 def check_outputs(protos, x_host, y_host, qtype, world, sumM, rank) -> dict:

@@ -1,7 +1,9 @@
 set -x
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_attention.py -x -q 2>&1 | tail -15 > gpurun_out/b_tests.txt
-cat gpurun_out/b_tests.txt
-timeout 300 python tools/attn_bench.py 2>&1 | tail -6 > gpurun_out/b_attn.jsonl; cut -c1-200 gpurun_out/b_attn.jsonl
-for c in 0 128 2048; do timeout 300 python tools/layer_bench.py --ctx $c 2>&1 | tail -1; done > gpurun_out/b_layer.jsonl
-cut -c300-520 gpurun_out/b_layer.jsonl
+B="python bench.py --no-extras --no-cpu-baseline"
+for i in 1 2; do
+  timeout 300 $B 2>/dev/null | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('default  ', round(d['value'],1), round(d['config']['dependent_chain_GBps'],1), round(d['e2e']['value'],1), d['check']['ok'])"
+  timeout 300 $B --opt gemv_resident=3 2>/dev/null | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('resident3', round(d['value'],1), round(d['config']['dependent_chain_GBps'],1), round(d['e2e']['value'],1), d['check']['ok'])"
+  timeout 300 $B --opt gemv_resident=3 --opt gemv_stage_bytes=16384 2>/dev/null | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('res3/16K ', round(d['value'],1), round(d['config']['dependent_chain_GBps'],1), round(d['e2e']['value'],1), d['check']['ok'])"
+  timeout 300 $B --opt gemv_resident=3 --opt gemv_stage_bytes=24576 2>/dev/null | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('res3/24K ', round(d['value'],1), round(d['config']['dependent_chain_GBps'],1), round(d['e2e']['value'],1), d['check']['ok'])"
+done 2>&1 | grep -v "^+" | tee gpurun_out/r_resident_ab.txt
