@@ -84,8 +84,9 @@ __device__ __forceinline__ int dp4a_ss(uint32_t a, uint32_t b, int c) {
 template <int NP>
 struct XRegs {
     uint32_t q[NP][8];
-    float c;        // Q4_0: -8 * s * sumT;  Q4_1: s * sumT;  Q8_0: unused
+    float c;        // Q4_0: -8 * s * sumT;  Q4_1 / Q4_K: s * sumT;  Q8_0 / Q8_K: unused;  Q2_K: s * sumT of elements 0..15
     float s;        // 2^(E-22) (NP = 3) or 2^(E-14) (NP = 2)
+    float c2;       // Q2_K only: s * sumT of elements 16..31 (the block column spans two 16-element sub-blocks)
 };
 
 // 16 quant bytes (4 aligned words) of 4-bit quants x the block's activations; exact int32
@@ -138,6 +139,72 @@ __device__ __forceinline__ float block_dot(const uint32_t *row, int b, const XRe
         const float d = h2f((uint16_t)(w[0] & 0xFFFFu)), m = h2f((uint16_t)(w[0] >> 16));
         const float f = (float)q4_block_isum(q, x);
         return fmaf(d, f * x.s, m * x.c);                   // d*s*I + m*s*sumT
+    } else if (TYPE == T_Q4_K) {
+        // the reference's own Q4_K (core/GGMLComputeOps.kt:262-306): 144-byte super-block = 36 words: d | dmin << 16,
+        // scales[12], then 8 sub-blocks of 16 quant bytes.  Block column b = sub-block b & 7 of super-block b >> 3; its
+        // quants are one aligned LDS.128.  w = (q/15) * ((sc & 63)/63 * d) + (qmin/63 * d + dmin).
+        const uint32_t *wp = row + 36 * (b >> 3);
+        const int sb = b & 7;
+        const uint4 qv = *(const uint4 *)(wp + 4 + 4 * sb);
+        const uint32_t q[4] = {qv.x, qv.y, qv.z, qv.w};
+        const uint32_t hdr = wp[0];
+        const uint32_t sbyte = (wp[1 + (sb >> 2)] >> (8 * (sb & 3))) & 0xFFu;
+        const int hi_i = 2 * sb + 1;                                   // scales[2 sb + 1] & 15 for sb <= 5, else 0
+        const uint32_t hbyte = sb <= 5 ? ((wp[1 + (hi_i >> 2)] >> (8 * (hi_i & 3))) & 0x0Fu) : 0u;
+        const float d = h2f((uint16_t)(hdr & 0xFFFFu)), dmin = h2f((uint16_t)(hdr >> 16));
+        const float scale = (float)(sbyte & 63u) * d * (1.0f / (63.0f * 15.0f));
+        const float mn = fmaf((float)((sbyte >> 6) | (hbyte << 2)) * (1.0f / 63.0f), d, dmin);
+        const float f = (float)q4_block_isum(q, x);
+        return fmaf(scale, f * x.s, mn * x.c);                          // scale*s*I + min*s*sumT
+    } else if (TYPE == T_Q2_K) {
+        // the reference's own Q2_K (core/GGMLComputeOps.kt:152-236): 84-byte super-block = 21 words: scales[16] (lo nibble
+        // scale, hi nibble min), 64 quant bytes (byte j = elements 4j..4j+3, 2 bits each), d | dmin << 16.  Block column
+        // b = sub-blocks 2 (b & 7) and 2 (b & 7) + 1 (16 elements, one quant word, own scale / min each).
+        // w = (q/3) * ((sc & 15)/15 * d) + ((sc >> 4) * d + dmin); plane word 4 h + j holds elements 16 h + {j, 4+j, 8+j, 12+j}.
+        const uint32_t *wp = row + 21 * (b >> 3);
+        const int sb = b & 7;
+        const uint32_t hdr = wp[20];
+        const uint32_t sc2 = (wp[sb >> 1] >> (16 * (sb & 1))) & 0xFFFFu;
+        const float d = h2f((uint16_t)(hdr & 0xFFFFu)), dmin = h2f((uint16_t)(hdr >> 16));
+        float r = 0.f;
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            const uint32_t w = wp[4 + 2 * sb + h];
+            int acc[NP];
+#pragma unroll
+            for (int pl = 0; pl < NP; pl++) acc[pl] = 0;
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const uint32_t q = (w >> (2 * j)) & 0x03030303u;
+#pragma unroll
+                for (int pl = 0; pl < NP; pl++)
+                    acc[pl] = (pl == NP - 1) ? dp4a_us(q, x.q[pl][4 * h + j], acc[pl]) : dp4a_uu(q, x.q[pl][4 * h + j], acc[pl]);
+            }
+            const int I = (NP == 3) ? (acc[NP - 1] << 16) + ((acc[1] << 8) + acc[0]) : (acc[1] << 8) + acc[0];
+            const uint32_t sm = (sc2 >> (8 * h)) & 0xFFu;
+            const float scale = (float)(sm & 15u) * d * (1.0f / 45.0f);
+            const float mn = fmaf((float)(sm >> 4), d, dmin);
+            r += fmaf(scale, (float)I * x.s, mn * (h ? x.c2 : x.c));
+        }
+        return r;
+    } else if (TYPE == T_Q8_K) {
+        // the reference's own Q8_K (core/GGMLComputeOps.kt:382-432): 292-byte super-block = 73 words: d (f32), 256 int8
+        const uint32_t *wp = row + 73 * (b >> 3) + 1 + 8 * (b & 7);
+        int acc[NP];
+#pragma unroll
+        for (int pl = 0; pl < NP; pl++) acc[pl] = 0;
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const uint32_t q = wp[j];
+#pragma unroll
+            for (int pl = 0; pl < NP; pl++)
+                acc[pl] = (pl == NP - 1) ? dp4a_ss(q, x.q[pl][j], acc[pl]) : dp4a_su(q, x.q[pl][j], acc[pl]);
+        }
+        const float d = __uint_as_float(row[73 * (b >> 3)]);
+        float f;
+        if (NP == 3) f = fmaf((float)acc[NP - 1], 65536.0f, (float)((acc[1] << 8) + acc[0]));
+        else f = (float)((acc[1] << 8) + acc[0]);
+        return d * (f * x.s);
     } else {
         const uint32_t *wp = row + 8 * b + (b >> 1);
         uint32_t w[9];
@@ -320,6 +387,7 @@ __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int ti
             T[i] = (int)__float_as_uint(fmaf(v[i], c, 12582912.0f)) - 0x4B400000;
             sumT += T[i];
         }
+        const int sumT_half = sumT;                       // this lane's 16 elements (Q2_K: one sub-block)
         sumT += __shfl_xor_sync(0xffffffffu, sumT, 1);   // both halves of the block
 #ifdef LK_GEMV_TIMELINE
         if (tid == 0 && base == 0) { if (sumT == 0x7FFFFFFF) xs[0] = 1; LK_TL(23); }
@@ -331,11 +399,15 @@ __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int ti
             for (int pl = 0; pl < NP; pl++) {
                 const uint32_t s2 = 0x0040u + 0x0011u * pl;   // byte pl of a, byte pl of b
                 uint32_t wds[4];
-                if (TYPE == T_Q8_0 || p.nib) {
+                if (TYPE == T_Q2_K) {
+#pragma unroll
+                    for (int j = 0; j < 4; j++)   // 2-bit field j of a quant word's four bytes = elements j, 4+j, 8+j, 12+j of my half
+                        wds[j] = __byte_perm(__byte_perm(T[j], T[4 + j], s2), __byte_perm(T[8 + j], T[12 + j], s2), 0x5410);
+                } else if (TYPE == T_Q8_0 || TYPE == T_Q8_K || p.nib) {
 #pragma unroll
                     for (int j = 0; j < 4; j++)
                         wds[j] = __byte_perm(__byte_perm(T[4 * j], T[4 * j + 1], s2), __byte_perm(T[4 * j + 2], T[4 * j + 3], s2), 0x5410);
-                    if (TYPE != T_Q8_0) {
+                    if (TYPE != T_Q8_0 && TYPE != T_Q8_K) {
                         // ggml order: quant word j holds elements 4j..4j+3 in its low nibbles (plane word 2j) and elements
                         // 16+4j.. in its high nibbles (plane word 2j+1): my half h fills words 2j + h
 #pragma unroll
@@ -352,6 +424,7 @@ __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int ti
                 *(uint4 *)(slot + pl * 8 + h * 4) = make_uint4(wds[0], wds[1], wds[2], wds[3]);
             }
             if (h == 0) { slot[NP * 8] = __float_as_uint((float)sumT); slot[NP * 8 + 1] = __float_as_uint(s); }
+            if (TYPE == T_Q2_K) slot[NP * 8 + 2 + h] = __float_as_uint((float)sumT_half);
         }
     }
 }
@@ -549,7 +622,8 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
             }
         const uint4 t = slot[NP * 2];
         x.s = __uint_as_float(t.y);
-        x.c = ((TYPE == T_Q4_0) ? -8.0f : 1.0f) * x.s * __uint_as_float(t.x);
+        x.c = ((TYPE == T_Q4_0) ? -8.0f : 1.0f) * x.s * __uint_as_float(TYPE == T_Q2_K ? t.z : t.x);
+        x.c2 = x.s * __uint_as_float(t.w);
     }
     if (tid == 0) LK_TL(5);
 
@@ -692,19 +766,25 @@ template <int TYPE, int NP>
 static cudaError_t launch_type(const GemvParams &p, bool fused, int grid, int smem, int pdl, cudaStream_t s) {
     return fused ? launch_fused<TYPE, NP, true>(p, grid, smem, pdl, s) : launch_fused<TYPE, NP, false>(p, grid, smem, pdl, s);
 }
+template <int TYPE, int NP>
+static cudaError_t launch_plain(const GemvParams &p, int grid, int smem, int pdl, cudaStream_t s) {   // K-quants: no fused variants
+    return launch_fused<TYPE, NP, false>(p, grid, smem, pdl, s);
+}
 
 cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const float *b, float *dst,
                         int64_t row_offset, const GemvPeers &peers, const GemvTuning &tune, int sm_count,
                         cudaStream_t s, const GemvFusion *fusion) {
+    const bool kq = type == T_Q4_K || type == T_Q8_K || type == T_Q2_K;     // the reference's K-quant super-blocks (256 elements)
+    if (kq && ((K % 256) != 0 || fusion)) return cudaErrorNotSupported;
     const int bb = block_bytes(type);
-    if (bb == 0 || K <= 0 || M <= 0 || (K % 64) != 0 || K > 32 * 32 * 28 || M > (1 << 30))
+    if ((bb == 0 && !kq) || K <= 0 || M <= 0 || (K % 64) != 0 || K > 32 * 32 * 28 || M > (1 << 30))
         return cudaErrorNotSupported;
     if (((uintptr_t)a & 15) || ((uintptr_t)b & 15)) return cudaErrorNotSupported;
 
     GemvParams p = {};
     p.a = (const uint8_t *)a; p.b = b; p.dst = dst;
     p.npeers = (short)peers.n;
-    p.nib = (short)(tune.nibble_order ? 1 : 0);
+    p.nib = (short)((tune.nibble_order && !kq) ? 1 : 0);
     for (int i = 0; i < peers.n && i < 8; i++) p.peer[i] = peers.ptr[i];
     p.K = (int)K; p.M = (int)M; p.row_offset = row_offset;
     p.nseg = 1;
@@ -727,7 +807,7 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
     }
     p.tl = (unsigned long long *)tune.timeline;
     p.wait_mode = tune.wait_mode;
-    p.row_bytes = (int)(K / 32) * bb;
+    p.row_bytes = kq ? (int)(K / 256) * (type == T_Q4_K ? 144 : type == T_Q8_K ? 292 : 84) : (int)(K / 32) * bb;
     p.nblk = (int)(K / 32);
     p.ncw = (p.nblk + 31) / 32;
     const int target_warps = tune.variant > 0 ? tune.variant : 8;   // consumer warps to aim for
@@ -806,6 +886,12 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
         case T_Q4_0 * 4 + 3: return launch_type<T_Q4_0, 3>(p, fused, grid, smem, tune.pdl, s);
         case T_Q4_1 * 4 + 3: return launch_type<T_Q4_1, 3>(p, fused, grid, smem, tune.pdl, s);
         case T_Q8_0 * 4 + 3: return launch_type<T_Q8_0, 3>(p, fused, grid, smem, tune.pdl, s);
+        case T_Q4_K * 4 + 2: return launch_plain<T_Q4_K, 2>(p, grid, smem, tune.pdl, s);
+        case T_Q4_K * 4 + 3: return launch_plain<T_Q4_K, 3>(p, grid, smem, tune.pdl, s);
+        case T_Q8_K * 4 + 2: return launch_plain<T_Q8_K, 2>(p, grid, smem, tune.pdl, s);
+        case T_Q8_K * 4 + 3: return launch_plain<T_Q8_K, 3>(p, grid, smem, tune.pdl, s);
+        case T_Q2_K * 4 + 2: return launch_plain<T_Q2_K, 2>(p, grid, smem, tune.pdl, s);
+        case T_Q2_K * 4 + 3: return launch_plain<T_Q2_K, 3>(p, grid, smem, tune.pdl, s);
         default: return cudaErrorNotSupported;
     }
 }

@@ -459,6 +459,18 @@ lk_status lk_compute_matmul(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b,
     if (M == 0 || N == 0) return finish(sc);
 
     if (is_kq_type(a->type)) {     // core/GGMLComputeOps.kt:1481-1513 (+ computeDotProductBitNet158F32, :635-660)
+        if (N == 1 && a->type != LK_TYPE_BITNET_1_58 && K > 0 && K % 256 == 0) {
+            // whole super-blocks per row: the streaming DP4A GEMV (K1) takes the three K-quant formats as well
+            lk::GemvTuning tune = ctx->tune;
+            tune.pdl = (ctx->pdl_mode == 2) || (ctx->pdl_mode == 1 && ctx->capturing);
+            lk::GemvPeers none;
+            tune.wait_mode = lk::gemv_wait_mode(ctx, da, (size_t)lk_tensor_nbytes(a), db, (size_t)K * 4, dd, (size_t)M * 4, tune.pdl != 0);
+            if (sc.any_host) tune.wait_mode = 0;
+            const cudaError_t eg = lk::launch_gemv(a->type, da, K, M, (const float *)db, (float *)dd, 0, none, tune, ctx->sm_count, ctx->stream);
+            if (eg == cudaSuccess) { count_launch(ctx); return finish(sc); }
+            if (eg != cudaErrorNotSupported) return lk::cuda_fail(ctx, eg, "K-quant GEMV launch");
+            cudaGetLastError();
+        }
         chain_other(ctx, dd, (size_t)M * N * 4);
         const cudaError_t ek = lk::launch_kq_matmul(a->type, da, K, M, (const float *)db, N, (float *)dd, ctx->sm_count, ctx->stream);
         if (ek != cudaSuccess) return lk::cuda_fail(ctx, ek, "K-quant matmul launch");

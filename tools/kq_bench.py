@@ -68,7 +68,8 @@ def main():
             us = lkc.timer_stop() * 1e3 / (args.reps * ncopies)
             algo = wb + 4 * K + 4 * M
             gbps = algo / us / 1e3
-            print(json.dumps({"kernel": f"kq_gemv_kernel<{tname}>", "shape": f"{M}x{K}", "us_per_launch": round(us, 3),
+            kern = f"gemv_kernel<{tname}> (K1, DP4A planes)" if tname != "BITNET_1_58" else "kq_gemv_kernel<BITNET_1_58>"
+            print(json.dumps({"kernel": kern, "shape": f"{M}x{K}", "us_per_launch": round(us, 3),
                               "algorithmic_bytes": algo, "GBps": round(gbps, 1),
                               "hbm_frac": round(gbps / peak, 4) if peak else None, "copies": ncopies, "ok": ok}), flush=True)
             ga.deviceBuffer.free()
