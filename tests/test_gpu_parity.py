@@ -802,3 +802,37 @@ def test_gemv_ggml_order_against_reference_mul_mat(O, ga):
     ref_c, _ = R.mul_mat(Q4_0, gg, K, M, x, 1)
     assert rel_err(got, ref_c) <= 2e-2
     assert rel_err(got, O.matmul(Q4_0, O.repack_nibbles(Q4_0, gg, to_ggml=False), K, M, x, 1, nthreads=8)) <= MATMUL_REL_TOL
+
+
+@pytest.mark.parametrize("tname", ["Q4_0", "Q4_1"])
+@pytest.mark.parametrize("nib", [0, 1])
+def test_gemv_extreme_magnitudes_are_exact_integers(O, ga, tname, nib):
+    """Largest block fixed-point magnitudes (|T| = 2^22 on every element: x just below a power of two), every nibble 15 or
+    mixed signs: the integer plane sums and their combination must not overflow (K1's exactness claim, incl. the folded
+    high-nibble form lo (a - t) + r t)."""
+    gt, ot = QT[tname]
+    M, K = 8, 256
+    bb = gt.byteSize
+    raw = np.zeros((M * K // 32, bb), np.uint8)
+    raw[:, 0:2] = np.array([1.0], np.float16).view(np.uint8)          # d = 1
+    if tname == "Q4_1":
+        raw[:, 2:4] = np.array([0.0], np.float16).view(np.uint8)      # m = 0
+    raw[:, bb - 16:] = 0xFF                                           # every nibble 15
+    raw[1::2, bb - 16:] = 0xF0                                        # odd blocks: low nibbles 0, high 15
+    big = np.nextafter(np.float32(2.0), np.float32(0.0))
+    rng = np.random.default_rng(3)
+    for signs in (np.ones(K), np.where(np.arange(K) % 2 == 0, 1.0, -1.0), rng.choice([-1.0, 1.0], K)):
+        x = (big * signs).astype(np.float32)
+        from llama_kotlin_b200.ggml_compute_ops import _ctx_of
+        lkc = _ctx_of(ga)
+        lkc.set_option("nibble_order", nib)
+        try:
+            got = host_matmul(ga, gt, raw.reshape(-1), K, M, x, 1)
+        finally:
+            lkc.set_option("nibble_order", 0)
+        blocks = raw.reshape(-1) if nib == 0 else O.repack_nibbles(ot, raw.reshape(-1), to_ggml=False)
+        ref = O.matmul(ot, blocks, K, M, x, 1)
+        w = O.dequantize(ot, blocks, M * K).reshape(M, K).astype(np.float64)
+        exact = w @ x.astype(np.float64)
+        assert np.max(np.abs(got - exact)) <= 2e-6 * np.max(np.abs(w) @ np.abs(x.astype(np.float64)))
+        assert rel_err(got, ref) <= MATMUL_REL_TOL or np.max(np.abs(ref)) < 1e-3
