@@ -299,6 +299,18 @@ LK_API lk_status   lk_peer_push_f32(lk_ctx *ctx, lk_buf *local, uint64_t off, in
 LK_API lk_status   lk_compute_matmul_sharded(lk_ctx *ctx, const lk_tensor *a_shard, const lk_tensor *b,
                                       const lk_tensor *dst_full, int64_t row0, int64_t M_total,
                                       lk_buf *const *peer_dst, int32_t npeers);
+/* Sharded SwiGLU half of LlamaMLP.forward (model/LlamaModel.kt:159-176) in ONE launch, N == 1: this rank owns rows
+ * [row0, row0 + gate_shard.ne[1]) of the M_total-row gate and up weights (same type and shape).  With
+ * x' = RMSNorm(x, norm_w, eps) when norm_w != NULL (x' is also stored to normed_dst when given), else x' = x:
+ *   g = gate x', u = up x', silu_dst (optional) = silu(g), h = silu(g) * u
+ * written to rows [row0, ...) of g_full / u_full / silu_full / h_full (ne = [1, M_total]) on this rank, and h also into
+ * the same offsets of every peer's copy of h_full's buffer (peer_h, npeers as lk_compute_matmul_sharded) from the
+ * GEMV epilogue over NVLink; follow with lk_peer_barrier.  Same roundings as lk_compute_matmul_fused.            */
+LK_API lk_status   lk_compute_swiglu_sharded(lk_ctx *ctx, const lk_tensor *gate_shard, const lk_tensor *up_shard,
+                                      const lk_tensor *x, const lk_tensor *norm_w, float eps, const lk_tensor *normed_dst,
+                                      const lk_tensor *g_full, const lk_tensor *u_full, const lk_tensor *silu_full,
+                                      const lk_tensor *h_full, int64_t row0, int64_t M_total,
+                                      lk_buf *const *peer_h, int32_t npeers);
 
 #ifdef __cplusplus
 }

@@ -122,6 +122,7 @@ def lib() -> C.CDLL:
         "lk_peer_barrier": (i32, [vp, vp, C.POINTER(vp), i32, i32, u32]),
         "lk_peer_push_f32": (i32, [vp, vp, u64, i64, C.POINTER(vp), i32]),
         "lk_compute_matmul_sharded": (i32, [vp, tp, tp, tp, i64, i64, C.POINTER(vp), i32]),
+        "lk_compute_swiglu_sharded": (i32, [vp, tp, tp, tp, tp, C.c_float, tp, tp, tp, tp, tp, i64, i64, C.POINTER(vp), i32]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)

@@ -234,4 +234,71 @@ lk_status lk_compute_matmul_sharded(lk_ctx *ctx, const lk_tensor *a, const lk_te
     return LK_OK;
 }
 
+lk_status lk_compute_swiglu_sharded(lk_ctx *ctx, const lk_tensor *gate, const lk_tensor *up, const lk_tensor *x,
+                                    const lk_tensor *norm_w, float eps, const lk_tensor *normed_dst, const lk_tensor *g_full,
+                                    const lk_tensor *u_full, const lk_tensor *silu_full, const lk_tensor *h_full, int64_t row0,
+                                    int64_t M_total, lk_buf *const *peer_h, int32_t npeers) {
+    if (!ctx || !gate || !up || !x || !g_full || !u_full || !h_full) return lk::fail(ctx, LK_EINVAL_ARG, "lk_compute_swiglu_sharded: NULL argument");
+    const int64_t Ms = gate->ne[1], K = gate->ne[0];
+    if (up->type != gate->type || up->ne[0] != K || up->ne[1] != Ms) return lk::fail(ctx, LK_EINVAL_DIM, "sharded SwiGLU: gate and up shards must have one type and shape");
+    if (lk::block_bytes(gate->type) == 0) return lk::fail(ctx, LK_EINVAL_TYPE, "sharded SwiGLU: Q4_0/Q4_1/Q8_0 weights");
+    if (row0 < 0 || row0 + Ms > M_total) return lk::fail(ctx, LK_EINVAL_DIM, "shard rows outside dst");
+    if (npeers < 0 || npeers > 8) return lk::fail(ctx, LK_EINVAL_ARG, "sharded SwiGLU: at most 8 peers");
+    auto count = [](const lk_tensor *t) { int64_t n = 1; for (int d = 0; d < LK_MAX_DIMS; d++) n *= t->ne[d] > 0 ? t->ne[d] : 1; return n; };
+    struct Chk { const lk_tensor *t; int64_t n; };
+    const Chk chk[] = {{x, K}, {norm_w, K}, {normed_dst, K}, {g_full, M_total}, {u_full, M_total}, {silu_full, M_total}, {h_full, M_total}};
+    for (const Chk &c : chk) {
+        if (!c.t) continue;
+        if (c.t->type != LK_TYPE_F32) return lk::fail(ctx, LK_EINVAL_TYPE, "sharded SwiGLU: F32 vectors expected");
+        if (!c.t->dev_buf) return lk::fail(ctx, LK_EINVAL_ARG, "sharded SwiGLU: tensors must be device resident");
+        if (count(c.t) != c.n) return lk::fail(ctx, LK_EINVAL_DIM, "sharded SwiGLU: vector length mismatch");
+        if (c.t->data_offset + (uint64_t)c.n * 4 > c.t->dev_buf->size) return lk::fail(ctx, LK_EBOUNDS, "sharded SwiGLU: tensor bytes exceed the device buffer");
+    }
+    if (normed_dst && !norm_w) return lk::fail(ctx, LK_EINVAL_ARG, "sharded SwiGLU: normed_dst goes with norm_w");
+    for (const lk_tensor *t : {gate, up}) {
+        if (!t->dev_buf) return lk::fail(ctx, LK_EINVAL_ARG, "sharded SwiGLU: tensors must be device resident");
+        if (t->data_offset + (uint64_t)lk_tensor_nbytes(t) > t->dev_buf->size) return lk::fail(ctx, LK_EBOUNDS, "sharded SwiGLU: weight bytes exceed the device buffer");
+    }
+    auto ptr = [](const lk_tensor *t) { return t ? (uint8_t *)t->dev_buf->ptr + t->data_offset : nullptr; };
+    lk::GemvPeers peers;
+    for (int q = 0; q < npeers; q++) {
+        if (!peer_h || !peer_h[q] || peer_h[q] == h_full->dev_buf) continue;
+        if (h_full->data_offset + (uint64_t)M_total * 4 > peer_h[q]->size) return lk::fail(ctx, LK_EBOUNDS, "peer dst too small");
+        peers.ptr[peers.n++] = (float *)((uint8_t *)peer_h[q]->ptr + h_full->data_offset);
+    }
+    lk::GemvFusion fu;
+    if (norm_w) { fu.pro_mode = 1; fu.pro_w = (const float *)ptr(norm_w); fu.pro_eps = eps; fu.b_out = (float *)ptr(normed_dst); }
+    fu.nseg_extra = 1;
+    fu.a_extra[0] = ptr(up);
+    fu.dst_extra[0] = (float *)ptr(u_full);
+    fu.epi_mode = 1;
+    fu.epi_act = (float *)ptr(silu_full);
+    fu.epi_out = (float *)ptr(h_full);
+    lk::GemvTuning tune = ctx->tune;
+    tune.pdl = (ctx->pdl_mode == 2) || (ctx->pdl_mode == 1 && ctx->capturing);
+    const size_t abytes = (size_t)lk_tensor_nbytes(gate);
+    std::vector<std::pair<const void *, size_t>> rd, wr, wt;
+    if (norm_w) rd.push_back({ptr(norm_w), (size_t)K * 4});
+    if (normed_dst) wr.push_back({ptr(normed_dst), (size_t)K * 4});
+    wr.push_back({ptr(u_full) + row0 * 4, (size_t)Ms * 4});
+    wr.push_back({ptr(h_full) + row0 * 4, (size_t)Ms * 4});
+    if (silu_full) wr.push_back({ptr(silu_full) + row0 * 4, (size_t)Ms * 4});
+    wt.push_back({ptr(up), abytes});
+    tune.wait_mode = lk::gemv_wait_mode(ctx, ptr(gate), abytes, ptr(x), (size_t)K * 4, ptr(g_full) + row0 * 4, (size_t)Ms * 4,
+                                        tune.pdl != 0, &rd, &wr, &wt);
+    // the pair keeps both segments' partial sums of a CTA's rows in shared memory: a shard with many rows per CTA
+    // (G = 2 of the 70B FFN: 97 rows x 8192) is spread over 2 or 4 CTAs per SM instead
+    cudaError_t e = cudaErrorNotSupported;
+    for (int cps = tune.ctas_per_sm > 0 ? tune.ctas_per_sm : 1; cps <= 4 && e == cudaErrorNotSupported; cps *= 2) {
+        tune.ctas_per_sm = cps;
+        e = lk::launch_gemv(gate->type, ptr(gate), K, Ms, (const float *)ptr(x), (float *)ptr(g_full), row0, peers, tune,
+                            ctx->sm_count, ctx->stream, &fu);
+        if (e == cudaErrorNotSupported) cudaGetLastError();
+    }
+    if (e == cudaErrorNotSupported) return lk::fail(ctx, LK_ENOTIMPL, "sharded SwiGLU: shape not supported by the streaming GEMV");
+    if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "sharded SwiGLU launch");
+    if (ctx->capturing) ctx->capture_launches++; else ctx->launches++;
+    return LK_OK;
+}
+
 }  // extern "C"

@@ -493,7 +493,10 @@ __device__ __forceinline__ void finish_pair(const GemvParams &p, const float *re
             p.dst[o] = g;
             p.dst_seg[0][o] = u;
             if (p.epi_act) p.epi_act[o] = act;
-            p.epi_out[o] = __fmul_rn(act, u);
+            const float hv = __fmul_rn(act, u);
+            p.epi_out[o] = hv;
+#pragma unroll 1
+            for (int q = 0; q < p.npeers; q++) p.peer[q][o] = hv;      // sharded FFN: this rank's slice of h into every peer's copy
         }
     }
 }
@@ -793,7 +796,8 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
         p.pro_mode = fusion->pro_mode; p.pro_w = fusion->pro_w; p.pro_eps = fusion->pro_eps; p.b_out = fusion->b_out;
         p.residual = fusion->residual; p.dst_raw = fusion->dst_raw;
         if (fusion->nseg_extra < 0 || fusion->nseg_extra > 2) return cudaErrorNotSupported;
-        if (fusion->nseg_extra > 0 && (fusion->residual || peers.n > 0 || row_offset != 0)) return cudaErrorNotSupported;
+        // stacked segments take peers / a row offset only as the SwiGLU pair (sharded FFN: the peers then are copies of epi_out)
+        if (fusion->nseg_extra > 0 && (fusion->residual || ((peers.n > 0 || row_offset != 0) && fusion->epi_mode != 1))) return cudaErrorNotSupported;
         for (int i = 0; i < fusion->nseg_extra; i++) {
             if (!fusion->a_extra[i] || !fusion->dst_extra[i] || ((uintptr_t)fusion->a_extra[i] & 15)) return cudaErrorNotSupported;
             p.a_seg[i] = (const uint8_t *)fusion->a_extra[i];

@@ -45,7 +45,8 @@ struct GemvFusion {
     const float *residual = nullptr;   // dst = residual + a x b  (the following ADD)
     float *dst_raw = nullptr;       // also store the bare product (the unfused matmul's dst)
     // stacked segments: up to two more weights of the same type and shape, multiplied with the same activations by
-    // the same launch (Q/K/V, gate/up); no residual, no peers, no row offset with nseg_extra > 0
+    // the same launch (Q/K/V, gate/up); no residual with nseg_extra > 0; peers / a row offset only with epi_mode 1
+    // (the peers then receive epi_out: lk_compute_swiglu_sharded)
     int nseg_extra = 0;
     const void *a_extra[2] = {nullptr, nullptr};
     float *dst_extra[2] = {nullptr, nullptr};

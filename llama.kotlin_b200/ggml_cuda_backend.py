@@ -156,6 +156,12 @@ class GGMLCudaBackend:
             grp, count, peers = ex["shard_push"]
             grp.push(node.buffer, node.dataOffset, count, peers)
             return
+        if ex is not None and "shard_swiglu" in ex:       # sharded gate/up + SwiGLU (+ RMSNorm prologue) as one launch
+            d = ex["shard_swiglu"]
+            d["group"].computeSwigluSharded(ga, d["gate"], d["up"], d["x"], d["g_full"], d["u_full"], node, d["row0"],
+                                            d["M_total"], d.get("peers"), silu_full=d.get("silu_full"),
+                                            norm_w=d.get("norm_w"), eps=d.get("eps", 0.0), normed_dst=d.get("normed_dst"))
+            return
         if op == GGMLOp.NONE:
             return
         if op == GGMLOp.MUL_MAT and ex is not None and "shard" in ex:

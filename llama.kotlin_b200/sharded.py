@@ -98,6 +98,20 @@ class ShardGroup:
                                                   describe(graphAllocator, b), describe(graphAllocator, dst_full),
                                                   int(row0), int(M_total), arr if n else None, n), self.lk.handle)
 
+    def computeSwigluSharded(self, graphAllocator, gate_shard: GGMLTensor, up_shard: GGMLTensor, x: GGMLTensor,
+                             g_full: GGMLTensor, u_full: GGMLTensor, h_full: GGMLTensor, row0: int, M_total: int,
+                             peer_h: Sequence[object] = None, silu_full: GGMLTensor = None, norm_w: GGMLTensor = None,
+                             eps: float = 0.0, normed_dst: GGMLTensor = None) -> None:
+        """The sharded SwiGLU half of LlamaMLP.forward (model/LlamaModel.kt:159-176) as one launch: this rank's rows of
+        g = gate x', u = up x', h = silu(g) * u (x' = RMSNorm(x, norm_w, eps) when norm_w is given), h also stored into
+        every peer's copy of h_full (peer_h = map_dst_buffer of h_full's buffer); follow with barrier()."""
+        n = len(peer_h) if peer_h else 0
+        arr = (C.c_void_p * max(n, 1))(*[p if isinstance(p, C.c_void_p) else C.c_void_p(p) for p in (peer_h or [])])
+        d = lambda t: describe(graphAllocator, t) if t is not None else None   # noqa: E731
+        B.check(B.lib().lk_compute_swiglu_sharded(self.lk.handle, d(gate_shard), d(up_shard), d(x), d(norm_w), float(eps),
+                                                  d(normed_dst), d(g_full), d(u_full), d(silu_full), d(h_full), int(row0),
+                                                  int(M_total), arr if n else None, n), self.lk.handle)
+
     def barrier(self) -> None:
         """Every rank's preceding peer stores are visible everywhere after this (stream-ordered)."""
         arr = (C.c_void_p * self.world)(*[p if isinstance(p, C.c_void_p) else C.c_void_p(p) for p in self.peer_flags])

@@ -836,3 +836,50 @@ def test_gemv_extreme_magnitudes_are_exact_integers(O, ga, tname, nib):
         exact = w @ x.astype(np.float64)
         assert np.max(np.abs(got - exact)) <= 2e-6 * np.max(np.abs(w) @ np.abs(x.astype(np.float64)))
         assert rel_err(got, ref) <= MATMUL_REL_TOL or np.max(np.abs(ref)) < 1e-3
+
+
+@pytest.mark.parametrize("tname", ["Q4_0", "Q8_0"])
+@pytest.mark.parametrize("with_norm", [False, True])
+def test_swiglu_sharded_matches_the_separate_ops(O, tname, with_norm):
+    """lk_compute_swiglu_sharded on one rank (no peers): rows [row0, row0 + Ms) of g / u / silu / h are what the separate
+    matmul, SILU and MUL ops (and RMS_NORM before them) give, bit for bit where the fused single-GPU launch is; the rest
+    of the full-size vectors is left alone."""
+    gt, ot = QT[tname]
+    K, Ms, M_total, row0 = 512, 96, 384, 192
+    be = lk.GGMLCudaBackend(0)
+    ga = lk.GGMLGraphAllocator(be, size=16 << 20)
+    grp = lk.ShardGroup(be, 0, 1, lambda o: [o])
+    rng = np.random.default_rng(12)
+    wg, wu = (O.quantize(ot, rng.normal(0, 0.02, Ms * K).astype(np.float32)) for _ in range(2))
+    x0 = rng.normal(0, 1, K).astype(np.float32)
+    nw0 = rng.normal(1, 0.1, K).astype(np.float32)
+    gate = ga.allocateTensor(GGMLTensor(gt, [K, Ms]))
+    up = ga.allocateTensor(GGMLTensor(gt, [K, Ms]))
+    x = ga.allocateTensor(GGMLTensor(GGMLType.F32, [1, K]))
+    nw = ga.allocateTensor(GGMLTensor(GGMLType.F32, [K]))
+    xn = ga.allocateTensor(GGMLTensor(GGMLType.F32, [K]))
+    full = [ga.allocateTensor(GGMLTensor(GGMLType.F32, [1, M_total])) for _ in range(4)]    # g, u, silu, h
+    ga.setBytes(gate, wg)
+    ga.setBytes(up, wu)
+    ga.setBytes(x, x0)
+    ga.setBytes(nw, nw0)
+    mark = np.full(M_total, -7.0, np.float32)
+    for t in full:
+        ga.setBytes(t, mark)
+    grp.computeSwigluSharded(ga, gate, up, x, full[0], full[1], full[3], row0, M_total, None, silu_full=full[2],
+                             norm_w=nw if with_norm else None, eps=1e-6, normed_dst=xn if with_norm else None)
+    got = [ga.getFloats(t) for t in full]
+    xe = O.rms_norm(x0, nw0, 1e-6, K) if with_norm else x0
+    if with_norm:
+        assert np.allclose(ga.getFloats(xn), xe, rtol=3e-7, atol=1e-9)
+    g = O.matmul(ot, wg, K, Ms, xe, 1)
+    u = O.matmul(ot, wu, K, Ms, xe, 1)
+    sl = slice(row0, row0 + Ms)
+    assert rel_err(got[0][sl], g) <= MATMUL_REL_TOL and rel_err(got[1][sl], u) <= MATMUL_REL_TOL
+    # the epilogue applies the elementwise ops' own roundings to the g / u it stored
+    assert np.allclose(got[2][sl], O.silu(got[0][sl]), rtol=2e-6, atol=1e-12)       # device expf vs libm: <= 2 ulp
+    assert same_f32_bits(got[3][sl], O.mul(got[2][sl], got[1][sl]))
+    for v in got:
+        assert np.all(v[:row0] == -7.0) and np.all(v[row0 + Ms:] == -7.0)
+    grp.close()
+    be.free()

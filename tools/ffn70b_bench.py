@@ -53,6 +53,8 @@ def main():
     ap.add_argument("--layers", type=int, default=8)
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--fused", type=int, default=1, help="world > 1 with --exchange push: gate/up + SwiGLU (+ the RMSNorm before them) "
+                    "+ the push of h as ONE launch (lk_compute_swiglu_sharded); 0 = the separate ops")
     ap.add_argument("--exchange", default="push", choices=["push", "nccl"],
                     help="exchange 1 (h): peer stores + flag barrier, or ncclAllGather")
     args = ap.parse_args()
@@ -124,6 +126,24 @@ def main():
         g_full, u_full, a_full, h_full, y_full = vec(FFN), vec(FFN), vec(FFN), vec(FFN), vec(HIDDEN)
         keep.append((g_full, u_full, h_full, y_full))
         xin = view(cur, [1, HIDDEN])
+        fused = world > 1 and args.exchange == "push" and args.fused
+        if fused:
+            # [RMSNorm ->] gate/up -> SwiGLU -> h slice into every peer, one launch; then the flag barrier
+            d = {"group": group, "gate": w["gate"], "up": w["up"], "x": xin, "g_full": view(g_full, [1, FFN]),
+                 "u_full": view(u_full, [1, FFN]), "silu_full": view(a_full, [1, FFN]), "row0": f0, "M_total": FFN, "peers": peers}
+            if li > 0:          # the RMS_NORM that closes the previous FFN folds into this launch's prologue
+                d.update(x=view(prev_y, [1, HIDDEN]), norm_w=ones, eps=1e-6, normed_dst=cur)
+            nodes.append(node(GGMLOp.NONE, [1, FFN], [], h_full, {"shard_swiglu": d}))
+            nodes.append(node(GGMLOp.NONE, [1], [], h_full, {"shard_barrier": group}))
+            shd = {"shard": (group, h0, HIDDEN, peers)}
+            nodes.append(node(GGMLOp.MUL_MAT, [1, HIDDEN], [w["down"], view(h_full, [1, FFN])], y_full, shd))
+            nodes.append(node(GGMLOp.NONE, [1], [], y_full, {"shard_barrier": group}))
+            xn = vec(HIDDEN)
+            if li == L - 1:     # nothing follows: the closing RMS_NORM on its own
+                nodes.append(node(GGMLOp.RMS_NORM, [HIDDEN], [y_full, ones], xn))
+                nodes[-1].opParams[0] = 0x358637BD
+            prev_y, cur = y_full, xn
+            continue
         sh = {"shard": (group, f0, FFN, None)} if world > 1 else None
         nodes.append(node(GGMLOp.MUL_MAT, [1, FFN if world > 1 else fn_], [w["gate"], xin], g_full, sh))
         nodes.append(node(GGMLOp.MUL_MAT, [1, FFN if world > 1 else fn_], [w["up"], xin], u_full, sh))
@@ -195,7 +215,9 @@ def main():
                "aggregate_weight_GBps": wbytes_ffn / (per_ffn_us * 1e-6) / 1e9,
                "per_gpu_weight_GBps": wbytes_ffn / world / (per_ffn_us * 1e-6) / 1e9,
                "exchanges": "none" if world == 1 else
-               ("ncclAllGather" if args.exchange == "nccl" else "peer-store push + flag barrier") +
+               ("ncclAllGather" if args.exchange == "nccl" else
+                "fused gate/up + SwiGLU + RMSNorm launch with peer-store epilogue + flag barrier" if args.fused else
+                "peer-store push + flag barrier") +
                " (h, 112 KiB) + GEMV peer-store epilogue and flag barrier (y, 32 KiB)",
                "spot_check_rel_err": float(err), "all_ranks_identical_y": bool(same), "barrier_timed_out": bool(timed_out)}
         os.write(json_fd, (json.dumps(out) + "\n").encode())
