@@ -1,9 +1,13 @@
 /*
  * lk_oracle_kq.c — CPU restatement of the reference's K-quant and BitNet 1.58 paths.
  *
- * TEST INFRASTRUCTURE ONLY (see lk_oracle.h).  Parity status: pinned by source citation and by the accuracy
- * thresholds of nativeTest core/GGMLKQuantAccuracyTest.kt / GGMLBitNet158Test.kt (tests/test_oracle_kquants.py);
- * the reference holds no byte-level vectors for these formats.
+ * TEST INFRASTRUCTURE ONLY (see lk_oracle.h).  Parity status: PARITY UNPINNED for Q2_K / Q4_K in the strict sense — the
+ * reference holds no byte-level vectors for these formats, they are Kotlin-only (oracle/_ref, the tree's ggml C, cannot
+ * anchor them) and a literal restatement of its Q2_K / Q4_K quantizer + dequantizer pair does not meet the reference's
+ * own accuracy thresholds.  What does pin this file: source citation line by line, hand-computed block
+ * KATs, a second independent numpy restatement (tests/kq_np.py, bit for bit) and, for Q8_K and BitNet 1.58, the
+ * thresholds / expectations of nativeTest core/GGMLKQuantAccuracyTest.kt and GGMLBitNet158Test.kt
+ * (tests/test_oracle_kquants.py).
  *
  * These are the REFERENCE'S OWN formats, not ggml's: same block sizes as ggml-common.h (84 / 144 / 292 bytes per 256
  * elements) but a simpler field meaning, and the dot products address blocks as the Kotlin code does — including where
