@@ -191,6 +191,17 @@ typedef struct lk_matmul_fusion {
 #define LK_FUSE_SKIP_B_STORE 1
 LK_API lk_status   lk_compute_matmul_fused(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, const lk_tensor *dst,
                                            const lk_matmul_fusion *fusion);
+/* A run of DEPENDENT decode matmuls — the four launches of LlamaDecoderLayer.forward (model/LlamaModel.kt:253-285:
+ * [RMSNorm -> Q/K/V], [O + residual], [RMSNorm -> gate/up + SwiGLU], [down + residual]), possibly across layers — as ONE
+ * persistent launch: link i is exactly the call lk_compute_matmul_fused(a, b, dst, fusion) (fusion may be NULL = plain
+ * N == 1 matmul), links run in order with a grid-wide barrier between them and the weight stream runs ahead across the
+ * hand-offs.  Results are identical to issuing the links one by one.  Up to 8 links, one weight type, device-resident
+ * tensors; anything else returns LK_ENOTIMPL and the caller issues the links itself.                              */
+typedef struct lk_matmul_link {
+    const lk_tensor *a, *b, *dst;
+    const lk_matmul_fusion *fusion;
+} lk_matmul_link;
+LK_API lk_status   lk_compute_matmul_chain(lk_ctx *ctx, const lk_matmul_link *links, int32_t n);
 /* dequantizeTensor(graphAllocator, tensor) — core/GGMLComputeOps.kt:918-964. Bit-exact. dst F32, same ne. */
 LK_API lk_status   lk_compute_dequantize(lk_ctx *ctx, const lk_tensor *src, const lk_tensor *dst);
 /* computeAdd / computeMul F32 same-shape paths — core/GGMLComputeOps.kt:735-759, :811-835 */

@@ -48,6 +48,11 @@ class lk_matmul_fusion(C.Structure):
     ]
 
 
+class lk_matmul_link(C.Structure):
+    _fields_ = [("a", C.POINTER(lk_tensor)), ("b", C.POINTER(lk_tensor)), ("dst", C.POINTER(lk_tensor)),
+                ("fusion", C.POINTER(lk_matmul_fusion))]
+
+
 _lib = None
 
 
@@ -94,6 +99,7 @@ def lib() -> C.CDLL:
         "lk_host_free": (i32, [vp, vp]),
         "lk_compute_matmul": (i32, [vp, tp, tp, tp]),
         "lk_compute_matmul_fused": (i32, [vp, tp, tp, tp, C.POINTER(lk_matmul_fusion)]),
+        "lk_compute_matmul_chain": (i32, [vp, C.POINTER(lk_matmul_link), i32]),
         "lk_compute_dequantize": (i32, [vp, tp, tp]),
         "lk_compute_add": (i32, [vp, tp, tp, tp]),
         "lk_compute_mul": (i32, [vp, tp, tp, tp]),

@@ -46,6 +46,8 @@
 // Numerics: integer dot products are exact; the only roundings are the 23-bit
 // activation rounding and ~4 F32 ops per block.  Measured error vs the oracle is
 // ~1e-6 relative (bound documented in DESIGN.md), far inside the 1e-3 bar.
+#include <algorithm>
+
 #include "lk_common.cuh"
 #include "lk_kernels.h"
 
@@ -256,6 +258,7 @@ struct GemvParams {
     short npeers;
     short nib;            // Q4 nibble order: 0 Kotlin accessors (byte j = elements 2j, 2j+1), 1 ggml / GGUF (byte j = elements j, j+16)
     int rg_shift;         // rg == 1 << rg_shift (row groups are a power of two: no integer division per stage)
+    int ng;               // chained kernel only: warp groups of rg * ncw warps each; group g takes stages g, g + ng, ...
     int64_t row_offset;   // dst index of row 0 (sharded weights)
     unsigned long long *tl;         // timeline buffer (tools/gemv_timeline.cu builds only), else NULL
     // ---- 120 bytes
@@ -302,7 +305,12 @@ __device__ __forceinline__ float fmax3_nan_abs(float a, float b, float c) {   //
 // task = (block column, half): 16 consecutive floats; the two lanes of a pair share a block.
 // Conversion without F2I (quarter-rate pipe): fmaf(v, c, 1.5*2^23) leaves rint(v*c) in the low
 // mantissa bits; a non-finite element poisons the block scale with NaN instead.
-template <int TYPE, int NP, bool FUSED>
+// CG: read the activations / gain with ld.global.cg (L2 only).  The chained kernel below reads vectors that other CTAs
+// of the SAME launch wrote a phase earlier; a non-coherent (ld.global.nc) or L1-cached load could return a stale line.
+template <bool CG>
+__device__ __forceinline__ float4 ld_vec4(const float4 *q) { return CG ? __ldcg(q) : __ldg(q); }
+
+template <int TYPE, int NP, bool FUSED, bool CG = false>
 __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int tid, int nthreads) {
     constexpr int TB = NP * 8 - 2;     // |T| <= 2^TB: 22 (three byte planes) or 14 (two)
     const int ntasks = p.nblk * 2;
@@ -310,17 +318,46 @@ __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int ti
     // (F32 partials per thread, warp shuffles, one pass over <= 28 warp totals) and multiplies with 1/rms and the
     // gain while converting.  1/rms instead of the op's IEEE division: <= 2 ulp from the unfused RMSNorm.
     float rinv = 1.0f;
+    // chained kernel, K <= 16 * nthreads: every thread owns at most one task, so the values loaded for the sum of squares
+    // (and the gain, fetched under the same latency) stay in registers for the conversion: one L2 round trip on the
+    // hand-off's critical path instead of three.  Same per-thread order of operations as the two-pass code.
+    const bool keep = CG && FUSED && p.pro_mode == 1 && ntasks <= nthreads;
+    float v[16], gw[16];
     if (FUSED && p.pro_mode == 1) {
         float *part = (float *)(xs + (size_t)p.nblk * gemv_xslot_words(NP)) - 32;   // tail of the last slots: rewritten below
         float acc = 0.f;
+        if (keep) {
+            if (tid < ntasks) {
+                const float4 *src = (const float4 *)(p.b + (size_t)tid * 16);
+                const float4 *wsrc = (const float4 *)(p.pro_w + (size_t)tid * 16);
+                float4 f[4], g[4];
+#pragma unroll
+                for (int i = 0; i < 4; i++) f[i] = ld_vec4<CG>(src + i);
+                if (p.pro_w) {
+#pragma unroll
+                    for (int i = 0; i < 4; i++) g[i] = ld_vec4<CG>(wsrc + i);
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 4; i++) g[i] = make_float4(1.f, 1.f, 1.f, 1.f);
+                }
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    v[4 * i] = f[i].x; v[4 * i + 1] = f[i].y; v[4 * i + 2] = f[i].z; v[4 * i + 3] = f[i].w;
+                    gw[4 * i] = g[i].x; gw[4 * i + 1] = g[i].y; gw[4 * i + 2] = g[i].z; gw[4 * i + 3] = g[i].w;
+                }
+#pragma unroll
+                for (int i = 0; i < 16; i++) acc = fmaf(v[i], v[i], acc);
+            }
+        } else {
 #pragma unroll 1
         for (int task = tid; task < ntasks; task += nthreads) {
             const float4 *src = (const float4 *)(p.b + (size_t)task * 16);
 #pragma unroll
             for (int i = 0; i < 4; i++) {
-                const float4 f = __ldg(src + i);
+                const float4 f = ld_vec4<CG>(src + i);
                 acc = fmaf(f.x, f.x, acc); acc = fmaf(f.y, f.y, acc); acc = fmaf(f.z, f.z, acc); acc = fmaf(f.w, f.w, acc);
             }
+        }
         }
         acc = warp_sum(acc);
         if ((tid & 31) == 0) part[tid >> 5] = acc;
@@ -334,22 +371,28 @@ __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int ti
     for (int base = 0; base < ntasks; base += nthreads) {
         const int task = base + tid;
         const bool on = task < ntasks;
-        float v[16];
         if (on) {
+            if (!keep) {
             const float4 *src = (const float4 *)(p.b + (size_t)task * 16);
 #pragma unroll
             for (int i = 0; i < 4; i++) {
-                const float4 f = __ldg(src + i);
+                const float4 f = ld_vec4<CG>(src + i);
                 v[4 * i] = f.x; v[4 * i + 1] = f.y; v[4 * i + 2] = f.z; v[4 * i + 3] = f.w;
+            }
             }
             if (FUSED && p.pro_mode == 1) {
 #pragma unroll
                 for (int i = 0; i < 16; i++) v[i] = __fmul_rn(v[i], rinv);
-                if (p.pro_w) {
+                if (keep) {
+                    if (p.pro_w) {
+#pragma unroll
+                        for (int i = 0; i < 16; i++) v[i] = __fmul_rn(v[i], gw[i]);
+                    }
+                } else if (p.pro_w) {
                     const float4 *wsrc = (const float4 *)(p.pro_w + (size_t)task * 16);
 #pragma unroll
                     for (int i = 0; i < 4; i++) {
-                        const float4 f = __ldg(wsrc + i);
+                        const float4 f = ld_vec4<CG>(wsrc + i);
                         v[4 * i] = __fmul_rn(v[4 * i], f.x); v[4 * i + 1] = __fmul_rn(v[4 * i + 1], f.y);
                         v[4 * i + 2] = __fmul_rn(v[4 * i + 2], f.z); v[4 * i + 3] = __fmul_rn(v[4 * i + 3], f.w);
                     }
@@ -434,7 +477,7 @@ enum { GEMV_WAIT_FULL = 0, GEMV_WAIT_X = 1, GEMV_WAIT_END = 2 };
 // cross-lane part of the final reduction: 8 lanes per row, 4 rows per warp per pass
 __device__ __forceinline__ float silu_f(float x) { return __fmul_rn(x, __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-x)))); }   // = lk_elementwise.cu silu1
 
-template <bool FUSED>
+template <bool FUSED, bool CG = false>
 __device__ __forceinline__ void finish_rows(const GemvParams &p, float *dst, const float *red, int nred, int64_t out0, int warp, int lane) {
     const int sub = lane & 7, rsel = lane >> 3;
     const int nc4 = p.red_stride >> 2;   // float4 chunks per row (columns beyond npairs hold zeros)
@@ -457,7 +500,7 @@ __device__ __forceinline__ void finish_rows(const GemvParams &p, float *dst, con
             const int64_t o = out0 + r;
             if (FUSED && p.residual) {             // fused residual ADD (computeAdd's single F32 add, same rounding)
                 if (p.dst_raw) p.dst_raw[o] = v;
-                v = __fadd_rn(p.residual[o], v);
+                v = __fadd_rn(CG ? __ldcg(p.residual + o) : p.residual[o], v);
             }
             dst[o] = v;
 #pragma unroll 1
@@ -735,6 +778,252 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
 }
 
 // ---------------------------------------------------------------------------
+// K1c: a CHAIN of dependent GEMVs as one persistent launch.
+//
+// A decoder layer at batch 1 is four GEMV launches, each of which needs the whole output of the one before
+// ([RMSNorm -> Q/K/V], [O + residual], [RMSNorm -> gate/up + SwiGLU], [down + residual], model/LlamaModel.kt:253-285).
+// As separate launches every hand-off costs a grid completion + launch + parameter fetch + barrier set-up, and the
+// weight stream stops meanwhile.  Here one CTA per SM runs the phases back to back:
+//   * the producer warp streams the CTA's row range of phase 0, then of phase 1, ... through ONE ring of equally
+//     sized slots and never waits for anything but a free slot: weights do not depend on activations, so while the
+//     consumers sit in the hand-off the ring fills with the next phase's rows;
+//   * the consumers separate phases with a grid-wide barrier (arrive counter + generation word in global memory, the
+//     cooperative-groups pattern: bar.sync, one thread fences, arrives and polls) and read every vector another CTA
+//     may have written with ld.global.cg;
+//   * all CHAIN_W consumer warps take part in every phase's prologue, barriers and epilogue.  In the stage loop they
+//     work as `ng` independent groups of rg * ncw warps (K = 4096: two groups of 2 x 4; K = 11008: one group of 11,
+//     five warps without rows): group g computes stages g, g + ng, ... so that, as with two CTAs per SM, one group's
+//     barrier round or slow warp does not stall the other; every working warp waits for and releases every slot, in
+//     order, and warp 0 also releases it for the warps without rows.  Measured (profiles/r01t_gemv_chain_ab.txt): 12
+//     consumer warps with 128 registers beat 15 and 16 (96 registers: spills in the dot-product loop).
+// Results are bit-identical to the same launches issued one by one (same block_dot, same reduction order).
+constexpr int CHAIN_MAX = 8;      // phases per launch (2 decoder layers without attention)
+constexpr int CHAIN_W = 12;       // consumer warps (K up to 12288; with the producer 13 warps: 128 registers each)
+struct GemvChainParams {
+    GemvParams ph[CHAIN_MAX];     // cwarps = CHAIN_W, red_off / x_off / stage_off / nstages identical in every phase
+    int nphase;
+    int slot_bytes;               // ring slot size (>= every phase's stage_rows * row_bytes)
+    int wait_mode;                // GEMV_WAIT_FULL: a weight was written by an op that may still run -> the producer waits too
+    unsigned *bar;                // words 0-1: 64-bit arrival counter (8-byte aligned), word 2: time-outs (never in a healthy run)
+};
+static_assert(sizeof(GemvChainParams) <= 4000, "kernel parameter space");
+static_assert(sizeof(GemvParams) >= 260, "the parameter prefetch below touches five 64-byte lines");
+
+__device__ __forceinline__ unsigned long long ld_acquire_gpu(const unsigned long long *p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void red_release_gpu_add(unsigned long long *p, unsigned long long v) {
+    asm volatile("red.release.gpu.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+template <int TYPE, int NP>
+__global__ void __launch_bounds__((CHAIN_W + 1) * 32, 1) gemv_chain_kernel(const __grid_constant__ GemvChainParams cp) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint64_t *full = (uint64_t *)smem;                   // [GEMV_MAX_STAGES]
+    uint64_t *empty = full + GEMV_MAX_STAGES;            // [GEMV_MAX_STAGES]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int bid = (int)blockIdx.x;
+    const int nslots = cp.ph[0].nstages;
+    float *red = (float *)(smem + cp.ph[0].red_off);
+    uint32_t *xs = (uint32_t *)(smem + cp.ph[0].x_off);
+    uint8_t *ring = smem + cp.ph[0].stage_off;
+    constexpr int NCT = CHAIN_W * 32;
+
+    if (warp == CHAIN_W) {
+        // ===== producer warp: one thread streams this CTA's rows of every phase, in phase order =====
+        if (lane == 0) {
+#pragma unroll 1
+            for (int i = 0; i < nslots; i++) {
+                mbar_init(&full[i], 1);
+                mbar_init(&empty[i], CHAIN_W);
+            }
+            fence_mbar_init();
+        }
+        __syncwarp();
+        __syncthreads();   // consumers may now wait on the barriers
+        if (lane == 0) {
+            if (cp.wait_mode == GEMV_WAIT_FULL) pdl_wait();
+            const uint64_t pol_w = l2_policy_evict_first();
+            int s = 0, round = 0;
+#pragma unroll 1
+            for (int ph = 0; ph < cp.nphase; ph++) {
+                const GemvParams &p = cp.ph[ph];
+                const int ub = p.units_per_cta * bid + min(bid, p.units_rem);
+                const int nrows = (p.units_per_cta + (bid < p.units_rem ? 1 : 0)) * p.unit_rows;
+                const int64_t seg_off = (int64_t)ub * p.unit_rows * p.row_bytes;
+#pragma unroll 1
+                for (int seg = 0; seg < p.nseg; seg++) {
+                    const uint8_t *src = (seg == 0 ? p.a : p.a_seg[seg - 1]) + seg_off;
+#pragma unroll 1
+                    for (int left = nrows; left > 0;) {
+                        if (round > 0) mbar_wait(&empty[s], (round - 1) & 1);
+                        const int rows = min(p.stage_rows, left);
+                        const uint32_t bytes = (uint32_t)(rows * p.row_bytes);
+                        mbar_arrive_expect_tx(&full[s], bytes);
+                        tma_load_1d(ring + (size_t)s * cp.slot_bytes, src, bytes, &full[s], pol_w);
+                        src += bytes; left -= rows;
+                        if (++s == nslots) { s = 0; round++; }
+                    }
+                }
+            }
+        }
+        return;
+    }
+
+    // ===== consumer warps =====
+    __syncthreads();   // barriers initialised by the producer
+    pdl_wait();                // phase 0's activations may be the previous kernel's output
+    pdl_launch_dependents();   // the successor waits for this whole grid anyway; let it be scheduled early
+    // Grid barrier = one 64-bit arrival counter that only ever grows: every launch adds (nphase - 1) * gridDim.x, so between
+    // launches it is a multiple of gridDim.x, and a CTA that reads it late (others have already arrived at barrier 0, which
+    // cannot complete without this CTA) still finds the same base by rounding down.  Barrier k is complete when the counter
+    // reaches base + (k + 1) * gridDim.x: one release-add and one acquire-poll per CTA, no second hop through a last arriver.
+    unsigned long long *const bar_cnt = (unsigned long long *)cp.bar;
+    unsigned long long bar_base = 0;
+    if (tid == 0) {
+        bar_base = ld_acquire_gpu(bar_cnt);
+        bar_base -= bar_base % gridDim.x;
+    }
+    int s = 0, par = 0;
+    constexpr int UNR = 4;
+#pragma unroll 1
+    for (int ph = 0; ph < cp.nphase; ph++) {
+        const GemvParams &p = cp.ph[ph];
+        if (ph > 0) {
+            // ---- grid barrier: every CTA has stored the previous phase's outputs ----
+            asm volatile("bar.sync 1, %0;" ::"r"(NCT) : "memory");
+            if (tid == 0) {
+                red_release_gpu_add(bar_cnt, 1ull);
+                const unsigned long long target = bar_base + (unsigned long long)ph * gridDim.x;
+                unsigned polls = 0;
+                while ((long long)(ld_acquire_gpu(bar_cnt) - target) < 0) {
+                    if (++polls > (1u << 22)) { atomicAdd(cp.bar + 2, 1u); break; }   // never hang the device
+                }
+            }
+            asm volatile("bar.sync 1, %0;" ::"r"(NCT) : "memory");
+        }
+        if (tid == 32 && ph + 1 < cp.nphase) {   // warm the constant cache with the next phase's parameter lines
+            const int *q = (const int *)&cp.ph[ph + 1];
+            const int t0 = q[0], t1 = q[16], t2 = q[32], t3 = q[48], t4 = q[64];
+            asm volatile("" ::"r"(t0), "r"(t1), "r"(t2), "r"(t3), "r"(t4));
+        }
+        const int ub = p.units_per_cta * bid + min(bid, p.units_rem);
+        const int r_begin = ub * p.unit_rows;
+        const int nrows = (p.units_per_cta + (bid < p.units_rem ? 1 : 0)) * p.unit_rows;
+        const int gwarps = p.ncw << p.rg_shift;           // warps per group
+        const int grp = warp / gwarps;                    // my group
+        const int wig = warp - grp * gwarps;
+        const int cw = wig % p.ncw;                       // column warp
+        const int rgi = wig / p.ncw;                      // row group within my group
+        const bool working = grp < p.ng;                  // warps beyond ng groups have no rows in this phase: they skip the
+                                                          // ring altogether (no polling beside the working warps) and warp 0
+                                                          // releases every slot on their behalf
+        const uint32_t my_arrivals = warp == 0 ? (uint32_t)(1 + CHAIN_W - p.ng * gwarps) : 1u;
+        int turn = 0;                                     // whose stage comes next
+        const int col = cw * 32 + lane;                   // block column
+        const bool active = working && col < p.nblk;
+        const int colc = col < p.nblk ? col : 0;
+        const int row_words = p.row_bytes >> 2;
+        const int nseg = p.nseg, epi_mode = p.epi_mode;
+#pragma unroll 1
+        for (int r = warp; r < p.red_rows; r += CHAIN_W)
+            if (lane < GEMV_RED_PAD) red[r * p.red_stride + p.ncw * 8 + lane] = 0.f;
+        prep_x<TYPE, NP, true, true>(p, xs, tid, NCT);
+        asm volatile("bar.sync 1, %0;" ::"r"(NCT) : "memory");   // activation planes (and the padding zeros) written
+
+        XRegs<NP> x;
+        {
+            const uint4 *slot = (const uint4 *)(xs + (size_t)colc * gemv_xslot_words(NP));
+#pragma unroll
+            for (int pl = 0; pl < NP; pl++)
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    const uint4 v = slot[pl * 2 + h];
+                    x.q[pl][4 * h] = v.x; x.q[pl][4 * h + 1] = v.y; x.q[pl][4 * h + 2] = v.z; x.q[pl][4 * h + 3] = v.w;
+                }
+            const uint4 t = slot[NP * 2];
+            x.s = __uint_as_float(t.y);
+            x.c = ((TYPE == T_Q4_0) ? -8.0f : 1.0f) * x.s * __uint_as_float(t.x);
+            x.c2 = x.s * __uint_as_float(t.w);
+        }
+
+        const int rg_words = p.rg * row_words;
+        const int rstep = p.rg * p.red_stride;
+        int red_base = 0;
+        float *const rp0 = red + (size_t)rgi * p.red_stride + (col >> 2);
+        float *rp = rp0;
+#pragma unroll 1
+        for (int seg = 0; seg < nseg; seg++) {
+            float *const seg_dst = seg == 0 ? p.dst : p.dst_seg[seg - 1];
+            if (epi_mode == 1 && seg == 1) rp = rp0 + (size_t)p.pair_off * p.red_stride;
+#pragma unroll 1
+            for (int row0 = 0; row0 < nrows; row0 += p.stage_rows) {
+                if (epi_mode != 1 && row0 + p.stage_rows - red_base > p.red_rows) {
+                    // partial-sum buffer full (a CTA that owns more rows than it holds)
+                    asm volatile("bar.sync 1, %0;" ::"r"(NCT) : "memory");
+                    finish_rows<true, true>(p, seg_dst, red, row0 - red_base, p.row_offset + r_begin + red_base, warp, lane);
+                    asm volatile("bar.sync 1, %0;" ::"r"(NCT) : "memory");
+                    rp -= (size_t)(row0 - red_base) * p.red_stride;
+                    red_base = row0;
+                }
+                const int rows_here = min(p.stage_rows, nrows - row0);
+                int nr = (working && turn == grp) ? (rows_here - rgi + p.rg - 1) >> p.rg_shift : 0;   // my rows in this stage
+                if (++turn == p.ng) turn = 0;
+                if (working) mbar_wait(&full[s], par);
+                const uint32_t *wp = (const uint32_t *)(ring + (size_t)s * cp.slot_bytes) + (size_t)rgi * row_words;
+                float *rq = rp;
+#pragma unroll 1
+                for (; nr >= UNR; nr -= UNR) {
+                    float v[UNR];
+#pragma unroll
+                    for (int u = 0; u < UNR; u++) v[u] = block_dot<TYPE, NP>(wp + u * rg_words, colc, x);
+#pragma unroll
+                    for (int u = 0; u < UNR; u++) v[u] = active ? v[u] : 0.f;
+#pragma unroll
+                    for (int u = 0; u < UNR; u++) v[u] += __shfl_xor_sync(0xffffffffu, v[u], 1);
+#pragma unroll
+                    for (int u = 0; u < UNR; u++) v[u] += __shfl_xor_sync(0xffffffffu, v[u], 2);
+                    if ((lane & 3) == 0) {
+#pragma unroll
+                        for (int u = 0; u < UNR; u++) rq[u * rstep] = v[u];     // one partial per 4 block columns
+                    }
+                    wp += UNR * rg_words;
+                    rq += UNR * rstep;
+                }
+#pragma unroll 1
+                for (; nr > 0; nr--) {
+                    float v = block_dot<TYPE, NP>(wp, colc, x);
+                    v = active ? v : 0.f;
+                    v += __shfl_xor_sync(0xffffffffu, v, 1);
+                    v += __shfl_xor_sync(0xffffffffu, v, 2);
+                    if ((lane & 3) == 0) *rq = v;
+                    wp += rg_words;
+                    rq += rstep;
+                }
+                __syncwarp();
+                if (working && lane == 0) mbar_arrive_n(&empty[s], my_arrivals);  // this warp is done reading the slot
+                rp += (size_t)p.stage_rows * p.red_stride;
+                if (++s == nslots) { s = 0; par ^= 1; }
+            }
+            if (epi_mode == 1) continue;                // the pair is finished together below
+            asm volatile("bar.sync 1, %0;" ::"r"(NCT) : "memory");
+            finish_rows<true, true>(p, seg_dst, red, nrows - red_base, p.row_offset + r_begin + red_base, warp, lane);
+            if (seg + 1 < nseg) {                        // the buffer is reused by the next segment
+                asm volatile("bar.sync 1, %0;" ::"r"(NCT) : "memory");
+                rp = rp0;
+                red_base = 0;
+            }
+        }
+        if (epi_mode == 1) {
+            asm volatile("bar.sync 1, %0;" ::"r"(NCT) : "memory");
+            finish_pair(p, red, nrows, p.pair_off, p.row_offset + r_begin, warp, lane);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
 // host side: shape analysis + launch
 // ---------------------------------------------------------------------------
 template <int TYPE, int MAXW, int MINB, int NP, bool FUSED>
@@ -898,6 +1187,125 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
         case T_Q2_K * 4 + 3: return launch_plain<T_Q2_K, 3>(p, grid, smem, tune.pdl, s);
         default: return cudaErrorNotSupported;
     }
+}
+
+// ---- K1c host side: one parameter block per phase, common shared-memory layout --------------
+cudaError_t launch_gemv_chain(int type, int n, const GemvChainLink *links, const GemvTuning &tune, int sm_count,
+                              cudaStream_t s, unsigned *bar) {
+    if (n < 1 || n > CHAIN_MAX || !links || !bar || block_bytes(type) == 0) return cudaErrorNotSupported;
+    const int bb = block_bytes(type);
+    const int np = tune.act_planes == 2 ? 2 : 3;
+    const int grid = sm_count;
+    const int slot_target = (tune.stage_bytes > 0 ? tune.stage_bytes : 40 * 1024);
+    static_assert(CHAIN_MAX == GEMV_CHAIN_MAX, "lk_kernels.h");
+    GemvChainParams cp = {};
+    int red_bytes = 0, x_bytes = 0, slot_bytes = 0;
+    for (int i = 0; i < n; i++) {
+        const GemvChainLink &L = links[i];
+        const GemvFusion &f = L.fu;
+        GemvParams &p = cp.ph[i];
+        const int64_t K = L.K, M = L.M;
+        if (K <= 0 || M <= 0 || (K % 64) != 0 || K > 32 * 32 * CHAIN_W || M > (1 << 30)) return cudaErrorNotSupported;
+        if (((uintptr_t)L.a & 15) || ((uintptr_t)L.b & 15) || ((uintptr_t)f.pro_w & 15) || ((uintptr_t)f.b_out & 15)) return cudaErrorNotSupported;
+        p.a = (const uint8_t *)L.a; p.b = L.b; p.dst = L.dst;
+        p.nib = (short)(tune.nibble_order ? 1 : 0);
+        p.K = (int)K; p.M = (int)M;
+        p.pro_mode = f.pro_mode; p.pro_w = f.pro_w; p.pro_eps = f.pro_eps; p.b_out = f.b_out;
+        p.residual = f.residual; p.dst_raw = f.dst_raw;
+        if (f.nseg_extra < 0 || f.nseg_extra > 2 || (f.nseg_extra > 0 && f.residual)) return cudaErrorNotSupported;
+        for (int j = 0; j < f.nseg_extra; j++) {
+            if (!f.a_extra[j] || !f.dst_extra[j] || ((uintptr_t)f.a_extra[j] & 15)) return cudaErrorNotSupported;
+            p.a_seg[j] = (const uint8_t *)f.a_extra[j];
+            p.dst_seg[j] = f.dst_extra[j];
+        }
+        p.nseg = 1 + f.nseg_extra;
+        if (f.epi_mode == 1) {
+            if (f.nseg_extra != 1 || !f.epi_out) return cudaErrorNotSupported;
+            p.epi_mode = 1; p.epi_act = f.epi_act; p.epi_out = f.epi_out;
+        }
+        p.wait_mode = GEMV_WAIT_X;
+        p.row_bytes = (int)(K / 32) * bb;
+        p.nblk = (int)(K / 32);
+        p.ncw = (p.nblk + 31) / 32;
+        if (p.ncw > CHAIN_W) return cudaErrorNotSupported;
+        p.rg_shift = 0;
+        const int gtarget = tune.variant > 0 ? tune.variant : 8;   // warps per group to aim for (8: the single launch's shape)
+        while ((2 << p.rg_shift) * p.ncw <= gtarget) p.rg_shift++;
+        p.rg = 1 << p.rg_shift;                        // row groups per warp group
+        p.ng = CHAIN_W / (p.ncw * p.rg);               // warp groups taking turns at the stages
+        p.cwarps = CHAIN_W;                            // every consumer warp takes part in prologue / epilogue
+        p.unit_rows = 1;
+        while ((p.unit_rows * p.row_bytes) % 16) p.unit_rows *= 2;
+        if (M % p.unit_rows) return cudaErrorNotSupported;
+        int quant = p.unit_rows;                       // stage_rows: multiple of unit_rows (TMA size) and of rg
+        while (quant % p.rg) quant += p.unit_rows;
+        {
+            int q4 = p.unit_rows;                      // whole 4-row steps per warp where a slot has room for them
+            while (q4 % (p.rg * 4)) q4 += p.unit_rows;
+            if ((int64_t)q4 * p.row_bytes <= slot_target + slot_target / 4) quant = q4;
+        }
+        int sr = (slot_target / p.row_bytes / quant) * quant;
+        if (sr < quant) sr = quant;
+        p.stage_rows = sr;
+        if ((int64_t)sr * p.row_bytes > 72 * 1024) return cudaErrorNotSupported;
+        slot_bytes = std::max(slot_bytes, sr * p.row_bytes);
+        const int units = (int)(M / p.unit_rows);
+        const int max_cta_rows = (int)(((int64_t)units + grid - 1) / grid) * p.unit_rows;
+        p.units_per_cta = units / grid; p.units_rem = units % grid;
+        p.red_stride = p.ncw * 8 + GEMV_RED_PAD;
+        int red_rows = ((max_cta_rows + p.stage_rows - 1) / p.stage_rows) * p.stage_rows;
+        const int red_cap = (24 * 1024 / (p.red_stride * 4) / p.stage_rows) * p.stage_rows;
+        if (red_rows > red_cap) red_rows = red_cap;
+        if (red_rows < p.stage_rows) red_rows = p.stage_rows;
+        if (p.epi_mode == 1) {
+            p.pair_off = (max_cta_rows + 3) & ~3;
+            red_rows = 2 * p.pair_off;
+            if ((size_t)red_rows * p.red_stride * 4 > 40 * 1024) return cudaErrorNotSupported;
+        }
+        p.red_rows = red_rows;
+        red_bytes = std::max(red_bytes, red_rows * p.red_stride * 4);
+        x_bytes = std::max(x_bytes, p.nblk * gemv_xslot_words(np) * 4);
+    }
+    const int red_off = 256;
+    const int x_off = (red_off + red_bytes + 15) & ~15;
+    const int stage_off = (x_off + x_bytes + 127) & ~127;
+    slot_bytes = (slot_bytes + 127) & ~127;
+    int nslots = (227 * 1024 - stage_off) / slot_bytes;
+    if (tune.max_stages > 0 && nslots > tune.max_stages) nslots = tune.max_stages;
+    if (nslots > GEMV_MAX_STAGES) nslots = GEMV_MAX_STAGES;
+    if (nslots < 2) return cudaErrorNotSupported;
+    for (int i = 0; i < n; i++) {
+        cp.ph[i].red_off = red_off; cp.ph[i].x_off = x_off; cp.ph[i].stage_off = stage_off; cp.ph[i].nstages = nslots;
+    }
+    cp.nphase = n;
+    cp.slot_bytes = slot_bytes;
+    cp.wait_mode = tune.wait_mode == GEMV_WAIT_FULL ? GEMV_WAIT_FULL : GEMV_WAIT_X;
+    cp.bar = bar;
+    const int smem = stage_off + nslots * slot_bytes;
+
+    void (*kern)(const GemvChainParams) = nullptr;
+    switch (type * 4 + np) {
+        case T_Q4_0 * 4 + 2: kern = gemv_chain_kernel<T_Q4_0, 2>; break;
+        case T_Q4_1 * 4 + 2: kern = gemv_chain_kernel<T_Q4_1, 2>; break;
+        case T_Q8_0 * 4 + 2: kern = gemv_chain_kernel<T_Q8_0, 2>; break;
+        case T_Q4_0 * 4 + 3: kern = gemv_chain_kernel<T_Q4_0, 3>; break;
+        case T_Q4_1 * 4 + 3: kern = gemv_chain_kernel<T_Q4_1, 3>; break;
+        case T_Q8_0 * 4 + 3: kern = gemv_chain_kernel<T_Q8_0, 3>; break;
+        default: return cudaErrorNotSupported;
+    }
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3((unsigned)((CHAIN_W + 1) * 32));
+    cfg.dynamicSmemBytes = (size_t)smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = tune.pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, cp);
 }
 
 }  // namespace lk

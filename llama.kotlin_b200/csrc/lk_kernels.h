@@ -58,6 +58,20 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
                         int64_t row_offset, const GemvPeers &peers, const GemvTuning &tune, int sm_count,
                         cudaStream_t s, const GemvFusion *fusion = nullptr);
 
+// K1c: up to GEMV_CHAIN_MAX dependent GEMVs (each with its optional fusions, no peers) as ONE persistent launch with a
+// grid-wide barrier between phases; the weight stream runs ahead across the hand-offs.  Same results as the launches
+// issued one by one.  bar: 3 zero-initialised device words owned by the context (arrivals, generation, time-outs).
+constexpr int GEMV_CHAIN_MAX = 8;
+struct GemvChainLink {
+    const void *a = nullptr;
+    int64_t K = 0, M = 0;
+    const float *b = nullptr;
+    float *dst = nullptr;
+    GemvFusion fu;
+};
+cudaError_t launch_gemv_chain(int type, int n, const GemvChainLink *links, const GemvTuning &tune, int sm_count,
+                              cudaStream_t s, unsigned *bar);
+
 // Generic matmul for any (K, M, N) and a.type in {F32, Q4_0, Q4_1, Q8_0}; reference layouts.
 cudaError_t launch_matmul_generic(int type, const void *a, int64_t K, int64_t M, const float *b, int64_t N,
                                   float *dst, cudaStream_t s, int nib = 0);

@@ -136,6 +136,10 @@ lk_status lk_ctx_create(int32_t device, lk_ctx **out) {
     LK_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     LK_CUDA(nullptr, cudaEventCreate(&ctx->ev0));
     LK_CUDA(nullptr, cudaEventCreate(&ctx->ev1));
+    // grid-barrier words of the chained GEMV (arrivals, generation, time-outs); allocated here because nothing may be
+    // allocated-and-cleared while a launch sequence is being captured
+    LK_CUDA(nullptr, cudaMalloc((void **)&ctx->chain_bar, 16));
+    LK_CUDA(nullptr, cudaMemset(ctx->chain_bar, 0, 16));
     *out = ctx;
     return LK_OK;
 }
@@ -148,6 +152,7 @@ lk_status lk_ctx_destroy(lk_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     lk_comm_destroy(ctx);
     if (ctx->arena) cudaFree(ctx->arena);
+    if (ctx->chain_bar) cudaFree(ctx->chain_bar);
     if (ctx->gemm_ws) cudaFree(ctx->gemm_ws);
     for (void *w : ctx->gemm_ws_retired) cudaFree(w);
     if (ctx->attn_ws) cudaFree(ctx->attn_ws);
@@ -506,8 +511,23 @@ lk_status lk_compute_matmul(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b,
     return finish(sc);
 }
 
-lk_status lk_compute_matmul_fused(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, const lk_tensor *dst,
-                                  const lk_matmul_fusion *f) {
+// One fused GEMV, validated and resolved to device pointers: what lk_compute_matmul_fused launches on its own and
+// lk_compute_matmul_chain launches as one phase of a chain.
+namespace {
+struct FusedLaunch {
+    const void *a = nullptr;
+    int64_t K = 0, M = 0;
+    size_t abytes = 0;
+    const float *x = nullptr;
+    float *out = nullptr;
+    int type = 0;
+    lk::GemvFusion fu;
+    std::vector<std::pair<const void *, size_t>> rd, wr, wt;   // further reads / writes / weights (bookkeeping)
+};
+}  // namespace
+
+static lk_status fused_prepare(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, const lk_tensor *dst,
+                               const lk_matmul_fusion *f, FusedLaunch *L) {
     if (!ctx || !a || !b || !dst || !f) return fail(ctx, LK_EINVAL_ARG, "lk_compute_matmul_fused: NULL argument");
     const int64_t M = a->ne[1], K = a->ne[0], N = b->ne[0];
     if (K != b->ne[1]) return fail(ctx, LK_EINVAL_DIM, "Dim mismatch K: a.ne[0] != b.ne[1]");
@@ -545,9 +565,9 @@ lk_status lk_compute_matmul_fused(lk_ctx *ctx, const lk_tensor *a, const lk_tens
     if (f->norm_w && num_elements(f->norm_w) != K) return fail(ctx, LK_EINVAL_DIM, "fused matmul: norm_w must hold K elements");
     if (f->residual && (num_elements(f->residual) != M || num_elements(f->sum_dst) != M))
         return fail(ctx, LK_EINVAL_DIM, "fused matmul: residual and sum_dst must hold M elements");
-    LK_CUDA(ctx, cudaSetDevice(ctx->device));
     auto ptr = [](const lk_tensor *t) { return t ? (void *)((uint8_t *)t->dev_buf->ptr + t->data_offset) : nullptr; };
-    lk::GemvFusion fu;
+    lk::GemvFusion &fu = L->fu;
+    auto &rd = L->rd; auto &wr = L->wr; auto &wt = L->wt;
     const float *x = (const float *)ptr(b);
     if (f->norm_x) {
         fu.pro_mode = 1; fu.pro_w = (const float *)ptr(f->norm_w); fu.pro_eps = f->eps;
@@ -556,9 +576,6 @@ lk_status lk_compute_matmul_fused(lk_ctx *ctx, const lk_tensor *a, const lk_tens
     }
     float *out = (float *)ptr(dst);
     if (f->residual) { fu.residual = (const float *)ptr(f->residual); fu.dst_raw = out; out = (float *)ptr(f->sum_dst); }
-    lk::GemvTuning tune = ctx->tune;
-    tune.pdl = (ctx->pdl_mode == 2) || (ctx->pdl_mode == 1 && ctx->capturing);
-    std::vector<std::pair<const void *, size_t>> rd, wr, wt;
     rd.push_back({fu.pro_w, (size_t)K * 4});
     rd.push_back({fu.residual, (size_t)M * 4});
     wr.push_back({fu.b_out, (size_t)K * 4});
@@ -575,15 +592,92 @@ lk_status lk_compute_matmul_fused(lk_ctx *ctx, const lk_tensor *a, const lk_tens
         wr.push_back({fu.epi_out, (size_t)M * 4});
         wr.push_back({fu.epi_act, (size_t)M * 4});
     }
-    tune.wait_mode = lk::gemv_wait_mode(ctx, ptr(a), (size_t)lk_tensor_nbytes(a), x, (size_t)K * 4, out, (size_t)M * 4, tune.pdl != 0, &rd, &wr, &wt);
+    L->a = ptr(a); L->abytes = (size_t)lk_tensor_nbytes(a); L->K = K; L->M = M; L->x = x; L->out = out; L->type = a->type;
+    return LK_OK;
+}
+
+lk_status lk_compute_matmul_fused(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, const lk_tensor *dst,
+                                  const lk_matmul_fusion *f) {
+    FusedLaunch L;
+    const lk_status st = fused_prepare(ctx, a, b, dst, f, &L);
+    if (st != LK_OK) return st;
+    LK_CUDA(ctx, cudaSetDevice(ctx->device));
+    lk::GemvTuning tune = ctx->tune;
+    tune.pdl = (ctx->pdl_mode == 2) || (ctx->pdl_mode == 1 && ctx->capturing);
+    tune.wait_mode = lk::gemv_wait_mode(ctx, L.a, L.abytes, L.x, (size_t)L.K * 4, L.out, (size_t)L.M * 4, tune.pdl != 0, &L.rd, &L.wr, &L.wt);
     lk::GemvPeers none;
-    cudaError_t e = lk::launch_gemv(a->type, ptr(a), K, M, x, out, 0, none, tune, ctx->sm_count, ctx->stream, &fu);
+    cudaError_t e = lk::launch_gemv(L.type, L.a, L.K, L.M, L.x, L.out, 0, none, tune, ctx->sm_count, ctx->stream, &L.fu);
     if (e == cudaErrorNotSupported) {
         cudaGetLastError();
         chain_other(ctx, nullptr, 0);      // nothing was launched; the unfused ops that follow do their own bookkeeping
         return fail(ctx, LK_ENOTIMPL, "fused matmul: shape not supported by the streaming GEMV");
     }
     if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "fused matmul launch");
+    count_launch(ctx);
+    return LK_OK;
+}
+
+// A run of dependent fused GEMVs as ONE persistent launch (K1c, lk_gemv.cu): same results as lk_compute_matmul_fused
+// called once per link, in order.
+lk_status lk_compute_matmul_chain(lk_ctx *ctx, const lk_matmul_link *links, int32_t n) {
+    if (!ctx || !links) return fail(ctx, LK_EINVAL_ARG, "lk_compute_matmul_chain: NULL argument");
+    if (n < 1) return fail(ctx, LK_EINVAL_ARG, "lk_compute_matmul_chain: n must be >= 1");
+    if (n > lk::GEMV_CHAIN_MAX) return fail(ctx, LK_ENOTIMPL, "matmul chain: more links than one launch takes");
+    if (!ctx->chain_mode) return fail(ctx, LK_ENOTIMPL, "matmul chain: switched off (gemv_chain = 0)");
+    static const lk_matmul_fusion no_fusion = {};
+    std::vector<FusedLaunch> L((size_t)n);
+    for (int i = 0; i < n; i++) {
+        const lk_status st = fused_prepare(ctx, links[i].a, links[i].b, links[i].dst, links[i].fusion ? links[i].fusion : &no_fusion, &L[(size_t)i]);
+        if (st != LK_OK) return st;
+        if (L[(size_t)i].type != L[0].type) return fail(ctx, LK_ENOTIMPL, "matmul chain: one weight type per chain");
+    }
+    LK_CUDA(ctx, cudaSetDevice(ctx->device));
+    lk::GemvTuning tune = ctx->tune;
+    tune.pdl = (ctx->pdl_mode == 2) || (ctx->pdl_mode == 1 && ctx->capturing);
+    // The consumers wait for everything earlier before they read phase 0's activations; the producer prefetches weights
+    // before that wait unless an op that may still be running wrote one of them.
+    std::vector<lk::GemvChainLink> links_d((size_t)n);
+    bool weight_hazard = false;
+    typedef std::pair<uintptr_t, uintptr_t> Range;
+    auto hit = [&](const void *q, size_t bytes) {
+        const Range r((uintptr_t)q, (uintptr_t)q + bytes);
+        for (const auto *v : {&ctx->chain_writes, &ctx->other_writes})
+            for (const Range &w : *v)
+                if (r.first < w.second && w.first < r.second) return true;
+        return false;
+    };
+    for (int i = 0; i < n; i++) {
+        const FusedLaunch &F = L[(size_t)i];
+        lk::GemvChainLink &d = links_d[(size_t)i];
+        d.a = F.a; d.K = F.K; d.M = F.M; d.b = F.x; d.dst = F.out; d.fu = F.fu;
+        weight_hazard = weight_hazard || hit(F.a, F.abytes);
+        for (const auto &w : F.wt) if (w.first) weight_hazard = weight_hazard || hit(w.first, w.second);
+        // a weight that an earlier link of this chain writes cannot be prefetched at all: not one launch
+        for (int j = 0; j < i; j++) {
+            std::vector<std::pair<const void *, size_t>> wts = F.wt, outs = L[(size_t)j].wr;
+            wts.push_back({F.a, F.abytes});
+            outs.push_back({L[(size_t)j].out, (size_t)L[(size_t)j].M * 4});
+            for (const auto &w : wts)
+                for (const auto &o : outs)
+                    if (w.first && o.first && (uintptr_t)w.first < (uintptr_t)o.first + o.second && (uintptr_t)o.first < (uintptr_t)w.first + w.second)
+                        return fail(ctx, LK_ENOTIMPL, "matmul chain: a link's weight is written by an earlier link");
+        }
+    }
+    tune.wait_mode = weight_hazard ? 0 : 1;
+    const cudaError_t e = lk::launch_gemv_chain(L[0].type, n, links_d.data(), tune, ctx->sm_count, ctx->stream, ctx->chain_bar);
+    if (e == cudaErrorNotSupported) {
+        cudaGetLastError();
+        return fail(ctx, LK_ENOTIMPL, "matmul chain: shapes not supported as one launch");
+    }
+    if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "matmul chain launch");
+    // to whatever follows, the chain is one op that waits for everything before it and completes as a whole
+    ctx->other_writes.clear();
+    for (int i = 0; i < n; i++) {
+        const FusedLaunch &F = L[(size_t)i];
+        chain_other(ctx, F.out, (size_t)F.M * 4);
+        for (const auto &w : F.wr) if (w.first) chain_other(ctx, w.first, w.second);
+    }
+    ctx->chain_launches++;
     count_launch(ctx);
     return LK_OK;
 }
@@ -946,6 +1040,7 @@ lk_status lk_set_option(lk_ctx *ctx, const char *name, int64_t v) {
     else if (n == "gemv_smem_budget") ctx->tune.smem_budget = (int)v;
     else if (n == "gemv_ctas_per_sm") ctx->tune.ctas_per_sm = (int)v;
     else if (n == "gemv_overlap") ctx->overlap_mode = (int)v;
+    else if (n == "gemv_chain") ctx->chain_mode = v ? 1 : 0;
     else if (n == "gemv_act_planes") ctx->tune.act_planes = (v == 2) ? 2 : 3;
     else if (n == "nibble_order") ctx->tune.nibble_order = v ? 1 : 0;
     else if (n == "gemm_tc_min_n") ctx->gemm_tc_min_n = (int)v;
@@ -965,6 +1060,14 @@ int64_t lk_get_option(lk_ctx *ctx, const char *name) {
     if (n == "gemv_smem_budget") return ctx->tune.smem_budget;
     if (n == "gemv_ctas_per_sm") return ctx->tune.ctas_per_sm;
     if (n == "gemv_overlap") return ctx->overlap_mode;
+    if (n == "gemv_chain") return ctx->chain_mode;
+    if (n == "gemv_chain_launches") return ctx->chain_launches;
+    if (n == "gemv_chain_timeouts") {   // grid-barrier time-outs since the context was created (0 in a healthy run); reading synchronises
+        unsigned w[4] = {0, 0, 0, 0};
+        if (cudaStreamSynchronize(ctx->stream) != cudaSuccess || cudaMemcpy(w, ctx->chain_bar, 16, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+        if (w[2]) cudaMemset(ctx->chain_bar, 0, 16);   // a timed-out barrier leaves its arrival count behind
+        return (int64_t)w[2];
+    }
     if (n == "gemv_act_planes") return ctx->tune.act_planes;
     if (n == "nibble_order") return ctx->tune.nibble_order;
     if (n == "gemm_tc_min_n") return ctx->gemm_tc_min_n;

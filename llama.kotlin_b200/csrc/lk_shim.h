@@ -25,6 +25,9 @@ struct lk_ctx {
     // (programmatic dependent launch chain); see gemv_wait_mode() in lk_shim.cu.
     std::vector<std::pair<uintptr_t, uintptr_t>> chain_reads, chain_writes;
     std::vector<std::pair<uintptr_t, uintptr_t>> other_writes;   // outputs of non-GEMV ops since the last GEMV
+    uint32_t *chain_bar = nullptr;   // K1c grid barrier: arrivals, generation, time-outs
+    int chain_mode = 1;              // 0: lk_compute_matmul_chain declines (the caller issues the links one by one)
+    int64_t chain_launches = 0;
     int overlap_mode = 1;  // 0: every GEMV waits for its predecessor before reading x; 1: independent GEMVs overlap
     // device staging arena for host-resident tensors (bump allocated per op)
     uint8_t *arena = nullptr;

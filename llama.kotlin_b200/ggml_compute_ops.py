@@ -95,11 +95,9 @@ def computeMatMul(graphAllocator, context: GGMLContext, a: GGMLTensor, b: GGMLTe
                                       describe(graphAllocator, dst)), lk.handle)
 
 
-def computeMatMulFused(graphAllocator, context, a, b, dst, norm_x=None, norm_w=None, eps: float = 0.0,
-                       residual=None, sum_dst=None, store_b: bool = True, extra=(), silu_dst=None, mul_dst=None) -> bool:
-    """computeMatMul with the RMS_NORM that produces `b` and / or the ADD that consumes `dst` folded into the GEMV
-    launch (lk_compute_matmul_fused).  Returns False when the library declines the shape (LK_ENOTIMPL): the
-    caller then issues the unfused ops."""
+def _fusion_struct(graphAllocator, norm_x=None, norm_w=None, eps: float = 0.0, residual=None, sum_dst=None,
+                   store_b: bool = True, extra=(), silu_dst=None, mul_dst=None):
+    """lk_matmul_fusion for one launch; returns (struct, keep-alive list of the tensor descriptors it points to)."""
     keep = [describe(graphAllocator, t) if t is not None else None for t in (norm_x, norm_w, residual, sum_dst)]
     f = B.lk_matmul_fusion()
     f.norm_x = C.pointer(keep[0]) if keep[0] is not None else None
@@ -119,9 +117,40 @@ def computeMatMulFused(graphAllocator, context, a, b, dst, norm_x=None, norm_w=N
         if t is not None:
             keep.append(describe(graphAllocator, t))
             setattr(f, name, C.pointer(keep[-1]))
+    return f, keep
+
+
+def computeMatMulFused(graphAllocator, context, a, b, dst, **fusion) -> bool:
+    """computeMatMul with the RMS_NORM that produces `b` and / or the ADD that consumes `dst` folded into the GEMV
+    launch (lk_compute_matmul_fused); keywords: norm_x, norm_w, eps, residual, sum_dst, store_b, extra, silu_dst,
+    mul_dst.  Returns False when the library declines the shape (LK_ENOTIMPL): the caller then issues the unfused
+    ops."""
+    f, _keep = _fusion_struct(graphAllocator, **fusion)
     ctx = _ctx_of(graphAllocator)
     st = B.lib().lk_compute_matmul_fused(ctx.handle, describe(graphAllocator, a), describe(graphAllocator, b),
                                          describe(graphAllocator, dst), C.byref(f))
+    if st == B.LK_ENOTIMPL:
+        return False
+    B.check(st, ctx.handle)
+    return True
+
+
+def computeMatMulChain(graphAllocator, context, links) -> bool:
+    """A run of dependent decode matmuls as ONE persistent launch (lk_compute_matmul_chain): `links` is a list of
+    (a, b, dst, fusion keywords or None), each exactly one computeMatMulFused / computeMatMul (N == 1) call; they run in
+    order.  Returns False when the library declines (LK_ENOTIMPL): the caller then issues the links one by one."""
+    arr = (B.lk_matmul_link * len(links))()
+    keep = []
+    for i, (a, b, dst, fusion) in enumerate(links):
+        d = [describe(graphAllocator, a), describe(graphAllocator, b), describe(graphAllocator, dst)]
+        keep.append(d)
+        arr[i].a, arr[i].b, arr[i].dst = C.pointer(d[0]), C.pointer(d[1]), C.pointer(d[2])
+        if fusion:
+            f, k = _fusion_struct(graphAllocator, **fusion)
+            keep.append((f, k))
+            arr[i].fusion = C.pointer(f)
+    ctx = _ctx_of(graphAllocator)
+    st = B.lib().lk_compute_matmul_chain(ctx.handle, arr, len(links))
     if st == B.LK_ENOTIMPL:
         return False
     B.check(st, ctx.handle)

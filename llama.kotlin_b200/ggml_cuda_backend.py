@@ -101,6 +101,11 @@ class GGMLCudaBackend:
     def __init__(self, device: int = 0):
         self.lk = ops.LkContext(device)
         self.fuseOps = True          # fold RMS_NORM / ADD neighbours into the decode GEMV inside captured sequences
+        # runs of DEPENDENT decode GEMVs as one persistent launch (lk_compute_matmul_chain): True / False, or None = where
+        # it was measured to pay: graphs with an attention step between the runs (+19 % tok/s at 2048 cached positions;
+        # with a one-position context four separate launches are 2 % faster, profiles/r01t_gemv_chain_ab.txt)
+        self.chainOps = None
+        self.maxChain = 8            # links per launch (the library's limit)
         self._bt = GGMLCudaBufferType(self)
         self._captured = {}      # id(graph) -> (lk_graph handle, node signature)
         self.useCudaGraphs = True
@@ -300,6 +305,7 @@ class GGMLCudaBackend:
                             skip.update((si, mi))
             i = members[-1] + 1
         self._groups, self._pairs = group_of, pair_of
+        self._gemv = {i for i, t in enumerate(nodes) if is_gemv(t)}
         self._steps = self._planAttentionSteps(nodes, skip)
         return rms_of, add_of, skip
 
@@ -352,30 +358,107 @@ class GGMLCudaBackend:
             return
         rms_of, add_of, skip = self._plan(graph)
         stored = set()                       # RMS_NORM nodes whose dst has been written
+        pending = []                         # decode GEMVs (with their fusions) waiting to go out as one chained launch
+
+        def flush():
+            items, pending[:] = list(pending), []
+            for c in range(0, len(items), self.maxChain):
+                self._runChain(ga, nodes, items[c:c + self.maxChain], rms_of, add_of, stored)
+
+        chain = bool(self._steps) if self.chainOps is None else bool(self.chainOps)
         for i, node in enumerate(nodes):
-            if i in skip:
+            if i in skip or (pending and node.op == GGMLOp.NONE and not isinstance(node.extra, dict)):
                 continue
-            if i in self._steps:
-                rq, rk, ck, cv, fa = (nodes[k] for k in self._steps[i])
-                scale = struct.unpack("<f", struct.pack("<i", int(fa.opParams[0])))[0]
-                try:
-                    ops.computeAttentionStep(ga, None, rq.src[0], rk.src[0], cv.src[0], rq.src[2], rq.src[1], int(rq.opParams[0]),
-                                             ck.src[1], cv.src[1], scale, fa, qRopeDst=rq, kRopeDst=rk)
-                except NotImplementedError:      # the library declined this shape: the five ops, in graph order
-                    for k in self._steps[i]:
-                        self._computeNode(ga, nodes[k])
+            if chain and i in self._gemv:
+                # only DEPENDENT launches are chained (a link reads what the link before it wrote); independent GEMVs
+                # keep the pairwise-overlapped launches, which stream faster than any serial order
+                if pending and not self._dependsOn(nodes, i, pending[-1], rms_of, add_of):
+                    flush()
+                pending.append(i)
                 continue
-            if i in self._groups:
-                if self._runGroup(ga, nodes, i, rms_of, stored):
-                    continue
-                # declined: every member (and the SILU / MUL pair) on its own, in graph order
-                for m in self._groups[i]:
-                    self._runOne(ga, nodes, m, rms_of, add_of, stored)
-                if i in self._pairs:
-                    for k in self._pairs[i]:
-                        self._computeNode(ga, nodes[k])
-                continue
-            self._runOne(ga, nodes, i, rms_of, add_of, stored)
+            flush()
+            self._runPlanned(ga, nodes, i, rms_of, add_of, stored)
+        flush()
+
+    def _linkSpans(self, nodes, i, rms_of, add_of):
+        """(reads, writes) of the launch the planner makes at GEMV node i, weights left out."""
+        node = nodes[i]
+        reads, writes = [], [self._span(node)]
+        if i in rms_of:
+            r = nodes[rms_of[i]]
+            reads.append(self._span(r.src[0]))
+            writes.append(self._span(r))
+        else:
+            reads.append(self._span(node.src[1]))
+        if i in self._groups:
+            writes += [self._span(nodes[m]) for m in self._groups[i][1:]]
+            if i in self._pairs:
+                writes += [self._span(nodes[k]) for k in self._pairs[i]]
+        elif i in add_of:
+            a = nodes[add_of[i]]
+            reads.append(self._span(a.src[1] if self._key(a.src[0]) == self._key(node) else a.src[0]))
+            writes.append(self._span(a))
+        return reads, writes
+
+    def _dependsOn(self, nodes, i, j, rms_of, add_of) -> bool:
+        reads, _ = self._linkSpans(nodes, i, rms_of, add_of)
+        _, writes = self._linkSpans(nodes, j, rms_of, add_of)
+        return any(r[0] == w[0] and r[1] < w[2] and w[1] < r[2] for r in reads for w in writes)
+
+    def _linkArgs(self, nodes, i, rms_of, add_of, stored):
+        """(a, b, dst, fusion keywords) of the launch the planner makes at GEMV node i: one link of a chain."""
+        node, kw = nodes[i], {}
+        if i in self._groups:
+            kw["extra"] = [(nodes[m].src[0], nodes[m]) for m in self._groups[i][1:]]
+            if i in self._pairs:
+                si, mi = self._pairs[i]
+                kw.update(silu_dst=nodes[si], mul_dst=nodes[mi])
+        elif i in add_of:
+            a = nodes[add_of[i]]
+            kw.update(residual=a.src[1] if self._key(a.src[0]) == self._key(node) else a.src[0], sum_dst=a)
+        if i in rms_of:
+            r = nodes[rms_of[i]]
+            eps = struct.unpack("<f", struct.pack("<i", int(r.opParams[0])))[0]
+            kw.update(norm_x=r.src[0], norm_w=r.src[1], eps=eps, store_b=rms_of[i] not in stored)
+            stored.add(rms_of[i])
+        return (node.src[0], node.src[1], node, kw or None)
+
+    def _runChain(self, ga, nodes, items, rms_of, add_of, stored) -> None:
+        """Consecutive GEMV launches of the plan as one lk_compute_matmul_chain; one by one when the library declines."""
+        if len(items) >= 2:
+            saved = set(stored)
+            links = [self._linkArgs(nodes, i, rms_of, add_of, stored) for i in items]
+            if ops.computeMatMulChain(ga, None, links):
+                return
+            stored.clear()
+            stored.update(saved)
+        for i in items:
+            self._runPlanned(ga, nodes, i, rms_of, add_of, stored)
+
+    def _runPlanned(self, ga, nodes, i, rms_of, add_of, stored) -> None:
+        """Node i as the plan has it: attention step, stacked group, fused single launch or the plain op."""
+        node = nodes[i]
+        if i in self._steps:
+            rq, rk, ck, cv, fa = (nodes[k] for k in self._steps[i])
+            scale = struct.unpack("<f", struct.pack("<i", int(fa.opParams[0])))[0]
+            try:
+                ops.computeAttentionStep(ga, None, rq.src[0], rk.src[0], cv.src[0], rq.src[2], rq.src[1], int(rq.opParams[0]),
+                                         ck.src[1], cv.src[1], scale, fa, qRopeDst=rq, kRopeDst=rk)
+            except NotImplementedError:      # the library declined this shape: the five ops, in graph order
+                for k in self._steps[i]:
+                    self._computeNode(ga, nodes[k])
+            return
+        if i in self._groups:
+            if self._runGroup(ga, nodes, i, rms_of, stored):
+                return
+            # declined: every member (and the SILU / MUL pair) on its own, in graph order
+            for m in self._groups[i]:
+                self._runOne(ga, nodes, m, rms_of, add_of, stored)
+            if i in self._pairs:
+                for k in self._pairs[i]:
+                    self._computeNode(ga, nodes[k])
+            return
+        self._runOne(ga, nodes, i, rms_of, add_of, stored)
 
     def _runGroup(self, ga, nodes, i, rms_of, stored) -> bool:
         members = self._groups[i]

@@ -232,6 +232,10 @@ def test_decoder_layer_with_attention_decodes_tokens(O, tname, hidden, ffn, H):
     # the device caches hold the oracle's rows
     for la, (_, _, st) in zip(attn, host):
         assert rel_err(ga.getFloats(la.keys)[:ntok * hidden], st["kc"][:ntok * hidden]) <= 1e-3
+    # with attention steps in the graph the planner's own choice is the chained GEMV launch: [Q/K/V], attention,
+    # [O, gate/up, down, next layer's Q/K/V] as one launch, attention, [O, gate/up, down]
+    assert be.chainOps is None and be.lk.get_option("gemv_chain_launches") == 2
+    assert be.lk.get_option("gemv_chain_timeouts") == 0
     be.free()
 
 

@@ -1,0 +1,181 @@
+"""K1c — a run of dependent decode GEMVs as ONE persistent launch (lk_compute_matmul_chain, lk_gemv.cu
+gemv_chain_kernel): the four launches of LlamaDecoderLayer.forward (model/LlamaModel.kt:253-285) with a grid-wide
+barrier between them.  Checked against the same links issued one by one (bit for bit where no RMSNorm prologue is
+involved: the sum of squares is taken by twice as many threads in the chained kernel, so 1/rms may differ in its last
+bit) and, through the layer graph, against the oracle composition."""
+import numpy as np
+import pytest
+
+import llama_kotlin_b200 as lk
+from conftest import same_f32_bits, synth_acts, synth_weights
+from llama_kotlin_b200 import GGMLTensor, GGMLType
+from llama_kotlin_b200.ggml_compute_ops import computeMatMulChain
+from test_gpu_parity import MATMUL_REL_TOL, Q4_0, Q8_0, QT, rel_err
+
+pytestmark = pytest.mark.gpu
+BB = {"Q4_0": 18, "Q8_0": 34, "Q4_1": 20}
+
+
+def _dev(ga):
+    def dev(t, shape, data=None):
+        tt = ga.allocateTensor(GGMLTensor(t, shape))
+        if data is not None:
+            ga.setBytes(tt, data)
+        return tt
+    return dev
+
+
+@pytest.mark.parametrize("tname", ["Q4_0", "Q8_0", "Q4_1"])
+@pytest.mark.parametrize("hidden,ffn", [(128, 320), (512, 1408), (4096, 11008)])
+def test_chain_equals_the_links_one_by_one(O, tname, hidden, ffn):
+    """plain -> residual -> gate/up + SwiGLU -> down + residual: four links, every tensor any link writes is bit-identical
+    to what the same four lk_compute_matmul_fused calls store."""
+    gt, ot = QT[tname]
+    be = lk.GGMLCudaBackend(0)
+    wbytes = (2 * hidden * hidden + 3 * hidden * ffn) // 32 * BB[tname]
+    ga = lk.GGMLGraphAllocator(be, size=wbytes + 40 * (hidden + ffn) * 4 + (1 << 20))
+    dev = _dev(ga)
+    W1 = dev(gt, [hidden, hidden], O.quantize(ot, synth_weights(7000, hidden, hidden)))
+    W2 = dev(gt, [hidden, hidden], O.quantize(ot, synth_weights(7001, hidden, hidden)))
+    Wg = dev(gt, [hidden, ffn], O.quantize(ot, synth_weights(7002, ffn, hidden)))
+    Wu = dev(gt, [hidden, ffn], O.quantize(ot, synth_weights(7003, ffn, hidden)))
+    Wd = dev(gt, [ffn, hidden], O.quantize(ot, synth_weights(7004, hidden, ffn)))
+    x0, r0 = synth_acts(7005, hidden), synth_acts(7006, hidden)
+    x = dev(GGMLType.F32, [1, hidden], x0)
+    res = dev(GGMLType.F32, [hidden], r0)
+
+    def outputs():
+        z = lambda n, flat=False: dev(GGMLType.F32, [n] if flat else [1, n], np.zeros(n, np.float32))   # noqa: E731
+        return dict(y1=z(hidden), y2=z(hidden), s2=z(hidden, True), g=z(ffn), u=z(ffn), act=z(ffn, True), h=z(ffn, True),
+                    y3=z(hidden), s3=z(hidden, True))
+
+    def links(o):
+        col = lambda t: GGMLTensor(GGMLType.F32, [1, t.numElements()], bufferId=t.bufferId, dataOffset=t.dataOffset, buffer=t.buffer)   # noqa: E731
+        s2b, hb = col(o["s2"]), col(o["h"])
+        return [(W1, x, o["y1"], None),
+                (W2, o["y1"], o["y2"], dict(residual=res, sum_dst=o["s2"])),
+                (Wg, s2b, o["g"], dict(extra=[(Wu, o["u"])], silu_dst=o["act"], mul_dst=o["h"])),
+                (Wd, hb, o["y3"], dict(residual=o["s2"], sum_dst=o["s3"]))]
+    one, ch = outputs(), outputs()
+    for a, b, d, kw in links(one):
+        if kw is None:
+            lk.computeMatMul(ga, None, a, b, d)
+        else:
+            assert lk.computeMatMulFused(ga, None, a, b, d, **kw)
+    n0 = be.lk.get_option("gemv_chain_launches")
+    assert computeMatMulChain(ga, None, links(ch))
+    be.lk.sync()
+    assert be.lk.get_option("gemv_chain_launches") == n0 + 1
+    assert be.lk.get_option("gemv_chain_timeouts") == 0
+    for k in one:
+        assert same_f32_bits(ga.getFloats(ch[k]), ga.getFloats(one[k])), k
+    # and the first link against the oracle
+    assert rel_err(ga.getFloats(ch["y1"]), O.matmul(ot, O.quantize(ot, synth_weights(7000, hidden, hidden)), hidden, hidden, x0, 1)) <= MATMUL_REL_TOL
+    be.free()
+
+
+def test_chain_with_rms_prologues_and_many_launches(O):
+    """Two links with the RMSNorm prologue, launched 50 times back to back (the barrier words are reused by every
+    launch): same answer every time, within the 1/rms rounding of the separate launches."""
+    hidden, ffn = 512, 1408
+    be = lk.GGMLCudaBackend(0)
+    ga = lk.GGMLGraphAllocator(be, size=(hidden * hidden + 2 * hidden * ffn) // 32 * 18 + 64 * (hidden + ffn) * 4 + (1 << 20))
+    dev = _dev(ga)
+    Wq = dev(GGMLType.Q4_0, [hidden, hidden], O.quantize(Q4_0, synth_weights(7100, hidden, hidden)))
+    Wg = dev(GGMLType.Q4_0, [hidden, ffn], O.quantize(Q4_0, synth_weights(7101, ffn, hidden)))
+    Wu = dev(GGMLType.Q4_0, [hidden, ffn], O.quantize(Q4_0, synth_weights(7102, ffn, hidden)))
+    x = dev(GGMLType.F32, [hidden], synth_acts(7103, hidden) * 2)
+    w1 = dev(GGMLType.F32, [hidden], (1 + 0.1 * synth_acts(7104, hidden)).astype(np.float32))
+    w2 = dev(GGMLType.F32, [hidden], (1 + 0.1 * synth_acts(7105, hidden)).astype(np.float32))
+
+    def run(chain):
+        z = lambda n, flat=False: dev(GGMLType.F32, [n] if flat else [1, n], np.zeros(n, np.float32))   # noqa: E731
+        n1, q, s, n2, g, u, h = z(hidden), z(hidden), z(hidden, True), z(hidden), z(ffn), z(ffn), z(ffn, True)
+        ls = [(Wq, n1, q, dict(norm_x=x, norm_w=w1, eps=1e-6, residual=x, sum_dst=s)),
+              (Wg, n2, g, dict(norm_x=s, norm_w=w2, eps=1e-6, extra=[(Wu, u)], mul_dst=h))]
+        if chain:
+            assert computeMatMulChain(ga, None, ls)
+        else:
+            for a, b, d, kw in ls:
+                assert lk.computeMatMulFused(ga, None, a, b, d, **kw)
+        be.lk.sync()
+        return [ga.getFloats(t) for t in (n1, q, s, n2, g, u, h)]
+    ref = run(False)
+    first = run(True)
+    for a, b in zip(first, ref):
+        assert rel_err(a, b) <= 2e-6
+    for _ in range(50):
+        again = run(True)
+        for a, b in zip(again, first):
+            assert same_f32_bits(a, b)
+    assert be.lk.get_option("gemv_chain_timeouts") == 0
+    be.free()
+
+
+def test_chain_argument_errors_and_declines(O):
+    be = lk.GGMLCudaBackend(0)
+    ga = lk.GGMLGraphAllocator(be, size=1 << 22)
+    dev = _dev(ga)
+    K = M = 128
+    a4 = dev(GGMLType.Q4_0, [K, M], O.quantize(Q4_0, synth_weights(1, M, K)))
+    a8 = dev(GGMLType.Q8_0, [K, M], O.quantize(Q8_0, synth_weights(2, M, K)))
+    x = dev(GGMLType.F32, [1, K], synth_acts(3, K))
+    y = dev(GGMLType.F32, [1, M], np.zeros(M, np.float32))
+    z = dev(GGMLType.F32, [1, M], np.zeros(M, np.float32))
+    with pytest.raises(lk.IllegalArgumentException):
+        computeMatMulChain(ga, None, [])
+    assert computeMatMulChain(ga, None, [(a4, x, y, None)] * 9) is False            # more links than one launch takes
+    assert computeMatMulChain(ga, None, [(a4, x, y, None), (a8, y, z, None)]) is False   # one weight type per chain
+    bad = dev(GGMLType.F32, [1, M + 1], np.zeros(M + 1, np.float32))
+    with pytest.raises(lk.IllegalArgumentException):                                 # each link is validated like computeMatMul
+        computeMatMulChain(ga, None, [(a4, x, y, None), (a4, y, bad, None)])
+    be.lk.set_option("gemv_chain", 0)
+    assert computeMatMulChain(ga, None, [(a4, x, y, None), (a4, y, z, None)]) is False
+    be.lk.set_option("gemv_chain", 1)
+    assert computeMatMulChain(ga, None, [(a4, x, y, None), (a4, y, z, None)])
+    be.lk.sync()
+    ref = O.matmul(Q4_0, O.quantize(Q4_0, synth_weights(1, M, K)), K, M, synth_acts(3, K), 1)
+    assert rel_err(ga.getFloats(y), ref) <= MATMUL_REL_TOL
+    be.free()
+
+
+@pytest.mark.parametrize("hidden,ffn", [(256, 704), (4096, 11008)])
+def test_layer_graph_planner_chains_the_gemv_launches(O, hidden, ffn):
+    """graphCompute with the chain pass on and off: 8 GEMV launches of two layers become one chained launch, every
+    tensor the graph names agrees within the RMSNorm rounding, replays repeat bit for bit."""
+    from llama_kotlin_b200.llama_layer import alloc_layer, build_decoder_graph, weight_shapes
+    outs, launches = [], []
+    for chain in (True, False):
+        be = lk.GGMLCudaBackend(0)
+        be.chainOps = chain
+        shapes = weight_shapes(hidden, ffn)
+        ga = lk.GGMLGraphAllocator(be, size=2 * (sum(M * K // 32 * 18 for M, K in shapes.values()) + 64 * ffn * 4) + (1 << 20))
+        rng = np.random.default_rng(78)
+        x = ga.allocateTensor(GGMLTensor(GGMLType.F32, [hidden]))
+        ga.setBytes(x, rng.normal(0, 1, hidden).astype(np.float32))
+        stack = []
+        for li in range(2):
+            L = alloc_layer(ga, GGMLType.Q4_0, hidden, ffn)
+            for i, (n, (M, K)) in enumerate(shapes.items()):
+                ga.setBytes(L.weights[n], O.quantize(Q4_0, synth_weights(650 + 10 * li + i, M, K)))
+            ga.setBytes(L.attn_norm, (1 + 0.1 * rng.normal(0, 1, hidden)).astype(np.float32))
+            ga.setBytes(L.ffn_norm, (1 + 0.1 * rng.normal(0, 1, hidden)).astype(np.float32))
+            stack.append(L)
+        graph, out = build_decoder_graph(ga, stack, x, hidden, ffn)
+        before = be.lk.launch_count()
+        assert be.graphCompute(graph) == lk.GGMLStatus.SUCCESS
+        launches.append(be.lk.launch_count() - before)
+        first = [ga.getFloats(n) for n in graph.nodes]
+        for _ in range(5):
+            assert be.graphCompute(graph) == lk.GGMLStatus.SUCCESS
+        again = [ga.getFloats(n) for n in graph.nodes]
+        for a, b in zip(first, again):
+            assert same_f32_bits(a, b)
+        if chain:
+            assert be.lk.get_option("gemv_chain_launches") == 1
+            assert be.lk.get_option("gemv_chain_timeouts") == 0
+        outs.append(first)
+        be.free()
+    assert launches[0] < launches[1]
+    for c, u in zip(*outs):
+        assert rel_err(c, u) <= 2e-6

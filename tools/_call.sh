@@ -1,13 +1,11 @@
 set -x
 mkdir -p gpurun_out
-timeout 300 python -m pytest tests/test_gpu_parity.py -x -q -k "swiglu_sharded" 2>&1 | tail -2
-TR="python -m torch.distributed.run --nnodes=1 --master-addr 127.0.0.1"
-rm -f gpurun_out/u_ffn70b.jsonl
-for n in 8 4; do
-  timeout 300 $TR --nproc-per-node $n --master-port 2963$n tools/ffn70b_bench.py 2>gpurun_out/u_err_$n.txt | tail -1 >> gpurun_out/u_ffn70b.jsonl
+rm -f gpurun_out/w_*.txt
+timeout 300 python -m pytest tests/test_gpu_chain.py -x -q 2>&1 | tail -15 > gpurun_out/w_tests.txt
+for c in 0 128 512 2048; do
+for o in "max_chain=8" "max_chain=1"; do
+  timeout 200 python tools/layer_bench.py --ctx $c --opt $o 2>&1 | tail -1 | python -c "
+import json,sys
+d=json.loads(sys.stdin.read()); print('$o ctx$c', round(d['us_per_layer'],2), round(d['tok_s'],1), d['finite_output'])" >> gpurun_out/w_layer.txt
 done
-timeout 300 $TR --nproc-per-node 8 --master-port 29641 tools/ffn70b_bench.py --fused 0 2>/dev/null | tail -1 >> gpurun_out/u_ffn70b.jsonl
-python -c "
-import json
-for l in open('gpurun_out/u_ffn70b.jsonl'):
-    d=json.loads(l); print(d['n_gpus'], round(d['us_per_ffn'],1), round(d['aggregate_weight_GBps']), d['exchanges'][:40], d.get('spot_check_rel_err'), d.get('all_ranks_identical_y'), d.get('barrier_timed_out'))"
+done

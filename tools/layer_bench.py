@@ -104,6 +104,9 @@ def main():
         k, v = kv.split("=")
         if k == "nofuse":
             be.fuseOps = not int(v)
+        elif k == "max_chain":          # links per chained launch (1 = every GEMV its own launch)
+            be.maxChain = max(int(v), 1)
+            be.chainOps = None if int(v) == 0 else int(v) > 1      # 0 = the planner's own choice
         else:
             be.lk.set_option(k, int(v))
     peak = 0.0
