@@ -65,6 +65,9 @@ def run(lk, be, qtype: str = "Q4_0", layers: int = 32, steps: int = 50, warmup: 
     if drop_ops:     # timing experiments only (the numbers are then meaningless): how much of the step do these ops cost?
         graph.nodes = [n for n in graph.nodes if n.op.name not in drop_ops]
     lkc = be.lk
+    launches0, chains0 = lkc.launch_count(), int(lkc.get_option("gemv_chain_launches"))
+    assert be.graphCompute(graph) == lk.GGMLStatus.SUCCESS          # captures: the launch counters move here only
+    launches, chains = lkc.launch_count() - launches0, int(lkc.get_option("gemv_chain_launches")) - chains0
     for _ in range(warmup):
         assert be.graphCompute(graph) == lk.GGMLStatus.SUCCESS
     lkc.sync()
@@ -77,11 +80,11 @@ def run(lk, be, qtype: str = "Q4_0", layers: int = 32, steps: int = 50, warmup: 
     res = {"workload": f"synthetic Llama-2-7B decoder stack, {qtype}, batch 1, " +
                        (f"RoPE + KV cache + decode attention over {ctx_len} positions ({heads} heads), " if ctx_len else "one-position context, ") +
                        f"{layers} layers with distinct weights ({layers * wbytes / 1e9:.2f} GB > L2), {18 if ctx_len else 13} graph nodes per layer",
-           "ctx_len": ctx_len, "kv_bytes_read_per_layer": kv_read, "launches_per_token": int(be.lk.get_option("graph_launches")) if False else None,
+           "ctx_len": ctx_len, "kv_bytes_read_per_layer": kv_read, "launches_per_token": int(launches),
+           "chained_gemv_launches_per_token": int(chains),
            "layers": layers, "ms_per_token": ms, "tok_s": 1e3 / ms, "layer_tok_s": layers * 1e3 / ms,
            "us_per_layer": ms * 1e3 / layers, "weight_bytes_per_layer": wbytes,
            "weight_GBps": layers * wbytes / (ms * 1e-3) / 1e9, "finite_output": bool(np.all(np.isfinite(y)))}
-    res.pop("launches_per_token")
     res["hbm_GBps"] = layers * (wbytes + kv_read) / (ms * 1e-3) / 1e9      # weights + KV rows read per token
     if hbm_peak_gbs:
         res["hbm_frac"] = res["hbm_GBps"] / hbm_peak_gbs
