@@ -1,4 +1,3 @@
 mkdir -p gpurun_out
-rm -f gpurun_out/z_probe5.txt
-for m in headline pinned; do timeout 30 python tools/_probe.py $m 2>&1 | tail -3 >> gpurun_out/z_probe5.txt; done
-cat gpurun_out/z_probe5.txt
+timeout 40 python tools/_probe.py > gpurun_out/z_probe6.txt 2>&1
+tail -8 gpurun_out/z_probe6.txt

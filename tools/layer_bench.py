@@ -76,6 +76,7 @@ def run(lk, be, qtype: str = "Q4_0", layers: int = 32, steps: int = 50, warmup: 
         be.graphCompute(graph)
     ms = lkc.timer_stop() / steps
     y = ga.getFloats(out)
+    be.forgetGraph(graph)                 # the capture keeps the graph (and through it this allocator's memory) alive
     kv_read = 2 * ctx_len * hidden * 4
     res = {"workload": f"synthetic Llama-2-7B decoder stack, {qtype}, batch 1, " +
                        (f"RoPE + KV cache + decode attention over {ctx_len} positions ({heads} heads), " if ctx_len else "one-position context, ") +
