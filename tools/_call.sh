@@ -1,3 +1,3 @@
 mkdir -p gpurun_out
-timeout 40 python tools/_probe.py > gpurun_out/z_probe6.txt 2>&1
-tail -8 gpurun_out/z_probe6.txt
+timeout 35 python bench.py --no-cpu-baseline > gpurun_out/v_bench_nocpu.json 2>/dev/null
+tail -c 1500 gpurun_out/v_bench_nocpu.json
