@@ -195,8 +195,13 @@ LK_API lk_status   lk_compute_matmul_fused(lk_ctx *ctx, const lk_tensor *a, cons
  * [RMSNorm -> Q/K/V], [O + residual], [RMSNorm -> gate/up + SwiGLU], [down + residual]), possibly across layers — as ONE
  * persistent launch: link i is exactly the call lk_compute_matmul_fused(a, b, dst, fusion) (fusion may be NULL = plain
  * N == 1 matmul), links run in order with a grid-wide barrier between them and the weight stream runs ahead across the
- * hand-offs.  Results are identical to issuing the links one by one.  Up to 8 links, one weight type, device-resident
- * tensors; anything else returns LK_ENOTIMPL and the caller issues the links itself.                              */
+ * hand-offs.  Results are identical to issuing the links one by one (a link with the RMSNorm prologue may differ in
+ * the last bit of 1/rms: more threads share the sum of squares).  Up to 8 links, one weight type, device-resident
+ * tensors; anything else returns LK_ENOTIMPL and the caller issues the links itself.
+ * The launch is one CTA per SM and all of them must be resident at once: do not run it beside kernels of other
+ * streams that hold SMs indefinitely.  The barrier spins are bounded (the device never hangs); a time-out leaves wrong
+ * results behind and is counted: lk_get_option(ctx, "gemv_chain_timeouts") synchronises, returns the count since the
+ * last read (0 in a healthy run) and re-arms the barrier.  lk_set_option(ctx, "gemv_chain", 0) makes this call decline. */
 typedef struct lk_matmul_link {
     const lk_tensor *a, *b, *dst;
     const lk_matmul_fusion *fusion;
