@@ -519,6 +519,7 @@ def test_decoder_layer_graph_matches_oracle_composition(O, tname, hidden, ffn):
     for blocks, gains in host:
         ref = oracle_layer(O, ot, blocks, gains[0], gains[1], ref, hidden, ffn)
     assert rel_err(got, ref) <= MATMUL_REL_TOL
+    be.free()
 
 
 @pytest.mark.parametrize("tname", ["Q4_0", "Q8_0", "Q4_1"])
