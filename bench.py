@@ -276,6 +276,19 @@ def gpu_arm(args, rank: int, world: int, local_rank: int) -> dict:
     if sampler:
         sampler.window(w0, w1)
 
+    # ---- spread of single steps (median and p10 / p90): each step timed alone, a synchronize on both sides,
+    # so nothing overlaps across steps; not part of `value`
+    step_spread = None
+    if world == 1:
+        singles = []
+        for _ in range(min(args.steps, 50)):
+            lkc.timer_start()
+            step_device()
+            singles.append(lkc.timer_stop())
+        q = np.percentile(np.array(singles), [10, 50, 90])
+        step_spread = {"n": len(singles), "p10_ms": float(q[0]), "median_ms": float(q[1]), "p90_ms": float(q[2]),
+                       "how": "one graph replay between two CUDA events with a synchronize after each (no overlap between steps)"}
+
     # ---- same step with every GEMV forced to wait for its predecessor (a fully dependent chain) ----
     lkc.set_option("gemv_overlap", 0)
     graph_dep = GGMLCGraph(nodes=nodes, allocator=ga)
@@ -338,6 +351,7 @@ def gpu_arm(args, rank: int, world: int, local_rank: int) -> dict:
                                    "step with every GEMV made to wait for its predecessor before reading x",
                    "dependent_chain_GBps": bytes_step * args.steps / (ms_dep * 1e-3) / 1e9,
                    "activation_bits": int(8 * lkc.get_option("gemv_act_planes")),
+                   "single_step_spread": step_spread,
                    "parallelism": "single GPU" if world == 1 else
                                   f"weight rows sharded over {world} ranks (each rank a full 7B-shape shard), outputs stored "
                                   f"into every rank's dst over NVLink from the GEMV epilogue + one flag barrier per step",
