@@ -360,12 +360,12 @@ cudaError_t launch_attn_decode(const float *q, const float *kc, const float *vc,
     p.ws = (float *)((uint8_t *)workspace + (((size_t)nheads * 4 + 255) & ~(size_t)255));
     const dim3 grid((unsigned)nheads, (unsigned)attn_splits(nheads, max_seq, sm_count));
     const size_t smem = attn_smem_bytes(head_dim);
-    static bool attr_done = false;     // > 48 KB of dynamic shared memory needs the opt-in (once per process)
-    if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(attn_decode_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_smem_bytes(128));
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(attn_decode_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_smem_bytes(64));
+    {   // > 48 KB of dynamic shared memory needs the opt-in; the attribute belongs to the (function, device) pair, so it is
+        // set on every launch (a cheap call) instead of once per process: a second lk_ctx may sit on another GPU
+        cudaError_t e = head_dim == 128
+            ? cudaFuncSetAttribute(attn_decode_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_smem_bytes(128))
+            : cudaFuncSetAttribute(attn_decode_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_smem_bytes(64));
         if (e != cudaSuccess) return e;
-        attr_done = true;
     }
     CUtensorMap tmk, tmv;
     cudaError_t me = make_cache_map(&tmk, kc, head_dim, nheads, max_seq);

@@ -159,6 +159,8 @@ lk_status lk_peer_barrier(lk_ctx *ctx, lk_buf *own_flags, lk_buf *const *peer_fl
         memcpy(ctx->peer_flags_host, ptrs, sizeof(ptrs));
     }
     lk::chain_other(ctx, own_flags->ptr, own_flags->size);
+    ctx->barrier_flags = (uint32_t *)own_flags->ptr;
+    ctx->barrier_unchecked++;
     peer_barrier_kernel<<<1, 32, 0, ctx->stream>>>((uint32_t *)own_flags->ptr, (uint32_t *const *)ctx->peer_flags, n, rank, epoch);
     LK_CUDA(ctx, cudaGetLastError());
     if (ctx->capturing) ctx->capture_launches++; else ctx->launches++;

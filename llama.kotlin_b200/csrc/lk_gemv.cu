@@ -259,6 +259,7 @@ struct GemvParams {
     short nib;            // Q4 nibble order: 0 Kotlin accessors (byte j = elements 2j, 2j+1), 1 ggml / GGUF (byte j = elements j, j+16)
     int rg_shift;         // rg == 1 << rg_shift (row groups are a power of two: no integer division per stage)
     int ng;               // chained kernel only: warp groups of rg * ncw warps each; group g takes stages g, g + ng, ...
+    int fix_gap;          // range fix-up: a block with a non-zero |x| below 2^-fix_gap of the block maximum is flagged (>= 255: never)
     int64_t row_offset;   // dst index of row 0 (sharded weights)
     unsigned long long *tl;         // timeline buffer (tools/gemv_timeline.cu builds only), else NULL
     // ---- 120 bytes
@@ -301,6 +302,33 @@ __device__ __forceinline__ float fmax3_nan_abs(float a, float b, float c) {   //
     return d;
 }
 
+// ---- range fix-up -------------------------------------------------------------------------------------------------
+// The planes hold T_k = rint(x_k / s) with ONE scale s = 2^(E-22) per 32-element block, so an element 2^g times smaller
+// than its block's maximum keeps 23 - g bits and one more than 2^23 times smaller becomes 0, where the reference
+// (F32 per element, core/GGMLComputeOps.kt:43-145) keeps 24 bits of every x_k.  That only shows when the large
+// elements meet zero weights (Q4_0 nibble 8), but then it is a 100 % error.  prep_x therefore flags every block that
+// holds a non-zero element below 2^-fix_gap of the block maximum (bit mask in the side words below), and before the
+// partial sums of a row are reduced the CTA adds, for its rows and the flagged blocks only,
+//     sum_k w(i, k) * r_k,   r_k = x_k - T_k * s   (exact in F32: both are multiples of ulp(x_k), |r_k| <= s / 2)
+// with the reference's per-element weight formula, into the padding columns of the partial-sum buffer: x_k = T_k s + r_k
+// exactly, so a flagged block is computed from the full F32 activations.  Cold path: natural activations flag a
+// block in < 2 % of launches at the default fix_gap = 20 (P[|x| < 2^-20 max] ~ 2e-6 per element for N(0, 1)); the hot loop
+// is untouched.  Elements between 2^-fix_gap and 1 of the maximum carry the documented absolute error <= s / 2.
+constexpr int GEMV_SIDE_OFF = 128;        // bytes 128..255 of the barrier area: rinv, any-flag word, 28 mask words (896 block columns)
+struct GemvSide {
+    float rinv;
+    uint32_t any;
+    uint32_t mask[28];
+};
+static_assert(sizeof(GemvSide) <= 128, "side words share the first 256 bytes with the 16 mbarriers");
+template <int TYPE> __host__ __device__ constexpr bool gemv_has_fixup() { return TYPE == T_Q4_0 || TYPE == T_Q4_1 || TYPE == T_Q8_0; }
+
+__device__ __forceinline__ float fmin3_abs(float a, float b, float c) {   // min(|a|, |b|, |c|)
+    float d;
+    asm("min.abs.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+    return d;
+}
+
 // ---- activations -> byte planes, cooperatively by the consumer threads -------------------
 // task = (block column, half): 16 consecutive floats; the two lanes of a pair share a block.
 // Conversion without F2I (quarter-rate pipe): fmaf(v, c, 1.5*2^23) leaves rint(v*c) in the low
@@ -311,7 +339,7 @@ template <bool CG>
 __device__ __forceinline__ float4 ld_vec4(const float4 *q) { return CG ? __ldcg(q) : __ldg(q); }
 
 template <int TYPE, int NP, bool FUSED, bool CG = false>
-__device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int tid, int nthreads) {
+__device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int tid, int nthreads, GemvSide *side) {
     constexpr int TB = NP * 8 - 2;     // |T| <= 2^TB: 22 (three byte planes) or 14 (two)
     const int ntasks = p.nblk * 2;
     // Fused RMSNorm prologue (K3 folded in): every CTA needs all of x anyway, so it also takes the sum of squares
@@ -365,6 +393,7 @@ __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int ti
         float tot = 0.f;
         for (int w = 0; w < (nthreads >> 5); w++) tot += part[w];
         rinv = 1.0f / sqrtf(tot / (float)p.K + p.pro_eps);
+        if (tid == 0) side->rinv = rinv;
         asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory");     // `part` is about to be overwritten by the planes
     }
 #pragma unroll 1
@@ -418,6 +447,27 @@ __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int ti
         ab = max(ab, __shfl_xor_sync(0xffffffffu, ab, 1));   // unsigned order: finite < inf < NaN
         int e = (int)(ab >> 23);
         const bool nonfinite = e == 255;
+        if (gemv_has_fixup<TYPE>()) {
+            // Range check, cheap in the common case: min |x| over the block (3-input min.abs, 8 instructions).  Only a block
+            // whose smallest |x| is zero or below 2^-fix_gap of its maximum takes the exact look (smallest NON-ZERO |x| as
+            // 2 * bits - 1: the shift drops the sign, +-0 wraps to 0xFFFFFFFF); both lanes of a pair branch alike.
+            float amin = __uint_as_float(0x7F800000u);
+#pragma unroll
+            for (int i = 0; i < 16; i += 2) amin = fmin3_abs(amin, v[i], v[i + 1]);
+            uint32_t mb = __float_as_uint(amin);
+            mb = min(mb, __shfl_xor_sync(0xffffffffu, mb, 1));
+            if ((int)(mb >> 23) + p.fix_gap < e && !nonfinite) {
+                uint32_t mn = 0xFFFFFFFFu;
+#pragma unroll
+                for (int i = 0; i < 16; i++) mn = min(mn, __float_as_uint(v[i]) * 2u - 1u);
+                mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, 1));
+                const uint32_t t = mn + 1u;
+                if (on && (task & 1) == 0 && t != 0u && (int)(t >> 24) + p.fix_gap < e) {
+                    atomicOr(&side->mask[task >> 6], 1u << ((task >> 1) & 31));
+                    side->any = 1u;
+                }
+            }
+        }
         e = e < 24 ? 24 : e;
         // c = 2^(TB - (e - 126)) so that |x| < 2^(e-126) maps into |T| <= 2^TB;  s = 1/c.  A non-finite block gets
         // s = NaN, which poisons every product of the block whatever its T values are.
@@ -473,6 +523,67 @@ __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int ti
 }
 
 enum { GEMV_WAIT_FULL = 0, GEMV_WAIT_X = 1, GEMV_WAIT_END = 2 };
+
+
+
+// Cold path of the range fix-up (see GemvSide): for rows [row_first, row_first + n) of the packed matrix `a` and every
+// flagged block, sum_k w(i, k) * r_k into padding column j = (rank of the block among the flagged ones) & 7 of the
+// row's partial sums.  Scalars instead of the parameter struct: a reference to kernel parameters would force a local copy.
+template <int TYPE, int NP, bool CG>
+__device__ __noinline__ void gemv_fixup(const uint8_t *a, const float *b, const float *pro_w, int pro_mode, int nib, int row_bytes,
+                                        int nblk, int red_stride, int pad_col, int row_first, int n, float *red, const uint32_t *xs,
+                                        const GemvSide *side, int tid, int nct) {
+    const int nw = (nblk + 31) >> 5;
+    const float rinv = side->rinv;
+#pragma unroll 1
+    for (int item = tid; item < n * GEMV_RED_PAD; item += nct) {
+        const int r = item >> 3, j = item & 7;
+        const uint8_t *rowp = a + (size_t)(row_first + r) * row_bytes;
+        float sum = 0.f;
+        int idx = 0;
+#pragma unroll 1
+        for (int w = 0; w < nw; w++) {
+            uint32_t m = side->mask[w];
+#pragma unroll 1
+            while (m) {
+                const int bit = __ffs((int)m) - 1;
+                m &= m - 1;
+                if ((idx++ & 7) != j) continue;
+                const int blk = w * 32 + bit;
+                const float s = __uint_as_float(xs[(size_t)blk * gemv_xslot_words(NP) + NP * 8 + 1]);
+                const float c = __frcp_rn(s);                                 // a power of two: exact
+                const uint8_t *bp = rowp + (size_t)blk * block_bytes(TYPE);
+                const float d = h2f((uint16_t)(bp[0] | (bp[1] << 8)));
+                float mq = 0.f;
+                if (TYPE == T_Q4_1) mq = h2f((uint16_t)(bp[2] | (bp[3] << 8)));
+                constexpr int QOFF = TYPE == T_Q4_1 ? 4 : 2;
+                float acc = 0.f;
+#pragma unroll 1
+                for (int k = 0; k < 32; k++) {
+                    const int kk = blk * 32 + k;
+                    float v = CG ? __ldcg(b + kk) : b[kk];
+                    if (pro_mode == 1) {                                      // the fused RMSNorm prologue, same roundings as prep_x
+                        v = __fmul_rn(v, rinv);
+                        if (pro_w) v = __fmul_rn(v, CG ? __ldcg(pro_w + kk) : pro_w[kk]);
+                    }
+                    const int T = (int)__float_as_uint(fmaf(v, c, 12582912.0f)) - 0x4B400000;
+                    const float rk = fmaf(-(float)T, s, v);                   // exact residual
+                    float wv;                                                 // the reference's weight, core/GGMLComputeOps.kt:43-145
+                    if (TYPE == T_Q8_0) {
+                        wv = __fmul_rn(d, (float)(int8_t)bp[2 + k]);
+                    } else {
+                        const uint8_t byte = bp[QOFF + (nib ? (k & 15) : (k >> 1))];
+                        const float q = (float)((nib ? (k >> 4) : (k & 1)) ? (byte >> 4) : (byte & 15));
+                        wv = TYPE == T_Q4_0 ? __fmul_rn(d, __fsub_rn(q, 8.0f)) : __fadd_rn(__fmul_rn(d, q), mq);
+                    }
+                    acc = fmaf(wv, rk, acc);
+                }
+                sum += acc;
+            }
+        }
+        red[(size_t)r * red_stride + pad_col + j] = sum;
+    }
+}
 
 // cross-lane part of the final reduction: 8 lanes per row, 4 rows per warp per pass
 __device__ __forceinline__ float silu_f(float x) { return __fmul_rn(x, __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-x)))); }   // = lk_elementwise.cu silu1
@@ -557,6 +668,7 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
     float *red = (float *)(smem + p.red_off);            // [red_rows][red_stride]
     uint32_t *xs = (uint32_t *)(smem + p.x_off);         // [nblk][gemv_xslot_words(NP)]
     uint8_t *stage0 = smem + p.stage_off;
+    GemvSide *side = (GemvSide *)(smem + GEMV_SIDE_OFF);
 
     // The next kernel of the stream may be scheduled beside us as soon as every CTA has signalled.  An independent
     // launch (WAIT_END) signals at once; a launch that waits for its predecessor signals only after that wait, so
@@ -645,16 +757,25 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
 #pragma unroll 1
     for (int r = warp; r < p.red_rows; r += p.cwarps)
         if (lane < GEMV_RED_PAD) red[r * p.red_stride + p.ncw * 8 + lane] = 0.f;
+    if (warp == 0) { if (lane < 28) side->mask[lane] = 0u; if (lane == 28) side->any = 0u; }
     __syncthreads();   // barriers initialised by the producer
     if (p.wait_mode != GEMV_WAIT_END) {
         pdl_wait();                // activations may be the previous kernel's output
         pdl_launch_dependents();   // the next kernel can start its prologue / weight prefetch under our main loop
     }
     if (tid == 0) LK_TL(3);
-    prep_x<TYPE, NP, FUSED>(p, xs, tid, nct);
+    prep_x<TYPE, NP, FUSED>(p, xs, tid, nct, side);
     if (tid == 0) LK_TL(24);
     asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");   // activation planes written
     if (tid == 0) LK_TL(4);
+    // range fix-up (cold): some block holds elements its block scale cannot represent; see GemvSide.  The flag is re-read
+    // from shared memory at each site so that nothing extra stays live across the stage loop.
+#define LK_GEMV_FIXUP(CGF, PRO_W, PRO_MODE, NTHR, AW, ROW_FIRST, NROWS, REDP)                                                        \
+    if (gemv_has_fixup<TYPE>() && *(volatile uint32_t *)(smem + GEMV_SIDE_OFF + 4) != 0u) {                                            \
+        gemv_fixup<TYPE, NP, CGF>(AW, p.b, PRO_W, PRO_MODE, p.nib, p.row_bytes, p.nblk, p.red_stride, p.ncw * 8, ROW_FIRST, NROWS,   \
+                                  REDP, (const uint32_t *)(smem + p.x_off), (const GemvSide *)(smem + GEMV_SIDE_OFF), tid, NTHR);     \
+        asm volatile("bar.sync 1, %0;" ::"r"(NTHR) : "memory");                                                                      \
+    }
 
     XRegs<NP> x;
     {
@@ -691,6 +812,7 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
         if (epi_mode != 1 && row0 + p.stage_rows - red_base > p.red_rows) {
             // partial-sum buffer full (a CTA that owns more rows than it holds)
             asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
+            LK_GEMV_FIXUP(false, FUSED ? p.pro_w : nullptr, FUSED ? p.pro_mode : 0, nct, (!FUSED || seg == 0) ? p.a : p.a_seg[seg - 1], r_begin + red_base, row0 - red_base, red)
             finish_rows<FUSED>(p, seg_dst, red, row0 - red_base, p.row_offset + r_begin + red_base, warp, lane);
             asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
             rp -= (size_t)(row0 - red_base) * p.red_stride;
@@ -759,6 +881,7 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
     if (tid == 0) LK_TL(6);
     asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
     if (tid == 0) LK_TL(20);
+    LK_GEMV_FIXUP(false, FUSED ? p.pro_w : nullptr, FUSED ? p.pro_mode : 0, nct, (!FUSED || seg == 0) ? p.a : p.a_seg[seg - 1], r_begin + red_base, nrows - red_base, red)
     finish_rows<FUSED>(p, seg_dst, red, nrows - red_base, p.row_offset + r_begin + red_base, warp, lane);
     if (seg + 1 < nseg) {                        // the buffer is reused by the next segment
         asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
@@ -768,6 +891,8 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
     }
     if (epi_mode == 1) {
         asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
+        LK_GEMV_FIXUP(false, p.pro_w, p.pro_mode, nct, p.a, r_begin, nrows, red)
+        LK_GEMV_FIXUP(false, p.pro_w, p.pro_mode, nct, p.a_seg[0], r_begin, nrows, red + (size_t)p.pair_off * p.red_stride)
         finish_pair(p, red, nrows, p.pair_off, p.row_offset + r_begin, warp, lane);
     }
     if (tid == 0) {
@@ -829,6 +954,7 @@ __global__ void __launch_bounds__((CHAIN_W + 1) * 32, 1) gemv_chain_kernel(const
     float *red = (float *)(smem + cp.ph[0].red_off);
     uint32_t *xs = (uint32_t *)(smem + cp.ph[0].x_off);
     uint8_t *ring = smem + cp.ph[0].stage_off;
+    GemvSide *side = (GemvSide *)(smem + GEMV_SIDE_OFF);
     constexpr int NCT = CHAIN_W * 32;
 
     if (warp == CHAIN_W) {
@@ -873,6 +999,7 @@ __global__ void __launch_bounds__((CHAIN_W + 1) * 32, 1) gemv_chain_kernel(const
     }
 
     // ===== consumer warps =====
+    if (warp == 0) { if (lane < 28) side->mask[lane] = 0u; if (lane == 28) side->any = 0u; }
     __syncthreads();   // barriers initialised by the producer
     pdl_wait();                // phase 0's activations may be the previous kernel's output
     pdl_launch_dependents();   // the successor waits for this whole grid anyway; let it be scheduled early
@@ -930,7 +1057,7 @@ __global__ void __launch_bounds__((CHAIN_W + 1) * 32, 1) gemv_chain_kernel(const
 #pragma unroll 1
         for (int r = warp; r < p.red_rows; r += CHAIN_W)
             if (lane < GEMV_RED_PAD) red[r * p.red_stride + p.ncw * 8 + lane] = 0.f;
-        prep_x<TYPE, NP, true, true>(p, xs, tid, NCT);
+        prep_x<TYPE, NP, true, true>(p, xs, tid, NCT, side);
         asm volatile("bar.sync 1, %0;" ::"r"(NCT) : "memory");   // activation planes (and the padding zeros) written
 
         XRegs<NP> x;
@@ -963,6 +1090,7 @@ __global__ void __launch_bounds__((CHAIN_W + 1) * 32, 1) gemv_chain_kernel(const
                 if (epi_mode != 1 && row0 + p.stage_rows - red_base > p.red_rows) {
                     // partial-sum buffer full (a CTA that owns more rows than it holds)
                     asm volatile("bar.sync 1, %0;" ::"r"(NCT) : "memory");
+                    LK_GEMV_FIXUP(true, p.pro_w, p.pro_mode, NCT, seg == 0 ? p.a : p.a_seg[seg - 1], r_begin + red_base, row0 - red_base, red)
                     finish_rows<true, true>(p, seg_dst, red, row0 - red_base, p.row_offset + r_begin + red_base, warp, lane);
                     asm volatile("bar.sync 1, %0;" ::"r"(NCT) : "memory");
                     rp -= (size_t)(row0 - red_base) * p.red_stride;
@@ -1009,6 +1137,7 @@ __global__ void __launch_bounds__((CHAIN_W + 1) * 32, 1) gemv_chain_kernel(const
             }
             if (epi_mode == 1) continue;                // the pair is finished together below
             asm volatile("bar.sync 1, %0;" ::"r"(NCT) : "memory");
+            LK_GEMV_FIXUP(true, p.pro_w, p.pro_mode, NCT, seg == 0 ? p.a : p.a_seg[seg - 1], r_begin + red_base, nrows - red_base, red)
             finish_rows<true, true>(p, seg_dst, red, nrows - red_base, p.row_offset + r_begin + red_base, warp, lane);
             if (seg + 1 < nseg) {                        // the buffer is reused by the next segment
                 asm volatile("bar.sync 1, %0;" ::"r"(NCT) : "memory");
@@ -1018,8 +1147,12 @@ __global__ void __launch_bounds__((CHAIN_W + 1) * 32, 1) gemv_chain_kernel(const
         }
         if (epi_mode == 1) {
             asm volatile("bar.sync 1, %0;" ::"r"(NCT) : "memory");
+            LK_GEMV_FIXUP(true, p.pro_w, p.pro_mode, NCT, p.a, r_begin, nrows, red)
+            LK_GEMV_FIXUP(true, p.pro_w, p.pro_mode, NCT, p.a_seg[0], r_begin, nrows, red + (size_t)p.pair_off * p.red_stride)
             finish_pair(p, red, nrows, p.pair_off, p.row_offset + r_begin, warp, lane);
         }
+        // re-arm the range flags for the next phase (its prep_x runs after the grid barrier's bar.sync)
+        if (warp == 0 && side->any != 0u) { if (lane < 28) side->mask[lane] = 0u; if (lane == 28) side->any = 0u; }
     }
 }
 
@@ -1100,6 +1233,7 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
     }
     p.tl = (unsigned long long *)tune.timeline;
     p.wait_mode = tune.wait_mode;
+    p.fix_gap = tune.fix_gap >= 255 ? 255 : std::max(2, tune.fix_gap - (tune.act_planes == 2 ? 8 : 0));
     p.row_bytes = kq ? (int)(K / 256) * (type == T_Q4_K ? 144 : type == T_Q8_K ? 292 : 84) : (int)(K / 32) * bb;
     p.nblk = (int)(K / 32);
     p.ncw = (p.nblk + 31) / 32;
@@ -1224,15 +1358,19 @@ cudaError_t launch_gemv_chain(int type, int n, const GemvChainLink *links, const
             p.epi_mode = 1; p.epi_act = f.epi_act; p.epi_out = f.epi_out;
         }
         p.wait_mode = GEMV_WAIT_X;
+        p.fix_gap = tune.fix_gap >= 255 ? 255 : std::max(2, tune.fix_gap - (np == 2 ? 8 : 0));
         p.row_bytes = (int)(K / 32) * bb;
         p.nblk = (int)(K / 32);
         p.ncw = (p.nblk + 31) / 32;
         if (p.ncw > CHAIN_W) return cudaErrorNotSupported;
         p.rg_shift = 0;
-        const int gtarget = tune.variant > 0 ? tune.variant : 8;   // warps per group to aim for (8: the single launch's shape)
+        // warps per group to aim for (8: the single launch's shape), never more than the kernel has (gemv_warps = 16 is a
+        // setting the sweep tools use: unclamped it gave ng = 0, no warp arriving on empty[] and a producer that spins forever)
+        const int gtarget = std::min(tune.variant > 0 ? tune.variant : 8, CHAIN_W);
         while ((2 << p.rg_shift) * p.ncw <= gtarget) p.rg_shift++;
         p.rg = 1 << p.rg_shift;                        // row groups per warp group
         p.ng = CHAIN_W / (p.ncw * p.rg);               // warp groups taking turns at the stages
+        if (p.ng < 1) return cudaErrorNotSupported;
         p.cwarps = CHAIN_W;                            // every consumer warp takes part in prologue / epilogue
         p.unit_rows = 1;
         while ((p.unit_rows * p.row_bytes) % 16) p.unit_rows *= 2;
@@ -1295,6 +1433,14 @@ cudaError_t launch_gemv_chain(int type, int n, const GemvChainLink *links, const
     }
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
+    // The grid barrier needs every CTA resident at once.  What can be checked is checked: the device must be able to
+    // hold the grid (one CTA of this size per SM on an unpartitioned device); a launch that would not fit is declined
+    // and the caller issues the links one by one.  What cannot be checked from here (another stream or process holding
+    // SMs for longer than the barrier's bounded spin) ends as a counted time-out that lk_sync / lk_buf_download report.
+    int per_sm = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, (CHAIN_W + 1) * 32, (size_t)smem);
+    if (e != cudaSuccess) return e;
+    if (per_sm < 1 || (int64_t)per_sm * sm_count < grid) return cudaErrorNotSupported;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3((unsigned)((CHAIN_W + 1) * 32));

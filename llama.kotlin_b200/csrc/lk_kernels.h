@@ -20,6 +20,8 @@ struct GemvTuning {
     int row_quant = -1;     // stage rows a multiple of 4 per warp: -1 auto (dependent launches only), 0 never, 1 always
     int nibble_order = 0;   // Q4 blocks: 0 = the Kotlin accessors' order (byte j = elements 2j, 2j+1, core/GGMLTypes.kt:647-651),
                             // 1 = canonical ggml / GGUF order (byte j = elements j, j+16, ggml/src/ggml-quants.c:1524-1530)
+    int fix_gap = 20;       // range fix-up: blocks holding a non-zero |x| below 2^-fix_gap of the block maximum are recomputed from the
+                            // F32 activations (lk_gemv.cu, GemvSide); >= 255 switches the detection off
     int wait_mode = 1;      // 0 wait before the weight prefetch, 1 before reading x, 2 at the end (independent launch)
     void *timeline = nullptr;   // tools/gemv_timeline.cu only: per-CTA %globaltimer stamps
 };
@@ -84,11 +86,14 @@ cudaError_t launch_kq_dequantize(int type, const void *src, int64_t n, float *ds
 int kq_type_block_bytes(int type);    // 84 / 144 / 292 / 10, else 0
 int kq_type_block_elems(int type);    // 256 / 256 / 256 / 32, else 0
 
-// K2: tcgen05 prefill GEMM (lk_gemm_tc.cu).  workspace holds the FP16 copy of b.
+// K2: tcgen05 prefill GEMM (lk_gemm_tc.cu).  workspace holds the scaled FP16 copy (hi / lo parts) of b, the column
+// maxima and the column factors.
 size_t gemm_tc_workspace_bytes(int64_t K, int64_t N);
 // cluster: 1, 2 or 4 CTAs (consecutive row tiles) share each activation tile by TMA multicast.
+// precision: 2 = A and b as FP16 hi + lo pairs (3 MMAs per step, F32-grade operands; default), 1 = A hi + lo, b single
+// FP16 (2 MMAs), 0 = single FP16 operands (1 MMA).
 cudaError_t launch_gemm_tc(int type, const void *a, int64_t K, int64_t M, const float *b, int64_t N, float *dst,
-                           void *workspace, int sm_count, int cluster, cudaStream_t s, int nib = 0);
+                           void *workspace, int sm_count, int cluster, cudaStream_t s, int nib = 0, int precision = 2);
 
 // K3-K5 + R4
 // pdl: launch with programmatic stream serialization (the kernels wait for their predecessor themselves), so the

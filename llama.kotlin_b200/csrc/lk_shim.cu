@@ -30,6 +30,30 @@ void chain_other(lk_ctx *ctx, const void *dst, size_t bytes) {
     if (ctx->other_writes.size() > 64) { ctx->other_writes.clear(); ctx->other_writes.push_back(Range(0, ~(uintptr_t)0)); }
     ctx->other_writes.push_back(Range((uintptr_t)dst, (uintptr_t)dst + bytes));
 }
+lk_status check_async_faults(lk_ctx *ctx) {
+    if (ctx->capturing) return LK_OK;
+    if (ctx->chain_unchecked) {
+        ctx->chain_unchecked = 0;
+        unsigned w[4] = {0, 0, 0, 0};
+        if (cudaMemcpy(w, ctx->chain_bar, 16, cudaMemcpyDeviceToHost) != cudaSuccess) return cuda_fail(ctx, cudaGetLastError(), "reading the chain barrier words");
+        if (w[2]) {
+            cudaMemset(ctx->chain_bar, 0, 16);   // a timed-out barrier leaves its arrival count behind: re-arm
+            ctx->chain_timeouts_seen += w[2];
+            return fail(ctx, LK_ECUDA, "chained GEMV: the grid barrier timed out (" + std::to_string(w[2]) +
+                        " CTAs gave up): not all CTAs were resident at once; the results of that launch are invalid");
+        }
+    }
+    if (ctx->barrier_unchecked && ctx->barrier_flags) {
+        ctx->barrier_unchecked = 0;
+        uint32_t w = 0;
+        if (cudaMemcpy(&w, ctx->barrier_flags + 14, 4, cudaMemcpyDeviceToHost) != cudaSuccess) return cuda_fail(ctx, cudaGetLastError(), "reading the peer barrier words");
+        if (w) {
+            cudaMemset(ctx->barrier_flags + 14, 0, 4);
+            return fail(ctx, LK_ECUDA, "lk_peer_barrier: a peer did not arrive within the bounded wait; gathered outputs are invalid");
+        }
+    }
+    return LK_OK;
+}
 // ---- programmatic-dependent-launch chain bookkeeping ---------------------------------------
 // A GEMV launched with the PDL attribute may start while earlier GEMVs of the chain still run.
 // It may skip the wait on its predecessor (GEMV_WAIT_END, the kernel then waits at its very end so
@@ -167,7 +191,7 @@ lk_status lk_ctx_destroy(lk_ctx *ctx) {
 lk_status lk_sync(lk_ctx *ctx) {
     if (!ctx) return fail(nullptr, LK_EINVAL_ARG, "lk_sync: ctx is NULL");
     LK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    return LK_OK;
+    return lk::check_async_faults(ctx);
 }
 
 const char *lk_last_error(lk_ctx *ctx) { return ctx ? ctx->err.c_str() : g_noctx_err.c_str(); }
@@ -186,6 +210,7 @@ lk_status lk_timer_stop(lk_ctx *ctx, float *ms_out) {
     LK_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
     LK_CUDA(ctx, cudaEventSynchronize(ctx->ev1));
     LK_CUDA(ctx, cudaEventElapsedTime(ms_out, ctx->ev0, ctx->ev1));
+    if (cudaStreamQuery(ctx->stream) == cudaSuccess) return lk::check_async_faults(ctx);
     return LK_OK;
 }
 
@@ -243,7 +268,7 @@ lk_status lk_buf_download(lk_buf *buf, uint64_t off, void *host, uint64_t n) {
     LK_CUDA(ctx, cudaMemcpyAsync(host, (uint8_t *)buf->ptr + off, n, cudaMemcpyDeviceToHost, ctx->stream));
     chain_other(ctx, nullptr, 0);
     LK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    return LK_OK;
+    return lk::check_async_faults(ctx);
 }
 
 lk_status lk_buf_copy(lk_buf *dst, uint64_t doff, lk_buf *src, uint64_t soff, uint64_t n) {
@@ -406,6 +431,7 @@ lk_status finish(OpScope &sc) {
     if (sc.any_host) {
         LK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         chain_other(ctx, nullptr, 0);
+        return lk::check_async_faults(ctx);
     }
     return LK_OK;
 }
@@ -498,8 +524,8 @@ lk_status lk_compute_matmul(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b,
         if ((st = gemm_ws_reserve(ctx, lk::gemm_tc_workspace_bytes(K, N))) != LK_OK) return st;
         chain_other(ctx, dd, (size_t)M * N * 4);
         void *ws = (void *)(((uintptr_t)ctx->gemm_ws + 1023) & ~(uintptr_t)1023);
-        e = lk::launch_gemm_tc(a->type, da, K, M, (const float *)db, N, (float *)dd, ws, ctx->sm_count, ctx->gemm_tc_cluster, ctx->stream, ctx->tune.nibble_order);
-        if (e == cudaSuccess) { launched = 2; ctx->gemm_tc_launches++; }   // pack_b_kernel + gemm_tc_kernel
+        e = lk::launch_gemm_tc(a->type, da, K, M, (const float *)db, N, (float *)dd, ws, ctx->sm_count, ctx->gemm_tc_cluster, ctx->stream, ctx->tune.nibble_order, ctx->gemm_tc_precision);
+        if (e == cudaSuccess) { launched = 3; ctx->gemm_tc_launches++; }   // colmax_kernel + pack_b_kernel + gemm_tc_kernel
     }
     if (e == cudaErrorNotSupported) {
         cudaGetLastError();
@@ -678,6 +704,7 @@ lk_status lk_compute_matmul_chain(lk_ctx *ctx, const lk_matmul_link *links, int3
         for (const auto &w : F.wr) if (w.first) chain_other(ctx, w.first, w.second);
     }
     ctx->chain_launches++;
+    ctx->chain_unchecked++;
     count_launch(ctx);
     return LK_OK;
 }
@@ -991,6 +1018,8 @@ lk_status lk_capture_begin(lk_ctx *ctx) {
     LK_CUDA(ctx, cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
     ctx->capturing = true;
     ctx->capture_launches = 0;
+    ctx->capture_chain0 = ctx->chain_unchecked;
+    ctx->capture_barrier0 = ctx->barrier_unchecked;
     chain_other(ctx, nullptr, 0);
     return LK_OK;
 }
@@ -1007,6 +1036,10 @@ lk_status lk_capture_end(lk_ctx *ctx, lk_graph **out) {
     if (e != cudaSuccess) { cudaGraphDestroy(g); return lk::cuda_fail(ctx, e, "cudaGraphInstantiate"); }
     lk_graph *gr = new lk_graph();
     gr->ctx = ctx; gr->graph = g; gr->exec = ex; gr->launches = ctx->capture_launches;
+    gr->chain_launches = ctx->chain_unchecked - ctx->capture_chain0;       // what a replay of this graph contains
+    gr->barrier_launches = ctx->barrier_unchecked - ctx->capture_barrier0;
+    ctx->chain_unchecked = ctx->capture_chain0;                             // capturing launched nothing
+    ctx->barrier_unchecked = ctx->capture_barrier0;
     *out = gr;
     return LK_OK;
 }
@@ -1014,6 +1047,8 @@ lk_status lk_capture_end(lk_ctx *ctx, lk_graph **out) {
 lk_status lk_graph_launch(lk_ctx *ctx, lk_graph *g) {
     if (!ctx || !g) return fail(ctx, LK_EINVAL_ARG, "lk_graph_launch: NULL argument");
     LK_CUDA(ctx, cudaGraphLaunch(g->exec, ctx->stream));
+    ctx->chain_unchecked += g->chain_launches;
+    ctx->barrier_unchecked += g->barrier_launches;
     chain_other(ctx, nullptr, 0);
     ctx->launches += g->launches;
     return LK_OK;
@@ -1043,8 +1078,10 @@ lk_status lk_set_option(lk_ctx *ctx, const char *name, int64_t v) {
     else if (n == "gemv_chain") ctx->chain_mode = v ? 1 : 0;
     else if (n == "gemv_act_planes") ctx->tune.act_planes = (v == 2) ? 2 : 3;
     else if (n == "nibble_order") ctx->tune.nibble_order = v ? 1 : 0;
+    else if (n == "gemv_fix_gap") ctx->tune.fix_gap = v < 2 ? 2 : v > 255 ? 255 : (int)v;
     else if (n == "gemm_tc_min_n") ctx->gemm_tc_min_n = (int)v;
     else if (n == "gemm_tc_cluster") ctx->gemm_tc_cluster = (int)v;
+    else if (n == "gemm_tc_precision") ctx->gemm_tc_precision = v < 0 ? 0 : v > 2 ? 2 : (int)v;
     else return fail(ctx, LK_EINVAL_ARG, "lk_set_option: unknown option " + n);
     return LK_OK;
 }
@@ -1066,13 +1103,18 @@ int64_t lk_get_option(lk_ctx *ctx, const char *name) {
         unsigned w[4] = {0, 0, 0, 0};
         if (cudaStreamSynchronize(ctx->stream) != cudaSuccess || cudaMemcpy(w, ctx->chain_bar, 16, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
         if (w[2]) cudaMemset(ctx->chain_bar, 0, 16);   // a timed-out barrier leaves its arrival count behind
-        return (int64_t)w[2];
+        ctx->chain_unchecked = 0;
+        const int64_t seen = ctx->chain_timeouts_seen + (int64_t)w[2];   // incl. those lk_sync already reported
+        ctx->chain_timeouts_seen = 0;
+        return seen;
     }
     if (n == "gemv_act_planes") return ctx->tune.act_planes;
     if (n == "nibble_order") return ctx->tune.nibble_order;
+    if (n == "gemv_fix_gap") return ctx->tune.fix_gap;
     if (n == "gemm_tc_min_n") return ctx->gemm_tc_min_n;
     if (n == "gemm_tc_cluster") return ctx->gemm_tc_cluster;
     if (n == "gemm_tc_launches") return ctx->gemm_tc_launches;
+    if (n == "gemm_tc_precision") return ctx->gemm_tc_precision;
     return -1;
 }
 

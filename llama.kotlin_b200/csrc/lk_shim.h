@@ -28,6 +28,11 @@ struct lk_ctx {
     uint32_t *chain_bar = nullptr;   // K1c grid barrier: arrivals, generation, time-outs
     int chain_mode = 1;              // 0: lk_compute_matmul_chain declines (the caller issues the links one by one)
     int64_t chain_launches = 0;
+    int64_t chain_unchecked = 0;     // chained launches since the time-out word was last read (lk::check_async_faults)
+    uint32_t *barrier_flags = nullptr;   // this rank's flag words of lk_peer_barrier (word 14 = time-out), NULL before the first barrier
+    int64_t barrier_unchecked = 0;
+    int64_t capture_chain0 = 0, capture_barrier0 = 0;   // the two counters at lk_capture_begin
+    int64_t chain_timeouts_seen = 0;     // time-outs already reported through a status, not yet read through the option
     int overlap_mode = 1;  // 0: every GEMV waits for its predecessor before reading x; 1: independent GEMVs overlap
     // device staging arena for host-resident tensors (bump allocated per op)
     uint8_t *arena = nullptr;
@@ -41,6 +46,7 @@ struct lk_ctx {
     size_t attn_ws_size = 0;
     std::vector<void *> attn_ws_retired;
     int gemm_tc_min_n = 16;                // N >= this takes the tcgen05 GEMM (0 = never); smaller N the generic kernel
+    int gemm_tc_precision = 2;             // FP16 parts per operand of the tcgen05 GEMM: 2 = A hi+lo x b hi+lo (F32-grade, default), 1 = A hi+lo x b, 0 = single
     int gemm_tc_cluster = 1;               // CTAs per cluster sharing an activation tile by multicast (1, 2, 4); 1 measured fastest
     int64_t gemm_tc_launches = 0;          // tcgen05 GEMM launches so far (tests assert the path taken)
     // multi-GPU
@@ -62,12 +68,17 @@ struct lk_graph {
     cudaGraph_t graph = nullptr;
     cudaGraphExec_t exec = nullptr;
     int64_t launches = 0;  // kernels per replay
+    int64_t chain_launches = 0, barrier_launches = 0;   // chained GEMVs / peer barriers per replay (their time-out words are checked at the next sync)
 };
 
 namespace lk {
 lk_status fail(lk_ctx *ctx, lk_status st, const std::string &msg);
 lk_status cuda_fail(lk_ctx *ctx, cudaError_t e, const char *what);
 void chain_other(lk_ctx *ctx, const void *dst, size_t bytes);
+// After a synchronisation point: did a device-side bounded spin give up since the last check (grid barrier of the
+// chained GEMV, cross-GPU flag barrier)?  Such a launch leaves wrong results behind, so every entry point that
+// synchronises (lk_sync, lk_buf_download, lk_timer_stop, host-staged ops) returns LK_ECUDA once and re-arms the barrier.
+lk_status check_async_faults(lk_ctx *ctx);
 // where a PDL-launched GEMV must wait (GEMV_WAIT_*), and chain bookkeeping for it
 int gemv_wait_mode(lk_ctx *ctx, const void *a, size_t abytes, const void *b, size_t bbytes, const void *d, size_t dbytes,
                    bool pdl, const std::vector<std::pair<const void *, size_t>> *more_reads = nullptr,

@@ -110,6 +110,11 @@ class GGMLCudaBackend:
         self._captured = {}      # id(graph) -> (lk_graph handle, node signature, fast key)
         self._graphRefs = {}     # id(graph) -> graph
         self.useCudaGraphs = True
+        # graphCompute is stream-ordered (asynchronous) like every device-resident op.  A device-side fault of the step —
+        # the chained GEMV's grid barrier or a cross-GPU flag barrier giving up after its bounded wait — is reported by
+        # the next call that synchronises (synchronize(), getTensor).  With checkFaults = True graphCompute synchronises
+        # itself and returns GGMLStatus.FAILED for the step that faulted (tests, benches, debugging).
+        self.checkFaults = False
 
     # -- GGMLBackend ---------------------------------------------------------------
     def getGuid(self) -> str:
@@ -567,6 +572,8 @@ class GGMLCudaBackend:
                 B.check(B.lib().lk_graph_launch(self.lk.handle, ent[0]), self.lk.handle)
             else:
                 self._runNodes(ga, graph, fuse=False)
+            if self.checkFaults:
+                self.lk.sync()                   # raises IllegalStateException if a bounded device-side wait gave up
             return GGMLStatus.SUCCESS
         except (B.IllegalArgumentException, B.IndexOutOfBoundsException, B.IllegalStateException,
                 NotImplementedError) as e:

@@ -179,3 +179,32 @@ def test_layer_graph_planner_chains_the_gemv_launches(O, hidden, ffn):
     assert launches[0] < launches[1]
     for c, u in zip(*outs):
         assert rel_err(c, u) <= 2e-6
+
+
+@pytest.mark.parametrize("warps", [4, 12, 16])
+@pytest.mark.parametrize("hidden,ffn", [(4096, 11008), (512, 1408)])
+def test_chain_with_the_gemv_warps_option(O, warps, hidden, ffn):
+    """gemv_warps above the chain kernel's 12 consumer warps (16 is what tools/gemv_sweep.py sets) used to give
+    a phase with no working warp and a producer that spins for ever.  The target is clamped now; a shape that still
+    leaves no warp group is declined.  Either way the call returns and the results are the separate launches'."""
+    be = lk.GGMLCudaBackend(0)
+    ga = lk.GGMLGraphAllocator(be, size=(hidden * hidden + hidden * ffn) // 32 * 18 + 16 * (hidden + ffn) * 4 + (1 << 20))
+    dev = _dev(ga)
+    W1 = dev(GGMLType.Q4_0, [hidden, hidden], O.quantize(Q4_0, synth_weights(7200, hidden, hidden)))
+    W2 = dev(GGMLType.Q4_0, [hidden, ffn], O.quantize(Q4_0, synth_weights(7201, ffn, hidden)))
+    x = dev(GGMLType.F32, [1, hidden], synth_acts(7202, hidden))
+    z = lambda n: dev(GGMLType.F32, [1, n], np.zeros(n, np.float32))   # noqa: E731
+    y1, y2, c1, c2 = z(hidden), z(ffn), z(hidden), z(ffn)
+    lk.computeMatMul(ga, None, W1, x, y1)
+    lk.computeMatMul(ga, None, W2, y1, y2)
+    be.lk.set_option("gemv_warps", warps)
+    try:
+        took = computeMatMulChain(ga, None, [(W1, x, c1, None), (W2, c1, c2, None)])
+        be.lk.sync()
+    finally:
+        be.lk.set_option("gemv_warps", 0)
+    if took:
+        assert same_f32_bits(ga.getFloats(c1), ga.getFloats(y1))
+        assert same_f32_bits(ga.getFloats(c2), ga.getFloats(y2))
+    assert be.lk.get_option("gemv_chain_timeouts") == 0
+    be.free()

@@ -28,6 +28,7 @@ def main():
     ap.add_argument("--rotate-mb", type=int, default=256)
     ap.add_argument("--reps", type=int, default=10)
     ap.add_argument("--cluster", type=int, default=0, help="gemm_tc_cluster option (0 = library default)")
+    ap.add_argument("--precision", type=int, default=-1, help="gemm_tc_precision option: 0 / 1 / 2 FP16 parts per operand (-1 = library default)")
     ap.add_argument("--generic", action="store_true", help="time the CUDA-core kernel instead (gemm_tc_min_n=0)")
     args = ap.parse_args()
 
@@ -42,6 +43,8 @@ def main():
         lkc.set_option("gemm_tc_min_n", 0)
     if args.cluster:
         lkc.set_option("gemm_tc_cluster", args.cluster)
+    if args.precision >= 0:
+        lkc.set_option("gemm_tc_precision", args.precision)
     rng = np.random.default_rng(1)
     for shp in args.shapes:
         M, K, N = (int(v) for v in shp.split("x"))
@@ -76,6 +79,7 @@ def main():
                           "TFLOPs": round(2.0 * M * K * N / (ms * 1e-3) / 1e12, 1),
                           "weight_GBps": round(wb / (ms * 1e-3) / 1e9, 1), "copies": ncopies,
                           "path": "generic" if args.generic else "tcgen05", "cluster": lkc.get_option("gemm_tc_cluster"),
+                          "precision": lkc.get_option("gemm_tc_precision"),
                           "tc_launches_seen": lkc.get_option("gemm_tc_launches") - before}), flush=True)
 
 
