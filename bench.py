@@ -14,10 +14,13 @@ HBM), replayed as one captured op sequence (GGMLCudaBackend.graphCompute -> CUDA
             the oracle's restatement of the reference CPU loops (oracle/, the Kotlin reference
             cannot be built here: no JVM / Konan) on a bounded row sample of the same workload
 
-N > 1 (torchrun, one rank per GPU): weight rows sharded over ranks (rank r owns rows
-[r*M, (r+1)*M) of an N*M-row matrix, i.e. each rank keeps a full 7B-shape shard: weak scaling),
-outputs exchanged into every rank's dst by NVLink peer stores from the GEMV epilogue plus a
-flag barrier (NCCL all-gather with --gather nccl).
+N > 1 (torchrun, one rank per GPU): BASELINE.json configs[4] — the FFN of a synthetic Llama-2-70B layer
+(gate/up 28672x8192, down 8192x28672, Q4_0) with the weight rows sharded over the N ranks, 8 chained FFNs
+per step, both exchanges (h, y) on the critical path: STRONG scaling, value = total weight bytes / time
+(SURVEY §8e).  Exchanges: peer stores from the GEMV epilogue over NVLink with the arrival / wait folded into
+the launches (--gather sync, default), with separate flag-barrier launches (--gather barrier), or
+ncclAllGather for h (--gather nccl).  The weak-scaled config-2 step of round 1 (every rank a full 7B-shape
+shard, one exchange point per step) is kept under config.other_paths.weak_config2.
 """
 from __future__ import annotations
 
@@ -152,9 +155,21 @@ def cpu_arm(qtype: str, seconds_budget: float, steps: int, warmup: int, threads:
             O.matmul(tid, a, K, rows, x, 1, nthreads=threads, rows=(0, min(R, rows)))
     dt = time.perf_counter() - t0
     nbytes = steps * sum(min(R, rows) * K // 32 * bb + 4 * K + 4 * min(R, rows) for rows, K, _, _ in mats)
+    # the reference's real execution mode: ONE thread (core/GGMLScheduler.kt:165-171 runs nodes serially, computeMatMul has
+    # no threading), same loops, on a smaller row sample (~3 s)
+    R1 = int(max(1, min(R, 3.0 * macs_per_s / max(threads, 1) / total_k)))
+    t1 = time.perf_counter()
+    for rows, K, a, x in mats:
+        O.matmul(tid, a, K, rows, x, 1, nthreads=1, rows=(0, min(R1, rows)))
+    dt1 = time.perf_counter() - t1
+    nbytes1 = sum(min(R1, rows) * K // 32 * bb + 4 * K + 4 * min(R1, rows) for rows, K, _, _ in mats)
     return {"value": nbytes / dt / 1e9, "unit": "GB/s", "cores": threads, "kind": "port",
-            "sample": f"first {R} rows of each of the 3 {qtype} GEMV shapes per step, {steps} steps, "
-                      f"oracle/lk_oracle.c (C restatement of computeMatMul; Kotlin/Native not buildable here)",
+            "sample": f"first {R} rows of each of the 3 {qtype} GEMV shapes per step (a row sample of the 96-GEMV step: the rate "
+                      f"per byte is what is compared), {steps} steps, oracle/lk_oracle.c (C restatement of computeMatMul; "
+                      f"Kotlin/Native not buildable here); weights of the sample ({nbytes // max(steps, 1) // (1 << 20)} MiB) partly live in "
+                      f"the host's last-level cache",
+            "single_thread": {"value": nbytes1 / dt1 / 1e9, "unit": "GB/s", "cores": 1,
+                              "sample": f"first {R1} rows of each shape, one pass: the reference itself is single-threaded"},
             "ms_per_step": dt / steps * 1e3}
 
 
@@ -169,25 +184,110 @@ def pinned_array(lkctx, nbytes: int) -> np.ndarray:
 
 
 def gpu_arm(args, rank: int, world: int, local_rank: int) -> dict:
+    """N = 1: the config-2 step (headline) with the other measured paths beside it.  N > 1: config 5 (70B FFN, rows
+    sharded, strong scaling) as the line, the weak-scaled config-2 step under config.other_paths."""
     import torch
     import torch.distributed as dist
 
     import llama_kotlin_b200 as lk
-    from llama_kotlin_b200 import GGMLCGraph, GGMLOp, GGMLTensor, GGMLType
 
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group(backend="cpu:gloo,cuda:nccl", rank=rank, world_size=world,
                                 device_id=torch.device("cuda", local_rank))
+    be = lk.GGMLCudaBackend(local_rank)
+    for opt in args.opt or []:
+        k, v = opt.split("=")
+        be.lk.set_option(k, int(v))
+    if world == 1:
+        res = config2_arm(args, rank, world, local_rank, lk, be, dist, torch)
+    else:
+        res = config5_arm(args, rank, world, local_rank, lk, be, dist, torch)
+    be.free()
+    if world > 1:
+        dist.destroy_process_group()
+    return res
+
+
+def config5_arm(args, rank, world, local_rank, lk, be, dist, torch) -> dict:
+    """BASELINE configs[4] on `world` GPUs; see the module docstring."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import ffn70b_bench
+    peaks = load_peaks()
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    w0 = time.time()
+    l0 = be.lk.launch_count()
+    r = ffn70b_bench.run(lk, be, dist, rank, world, layers=8, steps=args.steps, warmup=max(args.warmup, 3),
+                         mode=args.gather, e2e_steps=min(args.steps, 100))
+    launches = r["launches_per_step"] * args.steps
+    if sampler:
+        sampler.window(w0, time.time())
+    clocks = sampler.stop() if sampler else None
+    # the same step with the round-1 exchanges, for the record (short)
+    alt = {}
+    for mode in ("barrier", "nccl"):
+        if mode != args.gather:
+            a = ffn70b_bench.run(lk, be, dist, rank, world, layers=8, steps=max(10, args.steps // 4), warmup=3, mode=mode)
+            alt[mode] = {k: a[k] for k in ("us_per_ffn", "aggregate_weight_GBps", "launches_per_step", "all_ranks_identical_y",
+                                           "barrier_timed_out")}
+    weak = None
+    if not args.no_extras:
+        wargs = argparse.Namespace(**vars(args))
+        wargs.steps = max(20, args.steps // 4)
+        weak = config2_arm(wargs, rank, world, local_rank, lk, be, dist, torch, brief=True)
+    value = r["aggregate_weight_GBps"]
+    per_rank = r["per_gpu_weight_GBps"]
+    res = {
+        "metric": "Q4_0 matmul aggregate GB/s, Llama-2-70B FFN rows sharded over N GPUs (weight bytes / time incl. both exchanges)",
+        "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f32 (int4 x 24-bit block-fixed-point activations on DP4A, exact int32 block sums, F32 scales and sums)",
+        "data": "synthetic",
+        "config": {"workload": r["workload"], "baseline_config": "BASELINE.json configs[4]", "exchange": r["exchanges"],
+                   "gather": args.gather, "us_per_ffn": r["us_per_ffn"], "weight_bytes_per_ffn": r["weight_bytes_per_ffn"],
+                   "per_gpu_weight_GBps": per_rank, "launches_per_step": r["launches_per_step"],
+                   "l2": f"inputs larger than L2: every rank streams {8 * r['weight_bytes_per_ffn'] // world} B of distinct weights per step",
+                   "parallelism": f"weight rows sharded over {world} ranks, replicated activations, outputs stored into every rank's "
+                                  f"vectors over NVLink from the GEMV epilogue",
+                   "single_gpu_base": "the N = 1 line of this script reports the same 8-FFN step on one GPU under "
+                                      "config.other_paths.ffn70b_1gpu (strong-scaling efficiency = value(N) / (N x that))",
+                   "check": {"spot_check_rel_err": r["spot_check_rel_err"], "all_ranks_identical_y": r["all_ranks_identical_y"],
+                             "barrier_timed_out": r["barrier_timed_out"]},
+                   "other_exchanges": alt,
+                   "other_paths": {"weak_config2": weak}},
+        "e2e": {"value": r["e2e"]["aggregate_weight_GBps"], "unit": "GB/s", "h2d_bytes_per_step": r["e2e"]["h2d_bytes_per_step"],
+                "d2h_bytes_per_step": r["e2e"]["d2h_bytes_per_step"], "ms_per_step": r["e2e"]["ms_per_step"], "api": r["e2e"]["api"]},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "achieved": per_rank, "peak": peak, "unit": "GB/s", "frac": per_rank / peak, "traffic": None,
+                     "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s (B200_PROFILING.md)",
+                     "frac_of_nominal_8000": per_rank / 8000.0, "kernel": "lk::gemv_kernel<Q4_0, fused> (per rank, incl. the exchanges)",
+                     "avg_launch_us": r["ms_per_step"] * 1e3 / max(r["launches_per_step"], 1),
+                     "algorithmic_bytes_per_launch": 8 * r["weight_bytes_per_ffn"] / world / max(r["launches_per_step"], 1)},
+        "clocks": clocks,
+        "check": {"max_err_vs_f64_rows": r["spot_check_rel_err"],
+                  "ok": bool(r["spot_check_rel_err"] <= 1e-3 and r["all_ranks_identical_y"] and not r["barrier_timed_out"])},
+    }
+    return res
+
+
+def load_peaks() -> dict:
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f)
+    except OSError:
+        return {}
+
+
+def config2_arm(args, rank, world, local_rank, lk, be, dist, torch, brief: bool = False) -> dict:
+    """The config-2 step (see the module docstring).  brief: device-resident timing and the check only (the weak-scaled
+    line under other_paths at N > 1)."""
+    from llama_kotlin_b200 import GGMLCGraph, GGMLOp, GGMLTensor, GGMLType
     qtype = args.qtype
     gt = {"Q4_0": GGMLType.Q4_0, "Q4_1": GGMLType.Q4_1, "Q8_0": GGMLType.Q8_0}[qtype]
     bb = BLOCK_BYTES[qtype]
     layers = args.layers
-    be = lk.GGMLCudaBackend(local_rank)
     lkc = be.lk
-    for opt in args.opt or []:
-        k, v = opt.split("=")
-        lkc.set_option(k, int(v))
 
     # ---- device layout: [weights: layers x 3 matrices][acts: layers x sum K][dst: layers x sum M x world]
     wbytes = [M * K // 32 * bb for M, K in SHAPES]
@@ -279,7 +379,7 @@ def gpu_arm(args, rank: int, world: int, local_rank: int) -> dict:
     # ---- spread of single steps (median and p10 / p90): each step timed alone, a synchronize on both sides,
     # so nothing overlaps across steps; not part of `value`
     step_spread = None
-    if world == 1:
+    if world == 1 and not brief:
         singles = []
         for _ in range(min(args.steps, 50)):
             lkc.timer_start()
@@ -289,35 +389,39 @@ def gpu_arm(args, rank: int, world: int, local_rank: int) -> dict:
         step_spread = {"n": len(singles), "p10_ms": float(q[0]), "median_ms": float(q[1]), "p90_ms": float(q[2]),
                        "how": "one graph replay between two CUDA events with a synchronize after each (no overlap between steps)"}
 
-    # ---- same step with every GEMV forced to wait for its predecessor (a fully dependent chain) ----
-    lkc.set_option("gemv_overlap", 0)
-    graph_dep = GGMLCGraph(nodes=nodes, allocator=ga)
+    ms_dep = e2e_s = float("nan")
+    if not brief:
+        # ---- same step with every GEMV forced to wait for its predecessor (a fully dependent chain) ----
+        lkc.set_option("gemv_overlap", 0)
+        graph_dep = GGMLCGraph(nodes=nodes, allocator=ga)
 
-    def step_dep():
-        if be.graphCompute(graph_dep) != lk.GGMLStatus.SUCCESS:
-            raise RuntimeError("graphCompute FAILED")
-    for _ in range(3):
-        step_dep()
-    barrier()
-    lkc.timer_start()
-    for _ in range(args.steps):
-        step_dep()
-    ms_dep = lkc.timer_stop()
-    barrier()
-    lkc.set_option("gemv_overlap", 1)
+        def step_dep():
+            if be.graphCompute(graph_dep) != lk.GGMLStatus.SUCCESS:
+                raise RuntimeError("graphCompute FAILED")
+        for _ in range(3):
+            step_dep()
+        barrier()
+        lkc.timer_start()
+        for _ in range(args.steps):
+            step_dep()
+        ms_dep = lkc.timer_stop()
+        barrier()
+        lkc.set_option("gemv_overlap", 1)
 
-    # ---- end to end: host activations in, host results out, every step -----------------------
-    for _ in range(3):
-        step_e2e()
-    barrier()
-    e0 = time.time()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        step_e2e()
-    barrier()
-    e2e_s = time.perf_counter() - t0
-    if sampler:
-        sampler.window(e0, time.time())
+        # ---- end to end: host activations in, host results out, every step -----------------------
+        for _ in range(3):
+            step_e2e()
+        barrier()
+        e0 = time.time()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            step_e2e()
+        barrier()
+        e2e_s = time.perf_counter() - t0
+        if sampler:
+            sampler.window(e0, time.time())
+    else:
+        ga.deviceBuffer.getTensor(dst_all, y_host.view(np.uint8), 0, y_host.nbytes)     # for the check below
 
     if world > 1:
         t = torch.tensor([ms, e2e_s, ms_dep], dtype=torch.float64, device="cuda")
@@ -328,12 +432,7 @@ def gpu_arm(args, rank: int, world: int, local_rank: int) -> dict:
     # ---- spot check of the timed outputs against exact f64 arithmetic on the host (numpy, not the oracle)
     chk = check_outputs(protos, x_host, y_host, qtype, world, sumM, rank)
 
-    peaks = {}
-    try:
-        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-            peaks = json.load(f)
-    except OSError:
-        pass
+    peaks = load_peaks()
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
     value = bytes_step * args.steps / (ms * 1e-3) / 1e9
@@ -341,7 +440,7 @@ def gpu_arm(args, rank: int, world: int, local_rank: int) -> dict:
     res = {
         "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "scaling": "weak", "vs_baseline": None, "dtype": DTYPE, "data": "synthetic",
         "config": {"workload": workload_name(qtype, layers),
                    "qtype": qtype, "layers": layers, "gemv_per_step": n_gemv,
                    "weight_bytes_per_step_per_gpu": layers * sum(wbytes),
@@ -369,25 +468,93 @@ def gpu_arm(args, rank: int, world: int, local_rank: int) -> dict:
                      "algorithmic_bytes_per_launch": bytes_step / world / n_gemv},
         "clocks": clocks, "check": chk,
     }
-    traffic_file = os.path.join(ROOT, "profiles", "gemv_traffic.json")
-    if os.path.exists(traffic_file):
-        with open(traffic_file) as f:
-            res["roofline"]["traffic"] = json.load(f).get(qtype)
+    res["roofline"].update(measured_traffic(qtype))
     if group is not None:
         res["config"]["barrier_timed_out"] = group.timed_out()
         barrier()
+        be.releaseGraphs()
         group.close()
+    if brief:
+        return {k: res[k] for k in ("metric", "value", "unit", "ms_per_step", "scaling", "gpu_launches", "check")} | {
+            "workload": res["config"]["workload"], "parallelism": res["config"]["parallelism"],
+            "barrier_timed_out": res["config"].get("barrier_timed_out"), "roofline_frac_per_gpu": res["roofline"]["frac"]}
     if world == 1 and not args.no_extras:
         # the other two measured paths of the scope table, reported beside the headline (not part of `value`)
         res["config"]["other_paths"] = {"prefill_gemm": prefill_gemm_line(lk, be, peaks),
                                         "layer_graph": layer_graph_line(lk, be, peak),
                                         "layer_graph_ctx2048": layer_graph_line(lk, be, peak, ctx_len=2048),
                                         "gemv_act16": act16_line(lk, be, graph, step_device, args, bytes_step, peak,
-                                                                 protos, x_host, y_host, ga, dst_all, qtype)}
-    be.free()
-    if world > 1:
-        dist.destroy_process_group()
+                                                                 protos, x_host, y_host, ga, dst_all, qtype),
+                                        "elementwise": elementwise_lines(lk, be, peak),
+                                        "ffn70b_1gpu": ffn70b_line(lk, be, dist, peak)}
     return res
+
+
+DTYPE = ("f32 output; inner products int4/int8 x 24-bit block-fixed-point activations on DP4A with exact int32 block sums, "
+         "F32 scales and F32 sums across blocks (K1); tcgen05 GEMM: FP16 hi+lo operand pairs, F32 accumulation (K2)")
+
+
+def measured_traffic(qtype: str) -> dict:
+    """roofline.traffic = DRAM bytes per launch from an ncu capture of THIS binary (tools/measure_traffic.py writes
+    profiles/gemv_traffic.json with the library's sha256); a record taken from another build is not reported."""
+    import hashlib
+    path = os.path.join(ROOT, "profiles", "gemv_traffic.json")
+    lib = os.path.join(ROOT, "llama.kotlin_b200", "libllamakotlin_cuda.so")
+    out = {"traffic": None, "traffic_source": "no ncu capture of this binary (profiles/gemv_traffic.json is from another build)"}
+    try:
+        with open(path) as f:
+            rec = json.load(f)
+        with open(lib, "rb") as f:
+            sha = hashlib.sha256(f.read()).hexdigest()
+        if rec.get("library_sha256") == sha and rec.get(qtype) is not None:
+            out = {"traffic": rec[qtype], "traffic_source": rec.get("how", "ncu dram__bytes_read.sum + dram__bytes_write.sum, mean per launch")}
+    except (OSError, ValueError):
+        pass
+    return out
+
+
+def elementwise_lines(lk, be, peak) -> dict:
+    """RMSNorm / SiLU*up / softmax stand-alone kernels against the HBM roofline (SURVEY §8d algorithmic bytes per
+    element: 12 / 12 / 8), on vectors larger than L2 so that every launch streams HBM."""
+    from llama_kotlin_b200 import GGMLTensor, GGMLType
+    lkc = be.lk
+    ne0, rows = 4096, 16384                      # 268 MB per F32 tensor
+    n = ne0 * rows
+    ga = lk.GGMLGraphAllocator(be, size=3 * n * 4 + ne0 * 4 + (1 << 20))
+    x = ga.allocateTensor(GGMLTensor(GGMLType.F32, [ne0, rows]))
+    y = ga.allocateTensor(GGMLTensor(GGMLType.F32, [ne0, rows]))
+    d = ga.allocateTensor(GGMLTensor(GGMLType.F32, [ne0, rows]))
+    w = ga.allocateTensor(GGMLTensor(GGMLType.F32, [ne0]))
+    rng = np.random.default_rng(8)
+    chunk = rng.normal(0, 1, ne0 * 256).astype(np.float32)
+    for t in (x, y):
+        for r0 in range(0, rows, 256):
+            ga.deviceBuffer.setTensor(t, chunk, r0 * ne0 * 4, chunk.nbytes)
+    ga.setBytes(w, np.ones(ne0, np.float32))
+    out = {}
+    for name, fn, bpe in (("rms_norm", lambda: lk.computeRmsNorm(ga, None, x, w, 1e-6, d), 8 + 4.0 / rows),
+                          ("silu_mul", lambda: lk.computeSiluMul(ga, None, x, y, d), 12),
+                          ("softmax", lambda: lk.computeSoftMax(ga, None, x, d), 8)):
+        for _ in range(2):
+            fn()
+        lkc.sync()
+        lkc.timer_start()
+        for _ in range(5):
+            fn()
+        ms = lkc.timer_stop() / 5
+        gbps = n * bpe / (ms * 1e-3) / 1e9
+        out[name] = {"elements": n, "row": ne0, "algorithmic_bytes_per_element": round(bpe, 3), "ms": ms, "GBps": gbps,
+                     "roofline": {"bound": "hbm", "achieved": gbps, "peak": peak, "unit": "GB/s", "frac": gbps / peak}}
+    return out
+
+
+def ffn70b_line(lk, be, dist, peak) -> dict:
+    """BASELINE configs[4] on ONE GPU: the strong-scaling base of the --gpus N > 1 lines (same 8-FFN step)."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import ffn70b_bench
+    r = ffn70b_bench.run(lk, be, dist, 0, 1, layers=8, steps=20, warmup=3)
+    return {k: r[k] for k in ("workload", "us_per_ffn", "ms_per_step", "aggregate_weight_GBps", "launches_per_step",
+                              "spot_check_rel_err")} | {"hbm_frac": r["aggregate_weight_GBps"] / peak}
 
 
 def workload_name(qtype: str, layers: int) -> str:
@@ -521,6 +688,8 @@ def main():
     ap.add_argument("--qtype", default="Q4_0", choices=list(BLOCK_BYTES))
     ap.add_argument("--layers", type=int, default=32)
     ap.add_argument("--opt", action="append", help="lk_set_option name=value (tuning experiments)")
+    ap.add_argument("--gather", default="sync", choices=["sync", "barrier", "nccl"],
+                    help="N > 1: how the two exchanges of the sharded FFN are made (see the module docstring)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the config-3 / config-4 lines under config.other_paths")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
@@ -545,9 +714,10 @@ def main():
         out = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": "GB/s", "n_gpus": args.gpus,
                "steps": args.steps, "warmup": max(args.warmup, 1), "ms_per_step": r["ms_per_step"],
                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-               "config": {"workload": workload_name(args.qtype, args.layers),
+               "config": {"workload": workload_name(args.qtype, args.layers), "qtype": args.qtype, "layers": args.layers,
+                          "gemv_per_step": args.layers * len(SHAPES),
                           "sample": "each step is a bounded row sample of that workload, see cpu_baseline.sample"},
-               "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+               "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample", "single_thread")},
                "e2e": {"value": r["value"], "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                "gpu_launches": 0}
         emit(out)
@@ -557,7 +727,7 @@ def main():
     if rank == 0:
         if not args.no_cpu_baseline and world == 1:
             r = cpu_arm(args.qtype, args.cpu_seconds, 5, 1, threads)
-            res["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
+            res["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample", "single_thread")}
         emit(res)
 
 

@@ -41,7 +41,7 @@ extern "C" {
 #define LK_API
 #endif
 
-#define LK_ABI_VERSION 1
+#define LK_ABI_VERSION 2
 #define LK_MAX_DIMS 4           /* GGML_MAX_DIMS, core/GGMLTypes.kt:67 */
 
 /* GGMLType ordinals, core/GGMLTypes.kt:145-153 */
@@ -95,9 +95,14 @@ typedef struct lk_graph lk_graph;  /* captured op sequence (CUDA graph) */
  *   host_base = address of graphAllocator.buffers[bufferId][0] while pinned
  *               (usePinned { addressOf(0) }); buffer_size = that array's size.
  *   dev_buf   = a device buffer from lk_buf_alloc (GGMLCudaBuffer).
- * data_offset = tensor.dataOffset.  nb[] is accepted for completeness; block
- * types ignore it like the reference does and F32 tensors must be
- * contiguous (nb[0]==4, nb[d]==nb[d-1]*ne[d-1]) or all-zero (= contiguous).   */
+ * data_offset = tensor.dataOffset.  nb[]: block types ignore it like the
+ * reference does.  F32 tensors are addressed through nb[] like
+ * GGMLTensor.getFloat / setFloat (core/GGMLTypes.kt:328-380): element
+ * (i0..i3) at data_offset + sum i_d * nb[d]; all-zero nb[] means contiguous.
+ * A non-contiguous F32 operand is gathered into (a result scattered from) a
+ * contiguous staging copy by one extra kernel; strides must be multiples of
+ * 4 bytes; not available inside a captured sequence or in the fused / sharded
+ * entry points (device-resident contiguous vectors only).                     */
 typedef struct lk_tensor {
     int32_t  type;
     int32_t  reserved;
@@ -156,10 +161,23 @@ LK_API lk_status   lk_host_free(lk_ctx *ctx, void *p);
  * Validation order and error classes follow the cited reference lines.       */
 
 /* computeMatMul(graphAllocator, context, a, b, dst) — core/GGMLComputeOps.kt:1435.
- * a.type in {F32, Q4_0, Q4_1, Q8_0}, b F32, dst F32.
- *   N == 1 (and K % 64 == 0)  -> K1 streaming decode GEMV
- *   N >= 64, Q types           -> K2 tcgen05 prefill GEMM (FP16 operands, F32 accumulate)
- *   otherwise                  -> generic F32 kernel                          */
+ * a.type in {F32, Q4_0, Q4_1, Q8_0} (and the K-quant / BitNet types above), b F32, dst F32.  Routing:
+ *   N == 1, K % 64 == 0        -> K1 streaming decode GEMV (lk_gemv.cu)
+ *   N >= 2, K % 256 == 0, M*K*N >= 2^21 (options gemm_tc_min_n = 2, gemm_tc_min_work)
+ *                              -> K2 tcgen05 GEMM (lk_gemm_tc.cu); N < 32 is padded to one 32-column tile
+ *   otherwise                  -> generic F32 kernel (the reference's per-element arithmetic, warp-strided sums)
+ * Arithmetic contract (the reference is F32 throughout, :1516-1527; tolerance of the path: 1e-3 of max|dst|):
+ *   K1: integer block dot products are exact; the activations are held as T_k = rint(x_k * 2^(22-E)) with ONE exponent E
+ *       per 32-element block (E = exponent of the block's max |x|), so x_k carries an absolute error <= 2^(E-23):
+ *       |dst_i - exact_i| <= 2^-23 * sum_k |w_ik| * bmax(k) + F32 summation terms (measured 1e-6 .. 4e-6 of max|dst|).
+ *       A block that holds a non-zero |x| below 2^-20 of its maximum (option gemv_fix_gap) is recomputed from the F32
+ *       activations (exact residuals), so elements the block scale cannot represent are not lost; non-finite
+ *       activations give non-finite outputs like the reference.
+ *   K2: option gemm_tc_precision = 2 (default): d*q and b as FP16 hi + lo pairs (d*q exactly; b to 22 bits), three
+ *       MMAs per K step, F32 accumulation in tensor memory: max-norm error ~4e-6; per element <= 1.5e-6 * K relative
+ *       (the accumulator truncates).  1: exact weights x FP16 activations (max-norm ~2.5e-4).  0: single FP16 operands
+ *       (~3e-4, up to 1.02e-3 on periodic data).  Any F32 magnitude of b is accepted (per-column power-of-two scaling,
+ *       exact); weight scales that could leave the FP16 range make the affected tile take an F32 path.                */
 LK_API lk_status   lk_compute_matmul(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, const lk_tensor *dst);
 
 /* computeMatMul with its neighbours in the layer graph folded into the launch (op order of
@@ -209,6 +227,11 @@ typedef struct lk_matmul_link {
 LK_API lk_status   lk_compute_matmul_chain(lk_ctx *ctx, const lk_matmul_link *links, int32_t n);
 /* dequantizeTensor(graphAllocator, tensor) — core/GGMLComputeOps.kt:918-964. Bit-exact. dst F32, same ne. */
 LK_API lk_status   lk_compute_dequantize(lk_ctx *ctx, const lk_tensor *src, const lk_tensor *dst);
+/* quantizeTensor(graphAllocator, tensor, targetType) — core/GGMLComputeOps.kt:1040-1433 (Q8_0 :1058-1071, Q4_0 :1072-1087,
+ * Q4_1 :1162-1203), destination-based: src F32, dst Q8_0 / Q4_0 / Q4_1 with the same element count (a multiple of 32).
+ * Bit-exact with the reference incl. floatToHalf's half-denormal off-by-one (core/NumericConversions.kt:83) and the
+ * Kotlin quantizers' formulas (Q4_0: d = amax / 8, round-half-even), in the context's nibble_order.                */
+LK_API lk_status   lk_compute_quantize(lk_ctx *ctx, const lk_tensor *src, const lk_tensor *dst);
 /* computeAdd / computeMul F32 same-shape paths — core/GGMLComputeOps.kt:735-759, :811-835 */
 LK_API lk_status   lk_compute_add(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, const lk_tensor *dst);
 LK_API lk_status   lk_compute_mul(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, const lk_tensor *dst);
@@ -270,6 +293,50 @@ LK_API lk_status   lk_capture_end(lk_ctx *ctx, lk_graph **out);
 LK_API lk_status   lk_graph_launch(lk_ctx *ctx, lk_graph *g);
 LK_API lk_status   lk_graph_destroy(lk_graph *g);
 
+/* ---- whole graphs: GGMLBackend.graphCompute with the fusion / chaining plan inside the library ------------------
+ * GGMLComputeOps.computeGraph walks graph.nodes[0 .. nNodes) with `when (node.op)` (core/GGMLComputeOps.kt:2515-2550).
+ * lk_graph_compute takes the same node list — every node with its op, its own tensor (the dst), its sources and
+ * opParams — plans which neighbours fold into the decode GEMV launches (RMS_NORM -> MUL_MAT x up to 3, MUL_MAT -> ADD,
+ * gate / up -> SILU -> MUL, runs of dependent launches as lk_compute_matmul_chain, ROPE ROPE CPY CPY FLASH_ATTN as
+ * lk_compute_attention_step) and issues the calls on the ctx stream; a launch the library declines for its shape falls
+ * back to the unfused ops in graph order.  Every folded node's dst is still written.  Call it between
+ * lk_capture_begin / lk_capture_end to get a replayable lk_graph (device-resident tensors), or directly.
+ * Source slots per op (the node constructors of model/GGMLIntegration.kt:118-220 and this ABI's attention ops):
+ *   MUL_MAT a, b | ADD / MUL a, b | SILU / SOFT_MAX / SCALE x | RMS_NORM x, weight | ROPE x, position, table |
+ *   CPY new rows, cache, position | FLASH_ATTN q, key cache, value cache, position;
+ *   op_params[0]: RMS_NORM eps bits, SCALE factor bits, FLASH_ATTN scale bits, ROPE headDim.                       */
+enum {
+    LK_OP_NONE = 0, LK_OP_ADD = 1, LK_OP_MUL = 2, LK_OP_MUL_MAT = 3, LK_OP_RMS_NORM = 4, LK_OP_SILU = 5, LK_OP_SOFT_MAX = 6,
+    LK_OP_SCALE = 7, LK_OP_ROPE = 8, LK_OP_CPY = 9, LK_OP_FLASH_ATTN = 10
+};
+typedef struct lk_graph_node {
+    int32_t   op;
+    int32_t   n_src;             /* 0 .. 4 */
+    lk_tensor dst;               /* the node's own tensor */
+    lk_tensor src[4];
+    int32_t   op_params[4];
+} lk_graph_node;
+/* One launch of the plan (lk_graph_plan: the planning half alone, host logic only, no device needed).  Index fields
+ * are node indices, -1 = none.  Consecutive launches with the same chain >= 0 go out as one lk_compute_matmul_chain. */
+enum { LK_PLAN_NODE = 0, LK_PLAN_FUSED = 1, LK_PLAN_ATTN_STEP = 2 };
+typedef struct lk_plan_launch {
+    int32_t kind;
+    int32_t node;                /* the node the launch is made at (LK_PLAN_ATTN_STEP: the ROPE(q) node) */
+    int32_t rms, add;            /* RMS_NORM / ADD node folded into this GEMV */
+    int32_t n_extra, extra[2];   /* stacked MUL_MAT nodes */
+    int32_t silu, mul;           /* SwiGLU epilogue */
+    int32_t store_b;             /* 1: this launch also stores the RMS_NORM's dst (the first consumer does) */
+    int32_t chain;
+    int32_t attn[5];             /* LK_PLAN_ATTN_STEP: ROPE(q), ROPE(k), CPY(k), CPY(v), FLASH_ATTN */
+} lk_plan_launch;
+/* chain_mode: -1 = where it was measured to pay (graphs with an attention step between the runs), 0 never, 1 always */
+LK_API lk_status   lk_graph_plan(const lk_graph_node *nodes, int32_t n, int32_t chain_mode, lk_plan_launch *out,
+                                 int32_t max_out, int32_t *n_out);
+#define LK_GRAPH_NO_FUSION    1   /* node by node, like the reference's interpreter */
+#define LK_GRAPH_CHAIN_ALWAYS 2
+#define LK_GRAPH_CHAIN_NEVER  4
+LK_API lk_status   lk_graph_compute(lk_ctx *ctx, const lk_graph_node *nodes, int32_t n, int32_t flags);
+
 /* ---- options ----------------------------------------------------------------
  * "nibble_order" (product option): how the 32 four-bit quants of a Q4_0 / Q4_1 block lie in its 16
  *   quant bytes.  0 (default) = the reference's accessors, getQ4_0NibbleWeight / getQ4_1NibbleWeight
@@ -327,6 +394,36 @@ LK_API lk_status   lk_compute_swiglu_sharded(lk_ctx *ctx, const lk_tensor *gate_
                                       const lk_tensor *g_full, const lk_tensor *u_full, const lk_tensor *silu_full,
                                       const lk_tensor *h_full, int64_t row0, int64_t M_total,
                                       lk_buf *const *peer_h, int32_t npeers);
+
+/* The exchange folded into the sharded launches themselves (no lk_peer_barrier launch between producer and consumer).
+ * An exchange point ("slot", 0 .. LK_MAX_EXCHANGE_SLOTS-1) is a 64-bit arrival counter inside every rank's flag buffer
+ * (LK_FLAG_BYTES bytes, zeroed before first use, peer-mapped like for lk_peer_barrier; the barrier's 16 words are its
+ * first 64 bytes, so one buffer serves both):
+ *   signal_slot >= 0: when every CTA of this launch has finished its peer stores, the last one arrives (+1, release at
+ *                     system scope) on that slot of EVERY rank's flag buffer;
+ *   wait_slot   >= 0: before the launch reads its activations it waits until that slot of THIS rank's flag buffer has
+ *                     received one arrival from every rank (nranks per use of the slot: counters only grow, the epoch of
+ *                     a launch is counted on the device, so a captured sequence can be replayed).
+ * One producer launch and one consumer launch per use of a slot on every rank, in the same order on every rank; a vector
+ * that peers write may be rewritten only by a launch that comes after a wait on a LATER exchange of the same ranks
+ * (then every reader is known to have finished), which the FFN pattern [SwiGLU -> slot 0 -> down -> slot 1 -> next SwiGLU]
+ * satisfies.  The wait is bounded (~2 s); a time-out is counted and makes the next synchronising call return LK_ECUDA. */
+#define LK_FLAG_BYTES 512
+#define LK_MAX_EXCHANGE_SLOTS 8
+typedef struct lk_shard_sync {
+    lk_buf *const *peer_flags;   /* flag buffer of every rank, entry `rank` = this rank's own */
+    int32_t nranks, rank;
+    int32_t wait_slot;           /* -1: no wait */
+    int32_t signal_slot;         /* -1: no signal */
+} lk_shard_sync;
+LK_API lk_status   lk_compute_matmul_sharded_sync(lk_ctx *ctx, const lk_tensor *a_shard, const lk_tensor *b,
+                                      const lk_tensor *dst_full, int64_t row0, int64_t M_total,
+                                      lk_buf *const *peer_dst, int32_t npeers, const lk_shard_sync *sync);
+LK_API lk_status   lk_compute_swiglu_sharded_sync(lk_ctx *ctx, const lk_tensor *gate_shard, const lk_tensor *up_shard,
+                                      const lk_tensor *x, const lk_tensor *norm_w, float eps, const lk_tensor *normed_dst,
+                                      const lk_tensor *g_full, const lk_tensor *u_full, const lk_tensor *silu_full,
+                                      const lk_tensor *h_full, int64_t row0, int64_t M_total,
+                                      lk_buf *const *peer_h, int32_t npeers, const lk_shard_sync *sync);
 
 #ifdef __cplusplus
 }

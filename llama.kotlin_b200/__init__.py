@@ -9,7 +9,7 @@ from .ggml_alloc import GGMLGraphAllocator  # noqa: F401
 from .ggml_compute_ops import (LkContext, computeAdd, computeMatMul, computeMatMulFused, computeMul,  # noqa: F401
                                computeRmsNorm, computeSilu, computeSiluMul, computeSoftMax,
                                KVCache, computeAttentionDecode, computeAttentionStep, computeKvAppend, computeRope, computeScale, ropeTable,
-                               default_context, dequantizeTensor)
+                               default_context, dequantizeTensor, computeQuantize, quantizeTensor, computeMatMulChain)
 from .ggml_cuda_backend import (GGMLCudaBackend, GGMLCudaBuffer, GGMLCudaBufferType)  # noqa: F401
 from .llama_layer import (DecoderLayer, alloc_layer, append_layer_nodes, build_decoder_graph,  # noqa: F401
                           weight_shapes)

@@ -53,6 +53,30 @@ class lk_matmul_link(C.Structure):
                 ("fusion", C.POINTER(lk_matmul_fusion))]
 
 
+class lk_graph_node(C.Structure):
+    _fields_ = [("op", C.c_int32), ("n_src", C.c_int32), ("dst", lk_tensor), ("src", lk_tensor * 4), ("op_params", C.c_int32 * 4)]
+
+
+class lk_plan_launch(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("node", C.c_int32), ("rms", C.c_int32), ("add", C.c_int32), ("n_extra", C.c_int32),
+                ("extra", C.c_int32 * 2), ("silu", C.c_int32), ("mul", C.c_int32), ("store_b", C.c_int32), ("chain", C.c_int32),
+                ("attn", C.c_int32 * 5)]
+
+
+LK_OP = {"NONE": 0, "ADD": 1, "MUL": 2, "MUL_MAT": 3, "RMS_NORM": 4, "SILU": 5, "SOFT_MAX": 6, "SCALE": 7, "ROPE": 8, "CPY": 9,
+         "FLASH_ATTN": 10}
+LK_PLAN_NODE, LK_PLAN_FUSED, LK_PLAN_ATTN_STEP = 0, 1, 2
+LK_GRAPH_NO_FUSION, LK_GRAPH_CHAIN_ALWAYS, LK_GRAPH_CHAIN_NEVER = 1, 2, 4
+
+
+class lk_shard_sync(C.Structure):
+    _fields_ = [("peer_flags", C.POINTER(C.c_void_p)), ("nranks", C.c_int32), ("rank", C.c_int32),
+                ("wait_slot", C.c_int32), ("signal_slot", C.c_int32)]
+
+
+LK_FLAG_BYTES = 512
+LK_MAX_EXCHANGE_SLOTS = 8
+
 _lib = None
 
 
@@ -101,6 +125,7 @@ def lib() -> C.CDLL:
         "lk_compute_matmul_fused": (i32, [vp, tp, tp, tp, C.POINTER(lk_matmul_fusion)]),
         "lk_compute_matmul_chain": (i32, [vp, C.POINTER(lk_matmul_link), i32]),
         "lk_compute_dequantize": (i32, [vp, tp, tp]),
+        "lk_compute_quantize": (i32, [vp, tp, tp]),
         "lk_compute_add": (i32, [vp, tp, tp, tp]),
         "lk_compute_mul": (i32, [vp, tp, tp, tp]),
         "lk_compute_rms_norm": (i32, [vp, tp, tp, C.c_float, tp]),
@@ -117,6 +142,8 @@ def lib() -> C.CDLL:
         "lk_capture_end": (i32, [vp, C.POINTER(vp)]),
         "lk_graph_launch": (i32, [vp, vp]),
         "lk_graph_destroy": (i32, [vp]),
+        "lk_graph_plan": (i32, [C.POINTER(lk_graph_node), i32, i32, C.POINTER(lk_plan_launch), i32, C.POINTER(i32)]),
+        "lk_graph_compute": (i32, [vp, C.POINTER(lk_graph_node), i32, i32]),
         "lk_set_option": (i32, [vp, C.c_char_p, i64]),
         "lk_get_option": (i64, [vp, C.c_char_p]),
         "lk_comm_unique_id": (i32, [vp]),
@@ -129,6 +156,9 @@ def lib() -> C.CDLL:
         "lk_peer_push_f32": (i32, [vp, vp, u64, i64, C.POINTER(vp), i32]),
         "lk_compute_matmul_sharded": (i32, [vp, tp, tp, tp, i64, i64, C.POINTER(vp), i32]),
         "lk_compute_swiglu_sharded": (i32, [vp, tp, tp, tp, tp, C.c_float, tp, tp, tp, tp, tp, i64, i64, C.POINTER(vp), i32]),
+        "lk_compute_matmul_sharded_sync": (i32, [vp, tp, tp, tp, i64, i64, C.POINTER(vp), i32, C.POINTER(lk_shard_sync)]),
+        "lk_compute_swiglu_sharded_sync": (i32, [vp, tp, tp, tp, tp, C.c_float, tp, tp, tp, tp, tp, i64, i64, C.POINTER(vp), i32,
+                                                 C.POINTER(lk_shard_sync)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)

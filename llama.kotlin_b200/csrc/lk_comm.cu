@@ -160,10 +160,42 @@ lk_status lk_peer_barrier(lk_ctx *ctx, lk_buf *own_flags, lk_buf *const *peer_fl
     }
     lk::chain_other(ctx, own_flags->ptr, own_flags->size);
     ctx->barrier_flags = (uint32_t *)own_flags->ptr;
+    ctx->barrier_flags_bytes = own_flags->size;
     ctx->barrier_unchecked++;
     peer_barrier_kernel<<<1, 32, 0, ctx->stream>>>((uint32_t *)own_flags->ptr, (uint32_t *const *)ctx->peer_flags, n, rank, epoch);
     LK_CUDA(ctx, cudaGetLastError());
     if (ctx->capturing) ctx->capture_launches++; else ctx->launches++;
+    return LK_OK;
+}
+
+
+// ---- exchange points inside the flag buffers (lk_shard_sync, include/llamakotlin_cuda.h) ------------------------------
+// bytes 0..63: the 16 words of lk_peer_barrier; 64 + 8 s: arrival counter of slot s (the only words peers write);
+// 128 + 8 s: local CTA counter of the signalling launch; 192 + 8 s: local ticket counter of the waiting launch; 256: time-outs
+static lk_status build_sync(lk_ctx *ctx, const lk_shard_sync *sy, lk::GemvSync *out, const char *who) {
+    if (!sy) return LK_OK;
+    if (!sy->peer_flags || sy->nranks < 1 || sy->nranks > 8 || sy->rank < 0 || sy->rank >= sy->nranks)
+        return lk::fail(ctx, LK_EINVAL_ARG, std::string(who) + ": bad lk_shard_sync");
+    if (sy->wait_slot >= LK_MAX_EXCHANGE_SLOTS || sy->signal_slot >= LK_MAX_EXCHANGE_SLOTS)
+        return lk::fail(ctx, LK_EINVAL_ARG, std::string(who) + ": exchange slot out of range");
+    for (int q = 0; q < sy->nranks; q++)
+        if (!sy->peer_flags[q] || sy->peer_flags[q]->size < LK_FLAG_BYTES)
+            return lk::fail(ctx, LK_EBOUNDS, std::string(who) + ": flag buffers must hold LK_FLAG_BYTES");
+    uint8_t *own = (uint8_t *)sy->peer_flags[sy->rank]->ptr;
+    out->timeout = (unsigned *)(own + 256);
+    if (sy->signal_slot >= 0) {
+        out->sig_n = sy->nranks;
+        for (int q = 0; q < sy->nranks; q++) out->sig_peer[q] = (unsigned long long *)((uint8_t *)sy->peer_flags[q]->ptr + 64 + 8 * sy->signal_slot);
+        out->sig_done = (unsigned long long *)(own + 128 + 8 * sy->signal_slot);
+    }
+    if (sy->wait_slot >= 0) {
+        out->wait_n = sy->nranks;
+        out->wait_ctr = (unsigned long long *)(own + 64 + 8 * sy->wait_slot);
+        out->wait_ticket = (unsigned long long *)(own + 192 + 8 * sy->wait_slot);
+    }
+    ctx->barrier_flags = (uint32_t *)own;
+    ctx->barrier_flags_bytes = sy->peer_flags[sy->rank]->size;
+    ctx->barrier_unchecked++;
     return LK_OK;
 }
 
@@ -202,6 +234,12 @@ lk_status lk_peer_push_f32(lk_ctx *ctx, lk_buf *local, uint64_t off, int64_t cou
 
 lk_status lk_compute_matmul_sharded(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, const lk_tensor *dst,
                                     int64_t row0, int64_t M_total, lk_buf *const *peer_dst, int32_t npeers) {
+    return lk_compute_matmul_sharded_sync(ctx, a, b, dst, row0, M_total, peer_dst, npeers, nullptr);
+}
+
+lk_status lk_compute_matmul_sharded_sync(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b, const lk_tensor *dst,
+                                         int64_t row0, int64_t M_total, lk_buf *const *peer_dst, int32_t npeers,
+                                         const lk_shard_sync *sync) {
     if (!ctx || !a || !b || !dst) return lk::fail(ctx, LK_EINVAL_ARG, "lk_compute_matmul_sharded: NULL argument");
     const int64_t Ms = a->ne[1], K = a->ne[0];
     if (K != b->ne[1]) return lk::fail(ctx, LK_EINVAL_DIM, "Dim mismatch K: a.ne[0] != b.ne[1]");
@@ -227,9 +265,13 @@ lk_status lk_compute_matmul_sharded(lk_ctx *ctx, const lk_tensor *a, const lk_te
     // this launch writes rows [row0, row0 + Ms) of dst here and at the same offsets on every peer
     tune.wait_mode = lk::gemv_wait_mode(ctx, (uint8_t *)a->dev_buf->ptr + a->data_offset, (size_t)abytes,
                                         (uint8_t *)b->dev_buf->ptr + b->data_offset, (size_t)K * 4, d + row0, (size_t)Ms * 4, tune.pdl != 0);
+    lk::GemvSync gs;
+    const lk_status sst = build_sync(ctx, sync, &gs, "sharded matmul");
+    if (sst != LK_OK) return sst;
+    if (gs.wait_n && tune.wait_mode == 2) tune.wait_mode = 1;      // a launch that waits for its peers is not independent
     cudaError_t e = lk::launch_gemv(a->type, (uint8_t *)a->dev_buf->ptr + a->data_offset, K, Ms,
                                     (const float *)((uint8_t *)b->dev_buf->ptr + b->data_offset), d, row0, peers, tune,
-                                    ctx->sm_count, ctx->stream);
+                                    ctx->sm_count, ctx->stream, nullptr, sync ? &gs : nullptr);
     if (e == cudaErrorNotSupported) return lk::fail(ctx, LK_ENOTIMPL, "sharded matmul: shape not supported by the streaming GEMV");
     if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "sharded gemv launch");
     if (ctx->capturing) ctx->capture_launches++; else ctx->launches++;
@@ -240,6 +282,14 @@ lk_status lk_compute_swiglu_sharded(lk_ctx *ctx, const lk_tensor *gate, const lk
                                     const lk_tensor *norm_w, float eps, const lk_tensor *normed_dst, const lk_tensor *g_full,
                                     const lk_tensor *u_full, const lk_tensor *silu_full, const lk_tensor *h_full, int64_t row0,
                                     int64_t M_total, lk_buf *const *peer_h, int32_t npeers) {
+    return lk_compute_swiglu_sharded_sync(ctx, gate, up, x, norm_w, eps, normed_dst, g_full, u_full, silu_full, h_full, row0, M_total,
+                                          peer_h, npeers, nullptr);
+}
+
+lk_status lk_compute_swiglu_sharded_sync(lk_ctx *ctx, const lk_tensor *gate, const lk_tensor *up, const lk_tensor *x,
+                                         const lk_tensor *norm_w, float eps, const lk_tensor *normed_dst, const lk_tensor *g_full,
+                                         const lk_tensor *u_full, const lk_tensor *silu_full, const lk_tensor *h_full, int64_t row0,
+                                         int64_t M_total, lk_buf *const *peer_h, int32_t npeers, const lk_shard_sync *sync) {
     if (!ctx || !gate || !up || !x || !g_full || !u_full || !h_full) return lk::fail(ctx, LK_EINVAL_ARG, "lk_compute_swiglu_sharded: NULL argument");
     const int64_t Ms = gate->ne[1], K = gate->ne[0];
     if (up->type != gate->type || up->ne[0] != K || up->ne[1] != Ms) return lk::fail(ctx, LK_EINVAL_DIM, "sharded SwiGLU: gate and up shards must have one type and shape");
@@ -290,11 +340,15 @@ lk_status lk_compute_swiglu_sharded(lk_ctx *ctx, const lk_tensor *gate, const lk
                                         tune.pdl != 0, &rd, &wr, &wt);
     // the pair keeps both segments' partial sums of a CTA's rows in shared memory: a shard with many rows per CTA
     // (G = 2 of the 70B FFN: 97 rows x 8192) is spread over 2 or 4 CTAs per SM instead
+    lk::GemvSync gs;
+    const lk_status sst = build_sync(ctx, sync, &gs, "sharded SwiGLU");
+    if (sst != LK_OK) return sst;
+    if (gs.wait_n && tune.wait_mode == 2) tune.wait_mode = 1;      // a launch that waits for its peers is not independent
     cudaError_t e = cudaErrorNotSupported;
     for (int cps = tune.ctas_per_sm > 0 ? tune.ctas_per_sm : 1; cps <= 4 && e == cudaErrorNotSupported; cps *= 2) {
         tune.ctas_per_sm = cps;
         e = lk::launch_gemv(gate->type, ptr(gate), K, Ms, (const float *)ptr(x), (float *)ptr(g_full), row0, peers, tune,
-                            ctx->sm_count, ctx->stream, &fu);
+                            ctx->sm_count, ctx->stream, &fu, sync ? &gs : nullptr);
         if (e == cudaErrorNotSupported) cudaGetLastError();
     }
     if (e == cudaErrorNotSupported) return lk::fail(ctx, LK_ENOTIMPL, "sharded SwiGLU: shape not supported by the streaming GEMV");

@@ -327,4 +327,141 @@ cudaError_t launch_softmax(const float *x, int64_t ne0, int64_t nrows, float *ds
     return launch_kernel(softmax_kernel, dim3((unsigned)nrows), dim3(256), 0, s, pdl, x, ne0, dst);
 }
 
+// ---------------------------------------------------------------------------
+// A11 quantizeTensor — core/GGMLComputeOps.kt:1040-1203 (Q8_0 :1058-1071, Q4_0 :1072-1087, Q4_1 :1162-1203) with
+// floatToHalf, core/NumericConversions.kt:61-124, INCLUDING its half-denormal off-by-one (:83): bit-exact
+// with the reference, so blocks quantized on the device are the blocks the Kotlin code would have produced.
+// One warp per 32-element block (lane = element): HBM-bound, 4 B read + blockBytes/32 written per element.
+//   * every F32 operation is one IEEE operation in the reference's order (no FMA contraction);
+//   * kotlin.math.round = ties-to-even (rintf), Float.toInt() saturates, NaN -> 0, then coerceIn;
+//   * maxOf / minOf return NaN if either operand is NaN; among equal candidates (+0 / -0) the sequential scans
+//     `m = if (m < x) m else x` keep the LAST one, which the shuffle reduction reproduces with an index tie-break.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint16_t kt_float_to_half(float f) {
+    const uint32_t bits = __float_as_uint(f);
+    const uint32_t sign = (bits >> 16) & 0x8000u;
+    const int32_t a = (int32_t)(bits & 0x7FFFFFFFu);
+    if (a > 0x47FFEFFF) return (uint16_t)(sign | 0x7C00u | ((a & 0x007FFFFF) ? 0x0200u : 0u));   // overflow / inf / NaN (:67-73)
+    if (a < 0x38800000) {                                                                         // half denormal range (:75-100)
+        const uint32_t mant = ((uint32_t)a & 0x007FFFFFu) | 0x00800000u;
+        const int32_t shift = 127 - (a >> 23);                       // sic: the reference's off-by-one (should be 126 - exp)
+        const uint32_t hm = shift < 24 ? (mant >> (shift & 31)) : 0u;                             // Kotlin masks shift counts to 5 bits
+        const int32_t rb = (int32_t)(mant & ((1u << (shift & 31)) - 1u));
+        const int32_t half = (int32_t)(1u << ((shift - 1) & 31));
+        if (rb > half || (rb == half && (hm & 1u))) {
+            const uint32_t t = hm + 1u;
+            return (uint16_t)(sign | (t == 0x0400u ? (1u << 10) : t));
+        }
+        return (uint16_t)(sign | hm);
+    }
+    const uint32_t he = (((uint32_t)a >> 23) - 112u) << 10;                                       // normal range (:102-122)
+    uint32_t hm = ((uint32_t)a & 0x007FFFFFu) >> 13;
+    if ((a & 0x00001000) && ((a & 0x00000FFF) || (hm & 1u))) {
+        hm++;
+        if (hm == 0x0400u) return (uint16_t)(sign | (he + (1u << 10)));
+    }
+    return (uint16_t)(sign | he | hm);
+}
+
+__device__ __forceinline__ int kt_round_clamp(float v, int lo, int hi) {   // round(v).toInt().coerceIn(lo, hi)
+    const float r = rintf(v);
+    if (r != r) return 0 < lo ? lo : (0 > hi ? hi : 0);
+    if (r <= (float)lo) return lo;
+    if (r >= (float)hi) return hi;
+    return (int)r;
+}
+
+// warp-wide min / max with the sequential scan's semantics (see above); every lane gets the result
+template <bool MAX>
+__device__ __forceinline__ float kt_warp_extreme(float v, int lane) {
+    int idx = lane;
+    bool nan = v != v;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, v, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+        const bool better = MAX ? (ov > v) : (ov < v);
+        if (better || (ov == v && oi > idx)) { v = ov; idx = oi; }
+    }
+    nan = __any_sync(0xffffffffu, nan);
+    return nan ? __uint_as_float(0x7FC00000u) : v;
+}
+
+template <int TYPE>
+__global__ void __launch_bounds__(256) quantize_kernel(const float *__restrict__ x, int64_t nblocks, uint8_t *__restrict__ out, int nib) {
+    constexpr int BB = block_bytes(TYPE);
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t b = warp; b < nblocks; b += nwarps) {
+        const float v = x[b * 32 + lane];
+        uint8_t *ob = out + b * BB;
+        int q;
+        if (TYPE == T_Q4_1) {
+            const float fmin = kt_warp_extreme<false>(v, lane), fmax = kt_warp_extreme<true>(v, lane);
+            float d = __fdiv_rn(__fsub_rn(fmax, fmin), 15.0f);
+            if (d == 0.0f) d = 1.0f;
+            const float inv = __fdiv_rn(1.0f, d);
+            if (lane == 0) {
+                *(uint16_t *)ob = kt_float_to_half(d);
+                *(uint16_t *)(ob + 2) = kt_float_to_half(fmin);
+            }
+            q = kt_round_clamp(__fmul_rn(__fsub_rn(v, fmin), inv), 0, 15);
+        } else {
+            // amax = 0f; for each: amax = maxOf(amax, abs(x)): values are >= +0, ties are identical bit patterns
+            const float amax = kt_warp_extreme<true>(fabsf(v), lane);
+            const float scale = amax == 0.0f ? 1.0f : __fdiv_rn(amax, TYPE == T_Q8_0 ? 127.0f : 8.0f);
+            const float inv = (TYPE == T_Q4_0 && scale == 0.0f) ? 0.0f : __fdiv_rn(1.0f, scale);
+            if (lane == 0) *(uint16_t *)ob = kt_float_to_half(scale);
+            if (TYPE == T_Q8_0) q = kt_round_clamp(__fmul_rn(v, inv), -128, 127);
+            else q = kt_round_clamp(__fadd_rn(__fmul_rn(v, inv), 8.0f), 0, 15);
+        }
+        if (TYPE == T_Q8_0) {
+            ob[2 + lane] = (uint8_t)(int8_t)q;
+        } else {
+            constexpr int QOFF = TYPE == T_Q4_0 ? 2 : 4;
+            // Kotlin order: byte j = elements 2j (low nibble), 2j+1 (high); ggml order: byte j = elements j (low), j+16 (high)
+            const int partner = __shfl_xor_sync(0xffffffffu, q, nib ? 16 : 1);
+            if (nib ? lane < 16 : (lane & 1) == 0)
+                ob[QOFF + (nib ? lane : lane >> 1)] = (uint8_t)((q & 15) | ((partner & 15) << 4));
+        }
+    }
+}
+
+cudaError_t launch_quantize(int type, const float *x, int64_t n, void *out, cudaStream_t s, int nib) {
+    if (n == 0) return cudaSuccess;
+    const int64_t nblocks = n / 32;
+    const int grid = grid_for(nblocks * 32, 256);
+    switch (type) {
+        case T_Q8_0: quantize_kernel<T_Q8_0><<<grid, 256, 0, s>>>(x, nblocks, (uint8_t *)out, nib); break;
+        case T_Q4_0: quantize_kernel<T_Q4_0><<<grid, 256, 0, s>>>(x, nblocks, (uint8_t *)out, nib); break;
+        case T_Q4_1: quantize_kernel<T_Q4_1><<<grid, 256, 0, s>>>(x, nblocks, (uint8_t *)out, nib); break;
+        default: return cudaErrorNotSupported;
+    }
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
+// A9 strided F32 tensors (GGMLTensor.getFloat / setFloat through nb[], core/GGMLTypes.kt:328-380): gather a strided
+// tensor into the contiguous layout the kernels take, or scatter a contiguous result back through dst's strides.
+// Element (i0, i1, i2, i3) lives at byte offset sum i_d * nb[d].
+// ---------------------------------------------------------------------------
+struct StrideDesc { int64_t ne[4]; int64_t nb[4]; };
+__global__ void __launch_bounds__(256) strided_copy_kernel(const uint8_t *__restrict__ src, uint8_t *__restrict__ dst, StrideDesc d, int64_t n, int scatter) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        int64_t r = i, off = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) { const int64_t ik = r % d.ne[k]; r /= d.ne[k]; off += ik * d.nb[k]; }
+        if (scatter) *(float *)(dst + off) = ((const float *)src)[i];
+        else ((float *)dst)[i] = *(const float *)(src + off);
+    }
+}
+cudaError_t launch_strided_copy(const void *src, void *dst, const int64_t ne[4], const uint64_t nb[4], int scatter, cudaStream_t s) {
+    StrideDesc d;
+    int64_t n = 1;
+    for (int k = 0; k < 4; k++) { d.ne[k] = ne[k] > 0 ? ne[k] : 1; d.nb[k] = (int64_t)nb[k]; n *= d.ne[k]; }
+    if (n == 0) return cudaSuccess;
+    strided_copy_kernel<<<grid_for(n, 256), 256, 0, s>>>((const uint8_t *)src, (uint8_t *)dst, d, n, scatter);
+    return cudaGetLastError();
+}
+
 }  // namespace lk

@@ -773,7 +773,7 @@ static int plan_bn(int type, int64_t M, int64_t N, int sm_count, int cs, int ap,
 cudaError_t launch_gemm_tc(int type, const void *a, int64_t K, int64_t M, const float *b, int64_t N, float *dst,
                            void *workspace, int sm_count, int cluster, cudaStream_t s, int nib, int precision) {
     if (type != T_Q8_0 && type != T_Q4_0 && type != T_Q4_1) return cudaErrorNotSupported;
-    if (K <= 0 || K % TC_CHUNK_K || N < 16 || M < 1 || M > (1 << 30) || N > (1 << 20) || K > (1 << 24)) return cudaErrorNotSupported;
+    if (K <= 0 || K % TC_CHUNK_K || N < 2 || M < 1 || M > (1 << 30) || N > (1 << 20) || K > (1 << 24)) return cudaErrorNotSupported;
     if (((uintptr_t)a & 15) || ((uintptr_t)workspace & 1023) || ((uintptr_t)b & 3)) return cudaErrorNotSupported;
     const int prec = precision < 0 ? 0 : precision > 2 ? 2 : precision;
     const int ap = prec >= 1 ? 2 : 1, bparts = prec >= 2 ? 2 : 1;

@@ -279,6 +279,15 @@ struct GemvParams {
     const uint8_t *a_seg[2];
     float *dst_seg[2];
     float *epi_act, *epi_out;
+    // ---- cross-GPU exchange folded into the launch (sharded matmuls, FUSED instantiation only; see GemvSync in lk_kernels.h)
+    int out_off;                          // npeers > 0: byte offset of the output staging row (floats) the coalesced peer stores read
+    int sig_n;                            // > 0: when the whole grid has stored, arrive on sig_peer[0..sig_n) (one per rank, own included)
+    int wait_n;                           // > 0: before reading the activations wait for wait_n arrivals per epoch on wait_ctr
+    unsigned long long *sig_peer[8];      // every rank's arrival counter of the signalled exchange point (peer-mapped)
+    unsigned long long *sig_done;         // local: CTAs of this launch that have stored (the last one signals and re-arms it)
+    unsigned long long *wait_ctr;         // local arrival counter of the awaited exchange point (monotonic)
+    unsigned long long *wait_ticket;      // local: consumer CTAs that have taken a ticket (ticket / grid = epoch)
+    unsigned *sync_timeout;               // local: bounded waits that gave up (never in a healthy run)
 };
 
 #ifdef LK_GEMV_TIMELINE
@@ -460,7 +469,8 @@ __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int ti
                 uint32_t mn = 0xFFFFFFFFu;
 #pragma unroll
                 for (int i = 0; i < 16; i++) mn = min(mn, __float_as_uint(v[i]) * 2u - 1u);
-                mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, 1));
+                // only the two lanes of this pair are known to be here (the branch is data dependent): pair mask, not the full warp
+                mn = min(mn, __shfl_xor_sync(3u << ((tid & 31) & ~1), mn, 1));
                 const uint32_t t = mn + 1u;
                 if (on && (task & 1) == 0 && t != 0u && (int)(t >> 24) + p.fix_gap < e) {
                     atomicOr(&side->mask[task >> 6], 1u << ((task >> 1) & 31));
@@ -588,6 +598,53 @@ __device__ __noinline__ void gemv_fixup(const uint8_t *a, const float *b, const 
 // cross-lane part of the final reduction: 8 lanes per row, 4 rows per warp per pass
 __device__ __forceinline__ float silu_f(float x) { return __fmul_rn(x, __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-x)))); }   // = lk_elementwise.cu silu1
 
+
+// ---- cross-GPU exchange, device side -----------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void red_release_sys_add(unsigned long long *p, unsigned long long v) {
+    asm volatile("red.release.sys.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+// this CTA's n outputs (staged in shared memory by finish_rows / finish_pair) into every peer's copy of dst: one warp per
+// peer, lanes on consecutive floats, so the NVLink writes leave as whole 128-byte lines instead of one 4-byte packet per row
+__device__ __forceinline__ void peer_store_rows(const GemvParams &p, const float *outbuf, int n, int64_t out0, int warp, int lane) {
+#pragma unroll 1
+    for (int q = warp; q < p.npeers; q += p.cwarps) {
+        float *dstq = p.peer[q] + out0;
+#pragma unroll 1
+        for (int i = lane; i < n; i += 32) dstq[i] = outbuf[i];
+    }
+}
+// After the last peer store of the CTA (call with all consumer threads): the last CTA of the grid to get here arrives on
+// every rank's counter.  fence + atomic in every CTA, atomic + fence in the last one: every CTA's peer stores are ordered
+// before the remote arrivals (the "last block" pattern, at system scope).
+__device__ __forceinline__ void exchange_signal(const GemvParams &p, int tid, int nct) {
+    asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
+    if (tid == 0) {
+        __threadfence_system();
+        const unsigned long long done = atomicAdd(p.sig_done, 1ull);
+        if (done == (unsigned long long)gridDim.x - 1ull) {
+            atomicExch(p.sig_done, 0ull);              // re-armed for the next launch that signals this exchange point
+            __threadfence_system();
+#pragma unroll 1
+            for (int q = 0; q < p.sig_n; q++) red_release_sys_add(p.sig_peer[q], 1ull);
+        }
+    }
+}
+// Before the activations are read: wait until every rank's producer launch of this epoch has arrived.  The counter only
+// grows (wait_n per epoch); the epoch is this CTA's ticket / grid size.  Bounded: a rank that died cannot hang the device;
+// a time-out is counted and reported by the next synchronising call on the context.
+__device__ __forceinline__ void exchange_wait(const GemvParams &p, unsigned long long ticket) {
+    const unsigned long long target = (ticket / gridDim.x + 1ull) * (unsigned long long)p.wait_n;
+    const long long t0 = clock64();
+    while (ld_acquire_sys(p.wait_ctr) < target) {
+        if (clock64() - t0 > 4000000000ll) { atomicAdd(p.sync_timeout, 1u); break; }
+    }
+}
+
 template <bool FUSED, bool CG = false>
 __device__ __forceinline__ void finish_rows(const GemvParams &p, float *dst, const float *red, int nred, int64_t out0, int warp, int lane) {
     const int sub = lane & 7, rsel = lane >> 3;
@@ -614,8 +671,7 @@ __device__ __forceinline__ void finish_rows(const GemvParams &p, float *dst, con
                 v = __fadd_rn(CG ? __ldcg(p.residual + o) : p.residual[o], v);
             }
             dst[o] = v;
-#pragma unroll 1
-            for (int q = 0; q < p.npeers; q++) p.peer[q][o] = v;
+            if (FUSED && p.npeers) ((float *)((uint8_t *)red - p.red_off + p.out_off))[r] = v;   // staged for peer_store_rows
         }
     }
 }
@@ -649,8 +705,7 @@ __device__ __forceinline__ void finish_pair(const GemvParams &p, const float *re
             if (p.epi_act) p.epi_act[o] = act;
             const float hv = __fmul_rn(act, u);
             p.epi_out[o] = hv;
-#pragma unroll 1
-            for (int q = 0; q < p.npeers; q++) p.peer[q][o] = hv;      // sharded FFN: this rank's slice of h into every peer's copy
+            if (p.npeers) ((float *)((uint8_t *)red - p.red_off + p.out_off))[r] = hv;   // sharded FFN: staged for peer_store_rows
         }
     }
 }
@@ -758,13 +813,19 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
     for (int r = warp; r < p.red_rows; r += p.cwarps)
         if (lane < GEMV_RED_PAD) red[r * p.red_stride + p.ncw * 8 + lane] = 0.f;
     if (warp == 0) { if (lane < 28) side->mask[lane] = 0u; if (lane == 28) side->any = 0u; }
+    unsigned long long xticket = 0;
+    if (FUSED && p.wait_n > 0 && tid == 0) xticket = atomicAdd(p.wait_ticket, 1ull);   // issued early: its latency hides under the barrier below
     __syncthreads();   // barriers initialised by the producer
     if (p.wait_mode != GEMV_WAIT_END) {
         pdl_wait();                // activations may be the previous kernel's output
         pdl_launch_dependents();   // the next kernel can start its prologue / weight prefetch under our main loop
     }
+    if (FUSED && p.wait_n > 0) {   // sharded matmul: the activations are gathered from every rank (peer stores + arrival counters)
+        if (tid == 0) exchange_wait(p, xticket);
+        asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
+    }
     if (tid == 0) LK_TL(3);
-    prep_x<TYPE, NP, FUSED>(p, xs, tid, nct, side);
+    prep_x<TYPE, NP, FUSED, FUSED>(p, xs, tid, nct, side);   // fused launches read x with ld.global.cg: it may have been written over NVLink
     if (tid == 0) LK_TL(24);
     asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");   // activation planes written
     if (tid == 0) LK_TL(4);
@@ -812,8 +873,12 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
         if (epi_mode != 1 && row0 + p.stage_rows - red_base > p.red_rows) {
             // partial-sum buffer full (a CTA that owns more rows than it holds)
             asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
-            LK_GEMV_FIXUP(false, FUSED ? p.pro_w : nullptr, FUSED ? p.pro_mode : 0, nct, (!FUSED || seg == 0) ? p.a : p.a_seg[seg - 1], r_begin + red_base, row0 - red_base, red)
+            LK_GEMV_FIXUP(FUSED, FUSED ? p.pro_w : nullptr, FUSED ? p.pro_mode : 0, nct, (!FUSED || seg == 0) ? p.a : p.a_seg[seg - 1], r_begin + red_base, row0 - red_base, red)
             finish_rows<FUSED>(p, seg_dst, red, row0 - red_base, p.row_offset + r_begin + red_base, warp, lane);
+            if (FUSED && p.npeers) {
+                asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
+                peer_store_rows(p, (const float *)(smem + p.out_off), row0 - red_base, p.row_offset + r_begin + red_base, warp, lane);
+            }
             asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
             rp -= (size_t)(row0 - red_base) * p.red_stride;
             red_base = row0;
@@ -881,8 +946,12 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
     if (tid == 0) LK_TL(6);
     asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
     if (tid == 0) LK_TL(20);
-    LK_GEMV_FIXUP(false, FUSED ? p.pro_w : nullptr, FUSED ? p.pro_mode : 0, nct, (!FUSED || seg == 0) ? p.a : p.a_seg[seg - 1], r_begin + red_base, nrows - red_base, red)
+    LK_GEMV_FIXUP(FUSED, FUSED ? p.pro_w : nullptr, FUSED ? p.pro_mode : 0, nct, (!FUSED || seg == 0) ? p.a : p.a_seg[seg - 1], r_begin + red_base, nrows - red_base, red)
     finish_rows<FUSED>(p, seg_dst, red, nrows - red_base, p.row_offset + r_begin + red_base, warp, lane);
+    if (FUSED && p.npeers) {
+        asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
+        peer_store_rows(p, (const float *)(smem + p.out_off), nrows - red_base, p.row_offset + r_begin + red_base, warp, lane);
+    }
     if (seg + 1 < nseg) {                        // the buffer is reused by the next segment
         asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
         rp = rp0;
@@ -891,10 +960,15 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
     }
     if (epi_mode == 1) {
         asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
-        LK_GEMV_FIXUP(false, p.pro_w, p.pro_mode, nct, p.a, r_begin, nrows, red)
-        LK_GEMV_FIXUP(false, p.pro_w, p.pro_mode, nct, p.a_seg[0], r_begin, nrows, red + (size_t)p.pair_off * p.red_stride)
+        LK_GEMV_FIXUP(FUSED, p.pro_w, p.pro_mode, nct, p.a, r_begin, nrows, red)
+        LK_GEMV_FIXUP(FUSED, p.pro_w, p.pro_mode, nct, p.a_seg[0], r_begin, nrows, red + (size_t)p.pair_off * p.red_stride)
         finish_pair(p, red, nrows, p.pair_off, p.row_offset + r_begin, warp, lane);
+        if (p.npeers) {
+            asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
+            peer_store_rows(p, (const float *)(smem + p.out_off), nrows, p.row_offset + r_begin, warp, lane);
+        }
     }
+    if (FUSED && p.sig_n > 0) exchange_signal(p, tid, nct);   // the grid's last CTA to get here arrives on every rank's counter
     if (tid == 0) {
         LK_TL(7);
         // keep completion order = launch order so a later launch's wait covers every earlier one
@@ -1198,7 +1272,7 @@ static cudaError_t launch_plain(const GemvParams &p, int grid, int smem, int pdl
 
 cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const float *b, float *dst,
                         int64_t row_offset, const GemvPeers &peers, const GemvTuning &tune, int sm_count,
-                        cudaStream_t s, const GemvFusion *fusion) {
+                        cudaStream_t s, const GemvFusion *fusion, const GemvSync *sync) {
     const bool kq = type == T_Q4_K || type == T_Q8_K || type == T_Q2_K;     // the reference's K-quant super-blocks (256 elements)
     if (kq && ((K % 256) != 0 || fusion)) return cudaErrorNotSupported;
     const int bb = block_bytes(type);
@@ -1230,6 +1304,14 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
             if (fusion->nseg_extra != 1 || !fusion->epi_out) return cudaErrorNotSupported;
             p.epi_mode = 1; p.epi_act = fusion->epi_act; p.epi_out = fusion->epi_out;
         }
+    }
+    if (sync) {
+        if (kq || sync->sig_n < 0 || sync->sig_n > 8 || sync->wait_n < 0) return cudaErrorNotSupported;
+        p.sig_n = sync->sig_n; p.sig_done = sync->sig_done;
+        for (int i = 0; i < sync->sig_n; i++) p.sig_peer[i] = sync->sig_peer[i];
+        p.wait_n = sync->wait_n; p.wait_ctr = sync->wait_ctr; p.wait_ticket = sync->wait_ticket;
+        p.sync_timeout = sync->timeout;
+        if ((p.sig_n && !p.sig_done) || (p.wait_n && (!p.wait_ctr || !p.wait_ticket)) || !p.sync_timeout) return cudaErrorNotSupported;
     }
     p.tl = (unsigned long long *)tune.timeline;
     p.wait_mode = tune.wait_mode;
@@ -1291,7 +1373,8 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
     }
     p.red_rows = red_rows;
     p.red_off = 256;
-    p.x_off = (p.red_off + p.red_rows * p.red_stride * 4 + 15) & ~15;
+    p.out_off = p.red_off + p.red_rows * p.red_stride * 4;            // output staging row for the coalesced peer stores
+    p.x_off = (p.out_off + (p.npeers > 0 ? p.red_rows * 4 : 0) + 15) & ~15;
     const int np = tune.act_planes == 2 ? 2 : 3;
     p.stage_off = (p.x_off + p.nblk * gemv_xslot_words(np) * 4 + 127) & ~127;
     int nst = (budget - p.stage_off) / stage_bytes;
@@ -1304,7 +1387,9 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
     }
     p.nstages = nst;
     const int smem = p.stage_off + nst * stage_bytes;
-    const bool fused = p.pro_mode != 0 || p.residual != nullptr || p.nseg > 1;
+    // peer stores and the exchange signal / wait live in the fused instantiation only (the plain kernel keeps its size)
+    const bool fused = p.pro_mode != 0 || p.residual != nullptr || p.nseg > 1 || p.npeers > 0 || p.sig_n > 0 || p.wait_n > 0;
+    if (kq && fused) return cudaErrorNotSupported;
 
     switch (type * 4 + np) {
         case T_Q4_0 * 4 + 2: return launch_type<T_Q4_0, 2>(p, fused, grid, smem, tune.pdl, s);

@@ -30,6 +30,11 @@ struct GemvTuning {
 // nib: nibble order of Q4 blocks (GemvTuning::nibble_order)
 cudaError_t launch_dequantize(int type, const void *src, int64_t n, float *dst, cudaStream_t s, int nib = 0);
 
+// A11: quantizeTensor on the device, bit-exact with core/GGMLComputeOps.kt:1058-1087 / :1162-1203 (incl. floatToHalf's F11)
+cudaError_t launch_quantize(int type, const float *x, int64_t n, void *out, cudaStream_t s, int nib = 0);
+// A9: gather a strided F32 tensor into contiguous order (scatter = 0) or scatter a contiguous one through strides (1)
+cudaError_t launch_strided_copy(const void *src, void *dst, const int64_t ne[4], const uint64_t nb[4], int scatter, cudaStream_t s);
+
 // K1: decode GEMV, N == 1, K % 64 == 0.  Returns cudaErrorNotSupported when the
 // shape cannot take the streaming path (caller then uses the generic kernel).
 // dst_peers/npeers: optional extra destinations (peer-mapped buffers) for the
@@ -56,9 +61,23 @@ struct GemvFusion {
     float *epi_act = nullptr;       //   optional: silu(dst) (the SILU node's dst)
     float *epi_out = nullptr;
 };
+// Cross-GPU exchange folded into a sharded launch (no separate barrier kernel, SURVEY §8e / DESIGN §6).  An exchange
+// point is a 64-bit arrival counter in every rank's peer-mapped flag buffer:
+//   signal: when all CTAs of this launch have done their peer stores, the last one arrives (+1, release at system scope)
+//           on every rank's counter (sig_peer[0..sig_n), own rank included); sig_done is a local CTA counter it re-arms;
+//   wait:   before the launch reads its activations every CTA waits until the local counter has received wait_n arrivals
+//           of its epoch (epoch = ticket / grid size, wait_ticket is a local counter); bounded, time-outs counted in *timeout.
+struct GemvSync {
+    int sig_n = 0;
+    unsigned long long *sig_peer[8] = {};
+    unsigned long long *sig_done = nullptr;
+    int wait_n = 0;
+    unsigned long long *wait_ctr = nullptr, *wait_ticket = nullptr;
+    unsigned *timeout = nullptr;
+};
 cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const float *b, float *dst,
                         int64_t row_offset, const GemvPeers &peers, const GemvTuning &tune, int sm_count,
-                        cudaStream_t s, const GemvFusion *fusion = nullptr);
+                        cudaStream_t s, const GemvFusion *fusion = nullptr, const GemvSync *sync = nullptr);
 
 // K1c: up to GEMV_CHAIN_MAX dependent GEMVs (each with its optional fusions, no peers) as ONE persistent launch with a
 // grid-wide barrier between phases; the weight stream runs ahead across the hand-offs.  Same results as the launches

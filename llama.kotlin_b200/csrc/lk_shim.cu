@@ -45,11 +45,14 @@ lk_status check_async_faults(lk_ctx *ctx) {
     }
     if (ctx->barrier_unchecked && ctx->barrier_flags) {
         ctx->barrier_unchecked = 0;
-        uint32_t w = 0;
+        uint32_t w = 0, w2 = 0;
         if (cudaMemcpy(&w, ctx->barrier_flags + 14, 4, cudaMemcpyDeviceToHost) != cudaSuccess) return cuda_fail(ctx, cudaGetLastError(), "reading the peer barrier words");
-        if (w) {
-            cudaMemset(ctx->barrier_flags + 14, 0, 4);
-            return fail(ctx, LK_ECUDA, "lk_peer_barrier: a peer did not arrive within the bounded wait; gathered outputs are invalid");
+        if (ctx->barrier_flags_bytes >= LK_FLAG_BYTES && cudaMemcpy(&w2, ctx->barrier_flags + 64, 4, cudaMemcpyDeviceToHost) != cudaSuccess)
+            return cuda_fail(ctx, cudaGetLastError(), "reading the exchange time-out word");
+        if (w || w2) {
+            if (w) cudaMemset(ctx->barrier_flags + 14, 0, 4);
+            if (w2) cudaMemset(ctx->barrier_flags + 64, 0, 4);
+            return fail(ctx, LK_ECUDA, "cross-GPU exchange: a peer did not arrive within the bounded wait; gathered outputs are invalid");
         }
     }
     return LK_OK;
@@ -307,9 +310,14 @@ lk_status lk_host_free(lk_ctx *ctx, void *p) {
 namespace {
 
 struct Staged {
-    void *dev = nullptr;       // device address the kernel uses
+    void *dev = nullptr;       // device address the kernel uses (contiguous)
     void *host = nullptr;      // non-NULL: copy back to here after the op (outputs only)
-    int64_t bytes = 0;
+    int64_t bytes = 0;         // bytes copied back to `host`
+    // strided F32 output (A9): the kernel wrote `dev` in contiguous order; scatter it through the strides into
+    // scatter_base (the tensor's first byte on the device: its own buffer, or the staged copy of its host byte range)
+    void *scatter_base = nullptr;
+    int64_t ne[4] = {1, 1, 1, 1};
+    uint64_t nb[4] = {0, 0, 0, 0};
 };
 
 struct OpScope {
@@ -377,12 +385,32 @@ bool contiguous_f32(const lk_tensor *t) {
     }
     return true;
 }
+bool strided_f32(const lk_tensor *t) { return t && (t->type == LK_TYPE_F32 || t->type == LK_TYPE_I32) && !contiguous_f32(t); }
+// bytes from the tensor's first byte to one past its last element when addressed through nb[] (getElementByteOffset,
+// core/GGMLTypes.kt:328-357); strides must be multiples of 4 (aligned F32 accesses on the device)
+int64_t strided_extent(const lk_tensor *t) {
+    int64_t ext = 4;
+    for (int d = 0; d < LK_MAX_DIMS; d++) {
+        const int64_t n = t->ne[d] > 0 ? t->ne[d] : 1;
+        if (t->nb[d] % 4) return -1;
+        ext += (n - 1) * (int64_t)t->nb[d];
+    }
+    return ext;
+}
 
-// total staging bytes the host tensors of one op need (each rounded to 256)
+// total staging bytes the host tensors of one op need (each rounded to 256); a strided F32 tensor also needs its
+// contiguous copy (and, when host resident, the copy of the byte range it spans)
 size_t host_need(std::initializer_list<const lk_tensor *> ts) {
     size_t need = 0;
-    for (const lk_tensor *t : ts)
-        if (t && !t->dev_buf) need += ((size_t)lk_tensor_nbytes(t) + 255) & ~(size_t)255;
+    for (const lk_tensor *t : ts) {
+        if (!t) continue;
+        if (strided_f32(t)) {
+            need += ((size_t)lk_tensor_nbytes(t) + 255) & ~(size_t)255;
+            if (!t->dev_buf) { const int64_t e = strided_extent(t); if (e > 0) need += ((size_t)e + 255) & ~(size_t)255; }
+        } else if (!t->dev_buf) {
+            need += ((size_t)lk_tensor_nbytes(t) + 255) & ~(size_t)255;
+        }
+    }
     return need;
 }
 
@@ -390,44 +418,73 @@ lk_status resolve(OpScope &sc, const lk_tensor *t, bool is_output, void **dev_ou
     lk_ctx *ctx = sc.ctx;
     const int64_t nbytes = lk_tensor_nbytes(t);
     if (nbytes < 0) return fail(ctx, LK_ENOTIMPL, std::string(name) + ": unsupported tensor type");
-    if (t->type == LK_TYPE_F32 && !contiguous_f32(t))
-        return fail(ctx, LK_EINVAL_ARG, std::string(name) + ": F32 tensors must be contiguous");
     if ((t->dev_buf != nullptr) == (t->host_base != nullptr))
         return fail(ctx, LK_EINVAL_ARG, std::string(name) + ": exactly one of host_base / dev_buf must be set");
+    const bool strided = strided_f32(t);
+    const int64_t span = strided ? strided_extent(t) : nbytes;      // bytes of the buffer the tensor touches
+    if (strided && span < 0) return fail(ctx, LK_EINVAL_ARG, std::string(name) + ": F32 strides must be multiples of 4 bytes");
+    const uint64_t bsize = t->dev_buf ? t->dev_buf->size : t->buffer_size;
+    if (t->data_offset > bsize || (uint64_t)span > bsize - t->data_offset)      // IndexOutOfBounds semantics of the accessors (core/GGMLTypes.kt:556-558)
+        return fail(ctx, LK_EBOUNDS, std::string(name) + (t->dev_buf ? ": tensor bytes exceed the device buffer" : ": tensor bytes exceed the host buffer"));
+    uint8_t *base;             // the tensor's first byte on the device
     if (t->dev_buf) {
-        lk_buf *b = t->dev_buf;
-        if (t->data_offset > b->size || (uint64_t)nbytes > b->size - t->data_offset)
-            return fail(ctx, LK_EBOUNDS, std::string(name) + ": tensor bytes exceed the device buffer");
-        if (t->data_offset % 16)  // GGMLDynTensorAllocator alignment, core/GGMLAlloc.kt:122,149
+        if (t->data_offset % (strided ? 4 : 16))  // GGMLDynTensorAllocator alignment, core/GGMLAlloc.kt:122,149
             return fail(ctx, LK_EINVAL_ARG, std::string(name) + ": dataOffset must be 16-byte aligned on device");
-        *dev_out = (uint8_t *)b->ptr + t->data_offset;
-        return LK_OK;
+        base = (uint8_t *)t->dev_buf->ptr + t->data_offset;
+        if (!strided) { *dev_out = base; return LK_OK; }
+        if (ctx->capturing) return fail(ctx, LK_EINVAL_ARG, std::string(name) + ": strided tensors cannot be used inside a captured sequence");
+    } else {
+        if (ctx->capturing)
+            return fail(ctx, LK_EINVAL_ARG, std::string(name) + ": host tensors cannot be used inside a captured sequence");
+        sc.any_host = true;
+        base = ctx->arena + ctx->arena_used;
+        ctx->arena_used += ((size_t)span + 255) & ~(size_t)255;
+        uint8_t *h = (uint8_t *)t->host_base + t->data_offset;
+        // inputs are uploaded; so is the byte range of a strided output (the bytes between its elements must survive)
+        if ((!is_output || strided) && span) {
+            LK_CUDA(ctx, cudaMemcpyAsync(base, h, (size_t)span, cudaMemcpyHostToDevice, ctx->stream));
+            chain_other(ctx, base, (size_t)span);
+        }
+        if (is_output) {
+            Staged s; s.dev = base; s.host = h; s.bytes = span;
+            if (!strided) { sc.outs.push_back(s); *dev_out = base; return LK_OK; }
+        } else if (!strided) {
+            *dev_out = base;
+            return LK_OK;
+        }
     }
-    // host tensor: IndexOutOfBounds semantics of the accessors (core/GGMLTypes.kt:556-558)
-    if (t->data_offset > t->buffer_size || (uint64_t)nbytes > t->buffer_size - t->data_offset)
-        return fail(ctx, LK_EBOUNDS, std::string(name) + ": tensor bytes exceed the host buffer");
-    if (ctx->capturing)
-        return fail(ctx, LK_EINVAL_ARG, std::string(name) + ": host tensors cannot be used inside a captured sequence");
-    sc.any_host = true;
-    uint8_t *d = ctx->arena + ctx->arena_used;
+    // strided F32 (A9): a contiguous copy in the arena is what the kernel sees
+    uint8_t *c = ctx->arena + ctx->arena_used;
     ctx->arena_used += ((size_t)nbytes + 255) & ~(size_t)255;
-    uint8_t *h = (uint8_t *)t->host_base + t->data_offset;
     if (is_output) {
-        Staged s; s.dev = d; s.host = h; s.bytes = nbytes;
+        Staged s; s.dev = c; s.scatter_base = base;
+        for (int d = 0; d < LK_MAX_DIMS; d++) { s.ne[d] = t->ne[d] > 0 ? t->ne[d] : 1; s.nb[d] = t->nb[d]; }
+        if (!t->dev_buf) { s.host = (uint8_t *)t->host_base + t->data_offset; s.bytes = span; }
         sc.outs.push_back(s);
-    } else if (nbytes) {
-        LK_CUDA(ctx, cudaMemcpyAsync(d, h, (size_t)nbytes, cudaMemcpyHostToDevice, ctx->stream));
-        chain_other(ctx, d, (size_t)nbytes);
+    } else {
+        int64_t ne[4];
+        for (int d = 0; d < LK_MAX_DIMS; d++) ne[d] = t->ne[d] > 0 ? t->ne[d] : 1;
+        const cudaError_t e = lk::launch_strided_copy(base, c, ne, t->nb, 0, ctx->stream);
+        if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "strided gather");
+        chain_other(ctx, c, (size_t)nbytes);
     }
-    *dev_out = d;
+    *dev_out = c;
     return LK_OK;
 }
 
-// copy staged outputs back and make dst valid on return (reference semantics)
+// scatter strided outputs, copy staged outputs back and make dst valid on return (reference semantics)
 lk_status finish(OpScope &sc) {
     lk_ctx *ctx = sc.ctx;
-    for (const Staged &s : sc.outs)
-        if (s.bytes) LK_CUDA(ctx, cudaMemcpyAsync(s.host, s.dev, (size_t)s.bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    for (const Staged &s : sc.outs) {
+        if (s.scatter_base) {
+            const cudaError_t e = lk::launch_strided_copy(s.dev, s.scatter_base, s.ne, s.nb, 1, ctx->stream);
+            if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "strided scatter");
+            chain_other(ctx, nullptr, 0);
+            if (s.host && s.bytes) LK_CUDA(ctx, cudaMemcpyAsync(s.host, s.scatter_base, (size_t)s.bytes, cudaMemcpyDeviceToHost, ctx->stream));
+        } else if (s.bytes) {
+            LK_CUDA(ctx, cudaMemcpyAsync(s.host, s.dev, (size_t)s.bytes, cudaMemcpyDeviceToHost, ctx->stream));
+        }
+    }
     if (sc.any_host) {
         LK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         chain_other(ctx, nullptr, 0);
@@ -520,7 +577,11 @@ lk_status lk_compute_matmul(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b,
         e = lk::launch_gemv(a->type, da, K, M, (const float *)db, (float *)dd, 0, none, tune, ctx->sm_count, ctx->stream);
     }
     int launched = 1;
-    if (N > 1 && is_block_type(a->type) && ctx->gemm_tc_min_n > 0 && N >= ctx->gemm_tc_min_n && K > 0 && K % 256 == 0) {
+    // Batched case (N >= 2): the tcgen05 GEMM whenever the packed rows are TMA-addressable (K % 256 == 0: 16-byte row pitch)
+    // and the product is big enough to pay for its three launches; small N is padded to one 32-column tile, so the
+    // weights are still streamed and dequantised exactly once.  Everything else: the generic F32 kernel.
+    if (N > 1 && is_block_type(a->type) && ctx->gemm_tc_min_n > 0 && N >= ctx->gemm_tc_min_n && K > 0 && K % 256 == 0 &&
+        (double)M * (double)K * (double)N >= (double)ctx->gemm_tc_min_work) {
         if ((st = gemm_ws_reserve(ctx, lk::gemm_tc_workspace_bytes(K, N))) != LK_OK) return st;
         chain_other(ctx, dd, (size_t)M * N * 4);
         void *ws = (void *)(((uintptr_t)ctx->gemm_ws + 1023) & ~(uintptr_t)1023);
@@ -729,6 +790,29 @@ lk_status lk_compute_dequantize(lk_ctx *ctx, const lk_tensor *src, const lk_tens
     cudaError_t e = is_kq_type(src->type) ? lk::launch_kq_dequantize(src->type, ds, n, (float *)dd, ctx->stream)
                                           : lk::launch_dequantize(src->type, ds, n, (float *)dd, ctx->stream, ctx->tune.nibble_order);
     if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "dequantize launch");
+    count_launch(ctx);
+    return finish(sc);
+}
+
+// quantizeTensor(graphAllocator, tensor, targetType) — core/GGMLComputeOps.kt:1040-1433, destination-based: src F32, dst
+// Q8_0 / Q4_0 / Q4_1 with the same element count (a multiple of 32, require(...) at :1059 / :1073 / :1163).  Bit-exact.
+lk_status lk_compute_quantize(lk_ctx *ctx, const lk_tensor *src, const lk_tensor *dst) {
+    if (!ctx || !src || !dst) return fail(ctx, LK_EINVAL_ARG, "lk_compute_quantize: NULL argument");
+    if (src->type != LK_TYPE_F32) return fail(ctx, LK_EINVAL_TYPE, "quantize: source must be F32");
+    if (!is_block_type(dst->type)) return fail(ctx, LK_ENOTIMPL, "quantize: destination must be Q8_0, Q4_0 or Q4_1 on this device path");
+    const int64_t n = num_elements(src);
+    if (n != num_elements(dst)) return fail(ctx, LK_EINVAL_DIM, "quantize: element counts differ");
+    if (n % LK_QK) return fail(ctx, LK_EINVAL_DIM, "quantize: element count must be a multiple of 32");
+    LK_CUDA(ctx, cudaSetDevice(ctx->device));
+    OpScope sc(ctx);
+    lk_status st = arena_reserve(ctx, host_need({src, dst}));
+    if (st != LK_OK) return st;
+    void *ds, *dd;
+    if ((st = resolve(sc, src, false, &ds, "src")) != LK_OK) return st;
+    if ((st = resolve(sc, dst, true, &dd, "dst")) != LK_OK) return st;
+    chain_other(ctx, dd, (size_t)lk_tensor_nbytes(dst));
+    const cudaError_t e = lk::launch_quantize(dst->type, (const float *)ds, n, dd, ctx->stream, ctx->tune.nibble_order);
+    if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "quantize launch");
     count_launch(ctx);
     return finish(sc);
 }
@@ -1080,6 +1164,7 @@ lk_status lk_set_option(lk_ctx *ctx, const char *name, int64_t v) {
     else if (n == "nibble_order") ctx->tune.nibble_order = v ? 1 : 0;
     else if (n == "gemv_fix_gap") ctx->tune.fix_gap = v < 2 ? 2 : v > 255 ? 255 : (int)v;
     else if (n == "gemm_tc_min_n") ctx->gemm_tc_min_n = (int)v;
+    else if (n == "gemm_tc_min_work") ctx->gemm_tc_min_work = v < 0 ? 0 : v;
     else if (n == "gemm_tc_cluster") ctx->gemm_tc_cluster = (int)v;
     else if (n == "gemm_tc_precision") ctx->gemm_tc_precision = v < 0 ? 0 : v > 2 ? 2 : (int)v;
     else return fail(ctx, LK_EINVAL_ARG, "lk_set_option: unknown option " + n);
@@ -1112,6 +1197,7 @@ int64_t lk_get_option(lk_ctx *ctx, const char *name) {
     if (n == "nibble_order") return ctx->tune.nibble_order;
     if (n == "gemv_fix_gap") return ctx->tune.fix_gap;
     if (n == "gemm_tc_min_n") return ctx->gemm_tc_min_n;
+    if (n == "gemm_tc_min_work") return ctx->gemm_tc_min_work;
     if (n == "gemm_tc_cluster") return ctx->gemm_tc_cluster;
     if (n == "gemm_tc_launches") return ctx->gemm_tc_launches;
     if (n == "gemm_tc_precision") return ctx->gemm_tc_precision;

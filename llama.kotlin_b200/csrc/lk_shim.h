@@ -30,6 +30,7 @@ struct lk_ctx {
     int64_t chain_launches = 0;
     int64_t chain_unchecked = 0;     // chained launches since the time-out word was last read (lk::check_async_faults)
     uint32_t *barrier_flags = nullptr;   // this rank's flag words of lk_peer_barrier (word 14 = time-out), NULL before the first barrier
+    uint64_t barrier_flags_bytes = 0;
     int64_t barrier_unchecked = 0;
     int64_t capture_chain0 = 0, capture_barrier0 = 0;   // the two counters at lk_capture_begin
     int64_t chain_timeouts_seen = 0;     // time-outs already reported through a status, not yet read through the option
@@ -45,7 +46,8 @@ struct lk_ctx {
     void *attn_ws = nullptr;
     size_t attn_ws_size = 0;
     std::vector<void *> attn_ws_retired;
-    int gemm_tc_min_n = 16;                // N >= this takes the tcgen05 GEMM (0 = never); smaller N the generic kernel
+    int gemm_tc_min_n = 2;                 // N >= this takes the tcgen05 GEMM (0 = never)
+    int64_t gemm_tc_min_work = 1 << 21;    // ... if M * K * N is at least this many multiply-adds (three launches must pay)
     int gemm_tc_precision = 2;             // FP16 parts per operand of the tcgen05 GEMM: 2 = A hi+lo x b hi+lo (F32-grade, default), 1 = A hi+lo x b, 0 = single
     int gemm_tc_cluster = 1;               // CTAs per cluster sharing an activation tile by multicast (1, 2, 4); 1 measured fastest
     int64_t gemm_tc_launches = 0;          // tcgen05 GEMM launches so far (tests assert the path taken)

@@ -310,3 +310,30 @@ def dequantizeTensor(graphAllocator, tensor: GGMLTensor) -> GGMLTensor:
     B.check(B.lib().lk_compute_dequantize(lk.handle, describe(graphAllocator, tensor), d), lk.handle)
     res.data = out
     return res
+
+
+def computeQuantize(graphAllocator, context, src: GGMLTensor, dst: GGMLTensor) -> None:
+    """Destination-based quantizeTensor (lk_compute_quantize): src F32 -> dst Q8_0 / Q4_0 / Q4_1 in the allocator's buffer,
+    bit-exact with core/GGMLComputeOps.kt:1058-1087 / :1162-1203."""
+    lk = _ctx_of(graphAllocator)
+    B.check(B.lib().lk_compute_quantize(lk.handle, describe(graphAllocator, src), describe(graphAllocator, dst)), lk.handle)
+
+
+def quantizeTensor(graphAllocator, tensor: GGMLTensor, targetType: GGMLType) -> GGMLTensor:
+    """core/GGMLComputeOps.kt:1040 — returns a tensor of `targetType` whose `data` holds the packed blocks (like the
+    reference, the result lives in result.data with bufferId = -1, SURVEY F8: copy it into an allocator buffer before
+    handing it to computeMatMul)."""
+    lk = _ctx_of(graphAllocator)
+    targetType = GGMLType(targetType)
+    n = tensor.numElements()
+    out = np.empty(n // targetType.blockElements * targetType.byteSize, dtype=np.uint8)
+    res = GGMLTensor(type=targetType, ne=list(tensor.ne))
+    d = B.lk_tensor()
+    d.type = int(targetType)
+    for i in range(4):
+        d.ne[i] = int(tensor.ne[i])
+    d.host_base = out.ctypes.data
+    d.buffer_size = max(out.nbytes, 1)
+    B.check(B.lib().lk_compute_quantize(lk.handle, describe(graphAllocator, tensor), d), lk.handle)
+    res.data = out
+    return res

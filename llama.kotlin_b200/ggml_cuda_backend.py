@@ -13,6 +13,7 @@ import numpy as np
 
 from . import _binding as B
 from . import ggml_compute_ops as ops
+from .ggml_compute_ops import describe as _describe
 from .ggml_types import GGMLCGraph, GGMLOp, GGMLStatus, GGMLTensor, GGMLType
 
 
@@ -115,6 +116,10 @@ class GGMLCudaBackend:
         # the next call that synchronises (synchronize(), getTensor).  With checkFaults = True graphCompute synchronises
         # itself and returns GGMLStatus.FAILED for the step that faulted (tests, benches, debugging).
         self.checkFaults = False
+        # graphs without backend-private nodes (sharded matmuls, exchanges) are planned and issued by the library itself
+        # (lk_graph_compute: the same algorithm as _plan / _runNodes below, behind the C ABI so that the Kotlin binding gets
+        # the fused and chained launches without a port); False keeps the Python planner for every graph
+        self.useLibraryPlanner = True
 
     # -- GGMLBackend ---------------------------------------------------------------
     def getGuid(self) -> str:
@@ -172,13 +177,15 @@ class GGMLCudaBackend:
             d = ex["shard_swiglu"]
             d["group"].computeSwigluSharded(ga, d["gate"], d["up"], d["x"], d["g_full"], d["u_full"], node, d["row0"],
                                             d["M_total"], d.get("peers"), silu_full=d.get("silu_full"),
-                                            norm_w=d.get("norm_w"), eps=d.get("eps", 0.0), normed_dst=d.get("normed_dst"))
+                                            norm_w=d.get("norm_w"), eps=d.get("eps", 0.0), normed_dst=d.get("normed_dst"),
+                                            sync=d.get("sync"))
             return
         if op == GGMLOp.NONE:
             return
         if op == GGMLOp.MUL_MAT and ex is not None and "shard" in ex:
-            grp, row0, m_total, peers = ex["shard"]
-            grp.computeMatMulSharded(ga, node.src[0], node.src[1], node, row0, m_total, peers)
+            grp, row0, m_total, peers = ex["shard"][:4]
+            grp.computeMatMulSharded(ga, node.src[0], node.src[1], node, row0, m_total, peers,
+                                     sync=ex["shard"][4] if len(ex["shard"]) > 4 else None)
         elif op == GGMLOp.MUL_MAT:       # computeMulMat, core/GGMLComputeOps.kt:2647-2652
             ops.computeMatMul(ga, None, node.src[0], node.src[1], node)
         elif op == GGMLOp.ADD:
@@ -357,8 +364,52 @@ class GGMLCudaBackend:
             skip.update(idx[1:])
         return steps
 
+    # -- the graph as the C ABI takes it -------------------------------------------------------------------
+    @staticmethod
+    def nodeArray(ga, graph: GGMLCGraph):
+        """lk_graph_node[] of a graph, or None if it holds a node only this Python backend understands (`extra` dicts of
+        sharded.py) or an op outside the ABI's list."""
+        nodes = graph.nodes
+        arr = (B.lk_graph_node * max(len(nodes), 1))()
+        for i, nd in enumerate(nodes):
+            if isinstance(nd.extra, dict) or nd.op.name not in B.LK_OP:
+                return None
+            srcs = [s_ for s_ in nd.src[:4]]
+            while srcs and srcs[-1] is None:
+                srcs.pop()
+            if any(s_ is None for s_ in srcs):
+                return None
+            arr[i].op = B.LK_OP[nd.op.name]
+            arr[i].n_src = len(srcs)
+            arr[i].dst = _describe(ga, nd)
+            for k, s_ in enumerate(srcs):
+                arr[i].src[k] = _describe(ga, s_)
+            for k in range(4):
+                arr[i].op_params[k] = C.c_int32(int(nd.opParams[k]) & 0xFFFFFFFF).value
+        return arr
+
+    @staticmethod
+    def libraryPlan(ga, graph: GGMLCGraph, chain_mode: int = -1):
+        """lk_graph_plan of the graph as a list of dicts (tests; tools): the launches the library would make."""
+        arr = GGMLCudaBackend.nodeArray(ga, graph)
+        if arr is None:
+            return None
+        n = C.c_int32()
+        out = (B.lk_plan_launch * (len(graph.nodes) + 1))()
+        B.check(B.lib().lk_graph_plan(arr, len(graph.nodes), chain_mode, out, len(graph.nodes) + 1, C.byref(n)))
+        return [dict(kind=L.kind, node=L.node, rms=L.rms, add=L.add, extra=list(L.extra[:L.n_extra]), silu=L.silu, mul=L.mul,
+                     store_b=L.store_b, chain=L.chain, attn=list(L.attn) if L.kind == B.LK_PLAN_ATTN_STEP else None) for L in out[:n.value]]
+
     def _runNodes(self, ga, graph: GGMLCGraph, fuse: bool) -> None:
         nodes = graph.nodes
+        if self.useLibraryPlanner:
+            arr = self.nodeArray(ga, graph)
+            if arr is not None:
+                flags = 0 if fuse else B.LK_GRAPH_NO_FUSION
+                if fuse and self.chainOps is not None:
+                    flags |= B.LK_GRAPH_CHAIN_ALWAYS if self.chainOps else B.LK_GRAPH_CHAIN_NEVER
+                B.check(B.lib().lk_graph_compute(self.lk.handle, arr, len(nodes), flags), self.lk.handle)
+                return
         if not fuse:
             for node in nodes:
                 self._computeNode(ga, node)

@@ -1,0 +1,42 @@
+"""Multi-GPU parity under `pytest -m gpu` (skipped on a box with fewer than 2 GPUs): the row-sharded FFN of BASELINE
+config 5 at a small size on 2 ranks.  SURVEY §8(e) / VERDICT r1 weak #4: the fused exchange (peer-store epilogue, arrival
+and wait folded into the launches), the round-1 exchange (separate flag-barrier launches), the NCCL all-gather baseline
+and the unsharded single-GPU ops must agree bit for bit on everything the first FFN writes, every rank must hold the
+same gathered vectors, replays must repeat bit for bit, and no bounded wait may give up."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _ngpus():
+    try:
+        import torch
+        return torch.cuda.device_count()
+    except Exception:
+        return 0
+
+
+@pytest.mark.parametrize("hidden,ffn", [(512, 1408), (8192, 28672)])
+def test_sharded_ffn_two_ranks(hidden, ffn):
+    if _ngpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29541", os.path.join(ROOT, "tests", "multi_worker.py"), str(hidden), str(ffn)]
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert p.returncode == 0, p.stderr[-3000:]
+    res = json.loads(p.stdout.strip().splitlines()[-1])
+    assert res["all_ranks_identical"], res
+    assert not res["timed_out"], res
+    for m in ("sync", "barrier", "nccl"):
+        assert res[m + "_replays_identical"], (m, res)
+    assert res["sync_eq_barrier_layer0"] and res["sync_eq_nccl_layer0"] and res["sync_eq_single_layer0"], res
+    assert res["gathered_gemv_eq_fused_g"], res
+    assert res["sync_vs_barrier_out_err"] == 0.0, res            # same launches, only the exchange differs
+    assert res["sync_vs_nccl_out_err"] <= 1e-5 and res["sync_vs_single_out_err"] <= 1e-5, res     # RMSNorm prologue vs op: 1/rms rounding
+    assert res["oracle_err"] <= 1e-3, res

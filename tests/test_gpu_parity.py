@@ -118,6 +118,98 @@ def test_dequantize_golden_kats(O, ga, golden):
         assert same_f32_bits(got, np.frombuffer(bytes.fromhex(g["dequant_f32_hex"]), dtype=np.float32)), name
 
 
+# ---- A11 quantizeTensor on the device: bit-exact --------------------------------------------------
+def _quant_inputs():
+    rng = np.random.default_rng(23)
+    base = rng.normal(0.0, 0.02, 32 * 4096).astype(np.float32)
+    edge = np.zeros(32 * 16, np.float32)
+    edge[32:64] = rng.normal(0, 1e-4, 32)                 # amax ~ 3e-4: Q8_0 scale 2.4e-6, half denormal -> floatToHalf's F11 branch
+    edge[64:96] = rng.normal(0, 3e-6, 32)                 # Q4_0 scale in the half-denormal range too
+    edge[96:128] = 5.0                                    # constant block: Q4_1 d = 0 -> 1
+    edge[128:160] = np.where(np.arange(32) % 2 == 0, 0.0, -0.0)       # +-0 ties: fmin / fmax keep the LAST candidate
+    edge[160:192] = rng.normal(0, 1, 32); edge[165] = np.nan          # NaN propagates through maxOf / minOf
+    edge[192:224] = rng.normal(0, 1, 32); edge[200] = np.inf
+    edge[224:256] = rng.normal(0, 1e4, 32)                # scale above the half range: overflow branch of floatToHalf
+    edge[256:288] = np.float32(70000.0) * rng.choice([-1, 1], 32)
+    edge[288:320] = (np.arange(32) - 15.5).astype(np.float32)         # exact .5 ties of round-half-even
+    edge[320:352] = rng.normal(0, 1, 32).astype(np.float32) * np.float32(2.0 ** -20)
+    edge[352:384] = np.float32(6.0e-5)                    # around the smallest normal half
+    return {"synthetic": base, "edge": edge, "uniform": rng.uniform(-3, 3, 32 * 1031).astype(np.float32)}
+
+
+@pytest.mark.parametrize("tname", ["Q8_0", "Q4_0", "Q4_1"])
+@pytest.mark.parametrize("which", ["synthetic", "edge", "uniform"])
+def test_quantize_bit_exact(O, ga, tname, which):
+    """lk_compute_quantize against the oracle's restatement of quantizeTensor (core/GGMLComputeOps.kt:1058-1087,
+    :1162-1203; floatToHalf incl. F11): every byte equal, host- and device-resident."""
+    gt, ot = QT[tname]
+    x = _quant_inputs()[which]
+    want = O.quantize(ot, x)
+    ga.reset()
+    src = ga.allocateTensor(GGMLTensor(GGMLType.F32, [x.size]))
+    ga.setBytes(src, x)
+    got = lk.quantizeTensor(ga, src, gt).data
+    assert got.dtype == np.uint8 and got.size == want.size
+    bad = np.nonzero(got != want)[0]
+    assert bad.size == 0, (tname, which, bad[:8], got[bad[:8]], want[bad[:8]])
+    dst = ga.allocateTensor(GGMLTensor(gt, [x.size]))
+    lk.computeQuantize(ga, None, src, dst)
+    assert np.array_equal(ga.getBytes(dst), want)
+    # and the round trip through the device dequantizer is the oracle's
+    assert same_f32_bits(lk.dequantizeTensor(ga, dst).data, O.dequantize(ot, want, x.size))
+
+
+def test_quantize_errors(ga):
+    ga.reset()
+    src = ga.allocateTensor(GGMLTensor(GGMLType.F32, [48]))
+    with pytest.raises(lk.IllegalArgumentException):          # require(numElements % QK == 0)
+        lk.quantizeTensor(ga, src, GGMLType.Q8_0)
+
+
+# ---- A9 strided F32 operands (getFloat / setFloat through nb[], core/GGMLTypes.kt:328-380) ----------------
+def test_matmul_with_strided_f32_operands(O, ga):
+    """b given as a transposed view (K fastest in memory: nb = [4K, 4]) and dst as a view with padded rows: the
+    result is what the contiguous call gives, bit for bit, and the bytes between dst's rows are untouched."""
+    M, K, N = 64, 256, 6
+    blocks = O.quantize(Q8_0, synth_weights(61, M, K))
+    x = synth_acts(61, K, N)                      # contiguous layout: element (j, k) at j + k * N
+    want = host_matmul(ga, GGMLType.Q8_0, blocks, K, M, x, N)
+    ga.reset()
+    a = ga.allocateTensor(GGMLTensor(GGMLType.Q8_0, [K, M]))
+    ga.setBytes(a, blocks)
+    bt = ga.allocateTensor(GGMLTensor(GGMLType.F32, [K, N]))          # storage of the transpose: element (j, k) at k + j * K
+    ga.setBytes(bt, np.ascontiguousarray(x.reshape(K, N).T))
+    b = GGMLTensor(GGMLType.F32, [N, K], nb=[4 * K, 4, 4 * K * N, 4 * K * N], bufferId=bt.bufferId, dataOffset=bt.dataOffset)
+    pad = 10                                       # dst rows of N floats, stored pad floats apart
+    store = ga.allocateTensor(GGMLTensor(GGMLType.F32, [pad, M]))
+    ga.setBytes(store, np.full(pad * M, -7.0, np.float32))
+    d = GGMLTensor(GGMLType.F32, [N, M], nb=[4, 4 * pad, 4 * pad * M, 4 * pad * M], bufferId=store.bufferId, dataOffset=store.dataOffset)
+    lk.computeMatMul(ga, None, a, b, d)
+    got = ga.getFloats(store).reshape(M, pad)
+    assert same_f32_bits(got[:, :N].reshape(-1), want)
+    assert np.all(got[:, N:] == -7.0)
+    # out-of-bounds through the strides -> IndexOutOfBoundsException
+    far = GGMLTensor(GGMLType.F32, [N, M], nb=[4, 1 << 30, 1 << 40, 1 << 40], bufferId=store.bufferId, dataOffset=store.dataOffset)
+    with pytest.raises(lk.IndexOutOfBoundsException):
+        lk.computeMatMul(ga, None, a, b, far)
+
+
+def test_elementwise_with_strided_operands_on_device(O):
+    be = lk.GGMLCudaBackend(0)
+    ga2 = lk.GGMLGraphAllocator(be, size=1 << 20)
+    n, st = 1000, 3
+    raw = np.random.default_rng(5).normal(0, 1, n * st).astype(np.float32)
+    s_ = ga2.allocateTensor(GGMLTensor(GGMLType.F32, [n * st]))
+    ga2.setBytes(s_, raw)
+    y = ga2.allocateTensor(GGMLTensor(GGMLType.F32, [n]))
+    ga2.setBytes(y, raw[:n])
+    xs = GGMLTensor(GGMLType.F32, [n], nb=[4 * st, 4 * st * n, 4 * st * n, 4 * st * n], bufferId=s_.bufferId, dataOffset=s_.dataOffset, buffer=s_.buffer)
+    dst = ga2.allocateTensor(GGMLTensor(GGMLType.F32, [n]))
+    lk.computeAdd(ga2, None, xs, y, dst)
+    assert same_f32_bits(ga2.getFloats(dst), O.add(raw[::st].copy(), raw[:n]))
+    be.free()
+
+
 # ---- K1 decode GEMV --------------------------------------------------------------------
 @pytest.mark.parametrize("tname", ["Q8_0", "Q4_0", "Q4_1"])
 @pytest.mark.parametrize("M,K", [(8, 64), (16, 128), (33, 192), (148, 2048), (1000, 4096), (296, 8192),

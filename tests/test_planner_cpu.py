@@ -40,6 +40,7 @@ class Recorder:
 def make_backend(chain=None):
     be = object.__new__(GGMLCudaBackend)      # no context: the planner itself never touches the library
     be.fuseOps, be.chainOps, be.maxChain = True, chain, 8
+    be.useLibraryPlanner = False              # these tests watch the Python planner's calls; the C planner is compared below
     return be
 
 
@@ -158,3 +159,87 @@ def test_fast_key_follows_node_identity_and_offsets():
     swapped = GGMLCGraph(nodes=graph.nodes[:5] + [clone] + graph.nodes[6:], allocator=ga)
     assert GGMLCudaBackend._fastKey(swapped) != k0                              # another object in the same place
     assert GGMLCudaBackend._signature(swapped) == GGMLCudaBackend._signature(graph)   # ... that the full signature equates
+
+
+# ---- the planner behind the C ABI (lk_graph_plan, csrc/lk_planner.cu): same decisions as the Python planner ------------
+import pytest
+
+from llama_kotlin_b200 import _binding as B
+
+
+def _python_launches(be, ga, graph, monkeypatch):
+    """What the Python planner issues, as comparable records keyed by node index."""
+    idx = {id(n): i for i, n in enumerate(graph.nodes)}
+    calls = run(be, ga, graph, Recorder(), monkeypatch)
+    out = []
+
+    def fused_rec(a, b, dst, kw, chain):
+        kw = kw or {}
+        r = dict(kind="fused" if kw else "node", node=idx[id(dst)], chain=chain,
+                 rms=None, add=idx[id(kw["sum_dst"])] if "sum_dst" in kw else None,
+                 extra=[idx[id(d)] for _, d in kw.get("extra", [])],
+                 silu=idx[id(kw["silu_dst"])] if kw.get("silu_dst") is not None else None,
+                 mul=idx[id(kw["mul_dst"])] if kw.get("mul_dst") is not None else None,
+                 store_b=bool(kw.get("store_b", True)) if "norm_x" in kw else None)
+        if "norm_x" in kw:      # the RMS_NORM node whose dst is this launch's b
+            r["rms"] = next(i for i, n in enumerate(graph.nodes) if n.op == GGMLOp.RMS_NORM and n.dataOffset == b.dataOffset)
+        return r
+    cid = 0
+    for c in calls:
+        if c[0] == "fused":
+            out.append(fused_rec(c[1], c[2], c[3], c[4], -1))
+        elif c[0] == "chain":
+            for (a, b, dst, kw) in c[1]:
+                out.append(fused_rec(a, b, dst, kw, cid))
+            cid += 1
+        elif c[0] == "attn_step":
+            out.append(dict(kind="attn"))
+        else:
+            out.append(dict(kind="node", name=c[0]))
+    return out
+
+
+def _library_launches(ga, graph, chain_mode):
+    plan = GGMLCudaBackend.libraryPlan(ga, graph, chain_mode)
+    out = []
+    for L in plan:
+        if L["kind"] == B.LK_PLAN_ATTN_STEP:
+            out.append(dict(kind="attn"))
+        elif L["kind"] == B.LK_PLAN_NODE and L["chain"] < 0 and graph.nodes[L["node"]].op != GGMLOp.MUL_MAT:
+            out.append(dict(kind="node", name=None))
+        else:
+            nn = lambda v: None if v < 0 else v   # noqa: E731
+            out.append(dict(kind="fused" if L["kind"] == B.LK_PLAN_FUSED else "node", node=L["node"], chain=L["chain"], rms=nn(L["rms"]),
+                            add=nn(L["add"]), extra=L["extra"], silu=nn(L["silu"]), mul=nn(L["mul"]),
+                            store_b=bool(L["store_b"]) if L["rms"] >= 0 else None))
+    return out
+
+
+@pytest.mark.parametrize("attention", [False, True])
+@pytest.mark.parametrize("chain", [None, True, False])
+def test_library_planner_makes_the_python_planner_s_launches(monkeypatch, attention, chain):
+    """lk_graph_plan through ctypes on the decoder-layer graph (with and without the attention core, chaining on / off /
+    automatic): launch for launch what GGMLCudaBackend._plan / _runNodes issue — fused neighbours, stacked groups, the
+    SwiGLU pair, which launch stores the RMS_NORM's dst, which launches form one chain, the attention steps."""
+    ga, graph = make_graph(2, attention=attention)
+    py = _python_launches(make_backend(chain), ga, graph, monkeypatch)
+    lib = _library_launches(ga, graph, -1 if chain is None else int(chain))
+    assert len(py) == len(lib)
+    for a, b in zip(py, lib):
+        assert a["kind"] == b["kind"], (a, b)
+        if a["kind"] == "fused" or (a["kind"] == "node" and "node" in a and "node" in b):
+            for k in ("node", "chain", "rms", "add", "extra", "silu", "mul", "store_b"):
+                assert a[k] == b[k], (k, a, b)
+
+
+def test_library_planner_plain_graph_and_argument_errors():
+    ga = GGMLGraphAllocator(None, size=1 << 20)
+    a = ga.allocateTensor(GGMLTensor(GGMLType.F32, [8]))
+    b = ga.allocateTensor(GGMLTensor(GGMLType.F32, [8]))
+    d = GGMLTensor(GGMLType.F32, [8], op=GGMLOp.ADD, src=[a, b] + [None] * 8, bufferId=0, dataOffset=ga.allocateTensor(GGMLTensor(GGMLType.F32, [8])).dataOffset)
+    g = GGMLCGraph(nodes=[d], allocator=ga)
+    plan = GGMLCudaBackend.libraryPlan(ga, g)
+    assert len(plan) == 1 and plan[0]["kind"] == B.LK_PLAN_NODE and plan[0]["node"] == 0 and plan[0]["chain"] == -1
+    n = B.C.c_int32()
+    assert B.lib().lk_graph_plan(None, 3, -1, None, 0, B.C.byref(n)) == B.LK_EINVAL_ARG
+    assert B.lib().lk_graph_plan(None, 0, -1, None, 0, B.C.byref(n)) == B.LK_OK and n.value == 0
