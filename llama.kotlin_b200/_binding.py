@@ -10,7 +10,8 @@ import os
 import re
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libllamakotlin_cuda.so")
+# LK_LIBRARY: another build of the same library (A/B measurements under tools/); symbols it lacks are left unbound
+LIB_PATH = os.environ.get("LK_LIBRARY") or os.path.join(_HERE, "libllamakotlin_cuda.so")
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "llamakotlin_cuda.h")
 
 LK_OK, LK_EINVAL_DIM, LK_EINVAL_TYPE, LK_EBOUNDS, LK_ENOTIMPL, LK_ECUDA, LK_ENCCL, LK_EINVAL_ARG, LK_ENOMEM = range(9)
@@ -161,6 +162,8 @@ def lib() -> C.CDLL:
                                                  C.POINTER(lk_shard_sync)]),
     }
     for name, (res, args) in sig.items():
+        if not hasattr(L, name) and os.environ.get("LK_LIBRARY"):
+            continue
         fn = getattr(L, name)
         fn.restype, fn.argtypes = res, args
     _lib = L

@@ -298,8 +298,9 @@ __device__ __forceinline__ unsigned long long lk_gtime() {
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
     return t;
 }
+__device__ __forceinline__ unsigned lk_smid() { unsigned v; asm volatile("mov.u32 %0, %%smid;" : "=r"(v)); return v; }
 #define LK_TL(slot) do { if (p.tl) { unsigned long long *q_ = p.tl + (size_t)blockIdx.x * LK_TL_SLOTS; \
-    if ((slot) == 0) { q_[0] = lk_gtime(); q_[31] = (unsigned long long)clock64(); } \
+    if ((slot) == 0) { q_[0] = lk_gtime(); q_[31] = (unsigned long long)clock64(); q_[30] = lk_smid(); } \
     else { q_[(slot)] = (unsigned long long)clock64(); if ((slot) == 7) q_[29] = lk_gtime(); } } } while (0)
 #else
 #define LK_TL(slot) do { } while (0)
@@ -330,7 +331,15 @@ struct GemvSide {
     uint32_t mask[28];
 };
 static_assert(sizeof(GemvSide) <= 128, "side words share the first 256 bytes with the 16 mbarriers");
+#ifdef LK_GEMV_NO_RANGE_FIX     // A/B builds only (tools/ab_build.sh): what the detection and the cold call sites cost
+template <int TYPE> __host__ __device__ constexpr bool gemv_has_fixup() { return false; }
+#else
 template <int TYPE> __host__ __device__ constexpr bool gemv_has_fixup() { return TYPE == T_Q4_0 || TYPE == T_Q4_1 || TYPE == T_Q8_0; }
+#endif
+// Where the detection sits was measured on one B200 box (profiles/r02_gemv_range_fix_ab.txt, headline step, GB/s):
+// round-1 kernel 4610; no detection 4557; detection inside prep_x (this code) 4490; detection by a dedicated 10th warp
+// that scans x beside the consumers 4016 (the extra warp alone, exiting at once, already costs 1.5 %); detection by the
+// idle lanes of the producer warp: slower still (they share a warp with the lane that streams the weights).
 
 __device__ __forceinline__ float fmin3_abs(float a, float b, float c) {   // min(|a|, |b|, |c|)
     float d;

@@ -402,7 +402,7 @@ class GGMLCudaBackend:
 
     def _runNodes(self, ga, graph: GGMLCGraph, fuse: bool) -> None:
         nodes = graph.nodes
-        if self.useLibraryPlanner:
+        if self.useLibraryPlanner and hasattr(B.lib(), "lk_graph_compute"):     # (an older build under LK_LIBRARY may lack it)
             arr = self.nodeArray(ga, graph)
             if arr is not None:
                 flags = 0 if fuse else B.LK_GRAPH_NO_FUSION

@@ -34,6 +34,7 @@ def main():
         dist.all_gather_object(out, obj)
         return out
     group = lk.ShardGroup(be, rank, world, exchange)
+    group.init_nccl()        # outside any capture: the communicator cannot be created while a sequence is being recorded
     # full weights, same on every rank (seeded); every rank cuts out its rows
     full = {}
     for li in range(layers):

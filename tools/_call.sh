@@ -1,9 +1,13 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -q -x > gpurun_out/b_tests_all.txt 2>&1; echo "all rc=$?" >> gpurun_out/b_tests_all.txt
-tail -25 gpurun_out/b_tests_all.txt
-timeout 300 python bench.py --no-cpu-baseline > gpurun_out/b_bench.json 2>gpurun_out/b_bench.err; echo "bench rc=$?"; tail -c 600 gpurun_out/b_bench.json; tail -5 gpurun_out/b_bench.err
-timeout 100 python bench.py --no-cpu-baseline --no-extras --opt gemv_fix_gap=255 > gpurun_out/b_bench_nofix.json 2>gpurun_out/b_bench_nofix.err; python -c "
+timeout 500 python -m pytest tests -m gpu -q -x --timeout=120 > gpurun_out/g_tests_all.txt 2>&1; echo "all rc=$?" >> gpurun_out/g_tests_all.txt
+tail -8 gpurun_out/g_tests_all.txt
+for v in cur r1 nofix cur r1 nofix; do
+  if [ $v = cur ]; then unset LK_LIBRARY; else export LK_LIBRARY=$PWD/tools/_ab/lib_$v.so; fi
+  timeout 60 python bench.py --no-cpu-baseline --no-extras --steps 200 > gpurun_out/g_bench_$v.json 2>gpurun_out/g_bench_$v.err
+  python -c "
 import json
-for f in ('b_bench','b_bench_nofix'):
-    d=json.load(open('gpurun_out/'+f+'.json')); print(f, d['value'], d['config']['dependent_chain_GBps'], d['e2e']['value'])
-"
+d=json.load(open('gpurun_out/g_bench_$v.json')); print('$v', round(d['value'],1), round(d['config']['dependent_chain_GBps'],1), round(d['e2e']['value'],1))
+" 2>&1 | tail -1
+done
+unset LK_LIBRARY
+timeout 60 tools/overlap_timeline 24 2 > gpurun_out/g_overlap_timeline.txt 2>&1; tail -3 gpurun_out/g_overlap_timeline.txt
