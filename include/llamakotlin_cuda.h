@@ -271,6 +271,21 @@ LK_API lk_status   lk_compute_kv_append(lk_ctx *ctx, const lk_tensor *src, const
 LK_API lk_status   lk_compute_attention_decode(lk_ctx *ctx, const lk_tensor *q, const lk_tensor *kcache,
                                                const lk_tensor *vcache, const lk_tensor *pos, float scale,
                                                const lk_tensor *dst);
+/* lk_compute_attention_decode for callers that cannot allocate (code under CUDA-graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments, same kernel and same results as lk_compute_attention_decode, but the call allocates nothing — no
+ * cudaMalloc, cudaFree, pinned memory or staging arena: all tensors must be device-resident and contiguous (a host
+ * tensor returns LK_EINVAL_ARG), and the kernel's scratch memory (per-head tickets + split partials) is a file-scope
+ * static device array of LK_ATTN_NOALLOC_SCRATCH_BYTES that every GPU which loads the library holds until the process
+ * exits.  A shape that needs more (256-byte-rounded numHeads * 4 + numHeads * splits * (headDim + 4) * 4 bytes, splits
+ * <= 3 * SMs / numHeads: 234 KB for 32 heads of 128) is rejected with LK_EINVAL_ARG and a message that names both
+ * sizes.  All calls on one device share the array and find the previous call's contents in it (the part that must
+ * start at zero is cleared in front of every launch, stream-ordered): calls that overlap on the GPU — two streams or
+ * two contexts of one device — race; serialise them.                                                              */
+#define LK_ATTN_NOALLOC_SCRATCH_BYTES (512 * 1024)
+LK_API lk_status   lk_compute_attention_decode_noalloc(lk_ctx *ctx, const lk_tensor *q, const lk_tensor *kcache,
+                                                       const lk_tensor *vcache, const lk_tensor *pos, float scale,
+                                                       const lk_tensor *dst);
 /* One decode step of LlamaAttention.forward's core in ONE launch, model/LlamaAttention.kt:87-99 + :104-123:
  * qRope = applyRoPE(q), kRope = applyRoPE(k), kvCache.updateKey(kRope), kvCache.updateValue(v), computeAttention.
  * q, k, v: this token's projections (numHeads * headDim floats each) before RoPE; table / pos / head_dim as

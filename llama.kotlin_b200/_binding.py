@@ -138,6 +138,7 @@ def lib() -> C.CDLL:
         "lk_compute_rope": (i32, [vp, tp, tp, tp, i32, tp]),
         "lk_compute_kv_append": (i32, [vp, tp, tp, tp]),
         "lk_compute_attention_decode": (i32, [vp, tp, tp, tp, tp, C.c_float, tp]),
+        "lk_compute_attention_decode_noalloc": (i32, [vp, tp, tp, tp, tp, C.c_float, tp]),
         "lk_compute_attention_step": (i32, [vp, tp, tp, tp, tp, tp, i32, tp, tp, C.c_float, tp, tp, tp]),
         "lk_capture_begin": (i32, [vp]),
         "lk_capture_end": (i32, [vp, C.POINTER(vp)]),

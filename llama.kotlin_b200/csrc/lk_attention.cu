@@ -375,4 +375,47 @@ cudaError_t launch_attn_decode(const float *q, const float *kc, const float *vc,
     return launch_kernel(attn_decode_kernel<64>, grid, dim3(ATT_THREADS), smem, s, pdl, p, tmk, tmv);
 }
 
+// ---- the variant that allocates nothing (lk_compute_attention_decode_noalloc) ---------------------------------------
+// Added for callers that cannot call cudaMalloc (code under CUDA-graph capture,
+// tight serving loops, harnesses that forbid it); no counterpart in the reference.  The scratch memory of the decode
+// attention (per-head tickets + the split partials the last CTA of a head merges) lives in this file-scope device array
+// instead of the context's cudaMalloc'ed workspace: ATTN_STATIC_SCRATCH_BYTES on every GPU that loads the library, held
+// until the process exits.  Host code may not pass the array's NAME to a kernel (in host code it is a host-side
+// stand-in, not a device address): the device address is fetched once per device, with that device current, by
+// cudaGetSymbolAddress below.  Every call on a device shares the array and finds the last call's contents in it: the
+// tickets, which must start at zero, are cleared by a stream-ordered memset in front of every launch; the partials are
+// written before they are read.  Two calls that overlap on the GPU (two streams, two contexts of one device) race.
+constexpr size_t ATTN_STATIC_SCRATCH_BYTES = 512 * 1024;
+static __device__ __align__(256) unsigned char g_attn_static_scratch[ATTN_STATIC_SCRATCH_BYTES];
+constexpr int ATTN_STATIC_MAX_DEVICES = 64;
+static void *g_attn_static_addr[ATTN_STATIC_MAX_DEVICES];     // device address of the array, per device (0 = not fetched yet)
+
+size_t attn_static_scratch_capacity() { return ATTN_STATIC_SCRATCH_BYTES; }
+// what one launch really touches: the tickets (rounded to 256 bytes) + nheads * splits partials of (head_dim + 4) floats
+size_t attn_scratch_needed(int head_dim, int nheads, int64_t max_seq, int sm_count) {
+    if (nheads <= 0 || max_seq <= 0) return 0;
+    return (((size_t)nheads * 4 + 255) & ~(size_t)255) + (size_t)nheads * attn_splits(nheads, max_seq, sm_count) * (head_dim + 4) * 4;
+}
+
+cudaError_t launch_attn_decode_static(int device, const float *q, const float *kc, const float *vc, const int32_t *pos, int head_dim,
+                                      int nheads, int64_t max_seq, float scale, float *dst, int sm_count, cudaStream_t s) {
+    if (device < 0 || device >= ATTN_STATIC_MAX_DEVICES) return cudaErrorInvalidDevice;
+    if (attn_scratch_needed(head_dim, nheads, max_seq, sm_count) > ATTN_STATIC_SCRATCH_BYTES) return cudaErrorInvalidValue;
+    int cur = -1;
+    cudaError_t e = cudaGetDevice(&cur);
+    if (e != cudaSuccess) return e;
+    if (cur != device) return cudaErrorInvalidDevice;          // the symbol's address is per device: that device must be current
+    if (!g_attn_static_addr[device]) {
+        void *ptr = nullptr;
+        e = cudaGetSymbolAddress(&ptr, g_attn_static_scratch);
+        if (e != cudaSuccess) return e;
+        if (!ptr || ((uintptr_t)ptr & 255)) return cudaErrorInvalidSymbol;
+        g_attn_static_addr[device] = ptr;
+    }
+    void *scratch = g_attn_static_addr[device];
+    e = cudaMemsetAsync(scratch, 0, ((size_t)nheads * 4 + 255) & ~(size_t)255, s);      // tickets start at zero whatever the last call left
+    if (e != cudaSuccess) return e;
+    return launch_attn_decode(q, kc, vc, pos, head_dim, nheads, max_seq, scale, dst, scratch, sm_count, s, false, nullptr);
+}
+
 }  // namespace lk

@@ -144,4 +144,11 @@ cudaError_t launch_attn_decode(const float *q, const float *kc, const float *vc,
                                int nheads, int64_t max_seq, float scale, float *dst, void *workspace, int sm_count,
                                cudaStream_t s, bool pdl = false, const AttnStep *step = nullptr);
 
+// The decode attention with its scratch memory in a file-scope static device array (no allocation of any kind); see
+// lk_attention.cu.  cudaErrorInvalidValue: the shape needs more than attn_static_scratch_capacity() bytes.
+size_t attn_static_scratch_capacity();
+size_t attn_scratch_needed(int head_dim, int nheads, int64_t max_seq, int sm_count);
+cudaError_t launch_attn_decode_static(int device, const float *q, const float *kc, const float *vc, const int32_t *pos, int head_dim,
+                                      int nheads, int64_t max_seq, float scale, float *dst, int sm_count, cudaStream_t s);
+
 }  // namespace lk

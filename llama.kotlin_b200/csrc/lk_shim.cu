@@ -1042,6 +1042,49 @@ lk_status lk_compute_attention_decode(lk_ctx *ctx, const lk_tensor *q, const lk_
     return finish(sc);
 }
 
+// lk_compute_attention_decode without any allocation (no counterpart in the reference):
+// device-resident contiguous tensors only — a host tensor would need the staging arena — and the scratch
+// memory is the static device array of lk_attention.cu.  Calls no cudaMalloc / cudaFree and nothing that allocates device
+// or pinned memory; the only host-side growth possible is the small std::vector of the launch bookkeeping.
+lk_status lk_compute_attention_decode_noalloc(lk_ctx *ctx, const lk_tensor *q, const lk_tensor *kcache, const lk_tensor *vcache,
+                                              const lk_tensor *pos, float scale, const lk_tensor *dst) {
+    if (!ctx || !q || !kcache || !vcache || !pos || !dst) return fail(ctx, LK_EINVAL_ARG, "attention (noalloc): NULL argument");
+    if (q->type != LK_TYPE_F32 || kcache->type != LK_TYPE_F32 || vcache->type != LK_TYPE_F32 || dst->type != LK_TYPE_F32)
+        return fail(ctx, LK_EINVAL_TYPE, "attention (noalloc): F32 only");
+    lk_status st = pos_check(ctx, pos, "attention (noalloc)");
+    if (st != LK_OK) return st;
+    const int64_t D = kcache->ne[0], H = kcache->ne[1], max_seq = kcache->ne[2] > 0 ? kcache->ne[2] : 1;
+    if (!same_shape(kcache, vcache)) return fail(ctx, LK_EINVAL_DIM, "attention (noalloc): key and value caches differ in shape");
+    if (num_elements(q) != D * H || !same_shape(q, dst)) return fail(ctx, LK_EINVAL_DIM, "attention (noalloc): q / dst must hold headDim * numHeads elements");
+    const lk_tensor *all[] = {q, kcache, vcache, pos, dst};
+    void *ptr[5];
+    for (int i = 0; i < 5; i++) {
+        const lk_tensor *t = all[i];
+        if (!t->dev_buf || t->host_base)
+            return fail(ctx, LK_EINVAL_ARG, "attention (noalloc): device-resident tensors only (this entry point allocates nothing, so it cannot stage host tensors)");
+        if (!contiguous_f32(t)) return fail(ctx, LK_EINVAL_ARG, "attention (noalloc): contiguous tensors only");
+        const int64_t nb = lk_tensor_nbytes(t);
+        if (nb < 0 || t->data_offset > t->dev_buf->size || (uint64_t)nb > t->dev_buf->size - t->data_offset)
+            return fail(ctx, LK_EBOUNDS, "attention (noalloc): tensor bytes exceed the device buffer");
+        if (t->data_offset % 16) return fail(ctx, LK_EINVAL_ARG, "attention (noalloc): dataOffset must be 16-byte aligned on device");
+        ptr[i] = (uint8_t *)t->dev_buf->ptr + t->data_offset;
+    }
+    if (D != 64 && D != 128) return fail(ctx, LK_ENOTIMPL, "attention (noalloc): headDim must be 64 or 128");
+    if (H <= 0 || H > (1 << 20) || max_seq > (1 << 24)) return fail(ctx, LK_EINVAL_DIM, "attention (noalloc): bad numHeads / maxSeq");
+    const size_t need = lk::attn_scratch_needed((int)D, (int)H, max_seq, ctx->sm_count), cap = lk::attn_static_scratch_capacity();
+    if (need > cap)
+        return fail(ctx, LK_EINVAL_ARG, "attention (noalloc): this shape needs " + std::to_string(need) + " bytes of scratch memory, the static array holds " +
+                    std::to_string(cap) + " (LK_ATTN_NOALLOC_SCRATCH_BYTES); use lk_compute_attention_decode");
+    LK_CUDA(ctx, cudaSetDevice(ctx->device));
+    chain_other(ctx, ptr[4], (size_t)D * H * 4);
+    const cudaError_t e = lk::launch_attn_decode_static(ctx->device, (const float *)ptr[0], (const float *)ptr[1], (const float *)ptr[2],
+                                                        (const int32_t *)ptr[3], (int)D, (int)H, max_seq, scale, (float *)ptr[4], ctx->sm_count, ctx->stream);
+    if (e == cudaErrorNotSupported) return fail(ctx, LK_ENOTIMPL, "attention (noalloc): unsupported shape / alignment");
+    if (e != cudaSuccess) return lk::cuda_fail(ctx, e, "attention (noalloc) launch");
+    count_launch(ctx);
+    return LK_OK;
+}
+
 lk_status lk_compute_attention_step(lk_ctx *ctx, const lk_tensor *q, const lk_tensor *k, const lk_tensor *v,
                                     const lk_tensor *table, const lk_tensor *pos, int32_t head_dim, const lk_tensor *kcache,
                                     const lk_tensor *vcache, float scale, const lk_tensor *q_rope_dst,
