@@ -627,27 +627,30 @@ __device__ __forceinline__ void peer_store_rows(const GemvParams &p, const float
         for (int i = lane; i < n; i += 32) dstq[i] = outbuf[i];
     }
 }
-// After the last peer store of the CTA (call with all consumer threads): the last CTA of the grid to get here arrives on
-// every rank's counter.  fence + atomic in every CTA, atomic + fence in the last one: every CTA's peer stores are ordered
-// before the remote arrivals (the "last block" pattern, at system scope).
+// After the last peer store of the CTA (call with all consumer threads): EVERY CTA arrives on every rank's counter, with a
+// weight — the CTAs of one launch add up to EXCHANGE_UNIT whatever the grid size — so the waiting side needs to know the
+// number of ranks only, and nothing funnels through a last CTA (that cost a local atomic round trip and a second
+// system-scope fence on the critical path).  fence.sys after the bar.sync: this CTA's peer stores (made by its other
+// threads) are performed at system scope before the arrival is issued (release pattern: fence; relaxed red).
+constexpr unsigned long long EXCHANGE_UNIT = 1ull << 20;
+__device__ __forceinline__ void red_relaxed_sys_add(unsigned long long *p, unsigned long long v) {
+    asm volatile("red.relaxed.sys.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
 __device__ __forceinline__ void exchange_signal(const GemvParams &p, int tid, int nct) {
     asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
     if (tid == 0) {
+        const unsigned long long g = gridDim.x, c = blockIdx.x;
+        const unsigned long long w = (c + 1ull) * EXCHANGE_UNIT / g - c * EXCHANGE_UNIT / g;
         __threadfence_system();
-        const unsigned long long done = atomicAdd(p.sig_done, 1ull);
-        if (done == (unsigned long long)gridDim.x - 1ull) {
-            atomicExch(p.sig_done, 0ull);              // re-armed for the next launch that signals this exchange point
-            __threadfence_system();
 #pragma unroll 1
-            for (int q = 0; q < p.sig_n; q++) red_release_sys_add(p.sig_peer[q], 1ull);
-        }
+        for (int q = 0; q < p.sig_n; q++) red_relaxed_sys_add(p.sig_peer[q], w);
     }
 }
 // Before the activations are read: wait until every rank's producer launch of this epoch has arrived.  The counter only
-// grows (wait_n per epoch); the epoch is this CTA's ticket / grid size.  Bounded: a rank that died cannot hang the device;
+// grows (wait_n * EXCHANGE_UNIT per epoch); the epoch is this CTA's ticket / grid size.  Bounded: a rank that died cannot hang the device;
 // a time-out is counted and reported by the next synchronising call on the context.
 __device__ __forceinline__ void exchange_wait(const GemvParams &p, unsigned long long ticket) {
-    const unsigned long long target = (ticket / gridDim.x + 1ull) * (unsigned long long)p.wait_n;
+    const unsigned long long target = (ticket / gridDim.x + 1ull) * (unsigned long long)p.wait_n * EXCHANGE_UNIT;
     const long long t0 = clock64();
     while (ld_acquire_sys(p.wait_ctr) < target) {
         if (clock64() - t0 > 4000000000ll) { atomicAdd(p.sync_timeout, 1u); break; }

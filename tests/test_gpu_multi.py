@@ -36,7 +36,7 @@ def test_sharded_ffn_two_ranks(hidden, ffn):
     for m in ("sync", "barrier", "nccl"):
         assert res[m + "_replays_identical"], (m, res)
     assert res["sync_eq_barrier_layer0"] and res["sync_eq_nccl_layer0"] and res["sync_eq_single_layer0"], res
-    assert res["gathered_gemv_eq_fused_g"], res
+    assert res["gathered_gemv_eq_single_gpu"], res
     assert res["sync_vs_barrier_out_err"] == 0.0, res            # same launches, only the exchange differs
     assert res["sync_vs_nccl_out_err"] <= 1e-5 and res["sync_vs_single_out_err"] <= 1e-5, res     # RMSNorm prologue vs op: 1/rms rounding
     assert res["oracle_err"] <= 1e-3, res
