@@ -353,10 +353,15 @@ __device__ __forceinline__ float fmin3_abs(float a, float b, float c) {   // min
 // mantissa bits; a non-finite element poisons the block scale with NaN instead.
 // CG: read the activations / gain with ld.global.cg (L2 only).  The chained kernel below reads vectors that other CTAs
 // of the SAME launch wrote a phase earlier; a non-coherent (ld.global.nc) or L1-cached load could return a stale line.
-template <bool CG>
-__device__ __forceinline__ float4 ld_vec4(const float4 *q) { return CG ? __ldcg(q) : __ldg(q); }
+// CG = 0: ld.global.nc (read-only data path); 1: ld.global.cg (L2 only: the chained kernel, whose CTAs read vectors that
+// other CTAs of the SAME launch wrote a phase earlier — an L1 line from the earlier phase would be stale); 2: plain
+// ld.global (L1-allocating): the fused / sharded launches, whose activations may have been written over NVLink while
+// the kernel was already running — but never read by it before its acquire, so no stale L1 line can exist, and the
+// second and third pass of the RMSNorm prologue hit L1 instead of paying the L2 latency again.
+template <int CG>
+__device__ __forceinline__ float4 ld_vec4(const float4 *q) { return CG == 1 ? __ldcg(q) : CG == 2 ? *q : __ldg(q); }
 
-template <int TYPE, int NP, bool FUSED, bool CG = false>
+template <int TYPE, int NP, bool FUSED, int CG = 0>
 __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int tid, int nthreads, GemvSide *side) {
     constexpr int TB = NP * 8 - 2;     // |T| <= 2^TB: 22 (three byte planes) or 14 (two)
     const int ntasks = p.nblk * 2;
@@ -367,7 +372,7 @@ __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int ti
     // chained kernel, K <= 16 * nthreads: every thread owns at most one task, so the values loaded for the sum of squares
     // (and the gain, fetched under the same latency) stay in registers for the conversion: one L2 round trip on the
     // hand-off's critical path instead of three.  Same per-thread order of operations as the two-pass code.
-    const bool keep = CG && FUSED && p.pro_mode == 1 && ntasks <= nthreads;
+    const bool keep = CG == 1 && FUSED && p.pro_mode == 1 && ntasks <= nthreads;
     float v[16], gw[16];
     if (FUSED && p.pro_mode == 1) {
         float *part = (float *)(xs + (size_t)p.nblk * gemv_xslot_words(NP)) - 32;   // tail of the last slots: rewritten below
@@ -657,7 +662,7 @@ __device__ __forceinline__ void exchange_wait(const GemvParams &p, unsigned long
     }
 }
 
-template <bool FUSED, bool CG = false>
+template <bool FUSED, bool CG = false, bool PEER = FUSED>
 __device__ __forceinline__ void finish_rows(const GemvParams &p, float *dst, const float *red, int nred, int64_t out0, int warp, int lane) {
     const int sub = lane & 7, rsel = lane >> 3;
     const int nc4 = p.red_stride >> 2;   // float4 chunks per row (columns beyond npairs hold zeros)
@@ -683,7 +688,7 @@ __device__ __forceinline__ void finish_rows(const GemvParams &p, float *dst, con
                 v = __fadd_rn(CG ? __ldcg(p.residual + o) : p.residual[o], v);
             }
             dst[o] = v;
-            if (FUSED && p.npeers) ((float *)((uint8_t *)red - p.red_off + p.out_off))[r] = v;   // staged for peer_store_rows
+            if (PEER && p.npeers) ((float *)((uint8_t *)red - p.red_off + p.out_off))[r] = v;   // staged for peer_store_rows
         }
     }
 }
@@ -727,8 +732,12 @@ __device__ __forceinline__ void finish_pair(const GemvParams &p, const float *re
 // this one and streams its weights while this one computes.
 // FUSED = false is the plain computeMatMul launch: no prologue, one weight segment, plain store (the fused
 // variants cost the plain one ~8 % when they share its code: measured, profiles/r01j_gemv_ab.txt).
-template <int TYPE, int MAXW, int MINB, int NP, bool FUSED>
+// MODE 0: the plain launch.  1: every fusion (prologue, segments, epilogues) + peers + exchange.  2: the plain launch with
+// peer stores and the exchange signal / wait only (lk_compute_matmul_sharded: the 28-warp instantiation of mode 1 spills
+// under its 64-register cap, this one does not).
+template <int TYPE, int MAXW, int MINB, int NP, int MODE>
 __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvParams p) {
+    constexpr bool FUSED = MODE == 1, PEER = MODE != 0;
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t *full = (uint64_t *)smem;                   // [GEMV_MAX_STAGES]
     uint64_t *empty = full + GEMV_MAX_STAGES;            // [GEMV_MAX_STAGES]
@@ -826,18 +835,18 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
         if (lane < GEMV_RED_PAD) red[r * p.red_stride + p.ncw * 8 + lane] = 0.f;
     if (warp == 0) { if (lane < 28) side->mask[lane] = 0u; if (lane == 28) side->any = 0u; }
     unsigned long long xticket = 0;
-    if (FUSED && p.wait_n > 0 && tid == 0) xticket = atomicAdd(p.wait_ticket, 1ull);   // issued early: its latency hides under the barrier below
+    if (PEER && p.wait_n > 0 && tid == 0) xticket = atomicAdd(p.wait_ticket, 1ull);   // issued early: its latency hides under the barrier below
     __syncthreads();   // barriers initialised by the producer
     if (p.wait_mode != GEMV_WAIT_END) {
         pdl_wait();                // activations may be the previous kernel's output
         pdl_launch_dependents();   // the next kernel can start its prologue / weight prefetch under our main loop
     }
-    if (FUSED && p.wait_n > 0) {   // sharded matmul: the activations are gathered from every rank (peer stores + arrival counters)
+    if (PEER && p.wait_n > 0) {   // sharded matmul: the activations are gathered from every rank (peer stores + arrival counters)
         if (tid == 0) exchange_wait(p, xticket);
         asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
     }
     if (tid == 0) LK_TL(3);
-    prep_x<TYPE, NP, FUSED, FUSED>(p, xs, tid, nct, side);   // fused launches read x with ld.global.cg: it may have been written over NVLink
+    prep_x<TYPE, NP, FUSED, PEER ? 2 : 0>(p, xs, tid, nct, side);   // fused launches: plain L1-allocating loads (see ld_vec4)
     if (tid == 0) LK_TL(24);
     asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");   // activation planes written
     if (tid == 0) LK_TL(4);
@@ -885,9 +894,9 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
         if (epi_mode != 1 && row0 + p.stage_rows - red_base > p.red_rows) {
             // partial-sum buffer full (a CTA that owns more rows than it holds)
             asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
-            LK_GEMV_FIXUP(FUSED, FUSED ? p.pro_w : nullptr, FUSED ? p.pro_mode : 0, nct, (!FUSED || seg == 0) ? p.a : p.a_seg[seg - 1], r_begin + red_base, row0 - red_base, red)
-            finish_rows<FUSED>(p, seg_dst, red, row0 - red_base, p.row_offset + r_begin + red_base, warp, lane);
-            if (FUSED && p.npeers) {
+            LK_GEMV_FIXUP(PEER, FUSED ? p.pro_w : nullptr, FUSED ? p.pro_mode : 0, nct, (!FUSED || seg == 0) ? p.a : p.a_seg[seg - 1], r_begin + red_base, row0 - red_base, red)
+            finish_rows<FUSED, false, PEER>(p, seg_dst, red, row0 - red_base, p.row_offset + r_begin + red_base, warp, lane);
+            if (PEER && p.npeers) {
                 asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
                 peer_store_rows(p, (const float *)(smem + p.out_off), row0 - red_base, p.row_offset + r_begin + red_base, warp, lane);
             }
@@ -958,9 +967,9 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
     if (tid == 0) LK_TL(6);
     asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
     if (tid == 0) LK_TL(20);
-    LK_GEMV_FIXUP(FUSED, FUSED ? p.pro_w : nullptr, FUSED ? p.pro_mode : 0, nct, (!FUSED || seg == 0) ? p.a : p.a_seg[seg - 1], r_begin + red_base, nrows - red_base, red)
-    finish_rows<FUSED>(p, seg_dst, red, nrows - red_base, p.row_offset + r_begin + red_base, warp, lane);
-    if (FUSED && p.npeers) {
+    LK_GEMV_FIXUP(PEER, FUSED ? p.pro_w : nullptr, FUSED ? p.pro_mode : 0, nct, (!FUSED || seg == 0) ? p.a : p.a_seg[seg - 1], r_begin + red_base, nrows - red_base, red)
+    finish_rows<FUSED, false, PEER>(p, seg_dst, red, nrows - red_base, p.row_offset + r_begin + red_base, warp, lane);
+    if (PEER && p.npeers) {
         asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
         peer_store_rows(p, (const float *)(smem + p.out_off), nrows - red_base, p.row_offset + r_begin + red_base, warp, lane);
     }
@@ -972,15 +981,15 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
     }
     if (epi_mode == 1) {
         asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
-        LK_GEMV_FIXUP(FUSED, p.pro_w, p.pro_mode, nct, p.a, r_begin, nrows, red)
-        LK_GEMV_FIXUP(FUSED, p.pro_w, p.pro_mode, nct, p.a_seg[0], r_begin, nrows, red + (size_t)p.pair_off * p.red_stride)
+        LK_GEMV_FIXUP(PEER, p.pro_w, p.pro_mode, nct, p.a, r_begin, nrows, red)
+        LK_GEMV_FIXUP(PEER, p.pro_w, p.pro_mode, nct, p.a_seg[0], r_begin, nrows, red + (size_t)p.pair_off * p.red_stride)
         finish_pair(p, red, nrows, p.pair_off, p.row_offset + r_begin, warp, lane);
         if (p.npeers) {
             asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
             peer_store_rows(p, (const float *)(smem + p.out_off), nrows, p.row_offset + r_begin, warp, lane);
         }
     }
-    if (FUSED && p.sig_n > 0) exchange_signal(p, tid, nct);   // the grid's last CTA to get here arrives on every rank's counter
+    if (PEER && p.sig_n > 0) exchange_signal(p, tid, nct);   // every CTA arrives on every rank's counter
     if (tid == 0) {
         LK_TL(7);
         // keep completion order = launch order so a later launch's wait covers every earlier one
@@ -1143,7 +1152,7 @@ __global__ void __launch_bounds__((CHAIN_W + 1) * 32, 1) gemv_chain_kernel(const
 #pragma unroll 1
         for (int r = warp; r < p.red_rows; r += CHAIN_W)
             if (lane < GEMV_RED_PAD) red[r * p.red_stride + p.ncw * 8 + lane] = 0.f;
-        prep_x<TYPE, NP, true, true>(p, xs, tid, NCT, side);
+        prep_x<TYPE, NP, true, 1>(p, xs, tid, NCT, side);
         asm volatile("bar.sync 1, %0;" ::"r"(NCT) : "memory");   // activation planes (and the padding zeros) written
 
         XRegs<NP> x;
@@ -1245,9 +1254,9 @@ __global__ void __launch_bounds__((CHAIN_W + 1) * 32, 1) gemv_chain_kernel(const
 // ---------------------------------------------------------------------------
 // host side: shape analysis + launch
 // ---------------------------------------------------------------------------
-template <int TYPE, int MAXW, int MINB, int NP, bool FUSED>
+template <int TYPE, int MAXW, int MINB, int NP, int MODE>
 static cudaError_t launch_one(const GemvParams &p, int grid, int smem, int pdl, cudaStream_t s) {
-    auto kern = gemv_kernel<TYPE, MAXW, MINB, NP, FUSED>;
+    auto kern = gemv_kernel<TYPE, MAXW, MINB, NP, MODE>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
@@ -1265,21 +1274,22 @@ static cudaError_t launch_one(const GemvParams &p, int grid, int smem, int pdl, 
     return cudaLaunchKernelEx(&cfg, kern, p);
 }
 
-template <int TYPE, int NP, bool FUSED>
+template <int TYPE, int NP, int MODE>
 static cudaError_t launch_fused(const GemvParams &p, int grid, int smem, int pdl, cudaStream_t s) {
-    if (p.cwarps <= 8) return launch_one<TYPE, 8, 2, NP, FUSED>(p, grid, smem, pdl, s);
-    if (p.cwarps <= 12) return launch_one<TYPE, 12, 2, NP, FUSED>(p, grid, smem, pdl, s);
-    if (p.cwarps <= 16) return launch_one<TYPE, 16, 2, NP, FUSED>(p, grid, smem, pdl, s);
-    return launch_one<TYPE, 28, 1, NP, FUSED>(p, grid, smem, pdl, s);   // K up to 28672 (Llama-2-70B down projection): one CTA per SM
+    if (p.cwarps <= 8) return launch_one<TYPE, 8, 2, NP, MODE>(p, grid, smem, pdl, s);
+    if (p.cwarps <= 12) return launch_one<TYPE, 12, 2, NP, MODE>(p, grid, smem, pdl, s);
+    if (p.cwarps <= 16) return launch_one<TYPE, 16, 2, NP, MODE>(p, grid, smem, pdl, s);
+    return launch_one<TYPE, 28, 1, NP, MODE>(p, grid, smem, pdl, s);   // K up to 28672 (Llama-2-70B down projection): one CTA per SM
 }
 
 template <int TYPE, int NP>
-static cudaError_t launch_type(const GemvParams &p, bool fused, int grid, int smem, int pdl, cudaStream_t s) {
-    return fused ? launch_fused<TYPE, NP, true>(p, grid, smem, pdl, s) : launch_fused<TYPE, NP, false>(p, grid, smem, pdl, s);
+static cudaError_t launch_type(const GemvParams &p, int mode, int grid, int smem, int pdl, cudaStream_t s) {
+    return mode == 1 ? launch_fused<TYPE, NP, 1>(p, grid, smem, pdl, s) : mode == 2 ? launch_fused<TYPE, NP, 2>(p, grid, smem, pdl, s)
+                                                                                    : launch_fused<TYPE, NP, 0>(p, grid, smem, pdl, s);
 }
 template <int TYPE, int NP>
 static cudaError_t launch_plain(const GemvParams &p, int grid, int smem, int pdl, cudaStream_t s) {   // K-quants: no fused variants
-    return launch_fused<TYPE, NP, false>(p, grid, smem, pdl, s);
+    return launch_fused<TYPE, NP, 0>(p, grid, smem, pdl, s);
 }
 
 cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const float *b, float *dst,
@@ -1400,7 +1410,8 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
     p.nstages = nst;
     const int smem = p.stage_off + nst * stage_bytes;
     // peer stores and the exchange signal / wait live in the fused instantiation only (the plain kernel keeps its size)
-    const bool fused = p.pro_mode != 0 || p.residual != nullptr || p.nseg > 1 || p.npeers > 0 || p.sig_n > 0 || p.wait_n > 0;
+    const bool full = p.pro_mode != 0 || p.residual != nullptr || p.nseg > 1;
+    const int fused = full ? 1 : (p.npeers > 0 || p.sig_n > 0 || p.wait_n > 0) ? 2 : 0;     // kernel MODE
     if (kq && fused) return cudaErrorNotSupported;
 
     switch (type * 4 + np) {
