@@ -414,11 +414,11 @@ LK_API lk_status   lk_compute_swiglu_sharded(lk_ctx *ctx, const lk_tensor *gate_
  * An exchange point ("slot", 0 .. LK_MAX_EXCHANGE_SLOTS-1) is a 64-bit arrival counter inside every rank's flag buffer
  * (LK_FLAG_BYTES bytes, zeroed before first use, peer-mapped like for lk_peer_barrier; the barrier's 16 words are its
  * first 64 bytes, so one buffer serves both):
- *   signal_slot >= 0: when every CTA of this launch has finished its peer stores, the last one arrives (+1, release at
- *                     system scope) on that slot of EVERY rank's flag buffer;
+ *   signal_slot >= 0: every CTA of this launch, after its peer stores and a system-scope fence, arrives on that slot of
+ *                     EVERY rank's flag buffer (a weighted add; one launch adds up to 2^20 per rank whatever its grid);
  *   wait_slot   >= 0: before the launch reads its activations it waits until that slot of THIS rank's flag buffer has
- *                     received one arrival from every rank (nranks per use of the slot: counters only grow, the epoch of
- *                     a launch is counted on the device, so a captured sequence can be replayed).
+ *                     received a whole launch's arrivals from every rank (counters only grow, the epoch of a launch is
+ *                     counted on the device, so a captured sequence can be replayed).
  * One producer launch and one consumer launch per use of a slot on every rank, in the same order on every rank; a vector
  * that peers write may be rewritten only by a launch that comes after a wait on a LATER exchange of the same ranks
  * (then every reader is known to have finished), which the FFN pattern [SwiGLU -> slot 0 -> down -> slot 1 -> next SwiGLU]

@@ -361,8 +361,12 @@ __device__ __forceinline__ float fmin3_abs(float a, float b, float c) {   // min
 template <int CG>
 __device__ __forceinline__ float4 ld_vec4(const float4 *q) { return CG == 1 ? __ldcg(q) : CG == 2 ? *q : __ldg(q); }
 
+// pre / use_pre: the first round's 16 activations of this thread, loaded by the caller at kernel entry (independent
+// launches: x is final before the kernel starts, so its DRAM latency — every launch has its own cold x — hides under the
+// barrier set-up instead of heading the critical path; ncu: 26 % of the stall samples sat on the first use of that load).
 template <int TYPE, int NP, bool FUSED, int CG = 0>
-__device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int tid, int nthreads, GemvSide *side) {
+__device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int tid, int nthreads, GemvSide *side,
+                                       const float4 *pre = nullptr, bool use_pre = false) {
     constexpr int TB = NP * 8 - 2;     // |T| <= 2^TB: 22 (three byte planes) or 14 (two)
     const int ntasks = p.nblk * 2;
     // Fused RMSNorm prologue (K3 folded in): every CTA needs all of x anyway, so it also takes the sum of squares
@@ -426,9 +430,10 @@ __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int ti
         if (on) {
             if (!keep) {
             const float4 *src = (const float4 *)(p.b + (size_t)task * 16);
+            const bool from_pre = pre != nullptr && use_pre && base == 0;
 #pragma unroll
             for (int i = 0; i < 4; i++) {
-                const float4 f = ld_vec4<CG>(src + i);
+                const float4 f = from_pre ? pre[i] : ld_vec4<CG>(src + i);
                 v[4 * i] = f.x; v[4 * i + 1] = f.y; v[4 * i + 2] = f.z; v[4 * i + 3] = f.w;
             }
             }
@@ -732,12 +737,14 @@ __device__ __forceinline__ void finish_pair(const GemvParams &p, const float *re
 // this one and streams its weights while this one computes.
 // FUSED = false is the plain computeMatMul launch: no prologue, one weight segment, plain store (the fused
 // variants cost the plain one ~8 % when they share its code: measured, profiles/r01j_gemv_ab.txt).
-// MODE 0: the plain launch.  1: every fusion (prologue, segments, epilogues) + peers + exchange.  2: the plain launch with
+// MODE 0: the plain launch.  3: the plain launch that is independent of everything in flight (WAIT_END; its activations
+// are preloaded at kernel entry).  1: every fusion (prologue, segments, epilogues) + peers + exchange.  2: the plain launch with
 // peer stores and the exchange signal / wait only (lk_compute_matmul_sharded: the 28-warp instantiation of mode 1 spills
 // under its 64-register cap, this one does not).
 template <int TYPE, int MAXW, int MINB, int NP, int MODE>
 __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvParams p) {
-    constexpr bool FUSED = MODE == 1, PEER = MODE != 0;
+    constexpr bool FUSED = MODE == 1, PEER = MODE == 1 || MODE == 2;
+    constexpr bool INDEP = MODE == 3;     // MODE 3: the plain launch in WAIT_END mode (independent of everything in flight), known at compile time
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t *full = (uint64_t *)smem;                   // [GEMV_MAX_STAGES]
     uint64_t *empty = full + GEMV_MAX_STAGES;            // [GEMV_MAX_STAGES]
@@ -750,7 +757,7 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
     // launch (WAIT_END) signals at once; a launch that waits for its predecessor signals only after that wait, so
     // that whatever starts next finds everything before this launch complete (the host-side bookkeeping,
     // gemv_wait_mode in lk_shim.cu, closes its in-flight set at exactly that point).
-    if (p.wait_mode == GEMV_WAIT_END) pdl_launch_dependents();
+    if (INDEP || p.wait_mode == GEMV_WAIT_END) pdl_launch_dependents();
     {   // touch both hot parameter lines now: the two constant-cache misses overlap instead of serialising later
         const int t0 = p.K, t1 = p.red_stride;
         asm volatile("" ::"r"(t0), "r"(t1));
@@ -789,7 +796,7 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
                 mbar_init(&empty[i], p.cwarps);
             }
             fence_mbar_init();
-            if (p.wait_mode == GEMV_WAIT_FULL) pdl_wait();
+            if (!INDEP && p.wait_mode == GEMV_WAIT_FULL) pdl_wait();
             pol_w = l2_policy_evict_first();
 #pragma unroll 1
             for (; s < p.nstages && advance(); s++) {   // first pass over the ring: no waiting
@@ -824,6 +831,14 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
     // ===== consumer warps =====
     // Everything that does not depend on the activations happens before griddepcontrol.wait.
     const int nct = p.cwarps * 32;
+    // an independent launch (WAIT_END) may read its activations at once: issue the first round's loads now
+    float4 pre[4];
+    constexpr bool use_pre = INDEP;
+    if (use_pre && tid < p.nblk * 2) {
+        const float4 *src = (const float4 *)(p.b + (size_t)tid * 16);
+#pragma unroll
+        for (int i = 0; i < 4; i++) pre[i] = __ldg(src + i);
+    }
     const int cw = p.rg == 1 ? warp : warp % p.ncw;   // column warp
     const int rgi = p.rg == 1 ? 0 : warp / p.ncw;     // row group
     const int col = cw * 32 + lane;                   // block column
@@ -837,7 +852,7 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
     unsigned long long xticket = 0;
     if (PEER && p.wait_n > 0 && tid == 0) xticket = atomicAdd(p.wait_ticket, 1ull);   // issued early: its latency hides under the barrier below
     __syncthreads();   // barriers initialised by the producer
-    if (p.wait_mode != GEMV_WAIT_END) {
+    if (!INDEP && p.wait_mode != GEMV_WAIT_END) {
         pdl_wait();                // activations may be the previous kernel's output
         pdl_launch_dependents();   // the next kernel can start its prologue / weight prefetch under our main loop
     }
@@ -846,7 +861,7 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
         asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
     }
     if (tid == 0) LK_TL(3);
-    prep_x<TYPE, NP, FUSED, PEER ? 2 : 0>(p, xs, tid, nct, side);   // fused launches: plain L1-allocating loads (see ld_vec4)
+    prep_x<TYPE, NP, FUSED, PEER ? 2 : 0>(p, xs, tid, nct, side, INDEP ? pre : nullptr, use_pre);   // fused launches: plain L1-allocating loads (see ld_vec4)
     if (tid == 0) LK_TL(24);
     asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");   // activation planes written
     if (tid == 0) LK_TL(4);
@@ -993,7 +1008,7 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
     if (tid == 0) {
         LK_TL(7);
         // keep completion order = launch order so a later launch's wait covers every earlier one
-        if (p.wait_mode == GEMV_WAIT_END) pdl_wait();
+        if (INDEP || p.wait_mode == GEMV_WAIT_END) pdl_wait();
     }
 }
 
@@ -1285,7 +1300,7 @@ static cudaError_t launch_fused(const GemvParams &p, int grid, int smem, int pdl
 template <int TYPE, int NP>
 static cudaError_t launch_type(const GemvParams &p, int mode, int grid, int smem, int pdl, cudaStream_t s) {
     return mode == 1 ? launch_fused<TYPE, NP, 1>(p, grid, smem, pdl, s) : mode == 2 ? launch_fused<TYPE, NP, 2>(p, grid, smem, pdl, s)
-                                                                                    : launch_fused<TYPE, NP, 0>(p, grid, smem, pdl, s);
+         : mode == 3 ? launch_fused<TYPE, NP, 3>(p, grid, smem, pdl, s) : launch_fused<TYPE, NP, 0>(p, grid, smem, pdl, s);
 }
 template <int TYPE, int NP>
 static cudaError_t launch_plain(const GemvParams &p, int grid, int smem, int pdl, cudaStream_t s) {   // K-quants: no fused variants
@@ -1411,8 +1426,8 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
     const int smem = p.stage_off + nst * stage_bytes;
     // peer stores and the exchange signal / wait live in the fused instantiation only (the plain kernel keeps its size)
     const bool full = p.pro_mode != 0 || p.residual != nullptr || p.nseg > 1;
-    const int fused = full ? 1 : (p.npeers > 0 || p.sig_n > 0 || p.wait_n > 0) ? 2 : 0;     // kernel MODE
-    if (kq && fused) return cudaErrorNotSupported;
+    const int fused = full ? 1 : (p.npeers > 0 || p.sig_n > 0 || p.wait_n > 0) ? 2 : (!kq && p.wait_mode == GEMV_WAIT_END) ? 3 : 0;     // kernel MODE
+    if (kq && fused) return cudaErrorNotSupported;     // (the K-quant instantiations are mode 0 only)
 
     switch (type * 4 + np) {
         case T_Q4_0 * 4 + 2: return launch_type<T_Q4_0, 2>(p, fused, grid, smem, tune.pdl, s);

@@ -63,10 +63,11 @@ struct GemvFusion {
 };
 // Cross-GPU exchange folded into a sharded launch (no separate barrier kernel, SURVEY §8e / DESIGN §6).  An exchange
 // point is a 64-bit arrival counter in every rank's peer-mapped flag buffer:
-//   signal: when all CTAs of this launch have done their peer stores, the last one arrives (+1, release at system scope)
-//           on every rank's counter (sig_peer[0..sig_n), own rank included); sig_done is a local CTA counter it re-arms;
-//   wait:   before the launch reads its activations every CTA waits until the local counter has received wait_n arrivals
-//           of its epoch (epoch = ticket / grid size, wait_ticket is a local counter); bounded, time-outs counted in *timeout.
+//   signal: every CTA of the launch, after its peer stores and a system-scope fence, adds its weight to every rank's
+//           counter (sig_peer[0..sig_n), own rank included); the weights of one launch add up to 2^20 whatever its grid;
+//   wait:   before the launch reads its activations every CTA waits until the local counter has received wait_n * 2^20 of
+//           its epoch (epoch = ticket / grid size, wait_ticket is a local counter); bounded, time-outs counted in *timeout.
+// sig_done is unused since the per-CTA arrival replaced the last-CTA funnel (kept so that the flag-buffer layout stays).
 struct GemvSync {
     int sig_n = 0;
     unsigned long long *sig_peer[8] = {};

@@ -1,8 +1,11 @@
 mkdir -p gpurun_out
-timeout 420 python -m pytest tests/test_gpu_multi.py -m gpu -q -x --timeout=300 > gpurun_out/k_tests_multi.txt 2>&1; echo "multi rc=$?" >> gpurun_out/k_tests_multi.txt
-tail -6 gpurun_out/k_tests_multi.txt | cut -c1-600
-timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 50 --warmup 3 --no-extras > gpurun_out/k_bench_n2.json 2>gpurun_out/k_bench_n2.err; echo "bench2 rc=$?"
-python -c "
+timeout 300 python -m pytest tests/test_gpu_parity.py tests/test_gpu_chain.py tests/test_gpu_kquants.py -m gpu -q -x --timeout=120 -k "gemv or chain or fused or layer or kq or matmul" > gpurun_out/n_tests.txt 2>&1; echo "rc=$?" >> gpurun_out/n_tests.txt
+tail -3 gpurun_out/n_tests.txt
+for v in cur r1 cur r1; do
+  if [ $v = cur ]; then unset LK_LIBRARY; else export LK_LIBRARY=$PWD/tools/_ab/lib_$v.so; fi
+  timeout 60 python bench.py --no-cpu-baseline --no-extras --steps 200 > gpurun_out/n_bench_$v.json 2>gpurun_out/n_bench_$v.err
+  python -c "
 import json
-d=json.load(open('gpurun_out/k_bench_n2.json')); print('n2', round(d['value'],1), d['config']['us_per_ffn'], d['config']['launches_per_step'], d['e2e']['value'], d['config']['other_exchanges'])
-"
+d=json.load(open('gpurun_out/n_bench_$v.json')); print('$v', round(d['value'],1), round(d['config']['dependent_chain_GBps'],1), round(d['e2e']['value'],1), d['roofline']['frac'])
+" 2>&1 | tail -1
+done
