@@ -373,10 +373,10 @@ __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int ti
     // (F32 partials per thread, warp shuffles, one pass over <= 28 warp totals) and multiplies with 1/rms and the
     // gain while converting.  1/rms instead of the op's IEEE division: <= 2 ulp from the unfused RMSNorm.
     float rinv = 1.0f;
-    // chained kernel, K <= 16 * nthreads: every thread owns at most one task, so the values loaded for the sum of squares
+    // chained kernel and fused launches, K <= 16 * nthreads: every thread owns at most one task, so the values loaded for the sum of squares
     // (and the gain, fetched under the same latency) stay in registers for the conversion: one L2 round trip on the
     // hand-off's critical path instead of three.  Same per-thread order of operations as the two-pass code.
-    const bool keep = CG == 1 && FUSED && p.pro_mode == 1 && ntasks <= nthreads;
+    const bool keep = CG != 0 && FUSED && p.pro_mode == 1 && ntasks <= nthreads;
     float v[16], gw[16];
     if (FUSED && p.pro_mode == 1) {
         float *part = (float *)(xs + (size_t)p.nblk * gemv_xslot_words(NP)) - 32;   // tail of the last slots: rewritten below

@@ -1,13 +1,14 @@
 /*
  * lk_oracle_kq.c — CPU restatement of the reference's K-quant and BitNet 1.58 paths.
  *
- * TEST INFRASTRUCTURE ONLY (see lk_oracle.h).  Parity status: PARITY UNPINNED for Q2_K / Q4_K in the strict sense — the
- * reference holds no byte-level vectors for these formats, they are Kotlin-only (oracle/_ref, the tree's ggml C, cannot
- * anchor them) and a literal restatement of its Q2_K / Q4_K quantizer + dequantizer pair does not meet the reference's
- * own accuracy thresholds.  What does pin this file: source citation line by line, hand-computed block
- * KATs, a second independent numpy restatement (tests/kq_np.py, bit for bit) and, for Q8_K and BitNet 1.58, the
- * thresholds / expectations of nativeTest core/GGMLKQuantAccuracyTest.kt and GGMLBitNet158Test.kt
- * (tests/test_oracle_kquants.py).
+ * TEST INFRASTRUCTURE ONLY (see lk_oracle.h).  Parity status: PINNED BY HAND-WORKED BLOCKS.  The reference holds no
+ * byte-level vectors for these formats and they are Kotlin-only (oracle/_ref, the tree's ggml C, cannot anchor them), so
+ * this file is pinned by (1) blocks whose bytes and values are derived by hand, line by line, from the cited Kotlin
+ * (tests/golden/make_kquant_golden.py -> kquant_reference_tests.json; no oracle call produces the expected fields),
+ * (2) a second independent numpy restatement (tests/kq_np.py, bit for bit), (3) the inputs and thresholds of
+ * nativeTest core/GGMLKQuantAccuracyTest.kt and GGMLBitNet158Test.kt.  Those hand-worked blocks also show that the
+ * reference's Q2_K and Q4_K quantizer / dequantizer pairs are not inverses of each other, which is why its
+ * own MSE thresholds for those two formats cannot be met by its own code; Q8_K's and BitNet's are met.
  *
  * These are the REFERENCE'S OWN formats, not ggml's: same block sizes as ggml-common.h (84 / 144 / 292 bytes per 256
  * elements) but a simpler field meaning, and the dot products address blocks as the Kotlin code does — including where

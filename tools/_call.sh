@@ -1,11 +1,16 @@
 mkdir -p gpurun_out
-timeout 300 python -m pytest tests/test_gpu_parity.py tests/test_gpu_chain.py tests/test_gpu_kquants.py -m gpu -q -x --timeout=120 -k "gemv or chain or fused or layer or kq or matmul" > gpurun_out/n_tests.txt 2>&1; echo "rc=$?" >> gpurun_out/n_tests.txt
-tail -3 gpurun_out/n_tests.txt
-for v in cur r1 cur r1; do
-  if [ $v = cur ]; then unset LK_LIBRARY; else export LK_LIBRARY=$PWD/tools/_ab/lib_$v.so; fi
-  timeout 60 python bench.py --no-cpu-baseline --no-extras --steps 200 > gpurun_out/n_bench_$v.json 2>gpurun_out/n_bench_$v.err
-  python -c "
-import json
-d=json.load(open('gpurun_out/n_bench_$v.json')); print('$v', round(d['value'],1), round(d['config']['dependent_chain_GBps'],1), round(d['e2e']['value'],1), d['roofline']['frac'])
-" 2>&1 | tail -1
+timeout 300 python -m pytest tests/test_gpu_parity.py tests/test_gpu_chain.py -m gpu -q -x --timeout=120 -k "fused or layer or rms_norm or softmax or chain" > gpurun_out/r_tests.txt 2>&1; echo "rc=$?" >> gpurun_out/r_tests.txt; tail -3 gpurun_out/r_tests.txt | cut -c1-300
+for o in "" "--opt gemv_ctas_per_sm=2" "--opt gemv_warps=16" "--opt gemv_ctas_per_sm=2 --opt gemv_smem_budget=57344"; do
+  echo "== layer_bench $o"; timeout 120 python tools/layer_bench.py --steps 30 $o 2>/dev/null | python -c "
+import json,sys
+d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print(round(d['tok_s'],1), round(d['us_per_layer'],2), d['launches_per_token'])"
 done
+echo "== ctx 2048"; timeout 120 python tools/layer_bench.py --steps 30 --ctx 2048 2>/dev/null | python -c "
+import json,sys
+d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print(round(d['tok_s'],1), round(d['us_per_layer'],2))"
+LK_LIBRARY=$PWD/tools/_ab/lib_r1.so timeout 120 python tools/layer_bench.py --steps 30 2>/dev/null | python -c "
+import json,sys
+d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('r1', round(d['tok_s'],1), round(d['us_per_layer'],2))"
+timeout 100 python bench.py --no-cpu-baseline 2>/dev/null | python -c "
+import json,sys
+d=json.loads(sys.stdin.read()); e=d['config']['other_paths']['elementwise']; print({k:(round(v['GBps']),round(v['roofline']['frac'],3)) for k,v in e.items()})"
