@@ -364,7 +364,7 @@ __device__ __forceinline__ float4 ld_vec4(const float4 *q) { return CG == 1 ? __
 // pre / use_pre: the first round's 16 activations of this thread, loaded by the caller at kernel entry (independent
 // launches: x is final before the kernel starts, so its DRAM latency — every launch has its own cold x — hides under the
 // barrier set-up instead of heading the critical path; ncu: 26 % of the stall samples sat on the first use of that load).
-template <int TYPE, int NP, bool FUSED, int CG = 0>
+template <int TYPE, int NP, bool FUSED, int CG = 0, bool DETECT = true>
 __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int tid, int nthreads, GemvSide *side,
                                        const float4 *pre = nullptr, bool use_pre = false) {
     constexpr int TB = NP * 8 - 2;     // |T| <= 2^TB: 22 (three byte planes) or 14 (two)
@@ -475,7 +475,7 @@ __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int ti
         ab = max(ab, __shfl_xor_sync(0xffffffffu, ab, 1));   // unsigned order: finite < inf < NaN
         int e = (int)(ab >> 23);
         const bool nonfinite = e == 255;
-        if (gemv_has_fixup<TYPE>()) {
+        if (DETECT && gemv_has_fixup<TYPE>()) {
             // Range check, cheap in the common case: min |x| over the block (3-input min.abs, 8 instructions).  Only a block
             // whose smallest |x| is zero or below 2^-fix_gap of its maximum takes the exact look (smallest NON-ZERO |x| as
             // 2 * bits - 1: the shift drops the sign, +-0 wraps to 0xFFFFFFFF); both lanes of a pair branch alike.
@@ -551,6 +551,46 @@ __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int ti
     }
 }
 
+// this thread's block column of the activation planes: shared memory -> registers
+template <int TYPE, int NP>
+__device__ __forceinline__ void load_xregs(XRegs<NP> &x, const uint32_t *xs, int colc) {
+    const uint4 *slot = (const uint4 *)(xs + (size_t)colc * gemv_xslot_words(NP));
+#pragma unroll
+    for (int pl = 0; pl < NP; pl++)
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            const uint4 v = slot[pl * 2 + h];
+            x.q[pl][4 * h] = v.x; x.q[pl][4 * h + 1] = v.y; x.q[pl][4 * h + 2] = v.z; x.q[pl][4 * h + 3] = v.w;
+        }
+    const uint4 t = slot[NP * 2];
+    x.s = __uint_as_float(t.y);
+    x.c = ((TYPE == T_Q4_0) ? -8.0f : 1.0f) * x.s * __uint_as_float(TYPE == T_Q2_K ? t.z : t.x);
+    x.c2 = x.s * __uint_as_float(t.w);
+}
+
+#ifndef LK_CHAIN_DETECT        // A/B builds only (tools/ab_build.sh)
+#define LK_CHAIN_DETECT true
+#endif
+#ifndef LK_GEMV_DETECT
+#define LK_GEMV_DETECT true
+#endif
+#ifdef LK_CHAIN_NO_SITES
+#define LK_CHAIN_FIXUP(...)
+#elif defined(LK_CHAIN_SITE_STUB)     // the flag test and a call of a trivial function
+__device__ __noinline__ void gemv_fixup_stub(float *red, int tid) { red[tid] += 1.0f; }
+#define LK_CHAIN_FIXUP(CGF, PRO_W, PRO_MODE, NTHR, AW, ROW_FIRST, NROWS, REDP) \
+    if (*(volatile uint32_t *)(smem + GEMV_SIDE_OFF + 4) != 0u) gemv_fixup_stub(REDP, tid);
+#elif defined(LK_CHAIN_SITE_TRAP)     // the flag test alone
+#define LK_CHAIN_FIXUP(CGF, PRO_W, PRO_MODE, NTHR, AW, ROW_FIRST, NROWS, REDP) \
+    if (*(volatile uint32_t *)(smem + GEMV_SIDE_OFF + 4) != 0u) __trap();
+#else
+#define LK_CHAIN_FIXUP(CGF, PRO_W, PRO_MODE, NTHR, AW, ROW_FIRST, NROWS, REDP)                                            \
+    if (gemv_has_fixup<TYPE>() && __builtin_expect(*(volatile uint32_t *)(smem + GEMV_SIDE_OFF + 4) != 0u, 0)) {                                \
+        gemv_fixup<TYPE, NP, 1, true, NTHR>(&p, AW, ROW_FIRST, NROWS, REDP, smem);                                        \
+        asm volatile("bar.sync 1, %0;" ::"r"(NTHR) : "memory");                                                          \
+        load_xregs<TYPE, NP>(x, xs, colc);      /* nothing of x has to survive the call */                                \
+    }
+#endif
 enum { GEMV_WAIT_FULL = 0, GEMV_WAIT_X = 1, GEMV_WAIT_END = 2 };
 
 
@@ -558,10 +598,13 @@ enum { GEMV_WAIT_FULL = 0, GEMV_WAIT_X = 1, GEMV_WAIT_END = 2 };
 // Cold path of the range fix-up (see GemvSide): for rows [row_first, row_first + n) of the packed matrix `a` and every
 // flagged block, sum_k w(i, k) * r_k into padding column j = (rank of the block among the flagged ones) & 7 of the
 // row's partial sums.  Scalars instead of the parameter struct: a reference to kernel parameters would force a local copy.
+#ifndef LK_FIXUP_ATTR           // A/B builds only (tools/ab_build.sh)
+#define LK_FIXUP_ATTR __noinline__
+#endif
 template <int TYPE, int NP, bool CG>
-__device__ __noinline__ void gemv_fixup(const uint8_t *a, const float *b, const float *pro_w, int pro_mode, int nib, int row_bytes,
-                                        int nblk, int red_stride, int pad_col, int row_first, int n, float *red, const uint32_t *xs,
-                                        const GemvSide *side, int tid, int nct) {
+__device__ __forceinline__ void gemv_fixup_body(const uint8_t *a, const float *b, const float *pro_w, int pro_mode, int nib, int row_bytes,
+                                                int nblk, int red_stride, int pad_col, int row_first, int n, float *red, const uint32_t *xs,
+                                                const GemvSide *side, int tid, int nct) {
     const int nw = (nblk + 31) >> 5;
     const float rinv = side->rinv;
 #pragma unroll 1
@@ -612,6 +655,18 @@ __device__ __noinline__ void gemv_fixup(const uint8_t *a, const float *b, const 
         }
         red[(size_t)r * red_stride + pad_col + j] = sum;
     }
+}
+// The call: six arguments, everything else read through the pointer to the launch's (or the phase's) parameters — the
+// kernel parameter is __grid_constant__, so its address is a plain generic pointer into the constant bank, no local copy.
+// A sixteen-argument call at the four sites made the kernels spill (ptxas: up to 200 bytes under the 56-register cap) and
+// cost the chained kernel 7 % although the call is never taken on natural data (profiles/r02_gemv_range_fix_ab.txt);
+// the callers also reload their activation registers after the call instead of keeping them alive across it.
+// NCT > 0: compile-time thread count (chained kernel); else cwarps * 32.  FUSED: the launch may carry the RMSNorm prologue.
+template <int TYPE, int NP, int CG, bool FUSED, int NCT>
+__device__ LK_FIXUP_ATTR void gemv_fixup(const GemvParams *pp, const uint8_t *a, int row_first, int n, float *red, const uint8_t *smem) {
+    gemv_fixup_body<TYPE, NP, CG != 0>(a, pp->b, FUSED ? pp->pro_w : nullptr, FUSED ? pp->pro_mode : 0, pp->nib, pp->row_bytes, pp->nblk,
+                                       pp->red_stride, pp->ncw * 8, row_first, n, red, (const uint32_t *)(smem + pp->x_off),
+                                       (const GemvSide *)(smem + GEMV_SIDE_OFF), (int)threadIdx.x, NCT > 0 ? NCT : pp->cwarps * 32);
 }
 
 // cross-lane part of the final reduction: 8 lanes per row, 4 rows per warp per pass
@@ -742,7 +797,7 @@ __device__ __forceinline__ void finish_pair(const GemvParams &p, const float *re
 // peer stores and the exchange signal / wait only (lk_compute_matmul_sharded: the 28-warp instantiation of mode 1 spills
 // under its 64-register cap, this one does not).
 template <int TYPE, int MAXW, int MINB, int NP, int MODE>
-__global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvParams p) {
+__global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const __grid_constant__ GemvParams p) {
     constexpr bool FUSED = MODE == 1, PEER = MODE == 1 || MODE == 2;
     constexpr bool INDEP = MODE == 3;     // MODE 3: the plain launch in WAIT_END mode (independent of everything in flight), known at compile time
     extern __shared__ __align__(128) uint8_t smem[];
@@ -861,34 +916,25 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
         asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
     }
     if (tid == 0) LK_TL(3);
-    prep_x<TYPE, NP, FUSED, PEER ? 2 : 0>(p, xs, tid, nct, side, INDEP ? pre : nullptr, use_pre);   // fused launches: plain L1-allocating loads (see ld_vec4)
+    prep_x<TYPE, NP, FUSED, PEER ? 2 : 0, LK_GEMV_DETECT>(p, xs, tid, nct, side, INDEP ? pre : nullptr, use_pre);   // fused launches: plain L1-allocating loads (see ld_vec4)
     if (tid == 0) LK_TL(24);
     asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");   // activation planes written
     if (tid == 0) LK_TL(4);
     // range fix-up (cold): some block holds elements its block scale cannot represent; see GemvSide.  The flag is re-read
     // from shared memory at each site so that nothing extra stays live across the stage loop.
-#define LK_GEMV_FIXUP(CGF, PRO_W, PRO_MODE, NTHR, AW, ROW_FIRST, NROWS, REDP)                                                        \
-    if (gemv_has_fixup<TYPE>() && *(volatile uint32_t *)(smem + GEMV_SIDE_OFF + 4) != 0u) {                                            \
-        gemv_fixup<TYPE, NP, CGF>(AW, p.b, PRO_W, PRO_MODE, p.nib, p.row_bytes, p.nblk, p.red_stride, p.ncw * 8, ROW_FIRST, NROWS,   \
-                                  REDP, (const uint32_t *)(smem + p.x_off), (const GemvSide *)(smem + GEMV_SIDE_OFF), tid, NTHR);     \
-        asm volatile("bar.sync 1, %0;" ::"r"(NTHR) : "memory");                                                                      \
+#ifdef LK_GEMV_NO_SITES
+#define LK_GEMV_FIXUP(...)
+#else
+#define LK_GEMV_FIXUP(AW, ROW_FIRST, NROWS, REDP)                                                                          \
+    if (gemv_has_fixup<TYPE>() && __builtin_expect(*(volatile uint32_t *)(smem + GEMV_SIDE_OFF + 4) != 0u, 0)) {                                \
+        gemv_fixup<TYPE, NP, PEER ? 2 : 0, FUSED, 0>(&p, AW, ROW_FIRST, NROWS, REDP, smem);                              \
+        asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");                                                           \
+        load_xregs<TYPE, NP>(x, xs, colc);      /* nothing of x has to survive the call */                                \
     }
+#endif
 
     XRegs<NP> x;
-    {
-        const uint4 *slot = (const uint4 *)(xs + (size_t)colc * gemv_xslot_words(NP));
-#pragma unroll
-        for (int pl = 0; pl < NP; pl++)
-#pragma unroll
-            for (int h = 0; h < 2; h++) {
-                const uint4 v = slot[pl * 2 + h];
-                x.q[pl][4 * h] = v.x; x.q[pl][4 * h + 1] = v.y; x.q[pl][4 * h + 2] = v.z; x.q[pl][4 * h + 3] = v.w;
-            }
-        const uint4 t = slot[NP * 2];
-        x.s = __uint_as_float(t.y);
-        x.c = ((TYPE == T_Q4_0) ? -8.0f : 1.0f) * x.s * __uint_as_float(TYPE == T_Q2_K ? t.z : t.x);
-        x.c2 = x.s * __uint_as_float(t.w);
-    }
+    load_xregs<TYPE, NP>(x, xs, colc);
     if (tid == 0) LK_TL(5);
 
     // Stage loop: one barrier wait / release per stage; inside, this warp's rows (rgi, rgi+rg, ...)
@@ -909,7 +955,7 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
         if (epi_mode != 1 && row0 + p.stage_rows - red_base > p.red_rows) {
             // partial-sum buffer full (a CTA that owns more rows than it holds)
             asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
-            LK_GEMV_FIXUP(PEER, FUSED ? p.pro_w : nullptr, FUSED ? p.pro_mode : 0, nct, (!FUSED || seg == 0) ? p.a : p.a_seg[seg - 1], r_begin + red_base, row0 - red_base, red)
+            LK_GEMV_FIXUP((!FUSED || seg == 0) ? p.a : p.a_seg[seg - 1], r_begin + red_base, row0 - red_base, red)
             finish_rows<FUSED, false, PEER>(p, seg_dst, red, row0 - red_base, p.row_offset + r_begin + red_base, warp, lane);
             if (PEER && p.npeers) {
                 asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
@@ -982,7 +1028,7 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
     if (tid == 0) LK_TL(6);
     asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
     if (tid == 0) LK_TL(20);
-    LK_GEMV_FIXUP(PEER, FUSED ? p.pro_w : nullptr, FUSED ? p.pro_mode : 0, nct, (!FUSED || seg == 0) ? p.a : p.a_seg[seg - 1], r_begin + red_base, nrows - red_base, red)
+    LK_GEMV_FIXUP((!FUSED || seg == 0) ? p.a : p.a_seg[seg - 1], r_begin + red_base, nrows - red_base, red)
     finish_rows<FUSED, false, PEER>(p, seg_dst, red, nrows - red_base, p.row_offset + r_begin + red_base, warp, lane);
     if (PEER && p.npeers) {
         asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
@@ -996,8 +1042,8 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const GemvP
     }
     if (epi_mode == 1) {
         asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
-        LK_GEMV_FIXUP(PEER, p.pro_w, p.pro_mode, nct, p.a, r_begin, nrows, red)
-        LK_GEMV_FIXUP(PEER, p.pro_w, p.pro_mode, nct, p.a_seg[0], r_begin, nrows, red + (size_t)p.pair_off * p.red_stride)
+        LK_GEMV_FIXUP(p.a, r_begin, nrows, red)
+        LK_GEMV_FIXUP(p.a_seg[0], r_begin, nrows, red + (size_t)p.pair_off * p.red_stride)
         finish_pair(p, red, nrows, p.pair_off, p.row_offset + r_begin, warp, lane);
         if (p.npeers) {
             asm volatile("bar.sync 1, %0;" ::"r"(nct) : "memory");
@@ -1167,24 +1213,11 @@ __global__ void __launch_bounds__((CHAIN_W + 1) * 32, 1) gemv_chain_kernel(const
 #pragma unroll 1
         for (int r = warp; r < p.red_rows; r += CHAIN_W)
             if (lane < GEMV_RED_PAD) red[r * p.red_stride + p.ncw * 8 + lane] = 0.f;
-        prep_x<TYPE, NP, true, 1>(p, xs, tid, NCT, side);
+        prep_x<TYPE, NP, true, 1, LK_CHAIN_DETECT>(p, xs, tid, NCT, side);
         asm volatile("bar.sync 1, %0;" ::"r"(NCT) : "memory");   // activation planes (and the padding zeros) written
 
         XRegs<NP> x;
-        {
-            const uint4 *slot = (const uint4 *)(xs + (size_t)colc * gemv_xslot_words(NP));
-#pragma unroll
-            for (int pl = 0; pl < NP; pl++)
-#pragma unroll
-                for (int h = 0; h < 2; h++) {
-                    const uint4 v = slot[pl * 2 + h];
-                    x.q[pl][4 * h] = v.x; x.q[pl][4 * h + 1] = v.y; x.q[pl][4 * h + 2] = v.z; x.q[pl][4 * h + 3] = v.w;
-                }
-            const uint4 t = slot[NP * 2];
-            x.s = __uint_as_float(t.y);
-            x.c = ((TYPE == T_Q4_0) ? -8.0f : 1.0f) * x.s * __uint_as_float(t.x);
-            x.c2 = x.s * __uint_as_float(t.w);
-        }
+        load_xregs<TYPE, NP>(x, xs, colc);
 
         const int rg_words = p.rg * row_words;
         const int rstep = p.rg * p.red_stride;
@@ -1200,7 +1233,7 @@ __global__ void __launch_bounds__((CHAIN_W + 1) * 32, 1) gemv_chain_kernel(const
                 if (epi_mode != 1 && row0 + p.stage_rows - red_base > p.red_rows) {
                     // partial-sum buffer full (a CTA that owns more rows than it holds)
                     asm volatile("bar.sync 1, %0;" ::"r"(NCT) : "memory");
-                    LK_GEMV_FIXUP(true, p.pro_w, p.pro_mode, NCT, seg == 0 ? p.a : p.a_seg[seg - 1], r_begin + red_base, row0 - red_base, red)
+                    LK_CHAIN_FIXUP(true, p.pro_w, p.pro_mode, NCT, seg == 0 ? p.a : p.a_seg[seg - 1], r_begin + red_base, row0 - red_base, red)
                     finish_rows<true, true>(p, seg_dst, red, row0 - red_base, p.row_offset + r_begin + red_base, warp, lane);
                     asm volatile("bar.sync 1, %0;" ::"r"(NCT) : "memory");
                     rp -= (size_t)(row0 - red_base) * p.red_stride;
@@ -1247,7 +1280,7 @@ __global__ void __launch_bounds__((CHAIN_W + 1) * 32, 1) gemv_chain_kernel(const
             }
             if (epi_mode == 1) continue;                // the pair is finished together below
             asm volatile("bar.sync 1, %0;" ::"r"(NCT) : "memory");
-            LK_GEMV_FIXUP(true, p.pro_w, p.pro_mode, NCT, seg == 0 ? p.a : p.a_seg[seg - 1], r_begin + red_base, nrows - red_base, red)
+            LK_CHAIN_FIXUP(true, p.pro_w, p.pro_mode, NCT, seg == 0 ? p.a : p.a_seg[seg - 1], r_begin + red_base, nrows - red_base, red)
             finish_rows<true, true>(p, seg_dst, red, nrows - red_base, p.row_offset + r_begin + red_base, warp, lane);
             if (seg + 1 < nseg) {                        // the buffer is reused by the next segment
                 asm volatile("bar.sync 1, %0;" ::"r"(NCT) : "memory");
@@ -1257,8 +1290,8 @@ __global__ void __launch_bounds__((CHAIN_W + 1) * 32, 1) gemv_chain_kernel(const
         }
         if (epi_mode == 1) {
             asm volatile("bar.sync 1, %0;" ::"r"(NCT) : "memory");
-            LK_GEMV_FIXUP(true, p.pro_w, p.pro_mode, NCT, p.a, r_begin, nrows, red)
-            LK_GEMV_FIXUP(true, p.pro_w, p.pro_mode, NCT, p.a_seg[0], r_begin, nrows, red + (size_t)p.pair_off * p.red_stride)
+            LK_CHAIN_FIXUP(true, p.pro_w, p.pro_mode, NCT, p.a, r_begin, nrows, red)
+            LK_CHAIN_FIXUP(true, p.pro_w, p.pro_mode, NCT, p.a_seg[0], r_begin, nrows, red + (size_t)p.pair_off * p.red_stride)
             finish_pair(p, red, nrows, p.pair_off, p.row_offset + r_begin, warp, lane);
         }
         // re-arm the range flags for the next phase (its prep_x runs after the grid barrier's bar.sync)

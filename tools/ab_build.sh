@@ -14,8 +14,18 @@ done
 git -C "$ROOT" show faf9642:include/llamakotlin_cuda.h > ../include_r1/llamakotlin_cuda.h
 sed -i 's#../../include/llamakotlin_cuda.h#../include_r1/llamakotlin_cuda.h#g; s#OUT       := ../libllamakotlin_cuda.so#OUT       := ../lib_r1.so#' Makefile lk_shim.h
 make -j4 > build.log 2>&1
-cd ../nofix
-cp "$ROOT"/llama.kotlin_b200/csrc/{Makefile,*.cu,*.cuh,*.h} .
-sed -i 's#OUT       := ../libllamakotlin_cuda.so#OUT       := ../lib_nofix.so#; s#NVCCFLAGS := #NVCCFLAGS := -DLK_GEMV_NO_RANGE_FIX #; s#../../include/llamakotlin_cuda.h#../../../include/llamakotlin_cuda.h#g' Makefile lk_shim.h
-make -j4 > build.log 2>&1
+cd "$ROOT"
+# variant <name> <extra nvcc flags>: the current sources with the flags -> tools/_ab/lib_<name>.so
+variant() {
+  mkdir -p "$ROOT/tools/_ab/$1"
+  cd "$ROOT/tools/_ab/$1"
+  cp "$ROOT"/llama.kotlin_b200/csrc/{Makefile,*.cu,*.cuh,*.h} .
+  sed -i "s#OUT       := ../libllamakotlin_cuda.so#OUT       := ../lib_$1.so#; s#NVCCFLAGS := #NVCCFLAGS := $2 #; s#../../include/llamakotlin_cuda.h#../../../include/llamakotlin_cuda.h#g" Makefile lk_shim.h
+  make -j4 > build.log 2>&1
+  cd "$ROOT"
+}
+variant nofix -DLK_GEMV_NO_RANGE_FIX
+for v in "$@"; do      # further variants as name=flags, e.g.  chain_nodetect=-DLK_CHAIN_DETECT=false
+  variant "${v%%=*}" "${v#*=}"
+done
 ls -la "$ROOT"/tools/_ab/*.so
