@@ -346,10 +346,40 @@ def config2_arm(args, rank, world, local_rank, lk, be, dist, torch, brief: bool 
         if st != lk.GGMLStatus.SUCCESS:
             raise RuntimeError("graphCompute FAILED")
 
-    def step_e2e():
+    def step_e2e_serial():     # round 1's form: both copies in full around the step
         ga.deviceBuffer.setTensor(acts_all, x_host, 0, x_host.nbytes)          # H2D, pinned
         step_device()
         ga.deviceBuffer.getTensor(dst_all, y_host.view(np.uint8), 0, y_host.nbytes)  # D2H (synchronises)
+
+    # The same bytes, copied per layer inside the step (graphCompute(hostIO=...) -> lk_graph_compute_io): layer l's
+    # activations go up right before its first GEMV, its results come down right after its last one, on copy streams
+    # beside the compute stream; the step ends when the last download has (synchronize()).
+    graph_io = GGMLCGraph(nodes=nodes, allocator=ga)
+    host_io = []
+    sched = [int(v) for v in args.io_schedule.split(",")] if args.io_schedule else []
+    if sum(sched) != layers or min(sched, default=0) < 1:      # other layer counts: 1, 1, 2, 4, ...
+        sched, left, c = [], layers, 1
+        while left > 0:
+            sched.append(min(c, left))
+            left -= sched[-1]
+            c = c * 2 if len(sched) > 1 else 1
+    # uploads: small chunk first (the step starts after 1 layer's activations), growing; downloads: the mirror image
+    # (the step ends one small chunk after its last launch)
+    l0 = 0
+    for nl in sched:
+        xv = GGMLTensor(GGMLType.F32, [nl * sumK], bufferId=0, dataOffset=acts_all.dataOffset + l0 * sumK * 4, buffer=ga.deviceBuffer)
+        host_io.append(("in", xv, x_host[l0 * sumK:(l0 + nl) * sumK]))
+        l0 += nl
+    l0 = 0
+    for nl in reversed(sched):
+        yv = GGMLTensor(GGMLType.F32, [nl * sumM], bufferId=0, dataOffset=dst_all.dataOffset + l0 * sumM * 4, buffer=ga.deviceBuffer)
+        host_io.append(("out", yv, y_host[l0 * sumM:(l0 + nl) * sumM]))
+        l0 += nl
+
+    def step_e2e():
+        if be.graphCompute(graph_io, hostIO=host_io) != lk.GGMLStatus.SUCCESS:
+            raise RuntimeError("graphCompute FAILED")
+        be.synchronize()
 
     bytes_step = layers * sum(algo_bytes(M, K, bb) for M, K in SHAPES) * world
     sampler = ClockSampler(local_rank) if rank == 0 else None
@@ -389,7 +419,7 @@ def config2_arm(args, rank, world, local_rank, lk, be, dist, torch, brief: bool 
         step_spread = {"n": len(singles), "p10_ms": float(q[0]), "median_ms": float(q[1]), "p90_ms": float(q[2]),
                        "how": "one graph replay between two CUDA events with a synchronize after each (no overlap between steps)"}
 
-    ms_dep = e2e_s = float("nan")
+    ms_dep = e2e_s = e2e_serial_s = float("nan")
     if not brief:
         # ---- same step with every GEMV forced to wait for its predecessor (a fully dependent chain) ----
         lkc.set_option("gemv_overlap", 0)
@@ -420,6 +450,19 @@ def config2_arm(args, rank, world, local_rank, lk, be, dist, torch, brief: bool 
         e2e_s = time.perf_counter() - t0
         if sampler:
             sampler.window(e0, time.time())
+        y_pipelined = y_host.copy()
+        y_host[:] = 0
+        for _ in range(3):
+            step_e2e_serial()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            step_e2e_serial()
+        barrier()
+        e2e_serial_s = time.perf_counter() - t0
+        # the two forms must deliver the same bytes (then the check below covers both)
+        if not np.array_equal(y_pipelined, y_host):
+            raise RuntimeError("pipelined and serial host copies disagree")
     else:
         ga.deviceBuffer.getTensor(dst_all, y_host.view(np.uint8), 0, y_host.nbytes)     # for the check below
 
@@ -458,7 +501,11 @@ def config2_arm(args, rank, world, local_rank, lk, be, dist, torch, brief: bool 
         "e2e": {"value": bytes_step * args.steps / e2e_s / 1e9, "unit": "GB/s",
                 "h2d_bytes_per_step": int(x_host.nbytes), "d2h_bytes_per_step": int(y_host.nbytes),
                 "ms_per_step": e2e_s / args.steps * 1e3,
-                "api": "GGMLCudaBuffer.setTensor + GGMLCudaBackend.graphCompute + GGMLCudaBuffer.getTensor"},
+                "api": "GGMLCudaBackend.graphCompute(graph, hostIO = per-layer pinned host slices) + synchronize(): "
+                       "lk_graph_compute_io issues each layer's upload before its first GEMV and its download after its last",
+                "serial_copies": {"value": bytes_step * args.steps / e2e_serial_s / 1e9, "ms_per_step": e2e_serial_s / args.steps * 1e3,
+                                  "api": "GGMLCudaBuffer.setTensor + GGMLCudaBackend.graphCompute + GGMLCudaBuffer.getTensor "
+                                         "(both copies in full around the step: round 1's form)"}},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": value / world, "peak": peak, "unit": "GB/s",
                      "frac": value / world / peak, "traffic": None, "peak_source": peak_src,
@@ -690,6 +737,8 @@ def main():
     ap.add_argument("--opt", action="append", help="lk_set_option name=value (tuning experiments)")
     ap.add_argument("--gather", default="sync", choices=["sync", "barrier", "nccl"],
                     help="N > 1: how the two exchanges of the sharded FFN are made (see the module docstring)")
+    ap.add_argument("--io-schedule", default="1,3,12,16",
+                    help="e2e: layers per upload chunk, in order (downloads use the reverse); must add up to --layers")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the config-3 / config-4 lines under config.other_paths")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)

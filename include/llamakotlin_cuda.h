@@ -41,7 +41,7 @@ extern "C" {
 #define LK_API
 #endif
 
-#define LK_ABI_VERSION 2
+#define LK_ABI_VERSION 3
 #define LK_MAX_DIMS 4           /* GGML_MAX_DIMS, core/GGMLTypes.kt:67 */
 
 /* GGMLType ordinals, core/GGMLTypes.kt:145-153 */
@@ -146,6 +146,18 @@ LK_API void       *lk_buf_device_ptr(lk_buf *buf);                              
 LK_API lk_status   lk_buf_upload(lk_buf *buf, uint64_t offset, const void *host, uint64_t n);   /* setTensor */
 LK_API lk_status   lk_buf_download(lk_buf *buf, uint64_t offset, void *host, uint64_t n);       /* getTensor */
 LK_API lk_status   lk_buf_copy(lk_buf *dst, uint64_t dst_off, lk_buf *src, uint64_t src_off, uint64_t n); /* copyTensor */
+/* setTensor / getTensor without the wait (core/GGMLBackend.kt:95-110 are synchronous; these are what lets the copies of
+ * a step overlap its launches).  The copies run on two streams of their own beside the compute stream:
+ *   upload_async   starts at once — it does NOT wait for launches already enqueued, so the caller must not overwrite
+ *                  memory they still read (double-buffer, or lk_sync between steps); every lk_compute_* call enqueued
+ *                  AFTER it waits for it.
+ *   download_async starts when everything enqueued on the compute stream so far has finished; `host` is valid after the
+ *                  next lk_sync (which waits for all three streams).
+ * `host` should be pinned (lk_host_alloc), else the driver serialises the copy.  Inside lk_capture_begin / _end the
+ * copies become nodes of the captured graph (the host addresses are part of it): uploads hang off the graph's root,
+ * downloads off the launch that precedes them, and a replay (lk_graph_launch) finishes only when they have.            */
+LK_API lk_status   lk_buf_upload_async(lk_buf *buf, uint64_t offset, const void *host, uint64_t n);
+LK_API lk_status   lk_buf_download_async(lk_buf *buf, uint64_t offset, void *host, uint64_t n);
 LK_API lk_status   lk_buf_clear(lk_buf *buf, uint8_t value);                    /* clear */
 /* Pinned host staging memory (page-locked) for callers without their own. */
 LK_API lk_status   lk_host_alloc(lk_ctx *ctx, uint64_t size, void **out);
@@ -351,6 +363,21 @@ LK_API lk_status   lk_graph_plan(const lk_graph_node *nodes, int32_t n, int32_t 
 #define LK_GRAPH_CHAIN_ALWAYS 2
 #define LK_GRAPH_CHAIN_NEVER  4
 LK_API lk_status   lk_graph_compute(lk_ctx *ctx, const lk_graph_node *nodes, int32_t n, int32_t flags);
+/* The same with the step's host copies scheduled inside it: every upload is issued (lk_buf_upload_async) right before
+ * the first launch that reads its region, every download (lk_buf_download_async) right after the last launch that
+ * writes it, so a caller whose activations arrive from and whose results go back to host memory (the reference's
+ * setTensor -> graphCompute -> getTensor sequence) pays one chunk of each at the ends of the step instead of both
+ * copies in full.  Split the transfers by consumer (e.g. one per layer) for the overlap to exist.                     */
+enum { LK_IO_UPLOAD = 0, LK_IO_DOWNLOAD = 1 };
+typedef struct lk_host_io {
+    int32_t   direction;         /* LK_IO_UPLOAD | LK_IO_DOWNLOAD */
+    int32_t   reserved;
+    lk_buf   *buf;
+    uint64_t  offset, bytes;     /* the region of buf */
+    void     *host;
+} lk_host_io;
+LK_API lk_status   lk_graph_compute_io(lk_ctx *ctx, const lk_graph_node *nodes, int32_t n, int32_t flags,
+                                       const lk_host_io *io, int32_t n_io);
 
 /* ---- options ----------------------------------------------------------------
  * "nibble_order" (product option): how the 32 four-bit quants of a Q4_0 / Q4_1 block lie in its 16

@@ -97,7 +97,43 @@ class GGMLCudaBackend(device: Int = 0) : GGMLBackend {
         GGMLStatus.FAILED
     }
 
-    fun forget(graph: GGMLCGraph) { captured.remove(graph)?.let { lk_graph_destroy(it) } }
+    fun forget(graph: GGMLCGraph) { captured.remove(graph)?.let { lk_graph_destroy(it) }; capturedIo.remove(graph)?.let { lk_graph_destroy(it) } }
+
+    /** One host copy of a step: `pinned` (from lk_host_alloc) <-> the bytes of `tensor` in its device buffer. */
+    class HostCopy(val upload: Boolean, val tensor: GGMLTensor, val pinned: COpaquePointer, val bytes: ULong)
+
+    private val capturedIo = HashMap<GGMLCGraph, CPointer<lk_graph>>()
+
+    /** setTensor -> graphCompute -> getTensor as ONE submission (lk_graph_compute_io): every upload is issued right
+     *  before the first launch that reads its region, every download right after the last launch that writes it, on copy
+     *  streams beside the compute stream.  Split the copies by consumer (e.g. per group of layers); the downloads are
+     *  complete after synchronize().  The copies are nodes of the captured graph: the same pinned addresses every step. */
+    fun graphCompute(graph: GGMLCGraph, copies: List<HostCopy>): GGMLStatus = try {
+        val g = capturedIo.getOrPut(graph) {
+            memScoped {
+                val nodes = nodeArray(graph.allocator!!, graph)
+                val io = allocArray<lk_host_io>(copies.size)
+                copies.forEachIndexed { k, c ->
+                    io[k].direction = if (c.upload) LK_IO_UPLOAD.toInt() else LK_IO_DOWNLOAD.toInt()
+                    io[k].buf = (c.tensor.buffer as GGMLCudaBuffer).handle
+                    io[k].offset = c.tensor.dataOffset
+                    io[k].bytes = c.bytes
+                    io[k].host = c.pinned
+                }
+                rethrow(lk.handle, lk_capture_begin(lk.handle))
+                val st = lk_graph_compute_io(lk.handle, nodes, graph.nNodes, 0, io, copies.size)
+                val out = alloc<CPointerVar<lk_graph>>()
+                val st2 = lk_capture_end(lk.handle, out.ptr)
+                rethrow(lk.handle, st); rethrow(lk.handle, st2)
+                out.value!!
+            }
+        }
+        rethrow(lk.handle, lk_graph_launch(lk.handle, g))
+        GGMLStatus.SUCCESS
+    } catch (e: Exception) {
+        println("CUDA backend graph computation failed: ${e.message}")
+        GGMLStatus.FAILED
+    }
 }
 
 /** Registration next to the CPU and Metal entries (core/GGMLBackend.kt:162-181):

@@ -64,6 +64,12 @@ class lk_plan_launch(C.Structure):
                 ("attn", C.c_int32 * 5)]
 
 
+class lk_host_io(C.Structure):
+    _fields_ = [("direction", C.c_int32), ("reserved", C.c_int32), ("buf", C.c_void_p), ("offset", C.c_uint64),
+                ("bytes", C.c_uint64), ("host", C.c_void_p)]
+
+
+LK_IO_UPLOAD, LK_IO_DOWNLOAD = 0, 1
 LK_OP = {"NONE": 0, "ADD": 1, "MUL": 2, "MUL_MAT": 3, "RMS_NORM": 4, "SILU": 5, "SOFT_MAX": 6, "SCALE": 7, "ROPE": 8, "CPY": 9,
          "FLASH_ATTN": 10}
 LK_PLAN_NODE, LK_PLAN_FUSED, LK_PLAN_ATTN_STEP = 0, 1, 2
@@ -146,6 +152,9 @@ def lib() -> C.CDLL:
         "lk_graph_destroy": (i32, [vp]),
         "lk_graph_plan": (i32, [C.POINTER(lk_graph_node), i32, i32, C.POINTER(lk_plan_launch), i32, C.POINTER(i32)]),
         "lk_graph_compute": (i32, [vp, C.POINTER(lk_graph_node), i32, i32]),
+        "lk_graph_compute_io": (i32, [vp, C.POINTER(lk_graph_node), i32, i32, C.POINTER(lk_host_io), i32]),
+        "lk_buf_upload_async": (i32, [vp, u64, vp, u64]),
+        "lk_buf_download_async": (i32, [vp, u64, vp, u64]),
         "lk_set_option": (i32, [vp, C.c_char_p, i64]),
         "lk_get_option": (i64, [vp, C.c_char_p]),
         "lk_comm_unique_id": (i32, [vp]),

@@ -374,10 +374,77 @@ static lk_status run_planned(lk_ctx *ctx, const lk_graph_node *nodes, const lk_p
     return LK_OK;
 }
 
-lk_status lk_graph_compute(lk_ctx *ctx, const lk_graph_node *nodes, int32_t n, int32_t flags) {
-    if (!ctx || (!nodes && n > 0) || n < 0) return lk::fail(ctx, LK_EINVAL_ARG, "lk_graph_compute: bad argument");
+// Host I/O of a graph: which launch each copy goes before (uploads: the first launch that reads the region) or after
+// (downloads: the last launch that writes it).  Launches are numbered in issue order; a chained run counts as one.
+namespace {
+struct IoSchedule {
+    std::vector<std::vector<int>> before, after;     // per launch slot: indices into io[]
+    std::vector<int> at_end;                         // downloads of regions no node writes
+};
+bool node_reads(const lk_graph_node &nd, const Span &r) {
+    for (int s = 0; s < nd.n_src && s < 4; s++) if (overlaps(span_of(nd.src[s]), r)) return true;
+    return false;
+}
+bool node_writes(const lk_graph_node &nd, const Span &r) {
+    if (nd.op == LK_OP_CPY) return nd.n_src > 1 && overlaps(span_of(nd.src[1]), r);   // the cache rows
+    return nd.op != LK_OP_NONE && overlaps(span_of(nd.dst), r);
+}
+IoSchedule schedule_io(const lk_graph_node *nodes, const std::vector<std::vector<int>> &covered, const lk_host_io *io, int n_io) {
+    IoSchedule S;
+    const int nl = (int)covered.size();
+    S.before.resize(nl + 1);
+    S.after.resize(nl + 1);
+    for (int k = 0; k < n_io; k++) {
+        const Span r{(const void *)io[k].buf, io[k].offset, io[k].offset + io[k].bytes};
+        int at = -1;
+        for (int l = 0; l < nl; l++) {
+            bool hit = false;
+            for (int j : covered[l]) hit = hit || (io[k].direction == LK_IO_UPLOAD ? node_reads(nodes[j], r) : node_writes(nodes[j], r));
+            if (!hit) continue;
+            at = l;
+            if (io[k].direction == LK_IO_UPLOAD) break;     // first reader; downloads keep the last writer
+        }
+        if (io[k].direction == LK_IO_UPLOAD) S.before[at < 0 ? 0 : at].push_back(k);
+        else if (at < 0) S.at_end.push_back(k);
+        else S.after[at].push_back(k);
+    }
+    return S;
+}
+lk_status issue_io(const lk_host_io &c) {
+    return c.direction == LK_IO_UPLOAD ? lk_buf_upload_async(c.buf, c.offset, c.host, c.bytes)
+                                       : lk_buf_download_async(c.buf, c.offset, c.host, c.bytes);
+}
+std::vector<int> launch_nodes(const lk_plan_launch &L) {
+    std::vector<int> v;
+    if (L.kind == LK_PLAN_ATTN_STEP) { for (int q = 0; q < 5; q++) v.push_back(L.attn[q]); return v; }
+    v.push_back(L.node);
+    if (L.kind == LK_PLAN_FUSED) {
+        if (L.rms >= 0) v.push_back(L.rms);
+        if (L.add >= 0) v.push_back(L.add);
+        for (int q = 0; q < L.n_extra; q++) v.push_back(L.extra[q]);
+        if (L.mul >= 0) { v.push_back(L.silu); v.push_back(L.mul); }
+    }
+    return v;
+}
+}  // namespace
+
+lk_status lk_graph_compute_io(lk_ctx *ctx, const lk_graph_node *nodes, int32_t n, int32_t flags, const lk_host_io *io, int32_t n_io) {
+    if (!ctx || (!nodes && n > 0) || n < 0 || n_io < 0 || (!io && n_io > 0)) return lk::fail(ctx, LK_EINVAL_ARG, "lk_graph_compute: bad argument");
+    for (int k = 0; k < n_io; k++)
+        if (!io[k].buf || !io[k].host || (io[k].direction != LK_IO_UPLOAD && io[k].direction != LK_IO_DOWNLOAD))
+            return lk::fail(ctx, LK_EINVAL_ARG, "lk_graph_compute_io: a copy needs a device buffer, a host address and a direction");
+    lk_status st;
     if (flags & LK_GRAPH_NO_FUSION) {
-        for (int i = 0; i < n; i++) { const lk_status st = run_node(ctx, nodes[i]); if (st != LK_OK) return st; }
+        std::vector<std::vector<int>> covered(n);
+        for (int i = 0; i < n; i++) covered[i].push_back(i);
+        const IoSchedule S = schedule_io(nodes, covered, io, n_io);
+        for (int i = 0; i < n; i++) {
+            for (int k : S.before[i]) if ((st = issue_io(io[k])) != LK_OK) return st;
+            if ((st = run_node(ctx, nodes[i])) != LK_OK) return st;
+            for (int k : S.after[i]) if ((st = issue_io(io[k])) != LK_OK) return st;
+        }
+        for (int k : S.before[n]) if ((st = issue_io(io[k])) != LK_OK) return st;
+        for (int k : S.at_end) if ((st = issue_io(io[k])) != LK_OK) return st;
         return LK_OK;
     }
     Planner P;
@@ -385,40 +452,57 @@ lk_status lk_graph_compute(lk_ctx *ctx, const lk_graph_node *nodes, int32_t n, i
     P.plan();
     const int chain_mode = (flags & LK_GRAPH_CHAIN_ALWAYS) ? 1 : (flags & LK_GRAPH_CHAIN_NEVER) ? 0 : -1;
     const std::vector<lk_plan_launch> L = P.launches(chain_mode, 8);
-    std::set<int> stored;
+    // launch slots: one per unchained launch, one per chained run
+    std::vector<std::pair<size_t, size_t>> slots;
     for (size_t i = 0; i < L.size();) {
-        if (L[i].chain < 0) {
-            const lk_status st = run_planned(ctx, nodes, L[i], stored);
-            if (st != LK_OK) return st;
-            i++;
-            continue;
-        }
-        size_t e = i;
-        while (e < L.size() && L[e].chain == L[i].chain) e++;
-        // consecutive dependent launches as one lk_compute_matmul_chain; one by one when the library declines
-        const std::set<int> saved = stored;
-        std::vector<lk_matmul_fusion> fus(e - i);
-        std::vector<lk_matmul_link> links(e - i);
-        for (size_t q = i; q < e; q++) {
-            const bool store_b = L[q].rms >= 0 && !stored.count(L[q].rms);
-            const bool has = L[q].kind == LK_PLAN_FUSED;
-            if (has) fill_fusion(nodes, L[q], &fus[q - i], store_b);
-            if (L[q].rms >= 0) stored.insert(L[q].rms);
-            links[q - i].a = &nodes[L[q].node].src[0];
-            links[q - i].b = &nodes[L[q].node].src[1];
-            links[q - i].dst = &nodes[L[q].node].dst;
-            links[q - i].fusion = has ? &fus[q - i] : nullptr;
-        }
-        lk_status st = lk_compute_matmul_chain(ctx, links.data(), (int32_t)links.size());
-        if (st == LK_ENOTIMPL) {
-            stored = saved;
-            for (size_t q = i; q < e; q++) if ((st = run_planned(ctx, nodes, L[q], stored)) != LK_OK) return st;
-        } else if (st != LK_OK) {
-            return st;
-        }
+        size_t e = i + 1;
+        if (L[i].chain >= 0) while (e < L.size() && L[e].chain == L[i].chain) e++;
+        slots.push_back({i, e});
         i = e;
     }
+    std::vector<std::vector<int>> covered(slots.size());
+    for (size_t q = 0; q < slots.size(); q++)
+        for (size_t i = slots[q].first; i < slots[q].second; i++)
+            for (int j : launch_nodes(L[i])) covered[q].push_back(j);
+    const IoSchedule S = schedule_io(nodes, covered, io, n_io);
+    std::set<int> stored;
+    for (size_t q = 0; q < slots.size(); q++) {
+        const size_t i = slots[q].first, e = slots[q].second;
+        for (int k : S.before[q]) if ((st = issue_io(io[k])) != LK_OK) return st;
+        if (L[i].chain < 0) {
+            if ((st = run_planned(ctx, nodes, L[i], stored)) != LK_OK) return st;
+        } else {
+            // consecutive dependent launches as one lk_compute_matmul_chain; one by one when the library declines
+            const std::set<int> saved = stored;
+            std::vector<lk_matmul_fusion> fus(e - i);
+            std::vector<lk_matmul_link> links(e - i);
+            for (size_t z = i; z < e; z++) {
+                const bool store_b = L[z].rms >= 0 && !stored.count(L[z].rms);
+                const bool has = L[z].kind == LK_PLAN_FUSED;
+                if (has) fill_fusion(nodes, L[z], &fus[z - i], store_b);
+                if (L[z].rms >= 0) stored.insert(L[z].rms);
+                links[z - i].a = &nodes[L[z].node].src[0];
+                links[z - i].b = &nodes[L[z].node].src[1];
+                links[z - i].dst = &nodes[L[z].node].dst;
+                links[z - i].fusion = has ? &fus[z - i] : nullptr;
+            }
+            st = lk_compute_matmul_chain(ctx, links.data(), (int32_t)links.size());
+            if (st == LK_ENOTIMPL) {
+                stored = saved;
+                for (size_t z = i; z < e; z++) if ((st = run_planned(ctx, nodes, L[z], stored)) != LK_OK) return st;
+            } else if (st != LK_OK) {
+                return st;
+            }
+        }
+        for (int k : S.after[q]) if ((st = issue_io(io[k])) != LK_OK) return st;
+    }
+    for (int k : S.before[slots.size()]) if ((st = issue_io(io[k])) != LK_OK) return st;
+    for (int k : S.at_end) if ((st = issue_io(io[k])) != LK_OK) return st;
     return LK_OK;
+}
+
+lk_status lk_graph_compute(lk_ctx *ctx, const lk_graph_node *nodes, int32_t n, int32_t flags) {
+    return lk_graph_compute_io(ctx, nodes, n, flags, nullptr, 0);
 }
 
 }  // extern "C"

@@ -163,6 +163,12 @@ lk_status lk_ctx_create(int32_t device, lk_ctx **out) {
     LK_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     LK_CUDA(nullptr, cudaEventCreate(&ctx->ev0));
     LK_CUDA(nullptr, cudaEventCreate(&ctx->ev1));
+    // copy streams of lk_buf_upload_async / lk_buf_download_async: made here so that a capture can record its fork event
+    LK_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->copy_in, cudaStreamNonBlocking));
+    LK_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->copy_out, cudaStreamNonBlocking));
+    LK_CUDA(nullptr, cudaEventCreateWithFlags(&ctx->ev_in, cudaEventDisableTiming));
+    LK_CUDA(nullptr, cudaEventCreateWithFlags(&ctx->ev_out, cudaEventDisableTiming));
+    LK_CUDA(nullptr, cudaEventCreateWithFlags(&ctx->ev_root, cudaEventDisableTiming));
     // grid-barrier words of the chained GEMV (arrivals, generation, time-outs); allocated here because nothing may be
     // allocated-and-cleared while a launch sequence is being captured
     LK_CUDA(nullptr, cudaMalloc((void **)&ctx->chain_bar, 16));
@@ -177,6 +183,11 @@ lk_status lk_ctx_destroy(lk_ctx *ctx) {
     if (!ctx) return LK_OK;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    if (ctx->copy_in) { cudaStreamSynchronize(ctx->copy_in); cudaStreamDestroy(ctx->copy_in); }
+    if (ctx->copy_out) { cudaStreamSynchronize(ctx->copy_out); cudaStreamDestroy(ctx->copy_out); }
+    if (ctx->ev_in) cudaEventDestroy(ctx->ev_in);
+    if (ctx->ev_out) cudaEventDestroy(ctx->ev_out);
+    if (ctx->ev_root) cudaEventDestroy(ctx->ev_root);
     lk_comm_destroy(ctx);
     if (ctx->arena) cudaFree(ctx->arena);
     if (ctx->chain_bar) cudaFree(ctx->chain_bar);
@@ -194,6 +205,11 @@ lk_status lk_ctx_destroy(lk_ctx *ctx) {
 lk_status lk_sync(lk_ctx *ctx) {
     if (!ctx) return fail(nullptr, LK_EINVAL_ARG, "lk_sync: ctx is NULL");
     LK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ctx->copies_pending && !ctx->capturing) {     // the asynchronous copies run beside the compute stream
+        if (ctx->copy_in) LK_CUDA(ctx, cudaStreamSynchronize(ctx->copy_in));
+        if (ctx->copy_out) LK_CUDA(ctx, cudaStreamSynchronize(ctx->copy_out));
+        ctx->copies_pending = false;
+    }
     return lk::check_async_faults(ctx);
 }
 
@@ -272,6 +288,38 @@ lk_status lk_buf_download(lk_buf *buf, uint64_t off, void *host, uint64_t n) {
     chain_other(ctx, nullptr, 0);
     LK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return lk::check_async_faults(ctx);
+}
+
+// ---- asynchronous host copies (pipelined host I/O of a step, include/llamakotlin_cuda.h) ----
+lk_status lk_buf_upload_async(lk_buf *buf, uint64_t off, const void *host, uint64_t n) {
+    lk_status st = buf_range(buf, off, n, "lk_buf_upload_async");
+    if (st != LK_OK) return st;
+    if (n == 0) return LK_OK;
+    if (!host) return fail(buf->ctx, LK_EINVAL_ARG, "lk_buf_upload_async: host is NULL");
+    lk_ctx *ctx = buf->ctx;
+    if (ctx->capturing && !ctx->cap_in) {     // fork from the root of the capture: the copy depends on nothing recorded so far
+        LK_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_in, ctx->ev_root, 0));
+        ctx->cap_in = true;
+    }
+    LK_CUDA(ctx, cudaMemcpyAsync((uint8_t *)buf->ptr + off, host, n, cudaMemcpyHostToDevice, ctx->copy_in));
+    LK_CUDA(ctx, cudaEventRecord(ctx->ev_in, ctx->copy_in));
+    LK_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_in, 0));   // a full dependency of whatever is enqueued next
+    ctx->copies_pending = true;
+    return LK_OK;
+}
+
+lk_status lk_buf_download_async(lk_buf *buf, uint64_t off, void *host, uint64_t n) {
+    lk_status st = buf_range(buf, off, n, "lk_buf_download_async");
+    if (st != LK_OK) return st;
+    if (n == 0) return LK_OK;
+    if (!host) return fail(buf->ctx, LK_EINVAL_ARG, "lk_buf_download_async: host is NULL");
+    lk_ctx *ctx = buf->ctx;
+    LK_CUDA(ctx, cudaEventRecord(ctx->ev_out, ctx->stream));          // everything enqueued on the compute stream so far
+    LK_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_out, ctx->ev_out, 0));
+    if (ctx->capturing) ctx->cap_out = true;
+    LK_CUDA(ctx, cudaMemcpyAsync(host, (uint8_t *)buf->ptr + off, n, cudaMemcpyDeviceToHost, ctx->copy_out));
+    ctx->copies_pending = true;
+    return LK_OK;
 }
 
 lk_status lk_buf_copy(lk_buf *dst, uint64_t doff, lk_buf *src, uint64_t soff, uint64_t n) {
@@ -1144,6 +1192,8 @@ lk_status lk_capture_begin(lk_ctx *ctx) {
     LK_CUDA(ctx, cudaSetDevice(ctx->device));
     LK_CUDA(ctx, cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
     ctx->capturing = true;
+    ctx->cap_in = ctx->cap_out = false;
+    LK_CUDA(ctx, cudaEventRecord(ctx->ev_root, ctx->stream));   // where a copy stream forks from
     ctx->capture_launches = 0;
     ctx->capture_chain0 = ctx->chain_unchecked;
     ctx->capture_barrier0 = ctx->barrier_unchecked;
@@ -1157,6 +1207,10 @@ lk_status lk_capture_end(lk_ctx *ctx, lk_graph **out) {
     ctx->capturing = false;
     chain_other(ctx, nullptr, 0);
     cudaGraph_t g = nullptr;
+    // copy streams that joined the capture come back to the compute stream before it ends
+    if (ctx->cap_in) { cudaEventRecord(ctx->ev_in, ctx->copy_in); cudaStreamWaitEvent(ctx->stream, ctx->ev_in, 0); }
+    if (ctx->cap_out) { cudaEventRecord(ctx->ev_out, ctx->copy_out); cudaStreamWaitEvent(ctx->stream, ctx->ev_out, 0); }
+    ctx->cap_in = ctx->cap_out = false;
     LK_CUDA(ctx, cudaStreamEndCapture(ctx->stream, &g));
     cudaGraphExec_t ex = nullptr;
     cudaError_t e = cudaGraphInstantiate(&ex, g, 0);

@@ -15,6 +15,12 @@ struct lk_ctx {
     int sm_count = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // lk_buf_upload_async / lk_buf_download_async: one stream per direction beside the compute stream (created on first
+    // use), one event per direction (recorded and waited on back to back), the fork event of a capture
+    cudaStream_t copy_in = nullptr, copy_out = nullptr;
+    cudaEvent_t ev_in = nullptr, ev_out = nullptr, ev_root = nullptr;
+    bool cap_in = false, cap_out = false;      // the copy streams have joined the capture in progress
+    bool copies_pending = false;               // asynchronous copies were issued since the last lk_sync
     std::string err;
     int64_t launches = 0;
     lk::GemvTuning tune;

@@ -74,6 +74,19 @@ class GGMLCudaBuffer:
         B.check(B.lib().lk_buf_download(self.handle, int(tensor.dataOffset) + offset, data.ctypes.data, int(size)),
                 self.lk.handle)
 
+    def setTensorAsync(self, tensor: GGMLTensor, data: np.ndarray, offset: int, size: int) -> None:
+        """setTensor without the wait (lk_buf_upload_async): the copy runs beside the compute stream, every op enqueued
+        after this call waits for it; `data` (pinned for the overlap to exist) must stay untouched until the backend's
+        next synchronize().  It does not wait for ops already enqueued (see the header)."""
+        B.check(B.lib().lk_buf_upload_async(self.handle, int(tensor.dataOffset) + offset, data.ctypes.data, int(size)),
+                self.lk.handle)
+
+    def getTensorAsync(self, tensor: GGMLTensor, data: np.ndarray, offset: int, size: int) -> None:
+        """getTensor without the wait (lk_buf_download_async): starts when everything enqueued so far has finished;
+        `data` is valid after the backend's next synchronize()."""
+        B.check(B.lib().lk_buf_download_async(self.handle, int(tensor.dataOffset) + offset, data.ctypes.data, int(size)),
+                self.lk.handle)
+
     def copyTensor(self, src: GGMLTensor, dst: GGMLTensor) -> bool:
         if not isinstance(src.buffer, GGMLCudaBuffer):
             return False
@@ -109,6 +122,7 @@ class GGMLCudaBackend:
         self.maxChain = 8            # links per launch (the library's limit)
         self._bt = GGMLCudaBufferType(self)
         self._captured = {}      # id(graph) -> (lk_graph handle, node signature, fast key)
+        self._ioKeys = {}        # id(hostIO list) -> (the list, its key): see graphCompute
         self._graphRefs = {}     # id(graph) -> graph
         self.useCudaGraphs = True
         # graphCompute is stream-ordered (asynchronous) like every device-resident op.  A device-side fault of the step —
@@ -400,7 +414,22 @@ class GGMLCudaBackend:
         return [dict(kind=L.kind, node=L.node, rms=L.rms, add=L.add, extra=list(L.extra[:L.n_extra]), silu=L.silu, mul=L.mul,
                      store_b=L.store_b, chain=L.chain, attn=list(L.attn) if L.kind == B.LK_PLAN_ATTN_STEP else None) for L in out[:n.value]]
 
-    def _runNodes(self, ga, graph: GGMLCGraph, fuse: bool) -> None:
+    @staticmethod
+    def _ioArray(hostIO):
+        """hostIO: [("in" | "out", tensor, host ndarray), ...] -> lk_host_io[] (the region is the array's bytes at the
+        tensor's offset in its device buffer)."""
+        arr = (B.lk_host_io * len(hostIO))()
+        for k, (direction, t, host) in enumerate(hostIO):
+            if direction not in ("in", "out") or not isinstance(t.buffer, GGMLCudaBuffer):
+                raise B.IllegalArgumentException("hostIO entries are ('in' | 'out', device-resident tensor, host array)")
+            arr[k].direction = B.LK_IO_UPLOAD if direction == "in" else B.LK_IO_DOWNLOAD
+            arr[k].buf = t.buffer.handle
+            arr[k].offset = int(t.dataOffset)
+            arr[k].bytes = int(host.nbytes)
+            arr[k].host = host.ctypes.data
+        return arr
+
+    def _runNodes(self, ga, graph: GGMLCGraph, fuse: bool, hostIO=None) -> None:
         nodes = graph.nodes
         if self.useLibraryPlanner and hasattr(B.lib(), "lk_graph_compute"):     # (an older build under LK_LIBRARY may lack it)
             arr = self.nodeArray(ga, graph)
@@ -408,8 +437,23 @@ class GGMLCudaBackend:
                 flags = 0 if fuse else B.LK_GRAPH_NO_FUSION
                 if fuse and self.chainOps is not None:
                     flags |= B.LK_GRAPH_CHAIN_ALWAYS if self.chainOps else B.LK_GRAPH_CHAIN_NEVER
-                B.check(B.lib().lk_graph_compute(self.lk.handle, arr, len(nodes), flags), self.lk.handle)
+                if hostIO:
+                    io = self._ioArray(hostIO)
+                    B.check(B.lib().lk_graph_compute_io(self.lk.handle, arr, len(nodes), flags, io, len(hostIO)), self.lk.handle)
+                else:
+                    B.check(B.lib().lk_graph_compute(self.lk.handle, arr, len(nodes), flags), self.lk.handle)
                 return
+        if hostIO:      # the Python planner does not place copies between launches: all uploads first, all downloads last
+            for direction, t, host in hostIO:
+                if direction == "in":
+                    t.buffer.setTensorAsync(t, host, 0, host.nbytes)
+            try:
+                self._runNodes(ga, graph, fuse, None)
+            finally:
+                for direction, t, host in hostIO:
+                    if direction == "out":
+                        t.buffer.getTensorAsync(t, host, 0, host.nbytes)
+            return
         if not fuse:
             for node in nodes:
                 self._computeNode(ga, node)
@@ -596,33 +640,50 @@ class GGMLCudaBackend:
             self.lk.sync()
             B.lib().lk_graph_destroy(ent[0])
 
-    def graphCompute(self, graph: GGMLCGraph) -> GGMLStatus:
-        """core/GGMLBackend.kt:145; exceptions become FAILED like GGMLCpuBackend.kt:168-175."""
+    def graphCompute(self, graph: GGMLCGraph, hostIO=None) -> GGMLStatus:
+        """core/GGMLBackend.kt:145; exceptions become FAILED like GGMLCpuBackend.kt:168-175.
+
+        hostIO (optional): [("in" | "out", tensor, host ndarray), ...] — host copies that belong to the step.  Each "in"
+        array is uploaded to its tensor right before the first launch that reads it, each "out" tensor downloaded right
+        after the last launch that writes it, on copy streams beside the compute stream (lk_graph_compute_io), so the
+        reference's setTensor -> graphCompute -> getTensor sequence costs one chunk of each copy at the ends of the step
+        instead of both in full.  Split the arrays by consumer (one per layer) for the overlap to exist; use pinned
+        arrays; the "out" arrays are valid after synchronize().  The host addresses are part of a captured sequence; pass the
+        same list object step after step (its key is computed once per object — build a new list to change it)."""
         ga = graph.allocator
         try:
+            iokey = None
+            if hostIO:      # the same list object step after step: its key (ctypes address look-ups) is computed once
+                memo = self._ioKeys.get(id(hostIO))
+                if memo is None or memo[0] is not hostIO or len(hostIO) != len(memo[1]):
+                    memo = (hostIO, tuple((d, id(t.buffer), int(t.dataOffset), int(h.nbytes), int(h.ctypes.data)) for d, t, h in hostIO))
+                    if len(self._ioKeys) > 64:
+                        self._ioKeys.clear()
+                    self._ioKeys[id(hostIO)] = memo
+                iokey = memo[1]
             ent = self._captured.get(id(graph)) if self.useCudaGraphs else None
-            if ent is not None and self._graphRefs.get(id(graph)) is graph and ent[2] == self._fastKey(graph):
+            if ent is not None and self._graphRefs.get(id(graph)) is graph and ent[2] == (self._fastKey(graph), iokey):
                 B.check(B.lib().lk_graph_launch(self.lk.handle, ent[0]), self.lk.handle)      # replay: one launch
             elif self.useCudaGraphs and self._allDevice(graph):
-                sig = self._signature(graph)
+                sig = (self._signature(graph), iokey)
                 if ent is None or ent[1] != sig:
                     if ent is not None:
                         B.lib().lk_graph_destroy(ent[0])
                     B.check(B.lib().lk_capture_begin(self.lk.handle), self.lk.handle)
                     try:
-                        self._runNodes(ga, graph, fuse=self.fuseOps)
+                        self._runNodes(ga, graph, fuse=self.fuseOps, hostIO=hostIO)
                     finally:
                         h = C.c_void_p()
                         st = B.lib().lk_capture_end(self.lk.handle, C.byref(h))
                     B.check(st, self.lk.handle)
-                    ent = (h, sig, self._fastKey(graph))
+                    ent = (h, sig, (self._fastKey(graph), iokey))
                 else:
-                    ent = (ent[0], sig, self._fastKey(graph))
+                    ent = (ent[0], sig, (self._fastKey(graph), iokey))
                 self._captured[id(graph)] = ent
                 self._graphRefs[id(graph)] = graph       # the id stays this graph's for as long as the capture exists
                 B.check(B.lib().lk_graph_launch(self.lk.handle, ent[0]), self.lk.handle)
             else:
-                self._runNodes(ga, graph, fuse=False)
+                self._runNodes(ga, graph, fuse=False, hostIO=hostIO)
             if self.checkFaults:
                 self.lk.sync()                   # raises IllegalStateException if a bounded device-side wait gave up
             return GGMLStatus.SUCCESS

@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
     assert len(names) >= 40
     for n in names:
         assert hasattr(L, n), f"{n} declared in the header but not exported"
-    assert L.lk_abi_version() == 2
+    assert L.lk_abi_version() == 3
 
 
 def test_binding_covers_every_declared_symbol():

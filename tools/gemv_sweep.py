@@ -29,6 +29,8 @@ def main():
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--opts", nargs="*", default=[""])
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--min-launches", type=int, default=0,
+                    help="launches per replay: the copies are reused round-robin (with a small --rotate-mb the weights stay in L2)")
     args = ap.parse_args()
 
     import llama_kotlin_b200 as lk
@@ -47,12 +49,13 @@ def main():
         M, K = (int(v) for v in shp.split("x"))
         wb = M * K // 32 * bb
         ncopies = max(2, (args.rotate_mb << 20) // wb)
-        ga = lk.GGMLGraphAllocator(be, size=ncopies * (wb + 256) + (K + M * ncopies) * 4 + (1 << 20))
+        nlaunch = max(ncopies, args.min_launches)
+        ga = lk.GGMLGraphAllocator(be, size=ncopies * (wb + 256) + (K + (M + 64) * nlaunch) * 4 + (1 << 20))
         proto = synth_blocks(rng, M, K, args.qtype)
         x = rng.normal(0, 1, K).astype(np.float32)
         b = ga.allocateTensor(GGMLTensor(GGMLType.F32, [1, K]))
         ga.setBytes(b, x)
-        nodes, first = [], None
+        nodes, first, mats = [], None, []
         for _ in range(ncopies):
             a = ga.allocateTensor(GGMLTensor(gt, [K, M]))
             if first is None:
@@ -60,7 +63,9 @@ def main():
                 first = a
             else:
                 ga.deviceBuffer.copyTensor(first, a)
-            d = ga.allocateTensor(GGMLTensor(GGMLType.F32, [1, M], op=GGMLOp.MUL_MAT, src=[a, b] + [None] * 8))
+            mats.append(a)
+        for i in range(nlaunch):
+            d = ga.allocateTensor(GGMLTensor(GGMLType.F32, [1, M], op=GGMLOp.MUL_MAT, src=[mats[i % ncopies], b] + [None] * 8))
             nodes.append(d)
         for optset in args.opts:
             cur = dict(defaults)
@@ -79,10 +84,10 @@ def main():
             for _ in range(args.reps):
                 be.graphCompute(graph)
             ms = lkc.timer_stop()
-            us = ms * 1e3 / (args.reps * ncopies)
+            us = ms * 1e3 / (args.reps * nlaunch)
             got = ga.getFloats(nodes[-1])
             print(json.dumps({"shape": shp, "qtype": args.qtype, "opts": optset or "default", "us_per_launch": round(us, 3),
-                              "GBps": round(algo_bytes(M, K, bb) / us / 1e3, 1), "copies": ncopies, "ok": ok,
+                              "GBps": round(algo_bytes(M, K, bb) / us / 1e3, 1), "copies": ncopies, "launches": nlaunch, "ok": ok,
                               "checksum": float(np.sum(got.astype(np.float64)))}), flush=True)
         ga.deviceBuffer.free()
     be.free()
