@@ -419,7 +419,7 @@ def config2_arm(args, rank, world, local_rank, lk, be, dist, torch, brief: bool 
         step_spread = {"n": len(singles), "p10_ms": float(q[0]), "median_ms": float(q[1]), "p90_ms": float(q[2]),
                        "how": "one graph replay between two CUDA events with a synchronize after each (no overlap between steps)"}
 
-    ms_dep = e2e_s = e2e_serial_s = float("nan")
+    ms_dep = e2e_s = e2e_serial_s = e2e_nocopy_s = float("nan")
     if not brief:
         # ---- same step with every GEMV forced to wait for its predecessor (a fully dependent chain) ----
         lkc.set_option("gemv_overlap", 0)
@@ -460,6 +460,16 @@ def config2_arm(args, rank, world, local_rank, lk, be, dist, torch, brief: bool 
             step_e2e_serial()
         barrier()
         e2e_serial_s = time.perf_counter() - t0
+        # what the call sequence costs with no copies at all (launch + synchronize per step): the floor of any e2e form
+        for _ in range(3):
+            step_device(); be.synchronize()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            step_device()
+            be.synchronize()
+        barrier()
+        e2e_nocopy_s = time.perf_counter() - t0
         # the two forms must deliver the same bytes (then the check below covers both)
         if not np.array_equal(y_pipelined, y_host):
             raise RuntimeError("pipelined and serial host copies disagree")
@@ -503,6 +513,7 @@ def config2_arm(args, rank, world, local_rank, lk, be, dist, torch, brief: bool 
                 "ms_per_step": e2e_s / args.steps * 1e3,
                 "api": "GGMLCudaBackend.graphCompute(graph, hostIO = per-layer pinned host slices) + synchronize(): "
                        "lk_graph_compute_io issues each layer's upload before its first GEMV and its download after its last",
+                "launch_and_sync_only_ms_per_step": e2e_nocopy_s / args.steps * 1e3,
                 "serial_copies": {"value": bytes_step * args.steps / e2e_serial_s / 1e9, "ms_per_step": e2e_serial_s / args.steps * 1e3,
                                   "api": "GGMLCudaBuffer.setTensor + GGMLCudaBackend.graphCompute + GGMLCudaBuffer.getTensor "
                                          "(both copies in full around the step: round 1's form)"}},
