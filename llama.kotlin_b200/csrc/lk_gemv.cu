@@ -89,7 +89,33 @@ struct XRegs {
     float c;        // Q4_0: -8 * s * sumT;  Q4_1 / Q4_K: s * sumT;  Q8_0 / Q8_K: unused;  Q2_K: s * sumT of elements 0..15
     float s;        // 2^(E-22) (NP = 3) or 2^(E-14) (NP = 2)
     float c2;       // Q2_K only: s * sumT of elements 16..31 (the block column spans two 16-element sub-blocks)
+    uint32_t aux;   // BITNET_1_58 only: shared-space address of this lane's copy of the byte -> five-trit table
+    uint32_t aux_sh;   // ... and log2 of the bytes between consecutive entries of one copy (3..7)
 };
+
+// BitNet 1.58 decode table (one per CTA, in shared memory): entry v = the five base-3 digits of byte v, each as a signed
+// byte digit - 1, twice: .x = (t0, t1, t2, t3), .y = (t1, t2, t3, t4).  With the tail of a five-digit group always in .y
+// and its head in .x, every word of four CONSECUTIVE elements is one PRMT of two table words (or a table word as is).
+#ifndef LK_BITNET_UNR
+#define LK_BITNET_UNR 4
+#endif
+struct BitnetLut { uint32_t w[512]; };
+constexpr BitnetLut make_bitnet_lut() {
+    BitnetLut t{};
+    for (uint32_t e = 0; e < 256; e++) {
+        uint32_t v = e, d[5] = {0, 0, 0, 0, 0};
+        for (int i = 0; i < 5; i++) { const uint32_t q = v / 3u; d[i] = (v - 3u * q - 1u) & 0xFFu; v = q; }
+        t.w[2 * e] = d[0] | (d[1] << 8) | (d[2] << 16) | (d[3] << 24);
+        t.w[2 * e + 1] = d[1] | (d[2] << 8) | (d[3] << 16) | (d[4] << 24);
+    }
+    return t;
+}
+__device__ const BitnetLut g_bitnet_lut = make_bitnet_lut();     // 2 KB, built by the compiler; every CTA copies it into shared memory
+__device__ __forceinline__ uint2 lds_u2(uint32_t addr) {
+    uint2 v;
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
+    return v;
+}
 
 // 16 quant bytes (4 aligned words) of 4-bit quants x the block's activations; exact int32
 template <int NP>
@@ -189,6 +215,50 @@ __device__ __forceinline__ float block_dot(const uint32_t *row, int b, const XRe
             r += fmaf(scale, (float)I * x.s, mn * (h ? x.c2 : x.c));
         }
         return r;
+    } else if (TYPE == T_BITNET_1_58) {
+        // the reference's BitNet 1.58 block (core/GGMLTypes.kt:920-1000, computeDotProductBitNet158F32
+        // core/GGMLComputeOps.kt:635-660): 10 bytes = d (f16), 7 bytes of 5 base-3 digits (element 5g + p = digit p of byte
+        // g, w = d * (digit - 1)), 1 unused.  Word-aligned for even b only.  Each digit byte goes through the CTA's table
+        // (7 LDS.64), 5 PRMTs put the trits in element order, and the block is a signed-byte dot product against the
+        // activation planes like Q8_0: exact int32, one I2F.  A byte >= 243 (leading digit 3: the reference throws
+        // IllegalStateException, core/GGMLTypes.kt:975-981) makes the product NaN.
+        const uint32_t *wp = row + 2 * b + (b >> 1);
+        const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2];
+        const uint32_t q0 = odd ? __byte_perm(w0, w1, 0x5432) : w0;      // d | B0 << 16 | B1 << 24
+        const uint32_t q1 = odd ? __byte_perm(w1, w2, 0x5432) : w1;      // B2 .. B5
+        const uint32_t q2 = odd ? (w2 >> 16) : w2;                       // B6 in byte 0
+        // x.aux = this lane's copy of the table (up to sixteen interleaved copies, entry v of copy r at byte
+        // (v << aux_sh) + 8 r: with sixteen, the lanes of a half-warp always hit sixteen different bank pairs; with one
+        // copy the look-ups run 3-4 deep in bank conflicts and the shared-memory pipe bounds the kernel — but a CTA
+        // with few rows spends longer filling sixteen copies than it loses to the conflicts, so the host picks)
+        const uint2 e0 = lds_u2(x.aux + (__byte_perm(q0, 0, 0x4442) << x.aux_sh)), e1 = lds_u2(x.aux + (__byte_perm(q0, 0, 0x4443) << x.aux_sh));
+        const uint2 e2 = lds_u2(x.aux + (__byte_perm(q1, 0, 0x4440) << x.aux_sh)), e3 = lds_u2(x.aux + (__byte_perm(q1, 0, 0x4441) << x.aux_sh));
+        const uint2 e4 = lds_u2(x.aux + (__byte_perm(q1, 0, 0x4442) << x.aux_sh)), e5 = lds_u2(x.aux + (__byte_perm(q1, 0, 0x4443) << x.aux_sh));
+        const uint2 e6 = lds_u2(x.aux + (__byte_perm(q2, 0, 0x4440) << x.aux_sh));
+        uint32_t q[8];
+        q[0] = e0.x;                                   // elements 0..3   = byte 0 digits 0..3
+        q[1] = __byte_perm(e0.y, e1.x, 0x6543);        // 4..7            = byte 0 digit 4, byte 1 digits 0..2
+        q[2] = __byte_perm(e1.y, e2.x, 0x5432);        // 8..11           = byte 1 digits 3, 4, byte 2 digits 0, 1
+        q[3] = __byte_perm(e2.y, e3.x, 0x4321);        // 12..15          = byte 2 digits 2..4, byte 3 digit 0
+        q[4] = e3.y;                                   // 16..19          = byte 3 digits 1..4
+        q[5] = e4.x;                                   // 20..23          = byte 4 digits 0..3
+        q[6] = __byte_perm(e4.y, e5.x, 0x6543);        // 24..27
+        q[7] = __byte_perm(e5.y, e6.x, 0x5432);        // 28..31          = byte 5 digits 3, 4, byte 6 digits 0, 1
+        int acc[NP];
+#pragma unroll
+        for (int pl = 0; pl < NP; pl++) acc[pl] = 0;
+#pragma unroll
+        for (int j = 0; j < 8; j++)
+#pragma unroll
+            for (int pl = 0; pl < NP; pl++)
+                acc[pl] = (pl == NP - 1) ? dp4a_ss(q[j], x.q[pl][j], acc[pl]) : dp4a_su(q[j], x.q[pl][j], acc[pl]);
+        // a digit byte v >= 243  <=>  bit 7 of v and bit 7 of (v & 0x7F) + 13
+        const uint32_t bad = (q0 & ((q0 & 0x7F7F7F7Fu) + 0x0D0D0D0Du) & 0x80800000u) | (q1 & ((q1 & 0x7F7F7F7Fu) + 0x0D0D0D0Du) & 0x80808080u) |
+                             (q2 & ((q2 & 0x7F7F7F7Fu) + 0x0D0D0D0Du) & 0x00000080u);
+        const float d = h2f((uint16_t)(q0 & 0xFFFFu));
+        const int I = (NP == 3) ? (acc[NP - 1] << 16) + ((acc[1] << 8) + acc[0]) : (acc[1] << 8) + acc[0];   // |I| <= 32 * 2^22
+        const float r = d * ((float)I * x.s);
+        return bad ? __uint_as_float(0x7FC00000u) : r;
     } else if (TYPE == T_Q8_K) {
         // the reference's own Q8_K (core/GGMLComputeOps.kt:382-432): 292-byte super-block = 73 words: d (f32), 256 int8
         const uint32_t *wp = row + 73 * (b >> 3) + 1 + 8 * (b & 7);
@@ -260,6 +330,8 @@ struct GemvParams {
     int rg_shift;         // rg == 1 << rg_shift (row groups are a power of two: no integer division per stage)
     int ng;               // chained kernel only: warp groups of rg * ncw warps each; group g takes stages g, g + ng, ...
     int fix_gap;          // range fix-up: a block with a non-zero |x| below 2^-fix_gap of the block maximum is flagged (>= 255: never)
+    int lut_off;          // BITNET_1_58: byte offset of the decode table in dynamic shared memory
+    int lut_shift;        // ... log2 of its interleaved copies (0..4): entry v of copy r at byte (v << (3 + lut_shift)) + 8 r
     int64_t row_offset;   // dst index of row 0 (sharded weights)
     unsigned long long *tl;         // timeline buffer (tools/gemv_timeline.cu builds only), else NULL
     // ---- 120 bytes
@@ -334,7 +406,7 @@ static_assert(sizeof(GemvSide) <= 128, "side words share the first 256 bytes wit
 #ifdef LK_GEMV_NO_RANGE_FIX     // A/B builds only (tools/ab_build.sh): what the detection and the cold call sites cost
 template <int TYPE> __host__ __device__ constexpr bool gemv_has_fixup() { return false; }
 #else
-template <int TYPE> __host__ __device__ constexpr bool gemv_has_fixup() { return TYPE == T_Q4_0 || TYPE == T_Q4_1 || TYPE == T_Q8_0; }
+template <int TYPE> __host__ __device__ constexpr bool gemv_has_fixup() { return TYPE == T_Q4_0 || TYPE == T_Q4_1 || TYPE == T_Q8_0 || TYPE == T_BITNET_1_58; }
 #endif
 // Where the detection sits was measured on one B200 box (profiles/r02_gemv_range_fix_ab.txt, headline step, GB/s):
 // round-1 kernel 4610; no detection 4557; detection inside prep_x (this code) 4490; detection by a dedicated 10th warp
@@ -525,11 +597,11 @@ __device__ __forceinline__ void prep_x(const GemvParams &p, uint32_t *xs, int ti
 #pragma unroll
                     for (int j = 0; j < 4; j++)   // 2-bit field j of a quant word's four bytes = elements j, 4+j, 8+j, 12+j of my half
                         wds[j] = __byte_perm(__byte_perm(T[j], T[4 + j], s2), __byte_perm(T[8 + j], T[12 + j], s2), 0x5410);
-                } else if (TYPE == T_Q8_0 || TYPE == T_Q8_K || p.nib) {
+                } else if (TYPE == T_Q8_0 || TYPE == T_Q8_K || TYPE == T_BITNET_1_58 || p.nib) {
 #pragma unroll
                     for (int j = 0; j < 4; j++)
                         wds[j] = __byte_perm(__byte_perm(T[4 * j], T[4 * j + 1], s2), __byte_perm(T[4 * j + 2], T[4 * j + 3], s2), 0x5410);
-                    if (TYPE != T_Q8_0 && TYPE != T_Q8_K) {
+                    if (TYPE != T_Q8_0 && TYPE != T_Q8_K && TYPE != T_BITNET_1_58) {
                         // ggml order: quant word j holds elements 4j..4j+3 in its low nibbles (plane word 2j) and elements
                         // 16+4j.. in its high nibbles (plane word 2j+1): my half h fills words 2j + h
 #pragma unroll
@@ -624,7 +696,7 @@ __device__ __forceinline__ void gemv_fixup_body(const uint8_t *a, const float *b
                 const int blk = w * 32 + bit;
                 const float s = __uint_as_float(xs[(size_t)blk * gemv_xslot_words(NP) + NP * 8 + 1]);
                 const float c = __frcp_rn(s);                                 // a power of two: exact
-                const uint8_t *bp = rowp + (size_t)blk * block_bytes(TYPE);
+                const uint8_t *bp = rowp + (size_t)blk * (TYPE == T_BITNET_1_58 ? 10 : block_bytes(TYPE));
                 const float d = h2f((uint16_t)(bp[0] | (bp[1] << 8)));
                 float mq = 0.f;
                 if (TYPE == T_Q4_1) mq = h2f((uint16_t)(bp[2] | (bp[3] << 8)));
@@ -643,6 +715,11 @@ __device__ __forceinline__ void gemv_fixup_body(const uint8_t *a, const float *b
                     float wv;                                                 // the reference's weight, core/GGMLComputeOps.kt:43-145
                     if (TYPE == T_Q8_0) {
                         wv = __fmul_rn(d, (float)(int8_t)bp[2 + k]);
+                    } else if (TYPE == T_BITNET_1_58) {                       // digit k % 5 of byte k / 5, core/GGMLTypes.kt:975-990
+                        const int g = (k * 13) >> 6;                          // k / 5 for k < 64
+                        uint32_t dv = bp[2 + g];
+                        for (int z = k - 5 * g; z > 0; z--) dv /= 3u;
+                        wv = __fmul_rn(d, (float)((int)(dv % 3u) - 1));
                     } else {
                         const uint8_t byte = bp[QOFF + (nib ? (k & 15) : (k >> 1))];
                         const float q = (float)((nib ? (k >> 4) : (k & 1)) ? (byte >> 4) : (byte & 15));
@@ -904,6 +981,17 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const __gri
     for (int r = warp; r < p.red_rows; r += p.cwarps)
         if (lane < GEMV_RED_PAD) red[r * p.red_stride + p.ncw * 8 + lane] = 0.f;
     if (warp == 0) { if (lane < 28) side->mask[lane] = 0u; if (lane == 28) side->any = 0u; }
+    uint32_t lut_addr = 0;
+    if (TYPE == T_BITNET_1_58) {            // the CTA's byte -> five-trit table (read after the bar.sync that follows prep_x)
+        lut_addr = smem_u32(smem + p.lut_off);
+        const int lsh = p.lut_shift;
+#pragma unroll 4
+        for (int i = tid; i < (256 << lsh); i += nct) {        // item i = entry i >> lsh, copy i & (copies - 1), at byte 8 i: conflict-free stores
+            const uint2 e = __ldg((const uint2 *)g_bitnet_lut.w + (i >> lsh));
+            asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(lut_addr + 8u * i), "r"(e.x), "r"(e.y) : "memory");
+        }
+        lut_addr += 8u * (lane & ((1 << lsh) - 1));
+    }
     unsigned long long xticket = 0;
     if (PEER && p.wait_n > 0 && tid == 0) xticket = atomicAdd(p.wait_ticket, 1ull);   // issued early: its latency hides under the barrier below
     __syncthreads();   // barriers initialised by the producer
@@ -934,12 +1022,14 @@ __global__ void __launch_bounds__((MAXW + 1) * 32, MINB) gemv_kernel(const __gri
 #endif
 
     XRegs<NP> x;
+    x.aux = lut_addr;
+    x.aux_sh = 3u + (uint32_t)p.lut_shift;
     load_xregs<TYPE, NP>(x, xs, colc);
     if (tid == 0) LK_TL(5);
 
     // Stage loop: one barrier wait / release per stage; inside, this warp's rows (rgi, rgi+rg, ...)
     // are processed UNR at a time so that UNR independent dot-product chains are in flight.
-    constexpr int UNR = 4;
+    constexpr int UNR = TYPE == T_BITNET_1_58 ? LK_BITNET_UNR : 4;    // (BitNet: 6 and 8 rows per step measured no faster, profiles/r02g_bitnet_gemv.txt)
     const int rg_words = p.rg * (p.row_bytes >> 2);
     int red_base = 0, s = 0, par = 0, it = 0;
     const uint32_t *sp = (const uint32_t *)stage0 + (size_t)rgi * (p.row_bytes >> 2);   // my first row of the stage
@@ -1343,9 +1433,10 @@ static cudaError_t launch_plain(const GemvParams &p, int grid, int smem, int pdl
 cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const float *b, float *dst,
                         int64_t row_offset, const GemvPeers &peers, const GemvTuning &tune, int sm_count,
                         cudaStream_t s, const GemvFusion *fusion, const GemvSync *sync) {
-    const bool kq = type == T_Q4_K || type == T_Q8_K || type == T_Q2_K;     // the reference's K-quant super-blocks (256 elements)
-    if (kq && ((K % 256) != 0 || fusion)) return cudaErrorNotSupported;
-    const int bb = block_bytes(type);
+    const bool bitnet = type == T_BITNET_1_58;                              // 10-byte blocks of 32 ternary weights
+    const bool kq = type == T_Q4_K || type == T_Q8_K || type == T_Q2_K || bitnet;     // the reference's K-quant super-blocks (256 elements) / BitNet: plain launches only
+    if (kq && ((!bitnet && (K % 256) != 0) || fusion)) return cudaErrorNotSupported;
+    const int bb = bitnet ? 10 : block_bytes(type);
     if ((bb == 0 && !kq) || K <= 0 || M <= 0 || (K % 64) != 0 || K > 32 * 32 * 28 || M > (1 << 30))
         return cudaErrorNotSupported;
     if (((uintptr_t)a & 15) || ((uintptr_t)b & 15)) return cudaErrorNotSupported;
@@ -1386,7 +1477,7 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
     p.tl = (unsigned long long *)tune.timeline;
     p.wait_mode = tune.wait_mode;
     p.fix_gap = tune.fix_gap >= 255 ? 255 : std::max(2, tune.fix_gap - (tune.act_planes == 2 ? 8 : 0));
-    p.row_bytes = kq ? (int)(K / 256) * (type == T_Q4_K ? 144 : type == T_Q8_K ? 292 : 84) : (int)(K / 32) * bb;
+    p.row_bytes = (kq && !bitnet) ? (int)(K / 256) * (type == T_Q4_K ? 144 : type == T_Q8_K ? 292 : 84) : (int)(K / 32) * bb;
     p.nblk = (int)(K / 32);
     p.ncw = (p.nblk + 31) / 32;
     const int target_warps = tune.variant > 0 ? tune.variant : 8;   // consumer warps to aim for
@@ -1409,13 +1500,13 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
     // best with stages of rg * 4 rows per 40 KB target (every warp gets whole 4-row steps, fewer barrier rounds on the
     // critical path); independent launches, which overlap pairwise on an SM, with 32 KB stages of any row count.
     const bool dependent = tune.wait_mode != GEMV_WAIT_END;
-    const int stage_target = tune.stage_bytes > 0 ? tune.stage_bytes : (dependent ? 40 : 32) * 1024;
+    const int stage_target = tune.stage_bytes > 0 ? tune.stage_bytes : bitnet ? 16 * 1024 : (dependent ? 40 : 32) * 1024;   // BitNet: 32 KB of the budget hold the table
     int quant = p.unit_rows;                       // stage_rows: multiple of unit_rows (TMA size) and of rg
     while (quant % p.rg) quant += p.unit_rows;
-    const bool row_quant = tune.row_quant < 0 ? dependent : tune.row_quant != 0;
+    const bool row_quant = tune.row_quant < 0 ? (dependent || bitnet) : tune.row_quant != 0;
     if (row_quant) {
         int q4 = p.unit_rows;
-        while (q4 % (p.rg * 4)) q4 += p.unit_rows;
+        while (q4 % (p.rg * (bitnet ? LK_BITNET_UNR : 4))) q4 += p.unit_rows;
         if ((int64_t)q4 * p.row_bytes <= stage_target + stage_target / 4) quant = q4;
     }
     int sr = (stage_target / p.row_bytes / quant) * quant;
@@ -1447,6 +1538,13 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
     p.x_off = (p.out_off + (p.npeers > 0 ? p.red_rows * 4 : 0) + 15) & ~15;
     const int np = tune.act_planes == 2 ? 2 : 3;
     p.stage_off = (p.x_off + p.nblk * gemv_xslot_words(np) * 4 + 127) & ~127;
+    if (bitnet) {       // interleaved copies of the 2 KB trit table: sixteen where a CTA has enough rows to pay for filling them
+        int copies = tune.bitnet_copies > 0 ? tune.bitnet_copies : ((int64_t)max_cta_rows * p.nblk >= 8192 ? 16 : 1);
+        p.lut_shift = 0;
+        while ((2 << p.lut_shift) <= copies) p.lut_shift++;
+        p.lut_off = p.stage_off;
+        p.stage_off += 2048 << p.lut_shift;
+    }
     int nst = (budget - p.stage_off) / stage_bytes;
     const int max_st = tune.max_stages > 0 ? tune.max_stages : GEMV_MAX_STAGES;
     if (nst > max_st) nst = max_st;
@@ -1475,6 +1573,8 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
         case T_Q8_K * 4 + 3: return launch_plain<T_Q8_K, 3>(p, grid, smem, tune.pdl, s);
         case T_Q2_K * 4 + 2: return launch_plain<T_Q2_K, 2>(p, grid, smem, tune.pdl, s);
         case T_Q2_K * 4 + 3: return launch_plain<T_Q2_K, 3>(p, grid, smem, tune.pdl, s);
+        case T_BITNET_1_58 * 4 + 2: return launch_plain<T_BITNET_1_58, 2>(p, grid, smem, tune.pdl, s);
+        case T_BITNET_1_58 * 4 + 3: return launch_plain<T_BITNET_1_58, 3>(p, grid, smem, tune.pdl, s);
         default: return cudaErrorNotSupported;
     }
 }

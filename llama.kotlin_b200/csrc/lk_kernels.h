@@ -15,6 +15,7 @@ struct GemvTuning {
     int smem_budget = 0;    // 0 = auto: bytes of dynamic smem per CTA
     int pdl = 1;            // programmatic dependent launch attribute
     int ctas_per_sm = 1;
+    int bitnet_copies = 0;  // BITNET_1_58: interleaved copies of the trit table in shared memory (1..16, power of two); 0 = by shape
     int act_planes = 3;     // activation fixed-point planes: 3 = 24-bit (default: as accurate as the F32 reference),
                             // 2 = 16-bit (opt-in: +8 % throughput, error 5e-5 of max instead of 2e-6)
     int row_quant = -1;     // stage rows a multiple of 4 per warp: -1 auto (dependent launches only), 0 never, 1 always

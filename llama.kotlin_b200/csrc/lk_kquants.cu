@@ -15,9 +15,9 @@
 //
 // Three kernels:
 //   kq_dequant_kernel   bit-exact with dequantizeTensor (one IEEE op per reference op, __fmul_rn / __fadd_rn / __fdiv_rn);
-//   kq_gemv_kernel      N == 1, rows of whole blocks, for BITNET_1_58 and for K-quant shapes K1 declines (Q2_K / Q4_K /
-//                       Q8_K with K % 256 == 0 normally run on the streaming DP4A GEMV of lk_gemv.cu, block_dot<T_Q4_K> etc.,
-//                       3-9 x faster: an int->F32 conversion + FMA per element is instruction-bound): one CTA per 4 rows, a 256-element super-block
+//   kq_gemv_kernel      N == 1, rows of whole blocks, for the shapes K1 declines (Q2_K / Q4_K / Q8_K with K % 256 == 0 and
+//                       BITNET_1_58 with K % 64 == 0 normally run on the streaming DP4A GEMV of lk_gemv.cu, block_dot<T_Q4_K>
+//                       etc., 3-9 x faster: an int->F32 conversion + FMA per element is instruction-bound): one CTA per 4 rows, a 256-element super-block
 //                       of each row per warp step (8 elements per lane, 4 / 2 / 8-byte quant loads, 2 x LDG.128 of x
 //                       shared by the 4 rows), per sub-block scale * sum(q x) + min * sum(x) in F32, shuffle + shared
 //                       reduction;  algorithmic bytes = M K/256 B + 4K + 4M;

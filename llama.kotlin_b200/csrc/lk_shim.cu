@@ -595,8 +595,8 @@ lk_status lk_compute_matmul(lk_ctx *ctx, const lk_tensor *a, const lk_tensor *b,
     if (M == 0 || N == 0) return finish(sc);
 
     if (is_kq_type(a->type)) {     // core/GGMLComputeOps.kt:1481-1513 (+ computeDotProductBitNet158F32, :635-660)
-        if (N == 1 && a->type != LK_TYPE_BITNET_1_58 && K > 0 && K % 256 == 0) {
-            // whole super-blocks per row: the streaming DP4A GEMV (K1) takes the three K-quant formats as well
+        if (N == 1 && K > 0 && (a->type == LK_TYPE_BITNET_1_58 ? K % 64 == 0 : K % 256 == 0)) {
+            // whole super-blocks per row: the streaming DP4A GEMV (K1) takes the three K-quant formats and BitNet 1.58 as well
             lk::GemvTuning tune = ctx->tune;
             tune.pdl = (ctx->pdl_mode == 2) || (ctx->pdl_mode == 1 && ctx->capturing);
             lk::GemvPeers none;
@@ -1258,6 +1258,7 @@ lk_status lk_set_option(lk_ctx *ctx, const char *name, int64_t v) {
     else if (n == "gemv_overlap") ctx->overlap_mode = (int)v;
     else if (n == "gemv_chain") ctx->chain_mode = v ? 1 : 0;
     else if (n == "gemv_act_planes") ctx->tune.act_planes = (v == 2) ? 2 : 3;
+    else if (n == "gemv_bitnet_copies") ctx->tune.bitnet_copies = (v == 1 || v == 2 || v == 4 || v == 8 || v == 16) ? (int)v : 0;
     else if (n == "nibble_order") ctx->tune.nibble_order = v ? 1 : 0;
     else if (n == "gemv_fix_gap") ctx->tune.fix_gap = v < 2 ? 2 : v > 255 ? 255 : (int)v;
     else if (n == "gemm_tc_min_n") ctx->gemm_tc_min_n = (int)v;
@@ -1291,6 +1292,7 @@ int64_t lk_get_option(lk_ctx *ctx, const char *name) {
         return seen;
     }
     if (n == "gemv_act_planes") return ctx->tune.act_planes;
+    if (n == "gemv_bitnet_copies") return ctx->tune.bitnet_copies;
     if (n == "nibble_order") return ctx->tune.nibble_order;
     if (n == "gemv_fix_gap") return ctx->tune.fix_gap;
     if (n == "gemm_tc_min_n") return ctx->gemm_tc_min_n;

@@ -130,6 +130,81 @@ def test_bitnet_invalid_byte_is_nan(ga):
     assert np.isnan(got[1]) and np.all(np.isfinite(np.delete(got, 1)))
 
 
+# ---- BitNet 1.58 on the streaming DP4A GEMV (K1, lk_gemv.cu block_dot<T_BITNET_1_58>): N == 1, K % 64 == 0 ----------------
+def _bitnet_exact(raw, K, M, x):
+    """float64 reference from the raw blocks: w = d * (digit - 1), core/GGMLTypes.kt:975-990"""
+    blk = raw.reshape(-1, 10)
+    d = blk[:, 0:2].copy().view(np.float16).astype(np.float64).reshape(-1)
+    dig = np.empty((blk.shape[0], 35), np.int64)
+    v = blk[:, 2:9].astype(np.int64)
+    for p in range(5):
+        dig[:, p::5] = v % 3
+        v //= 3
+    w = ((dig[:, :32] - 1) * d[:, None]).reshape(M, K)
+    return w @ x.astype(np.float64)
+
+
+@pytest.mark.parametrize("M,K", [(4, 64), (148, 128), (37 * 4, 1024), (4096, 4096), (1000, 11008), (4096, 28672)])
+def test_bitnet_streaming_gemv(O, ga, M, K):
+    raw = random_blocks(BITNET, M * K // 32, seed=M + K)
+    x = np.random.default_rng(K).normal(0, 1, K).astype(np.float32)
+    got = gpu_matmul(ga, BITNET, raw, K, M, x, 1)
+    want = _bitnet_exact(raw, K, M, x)
+    assert rel_err(got, want) <= 1e-5           # exact integer block sums, 24-bit activations: far inside the 1e-3 bar
+    if M * K <= 1 << 22:
+        assert rel_err(got, O.kq_matmul(BITNET, raw, K, M, x, 1)) <= TOL
+
+
+def test_bitnet_every_byte_value_in_every_position(ga):
+    """each digit byte 0..242 at each of the 7 positions of an even and of an odd block, one non-zero activation per
+    decoded element: the product is exactly d * (digit - 1) * x"""
+    K = 64
+    rows = []
+    for pos in range(7):
+        for blk in range(2):
+            for v in range(243):
+                r = np.zeros((2, 10), np.uint8)
+                r[:, 0:2] = np.array([1.0], np.float16).view(np.uint8)
+                r[:, 2:9] = 121                      # 121 = 11111 base 3: every weight 0
+                r[blk, 2 + pos] = v
+                rows.append(r.reshape(-1))
+    raw = np.concatenate(rows)
+    M = len(rows)
+    pad = (-M) % 4
+    raw = np.concatenate([raw, np.tile(rows[0], pad)])
+    M += pad
+    x = (np.arange(K) + 1).astype(np.float32)        # distinct integers: the sum identifies the digits
+    got = gpu_matmul(ga, BITNET, raw, K, M, x, 1)
+    want = _bitnet_exact(raw, K, M, x)
+    assert np.array_equal(got.astype(np.float64), want)
+
+
+@pytest.mark.parametrize("blk", [0, 1, 2, 3])
+@pytest.mark.parametrize("pos", range(7))
+def test_bitnet_streaming_invalid_byte_is_nan(ga, blk, pos):
+    M, K = 8, 128
+    raw = random_blocks(BITNET, M * K // 32, seed=5).reshape(M, K // 32, 10)
+    raw[:, :, 9] = 255                                # the unused byte may hold anything
+    raw[3, blk, 2 + pos] = 243 + (pos * 2 + blk) % 13
+    x = np.random.default_rng(1).normal(0, 1, K).astype(np.float32)
+    got = gpu_matmul(ga, BITNET, raw.reshape(-1), K, M, x, 1)
+    assert np.isnan(got[3]) and np.all(np.isfinite(np.delete(got, 3)))
+
+
+def test_bitnet_range_fixup(ga):
+    """a block whose large activation meets a zero weight: the small elements' products must survive (K1 range fix-up)"""
+    M, K = 8, 256
+    raw = random_blocks(BITNET, M * K // 32, seed=9).reshape(M, K // 32, 10)
+    raw[:, :, 0:2] = np.array([0.5], np.float16).view(np.uint8)
+    raw[:, 3, 2] = (raw[:, 3, 2] // 3) * 3 + 1        # digit 0 of byte 0 = 1: weight of element 0 of block 3 is zero
+    x = np.random.default_rng(2).normal(0, 1e-9, K).astype(np.float32)
+    x[3 * 32] = 3.0e4                                 # 2^45 above its neighbours
+    got = gpu_matmul(ga, BITNET, raw.reshape(-1), K, M, x, 1)
+    want = _bitnet_exact(raw.reshape(-1), K, M, x)
+    assert float(np.max(np.abs(want))) < 1e-6         # the large element contributes nothing
+    assert rel_err(got, want) <= 1e-5
+
+
 @pytest.mark.parametrize("t", TYPES)
 def test_errors(ga, t):
     gt = GGMLType(t)

@@ -24,6 +24,7 @@ def main():
     ap.add_argument("--shapes", nargs="*", default=["4096x4096", "11008x4096", "4096x11008"])
     ap.add_argument("--rotate-mb", type=int, default=512)
     ap.add_argument("--reps", type=int, default=20)
+    ap.add_argument("--opt", action="append", help="lk_set_option name=value")
     args = ap.parse_args()
 
     import llama_kotlin_b200 as lk
@@ -36,6 +37,9 @@ def main():
         pass
     be = lk.GGMLCudaBackend(0)
     lkc = be.lk
+    for kv in args.opt or []:
+        k, v = kv.split("=")
+        lkc.set_option(k, int(v))
     rng = np.random.default_rng(1)
     for tname in args.types:
         gt = getattr(GGMLType, tname)
@@ -68,7 +72,7 @@ def main():
             us = lkc.timer_stop() * 1e3 / (args.reps * ncopies)
             algo = wb + 4 * K + 4 * M
             gbps = algo / us / 1e3
-            kern = f"gemv_kernel<{tname}> (K1, DP4A planes)" if tname != "BITNET_1_58" else "kq_gemv_kernel<BITNET_1_58>"
+            kern = f"gemv_kernel<{tname}> (K1, DP4A planes)" if tname != "BITNET_1_58" else "gemv_kernel<BITNET_1_58> (K1, DP4A planes, trit table)"
             print(json.dumps({"kernel": kern, "shape": f"{M}x{K}", "us_per_launch": round(us, 3),
                               "algorithmic_bytes": algo, "GBps": round(gbps, 1),
                               "hbm_frac": round(gbps / peak, 4) if peak else None, "copies": ncopies, "ok": ok}), flush=True)
