@@ -184,7 +184,9 @@ LK_API lk_status   lk_host_free(lk_ctx *ctx, void *p);
  *       |dst_i - exact_i| <= 2^-23 * sum_k |w_ik| * bmax(k) + F32 summation terms (measured 1e-6 .. 4e-6 of max|dst|).
  *       A block that holds a non-zero |x| below 2^-20 of its maximum (option gemv_fix_gap) is recomputed from the F32
  *       activations (exact residuals), so elements the block scale cannot represent are not lost; non-finite
- *       activations give non-finite outputs like the reference.
+ *       activations give non-finite outputs like the reference.  The opt-in 16-bit mode (option gemv_act_planes = 2:
+ *       T_k = rint(x_k * 2^(14-E)), absolute error <= 2^(E-15) per element) runs without that recomputation unless
+ *       gemv_fix_gap is set as well (the gap then counts from 2^-12).
  *   K2: option gemm_tc_precision = 2 (default): d*q and b as FP16 hi + lo pairs (d*q exactly; b to 22 bits), three
  *       MMAs per K step, F32 accumulation in tensor memory: max-norm error ~4e-6; per element <= 1.5e-6 * K relative
  *       (the accumulator truncates).  1: exact weights x FP16 activations (max-norm ~2.5e-4).  0: single FP16 operands

@@ -408,10 +408,12 @@ template <int TYPE> __host__ __device__ constexpr bool gemv_has_fixup() { return
 #else
 template <int TYPE> __host__ __device__ constexpr bool gemv_has_fixup() { return TYPE == T_Q4_0 || TYPE == T_Q4_1 || TYPE == T_Q8_0 || TYPE == T_BITNET_1_58; }
 #endif
-// Where the detection sits was measured on one B200 box (profiles/r02_gemv_range_fix_ab.txt, headline step, GB/s):
-// round-1 kernel 4610; no detection 4557; detection inside prep_x (this code) 4490; detection by a dedicated 10th warp
-// that scans x beside the consumers 4016 (the extra warp alone, exiting at once, already costs 1.5 %); detection by the
-// idle lanes of the producer warp: slower still (they share a warp with the lane that streams the weights).
+// Where the detection sits and what the call sites cost was measured on one B200 box per run
+// (profiles/r02_gemv_range_fix_ab.txt, headline step, GB/s): without detection and sites 4705; detection inside prep_x
+// and light call sites (this code) 4626 (0.7 % each); the round-1 kernel 4613.  Rejected: detection by a dedicated 10th
+// warp that scans x beside the consumers (-10.6 %; the extra warp alone, exiting at once, already costs 1.5 %), by the
+// idle lanes of the producer warp (slower still: they share a warp with the lane that streams the weights), and a
+// sixteen-argument call at the sites (spills; -7 % on the chained kernel although never taken; see gemv_fixup below).
 
 __device__ __forceinline__ float fmin3_abs(float a, float b, float c) {   // min(|a|, |b|, |c|)
     float d;
@@ -1476,7 +1478,7 @@ cudaError_t launch_gemv(int type, const void *a, int64_t K, int64_t M, const flo
     }
     p.tl = (unsigned long long *)tune.timeline;
     p.wait_mode = tune.wait_mode;
-    p.fix_gap = tune.fix_gap >= 255 ? 255 : std::max(2, tune.fix_gap - (tune.act_planes == 2 ? 8 : 0));
+    p.fix_gap = (tune.fix_gap >= 255 || (tune.act_planes == 2 && !tune.fix_gap_set)) ? 255 : std::max(2, tune.fix_gap - (tune.act_planes == 2 ? 8 : 0));
     p.row_bytes = (kq && !bitnet) ? (int)(K / 256) * (type == T_Q4_K ? 144 : type == T_Q8_K ? 292 : 84) : (int)(K / 32) * bb;
     p.nblk = (int)(K / 32);
     p.ncw = (p.nblk + 31) / 32;
@@ -1614,7 +1616,7 @@ cudaError_t launch_gemv_chain(int type, int n, const GemvChainLink *links, const
             p.epi_mode = 1; p.epi_act = f.epi_act; p.epi_out = f.epi_out;
         }
         p.wait_mode = GEMV_WAIT_X;
-        p.fix_gap = tune.fix_gap >= 255 ? 255 : std::max(2, tune.fix_gap - (np == 2 ? 8 : 0));
+        p.fix_gap = (tune.fix_gap >= 255 || (np == 2 && !tune.fix_gap_set)) ? 255 : std::max(2, tune.fix_gap - (np == 2 ? 8 : 0));
         p.row_bytes = (int)(K / 32) * bb;
         p.nblk = (int)(K / 32);
         p.ncw = (p.nblk + 31) / 32;

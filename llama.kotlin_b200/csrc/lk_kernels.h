@@ -23,6 +23,8 @@ struct GemvTuning {
                             // 1 = canonical ggml / GGUF order (byte j = elements j, j+16, ggml/src/ggml-quants.c:1524-1530)
     int fix_gap = 20;       // range fix-up: blocks holding a non-zero |x| below 2^-fix_gap of the block maximum are recomputed from the
                             // F32 activations (lk_gemv.cu, GemvSide); >= 255 switches the detection off
+    bool fix_gap_set = false;   // the option was set by the caller: the opt-in 16-bit mode (act_planes = 2) runs without the fix-up
+                                // otherwise (its contract is the 2^-15 absolute bound; at gap 12 most launches would take the cold path)
     int wait_mode = 1;      // 0 wait before the weight prefetch, 1 before reading x, 2 at the end (independent launch)
     void *timeline = nullptr;   // tools/gemv_timeline.cu only: per-CTA %globaltimer stamps
 };

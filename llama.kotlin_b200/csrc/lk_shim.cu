@@ -1260,7 +1260,7 @@ lk_status lk_set_option(lk_ctx *ctx, const char *name, int64_t v) {
     else if (n == "gemv_act_planes") ctx->tune.act_planes = (v == 2) ? 2 : 3;
     else if (n == "gemv_bitnet_copies") ctx->tune.bitnet_copies = (v == 1 || v == 2 || v == 4 || v == 8 || v == 16) ? (int)v : 0;
     else if (n == "nibble_order") ctx->tune.nibble_order = v ? 1 : 0;
-    else if (n == "gemv_fix_gap") ctx->tune.fix_gap = v < 2 ? 2 : v > 255 ? 255 : (int)v;
+    else if (n == "gemv_fix_gap") { ctx->tune.fix_gap = v < 2 ? 2 : v > 255 ? 255 : (int)v; ctx->tune.fix_gap_set = true; }
     else if (n == "gemm_tc_min_n") ctx->gemm_tc_min_n = (int)v;
     else if (n == "gemm_tc_min_work") ctx->gemm_tc_min_work = v < 0 ? 0 : v;
     else if (n == "gemm_tc_cluster") ctx->gemm_tc_cluster = (int)v;

@@ -1,16 +1,6 @@
 #!/bin/bash
 mkdir -p gpurun_out
-: > gpurun_out/bitnet_unr.txt
-run() {
-echo "lib [$1] $2 $3" | tee -a gpurun_out/bitnet_unr.txt
-LK_LIBRARY=$1 timeout 600 python tools/kq_bench.py --types BITNET_1_58 --shapes 4096x4096 11008x4096 4096x11008 8192x8192 $2 $3 2>/dev/null | python -c "
-import sys,json
-for l in sys.stdin:
-    d=json.loads(l); print(' ', d['shape'], d['us_per_launch'], d['GBps'], d['hbm_frac'])
-" | tee -a gpurun_out/bitnet_unr.txt
-}
-run ""
-run tools/_ab/lib_bitnet_unr4.so
-run tools/_ab/lib_bitnet_unr6.so
-run "" --opt gemv_warps=16
-run tools/_ab/lib_bitnet_unr4.so --opt gemv_warps=16
+CMD="python bench.py --steps 2 --warmup 3 --no-extras --no-cpu-baseline"
+timeout 600 $CMD > gpurun_out/c_plain.log 2>&1 || { echo "plain run failed"; tail -5 gpurun_out/c_plain.log; exit 1; }
+timeout 1500 ncu --set full --clock-control none --import-source on -k regex:gemv_kernel -s 300 -c 3 -f -o gpurun_out/r02h_gemv $CMD > gpurun_out/c_ncu.log 2>&1
+echo "ncu rc $?"; ls -la gpurun_out/r02h_gemv.ncu-rep; tail -3 gpurun_out/c_ncu.log
