@@ -374,8 +374,13 @@ __device__ __forceinline__ unsigned lk_smid() { unsigned v; asm volatile("mov.u3
 #define LK_TL(slot) do { if (p.tl) { unsigned long long *q_ = p.tl + (size_t)blockIdx.x * LK_TL_SLOTS; \
     if ((slot) == 0) { q_[0] = lk_gtime(); q_[31] = (unsigned long long)clock64(); q_[30] = lk_smid(); } \
     else { q_[(slot)] = (unsigned long long)clock64(); if ((slot) == 7) q_[29] = lk_gtime(); } } } while (0)
+// chained kernel: per CTA 8 header words (0: %globaltimer at entry, 1: clock64 at entry, 2: %smid, 3: %globaltimer at exit)
+// + 8 clock64 stamps per phase (tools/chain_timeline.cu)
+#define LK_CTL_STRIDE (8 + 8 * 8)
+#define LK_CTL(ph, slot) do { if (cp.ph[0].tl) cp.ph[0].tl[(size_t)blockIdx.x * LK_CTL_STRIDE + 8 + (ph) * 8 + (slot)] = (unsigned long long)clock64(); } while (0)
 #else
 #define LK_TL(slot) do { } while (0)
+#define LK_CTL(ph, slot) do { } while (0)
 #endif
 
 __device__ __forceinline__ float fmax3_nan_abs(float a, float b, float c) {   // max(|a|, |b|, |c|), NaN if any is NaN
@@ -1241,6 +1246,7 @@ __global__ void __launch_bounds__((CHAIN_W + 1) * 32, 1) gemv_chain_kernel(const
                         if (++s == nslots) { s = 0; round++; }
                     }
                 }
+                LK_CTL(ph, 7);     // the phase's last copy is issued
             }
         }
         return;
@@ -1249,6 +1255,9 @@ __global__ void __launch_bounds__((CHAIN_W + 1) * 32, 1) gemv_chain_kernel(const
     // ===== consumer warps =====
     if (warp == 0) { if (lane < 28) side->mask[lane] = 0u; if (lane == 28) side->any = 0u; }
     __syncthreads();   // barriers initialised by the producer
+#ifdef LK_GEMV_TIMELINE
+    if (tid == 0 && cp.ph[0].tl) { unsigned long long *q_ = cp.ph[0].tl + (size_t)blockIdx.x * LK_CTL_STRIDE; q_[0] = lk_gtime(); q_[1] = (unsigned long long)clock64(); q_[2] = lk_smid(); }
+#endif
     pdl_wait();                // phase 0's activations may be the previous kernel's output
     pdl_launch_dependents();   // the successor waits for this whole grid anyway; let it be scheduled early
     // Grid barrier = one 64-bit arrival counter that only ever grows: every launch adds (nphase - 1) * gridDim.x, so between
@@ -1266,16 +1275,19 @@ __global__ void __launch_bounds__((CHAIN_W + 1) * 32, 1) gemv_chain_kernel(const
 #pragma unroll 1
     for (int ph = 0; ph < cp.nphase; ph++) {
         const GemvParams &p = cp.ph[ph];
+        if (tid == 0) LK_CTL(ph, 0);
         if (ph > 0) {
             // ---- grid barrier: every CTA has stored the previous phase's outputs ----
             asm volatile("bar.sync 1, %0;" ::"r"(NCT) : "memory");
             if (tid == 0) {
+                LK_CTL(ph, 1);
                 red_release_gpu_add(bar_cnt, 1ull);
                 const unsigned long long target = bar_base + (unsigned long long)ph * gridDim.x;
                 unsigned polls = 0;
                 while ((long long)(ld_acquire_gpu(bar_cnt) - target) < 0) {
                     if (++polls > (1u << 22)) { atomicAdd(cp.bar + 2, 1u); break; }   // never hang the device
                 }
+                LK_CTL(ph, 2);
             }
             asm volatile("bar.sync 1, %0;" ::"r"(NCT) : "memory");
         }
@@ -1307,9 +1319,13 @@ __global__ void __launch_bounds__((CHAIN_W + 1) * 32, 1) gemv_chain_kernel(const
             if (lane < GEMV_RED_PAD) red[r * p.red_stride + p.ncw * 8 + lane] = 0.f;
         prep_x<TYPE, NP, true, 1, LK_CHAIN_DETECT>(p, xs, tid, NCT, side);
         asm volatile("bar.sync 1, %0;" ::"r"(NCT) : "memory");   // activation planes (and the padding zeros) written
+        if (tid == 0) LK_CTL(ph, 3);
 
         XRegs<NP> x;
         load_xregs<TYPE, NP>(x, xs, colc);
+#ifdef LK_GEMV_TIMELINE
+        bool first_stage = true;
+#endif
 
         const int rg_words = p.rg * row_words;
         const int rstep = p.rg * p.red_stride;
@@ -1335,6 +1351,9 @@ __global__ void __launch_bounds__((CHAIN_W + 1) * 32, 1) gemv_chain_kernel(const
                 int nr = (working && turn == grp) ? (rows_here - rgi + p.rg - 1) >> p.rg_shift : 0;   // my rows in this stage
                 if (++turn == p.ng) turn = 0;
                 if (working) mbar_wait(&full[s], par);
+#ifdef LK_GEMV_TIMELINE
+                if (first_stage && tid == 0) { LK_CTL(ph, 4); first_stage = false; }
+#endif
                 const uint32_t *wp = (const uint32_t *)(ring + (size_t)s * cp.slot_bytes) + (size_t)rgi * row_words;
                 float *rq = rp;
 #pragma unroll 1
@@ -1370,6 +1389,7 @@ __global__ void __launch_bounds__((CHAIN_W + 1) * 32, 1) gemv_chain_kernel(const
                 rp += (size_t)p.stage_rows * p.red_stride;
                 if (++s == nslots) { s = 0; par ^= 1; }
             }
+            if (tid == 0 && seg + 1 == nseg) LK_CTL(ph, 5);
             if (epi_mode == 1) continue;                // the pair is finished together below
             asm volatile("bar.sync 1, %0;" ::"r"(NCT) : "memory");
             LK_CHAIN_FIXUP(true, p.pro_w, p.pro_mode, NCT, seg == 0 ? p.a : p.a_seg[seg - 1], r_begin + red_base, nrows - red_base, red)
@@ -1388,7 +1408,11 @@ __global__ void __launch_bounds__((CHAIN_W + 1) * 32, 1) gemv_chain_kernel(const
         }
         // re-arm the range flags for the next phase (its prep_x runs after the grid barrier's bar.sync)
         if (warp == 0 && side->any != 0u) { if (lane < 28) side->mask[lane] = 0u; if (lane == 28) side->any = 0u; }
+        if (tid == 0) LK_CTL(ph, 6);
     }
+#ifdef LK_GEMV_TIMELINE
+    if (tid == 0 && cp.ph[0].tl) cp.ph[0].tl[(size_t)blockIdx.x * LK_CTL_STRIDE + 3] = lk_gtime();
+#endif
 }
 
 // ---------------------------------------------------------------------------
@@ -1677,6 +1701,7 @@ cudaError_t launch_gemv_chain(int type, int n, const GemvChainLink *links, const
     cp.slot_bytes = slot_bytes;
     cp.wait_mode = tune.wait_mode == GEMV_WAIT_FULL ? GEMV_WAIT_FULL : GEMV_WAIT_X;
     cp.bar = bar;
+    cp.ph[0].tl = (unsigned long long *)tune.timeline;
     const int smem = stage_off + nslots * slot_bytes;
 
     void (*kern)(const GemvChainParams) = nullptr;

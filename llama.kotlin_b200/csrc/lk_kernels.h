@@ -96,6 +96,15 @@ struct GemvChainLink {
 };
 cudaError_t launch_gemv_chain(int type, int n, const GemvChainLink *links, const GemvTuning &tune, int sm_count,
                               cudaStream_t s, unsigned *bar);
+// K1m (lk_gemv_mma.cu): the same chain with the plane sums on the warp-level int8 MMA (16-row strips, 16 consumer warps
+// on K-slices); Q4_0, K % 256 == 0.  cudaErrorNotSupported for everything else: the caller then takes launch_gemv_chain.
+// bar: the same three words as launch_gemv_chain (the 64-bit counter doubles as the launch's epoch source); mbox: zero-initialised
+// device scratch of GEMV_MCHAIN_MBOX_BYTES owned by the context (activations handed from phase to phase as (value, epoch) pairs).
+constexpr int GEMV_MCHAIN_KMAX = 12288;
+constexpr size_t GEMV_MCHAIN_MBOX_BYTES = 2 * (size_t)GEMV_MCHAIN_KMAX * 8;
+constexpr size_t CHAIN_SCRATCH_BYTES = 256 + GEMV_MCHAIN_MBOX_BYTES;      // the context's chain words, then the mailbox
+cudaError_t launch_gemv_mchain(int type, int n, const GemvChainLink *links, const GemvTuning &tune, int sm_count,
+                               cudaStream_t s, unsigned *bar, void *mbox);
 
 // Generic matmul for any (K, M, N) and a.type in {F32, Q4_0, Q4_1, Q8_0}; reference layouts.
 cudaError_t launch_matmul_generic(int type, const void *a, int64_t K, int64_t M, const float *b, int64_t N,

@@ -37,7 +37,7 @@ lk_status check_async_faults(lk_ctx *ctx) {
         unsigned w[4] = {0, 0, 0, 0};
         if (cudaMemcpy(w, ctx->chain_bar, 16, cudaMemcpyDeviceToHost) != cudaSuccess) return cuda_fail(ctx, cudaGetLastError(), "reading the chain barrier words");
         if (w[2]) {
-            cudaMemset(ctx->chain_bar, 0, 16);   // a timed-out barrier leaves its arrival count behind: re-arm
+            cudaMemset(ctx->chain_bar, 0, lk::CHAIN_SCRATCH_BYTES);   // a timed-out barrier leaves its arrival count behind: re-arm (K1m: and the mailbox epochs)
             ctx->chain_timeouts_seen += w[2];
             return fail(ctx, LK_ECUDA, "chained GEMV: the grid barrier timed out (" + std::to_string(w[2]) +
                         " CTAs gave up): not all CTAs were resident at once; the results of that launch are invalid");
@@ -171,8 +171,9 @@ lk_status lk_ctx_create(int32_t device, lk_ctx **out) {
     LK_CUDA(nullptr, cudaEventCreateWithFlags(&ctx->ev_root, cudaEventDisableTiming));
     // grid-barrier words of the chained GEMV (arrivals, generation, time-outs); allocated here because nothing may be
     // allocated-and-cleared while a launch sequence is being captured
-    LK_CUDA(nullptr, cudaMalloc((void **)&ctx->chain_bar, 16));
-    LK_CUDA(nullptr, cudaMemset(ctx->chain_bar, 0, 16));
+    // ... followed, 256 bytes on, by K1m's mailbox (activations handed from phase to phase, lk_gemv_mma.cu)
+    LK_CUDA(nullptr, cudaMalloc((void **)&ctx->chain_bar, lk::CHAIN_SCRATCH_BYTES));
+    LK_CUDA(nullptr, cudaMemset(ctx->chain_bar, 0, lk::CHAIN_SCRATCH_BYTES));
     *out = ctx;
     return LK_OK;
 }
@@ -799,7 +800,16 @@ lk_status lk_compute_matmul_chain(lk_ctx *ctx, const lk_matmul_link *links, int3
         }
     }
     tune.wait_mode = weight_hazard ? 0 : 1;
-    const cudaError_t e = lk::launch_gemv_chain(L[0].type, n, links_d.data(), tune, ctx->sm_count, ctx->stream, ctx->chain_bar);
+    // K1m first (plane sums on the int8 MMA, hand-offs by mailbox: lk_gemv_mma.cu); what it declines — other types, K % 256 != 0,
+    // phases that share an output tensor — goes to K1c
+    cudaError_t e = cudaErrorNotSupported;
+    if (ctx->chain_mma) {
+        lk::GemvTuning tm = tune;
+        tm.max_stages = 0;
+        e = lk::launch_gemv_mchain(L[0].type, n, links_d.data(), tm, ctx->sm_count, ctx->stream, ctx->chain_bar, (uint8_t *)ctx->chain_bar + 256);
+        if (e == cudaErrorNotSupported) cudaGetLastError(); else if (e == cudaSuccess) ctx->chain_mma_launches++;
+    }
+    if (e == cudaErrorNotSupported) e = lk::launch_gemv_chain(L[0].type, n, links_d.data(), tune, ctx->sm_count, ctx->stream, ctx->chain_bar);
     if (e == cudaErrorNotSupported) {
         cudaGetLastError();
         return fail(ctx, LK_ENOTIMPL, "matmul chain: shapes not supported as one launch");
@@ -1257,6 +1267,7 @@ lk_status lk_set_option(lk_ctx *ctx, const char *name, int64_t v) {
     else if (n == "gemv_ctas_per_sm") ctx->tune.ctas_per_sm = (int)v;
     else if (n == "gemv_overlap") ctx->overlap_mode = (int)v;
     else if (n == "gemv_chain") ctx->chain_mode = v ? 1 : 0;
+    else if (n == "gemv_chain_mma") ctx->chain_mma = v ? 1 : 0;
     else if (n == "gemv_act_planes") ctx->tune.act_planes = (v == 2) ? 2 : 3;
     else if (n == "gemv_bitnet_copies") ctx->tune.bitnet_copies = (v == 1 || v == 2 || v == 4 || v == 8 || v == 16) ? (int)v : 0;
     else if (n == "nibble_order") ctx->tune.nibble_order = v ? 1 : 0;
@@ -1281,11 +1292,13 @@ int64_t lk_get_option(lk_ctx *ctx, const char *name) {
     if (n == "gemv_ctas_per_sm") return ctx->tune.ctas_per_sm;
     if (n == "gemv_overlap") return ctx->overlap_mode;
     if (n == "gemv_chain") return ctx->chain_mode;
+    if (n == "gemv_chain_mma") return ctx->chain_mma;
     if (n == "gemv_chain_launches") return ctx->chain_launches;
+    if (n == "gemv_chain_mma_launches") return ctx->chain_mma_launches;
     if (n == "gemv_chain_timeouts") {   // grid-barrier time-outs since the context was created (0 in a healthy run); reading synchronises
         unsigned w[4] = {0, 0, 0, 0};
         if (cudaStreamSynchronize(ctx->stream) != cudaSuccess || cudaMemcpy(w, ctx->chain_bar, 16, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
-        if (w[2]) cudaMemset(ctx->chain_bar, 0, 16);   // a timed-out barrier leaves its arrival count behind
+        if (w[2]) cudaMemset(ctx->chain_bar, 0, lk::CHAIN_SCRATCH_BYTES);   // a timed-out barrier leaves its arrival count behind
         ctx->chain_unchecked = 0;
         const int64_t seen = ctx->chain_timeouts_seen + (int64_t)w[2];   // incl. those lk_sync already reported
         ctx->chain_timeouts_seen = 0;

@@ -34,6 +34,8 @@ struct lk_ctx {
     uint32_t *chain_bar = nullptr;   // K1c grid barrier: arrivals, generation, time-outs
     int chain_mode = 1;              // 0: lk_compute_matmul_chain declines (the caller issues the links one by one)
     int64_t chain_launches = 0;
+    int chain_mma = 1;               // 1: chains go to K1m (lk_gemv_mma.cu) where it takes them, else to K1c
+    int64_t chain_mma_launches = 0;
     int64_t chain_unchecked = 0;     // chained launches since the time-out word was last read (lk::check_async_faults)
     uint32_t *barrier_flags = nullptr;   // this rank's flag words of lk_peer_barrier (word 14 = time-out), NULL before the first barrier
     uint64_t barrier_flags_bytes = 0;

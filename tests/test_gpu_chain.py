@@ -1,8 +1,10 @@
-"""K1c — a run of dependent decode GEMVs as ONE persistent launch (lk_compute_matmul_chain, lk_gemv.cu
-gemv_chain_kernel): the four launches of LlamaDecoderLayer.forward (model/LlamaModel.kt:253-285) with a grid-wide
-barrier between them.  Checked against the same links issued one by one (bit for bit where no RMSNorm prologue is
-involved: the sum of squares is taken by twice as many threads in the chained kernel, so 1/rms may differ in its last
-bit) and, through the layer graph, against the oracle composition."""
+"""K1c / K1m — a run of dependent decode GEMVs as ONE persistent launch (lk_compute_matmul_chain): the four launches of
+LlamaDecoderLayer.forward (model/LlamaModel.kt:253-285) back to back on one CTA per SM.  K1c (lk_gemv.cu
+gemv_chain_kernel, DP4A plane sums, a grid-wide barrier between phases) is checked against the same links issued one by
+one bit for bit where no RMSNorm prologue is involved.  K1m (lk_gemv_mma.cu, Q4_0 with K % 256 == 0: plane sums on the
+int8 MMA, 16 K-slices per row, activations handed over by mailbox instead of a barrier) sums in a different order, so it
+is checked to F32 rounding against the separate launches and with both halves of the parity statement against the
+oracle."""
 import numpy as np
 import pytest
 
@@ -10,7 +12,9 @@ import llama_kotlin_b200 as lk
 from conftest import same_f32_bits, synth_acts, synth_weights
 from llama_kotlin_b200 import GGMLTensor, GGMLType
 from llama_kotlin_b200.ggml_compute_ops import computeMatMulChain
-from test_gpu_parity import MATMUL_REL_TOL, Q4_0, Q8_0, QT, rel_err
+from test_gpu_parity import MATMUL_REL_TOL, Q4_0, Q8_0, QT, assert_matmul_parity, rel_err
+
+CHAIN_ORDER_TOL = 2e-6      # K1m against the separate launches: same arithmetic, different F32 summation order
 
 pytestmark = pytest.mark.gpu
 BB = {"Q4_0": 18, "Q8_0": 34, "Q4_1": 20}
@@ -25,13 +29,18 @@ def _dev(ga):
     return dev
 
 
+@pytest.mark.parametrize("mma", [1, 0])
 @pytest.mark.parametrize("tname", ["Q4_0", "Q8_0", "Q4_1"])
-@pytest.mark.parametrize("hidden,ffn", [(128, 320), (512, 1408), (4096, 11008)])
-def test_chain_equals_the_links_one_by_one(O, tname, hidden, ffn):
-    """plain -> residual -> gate/up + SwiGLU -> down + residual: four links, every tensor any link writes is bit-identical
-    to what the same four lk_compute_matmul_fused calls store."""
+@pytest.mark.parametrize("hidden,ffn", [(128, 320), (512, 1408), (512, 1536), (1024, 2816), (4096, 11008)])
+def test_chain_equals_the_links_one_by_one(O, tname, hidden, ffn, mma):
+    """plain -> residual -> gate/up + SwiGLU -> down + residual: four links.  K1c: every tensor any link writes is
+    bit-identical to what the same four lk_compute_matmul_fused calls store.  K1m (mma = 1, where it takes the chain):
+    equal to F32 rounding, and the last link's product meets both halves of the parity statement on its own input."""
+    if mma == 0 and (tname != "Q4_0" or hidden % 256 or ffn % 256):
+        pytest.skip("K1c takes this chain in the mma = 1 run already")
     gt, ot = QT[tname]
     be = lk.GGMLCudaBackend(0)
+    be.lk.set_option("gemv_chain_mma", mma)
     wbytes = (2 * hidden * hidden + 3 * hidden * ffn) // 32 * BB[tname]
     ga = lk.GGMLGraphAllocator(be, size=wbytes + 40 * (hidden + ffn) * 4 + (1 << 20))
     dev = _dev(ga)
@@ -62,13 +71,22 @@ def test_chain_equals_the_links_one_by_one(O, tname, hidden, ffn):
             lk.computeMatMul(ga, None, a, b, d)
         else:
             assert lk.computeMatMulFused(ga, None, a, b, d, **kw)
-    n0 = be.lk.get_option("gemv_chain_launches")
+    n0, m0 = be.lk.get_option("gemv_chain_launches"), be.lk.get_option("gemv_chain_mma_launches")
     assert computeMatMulChain(ga, None, links(ch))
     be.lk.sync()
     assert be.lk.get_option("gemv_chain_launches") == n0 + 1
     assert be.lk.get_option("gemv_chain_timeouts") == 0
+    took_mma = be.lk.get_option("gemv_chain_mma_launches") - m0
+    assert took_mma == (1 if (mma and tname == "Q4_0" and hidden % 256 == 0 and ffn % 256 == 0) else 0)
     for k in one:
-        assert same_f32_bits(ga.getFloats(ch[k]), ga.getFloats(one[k])), k
+        if took_mma:
+            assert rel_err(ga.getFloats(ch[k]), ga.getFloats(one[k])) <= CHAIN_ORDER_TOL, k
+        else:
+            assert same_f32_bits(ga.getFloats(ch[k]), ga.getFloats(one[k])), k
+    if took_mma:    # the down projection on the activations the chain itself produced
+        wd = O.quantize(ot, synth_weights(7004, hidden, ffn))
+        got = ga.getFloats(ch["y3"])
+        assert_matmul_parity(O, ot, wd, ffn, hidden, ga.getFloats(ch["h"]), 1, got, tag="K1m down")
     # and the first link against the oracle
     assert rel_err(ga.getFloats(ch["y1"]), O.matmul(ot, O.quantize(ot, synth_weights(7000, hidden, hidden)), hidden, hidden, x0, 1)) <= MATMUL_REL_TOL
     be.free()
@@ -188,6 +206,7 @@ def test_chain_with_the_gemv_warps_option(O, warps, hidden, ffn):
     a phase with no working warp and a producer that spins for ever.  The target is clamped now; a shape that still
     leaves no warp group is declined.  Either way the call returns and the results are the separate launches'."""
     be = lk.GGMLCudaBackend(0)
+    be.lk.set_option("gemv_chain_mma", 0)        # gemv_warps is K1c's option
     ga = lk.GGMLGraphAllocator(be, size=(hidden * hidden + hidden * ffn) // 32 * 18 + 16 * (hidden + ffn) * 4 + (1 << 20))
     dev = _dev(ga)
     W1 = dev(GGMLType.Q4_0, [hidden, hidden], O.quantize(Q4_0, synth_weights(7200, hidden, hidden)))
@@ -206,5 +225,102 @@ def test_chain_with_the_gemv_warps_option(O, warps, hidden, ffn):
     if took:
         assert same_f32_bits(ga.getFloats(c1), ga.getFloats(y1))
         assert same_f32_bits(ga.getFloats(c2), ga.getFloats(y2))
+    assert be.lk.get_option("gemv_chain_timeouts") == 0
+    be.free()
+
+
+def _two_links(O, be, ga, hidden, ffn, x0, seed=7300, nib=0):
+    dev = _dev(ga)
+    w1 = O.quantize(Q4_0, synth_weights(seed, ffn, hidden))
+    w2 = O.quantize(Q4_0, synth_weights(seed + 1, hidden, ffn))
+    W1 = dev(GGMLType.Q4_0, [hidden, ffn], O.repack_nibbles(Q4_0, w1, True) if nib else w1)
+    W2 = dev(GGMLType.Q4_0, [ffn, hidden], O.repack_nibbles(Q4_0, w2, True) if nib else w2)
+    x = dev(GGMLType.F32, [1, hidden], x0)
+    y1 = dev(GGMLType.F32, [1, ffn], np.zeros(ffn, np.float32))
+    y2 = dev(GGMLType.F32, [1, hidden], np.zeros(hidden, np.float32))
+    return (w1, w2), (W1, W2), x, y1, y2
+
+
+def test_mchain_takes_what_it_can_and_declines_the_rest(O):
+    """K1m orders its CTAs by the mailbox alone, so it declines chains in which a tensor the launch writes could be read
+    (or written again) by another CTA: two phases sharing an output, activations that are an older phase's output.  Those
+    go to K1c; either way the results are the oracle's."""
+    hidden, ffn = 512, 1536
+    be = lk.GGMLCudaBackend(0)
+    ga = lk.GGMLGraphAllocator(be, size=8 << 20)
+    x0 = synth_acts(7310, hidden)
+    (w1, w2), (W1, W2), x, y1, y2 = _two_links(O, be, ga, hidden, ffn, x0)
+    m0 = be.lk.get_option("gemv_chain_mma_launches")
+    assert computeMatMulChain(ga, None, [(W1, x, y1, None), (W2, y1, y2, None)])
+    be.lk.sync()
+    assert be.lk.get_option("gemv_chain_mma_launches") == m0 + 1
+    r1 = O.matmul(Q4_0, w1, hidden, ffn, x0, 1)
+    assert_matmul_parity(O, Q4_0, w1, hidden, ffn, x0, 1, ga.getFloats(y1), ref=r1, tag="link 0")
+    assert_matmul_parity(O, Q4_0, w2, ffn, hidden, ga.getFloats(y1), 1, ga.getFloats(y2), tag="link 1")
+    # (a) the third link writes the first link's output tensor again: not for K1m
+    dev = _dev(ga)
+    y3 = dev(GGMLType.F32, [1, hidden], np.zeros(hidden, np.float32))
+    first = ga.getFloats(y2).copy()
+    assert computeMatMulChain(ga, None, [(W1, x, y1, None), (W2, y1, y2, None), (W1, y2, y1, None)])
+    be.lk.sync()
+    assert be.lk.get_option("gemv_chain_mma_launches") == m0 + 1          # K1c took it
+    assert rel_err(ga.getFloats(y2), first) <= CHAIN_ORDER_TOL
+    assert_matmul_parity(O, Q4_0, w1, hidden, ffn, ga.getFloats(y2), 1, ga.getFloats(y1), tag="link 2 via K1c")
+    # (b) the third link multiplies with the FIRST link's output (two phases back): not for K1m either
+    y4 = dev(GGMLType.F32, [1, hidden], np.zeros(hidden, np.float32))
+    assert computeMatMulChain(ga, None, [(W1, x, y1, None), (W2, y1, y2, None), (W2, y1, y4, None)])
+    be.lk.sync()
+    assert be.lk.get_option("gemv_chain_mma_launches") == m0 + 1
+    assert rel_err(ga.getFloats(y4), first) <= CHAIN_ORDER_TOL
+    assert be.lk.get_option("gemv_chain_timeouts") == 0
+    del y3
+    be.free()
+
+
+def test_mchain_many_launches_graph_replays_and_kernel_switches(O):
+    """The mailbox epochs come from the context's monotonic counter, which K1c's barrier advances too: K1m launches,
+    K1c launches in between (gemv_chain_mma toggled) and replays of one captured K1m launch must all give the same answer."""
+    hidden, ffn = 1024, 2816
+    be = lk.GGMLCudaBackend(0)
+    ga = lk.GGMLGraphAllocator(be, size=16 << 20)
+    x0 = synth_acts(7320, hidden)
+    (w1, w2), (W1, W2), x, y1, y2 = _two_links(O, be, ga, hidden, ffn, x0)
+    ls = [(W1, x, y1, None), (W2, y1, y2, None)]
+    assert computeMatMulChain(ga, None, ls)
+    be.lk.sync()
+    ref1, ref2 = ga.getFloats(y1).copy(), ga.getFloats(y2).copy()
+    for i in range(40):
+        be.lk.set_option("gemv_chain_mma", 0 if i % 5 == 4 else 1)
+        ga.setBytes(y1, np.zeros(ffn, np.float32)); ga.setBytes(y2, np.zeros(hidden, np.float32))
+        assert computeMatMulChain(ga, None, ls)
+        be.lk.sync()
+        if i % 5 == 4:
+            assert rel_err(ga.getFloats(y2), ref2) <= CHAIN_ORDER_TOL
+        else:
+            assert same_f32_bits(ga.getFloats(y1), ref1) and same_f32_bits(ga.getFloats(y2), ref2), i
+    be.lk.set_option("gemv_chain_mma", 1)
+    assert be.lk.get_option("gemv_chain_timeouts") == 0
+    be.free()
+
+
+def test_mchain_ggml_nibble_order_and_nonfinite_activations(O):
+    hidden, ffn = 512, 1536
+    be = lk.GGMLCudaBackend(0)
+    be.lk.set_option("nibble_order", 1)
+    ga = lk.GGMLGraphAllocator(be, size=8 << 20)
+    x0 = synth_acts(7330, hidden)
+    (w1, w2), (W1, W2), x, y1, y2 = _two_links(O, be, ga, hidden, ffn, x0, nib=1)
+    m0 = be.lk.get_option("gemv_chain_mma_launches")
+    assert computeMatMulChain(ga, None, [(W1, x, y1, None), (W2, y1, y2, None)])
+    be.lk.sync()
+    assert be.lk.get_option("gemv_chain_mma_launches") == m0 + 1
+    assert_matmul_parity(O, Q4_0, w1, hidden, ffn, x0, 1, ga.getFloats(y1), tag="ggml order, link 0")
+    assert_matmul_parity(O, Q4_0, w2, ffn, hidden, ga.getFloats(y1), 1, ga.getFloats(y2), tag="ggml order, link 1")
+    # a NaN and an inf among the activations: every output that touches them is non-finite, like the reference's
+    xb = x0.copy(); xb[5] = np.nan; xb[300] = np.inf
+    ga.setBytes(x, xb)
+    assert computeMatMulChain(ga, None, [(W1, x, y1, None), (W2, y1, y2, None)])
+    be.lk.sync()
+    assert not np.any(np.isfinite(ga.getFloats(y1))) and not np.any(np.isfinite(ga.getFloats(y2)))
     assert be.lk.get_option("gemv_chain_timeouts") == 0
     be.free()

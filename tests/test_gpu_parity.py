@@ -1221,7 +1221,7 @@ def test_gemv_range_fixup_in_fused_and_chained_launches(O, tname):
     if computeMatMulChain(ga2, None, [(ta, tn, d0c, dict(norm_x=tx, norm_w=tg, eps=1e-6, extra=[(tb, d1c)], mul_dst=dmc)),
                                       (td, dmc_col, y, None)]):
         h = ga2.getFloats(dmc)
-        assert rel_err(h, ga2.getFloats(dm)) <= 1e-6          # 1/rms may differ in its last bit between the two kernels
+        assert rel_err(h, ga2.getFloats(dm)) <= 2e-6          # K1m (Q4_0) sums 16 K-slices and applies 1/rms to the finished row sums
         assert rel_err(ga2.getFloats(y), O.matmul(ot, wd, M, K, h, 1, nthreads=4)) <= MATMUL_REL_TOL
         assert be.lk.get_option("gemv_chain_timeouts") == 0
     be.free()
