@@ -46,9 +46,9 @@ constexpr int MC_XB = 96;               // bytes of activation planes per block:
 constexpr int MC_MASK_WORDS = 12;       // range flags: K <= 12288
 constexpr int MC_KMAX = GEMV_MCHAIN_KMAX;   // longest activation vector a mailbox buffer holds
 
-// header layout (bytes): 0 full[8] | 64 empty[8] | 128 stage_off[8] | 160 any | 164 rinv | 168 mask[12] | 224 zero[4] |
-//                        216 epoch base | 256 rms partials[16] | 384 producer queue: start[8], end[8]
-constexpr int MC_OFF_STAGE = 128, MC_OFF_ANY = 160, MC_OFF_RINV = 164, MC_OFF_MASK = 168, MC_OFF_EPOCH = 216, MC_OFF_ZERO = 224, MC_OFF_RMS = 256, MC_OFF_QUEUE = 384;
+// header layout (bytes): 0 full[8] | 64 empty[8] | 128 stage_off[8] | 160 any[2] | 168 epoch base | 176 zero[4] |
+//                        192 mask[2][12] | 288 sum-of-squares partials[2][16]       ([2]: by phase parity, see mc_prep_warp)
+constexpr int MC_OFF_STAGE = 128, MC_OFF_ANY = 160, MC_OFF_EPOCH = 168, MC_OFF_ZERO = 176, MC_OFF_MASK = 192, MC_OFF_RMS = 288;
 
 struct MPhase {
     const uint8_t *a[3];       // weight segments (identical shape), 16-byte aligned
@@ -59,7 +59,7 @@ struct MPhase {
     const float *residual;     // dst = residual + a x b
     float *dst_raw;            // optional: the bare product
     float *epi_act, *epi_out;  // epi_mode 1: silu(seg 0), silu(seg 0) * seg 1
-    float pro_eps;
+    float pro_eps, inv_k;      // inv_k = 1 / K
     int pro_mode, epi_mode, nseg;
     int K, M, nblk, row_bytes;
     int stride;                // shared-memory row stride (bytes) of a staged row chunk: >= its bytes, = 16 mod 32
@@ -75,7 +75,7 @@ struct MChainParams {
     MPhase ph[MC_MAX];
     int nphase;
     int wait_mode;
-    int part_off, x_off, sc_off, ring_off, ring_bytes;
+    int part_off, part_floats, x_off, sc_off, ring_off, ring_bytes;     // two partial-sum buffers of part_floats each (by phase parity)
     int inflight;              // stages the producer keeps in flight (issued, not landed); the ring holds more, landed ones
     unsigned *bar;             // words 0-1: the context's monotonic 64-bit launch / arrival counter (shared with K1c), word 2: time-outs
     uint2 *mbox;               // mailbox: 2 x MC_KMAX (value bits, epoch) pairs
@@ -156,6 +156,11 @@ __device__ __forceinline__ float mc_silu(float x) { return __fmul_rn(x, __fdiv_r
 __device__ __forceinline__ void mc_st_pair(uint2 *q, float v, uint32_t epoch) {
     asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(q), "r"(__float_as_uint(v)), "r"(epoch) : "memory");
 }
+__device__ __forceinline__ uint2 mc_ld_pair(const uint2 *q) {
+    uint2 v;
+    asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(q) : "memory");
+    return v;
+}
 __device__ __forceinline__ uint4 mc_ld_pairs(const uint2 *q) {       // two pairs
     uint4 v;
     asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(q) : "memory");
@@ -192,126 +197,141 @@ __device__ __forceinline__ void mc_load8(const MPhase &p, const uint2 *mb, uint3
 //   Q4, ggml order   (byte j = elements j, j+16):   [e0..e3 | e16..e19 | e4..e7 | e20..e23] + 8 h
 //   Q8_0:                                           [e0..e3 | e4..e7 | e8..e11 | e12..e15] + 16 h
 // Table entry of block b (16 bytes at sc + 16 b): s, c * s * sumT, 65536 s, 0  (c = -8 for Q4_0, else 1).
+// One round: the eight activations v of task `task` (block task >> 2, quarter task & 3; the four lanes of a block are adjacent)
 template <int TYPE>
-__device__ __forceinline__ void mc_prep(const MPhase &p, uint8_t *smem, const MChainParams &cp, int tid, const uint2 *mb, uint32_t epoch, int ph) {
-    const int ntasks = p.nblk * 4;
+__device__ __forceinline__ void mc_convert8(const MPhase &p, uint8_t *xs, float4 *sc, uint32_t *mask, uint32_t *any, int lane, int task, bool on, const float (&v)[8]) {
+    // max |v| over the block with NaN propagation: a NaN or inf element leaves exponent 255
+    float amax = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; i += 2) amax = mc_fmax3_nan_abs(amax, v[i], v[i + 1]);
+    uint32_t ab = __float_as_uint(amax) & 0x7FFFFFFFu;
+    ab = max(ab, __shfl_xor_sync(0xffffffffu, ab, 1));
+    ab = max(ab, __shfl_xor_sync(0xffffffffu, ab, 2));
+    int e = (int)(ab >> 23);
+    const bool nonfinite = e == 255;
+    {   // range check (lk_gemv.cu GemvSide): the block's smallest non-zero |x| below 2^-fix_gap of its maximum -> flag
+        float amin = __uint_as_float(0x7F800000u);
+#pragma unroll
+        for (int i = 0; i < 8; i += 2) amin = mc_fmin3_abs(amin, v[i], v[i + 1]);
+        uint32_t mb = __float_as_uint(amin);
+        mb = min(mb, __shfl_xor_sync(0xffffffffu, mb, 1));
+        mb = min(mb, __shfl_xor_sync(0xffffffffu, mb, 2));
+        if ((int)(mb >> 23) + p.fix_gap < e && !nonfinite) {     // all four lanes of the block branch alike
+            uint32_t mn = 0xFFFFFFFFu;
+#pragma unroll
+            for (int i = 0; i < 8; i++) mn = min(mn, __float_as_uint(v[i]) * 2u - 1u);    // +-0 wraps to 0xFFFFFFFF
+            const unsigned quad = 0xFu << (lane & ~3);
+            mn = min(mn, __shfl_xor_sync(quad, mn, 1));
+            mn = min(mn, __shfl_xor_sync(quad, mn, 2));
+            const uint32_t t = mn + 1u;
+            if (on && (task & 3) == 0 && t != 0u && (int)(t >> 24) + p.fix_gap < e) {
+                atomicOr(&mask[task >> 7], 1u << ((task >> 2) & 31));
+                *(volatile uint32_t *)any = 1u;
+            }
+        }
+    }
+    e = e < 24 ? 24 : e;
+    const float c = nonfinite ? 0.f : __uint_as_float((uint32_t)(253 + 22 - e) << 23);
+    const float s = nonfinite ? __uint_as_float(0x7FC00000u) : __uint_as_float((uint32_t)(e + 1 - 22) << 23);
+    int T[8];
+    int sumT = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        const int t = (int)__float_as_uint(fmaf(v[i], c, 12582912.0f)) - 0x4B400000;
+        sumT += t;
+        T[i] = t + 0x8080;
+    }
+    sumT += __shfl_xor_sync(0xffffffffu, sumT, 1);
+    sumT += __shfl_xor_sync(0xffffffffu, sumT, 2);
+    if (on) {
+        const int blk = task >> 2, q = task & 3;
+        uint8_t *slot = xs + (size_t)blk * MC_XB;
+#pragma unroll
+        for (int pl = 0; pl < 3; pl++) {
+            const uint32_t s2 = 0x0040u + 0x0011u * pl;       // byte pl of a, byte pl of b
+            const uint32_t flip = pl < 2 ? 0x80808080u : 0u;
+            uint32_t w0, w1;
+            if (TYPE == T_Q8_0 || p.nib) {                      // consecutive elements per word
+                w0 = __byte_perm(__byte_perm(T[0], T[1], s2), __byte_perm(T[2], T[3], s2), 0x5410) ^ flip;
+                w1 = __byte_perm(__byte_perm(T[4], T[5], s2), __byte_perm(T[6], T[7], s2), 0x5410) ^ flip;
+            } else {                                            // even elements, odd elements
+                w0 = __byte_perm(__byte_perm(T[0], T[2], s2), __byte_perm(T[4], T[6], s2), 0x5410) ^ flip;
+                w1 = __byte_perm(__byte_perm(T[1], T[3], s2), __byte_perm(T[5], T[7], s2), 0x5410) ^ flip;
+            }
+            if (TYPE != T_Q8_0 && p.nib) {                      // ggml order: elements 8q.. sit in half q & 1, words (q >> 1) and (q >> 1) + 2
+                uint32_t *d = (uint32_t *)(slot + pl * 32 + (q & 1) * 16 + (q >> 1) * 4);
+                d[0] = w0; d[2] = w1;
+            } else {
+                *(uint2 *)(slot + pl * 32 + (q >> 1) * 16 + (q & 1) * 8) = make_uint2(w0, w1);
+            }
+        }
+        if (q == 0) sc[blk] = make_float4(s, (TYPE == T_Q4_0 ? -8.0f : 1.0f) * s * (float)sumT, 65536.0f * s, 0.f);
+    }
+}
+
+// Every consumer warp converts the activations of ITS OWN K-slices (tasks [t0, t0 + n0) and [t1, t1 + n1), at most 96 = three
+// rounds of 32 lanes) and nobody else reads them in the stage loop, so a warp starts multiplying as soon as its own slice of
+// the mailbox has arrived: no CTA-wide barrier between the hand-off and the first MMA, and a late CTA of the previous phase
+// holds up only the warps whose slice it produces.  Everything a phase leaves in the header for its epilogue (range flags,
+// sum-of-squares partials) and the partial-sum buffer are double-buffered by phase parity, because a fast warp is already in
+// phase i + 1 while the epilogue threads of phase i still read them.
+// RMSNorm prologue (pro_mode 1) WITHOUT 1/rms on the hand-off's critical path: the planes are built from y = x * gain, the
+// sum of squares is taken on the side, and the positive scalar 1/rms multiplies the finished row sums in the epilogue
+// (dst = 1/rms * sum_k w_k y_k).  The first version normalised before converting: load -> sum -> shuffle tree -> barrier ->
+// 16 partials -> div, sqrt, div -> 16 multiplies in front of every conversion, 2.2 us of a 5 us hand-off even on an idle
+// memory system (profiles/r02i_mchain_small_shapes.txt).  Costs one more rounding per output (<= 2^-24 relative).
+template <int TYPE>
+__device__ __forceinline__ void mc_prep_warp(const MPhase &p, uint8_t *smem, const MChainParams &cp, int lane, int warp, const uint2 *mb, uint32_t epoch, int ph,
+                                             int t0, int n0, int t1, int n1) {
     uint8_t *xs = smem + cp.x_off;
     float4 *sc = (float4 *)(smem + cp.sc_off);
-    uint32_t *mask = (uint32_t *)(smem + MC_OFF_MASK);
-    // RMSNorm prologue (pro_mode 1) WITHOUT 1/rms on the hand-off's critical path: the planes are built from y = x * gain, the
-    // sum of squares is taken on the side, and the positive scalar 1/rms multiplies the finished row sums in the epilogue
-    // (dst = 1/rms * sum_k w_k y_k).  The first version normalised before converting: load -> sum -> shuffle tree -> barrier ->
-    // 16 partials -> div, sqrt, div -> 16 multiplies in front of every conversion, 2.2 us of a 5 us hand-off even on an idle
-    // memory system (profiles/r02i_mchain_small_shapes.txt).  Costs one more rounding per output (<= 2^-24 relative).
+    const int par = ph & 1;
+    uint32_t *mask = (uint32_t *)(smem + MC_OFF_MASK) + par * MC_MASK_WORDS;
+    uint32_t *any = (uint32_t *)(smem + MC_OFF_ANY) + par;
     const bool norm = p.pro_mode == 1;
-    float v[8];
+    const bool gain = norm && p.pro_w != nullptr;
+    const int nt = n0 + n1;
     float ssq = 0.f;
 #pragma unroll 1
-    for (int base = 0; base < ntasks; base += MC_NCT) {
-        const int task = base + tid;
-        const bool on = task < ntasks;
+    for (int r = 0; 32 * r < nt; r++) {               // K = 4096: one round; K = 11008: three (one L2 round trip each)
+        const int i = 32 * r + lane;
+        const bool on = i < nt;
+        const int task = i < n0 ? t0 + i : t1 + (i - n0);
+        float v[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) v[k] = 0.f;
+        float4 g0 = make_float4(1.f, 1.f, 1.f, 1.f), g1 = g0;
         if (on) {
-            float4 g0 = make_float4(1.f, 1.f, 1.f, 1.f), g1 = g0;
-            const bool gain = norm && p.pro_w != nullptr;
             if (gain) { const float4 *ws = (const float4 *)(p.pro_w + (size_t)task * 8); g0 = __ldcg(ws); g1 = __ldcg(ws + 1); }
             mc_load8(p, mb, epoch, cp.bar + 2, task, v);
+        }
 #ifdef LK_GEMV_TIMELINE
-            if (tid == 0 && base == 0) { if (v[0] + v[3] == 12345.f) xs[0] = 1; MC_TL(ph, 1); }      // first activations loaded
+        if (threadIdx.x == 0 && r == 0) { if (v[0] + v[3] == 12345.f) xs[0] = 1; MC_TL(ph, 1); }      // first activations loaded
 #endif
-            if (norm) {
+        if (norm) {
 #pragma unroll
-                for (int i = 0; i < 8; i++) ssq = fmaf(v[i], v[i], ssq);
-                if (gain) {
-                    v[0] = __fmul_rn(v[0], g0.x); v[1] = __fmul_rn(v[1], g0.y); v[2] = __fmul_rn(v[2], g0.z); v[3] = __fmul_rn(v[3], g0.w);
-                    v[4] = __fmul_rn(v[4], g1.x); v[5] = __fmul_rn(v[5], g1.y); v[6] = __fmul_rn(v[6], g1.z); v[7] = __fmul_rn(v[7], g1.w);
-                }
-            }
-        } else {
-#pragma unroll
-            for (int i = 0; i < 8; i++) v[i] = 0.f;
-        }
-        // max |v| over the block with NaN propagation: a NaN or inf element leaves exponent 255
-        float amax = 0.f;
-#pragma unroll
-        for (int i = 0; i < 8; i += 2) amax = mc_fmax3_nan_abs(amax, v[i], v[i + 1]);
-        uint32_t ab = __float_as_uint(amax) & 0x7FFFFFFFu;
-        ab = max(ab, __shfl_xor_sync(0xffffffffu, ab, 1));
-        ab = max(ab, __shfl_xor_sync(0xffffffffu, ab, 2));
-        int e = (int)(ab >> 23);
-        const bool nonfinite = e == 255;
-        {   // range check (lk_gemv.cu GemvSide): the block's smallest non-zero |x| below 2^-fix_gap of its maximum -> flag
-            float amin = __uint_as_float(0x7F800000u);
-#pragma unroll
-            for (int i = 0; i < 8; i += 2) amin = mc_fmin3_abs(amin, v[i], v[i + 1]);
-            uint32_t mb = __float_as_uint(amin);
-            mb = min(mb, __shfl_xor_sync(0xffffffffu, mb, 1));
-            mb = min(mb, __shfl_xor_sync(0xffffffffu, mb, 2));
-            if ((int)(mb >> 23) + p.fix_gap < e && !nonfinite) {     // all four lanes of the block branch alike
-                uint32_t mn = 0xFFFFFFFFu;
-#pragma unroll
-                for (int i = 0; i < 8; i++) mn = min(mn, __float_as_uint(v[i]) * 2u - 1u);    // +-0 wraps to 0xFFFFFFFF
-                const unsigned quad = 0xFu << ((tid & 31) & ~3);
-                mn = min(mn, __shfl_xor_sync(quad, mn, 1));
-                mn = min(mn, __shfl_xor_sync(quad, mn, 2));
-                const uint32_t t = mn + 1u;
-                if (on && (task & 3) == 0 && t != 0u && (int)(t >> 24) + p.fix_gap < e) {
-                    atomicOr(&mask[task >> 7], 1u << ((task >> 2) & 31));
-                    *(volatile uint32_t *)(smem + MC_OFF_ANY) = 1u;
-                }
+            for (int k = 0; k < 8; k++) ssq = fmaf(v[k], v[k], ssq);
+            if (gain) {
+                v[0] = __fmul_rn(v[0], g0.x); v[1] = __fmul_rn(v[1], g0.y); v[2] = __fmul_rn(v[2], g0.z); v[3] = __fmul_rn(v[3], g0.w);
+                v[4] = __fmul_rn(v[4], g1.x); v[5] = __fmul_rn(v[5], g1.y); v[6] = __fmul_rn(v[6], g1.z); v[7] = __fmul_rn(v[7], g1.w);
             }
         }
-        e = e < 24 ? 24 : e;
-        const float c = nonfinite ? 0.f : __uint_as_float((uint32_t)(253 + 22 - e) << 23);
-        const float s = nonfinite ? __uint_as_float(0x7FC00000u) : __uint_as_float((uint32_t)(e + 1 - 22) << 23);
-        int T[8];
-        int sumT = 0;
-#pragma unroll
-        for (int i = 0; i < 8; i++) {
-            const int t = (int)__float_as_uint(fmaf(v[i], c, 12582912.0f)) - 0x4B400000;
-            sumT += t;
-            T[i] = t + 0x8080;
-        }
-        sumT += __shfl_xor_sync(0xffffffffu, sumT, 1);
-        sumT += __shfl_xor_sync(0xffffffffu, sumT, 2);
-        if (on) {
-            const int blk = task >> 2, q = task & 3;
-            uint8_t *slot = xs + (size_t)blk * MC_XB;
-#pragma unroll
-            for (int pl = 0; pl < 3; pl++) {
-                const uint32_t s2 = 0x0040u + 0x0011u * pl;       // byte pl of a, byte pl of b
-                const uint32_t flip = pl < 2 ? 0x80808080u : 0u;
-                uint32_t w0, w1;
-                if (TYPE == T_Q8_0 || p.nib) {                      // consecutive elements per word
-                    w0 = __byte_perm(__byte_perm(T[0], T[1], s2), __byte_perm(T[2], T[3], s2), 0x5410) ^ flip;
-                    w1 = __byte_perm(__byte_perm(T[4], T[5], s2), __byte_perm(T[6], T[7], s2), 0x5410) ^ flip;
-                } else {                                            // even elements, odd elements
-                    w0 = __byte_perm(__byte_perm(T[0], T[2], s2), __byte_perm(T[4], T[6], s2), 0x5410) ^ flip;
-                    w1 = __byte_perm(__byte_perm(T[1], T[3], s2), __byte_perm(T[5], T[7], s2), 0x5410) ^ flip;
-                }
-                if (TYPE != T_Q8_0 && p.nib) {                      // ggml order: elements 8q.. sit in half q & 1, words (q >> 1) and (q >> 1) + 2
-                    uint32_t *d = (uint32_t *)(slot + pl * 32 + (q & 1) * 16 + (q >> 1) * 4);
-                    d[0] = w0; d[2] = w1;
-                } else {
-                    *(uint2 *)(slot + pl * 32 + (q >> 1) * 16 + (q & 1) * 8) = make_uint2(w0, w1);
-                }
-            }
-            if (q == 0) sc[blk] = make_float4(s, (TYPE == T_Q4_0 ? -8.0f : 1.0f) * s * (float)sumT, 65536.0f * s, 0.f);
-        }
+        mc_convert8<TYPE>(p, xs, sc, mask, any, lane, task, on, v);
     }
     if (norm) {
         ssq = warp_sum(ssq);
-        if ((tid & 31) == 0) ((float *)(smem + MC_OFF_RMS))[tid >> 5] = ssq;     // summed by one thread after the caller's barrier
+        if (lane == 0) ((float *)(smem + MC_OFF_RMS))[par * MC_W + warp] = ssq;     // summed in the epilogue
     }
+    __syncwarp();
 }
 
 // ---- cold path of the range fix-up: sum_k w(i, k) * r_k, r_k = x_k - T_k s, for the flagged blocks of this CTA's rows,
 // into fix-up column j = (rank of the block among the flagged ones) & 7 of the row's partial sums (lk_gemv.cu gemv_fixup_body)
 template <int TYPE>
-__device__ __noinline__ void mc_fixup(const MPhase *pp, const MChainParams *cpp, uint8_t *smem, int r_begin, int nrows, const uint2 *mb) {
+__device__ __noinline__ void mc_fixup(const MPhase *pp, const MChainParams *cpp, uint8_t *smem, int r_begin, int nrows, const uint2 *mb, int par, float *part) {
     const MPhase &p = *pp;
     const float4 *sc = (const float4 *)(smem + cpp->sc_off);
-    const uint32_t *mask = (const uint32_t *)(smem + MC_OFF_MASK);
-    float *part = (float *)(smem + cpp->part_off);
+    const uint32_t *mask = (const uint32_t *)(smem + MC_OFF_MASK) + par * MC_MASK_WORDS;
     const int nw = (p.nblk + 31) >> 5;
     constexpr int BB = block_bytes(TYPE);
     constexpr int QOFF = TYPE == T_Q4_1 ? 4 : 2;
@@ -511,8 +531,8 @@ __global__ void __launch_bounds__((MC_W + MC_PW) * 32, 1) gemv_mchain_kernel(con
     }
 
     // ===== consumer warps =====
-    if (tid < MC_MASK_WORDS) ((uint32_t *)(smem + MC_OFF_MASK))[tid] = 0u;
-    if (tid == MC_MASK_WORDS) *(uint32_t *)(smem + MC_OFF_ANY) = 0u;
+    if (tid < 2 * MC_MASK_WORDS) ((uint32_t *)(smem + MC_OFF_MASK))[tid] = 0u;
+    if (tid < 2) ((uint32_t *)(smem + MC_OFF_ANY))[tid] = 0u;
     __syncthreads();   // barriers initialised by the producer
 #ifdef LK_GEMV_TIMELINE
     if (tid == 0 && cp.tl) {
@@ -534,7 +554,16 @@ __global__ void __launch_bounds__((MC_W + MC_PW) * 32, 1) gemv_mchain_kernel(con
     const int bj = t >> 1, bh = t & 1;                     // A side: block of the pair, half of the block
     // B side: column n = lane >> 2 = 4 jc + plane, k-slots of lane t belong to block t >> 1: only matching lanes hold non-zero bytes
     const bool b_nz = (g & 3) < 3 && (g >> 2) == bj;
-    float *part = (float *)(smem + cp.part_off);
+    constexpr int BB = block_bytes(TYPE);
+    constexpr int QOFF = TYPE == T_Q4_1 ? 4 : 2;
+    // first quant byte of this lane within the pair, aligned down to a word; PRMT selector for the realignment
+    const int qbyte = bj * BB + QOFF + bh * (TYPE == T_Q8_0 ? 16 : 8);
+    const uint32_t sel = (qbyte & 2) ? 0x5432u : 0x3210u;
+    const uint32_t a_lane = (uint32_t)(qbyte & ~3), d_lane = (uint32_t)(bj * BB);       // + pair offset within the staged chunk
+    const uint32_t xb_lane = b_nz ? smem_base + cp.x_off + (uint32_t)(bj * MC_XB + (g & 3) * 32 + bh * 16) : smem_base + MC_OFF_ZERO;
+    const uint32_t bstep = b_nz ? 2u * MC_XB : 0u;
+    const uint32_t sc_lane = smem_base + cp.sc_off + (uint32_t)(bj * 16 + bh * 8);
+    const uint32_t ring_base = smem_base + cp.ring_off;
     int si = 0;
 #pragma unroll 1
     for (int ph = 0; ph < cp.nphase; ph++) {
@@ -545,49 +574,33 @@ __global__ void __launch_bounds__((MC_W + MC_PW) * 32, 1) gemv_mchain_kernel(con
             const int t0 = q[0], t1 = q[16], t2 = q[32];
             asm volatile("" ::"r"(t0), "r"(t1), "r"(t2));
         }
+        const int par = ph & 1;
         const int r_begin = p.rows_per_cta * bid + min(bid, p.rows_rem);
         const int nrows = p.rows_per_cta + (bid < p.rows_rem ? 1 : 0);
-        const uint2 *mb = cp.mbox + (size_t)(ph & 1) * MC_KMAX;          // this phase's activations, if they come by mailbox
+        const uint2 *mb = cp.mbox + (size_t)par * MC_KMAX;          // this phase's activations, if they come by mailbox
         const uint32_t epoch = epoch0 + (uint32_t)ph + 1u;
-        mc_prep<TYPE>(p, smem, cp, tid, mb, epoch, ph);
-        asm volatile("bar.sync 1, %0;" ::"r"(MC_NCT) : "memory");   // planes and table written
-        if (tid == 0) MC_TL(ph, 3);
         const bool norm = p.pro_mode == 1;
-        if (norm && tid == 33) {     // 1/rms, off the critical path: read again only after the stage loop's closing barrier
-            const float *q = (const float *)(smem + MC_OFF_RMS);
-            float tot = 0.f;
-#pragma unroll
-            for (int w = 0; w < MC_W; w++) tot += q[w];
-            *(volatile float *)(smem + MC_OFF_RINV) = 1.0f / sqrtf(tot / (float)p.K + p.pro_eps);
-        }
-        // this CTA's 1/grid slice of the normalised activations (the unfused RMSNorm node's tensor): operands fetched now, stored in the epilogue
-        float bo_x = 0.f, bo_g = 1.f;
-        const int bo_per = (p.K + (int)gridDim.x - 1) / (int)gridDim.x;
-        const int bo_k = bid * bo_per + tid;
-        const bool bo_on = norm && p.b_out && tid < bo_per && bo_k < p.K;
-        if (bo_on) {
-            bo_x = p.from_mbox ? __uint_as_float(((const volatile uint2 *)mb)[bo_k].x) : __ldcg(p.b + bo_k);
-            if (p.pro_w) bo_g = __ldcg(p.pro_w + bo_k);
-        }
-        // the residual of this thread's output row, fetched now so that its L2 latency is not part of the epilogue
-        float res_pre = 0.f;
-        if (p.residual && tid < nrows) res_pre = __ldcg(p.residual + r_begin + tid);
-
         // this warp's K-slice of each column chunk: block pairs [pw0, pw0 + np0) of chunk 0, [pw1, pw1 + np1) of chunk 1
-        constexpr int BB = block_bytes(TYPE);
-        constexpr int QOFF = TYPE == T_Q4_1 ? 4 : 2;
         const int nbp = p.nblk >> 1, c0 = p.c0, nchunk = p.nchunk, stride = p.stride, sr = p.sr, nseg = p.nseg, rows_max = p.rows_max;
         const int pw0 = (warp * c0) / MC_W, np0 = ((warp + 1) * c0) / MC_W - pw0;
         const int c1n = nbp - c0;
         const int pw1 = c0 + (warp * c1n) / MC_W, np1 = c0 + ((warp + 1) * c1n) / MC_W - pw1;
-        // first quant byte of this lane within the pair, aligned down to a word; PRMT selector for the realignment
-        const int qbyte = bj * BB + QOFF + bh * (TYPE == T_Q8_0 ? 16 : 8);
-        const uint32_t sel = (qbyte & 2) ? 0x5432u : 0x3210u;
-        const uint32_t a_lane = (uint32_t)(qbyte & ~3), d_lane = (uint32_t)(bj * BB);       // + pair offset within the staged chunk
-        const uint32_t xb_lane = b_nz ? smem_base + cp.x_off + (uint32_t)(bj * MC_XB + (g & 3) * 32 + bh * 16) : smem_base + MC_OFF_ZERO;
-        const uint32_t bstep = b_nz ? 2u * MC_XB : 0u;
-        const uint32_t sc_lane = smem_base + cp.sc_off + (uint32_t)(bj * 16 + bh * 8);
-        const uint32_t ring_base = smem_base + cp.ring_off;
+        // side loads whose latency hides under the stage loop: the residual of this thread's output row, and this CTA's 1/grid
+        // slice of the normalised activations (the unfused RMSNorm node's tensor, stored in the epilogue)
+        float res_pre = 0.f;
+        if (p.residual && tid < nrows) res_pre = __ldcg(p.residual + r_begin + tid);
+        float bo_g = 1.f;
+        uint2 bo_x = make_uint2(0u, epoch);
+        const int bo_per = (p.K + (int)gridDim.x - 1) / (int)gridDim.x;
+        const int bo_k = bid * bo_per + tid;
+        const bool bo_on = norm && p.b_out && tid < bo_per && bo_k < p.K;
+        if (bo_on) {
+            if (p.from_mbox) bo_x = mc_ld_pair(mb + bo_k); else bo_x.x = __float_as_uint(__ldcg(p.b + bo_k));
+            if (p.pro_w) bo_g = __ldcg(p.pro_w + bo_k);
+        }
+        // activations of this warp's slices -> planes + table (no CTA barrier: see mc_prep_warp)
+        mc_prep_warp<TYPE>(p, smem, cp, lane, warp, mb, epoch, ph, 8 * pw0, 8 * np0, 8 * pw1, 8 * np1);
+        if (tid == 0) MC_TL(ph, 3);
         // K = 4096: four pairs per warp, B fragments and table entries stay in registers for the phase
         const bool res4 = nchunk == 1 && nbp == 4 * MC_W;
         uint4 breg[4];
@@ -602,6 +615,7 @@ __global__ void __launch_bounds__((MC_W + MC_PW) * 32, 1) gemv_mchain_kernel(con
 #ifdef LK_GEMV_TIMELINE
         bool first_stage = true;
 #endif
+        float *part = (float *)(smem + cp.part_off) + (size_t)par * cp.part_floats;     // by phase parity (see mc_prep_warp)
         float *pr_lane = part + (size_t)g * MC_PS + warp;      // this lane's partial-sum slot of strip row g
 #pragma unroll 1
         for (int seg = 0; seg < nseg; seg++) {
@@ -648,15 +662,28 @@ __global__ void __launch_bounds__((MC_W + MC_PW) * 32, 1) gemv_mchain_kernel(con
                 }
             }
         }
+        if (bo_on && bo_x.y != epoch) {     // the slice element had not arrived when it was fetched before the loop: poll it now
+            const long long t0 = clock64();
+            do { bo_x = mc_ld_pair(mb + bo_k); } while (bo_x.y != epoch && clock64() - t0 < 2000000000ll);
+        }
         if (tid == 0) MC_TL(ph, 5);
-        asm volatile("bar.sync 1, %0;" ::"r"(MC_NCT) : "memory");   // every K-slice of every row is parked
-        const bool flagged = *(volatile uint32_t *)(smem + MC_OFF_ANY) != 0u;
+        asm volatile("bar.sync 1, %0;" ::"r"(MC_NCT) : "memory");   // every K-slice of every row is parked (and every warp has converted its activations)
+        const bool flagged = ((volatile uint32_t *)(smem + MC_OFF_ANY))[par] != 0u;
         if (__builtin_expect(flagged, 0)) {
-            mc_fixup<TYPE>(&p, &cp, smem, r_begin, nrows, mb);
+            mc_fixup<TYPE>(&p, &cp, smem, r_begin, nrows, mb, par, part);
             asm volatile("bar.sync 1, %0;" ::"r"(MC_NCT) : "memory");
+            // re-arm this parity's flags: the next phase uses the other set, the one after it starts behind another CTA barrier
+            if (tid < MC_MASK_WORDS) ((uint32_t *)(smem + MC_OFF_MASK))[par * MC_MASK_WORDS + tid] = 0u;
+            if (tid == MC_MASK_WORDS) ((uint32_t *)(smem + MC_OFF_ANY))[par] = 0u;
         }
         // ---- fixed-order reduction over the K-slices + epilogue, one thread per output ----
-        const float rinv = norm ? *(volatile float *)(smem + MC_OFF_RINV) : 1.0f;
+        float rinv = 1.0f;
+        if (norm && (tid < nseg * nrows || bo_on)) {      // 1/rms from the warps' sums of squares (MUFU.RSQ: <= 2 ulp)
+            const float *q = (const float *)(smem + MC_OFF_RMS) + par * MC_W;
+            float tot = ((q[0] + q[1]) + (q[2] + q[3])) + ((q[4] + q[5]) + (q[6] + q[7]));
+            tot += ((q[8] + q[9]) + (q[10] + q[11])) + ((q[12] + q[13]) + (q[14] + q[15]));
+            rinv = rsqrtf(fmaf(tot, p.inv_k, p.pro_eps));
+        }
         auto rowsum = [&](int prow) {
             const float *q = part + (size_t)prow * MC_PS;
             float v = ((q[0] + q[1]) + (q[2] + q[3])) + ((q[4] + q[5]) + (q[6] + q[7]));
@@ -669,35 +696,31 @@ __global__ void __launch_bounds__((MC_W + MC_PW) * 32, 1) gemv_mchain_kernel(con
         if (p.epi_mode == 1) {
             // gate/up pair (SwiGLU, LlamaMLP.forward model/LlamaModel.kt:159-176) with the elementwise kernels' roundings
             for (int r = tid; r < nrows; r += MC_NCT) {
-                const float gv = rowsum(r), uv = rowsum(p.rows_max + r);
+                const float gv = rowsum(r), uv = rowsum(rows_max + r);
                 const int64_t o = r_begin + r;
                 const float act = mc_silu(gv);
+                const float hv = __fmul_rn(act, uv);
+                if (feed == 4) mc_st_pair(mb_next + o, hv, epoch + 1u);      // first: the next phase waits for this store
+                p.epi_out[o] = hv;
                 p.dst[0][o] = gv;
                 p.dst[1][o] = uv;
                 if (p.epi_act) p.epi_act[o] = act;
-                const float hv = __fmul_rn(act, uv);
-                p.epi_out[o] = hv;
-                if (feed == 4) mc_st_pair(mb_next + o, hv, epoch + 1u);
             }
         } else {
-            for (int idx = tid; idx < p.nseg * nrows; idx += MC_NCT) {
+            for (int idx = tid; idx < nseg * nrows; idx += MC_NCT) {
                 const int seg = idx >= 2 * nrows ? 2 : idx >= nrows ? 1 : 0;
                 const int r = idx - seg * nrows;
-                float v = rowsum(seg * p.rows_max + r);
+                float v = rowsum(seg * rows_max + r);
                 const int64_t o = r_begin + r;
                 if (p.residual) {              // fused residual ADD (computeAdd's single F32 add); no stacked segments with a residual
                     if (p.dst_raw) p.dst_raw[o] = v;
                     v = __fadd_rn(idx == tid ? res_pre : __ldcg(p.residual + o), v);
                 }
-                p.dst[seg][o] = v;
                 if (feed == 1 + seg) mc_st_pair(mb_next + o, v, epoch + 1u);
+                p.dst[seg][o] = v;
             }
         }
-        if (bo_on) p.b_out[bo_k] = __fmul_rn(__fmul_rn(bo_x, rinv), bo_g);
-        if (flagged) {     // cold: re-arm the range flags before any thread runs ahead into the next phase's prep
-            if (tid <= MC_MASK_WORDS) { if (tid < MC_MASK_WORDS) ((uint32_t *)(smem + MC_OFF_MASK))[tid] = 0u; else *(uint32_t *)(smem + MC_OFF_ANY) = 0u; }
-            asm volatile("bar.sync 1, %0;" ::"r"(MC_NCT) : "memory");
-        }
+        if (bo_on) p.b_out[bo_k] = __fmul_rn(__fmul_rn(__uint_as_float(bo_x.x), rinv), bo_g);
         if (tid == 0) MC_TL(ph, 6);
     }
     if (tid == 0) asm volatile("red.relaxed.gpu.global.add.u64 [%0], %1;" ::"l"(bar_cnt), "l"(1ull) : "memory");   // this CTA is done with the launch
@@ -727,7 +750,7 @@ cudaError_t launch_gemv_mchain(int type, int n, const GemvChainLink *links, cons
         if (((uintptr_t)L.a & 15) || ((uintptr_t)L.b & 15) || ((uintptr_t)f.pro_w & 15) || ((uintptr_t)f.b_out & 15)) return cudaErrorNotSupported;
         p.a[0] = (const uint8_t *)L.a; p.b = L.b; p.dst[0] = L.dst;
         p.nib = tune.nibble_order ? 1 : 0;
-        p.K = (int)K; p.M = (int)M;
+        p.K = (int)K; p.M = (int)M; p.inv_k = (float)(1.0 / (double)K);
         p.pro_mode = f.pro_mode; p.pro_w = f.pro_w; p.pro_eps = f.pro_eps; p.b_out = f.b_out;
         p.residual = f.residual; p.dst_raw = f.dst_raw;
         if (f.nseg_extra < 0 || f.nseg_extra > 2 || (f.nseg_extra > 0 && f.residual)) return cudaErrorNotSupported;
@@ -810,7 +833,8 @@ cudaError_t launch_gemv_mchain(int type, int n, const GemvChainLink *links, cons
     cp.bar = bar;
     cp.tl = (unsigned long long *)tune.timeline;
     cp.part_off = MC_HDR;
-    cp.x_off = (cp.part_off + part_rows * MC_PS * 4 + 15) & ~15;
+    cp.part_floats = part_rows * MC_PS;
+    cp.x_off = (cp.part_off + 2 * part_rows * MC_PS * 4 + 15) & ~15;
     cp.sc_off = cp.x_off + nblk_max * MC_XB;
     cp.ring_off = (cp.sc_off + nblk_max * 16 + 127) & ~127;
     const int total = 227 * 1024;
