@@ -82,6 +82,7 @@ struct MChainParams {
     unsigned long long *tl;    // tools/chain_timeline.cu only
 };
 static_assert(sizeof(MChainParams) <= 4000, "kernel parameter space");
+static_assert(MC_NB == 8, "slot arithmetic in the stage loop");
 
 #ifdef LK_GEMV_TIMELINE
 #define MC_TL_STRIDE (8 + 8 * 8)
@@ -97,6 +98,18 @@ __device__ __forceinline__ uint4 mc_lds128(uint32_t a) {
     uint4 v;
     asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
     return v;
+}
+// mbarrier wait / arrive on a 32-bit shared address (no generic -> shared conversion per stage)
+__device__ __forceinline__ void mc_mbar_wait(uint32_t addr, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "MC_WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@!p bra MC_WAIT_%=;\n\t}"
+        ::"r"(addr), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void mc_mbar_arrive(uint32_t addr) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(addr) : "memory");
 }
 // D = A (16 x 32 bytes, row) x B (32 x 8 signed bytes, col) + C; SIGNED_A: Q8_0 quants, else nibbles / unsigned
 template <bool SIGNED_A>
@@ -196,7 +209,7 @@ __device__ __forceinline__ void mc_load8(const MPhase &p, const uint2 *mb, uint3
 //   Q4, Kotlin order (byte j = elements 2j, 2j+1):  [e0 e2 e4 e6 | e1 e3 e5 e7 | e8 e10 e12 e14 | e9 .. e15] + 16 h
 //   Q4, ggml order   (byte j = elements j, j+16):   [e0..e3 | e16..e19 | e4..e7 | e20..e23] + 8 h
 //   Q8_0:                                           [e0..e3 | e4..e7 | e8..e11 | e12..e15] + 16 h
-// Table entry of block b (16 bytes at sc + 16 b): s, c * s * sumT, 65536 s, 0  (c = -8 for Q4_0, else 1).
+// Table entry of block b (16 bytes at sc + 16 b): s, c * s * sumT, 65536 s, 0  (c = -8 for Q4_0, 1 for Q4_1, 0 for Q8_0).
 // One round: the eight activations v of task `task` (block task >> 2, quarter task & 3; the four lanes of a block are adjacent)
 template <int TYPE>
 __device__ __forceinline__ void mc_convert8(const MPhase &p, uint8_t *xs, float4 *sc, uint32_t *mask, uint32_t *any, int lane, int task, bool on, const float (&v)[8]) {
@@ -265,7 +278,7 @@ __device__ __forceinline__ void mc_convert8(const MPhase &p, uint8_t *xs, float4
                 *(uint2 *)(slot + pl * 32 + (q >> 1) * 16 + (q & 1) * 8) = make_uint2(w0, w1);
             }
         }
-        if (q == 0) sc[blk] = make_float4(s, (TYPE == T_Q4_0 ? -8.0f : 1.0f) * s * (float)sumT, 65536.0f * s, 0.f);
+        if (q == 0) sc[blk] = make_float4(s, TYPE == T_Q8_0 ? 0.f : (TYPE == T_Q4_0 ? -8.0f : 1.0f) * s * (float)sumT, 65536.0f * s, 0.f);
     }
 }
 
@@ -382,34 +395,76 @@ __device__ __noinline__ void mc_fixup(const MPhase *pp, const MChainParams *cpp,
     }
 }
 
-// ---- one stage: rows [0, n) of a strip x this warp's block pairs [0, npairs) --------------------------------------------
-// pa0 / pa1: shared addresses of this lane's first quant word (aligned down) in rows g and g + 8; pd0 / pd1: of the block's d.
+// ---- one block pair of a strip: rows g (and g + 8 if TWO) x the pair's 64 activations -------------------------------------
+// pa0 / pa1: shared addresses of this lane's first quant word (aligned down) in rows g and g + 8; pd0 / pd1: of the block's
+// first word (d, and m for Q4_1); b: this lane's B fragments of the pair's two MMAs; s: this lane's table entry half.
 template <int TYPE, bool TWO>
-__device__ __forceinline__ void mc_pairs(uint32_t pa0, uint32_t pa1, uint32_t pd0, uint32_t pd1, uint32_t pb, uint32_t bstep, uint32_t psc,
-                                         int npairs, uint32_t sel, float &acc0, float &acc1) {
-    if (TYPE == T_Q4_0) {
-#pragma unroll 2
-        for (int i = 0; i < npairs; i++) {
+__device__ __forceinline__ void mc_pair(uint32_t pa0, uint32_t pa1, uint32_t pd0, uint32_t pd1, const uint4 &b, const float2 &s, uint32_t sel,
+                                        float &acc0, float &acc1) {
+    int c[4];
+    if (TYPE == T_Q8_0) {
+        // 16 signed quant bytes per lane and row: four words, word-aligned for the odd block of a pair only
+        const uint32_t u0 = mc_lds32(pa0), u1 = mc_lds32(pa0 + 4), u2 = mc_lds32(pa0 + 8), u3 = mc_lds32(pa0 + 12), u4 = mc_lds32(pa0 + 16);
+        uint32_t r[4] = {0, 0, 0, 0};
+        if (TWO) {
+            const uint32_t v0 = mc_lds32(pa1), v1 = mc_lds32(pa1 + 4), v2 = mc_lds32(pa1 + 8), v3 = mc_lds32(pa1 + 12), v4 = mc_lds32(pa1 + 16);
+            r[0] = __byte_perm(v0, v1, sel); r[1] = __byte_perm(v1, v2, sel); r[2] = __byte_perm(v2, v3, sel); r[3] = __byte_perm(v3, v4, sel);
+        }
+        mc_imma0<true>(c, __byte_perm(u0, u1, sel), r[0], __byte_perm(u1, u2, sel), r[1], b.x, b.y);
+        mc_imma<true>(c, __byte_perm(u2, u3, sel), r[2], __byte_perm(u3, u4, sel), r[3], b.z, b.w);
+        const float d0 = h2f((uint16_t)mc_lds16(pd0));
+        acc0 = fmaf(d0, (float)(c[0] + (c[1] << 8)) * s.x, acc0);
+        if (TWO) {
+            const float d1 = h2f((uint16_t)mc_lds16(pd1));
+            acc1 = fmaf(d1, (float)(c[2] + (c[3] << 8)) * s.x, acc1);
+        }
+    } else {
+        // eight quant bytes (16 nibbles) per lane and row; Q4_0 blocks are word-aligned for the odd block of a pair only
+        uint32_t q0, q1, r0 = 0, r1 = 0;
+        if (TYPE == T_Q4_0) {
             const uint32_t u0 = mc_lds32(pa0), u1 = mc_lds32(pa0 + 4), u2 = mc_lds32(pa0 + 8);
-            const uint32_t q0 = __byte_perm(u0, u1, sel), q1 = __byte_perm(u1, u2, sel);
-            uint32_t r0 = 0, r1 = 0;
+            q0 = __byte_perm(u0, u1, sel); q1 = __byte_perm(u1, u2, sel);
             if (TWO) {
                 const uint32_t v0 = mc_lds32(pa1), v1 = mc_lds32(pa1 + 4), v2 = mc_lds32(pa1 + 8);
                 r0 = __byte_perm(v0, v1, sel); r1 = __byte_perm(v1, v2, sel);
             }
-            const uint4 b = mc_lds128(pb);
-            int c[4];
-            mc_imma0<false>(c, q0 & 0x0F0F0F0Fu, r0 & 0x0F0F0F0Fu, (q0 >> 4) & 0x0F0F0F0Fu, (r0 >> 4) & 0x0F0F0F0Fu, b.x, b.y);
-            mc_imma<false>(c, q1 & 0x0F0F0F0Fu, r1 & 0x0F0F0F0Fu, (q1 >> 4) & 0x0F0F0F0Fu, (r1 >> 4) & 0x0F0F0F0Fu, b.z, b.w);
-            const float2 s = mc_lds64f(psc);
+        } else {                                  // Q4_1: 20-byte blocks, quants at +4: always aligned
+            q0 = mc_lds32(pa0); q1 = mc_lds32(pa0 + 4);
+            if (TWO) { r0 = mc_lds32(pa1); r1 = mc_lds32(pa1 + 4); }
+        }
+        mc_imma0<false>(c, q0 & 0x0F0F0F0Fu, r0 & 0x0F0F0F0Fu, (q0 >> 4) & 0x0F0F0F0Fu, (r0 >> 4) & 0x0F0F0F0Fu, b.x, b.y);
+        mc_imma<false>(c, q1 & 0x0F0F0F0Fu, r1 & 0x0F0F0F0Fu, (q1 >> 4) & 0x0F0F0F0Fu, (r1 >> 4) & 0x0F0F0F0Fu, b.z, b.w);
+        if (TYPE == T_Q4_0) {                     // d * (s I - 8 s sumT)
             const float d0 = h2f((uint16_t)mc_lds16(pd0));
             acc0 = fmaf(d0, fmaf((float)(c[0] + (c[1] << 8)), s.x, s.y), acc0);
             if (TWO) {
                 const float d1 = h2f((uint16_t)mc_lds16(pd1));
                 acc1 = fmaf(d1, fmaf((float)(c[2] + (c[3] << 8)), s.x, s.y), acc1);
             }
-            pa0 += 36; pa1 += 36; pd0 += 36; pd1 += 36; pb += bstep; psc += 32;
+        } else {                                  // d s I + m s sumT
+            const uint32_t w0 = mc_lds32(pd0);
+            acc0 = fmaf(h2f((uint16_t)(w0 & 0xFFFFu)), (float)(c[0] + (c[1] << 8)) * s.x, acc0);
+            acc0 = fmaf(h2f((uint16_t)(w0 >> 16)), s.y, acc0);
+            if (TWO) {
+                const uint32_t w1 = mc_lds32(pd1);
+                acc1 = fmaf(h2f((uint16_t)(w1 & 0xFFFFu)), (float)(c[2] + (c[3] << 8)) * s.x, acc1);
+                acc1 = fmaf(h2f((uint16_t)(w1 >> 16)), s.y, acc1);
+            }
         }
+    }
+}
+
+// ---- one stage: rows [0, n) of a strip x this warp's block pairs [0, npairs) --------------------------------------------
+template <int TYPE, bool TWO>
+__device__ __forceinline__ void mc_pairs(uint32_t pa0, uint32_t pa1, uint32_t pd0, uint32_t pd1, uint32_t pb, uint32_t bstep, uint32_t psc,
+                                         int npairs, uint32_t sel, float &acc0, float &acc1) {
+    constexpr uint32_t PAIR_B = 2 * block_bytes(TYPE);
+#pragma unroll 2
+    for (int i = 0; i < npairs; i++) {
+        const uint4 b = mc_lds128(pb);
+        const float2 s = mc_lds64f(psc);
+        mc_pair<TYPE, TWO>(pa0, pa1, pd0, pd1, b, s, sel, acc0, acc1);
+        pa0 += PAIR_B; pa1 += PAIR_B; pd0 += PAIR_B; pd1 += PAIR_B; pb += bstep; psc += 32;
     }
 }
 
@@ -418,27 +473,10 @@ __device__ __forceinline__ void mc_pairs(uint32_t pa0, uint32_t pa1, uint32_t pd
 template <int TYPE, bool TWO>
 __device__ __forceinline__ void mc_pairs4(uint32_t pa0, uint32_t pa1, uint32_t pd0, uint32_t pd1, const uint4 (&breg)[4], const float2 (&sreg)[4],
                                           uint32_t sel, float &acc0, float &acc1) {
-    if (TYPE == T_Q4_0) {
+    constexpr uint32_t PAIR_B = 2 * block_bytes(TYPE);
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
-            const uint32_t u0 = mc_lds32(pa0 + 36 * i), u1 = mc_lds32(pa0 + 36 * i + 4), u2 = mc_lds32(pa0 + 36 * i + 8);
-            const uint32_t q0 = __byte_perm(u0, u1, sel), q1 = __byte_perm(u1, u2, sel);
-            uint32_t r0 = 0, r1 = 0;
-            if (TWO) {
-                const uint32_t v0 = mc_lds32(pa1 + 36 * i), v1 = mc_lds32(pa1 + 36 * i + 4), v2 = mc_lds32(pa1 + 36 * i + 8);
-                r0 = __byte_perm(v0, v1, sel); r1 = __byte_perm(v1, v2, sel);
-            }
-            int c[4];
-            mc_imma0<false>(c, q0 & 0x0F0F0F0Fu, r0 & 0x0F0F0F0Fu, (q0 >> 4) & 0x0F0F0F0Fu, (r0 >> 4) & 0x0F0F0F0Fu, breg[i].x, breg[i].y);
-            mc_imma<false>(c, q1 & 0x0F0F0F0Fu, r1 & 0x0F0F0F0Fu, (q1 >> 4) & 0x0F0F0F0Fu, (r1 >> 4) & 0x0F0F0F0Fu, breg[i].z, breg[i].w);
-            const float d0 = h2f((uint16_t)mc_lds16(pd0 + 36 * i));
-            acc0 = fmaf(d0, fmaf((float)(c[0] + (c[1] << 8)), sreg[i].x, sreg[i].y), acc0);
-            if (TWO) {
-                const float d1 = h2f((uint16_t)mc_lds16(pd1 + 36 * i));
-                acc1 = fmaf(d1, fmaf((float)(c[2] + (c[3] << 8)), sreg[i].x, sreg[i].y), acc1);
-            }
-        }
-    }
+    for (int i = 0; i < 4; i++)
+        mc_pair<TYPE, TWO>(pa0 + PAIR_B * i, pa1 + PAIR_B * i, pd0 + PAIR_B * i, pd1 + PAIR_B * i, breg[i], sreg[i], sel, acc0, acc1);
 }
 
 template <int TYPE>
@@ -502,7 +540,7 @@ __global__ void __launch_bounds__((MC_W + MC_PW) * 32, 1) gemv_mchain_kernel(con
                                 need = need || (live && wr < qe[j] && qs[j] < wr + bytes);
                             }
                             if (!need) break;
-                            mbar_wait(&empty[head & (MC_NB - 1)], (uint32_t)(head / MC_NB) & 1u);
+                            mbar_wait(&empty[head & (MC_NB - 1)], (uint32_t)(head / MC_NB) & 1u);     // (a __nanosleep between polls cost 1 %: the reaction time matters more than the issue slots)
                             head++;
                         }
                         // Pace the stream: at most `inflight` stages issued and not yet landed.  More requests in flight add no
@@ -626,12 +664,12 @@ __global__ void __launch_bounds__((MC_W + MC_PW) * 32, 1) gemv_mchain_kernel(con
                 const uint32_t ro_a = (uint32_t)((g < n ? g : 0) * stride), ro_b = (uint32_t)((g + 8 < n ? g + 8 : 0) * stride);
 #pragma unroll 1
                 for (int ch = 0; ch < nchunk; ch++) {
-                    const int slot = si & (MC_NB - 1);
-                    mbar_wait(&full[slot], (uint32_t)(si / MC_NB) & 1u);
+                    const uint32_t slot8 = (uint32_t)(si & (MC_NB - 1)) * 8u;
+                    mc_mbar_wait(smem_base + slot8, (uint32_t)(si >> 3) & 1u);
 #ifdef LK_GEMV_TIMELINE
                     if (first_stage && tid == 0) { MC_TL(ph, 4); first_stage = false; }
 #endif
-                    const uint32_t sbase = ring_base + stage_off[slot];
+                    const uint32_t sbase = ring_base + mc_lds32(smem_base + MC_OFF_STAGE + (slot8 >> 1));
                     const int pw = ch == 0 ? pw0 : pw1, npw = ch == 0 ? np0 : np1;
                     const uint32_t coff = (uint32_t)((pw - (ch == 0 ? 0 : c0)) * 2 * BB);     // this warp's first pair within the staged chunk
                     const uint32_t pa0 = sbase + ro_a + coff + a_lane, pa1 = sbase + ro_b + coff + a_lane;
@@ -657,7 +695,7 @@ __global__ void __launch_bounds__((MC_W + MC_PW) * 32, 1) gemv_mchain_kernel(con
                         if (g + 8 < n) pr[8 * MC_PS] = ch == 0 ? acc1 : pr[8 * MC_PS] + acc1;
                     }
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&empty[slot]);    // this warp is done reading the stage
+                    if (lane == 0) mc_mbar_arrive(smem_base + 64u + slot8);    // this warp is done reading the stage
                     si++;
                 }
             }
@@ -735,7 +773,7 @@ __global__ void __launch_bounds__((MC_W + MC_PW) * 32, 1) gemv_mchain_kernel(con
 cudaError_t launch_gemv_mchain(int type, int n, const GemvChainLink *links, const GemvTuning &tune, int sm_count, cudaStream_t s, unsigned *bar,
                                void *mbox) {
     if (n < 1 || n > MC_MAX || !links || !bar || !mbox) return cudaErrorNotSupported;
-    if (type != T_Q4_0) return cudaErrorNotSupported;
+    if (type != T_Q4_0 && type != T_Q4_1 && type != T_Q8_0) return cudaErrorNotSupported;
     if (tune.act_planes == 2) return cudaErrorNotSupported;      // the opt-in 16-bit mode stays on K1c
     const int bb = block_bytes(type);
     const int grid = sm_count;
@@ -843,7 +881,7 @@ cudaError_t launch_gemv_mchain(int type, int n, const GemvChainLink *links, cons
         if (2 * cp.ph[i].sr * cp.ph[i].stride > cp.ring_bytes) return cudaErrorNotSupported;
     const int smem = total;
 
-    void (*kern)(const MChainParams) = gemv_mchain_kernel<T_Q4_0>;
+    void (*kern)(const MChainParams) = type == T_Q4_0 ? gemv_mchain_kernel<T_Q4_0> : type == T_Q4_1 ? gemv_mchain_kernel<T_Q4_1> : gemv_mchain_kernel<T_Q8_0>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
     int per_sm = 0;     // the grid barrier needs every CTA resident at once (see launch_gemv_chain)

@@ -254,7 +254,12 @@ struct Planner {
             }
             pending.clear();
         };
-        const bool chain = chain_mode < 0 ? !steps.empty() : chain_mode != 0;
+        // the planner's own choice (chain_mode < 0): chain where it was measured to pay: graphs with an attention step
+        // between the runs (either chained kernel), and graphs whose decode GEMVs K1m takes (Q4_0, K % 256 == 0: 36.5 against
+        // 39.4 us per 7B layer as separate launches, profiles/r02j_layer_ab_per_warp_prep.txt)
+        bool k1m = !gemv.empty();
+        for (int i : gemv) k1m = k1m && nodes[i].src[0].type == LK_TYPE_Q4_0 && nodes[i].src[0].ne[0] % 256 == 0;
+        const bool chain = chain_mode < 0 ? (!steps.empty() || k1m) : chain_mode != 0;
         for (int i = 0; i < n; i++) {
             if (skip.count(i) || (!pending.empty() && nodes[i].op == LK_OP_NONE)) continue;
             if (chain && gemv.count(i)) {

@@ -117,7 +117,8 @@ class GGMLCudaBackend:
         self.fuseOps = True          # fold RMS_NORM / ADD neighbours into the decode GEMV inside captured sequences
         # runs of DEPENDENT decode GEMVs as one persistent launch (lk_compute_matmul_chain): True / False, or None = where
         # it was measured to pay: graphs with an attention step between the runs (+19 % tok/s at 2048 cached positions;
-        # with a one-position context four separate launches are 2 % faster, profiles/r01t_gemv_chain_ab.txt)
+        # with a one-position context four separate launches are 2 % faster than K1c, profiles/r01t_gemv_chain_ab.txt) and
+        # graphs whose GEMVs the MMA chain K1m takes (Q4_0, K % 256 == 0: 8 % faster than separate launches at ctx 0)
         self.chainOps = None
         self.maxChain = 8            # links per launch (the library's limit)
         self._bt = GGMLCudaBufferType(self)
@@ -467,7 +468,9 @@ class GGMLCudaBackend:
             for c in range(0, len(items), self.maxChain):
                 self._runChain(ga, nodes, items[c:c + self.maxChain], rms_of, add_of, stored)
 
-        chain = bool(self._steps) if self.chainOps is None else bool(self.chainOps)
+        # chainOps None: graphs with an attention step, and graphs whose decode GEMVs K1m takes (lk_planner.cu has the same rule)
+        k1m = bool(self._gemv) and all(nodes[i].src[0].type == GGMLType.Q4_0 and int(nodes[i].src[0].ne[0]) % 256 == 0 for i in self._gemv)
+        chain = (bool(self._steps) or k1m) if self.chainOps is None else bool(self.chainOps)
         for i, node in enumerate(nodes):
             if i in skip or (pending and node.op == GGMLOp.NONE and not isinstance(node.extra, dict)):
                 continue

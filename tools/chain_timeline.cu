@@ -139,5 +139,13 @@ int main(int argc, char **argv) {
             printf("   %-18s min %7.2f  med %7.2f  max %7.2f us\n", names[sl], v.front(), v[v.size() / 2], v.back());
         }
     }
+    if (getenv("LK_TL_DUMP")) {     // per-CTA rows of one phase: smid, rows, stamps
+        const int ph = atoi(getenv("LK_TL_DUMP"));
+        printf("phase %d per CTA: bid smid start x_loaded x_prepped first_stage loop_done finished prod_last\n", ph);
+        for (int b = 0; b < grid; b++) {
+            const unsigned long long *q = h.data() + (size_t)b * LK_CTL_STRIDE;
+            printf("%3d %3llu %7.2f %7.2f %7.2f %7.2f %7.2f %7.2f %7.2f\n", b, q[2], us(b, ph, 0), us(b, ph, 1), us(b, ph, 3), us(b, ph, 4), us(b, ph, 5), us(b, ph, 6), us(b, ph, 7));
+        }
+    }
     return 0;
 }

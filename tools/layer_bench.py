@@ -65,9 +65,10 @@ def run(lk, be, qtype: str = "Q4_0", layers: int = 32, steps: int = 50, warmup: 
     if drop_ops:     # timing experiments only (the numbers are then meaningless): how much of the step do these ops cost?
         graph.nodes = [n for n in graph.nodes if n.op.name not in drop_ops]
     lkc = be.lk
-    launches0, chains0 = lkc.launch_count(), int(lkc.get_option("gemv_chain_launches"))
+    launches0, chains0, mma0 = lkc.launch_count(), int(lkc.get_option("gemv_chain_launches")), int(lkc.get_option("gemv_chain_mma_launches"))
     assert be.graphCompute(graph) == lk.GGMLStatus.SUCCESS          # captures: the launch counters move here only
     launches, chains = lkc.launch_count() - launches0, int(lkc.get_option("gemv_chain_launches")) - chains0
+    mma_chains = int(lkc.get_option("gemv_chain_mma_launches")) - mma0        # of those, taken by K1m (lk_gemv_mma.cu)
     for _ in range(warmup):
         assert be.graphCompute(graph) == lk.GGMLStatus.SUCCESS
     lkc.sync()
@@ -82,7 +83,7 @@ def run(lk, be, qtype: str = "Q4_0", layers: int = 32, steps: int = 50, warmup: 
                        (f"RoPE + KV cache + decode attention over {ctx_len} positions ({heads} heads), " if ctx_len else "one-position context, ") +
                        f"{layers} layers with distinct weights ({layers * wbytes / 1e9:.2f} GB > L2), {18 if ctx_len else 13} graph nodes per layer",
            "ctx_len": ctx_len, "kv_bytes_read_per_layer": kv_read, "launches_per_token": int(launches),
-           "chained_gemv_launches_per_token": int(chains),
+           "chained_gemv_launches_per_token": int(chains), "of_those_on_the_mma_chain_kernel": int(mma_chains),
            "layers": layers, "ms_per_token": ms, "tok_s": 1e3 / ms, "layer_tok_s": layers * 1e3 / ms,
            "us_per_layer": ms * 1e3 / layers, "weight_bytes_per_layer": wbytes,
            "weight_GBps": layers * wbytes / (ms * 1e-3) / 1e9, "finite_output": bool(np.all(np.isfinite(y)))}
