@@ -226,14 +226,20 @@ LK_API lk_status   lk_compute_matmul_fused(lk_ctx *ctx, const lk_tensor *a, cons
 /* A run of DEPENDENT decode matmuls — the four launches of LlamaDecoderLayer.forward (model/LlamaModel.kt:253-285:
  * [RMSNorm -> Q/K/V], [O + residual], [RMSNorm -> gate/up + SwiGLU], [down + residual]), possibly across layers — as ONE
  * persistent launch: link i is exactly the call lk_compute_matmul_fused(a, b, dst, fusion) (fusion may be NULL = plain
- * N == 1 matmul), links run in order with a grid-wide barrier between them and the weight stream runs ahead across the
- * hand-offs.  Results are identical to issuing the links one by one (a link with the RMSNorm prologue may differ in
- * the last bit of 1/rms: more threads share the sum of squares).  Up to 8 links, one weight type, device-resident
- * tensors; anything else returns LK_ENOTIMPL and the caller issues the links itself.
+ * N == 1 matmul), links run in order and the weight stream runs ahead across the hand-offs.  Up to 8 links, one weight
+ * type, device-resident tensors; anything else returns LK_ENOTIMPL and the caller issues the links itself.
+ * Two kernels stand behind it.  K1m (lk_gemv_mma.cu; K % 256 == 0, every tensor the launch writes written by exactly one
+ * link, activations either the previous link's output or from outside the launch): plane sums on the warp-level int8
+ * MMA, phases handed over through a mailbox of (value, epoch) pairs instead of a barrier; results equal the links
+ * issued one by one to F32 rounding (same exact integer sums per block, different order of the F32 additions; measured
+ * <= 1e-6 of the largest output).  K1c (lk_gemv.cu; everything K1m declines, or everything after
+ * lk_set_option(ctx, "gemv_chain_mma", 0)): DP4A plane sums, a grid-wide barrier between links, results identical to the
+ * links issued one by one (a link with the RMSNorm prologue may differ in the last bit of 1/rms).
+ * lk_get_option(ctx, "gemv_chain_mma_launches") counts the launches K1m took.
  * The launch is one CTA per SM and all of them must be resident at once: do not run it beside kernels of other
- * streams that hold SMs indefinitely.  The barrier spins are bounded (the device never hangs); a time-out leaves wrong
+ * streams that hold SMs indefinitely.  The waits are bounded (the device never hangs); a time-out leaves wrong
  * results behind and is counted: lk_get_option(ctx, "gemv_chain_timeouts") synchronises, returns the count since the
- * last read (0 in a healthy run) and re-arms the barrier.  lk_set_option(ctx, "gemv_chain", 0) makes this call decline. */
+ * last read (0 in a healthy run) and re-arms the counter.  lk_set_option(ctx, "gemv_chain", 0) makes this call decline. */
 typedef struct lk_matmul_link {
     const lk_tensor *a, *b, *dst;
     const lk_matmul_fusion *fusion;
@@ -358,7 +364,8 @@ typedef struct lk_plan_launch {
     int32_t chain;
     int32_t attn[5];             /* LK_PLAN_ATTN_STEP: ROPE(q), ROPE(k), CPY(k), CPY(v), FLASH_ATTN */
 } lk_plan_launch;
-/* chain_mode: -1 = where it was measured to pay (graphs with an attention step between the runs), 0 never, 1 always */
+/* chain_mode: -1 = where it was measured to pay (graphs with an attention step between the runs, and graphs whose decode
+ * GEMVs are all Q4_0 with K % 256 == 0: the MMA chain kernel takes those), 0 never, 1 always */
 LK_API lk_status   lk_graph_plan(const lk_graph_node *nodes, int32_t n, int32_t chain_mode, lk_plan_launch *out,
                                  int32_t max_out, int32_t *n_out);
 #define LK_GRAPH_NO_FUSION    1   /* node by node, like the reference's interpreter */
