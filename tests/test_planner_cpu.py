@@ -44,12 +44,12 @@ def make_backend(chain=None):
     return be
 
 
-def make_graph(nlayers=2, attention=False):
+def make_graph(nlayers=2, attention=False, hidden=HIDDEN, ffn=FFN, qtype=GGMLType.Q4_0):
     ga = GGMLGraphAllocator(None, size=64 << 20)
-    x = ga.allocateTensor(GGMLTensor(GGMLType.F32, [HIDDEN]))
-    stack = [alloc_layer(ga, GGMLType.Q4_0, HIDDEN, FFN) for _ in range(nlayers)]
-    attn = alloc_attention(ga, HEADS, HIDDEN // HEADS, 16, nlayers) if attention else None
-    graph, out = build_decoder_graph(ga, stack, x, HIDDEN, FFN, attn=attn)
+    x = ga.allocateTensor(GGMLTensor(GGMLType.F32, [hidden]))
+    stack = [alloc_layer(ga, qtype, hidden, ffn) for _ in range(nlayers)]
+    attn = alloc_attention(ga, HEADS, hidden // HEADS, 16, nlayers) if attention else None
+    graph, out = build_decoder_graph(ga, stack, x, hidden, ffn, attn=attn)
     return ga, graph
 
 
@@ -85,6 +85,18 @@ def test_one_position_context_keeps_four_launches_per_layer(monkeypatch):
                                             ["eps", "extra", "mul_dst", "norm_w", "norm_x", "silu_dst", "store_b"],
                                             ["residual", "sum_dst"]]
     assert len(kws[0]["extra"]) == 2 and len(kws[2]["extra"]) == 1
+
+
+def test_one_position_context_chains_what_the_mma_chain_kernel_takes(monkeypatch):
+    """The planner's own choice: Q4_0 GEMVs with K % 256 == 0 (K1m, lk_gemv_mma.cu, takes them) go out as one chained launch
+    even without an attention step; another weight type or one K that is not a multiple of 256 keeps the separate launches."""
+    ga, graph = make_graph(2, hidden=256, ffn=768)
+    calls = run(make_backend(None), ga, graph, Recorder(), monkeypatch)
+    assert [c[0] for c in calls] == ["chain"] and len(calls[0][1]) == 8
+    ga, graph = make_graph(2, hidden=256, ffn=704)                  # the down projection's K = 704
+    assert [c[0] for c in run(make_backend(None), ga, graph, Recorder(), monkeypatch)] == ["fused"] * 8
+    ga, graph = make_graph(2, hidden=256, ffn=768, qtype=GGMLType.Q8_0)
+    assert [c[0] for c in run(make_backend(None), ga, graph, Recorder(), monkeypatch)] == ["fused"] * 8
 
 
 def test_explicit_chain_takes_all_dependent_launches(monkeypatch):
@@ -215,13 +227,14 @@ def _library_launches(ga, graph, chain_mode):
     return out
 
 
+@pytest.mark.parametrize("dims", [(HIDDEN, FFN), (256, 768)])
 @pytest.mark.parametrize("attention", [False, True])
 @pytest.mark.parametrize("chain", [None, True, False])
-def test_library_planner_makes_the_python_planner_s_launches(monkeypatch, attention, chain):
+def test_library_planner_makes_the_python_planner_s_launches(monkeypatch, attention, chain, dims):
     """lk_graph_plan through ctypes on the decoder-layer graph (with and without the attention core, chaining on / off /
     automatic): launch for launch what GGMLCudaBackend._plan / _runNodes issue — fused neighbours, stacked groups, the
     SwiGLU pair, which launch stores the RMS_NORM's dst, which launches form one chain, the attention steps."""
-    ga, graph = make_graph(2, attention=attention)
+    ga, graph = make_graph(2, attention=attention, hidden=dims[0], ffn=dims[1])
     py = _python_launches(make_backend(chain), ga, graph, monkeypatch)
     lib = _library_launches(ga, graph, -1 if chain is None else int(chain))
     assert len(py) == len(lib)
