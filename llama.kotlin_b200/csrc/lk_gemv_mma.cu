@@ -83,6 +83,7 @@ struct MChainParams {
 };
 static_assert(sizeof(MChainParams) <= 4000, "kernel parameter space");
 static_assert(MC_NB == 8, "slot arithmetic in the stage loop");
+static_assert(sizeof(MPhase) <= 192, "the parameter warm-up touches four lines");
 
 #ifdef LK_GEMV_TIMELINE
 #define MC_TL_STRIDE (8 + 8 * 8)
@@ -608,9 +609,9 @@ __global__ void __launch_bounds__((MC_W + MC_PW) * 32, 1) gemv_mchain_kernel(con
         const MPhase &p = cp.ph[ph];
         if (tid == 0) MC_TL(ph, 0);
         if (tid == 32 && ph + 1 < cp.nphase) {   // warm the constant cache with the next phase's parameter lines
-            const int *q = (const int *)&cp.ph[ph + 1];
-            const int t0 = q[0], t1 = q[16], t2 = q[32];
-            asm volatile("" ::"r"(t0), "r"(t1), "r"(t2));
+            const int *q = (const int *)&cp.ph[ph + 1];      // sizeof(MPhase) = 184, not line-aligned: up to four 64-byte lines
+            const int t0 = q[0], t1 = q[16], t2 = q[32], t3 = q[sizeof(MPhase) / 4 - 1];
+            asm volatile("" ::"r"(t0), "r"(t1), "r"(t2), "r"(t3));
         }
         const int par = ph & 1;
         const int r_begin = p.rows_per_cta * bid + min(bid, p.rows_rem);
@@ -706,6 +707,7 @@ __global__ void __launch_bounds__((MC_W + MC_PW) * 32, 1) gemv_mchain_kernel(con
         }
         if (tid == 0) MC_TL(ph, 5);
         asm volatile("bar.sync 1, %0;" ::"r"(MC_NCT) : "memory");   // every K-slice of every row is parked (and every warp has converted its activations)
+        if (tid == 0) MC_TL(ph, 2);
         const bool flagged = ((volatile uint32_t *)(smem + MC_OFF_ANY))[par] != 0u;
         if (__builtin_expect(flagged, 0)) {
             mc_fixup<TYPE>(&p, &cp, smem, r_begin, nrows, mb, par, part);

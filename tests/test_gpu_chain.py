@@ -327,3 +327,32 @@ def test_mchain_ggml_nibble_order_and_nonfinite_activations(O):
     assert not np.any(np.isfinite(ga.getFloats(y1))) and not np.any(np.isfinite(ga.getFloats(y2)))
     assert be.lk.get_option("gemv_chain_timeouts") == 0
     be.free()
+
+
+def test_mchain_links_with_activations_from_outside_the_launch(O):
+    """Not every link of a chain reads its predecessor: a link whose activations come from outside the launch is loaded
+    directly (no mailbox), a later link may still take the first link's residual-summed output by mailbox.  Three links:
+    y1 = W1 x; y2 = W2 z (z from outside); y3 = W3 y2 + y1 as residual (an earlier link's dst with the same row count)."""
+    hidden, ffn = 512, 1536
+    be = lk.GGMLCudaBackend(0)
+    ga = lk.GGMLGraphAllocator(be, size=8 << 20)
+    dev = _dev(ga)
+    w1 = O.quantize(Q4_0, synth_weights(7400, hidden, hidden))
+    w2 = O.quantize(Q4_0, synth_weights(7401, ffn, hidden))
+    w3 = O.quantize(Q4_0, synth_weights(7402, hidden, ffn))
+    W1, W2, W3 = dev(GGMLType.Q4_0, [hidden, hidden], w1), dev(GGMLType.Q4_0, [hidden, ffn], w2), dev(GGMLType.Q4_0, [ffn, hidden], w3)
+    x0, z0 = synth_acts(7403, hidden), synth_acts(7404, hidden)
+    x, z = dev(GGMLType.F32, [1, hidden], x0), dev(GGMLType.F32, [1, hidden], z0)
+    y1, y2, y3 = (dev(GGMLType.F32, [1, n], np.zeros(n, np.float32)) for n in (hidden, ffn, hidden))
+    s3 = dev(GGMLType.F32, [hidden], np.zeros(hidden, np.float32))
+    y1_flat = GGMLTensor(GGMLType.F32, [hidden], bufferId=y1.bufferId, dataOffset=y1.dataOffset, buffer=y1.buffer)
+    m0 = be.lk.get_option("gemv_chain_mma_launches")
+    assert computeMatMulChain(ga, None, [(W1, x, y1, None), (W2, z, y2, None), (W3, y2, y3, dict(residual=y1_flat, sum_dst=s3))])
+    be.lk.sync()
+    assert be.lk.get_option("gemv_chain_mma_launches") == m0 + 1 and be.lk.get_option("gemv_chain_timeouts") == 0
+    r1 = O.matmul(Q4_0, w1, hidden, hidden, x0, 1)
+    assert_matmul_parity(O, Q4_0, w1, hidden, hidden, x0, 1, ga.getFloats(y1), ref=r1, tag="link 0")
+    assert_matmul_parity(O, Q4_0, w2, hidden, ffn, z0, 1, ga.getFloats(y2), tag="link 1 (outside activations)")
+    assert_matmul_parity(O, Q4_0, w3, ffn, hidden, ga.getFloats(y2), 1, ga.getFloats(y3), tag="link 2 (mailbox)")
+    assert same_f32_bits(ga.getFloats(s3), (ga.getFloats(y1) + ga.getFloats(y3)).astype(np.float32))
+    be.free()

@@ -128,7 +128,7 @@ int main(int argc, char **argv) {
         if (!v) return -1.0;
         return (double)(q[0] - g0) / 1e3 + (double)(v - q[1]) / mhz;
     };
-    const char *names[8] = {"phase_start", "bar_arrive|x_loaded", "bar_passed|rinv", "x_prepped", "first_stage_full", "loop_done", "finished", "prod_last_issue"};
+    const char *names[8] = {"phase_start", "bar_arrive|x_loaded", "bar_passed|closing_barrier_passed", "x_prepped", "first_stage_full", "loop_done", "finished", "prod_last_issue"};
     for (int ph = 0; ph < nph; ph++) {
         printf("phase %d:\n", ph);
         for (int sl = 0; sl < 8; sl++) {
