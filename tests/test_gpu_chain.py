@@ -356,3 +356,26 @@ def test_mchain_links_with_activations_from_outside_the_launch(O):
     assert_matmul_parity(O, Q4_0, w3, ffn, hidden, ga.getFloats(y2), 1, ga.getFloats(y3), tag="link 2 (mailbox)")
     assert same_f32_bits(ga.getFloats(s3), (ga.getFloats(y1) + ga.getFloats(y3)).astype(np.float32))
     be.free()
+
+
+@pytest.mark.parametrize("M", [64, 148, 149, 600])
+def test_mchain_fewer_rows_than_ctas_and_ragged_shares(O, M):
+    """A link whose matrix has fewer rows than the grid has CTAs (some CTAs own nothing in that phase and still take part
+    in the hand-off as consumers of the next one), exactly one row per CTA, and ragged shares."""
+    K = 512
+    be = lk.GGMLCudaBackend(0)
+    ga = lk.GGMLGraphAllocator(be, size=8 << 20)
+    dev = _dev(ga)
+    w1 = O.quantize(Q4_0, synth_weights(7500 + M, K, K))
+    w2 = O.quantize(Q4_0, synth_weights(7600 + M, M, K))
+    W1, W2 = dev(GGMLType.Q4_0, [K, K], w1), dev(GGMLType.Q4_0, [K, M], w2)
+    x0 = synth_acts(7700 + M, K)
+    x = dev(GGMLType.F32, [1, K], x0)
+    y1, y2 = dev(GGMLType.F32, [1, K], np.zeros(K, np.float32)), dev(GGMLType.F32, [1, M], np.zeros(M, np.float32))
+    m0 = be.lk.get_option("gemv_chain_mma_launches")
+    assert computeMatMulChain(ga, None, [(W1, x, y1, None), (W2, y1, y2, None)])
+    be.lk.sync()
+    assert be.lk.get_option("gemv_chain_mma_launches") == m0 + 1 and be.lk.get_option("gemv_chain_timeouts") == 0
+    assert_matmul_parity(O, Q4_0, w1, K, K, x0, 1, ga.getFloats(y1), tag="link 0")
+    assert_matmul_parity(O, Q4_0, w2, K, M, ga.getFloats(y1), 1, ga.getFloats(y2), tag=f"link 1, M = {M}")
+    be.free()
