@@ -680,64 +680,68 @@ enum { GEMV_WAIT_FULL = 0, GEMV_WAIT_X = 1, GEMV_WAIT_END = 2 };
 #ifndef LK_FIXUP_ATTR           // A/B builds only (tools/ab_build.sh)
 #define LK_FIXUP_ATTR __noinline__
 #endif
+// Work split (round 2, second version): warp w owns rows w, w + nwarps, ... for EVERY flagged block and lane k owns element k
+// of the block — one residual per lane and block, one quant byte and one scale per lane and row, the block's sum by a shuffle
+// tree — so a single flagged block is spread over the whole CTA.  The first version gave each (row, column) to one thread
+// that walked the 32 elements with a dependent L2 load each: ~9 us per launch with one or two blocks flagged
+// (profiles/r02m_layer_types.txt).
 template <int TYPE, int NP, bool CG>
 __device__ __forceinline__ void gemv_fixup_body(const uint8_t *a, const float *b, const float *pro_w, int pro_mode, int nib, int row_bytes,
                                                 int nblk, int red_stride, int pad_col, int row_first, int n, float *red, const uint32_t *xs,
                                                 const GemvSide *side, int tid, int nct) {
     const int nw = (nblk + 31) >> 5;
     const float rinv = side->rinv;
+    const int warp = tid >> 5, lane = tid & 31, nwarps = nct >> 5;
+    constexpr int BBT = TYPE == T_BITNET_1_58 ? 10 : block_bytes(TYPE);
+    constexpr int QOFF = TYPE == T_Q4_1 ? 4 : 2;
+    // this lane's byte of a block and, for the 4-bit types, its nibble; BitNet: digit lane % 5 of byte lane / 5
+    const int g5 = (lane * 13) >> 6;                              // lane / 5 for lane < 64
+    const int qb = TYPE == T_Q8_0 ? lane : TYPE == T_BITNET_1_58 ? g5 : (nib ? (lane & 15) : (lane >> 1));
+    const bool hi = (TYPE == T_Q4_0 || TYPE == T_Q4_1) && (nib ? (lane >> 4) : (lane & 1));
+    for (int r = warp + nwarps * (lane >> 3); r < n; r += nwarps * 4) red[(size_t)r * red_stride + pad_col + (lane & 7)] = 0.f;
+    __syncwarp();
+    int idx = 0;
 #pragma unroll 1
-    for (int item = tid; item < n * GEMV_RED_PAD; item += nct) {
-        const int r = item >> 3, j = item & 7;
-        const uint8_t *rowp = a + (size_t)(row_first + r) * row_bytes;
-        float sum = 0.f;
-        int idx = 0;
+    for (int w = 0; w < nw; w++) {
+        uint32_t m = side->mask[w];
 #pragma unroll 1
-        for (int w = 0; w < nw; w++) {
-            uint32_t m = side->mask[w];
-#pragma unroll 1
-            while (m) {
-                const int bit = __ffs((int)m) - 1;
-                m &= m - 1;
-                if ((idx++ & 7) != j) continue;
-                const int blk = w * 32 + bit;
-                const float s = __uint_as_float(xs[(size_t)blk * gemv_xslot_words(NP) + NP * 8 + 1]);
-                const float c = __frcp_rn(s);                                 // a power of two: exact
-                const uint8_t *bp = rowp + (size_t)blk * (TYPE == T_BITNET_1_58 ? 10 : block_bytes(TYPE));
-                const float d = h2f((uint16_t)(bp[0] | (bp[1] << 8)));
-                float mq = 0.f;
-                if (TYPE == T_Q4_1) mq = h2f((uint16_t)(bp[2] | (bp[3] << 8)));
-                constexpr int QOFF = TYPE == T_Q4_1 ? 4 : 2;
-                float acc = 0.f;
-#pragma unroll 1
-                for (int k = 0; k < 32; k++) {
-                    const int kk = blk * 32 + k;
-                    float v = CG ? __ldcg(b + kk) : b[kk];
-                    if (pro_mode == 1) {                                      // the fused RMSNorm prologue, same roundings as prep_x
-                        v = __fmul_rn(v, rinv);
-                        if (pro_w) v = __fmul_rn(v, CG ? __ldcg(pro_w + kk) : pro_w[kk]);
-                    }
-                    const int T = (int)__float_as_uint(fmaf(v, c, 12582912.0f)) - 0x4B400000;
-                    const float rk = fmaf(-(float)T, s, v);                   // exact residual
-                    float wv;                                                 // the reference's weight, core/GGMLComputeOps.kt:43-145
-                    if (TYPE == T_Q8_0) {
-                        wv = __fmul_rn(d, (float)(int8_t)bp[2 + k]);
-                    } else if (TYPE == T_BITNET_1_58) {                       // digit k % 5 of byte k / 5, core/GGMLTypes.kt:975-990
-                        const int g = (k * 13) >> 6;                          // k / 5 for k < 64
-                        uint32_t dv = bp[2 + g];
-                        for (int z = k - 5 * g; z > 0; z--) dv /= 3u;
-                        wv = __fmul_rn(d, (float)((int)(dv % 3u) - 1));
-                    } else {
-                        const uint8_t byte = bp[QOFF + (nib ? (k & 15) : (k >> 1))];
-                        const float q = (float)((nib ? (k >> 4) : (k & 1)) ? (byte >> 4) : (byte & 15));
-                        wv = TYPE == T_Q4_0 ? __fmul_rn(d, __fsub_rn(q, 8.0f)) : __fadd_rn(__fmul_rn(d, q), mq);
-                    }
-                    acc = fmaf(wv, rk, acc);
-                }
-                sum += acc;
+        while (m) {
+            const int bit = __ffs((int)m) - 1;
+            m &= m - 1;
+            const int j = idx++ & 7;
+            const int blk = w * 32 + bit;
+            const float s = __uint_as_float(xs[(size_t)blk * gemv_xslot_words(NP) + NP * 8 + 1]);
+            const float c = __frcp_rn(s);                                 // a power of two: exact
+            const int kk = blk * 32 + lane;
+            float v = CG ? __ldcg(b + kk) : b[kk];
+            if (pro_mode == 1) {                                          // the fused RMSNorm prologue, same roundings as prep_x
+                v = __fmul_rn(v, rinv);
+                if (pro_w) v = __fmul_rn(v, CG ? __ldcg(pro_w + kk) : pro_w[kk]);
             }
+            const int T = (int)__float_as_uint(fmaf(v, c, 12582912.0f)) - 0x4B400000;
+            const float rk = fmaf(-(float)T, s, v);                       // exact residual of this lane's element
+#pragma unroll 2
+            for (int r = warp; r < n; r += nwarps) {
+                const uint8_t *bp = a + (size_t)(row_first + r) * row_bytes + (size_t)blk * BBT;
+                const uint32_t hdr = __ldg((const unsigned short *)bp) | (TYPE == T_Q4_1 ? (uint32_t)__ldg((const unsigned short *)bp + 1) << 16 : 0u);
+                const uint32_t byte = __ldg(bp + QOFF + qb);
+                const float d = h2f((uint16_t)(hdr & 0xFFFFu));
+                float wv;                                                 // the reference's weight, core/GGMLComputeOps.kt:43-145
+                if (TYPE == T_Q8_0) {
+                    wv = __fmul_rn(d, (float)(int8_t)byte);
+                } else if (TYPE == T_BITNET_1_58) {                       // digit lane % 5 of byte lane / 5, core/GGMLTypes.kt:975-990
+                    uint32_t dv = byte;
+                    for (int z = lane - 5 * g5; z > 0; z--) dv /= 3u;
+                    wv = __fmul_rn(d, (float)((int)(dv % 3u) - 1));
+                } else {
+                    const float q = (float)(hi ? (byte >> 4) : (byte & 15u));
+                    wv = TYPE == T_Q4_0 ? __fmul_rn(d, __fsub_rn(q, 8.0f)) : __fadd_rn(__fmul_rn(d, q), h2f((uint16_t)(hdr >> 16)));
+                }
+                const float sum = warp_sum(__fmul_rn(wv, rk));
+                if (lane == 0) red[(size_t)r * red_stride + pad_col + j] += sum;
+            }
+            __syncwarp();
         }
-        red[(size_t)r * red_stride + pad_col + j] = sum;
     }
 }
 // The call: six arguments, everything else read through the pointer to the launch's (or the phase's) parameters — the

@@ -64,7 +64,7 @@ struct MPhase {
     int K, M, nblk, row_bytes;
     int stride;                // shared-memory row stride (bytes) of a staged row chunk: >= its bytes, = 16 mod 32
     int sr;                    // rows per stage (strip): 16
-    int nchunk, c0;            // a strip is staged as nchunk (1 or 2) column chunks: block pairs [0, c0) and [c0, nblk / 2)
+    int nchunk, c0;            // a strip is staged as nchunk column chunks of c0 block pairs each (the last one may be shorter)
     int rows_per_cta, rows_rem;   // M = rows_per_cta * grid + rows_rem
     int rows_max;              // rows of the largest CTA share (segment s starts at partial-sum row s * rows_max)
     int fix_gap, nib;
@@ -283,8 +283,8 @@ __device__ __forceinline__ void mc_convert8(const MPhase &p, uint8_t *xs, float4
     }
 }
 
-// Every consumer warp converts the activations of ITS OWN K-slices (tasks [t0, t0 + n0) and [t1, t1 + n1), at most 96 = three
-// rounds of 32 lanes) and nobody else reads them in the stage loop, so a warp starts multiplying as soon as its own slice of
+// Every consumer warp converts the activations of ITS OWN K-slices (its block pairs of every column chunk: at most 96 tasks =
+// three rounds of 32 lanes) and nobody else reads them in the stage loop, so a warp starts multiplying as soon as its own slice of
 // the mailbox has arrived: no CTA-wide barrier between the hand-off and the first MMA, and a late CTA of the previous phase
 // holds up only the warps whose slice it produces.  Everything a phase leaves in the header for its epilogue (range flags,
 // sum-of-squares partials) and the partial-sum buffer are double-buffered by phase parity, because a fast warp is already in
@@ -296,7 +296,7 @@ __device__ __forceinline__ void mc_convert8(const MPhase &p, uint8_t *xs, float4
 // memory system (profiles/r02i_mchain_small_shapes.txt).  Costs one more rounding per output (<= 2^-24 relative).
 template <int TYPE>
 __device__ __forceinline__ void mc_prep_warp(const MPhase &p, uint8_t *smem, const MChainParams &cp, int lane, int warp, const uint2 *mb, uint32_t epoch, int ph,
-                                             int t0, int n0, int t1, int n1) {
+                                             int nbp, int c0, int nchunk) {
     uint8_t *xs = smem + cp.x_off;
     float4 *sc = (float4 *)(smem + cp.sc_off);
     const int par = ph & 1;
@@ -304,13 +304,26 @@ __device__ __forceinline__ void mc_prep_warp(const MPhase &p, uint8_t *smem, con
     uint32_t *any = (uint32_t *)(smem + MC_OFF_ANY) + par;
     const bool norm = p.pro_mode == 1;
     const bool gain = norm && p.pro_w != nullptr;
-    const int nt = n0 + n1;
+    // this warp's tasks (8 activations each): the eight tasks of every block pair of its slice of every chunk, flattened
+    int nt = 0;
+#pragma unroll 1
+    for (int ch = 0; ch < nchunk; ch++) { const int cl = min(c0, nbp - ch * c0); nt += 8 * (((warp + 1) * cl) / MC_W - (warp * cl) / MC_W); }
     float ssq = 0.f;
 #pragma unroll 1
     for (int r = 0; 32 * r < nt; r++) {               // K = 4096: one round; K = 11008: three (one L2 round trip each)
         const int i = 32 * r + lane;
         const bool on = i < nt;
-        const int task = i < n0 ? t0 + i : t1 + (i - n0);
+        int task = 0;
+        {
+            int rem = i;
+#pragma unroll 1
+            for (int ch = 0; ch < nchunk; ch++) {
+                const int cs = ch * c0, cl = min(c0, nbp - cs);
+                const int pw = cs + (warp * cl) / MC_W, n = 8 * (cs + ((warp + 1) * cl) / MC_W - pw);
+                if (rem < n || ch == nchunk - 1) { task = 8 * pw + rem; break; }
+                rem -= n;
+            }
+        }
         float v[8];
 #pragma unroll
         for (int k = 0; k < 8; k++) v[k] = 0.f;
@@ -340,7 +353,12 @@ __device__ __forceinline__ void mc_prep_warp(const MPhase &p, uint8_t *smem, con
 }
 
 // ---- cold path of the range fix-up: sum_k w(i, k) * r_k, r_k = x_k - T_k s, for the flagged blocks of this CTA's rows,
-// into fix-up column j = (rank of the block among the flagged ones) & 7 of the row's partial sums (lk_gemv.cu gemv_fixup_body)
+// into fix-up column j = (rank of the block among the flagged ones) & 7 of the row's partial sums (the arithmetic of
+// lk_gemv.cu gemv_fixup_body; the per-block sum is a shuffle tree here instead of a serial chain).  Warp w owns the rows
+// w, w + 16, ... of the CTA's share (all segments) for EVERY flagged block, lane k owns element k of the block: one load of
+// the residual per lane and block, one byte and one scale per lane and row, so even a single flagged block is spread over the
+// whole CTA (the first version looped over the 32 elements inside one thread per row with a dependent L2 load each: ~9 us
+// per phase with one or two blocks flagged, twice the phase itself; profiles/r02m_layer_types.txt, Q4_1).
 template <int TYPE>
 __device__ __noinline__ void mc_fixup(const MPhase *pp, const MChainParams *cpp, uint8_t *smem, int r_begin, int nrows, const uint2 *mb, int par, float *part) {
     const MPhase &p = *pp;
@@ -349,50 +367,54 @@ __device__ __noinline__ void mc_fixup(const MPhase *pp, const MChainParams *cpp,
     const int nw = (p.nblk + 31) >> 5;
     constexpr int BB = block_bytes(TYPE);
     constexpr int QOFF = TYPE == T_Q4_1 ? 4 : 2;
+    const int warp = (int)threadIdx.x >> 5, lane = (int)threadIdx.x & 31;
+    const int total = p.nseg * nrows;
+    // this lane's byte and nibble of a block (Q4: Kotlin order byte k / 2, ggml order byte k % 16)
+    const int qb = TYPE == T_Q8_0 ? lane : (p.nib ? (lane & 15) : (lane >> 1));
+    const bool hi = TYPE != T_Q8_0 && (p.nib ? (lane >> 4) : (lane & 1));
+    // my rows' fix-up columns start at zero
+    for (int rr = warp + MC_W * (lane >> 3); rr < total; rr += MC_W * 4) {
+        const int seg = rr >= 2 * nrows ? 2 : rr >= nrows ? 1 : 0;
+        part[(size_t)(seg * p.rows_max + rr - seg * nrows) * MC_PS + MC_W + (lane & 7)] = 0.f;
+    }
+    __syncwarp();
+    int idx = 0;
 #pragma unroll 1
-    for (int item = (int)threadIdx.x; item < p.nseg * nrows * 8; item += MC_NCT) {
-        const int rr = item >> 3, j = item & 7;
-        const int seg = rr / nrows, r = rr - seg * nrows;
-        const uint8_t *rowp = p.a[seg] + (size_t)(r_begin + r) * p.row_bytes;
-        float sum = 0.f;
-        int idx = 0;
+    for (int w = 0; w < nw; w++) {
+        uint32_t m = mask[w];
 #pragma unroll 1
-        for (int w = 0; w < nw; w++) {
-            uint32_t m = mask[w];
-#pragma unroll 1
-            while (m) {
-                const int bit = __ffs((int)m) - 1;
-                m &= m - 1;
-                if ((idx++ & 7) != j) continue;
-                const int blk = w * 32 + bit;
-                const float s = sc[blk].x;
-                const float c = __frcp_rn(s);                                 // a power of two: exact
-                const uint8_t *bp = rowp + (size_t)blk * BB;
-                const float d = h2f((uint16_t)(bp[0] | (bp[1] << 8)));
-                float mq = 0.f;
-                if (TYPE == T_Q4_1) mq = h2f((uint16_t)(bp[2] | (bp[3] << 8)));
-                float acc = 0.f;
-#pragma unroll 1
-                for (int k = 0; k < 32; k++) {
-                    const int kk = blk * 32 + k;
-                    float v = p.from_mbox ? __uint_as_float(((const volatile uint2 *)mb)[kk].x) : __ldcg(p.b + kk);
-                    if (p.pro_mode == 1 && p.pro_w) v = __fmul_rn(v, __ldcg(p.pro_w + kk));      // y = x * gain, as in mc_prep
-                    const int T = (int)__float_as_uint(fmaf(v, c, 12582912.0f)) - 0x4B400000;
-                    const float rk = fmaf(-(float)T, s, v);                   // exact residual
-                    float wv;                                                 // the reference's weight, core/GGMLComputeOps.kt:43-145
-                    if (TYPE == T_Q8_0) {
-                        wv = __fmul_rn(d, (float)(int8_t)bp[2 + k]);
-                    } else {
-                        const uint8_t byte = bp[QOFF + (p.nib ? (k & 15) : (k >> 1))];
-                        const float q = (float)((p.nib ? (k >> 4) : (k & 1)) ? (byte >> 4) : (byte & 15));
-                        wv = TYPE == T_Q4_0 ? __fmul_rn(d, __fsub_rn(q, 8.0f)) : __fadd_rn(__fmul_rn(d, q), mq);
-                    }
-                    acc = fmaf(wv, rk, acc);
+        while (m) {
+            const int bit = __ffs((int)m) - 1;
+            m &= m - 1;
+            const int j = idx++ & 7;
+            const int blk = w * 32 + bit;
+            const float s = sc[blk].x;
+            const float c = __frcp_rn(s);                                 // a power of two: exact
+            const int kk = blk * 32 + lane;
+            float v = p.from_mbox ? __uint_as_float(mc_ld_pair(mb + kk).x) : __ldcg(p.b + kk);
+            if (p.pro_mode == 1 && p.pro_w) v = __fmul_rn(v, __ldcg(p.pro_w + kk));      // y = x * gain, as in mc_prep_warp
+            const int T = (int)__float_as_uint(fmaf(v, c, 12582912.0f)) - 0x4B400000;
+            const float rk = fmaf(-(float)T, s, v);                       // exact residual of this lane's element
+#pragma unroll 2
+            for (int rr = warp; rr < total; rr += MC_W) {
+                const int seg = rr >= 2 * nrows ? 2 : rr >= nrows ? 1 : 0;
+                const int r = rr - seg * nrows;
+                const uint8_t *bp = p.a[seg] + (size_t)(r_begin + r) * p.row_bytes + (size_t)blk * BB;
+                const uint32_t hdr = __ldg((const unsigned short *)bp) | (TYPE == T_Q4_1 ? (uint32_t)__ldg((const unsigned short *)bp + 1) << 16 : 0u);
+                const uint32_t byte = __ldg(bp + QOFF + qb);
+                const float d = h2f((uint16_t)(hdr & 0xFFFFu));
+                float wv;                                                 // the reference's weight, core/GGMLComputeOps.kt:43-145
+                if (TYPE == T_Q8_0) {
+                    wv = __fmul_rn(d, (float)(int8_t)byte);
+                } else {
+                    const float q = (float)(hi ? (byte >> 4) : (byte & 15u));
+                    wv = TYPE == T_Q4_0 ? __fmul_rn(d, __fsub_rn(q, 8.0f)) : __fadd_rn(__fmul_rn(d, q), h2f((uint16_t)(hdr >> 16)));
                 }
-                sum += acc;
+                const float sum = warp_sum(__fmul_rn(wv, rk));
+                if (lane == 0) part[(size_t)(seg * p.rows_max + r) * MC_PS + MC_W + j] += sum;
             }
+            __syncwarp();
         }
-        part[(size_t)(seg * p.rows_max + r) * MC_PS + MC_W + j] = sum;
     }
 }
 
@@ -528,8 +550,8 @@ __global__ void __launch_bounds__((MC_W + MC_PW) * 32, 1) gemv_mchain_kernel(con
                     const int rows = min(sr, left);
 #pragma unroll 1
                     for (int ch = 0; ch < nchunk; ch++) {
-                        const uint32_t cbytes = (uint32_t)((ch == 0 ? c0 : nbp - c0) * PAIR_B);     // bytes of one row of this chunk
-                        const uint8_t *csrc = src + (ch == 0 ? 0 : c0 * PAIR_B);
+                        const uint32_t cbytes = (uint32_t)(min(c0, nbp - ch * c0) * PAIR_B);     // bytes of one row of this chunk
+                        const uint8_t *csrc = src + (size_t)ch * c0 * PAIR_B;
                         const uint32_t bytes = (uint32_t)(rows * stride);
                         if (wr + bytes > (uint32_t)cp.ring_bytes) wr = 0;
                         // the slot's barrier pair and the ring bytes must be free: wait for the oldest stages, in order, until they are
@@ -619,11 +641,10 @@ __global__ void __launch_bounds__((MC_W + MC_PW) * 32, 1) gemv_mchain_kernel(con
         const uint2 *mb = cp.mbox + (size_t)par * MC_KMAX;          // this phase's activations, if they come by mailbox
         const uint32_t epoch = epoch0 + (uint32_t)ph + 1u;
         const bool norm = p.pro_mode == 1;
-        // this warp's K-slice of each column chunk: block pairs [pw0, pw0 + np0) of chunk 0, [pw1, pw1 + np1) of chunk 1
+        // this warp's K-slice of column chunk ch (block pairs [ch c0, ch c0 + cl), cl = min(c0, nbp - ch c0)): pairs
+        // [ch c0 + (warp cl) / 16, ch c0 + ((warp + 1) cl) / 16)
         const int nbp = p.nblk >> 1, c0 = p.c0, nchunk = p.nchunk, stride = p.stride, sr = p.sr, nseg = p.nseg, rows_max = p.rows_max;
-        const int pw0 = (warp * c0) / MC_W, np0 = ((warp + 1) * c0) / MC_W - pw0;
-        const int c1n = nbp - c0;
-        const int pw1 = c0 + (warp * c1n) / MC_W, np1 = c0 + ((warp + 1) * c1n) / MC_W - pw1;
+        const int pw0 = (warp * min(c0, nbp)) / MC_W;           // first pair of the slice of chunk 0
         // side loads whose latency hides under the stage loop: the residual of this thread's output row, and this CTA's 1/grid
         // slice of the normalised activations (the unfused RMSNorm node's tensor, stored in the epilogue)
         float res_pre = 0.f;
@@ -638,7 +659,7 @@ __global__ void __launch_bounds__((MC_W + MC_PW) * 32, 1) gemv_mchain_kernel(con
             if (p.pro_w) bo_g = __ldcg(p.pro_w + bo_k);
         }
         // activations of this warp's slices -> planes + table (no CTA barrier: see mc_prep_warp)
-        mc_prep_warp<TYPE>(p, smem, cp, lane, warp, mb, epoch, ph, 8 * pw0, 8 * np0, 8 * pw1, 8 * np1);
+        mc_prep_warp<TYPE>(p, smem, cp, lane, warp, mb, epoch, ph, nbp, c0, nchunk);
         if (tid == 0) MC_TL(ph, 3);
         // K = 4096: four pairs per warp, B fragments and table entries stay in registers for the phase
         const bool res4 = nchunk == 1 && nbp == 4 * MC_W;
@@ -671,8 +692,9 @@ __global__ void __launch_bounds__((MC_W + MC_PW) * 32, 1) gemv_mchain_kernel(con
                     if (first_stage && tid == 0) { MC_TL(ph, 4); first_stage = false; }
 #endif
                     const uint32_t sbase = ring_base + mc_lds32(smem_base + MC_OFF_STAGE + (slot8 >> 1));
-                    const int pw = ch == 0 ? pw0 : pw1, npw = ch == 0 ? np0 : np1;
-                    const uint32_t coff = (uint32_t)((pw - (ch == 0 ? 0 : c0)) * 2 * BB);     // this warp's first pair within the staged chunk
+                    const int cs = ch * c0, cl = min(c0, nbp - cs);
+                    const int pw = cs + (warp * cl) / MC_W, npw = cs + ((warp + 1) * cl) / MC_W - pw;
+                    const uint32_t coff = (uint32_t)((pw - cs) * 2 * BB);     // this warp's first pair within the staged chunk
                     const uint32_t pa0 = sbase + ro_a + coff + a_lane, pa1 = sbase + ro_b + coff + a_lane;
                     const uint32_t pd0 = sbase + ro_a + coff + d_lane, pd1 = sbase + ro_b + coff + d_lane;
                     float acc0 = 0.f, acc1 = 0.f;
@@ -808,12 +830,19 @@ cudaError_t launch_gemv_mchain(int type, int n, const GemvChainLink *links, cons
         p.nblk = (int)(K / 32);
         p.row_bytes = p.nblk * bb;
         if (p.row_bytes % 16) return cudaErrorNotSupported;                  // one bulk copy per row
-        // a strip of 16 rows is staged whole if it fits ~42 KB, else as two column chunks (boundary at a multiple of 4 block
-        // pairs: every row chunk is then a 16-byte multiple at a 16-byte aligned address)
+        // a strip of 16 rows is staged whole if it fits ~42 KB, else as up to 8 equal column chunks (boundaries at multiples of 4
+        // block pairs: every row chunk is then a 16-byte multiple at a 16-byte aligned address)
         const int nbp = p.nblk / 2;
         p.sr = 16;
         p.nchunk = 1; p.c0 = nbp;
-        if (16 * (p.row_bytes + 16) > 42 * 1024) { p.nchunk = 2; p.c0 = ((nbp / 4 + 1) / 2) * 4; }
+        while (p.nchunk < 8 && 16 * (p.c0 * 2 * bb + 16) > 42 * 1024) {      // (nbp is a multiple of 4: K % 256 == 0)
+            p.nchunk++;
+            p.c0 = ((nbp / 4 + p.nchunk - 1) / p.nchunk) * 4;
+        }
+        p.nchunk = (nbp + p.c0 - 1) / p.c0;
+        // Q8_0 rows longer than two chunks: K1c's DP4A on whole bytes is the faster chain there (7B layer graph, same box:
+        // 54.9 us per layer on K1c, 58.4 on K1m with five chunks per strip; profiles/r02m_layer_types.txt)
+        if (type == T_Q8_0 && p.nchunk > 2) return cudaErrorNotSupported;
         const int cb = p.c0 * 2 * bb;                                        // bytes of the larger chunk of a row
         p.stride = cb + ((cb % 32) == 16 ? 0 : 16);                          // stride / 4 = 4 mod 8
         if (p.sr * p.stride > 56 * 1024) return cudaErrorNotSupported;

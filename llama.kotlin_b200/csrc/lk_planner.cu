@@ -255,10 +255,11 @@ struct Planner {
             pending.clear();
         };
         // the planner's own choice (chain_mode < 0): chain where it was measured to pay: graphs with an attention step
-        // between the runs (either chained kernel), and graphs whose decode GEMVs K1m takes (Q4_0, K % 256 == 0: 36.5 against
-        // 39.4 us per 7B layer as separate launches, profiles/r02j_layer_ab_per_warp_prep.txt)
+        // between the runs (either chained kernel), and graphs whose decode GEMVs all have K % 256 == 0 (K1m takes Q4_0 / Q4_1 and
+        // short Q8_0 rows, K1c the rest; per 7B layer, chained against separate launches: Q4_0 36.5 / 39.4 us, Q4_1 36.6 / 39.2,
+        // Q8_0 54.9 / 61.5; profiles/r02j_layer_ab_per_warp_prep.txt, r02m_layer_types.txt)
         bool k1m = !gemv.empty();
-        for (int i : gemv) k1m = k1m && nodes[i].src[0].type == LK_TYPE_Q4_0 && nodes[i].src[0].ne[0] % 256 == 0;
+        for (int i : gemv) k1m = k1m && nodes[i].src[0].ne[0] % 256 == 0;      // (every decode GEMV type has a chained kernel: is_gemv)
         const bool chain = chain_mode < 0 ? (!steps.empty() || k1m) : chain_mode != 0;
         for (int i = 0; i < n; i++) {
             if (skip.count(i) || (!pending.empty() && nodes[i].op == LK_OP_NONE)) continue;

@@ -468,8 +468,8 @@ class GGMLCudaBackend:
             for c in range(0, len(items), self.maxChain):
                 self._runChain(ga, nodes, items[c:c + self.maxChain], rms_of, add_of, stored)
 
-        # chainOps None: graphs with an attention step, and graphs whose decode GEMVs K1m takes (lk_planner.cu has the same rule)
-        k1m = bool(self._gemv) and all(nodes[i].src[0].type == GGMLType.Q4_0 and int(nodes[i].src[0].ne[0]) % 256 == 0 for i in self._gemv)
+        # chainOps None: graphs with an attention step, and graphs whose decode GEMVs all have K % 256 == 0 (lk_planner.cu has the same rule)
+        k1m = bool(self._gemv) and all(int(nodes[i].src[0].ne[0]) % 256 == 0 for i in self._gemv)
         chain = (bool(self._steps) or k1m) if self.chainOps is None else bool(self.chainOps)
         for i, node in enumerate(nodes):
             if i in skip or (pending and node.op == GGMLOp.NONE and not isinstance(node.extra, dict)):

@@ -79,7 +79,7 @@ def test_chain_equals_the_links_one_by_one(O, tname, hidden, ffn, mma):
     took_mma = be.lk.get_option("gemv_chain_mma_launches") - m0
     if not mma or hidden % 256 or ffn % 256:
         assert took_mma == 0
-    elif tname == "Q4_0" or ffn <= 4096:          # (Q8_0 rows of K = 11008 do not fit K1m's two column chunks: K1c)
+    elif tname != "Q8_0" or ffn <= 4096:          # (Q8_0 rows of K = 11008 would need five column chunks: K1c is the faster chain there)
         assert took_mma == 1
     for k in one:
         if took_mma:

@@ -89,14 +89,14 @@ def test_one_position_context_keeps_four_launches_per_layer(monkeypatch):
 
 def test_one_position_context_chains_what_the_mma_chain_kernel_takes(monkeypatch):
     """The planner's own choice: Q4_0 GEMVs with K % 256 == 0 (K1m, lk_gemv_mma.cu, takes them) go out as one chained launch
-    even without an attention step; another weight type or one K that is not a multiple of 256 keeps the separate launches."""
+    even without an attention step (so do the other two block types); one K that is not a multiple of 256 keeps the separate launches."""
     ga, graph = make_graph(2, hidden=256, ffn=768)
     calls = run(make_backend(None), ga, graph, Recorder(), monkeypatch)
     assert [c[0] for c in calls] == ["chain"] and len(calls[0][1]) == 8
     ga, graph = make_graph(2, hidden=256, ffn=704)                  # the down projection's K = 704
     assert [c[0] for c in run(make_backend(None), ga, graph, Recorder(), monkeypatch)] == ["fused"] * 8
-    ga, graph = make_graph(2, hidden=256, ffn=768, qtype=GGMLType.Q8_0)
-    assert [c[0] for c in run(make_backend(None), ga, graph, Recorder(), monkeypatch)] == ["fused"] * 8
+    ga, graph = make_graph(2, hidden=256, ffn=768, qtype=GGMLType.Q8_0)          # every type has a chained kernel
+    assert [c[0] for c in run(make_backend(None), ga, graph, Recorder(), monkeypatch)] == ["chain"]
 
 
 def test_explicit_chain_takes_all_dependent_launches(monkeypatch):
