@@ -541,6 +541,7 @@ def config2_arm(args, rank, world, local_rank, lk, be, dist, torch, brief: bool 
         res["config"]["other_paths"] = {"prefill_gemm": prefill_gemm_line(lk, be, peaks),
                                         "layer_graph": layer_graph_line(lk, be, peak),
                                         "layer_graph_ctx2048": layer_graph_line(lk, be, peak, ctx_len=2048),
+                                        "layer_graph_q8_0": layer_graph_line(lk, be, peak, qtype="Q8_0"),
                                         "gemv_act16": act16_line(lk, be, graph, step_device, args, bytes_step, peak,
                                                                  protos, x_host, y_host, ga, dst_all, qtype),
                                         "elementwise": elementwise_lines(lk, be, peak),
@@ -659,12 +660,12 @@ def prefill_gemm_line(lk, be, peaks) -> dict:
                          "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (cuBLAS bf16, same 16-bit tensor pipe)"}}
 
 
-def layer_graph_line(lk, be, hbm_peak, ctx_len: int = 0) -> dict:
+def layer_graph_line(lk, be, hbm_peak, ctx_len: int = 0, qtype: str = "Q4_0") -> dict:
     """BASELINE config 4: 32-layer synthetic Llama-2-7B decode step as one GGMLCGraph (tools/layer_bench.py); with
     ctx_len > 0 the layer also carries RoPE, the KV-cache append and decode attention over that many positions."""
     sys.path.insert(0, os.path.join(ROOT, "tools"))
     import layer_bench
-    return layer_bench.run(lk, be, "Q4_0", layers=32, steps=30, warmup=3, hbm_peak_gbs=hbm_peak, ctx_len=ctx_len)
+    return layer_bench.run(lk, be, qtype, layers=32, steps=30, warmup=3, hbm_peak_gbs=hbm_peak, ctx_len=ctx_len)
 
 
 def act16_line(lk, be, graph, step_device, args, bytes_step, peak, protos, x_host, y_host, ga, dst_all, qtype) -> dict:

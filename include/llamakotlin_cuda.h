@@ -365,7 +365,7 @@ typedef struct lk_plan_launch {
     int32_t attn[5];             /* LK_PLAN_ATTN_STEP: ROPE(q), ROPE(k), CPY(k), CPY(v), FLASH_ATTN */
 } lk_plan_launch;
 /* chain_mode: -1 = where it was measured to pay (graphs with an attention step between the runs, and graphs whose decode
- * GEMVs are all Q4_0 with K % 256 == 0: the MMA chain kernel takes those), 0 never, 1 always */
+ * GEMVs all have K % 256 == 0: the MMA chain kernel K1m takes Q4_0 / Q4_1 and short Q8_0 rows, K1c the rest), 0 never, 1 always */
 LK_API lk_status   lk_graph_plan(const lk_graph_node *nodes, int32_t n, int32_t chain_mode, lk_plan_launch *out,
                                  int32_t max_out, int32_t *n_out);
 #define LK_GRAPH_NO_FUSION    1   /* node by node, like the reference's interpreter */

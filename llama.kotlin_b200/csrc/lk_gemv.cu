@@ -680,6 +680,71 @@ enum { GEMV_WAIT_FULL = 0, GEMV_WAIT_X = 1, GEMV_WAIT_END = 2 };
 #ifndef LK_FIXUP_ATTR           // A/B builds only (tools/ab_build.sh)
 #define LK_FIXUP_ATTR __noinline__
 #endif
+// First version of the work split, kept for the stand-alone launches: one thread per (row, column) walks the flagged blocks'
+// 32 elements.  Slow when it runs (~9 us with one or two blocks flagged) but it never does on natural activations, and the
+// stand-alone kernels are compiled around it: with the cooperative version below as their callee ptxas schedules the hot
+// kernels differently (72 / 84 instead of 71 / 86 registers) and the headline step loses 2 % (4580-4590 -> 4487-4503 GB/s,
+// same box, three runs each) although the path is never taken.  The chained kernel K1c takes the cooperative version.
+template <int TYPE, int NP, bool CG>
+__device__ __forceinline__ void gemv_fixup_body_rows(const uint8_t *a, const float *b, const float *pro_w, int pro_mode, int nib, int row_bytes,
+                                                int nblk, int red_stride, int pad_col, int row_first, int n, float *red, const uint32_t *xs,
+                                                const GemvSide *side, int tid, int nct) {
+    const int nw = (nblk + 31) >> 5;
+    const float rinv = side->rinv;
+#pragma unroll 1
+    for (int item = tid; item < n * GEMV_RED_PAD; item += nct) {
+        const int r = item >> 3, j = item & 7;
+        const uint8_t *rowp = a + (size_t)(row_first + r) * row_bytes;
+        float sum = 0.f;
+        int idx = 0;
+#pragma unroll 1
+        for (int w = 0; w < nw; w++) {
+            uint32_t m = side->mask[w];
+#pragma unroll 1
+            while (m) {
+                const int bit = __ffs((int)m) - 1;
+                m &= m - 1;
+                if ((idx++ & 7) != j) continue;
+                const int blk = w * 32 + bit;
+                const float s = __uint_as_float(xs[(size_t)blk * gemv_xslot_words(NP) + NP * 8 + 1]);
+                const float c = __frcp_rn(s);                                 // a power of two: exact
+                const uint8_t *bp = rowp + (size_t)blk * (TYPE == T_BITNET_1_58 ? 10 : block_bytes(TYPE));
+                const float d = h2f((uint16_t)(bp[0] | (bp[1] << 8)));
+                float mq = 0.f;
+                if (TYPE == T_Q4_1) mq = h2f((uint16_t)(bp[2] | (bp[3] << 8)));
+                constexpr int QOFF = TYPE == T_Q4_1 ? 4 : 2;
+                float acc = 0.f;
+#pragma unroll 1
+                for (int k = 0; k < 32; k++) {
+                    const int kk = blk * 32 + k;
+                    float v = CG ? __ldcg(b + kk) : b[kk];
+                    if (pro_mode == 1) {                                      // the fused RMSNorm prologue, same roundings as prep_x
+                        v = __fmul_rn(v, rinv);
+                        if (pro_w) v = __fmul_rn(v, CG ? __ldcg(pro_w + kk) : pro_w[kk]);
+                    }
+                    const int T = (int)__float_as_uint(fmaf(v, c, 12582912.0f)) - 0x4B400000;
+                    const float rk = fmaf(-(float)T, s, v);                   // exact residual
+                    float wv;                                                 // the reference's weight, core/GGMLComputeOps.kt:43-145
+                    if (TYPE == T_Q8_0) {
+                        wv = __fmul_rn(d, (float)(int8_t)bp[2 + k]);
+                    } else if (TYPE == T_BITNET_1_58) {                       // digit k % 5 of byte k / 5, core/GGMLTypes.kt:975-990
+                        const int g = (k * 13) >> 6;                          // k / 5 for k < 64
+                        uint32_t dv = bp[2 + g];
+                        for (int z = k - 5 * g; z > 0; z--) dv /= 3u;
+                        wv = __fmul_rn(d, (float)((int)(dv % 3u) - 1));
+                    } else {
+                        const uint8_t byte = bp[QOFF + (nib ? (k & 15) : (k >> 1))];
+                        const float q = (float)((nib ? (k >> 4) : (k & 1)) ? (byte >> 4) : (byte & 15));
+                        wv = TYPE == T_Q4_0 ? __fmul_rn(d, __fsub_rn(q, 8.0f)) : __fadd_rn(__fmul_rn(d, q), mq);
+                    }
+                    acc = fmaf(wv, rk, acc);
+                }
+                sum += acc;
+            }
+        }
+        red[(size_t)r * red_stride + pad_col + j] = sum;
+    }
+}
 // Work split (round 2, second version): warp w owns rows w, w + nwarps, ... for EVERY flagged block and lane k owns element k
 // of the block — one residual per lane and block, one quant byte and one scale per lane and row, the block's sum by a shuffle
 // tree — so a single flagged block is spread over the whole CTA.  The first version gave each (row, column) to one thread
@@ -752,9 +817,14 @@ __device__ __forceinline__ void gemv_fixup_body(const uint8_t *a, const float *b
 // NCT > 0: compile-time thread count (chained kernel); else cwarps * 32.  FUSED: the launch may carry the RMSNorm prologue.
 template <int TYPE, int NP, int CG, bool FUSED, int NCT>
 __device__ LK_FIXUP_ATTR void gemv_fixup(const GemvParams *pp, const uint8_t *a, int row_first, int n, float *red, const uint8_t *smem) {
-    gemv_fixup_body<TYPE, NP, CG != 0>(a, pp->b, FUSED ? pp->pro_w : nullptr, FUSED ? pp->pro_mode : 0, pp->nib, pp->row_bytes, pp->nblk,
-                                       pp->red_stride, pp->ncw * 8, row_first, n, red, (const uint32_t *)(smem + pp->x_off),
-                                       (const GemvSide *)(smem + GEMV_SIDE_OFF), (int)threadIdx.x, NCT > 0 ? NCT : pp->cwarps * 32);
+    if (NCT > 0)       // the chained kernel
+        gemv_fixup_body<TYPE, NP, CG != 0>(a, pp->b, FUSED ? pp->pro_w : nullptr, FUSED ? pp->pro_mode : 0, pp->nib, pp->row_bytes, pp->nblk,
+                                           pp->red_stride, pp->ncw * 8, row_first, n, red, (const uint32_t *)(smem + pp->x_off),
+                                           (const GemvSide *)(smem + GEMV_SIDE_OFF), (int)threadIdx.x, NCT);
+    else
+        gemv_fixup_body_rows<TYPE, NP, CG != 0>(a, pp->b, FUSED ? pp->pro_w : nullptr, FUSED ? pp->pro_mode : 0, pp->nib, pp->row_bytes, pp->nblk,
+                                                pp->red_stride, pp->ncw * 8, row_first, n, red, (const uint32_t *)(smem + pp->x_off),
+                                                (const GemvSide *)(smem + GEMV_SIDE_OFF), (int)threadIdx.x, pp->cwarps * 32);
 }
 
 // cross-lane part of the final reduction: 8 lanes per row, 4 rows per warp per pass
