@@ -553,19 +553,30 @@ DTYPE = ("f32 output; inner products int4/int8 x 24-bit block-fixed-point activa
          "F32 scales and F32 sums across blocks (K1); tcgen05 GEMM: FP16 hi+lo operand pairs, F32 accumulation (K2)")
 
 
-def measured_traffic(qtype: str) -> dict:
-    """roofline.traffic = DRAM bytes per launch from an ncu capture of THIS binary (tools/measure_traffic.py writes
-    profiles/gemv_traffic.json with the library's sha256); a record taken from another build is not reported."""
+def kernel_sources_sha256() -> str:
+    """sha256 over the CUDA sources the library is built from (csrc/*.cu, *.cuh, *.h, Makefile, sorted by name).  The built
+    .so itself is not reproducible byte for byte (two builds of identical sources differ), so a record keyed on its hash
+    would be lost with every rebuild; identical sources give the same kernels."""
+    import glob
     import hashlib
+    h = hashlib.sha256()
+    d = os.path.join(ROOT, "llama.kotlin_b200", "csrc")
+    for path in sorted(glob.glob(os.path.join(d, "*.cu")) + glob.glob(os.path.join(d, "*.cuh")) + glob.glob(os.path.join(d, "*.h")) + [os.path.join(d, "Makefile")]):
+        h.update(os.path.basename(path).encode())
+        with open(path, "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()
+
+
+def measured_traffic(qtype: str) -> dict:
+    """roofline.traffic = DRAM bytes per launch from an ncu capture of THIS library (tools/measure_traffic.py writes
+    profiles/gemv_traffic.json with the hash of the kernel sources); a record taken from other sources is not reported."""
     path = os.path.join(ROOT, "profiles", "gemv_traffic.json")
-    lib = os.path.join(ROOT, "llama.kotlin_b200", "libllamakotlin_cuda.so")
-    out = {"traffic": None, "traffic_source": "no ncu capture of this binary (profiles/gemv_traffic.json is from another build)"}
+    out = {"traffic": None, "traffic_source": "no ncu capture of these kernel sources (profiles/gemv_traffic.json is from another build)"}
     try:
         with open(path) as f:
             rec = json.load(f)
-        with open(lib, "rb") as f:
-            sha = hashlib.sha256(f.read()).hexdigest()
-        if rec.get("library_sha256") == sha and rec.get(qtype) is not None:
+        if rec.get("sources_sha256") == kernel_sources_sha256() and rec.get(qtype) is not None:
             out = {"traffic": rec[qtype], "traffic_source": rec.get("how", "ncu dram__bytes_read.sum + dram__bytes_write.sum, mean per launch")}
     except (OSError, ValueError):
         pass

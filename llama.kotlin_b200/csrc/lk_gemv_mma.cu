@@ -20,7 +20,7 @@
 //     of one block -> I = c0 + (c1 << 8) exactly, one I2F, then F32 with the block's d (read from the row), the
 //     activation scale and the -8 s sumT term from a small per-block table: 13 instructions per row pair and block pair.
 // About 42 instructions per 1024 weight elements per warp instead of 62, the FMA pipe nearly idle, and all 16 consumer
-// warps work in every phase: a stage is one strip of <= 16 rows (8 for rows longer than 5 KB), warp w takes K-slice w
+// warps work in every phase: a stage is one strip of <= 16 rows (rows longer than ~2.6 KB in equal column chunks), warp w takes K-slice w
 // of it, parks its two row sums per lane quad in shared memory (no per-stage CTA barrier), one fixed-order reduction
 // per phase.  Rows are staged with one 1-D TMA bulk copy each at a padded stride (stride / 4 = 4 mod 8: the eight rows
 // a load instruction touches fall into different banks), in a byte ring of variable-size stages whose offsets the

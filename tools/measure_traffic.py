@@ -1,8 +1,8 @@
 #!/usr/bin/env python
 """roofline.traffic from an ncu capture of THIS binary: reads an .ncu-rep taken with `ncu --set full -k regex:gemv_kernel`
 over consecutive launches of the bench step (the three Llama-2-7B shapes in turn), takes dram__bytes_read.sum +
-dram__bytes_write.sum per launch, and writes profiles/gemv_traffic.json with the library's sha256 — bench.py reports the
-figure only while the library it times has that hash.   python tools/measure_traffic.py gpurun_out/prof.ncu-rep [Q4_0]"""
+dram__bytes_write.sum per launch, and writes profiles/gemv_traffic.json with the hash of the kernel sources (the built .so is
+not reproducible byte for byte) — bench.py reports the figure only while the sources it was built from have that hash.   python tools/measure_traffic.py gpurun_out/prof.ncu-rep [Q4_0]"""
 import csv
 import hashlib
 import io
@@ -30,8 +30,9 @@ def main():
            for r in data if "gemv_kernel" in r[ik]]
     if not per:
         sys.exit("no gemv_kernel launch in the report")
-    sha = hashlib.sha256(open(LIB, "rb").read()).hexdigest()
-    rec = {qtype: sum(p["bytes"] for p in per) / len(per), "launches": per, "library_sha256": sha,
+    sys.path.insert(0, ROOT)
+    from bench import kernel_sources_sha256
+    rec = {qtype: sum(p["bytes"] for p in per) / len(per), "launches": per, "sources_sha256": kernel_sources_sha256(),
            "how": f"ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum, mean over {len(per)} consecutive launches of the bench step ({os.path.basename(rep)})"}
     with open(os.path.join(ROOT, "profiles", "gemv_traffic.json"), "w") as f:
         json.dump(rec, f, indent=1)
