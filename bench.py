@@ -544,6 +544,7 @@ def config2_arm(args, rank, world, local_rank, lk, be, dist, torch, brief: bool 
                                         "layer_graph_q8_0": layer_graph_line(lk, be, peak, qtype="Q8_0"),
                                         "gemv_act16": act16_line(lk, be, graph, step_device, args, bytes_step, peak,
                                                                  protos, x_host, y_host, ga, dst_all, qtype),
+                                        "gemv_other_types": gemv_types_line(lk, be, peak, args.layers),
                                         "elementwise": elementwise_lines(lk, be, peak),
                                         "ffn70b_1gpu": ffn70b_line(lk, be, dist, peak)}
     return res
@@ -580,6 +581,69 @@ def measured_traffic(qtype: str) -> dict:
             out = {"traffic": rec[qtype], "traffic_source": rec.get("how", "ncu dram__bytes_read.sum + dram__bytes_write.sum, mean per launch")}
     except (OSError, ValueError):
         pass
+    return out
+
+
+def gemv_types_line(lk, be, peak, layers: int) -> dict:
+    """BASELINE configs 1 and 2 name Q8_0 and Q4_1 beside Q4_0: the headline step (layers x the three 7B shapes, every GEMV
+    with its own weights, activations and output, weights > L2) with those block types, device-timed like `value`; four rows
+    of the first GEMV of every shape are checked against f64 arithmetic on the same bytes."""
+    from llama_kotlin_b200 import GGMLCGraph, GGMLOp, GGMLTensor, GGMLType
+    out = {}
+    for qtype in ("Q4_1", "Q8_0"):
+        gt = getattr(GGMLType, qtype)
+        bb = BLOCK_BYTES[qtype]
+        rng = np.random.default_rng(97)
+        wbytes = sum(M * K // 32 * bb + 256 for M, K in SHAPES)
+        vec = sum((M + K + 128) * 4 for M, K in SHAPES)
+        ga = lk.GGMLGraphAllocator(be, size=layers * (wbytes + vec) + (4 << 20))
+        protos = [synth_blocks(rng, M, K, qtype) for M, K in SHAPES]
+        firsts, nodes, xs, chk = [None] * len(SHAPES), [], [], []
+        for li in range(layers):
+            for si, (M, K) in enumerate(SHAPES):
+                a = ga.allocateTensor(GGMLTensor(gt, [K, M]))
+                if firsts[si] is None:
+                    ga.setBytes(a, protos[si])
+                    firsts[si] = a
+                else:
+                    ga.deviceBuffer.copyTensor(firsts[si], a)
+                b = ga.allocateTensor(GGMLTensor(GGMLType.F32, [1, K]))
+                x = rng.normal(0, 1, K).astype(np.float32)
+                ga.setBytes(b, x)
+                d = ga.allocateTensor(GGMLTensor(GGMLType.F32, [1, M], op=GGMLOp.MUL_MAT, src=[a, b] + [None] * 8))
+                nodes.append(d)
+                if li == 0:
+                    chk.append((si, M, K, x, d))
+        graph = GGMLCGraph(nodes=nodes, allocator=ga)
+        ok = True
+        for _ in range(3):
+            ok = ok and be.graphCompute(graph) == lk.GGMLStatus.SUCCESS
+        be.lk.sync()
+        reps = 20
+        be.lk.timer_start()
+        for _ in range(reps):
+            be.graphCompute(graph)
+        ms = be.lk.timer_stop() / reps
+        err = 0.0
+        for si, M, K, x, d in chk:                     # rows 0..3 in f64 from the packed bytes (the reference's accessors)
+            blk = protos[si].reshape(M, K // 32, bb)[:4]
+            dsc = blk[:, :, 0:2].copy().view(np.float16).astype(np.float64)[:, :, 0]
+            if qtype == "Q8_0":
+                w = blk[:, :, 2:].view(np.int8).astype(np.float64) * dsc[:, :, None]
+            else:
+                mn = blk[:, :, 2:4].copy().view(np.float16).astype(np.float64)[:, :, 0]
+                q = blk[:, :, 4:]
+                nib = np.stack([q & 15, q >> 4], axis=-1).reshape(4, K // 32, 32).astype(np.float64)    # byte j = elements 2j, 2j + 1
+                w = nib * dsc[:, :, None] + mn[:, :, None]
+            ref = w.reshape(4, K) @ x.astype(np.float64)
+            got = ga.getFloats(d)[:4].astype(np.float64)
+            err = max(err, float(np.max(np.abs(got - ref)) / max(np.max(np.abs(ref)), 1e-30)))
+        nbytes = layers * sum(algo_bytes(M, K, bb) for M, K in SHAPES)
+        gbs = nbytes / (ms * 1e-3) / 1e9
+        out[qtype] = {"GBps": gbs, "ms_per_step": ms, "gemv_per_step": len(nodes), "frac_of_measured_hbm": gbs / peak if peak else None,
+                      "max_err_vs_f64_rows": err, "ok": bool(ok and err <= 1e-3)}
+        be.forgetGraph(graph)
+        ga.deviceBuffer.free()
     return out
 
 
