@@ -43,12 +43,13 @@ constexpr int MC_NB = 8;                // stages in flight (mbarrier pairs)
 constexpr int MC_PS = 25;               // floats per row of the partial-sum buffer: 16 K-slices, 8 fix-up columns, 1 pad (odd stride)
 constexpr int MC_HDR = 512;             // header bytes of dynamic shared memory
 constexpr int MC_XB = 96;               // bytes of activation planes per block: 3 planes x 2 halves x 16
-constexpr int MC_MASK_WORDS = 12;       // range flags: K <= 12288
+constexpr int MC_MASK_WORDS = 16;       // range flags: K <= 16384 (Llama-2-13B's down projection: 13824)
 constexpr int MC_KMAX = GEMV_MCHAIN_KMAX;   // longest activation vector a mailbox buffer holds
 
 // header layout (bytes): 0 full[8] | 64 empty[8] | 128 stage_off[8] | 160 any[2] | 168 epoch base | 176 zero[4] |
-//                        192 mask[2][12] | 288 sum-of-squares partials[2][16]       ([2]: by phase parity, see mc_prep_warp)
-constexpr int MC_OFF_STAGE = 128, MC_OFF_ANY = 160, MC_OFF_EPOCH = 168, MC_OFF_ZERO = 176, MC_OFF_MASK = 192, MC_OFF_RMS = 288;
+//                        192 mask[2][16] | 320 sum-of-squares partials[2][16]       ([2]: by phase parity, see mc_prep_warp)
+constexpr int MC_OFF_STAGE = 128, MC_OFF_ANY = 160, MC_OFF_EPOCH = 168, MC_OFF_ZERO = 176, MC_OFF_MASK = 192, MC_OFF_RMS = 320;
+static_assert(MC_OFF_MASK + 2 * MC_MASK_WORDS * 4 <= MC_OFF_RMS && MC_OFF_RMS + 2 * MC_W * 4 <= MC_HDR, "header layout");
 
 struct MPhase {
     const uint8_t *a[3];       // weight segments (identical shape), 16-byte aligned
@@ -283,8 +284,8 @@ __device__ __forceinline__ void mc_convert8(const MPhase &p, uint8_t *xs, float4
     }
 }
 
-// Every consumer warp converts the activations of ITS OWN K-slices (its block pairs of every column chunk: at most 96 tasks =
-// three rounds of 32 lanes) and nobody else reads them in the stage loop, so a warp starts multiplying as soon as its own slice of
+// Every consumer warp converts the activations of ITS OWN K-slices (its block pairs of every column chunk: at most 128 tasks =
+// four rounds of 32 lanes) and nobody else reads them in the stage loop, so a warp starts multiplying as soon as its own slice of
 // the mailbox has arrived: no CTA-wide barrier between the hand-off and the first MMA, and a late CTA of the previous phase
 // holds up only the warps whose slice it produces.  Everything a phase leaves in the header for its epilogue (range flags,
 // sum-of-squares partials) and the partial-sum buffer are double-buffered by phase parity, because a fast warp is already in

@@ -100,7 +100,7 @@ cudaError_t launch_gemv_chain(int type, int n, const GemvChainLink *links, const
 // on K-slices); Q4_0, K % 256 == 0.  cudaErrorNotSupported for everything else: the caller then takes launch_gemv_chain.
 // bar: the same three words as launch_gemv_chain (the 64-bit counter doubles as the launch's epoch source); mbox: zero-initialised
 // device scratch of GEMV_MCHAIN_MBOX_BYTES owned by the context (activations handed from phase to phase as (value, epoch) pairs).
-constexpr int GEMV_MCHAIN_KMAX = 12288;
+constexpr int GEMV_MCHAIN_KMAX = 16384;
 constexpr size_t GEMV_MCHAIN_MBOX_BYTES = 2 * (size_t)GEMV_MCHAIN_KMAX * 8;
 constexpr size_t CHAIN_SCRATCH_BYTES = 256 + GEMV_MCHAIN_MBOX_BYTES;      // the context's chain words, then the mailbox
 cudaError_t launch_gemv_mchain(int type, int n, const GemvChainLink *links, const GemvTuning &tune, int sm_count,

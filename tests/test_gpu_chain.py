@@ -379,3 +379,41 @@ def test_mchain_fewer_rows_than_ctas_and_ragged_shares(O, M):
     assert_matmul_parity(O, Q4_0, w1, K, K, x0, 1, ga.getFloats(y1), tag="link 0")
     assert_matmul_parity(O, Q4_0, w2, K, M, ga.getFloats(y1), 1, ga.getFloats(y2), tag=f"link 1, M = {M}")
     be.free()
+
+
+@pytest.mark.parametrize("tname", ["Q4_0", "Q4_1"])
+def test_mchain_llama_13b_shapes(O, tname):
+    """hidden 5120, FFN 13824 (Llama-2-13B): K = 13824 is beyond K1c's 12288, K1m stages such rows as column chunks.  Gate/up
+    + SwiGLU -> down + residual against the separate launches and, for the down projection, against the oracle."""
+    gt, ot = QT[tname]
+    hidden, ffn = 5120, 13824
+    be = lk.GGMLCudaBackend(0)
+    ga = lk.GGMLGraphAllocator(be, size=3 * hidden * ffn // 32 * BB[tname] + 64 * (hidden + ffn) * 4 + (1 << 20))
+    dev = _dev(ga)
+    wd = O.quantize(ot, synth_weights(7802, hidden, ffn))
+    Wg = dev(gt, [hidden, ffn], O.quantize(ot, synth_weights(7800, ffn, hidden)))
+    Wu = dev(gt, [hidden, ffn], O.quantize(ot, synth_weights(7801, ffn, hidden)))
+    Wd = dev(gt, [ffn, hidden], wd)
+    x = dev(GGMLType.F32, [1, hidden], synth_acts(7803, hidden))
+    res = dev(GGMLType.F32, [hidden], synth_acts(7804, hidden))
+
+    def run(chain):
+        z = lambda n, flat=False: dev(GGMLType.F32, [n] if flat else [1, n], np.zeros(n, np.float32))   # noqa: E731
+        g, u, h, y, s = z(ffn), z(ffn), z(ffn, True), z(hidden), z(hidden, True)
+        hb = GGMLTensor(GGMLType.F32, [1, ffn], bufferId=h.bufferId, dataOffset=h.dataOffset, buffer=h.buffer)
+        ls = [(Wg, x, g, dict(extra=[(Wu, u)], mul_dst=h)), (Wd, hb, y, dict(residual=res, sum_dst=s))]
+        if chain:
+            m0 = be.lk.get_option("gemv_chain_mma_launches")
+            assert computeMatMulChain(ga, None, ls)
+            be.lk.sync()
+            assert be.lk.get_option("gemv_chain_mma_launches") == m0 + 1 and be.lk.get_option("gemv_chain_timeouts") == 0
+        else:
+            for a, b, d, kw in ls:
+                assert lk.computeMatMulFused(ga, None, a, b, d, **kw)
+            be.lk.sync()
+        return [ga.getFloats(t) for t in (g, u, h, y, s)]
+    one, ch = run(False), run(True)
+    for a, b in zip(ch, one):
+        assert rel_err(a, b) <= CHAIN_ORDER_TOL
+    assert_matmul_parity(O, ot, wd, ffn, hidden, ch[2], 1, ch[3], tag="13B down projection on K1m")
+    be.free()

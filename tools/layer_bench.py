@@ -79,7 +79,7 @@ def run(lk, be, qtype: str = "Q4_0", layers: int = 32, steps: int = 50, warmup: 
     y = ga.getFloats(out)
     be.forgetGraph(graph)                 # the capture keeps the graph (and through it this allocator's memory) alive
     kv_read = 2 * ctx_len * hidden * 4
-    res = {"workload": f"synthetic Llama-2-7B decoder stack, {qtype}, batch 1, " +
+    res = {"workload": f"synthetic Llama-2-{'7B' if (hidden, ffn) == (4096, 11008) else f'shaped ({hidden} / {ffn})'} decoder stack, {qtype}, batch 1, " +
                        (f"RoPE + KV cache + decode attention over {ctx_len} positions ({heads} heads), " if ctx_len else "one-position context, ") +
                        f"{layers} layers with distinct weights ({layers * wbytes / 1e9:.2f} GB > L2), {18 if ctx_len else 13} graph nodes per layer",
            "ctx_len": ctx_len, "kv_bytes_read_per_layer": kv_read, "launches_per_token": int(launches),
@@ -101,6 +101,9 @@ def main():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--opt", action="append")
     ap.add_argument("--ctx", type=int, default=0, help="context length: > 0 runs the layer with RoPE, KV cache and decode attention")
+    ap.add_argument("--hidden", type=int, default=4096)
+    ap.add_argument("--ffn", type=int, default=11008)
+    ap.add_argument("--heads", type=int, default=32)
     ap.add_argument("--drop", nargs="*", default=[], help="op names to leave out (timing experiments), e.g. RMS_NORM ADD")
     args = ap.parse_args()
     import llama_kotlin_b200 as lk
@@ -119,7 +122,8 @@ def main():
         peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", 0))
     except Exception:
         pass
-    res = run(lk, be, args.qtype, args.layers, args.steps, hbm_peak_gbs=peak, drop_ops=tuple(args.drop), ctx_len=args.ctx)
+    res = run(lk, be, args.qtype, args.layers, args.steps, hbm_peak_gbs=peak, drop_ops=tuple(args.drop), ctx_len=args.ctx,
+              hidden=args.hidden, ffn=args.ffn, heads=args.heads)
     if args.drop:
         res["dropped_ops"] = args.drop
     print(json.dumps(res), flush=True)
